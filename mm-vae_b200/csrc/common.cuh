@@ -1,0 +1,145 @@
+// Shared device/host helpers for the mm-vae B200 kernels (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+namespace mmv {
+
+constexpr int kWarp = 32;
+
+// ---------------------------------------------------------------------------
+// error plumbing: every C-ABI entry returns 0 (EXIT_SUCCESS) or nonzero and
+// leaves a message retrievable through mmv_last_error (util.hh:35-80 keeps the
+// reference's "ELOG + EXIT_FAILURE" convention on the host side).
+// ---------------------------------------------------------------------------
+void set_error(const char *fmt, ...);
+const char *get_error();
+
+#define MMV_CUDA(expr)                                                           \
+    do {                                                                         \
+        cudaError_t _e = (expr);                                                 \
+        if (_e != cudaSuccess) {                                                 \
+            ::mmv::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr,       \
+                             cudaGetErrorString(_e));                            \
+            return 1;                                                            \
+        }                                                                        \
+    } while (0)
+
+#define MMV_CHECK(cond, ...)                 \
+    do {                                     \
+        if (!(cond)) {                       \
+            ::mmv::set_error(__VA_ARGS__);   \
+            return 1;                        \
+        }                                    \
+    } while (0)
+
+#define MMV_TRY(expr)            \
+    do {                         \
+        int _rc = (expr);        \
+        if (_rc != 0) return _rc; \
+    } while (0)
+
+inline size_t
+min_sz(size_t a, size_t b)
+{
+    return a < b ? a : b;
+}
+
+inline int
+ceil_div(int64_t a, int64_t b)
+{
+    return (int)((a + b - 1) / b);
+}
+
+// ---------------------------------------------------------------------------
+// device math.  Accurate libdevice versions on purpose: parity with the
+// reference's fp32 ATen ops is 1e-4 relative (BASELINE.json north_star).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float
+softplus_f(float x)
+{   // libtorch softplus, beta=1, threshold=20
+    return x > 20.f ? x : log1pf(expf(x));
+}
+
+__device__ __forceinline__ float
+sigmoid_f(float x)
+{
+    return 1.f / (1.f + expf(-x));
+}
+
+// digamma for x > 0: recurrence up to x >= 6, then the asymptotic series.
+__device__ __forceinline__ float
+digamma_f(float x)
+{
+    float acc = 0.f;
+    while (x < 6.f) {
+        acc -= 1.f / x;
+        x += 1.f;
+    }
+    const float r = 1.f / x, r2 = r * r;
+    // ln x - 1/(2x) - 1/(12x^2) + 1/(120x^4) - 1/(252x^6) + 1/(240x^8)
+    const float s = r2 * (1.f / 12.f - r2 * (1.f / 120.f - r2 * (1.f / 252.f - r2 * (1.f / 240.f))));
+    return acc + logf(x) - 0.5f * r - s;
+}
+
+// ---------------------------------------------------------------------------
+// warp / block reductions
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float
+warp_sum(float v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ float
+warp_max(float v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Block-wide sum of N values per thread; result valid in ALL threads.
+// `scratch` must hold N * 32 floats. Contains two __syncthreads.
+template <int N>
+__device__ __forceinline__ void
+block_sum(float (&v)[N], float *scratch)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nwarp = (blockDim.x + 31) >> 5;
+#pragma unroll
+    for (int k = 0; k < N; ++k) v[k] = warp_sum(v[k]);
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < N; ++k) scratch[k * 32 + warp] = v[k];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+        float t = lane < nwarp ? scratch[k * 32 + lane] : 0.f;
+        v[k] = warp_sum(t);
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float
+block_max(float v, float *scratch)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nwarp = (blockDim.x + 31) >> 5;
+    v = warp_max(v);
+    if (lane == 0) scratch[warp] = v;
+    __syncthreads();
+    float t = lane < nwarp ? scratch[lane] : -INFINITY;
+    v = warp_max(t);
+    __syncthreads();
+    return v;
+}
+
+} // namespace mmv

@@ -1,0 +1,244 @@
+// Device context, resident CSR storage, timers, error string — the plumbing
+// half of the C ABI declared in include/mmvae_b200.h.
+#include "common.cuh"
+#include "internal.hh"
+
+#include <cstdarg>
+#include <vector>
+
+namespace mmv {
+
+static thread_local char g_err[1024] = "";
+
+void
+set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+const char *
+get_error()
+{
+    return g_err;
+}
+
+} // namespace mmv
+
+using namespace mmv;
+
+extern "C" {
+
+const char *
+mmv_last_error(void)
+{
+    return get_error();
+}
+
+int
+mmv_ctx_create(int device, mmv_ctx **out)
+{
+    MMV_CHECK(out != nullptr, "mmv_ctx_create: out is NULL");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    MMV_CHECK(e == cudaSuccess && ndev > 0,
+              "mmv_ctx_create: no CUDA device (%s); this library has no CPU fallback",
+              e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    MMV_CHECK(device >= 0 && device < ndev, "mmv_ctx_create: device %d out of range [0,%d)", device, ndev);
+    MMV_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    MMV_CUDA(cudaGetDeviceProperties(&prop, device));
+    MMV_CHECK(prop.major == 10, "mmv_ctx_create: built for sm_100a (B200), found sm_%d%d", prop.major, prop.minor);
+    mmv_ctx *c = new mmv_ctx();
+    c->device = device;
+    c->num_sms = prop.multiProcessorCount;
+    MMV_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    MMV_CUDA(cudaEventCreate(&c->ev0));
+    MMV_CUDA(cudaEventCreate(&c->ev1));
+    *out = c;
+    return 0;
+}
+
+int
+mmv_ctx_destroy(mmv_ctx *c)
+{
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    mmv_comm_destroy(c);
+    cudaStreamSynchronize(c->stream);
+    cudaEventDestroy(c->ev0);
+    cudaEventDestroy(c->ev1);
+    cudaStreamDestroy(c->stream);
+    delete c;
+    return 0;
+}
+
+int
+mmv_ctx_sync(mmv_ctx *c)
+{
+    MMV_CHECK(c, "mmv_ctx_sync: NULL ctx");
+    MMV_CUDA(cudaSetDevice(c->device));
+    MMV_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int
+mmv_ctx_num_sms(mmv_ctx *c, int *out)
+{
+    MMV_CHECK(c && out, "mmv_ctx_num_sms: NULL");
+    *out = c->num_sms;
+    return 0;
+}
+
+int
+mmv_timer_start(mmv_ctx *c)
+{
+    MMV_CHECK(c, "mmv_timer_start: NULL ctx");
+    MMV_CUDA(cudaSetDevice(c->device));
+    MMV_CUDA(cudaEventRecord(c->ev0, c->stream));
+    return 0;
+}
+
+int
+mmv_timer_stop(mmv_ctx *c, float *ms)
+{
+    MMV_CHECK(c && ms, "mmv_timer_stop: NULL");
+    MMV_CUDA(cudaSetDevice(c->device));
+    MMV_CUDA(cudaEventRecord(c->ev1, c->stream));
+    MMV_CUDA(cudaEventSynchronize(c->ev1));
+    MMV_CUDA(cudaEventElapsedTime(ms, c->ev0, c->ev1));
+    return 0;
+}
+
+int
+mmv_host_alloc(void **out, int64_t bytes)
+{
+    MMV_CHECK(out && bytes >= 0, "mmv_host_alloc: bad arguments");
+    MMV_CUDA(cudaMallocHost(out, (size_t)(bytes > 0 ? bytes : 1)));
+    return 0;
+}
+
+int
+mmv_host_free(void *p)
+{
+    if (p) MMV_CUDA(cudaFreeHost(p));
+    return 0;
+}
+
+// ------------------------------------------------------------------ CSR
+static int
+csr_validate(int64_t n_cells, int64_t n_genes, const int64_t *indptr, const int32_t *indices, int64_t *max_row,
+             bool check_indices)
+{
+    MMV_CHECK(indptr[0] == 0, "csr: indptr[0] must be 0");
+    int64_t mx = 0;
+    for (int64_t i = 0; i < n_cells; ++i) {
+        const int64_t len = indptr[i + 1] - indptr[i];
+        MMV_CHECK(len >= 0, "csr: indptr not monotone at cell %ld", (long)i);
+        if (len > mx) mx = len;
+    }
+    const int64_t nnz = indptr[n_cells];
+    for (int64_t k = 0; check_indices && k < nnz; ++k)   // the reference does NOT check rows; we do
+        MMV_CHECK(indices[k] >= 0 && indices[k] < n_genes, "csr: gene index %d out of range [0,%ld)",
+                  indices[k], (long)n_genes);
+    *max_row = mx;
+    return 0;
+}
+
+int
+mmv_csr_create(mmv_ctx *ctx, int64_t max_cells, int64_t max_nnz, int64_t n_genes, int64_t c_dim, mmv_csr **out)
+{
+    MMV_CHECK(ctx && out, "mmv_csr_create: NULL");
+    MMV_CHECK(max_cells > 0 && n_genes > 0 && max_nnz >= 0 && c_dim >= 0, "mmv_csr_create: bad sizes");
+    MMV_CHECK(n_genes < (1LL << 31), "mmv_csr_create: n_genes must fit int32");
+    MMV_CUDA(cudaSetDevice(ctx->device));
+    mmv_csr *s = new mmv_csr();
+    s->ctx = ctx;
+    s->cap_cells = max_cells;
+    s->cap_nnz = max_nnz;
+    s->n_genes = n_genes;
+    s->c_dim = c_dim;
+    MMV_CUDA(cudaMalloc(&s->indptr, sizeof(int64_t) * (max_cells + 1)));
+    MMV_CUDA(cudaMalloc(&s->indices, sizeof(int32_t) * (max_nnz > 0 ? max_nnz : 1)));
+    MMV_CUDA(cudaMalloc(&s->vals, sizeof(float) * (max_nnz > 0 ? max_nnz : 1)));
+    if (c_dim > 0) MMV_CUDA(cudaMalloc(&s->cov, sizeof(float) * max_cells * c_dim));
+    *out = s;
+    return 0;
+}
+
+static int
+csr_update_impl(mmv_csr *s, int64_t n_cells, const int64_t *indptr, const int32_t *indices, const float *values,
+                const float *covar, bool check_indices)
+{
+    MMV_CHECK(s && indptr && (indices || indptr[n_cells] == 0) && (values || indptr[n_cells] == 0),
+              "mmv_csr_update: NULL");
+    MMV_CHECK(n_cells > 0 && n_cells <= s->cap_cells, "mmv_csr_update: %ld cells exceed capacity %ld",
+              (long)n_cells, (long)s->cap_cells);
+    const int64_t nnz = indptr[n_cells];
+    MMV_CHECK(nnz <= s->cap_nnz, "mmv_csr_update: %ld nonzeros exceed capacity %ld", (long)nnz, (long)s->cap_nnz);
+    int64_t mx = 0;
+    MMV_TRY(csr_validate(n_cells, s->n_genes, indptr, indices, &mx, check_indices));
+    cudaStream_t st = s->ctx->stream;
+    MMV_CUDA(cudaSetDevice(s->ctx->device));
+    MMV_CUDA(cudaMemcpyAsync(s->indptr, indptr, sizeof(int64_t) * (n_cells + 1), cudaMemcpyHostToDevice, st));
+    if (nnz > 0) {
+        MMV_CUDA(cudaMemcpyAsync(s->indices, indices, sizeof(int32_t) * nnz, cudaMemcpyHostToDevice, st));
+        MMV_CUDA(cudaMemcpyAsync(s->vals, values, sizeof(float) * nnz, cudaMemcpyHostToDevice, st));
+    }
+    s->has_cov = covar != nullptr;
+    if (covar) {
+        MMV_CHECK(s->c_dim > 0, "mmv_csr_update: covariates given but c_dim = 0");
+        MMV_CUDA(cudaMemcpyAsync(s->cov, covar, sizeof(float) * n_cells * s->c_dim, cudaMemcpyHostToDevice, st));
+    }
+    s->n_cells = n_cells;
+    s->nnz = nnz;
+    if (mx > s->max_row_nnz) s->max_row_nnz = mx;
+    s->h2d_bytes = sizeof(int64_t) * (n_cells + 1) + 8 * nnz + (covar ? sizeof(float) * n_cells * s->c_dim : 0);
+    return 0;
+}
+
+// Streaming path: gene ids are range-checked once per resident upload only; a
+// per-minibatch host scan of the nonzeros would cost more than the step itself.
+int
+mmv_csr_update(mmv_csr *s, int64_t n_cells, const int64_t *indptr, const int32_t *indices, const float *values,
+               const float *covar)
+{
+    return csr_update_impl(s, n_cells, indptr, indices, values, covar, false);
+}
+
+int
+mmv_csr_upload(mmv_ctx *ctx, int64_t n_cells, int64_t n_genes, const int64_t *indptr, const int32_t *indices,
+               const float *values, const float *covar, int64_t c_dim, mmv_csr **out)
+{
+    MMV_CHECK(ctx && indptr && out, "mmv_csr_upload: NULL");
+    MMV_CHECK(n_cells > 0, "mmv_csr_upload: empty matrix");
+    mmv_csr *s = nullptr;
+    MMV_TRY(mmv_csr_create(ctx, n_cells, indptr[n_cells], n_genes, covar ? c_dim : 0, &s));
+    if (!covar) s->c_dim = c_dim > 0 ? c_dim : 1;
+    int rc = csr_update_impl(s, n_cells, indptr, indices, values, covar, true);
+    if (rc == 0) rc = mmv_ctx_sync(ctx);   // host arrays are borrowed for the call only
+    if (rc != 0) {
+        mmv_csr_destroy(s);
+        return rc;
+    }
+    *out = s;
+    return 0;
+}
+
+int
+mmv_csr_destroy(mmv_csr *s)
+{
+    if (!s) return 0;
+    cudaSetDevice(s->ctx->device);
+    cudaStreamSynchronize(s->ctx->stream);
+    cudaFree(s->indptr);
+    cudaFree(s->indices);
+    cudaFree(s->vals);
+    cudaFree(s->cov);
+    delete s;
+    return 0;
+}
+
+} // extern "C"

@@ -1,0 +1,177 @@
+// K3 and small helpers: per-gene parameter prep, Gaussian reparameterisation +
+// KL (forward and backward), column sums, ReLU mask, Angular weight
+// normalisation (forward/backward).
+//
+// Reference call sites: reparameterize nb.hh:462-472 / vmf.hh:394-404,
+// kl_loss nb.hh:533-537 / vmf.hh:410-414, clamp(lnvar,-4,4) nb.hh:414,449 /
+// vmf.hh:262, covar_enc nb.hh:412 / vmf.hh:261, softplus(ln_x_sd)+eps
+// nb.hh:408-410 / vmf.hh:258, Angular angular.hh:34-42.
+#include "common.cuh"
+#include "kernels.hh"
+
+namespace mmv {
+
+// inv_t[j] = 1 / (softplus(ln_x_sd_j) + eps);  out = a + b + c (nullable) element-wise
+__global__ void
+gene_prep_kernel(const float *ln_x_sd, float eps, float *inv_t, int D)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < D) inv_t[j] = 1.f / (softplus_f(ln_x_sd[j]) + eps);
+}
+
+__global__ void
+vec_combine_kernel(const float *a, const float *b, const float *c, float sb, float sc, float *out, int n)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n) out[j] = (a ? a[j] : 0.f) + (b ? sb * b[j] : 0.f) + (c ? sc * c[j] : 0.f);
+}
+
+int
+launch_gene_prep(const float *ln_x_sd, float eps, float *inv_t, int D, cudaStream_t st)
+{
+    gene_prep_kernel<<<ceil_div(D, 256), 256, 0, st>>>(ln_x_sd, eps, inv_t, D);
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int
+launch_vec_combine(const float *a, const float *b, const float *c, float sb, float sc, float *out, int n,
+                   cudaStream_t st)
+{
+    vec_combine_kernel<<<ceil_div(n, 256), 256, 0, st>>>(a, b, c, sb, sc, out, n);
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------- reparam + KL
+// head = [mean_raw | lnvar_raw]  (B x 2R, from the stacked representation heads)
+__global__ void
+reparam_fwd_kernel(reparam_args_t a)
+{
+    const int R = a.R, n = a.B * R;
+    float kl = 0.f;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
+        const int i = idx / R, r = idx % R;
+        float mean = a.head[(size_t)i * 2 * R + r];
+        if (a.Wce) {   // + covar_enc(c)  (nb.hh:412,416)
+            const int64_t cell = a.cells ? (int64_t)a.cells[i] : (int64_t)i;
+            float hc = a.bce[r];
+            for (int c = 0; c < a.C; ++c)
+                hc = fmaf(a.cov ? a.cov[cell * a.C + c] : 1.f, a.Wce[r * a.C + c], hc);
+            mean += hc;
+        }
+        const float raw = a.head[(size_t)i * 2 * R + R + r];
+        const float lv = fminf(fmaxf(raw, -4.f), 4.f);
+        const float ev = expf(lv);
+        float z = mean;
+        if (a.eps) z = fmaf(a.eps[idx], expf(0.5f * lv), mean);   // nb.hh:466-468
+        a.mean[idx] = mean;
+        a.lnvar[idx] = lv;
+        a.z[idx] = z;
+        kl += 1.f + lv - mean * mean - ev;                        // nb.hh:536
+    }
+    __shared__ float scratch[32];
+    float k1[1] = { kl };
+    block_sum<1>(k1, scratch);
+    if (threadIdx.x == 0 && a.kl_acc) atomicAdd(a.kl_acc, (double)(-0.5f * k1[0]));
+}
+
+// dhead = [dmean | dlnvar_raw] given dz; loss = (... + w KL) / B
+__global__ void
+reparam_bwd_kernel(reparam_args_t a)
+{
+    const int R = a.R, n = a.B * R;
+    const float wB = a.kl_weight * a.inv_B;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
+        const int i = idx / R, r = idx % R;
+        const float dz = a.dz[idx];
+        const float mean = a.mean[idx], lv = a.lnvar[idx];
+        const float raw = a.head[(size_t)i * 2 * R + R + r];
+        const float dmean = fmaf(wB, mean, dz);
+        float dlv = -0.5f * wB * (1.f - expf(lv));
+        if (a.eps) dlv = fmaf(dz * 0.5f * a.eps[idx], expf(0.5f * lv), dlv);
+        if (!(raw >= -4.f && raw <= 4.f)) dlv = 0.f;              // clamp backward (inclusive)
+        a.dhead[(size_t)i * 2 * R + r] = dmean;
+        a.dhead[(size_t)i * 2 * R + R + r] = dlv;
+    }
+}
+
+int
+launch_reparam_fwd(const reparam_args_t &a, cudaStream_t st)
+{
+    const int n = a.B * a.R;
+    reparam_fwd_kernel<<<min(ceil_div(n, 256), 1024), 256, 0, st>>>(a);
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int
+launch_reparam_bwd(const reparam_args_t &a, cudaStream_t st)
+{
+    const int n = a.B * a.R;
+    reparam_bwd_kernel<<<min(ceil_div(n, 256), 1024), 256, 0, st>>>(a);
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ------------------------------------------------------------------ column sums
+// out[col * (1 + C) + 0]     += sum_i X[i, col]
+// out[col * (1 + C) + 1 + c] += sum_i X[i, col] * cov[cell_i, c]      (C may be 0)
+// The two destinations are separate arrays: out_sum[N] and out_cov[N x C].
+__global__ void
+colsum_kernel(colsum_args_t a)
+{
+    const int col = blockIdx.x * blockDim.x + threadIdx.x;
+    const int r0 = blockIdx.y * a.rows_per_cta, r1 = min(a.M, r0 + a.rows_per_cta);
+    if (col >= a.N) return;
+    float s = 0.f;
+    float sc[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) sc[c] = 0.f;
+    for (int i = r0; i < r1; ++i) {
+        const float v = a.X[(size_t)i * a.ldx + col];
+        s += v;
+        if (a.out_cov) {
+            const int64_t cell = a.cells ? (int64_t)a.cells[i] : (int64_t)i;
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                if (c < a.C) sc[c] = fmaf(v, a.cov ? a.cov[cell * a.C + c] : 1.f, sc[c]);
+        }
+    }
+    if (a.out_sum) atomicAdd(a.out_sum + col, s);
+    if (a.out_sum2) atomicAdd(a.out_sum2 + col, s);
+    if (a.out_sum3) atomicAdd(a.out_sum3 + col, s);
+    if (a.out_cov)
+        for (int c = 0; c < a.C; ++c) atomicAdd(a.out_cov + (size_t)col * a.C + c, sc[c]);
+}
+
+int
+launch_colsum(colsum_args_t a, cudaStream_t st)
+{
+    if (a.M <= 0 || a.N <= 0) return 0;
+    MMV_CHECK(a.C <= 8, "colsum: covariate dim %d > 8 not supported", a.C);
+    a.rows_per_cta = 64;
+    dim3 grid(ceil_div(a.N, 128), ceil_div(a.M, a.rows_per_cta));
+    colsum_kernel<<<grid, 128, 0, st>>>(a);
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ------------------------------------------------------------------- ReLU mask
+__global__ void
+relu_bwd_kernel(float *dX, const float *Y, size_t n)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        if (!(Y[i] > 0.f)) dX[i] = 0.f;
+}
+
+int
+launch_relu_bwd(float *dX, const float *Y, size_t n, cudaStream_t st)
+{
+    if (n == 0) return 0;
+    relu_bwd_kernel<<<(int)min_sz((n + 255) / 256, 4096), 256, 0, st>>>(dX, Y, n);
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+} // namespace mmv

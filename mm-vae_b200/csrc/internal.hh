@@ -1,0 +1,40 @@
+// Definitions of the opaque C-ABI handles (not installed; include/mmvae_b200.h
+// is the public face).
+#pragma once
+
+#include "../../include/mmvae_b200.h"
+#include "kernels.hh"
+
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+
+struct mmv_ctx {
+    int device = 0;
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // NCCL data-parallel state (comm.cu)
+    void *nccl_comm = nullptr;
+    int nranks = 1, rank = 0;
+};
+
+struct mmv_csr {
+    mmv_ctx *ctx = nullptr;
+    int64_t n_cells = 0, n_genes = 0, nnz = 0, c_dim = 0;
+    int64_t cap_cells = 0, cap_nnz = 0, max_row_nnz = 0;
+    int64_t *indptr = nullptr;
+    int32_t *indices = nullptr;
+    float *vals = nullptr;
+    float *cov = nullptr;      // [n_cells x c_dim]; nullptr / !has_cov = all ones
+    bool has_cov = false;
+    size_t h2d_bytes = 0;      // bytes copied by the last update (bench accounting)
+};
+
+namespace mmv {
+
+// comm.cu: sum-reduce over ranks on the ctx stream (no-ops when nranks == 1)
+int comm_allreduce_f32(mmv_ctx *ctx, float *buf, size_t n);
+int comm_allreduce_f64(mmv_ctx *ctx, double *buf, size_t n);
+
+} // namespace mmv

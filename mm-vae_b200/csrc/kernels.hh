@@ -1,0 +1,199 @@
+// Internal launcher interface between the C-ABI layer (model.cu) and the
+// sm_100a kernels.  Plain structs of device pointers; every launcher returns 0
+// or nonzero (message via mmv::get_error()).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cstddef>
+#include <cstdint>
+
+namespace mmv {
+
+// ---- K2 fp32 GEMM (gemm_f32.cu)
+struct gemm_args_t {
+    const float *A = nullptr, *B = nullptr;
+    float *C = nullptr;
+    const float *bias = nullptr;   // [N], added after alpha*AB + beta*C
+    int M = 0, N = 0, K = 0;
+    int lda = 0, ldb = 0, ldc = 0;
+    int transA = 0, transB = 0;
+    float alpha = 1.f, beta = 0.f;
+    int relu = 0;
+};
+int launch_gemm_f32(const gemm_args_t &g, cudaStream_t stream);
+
+// ---- K1 sparse encoder (sparse_encoder.cu)
+struct senc_args_t {
+    const int64_t *indptr = nullptr;
+    const int32_t *indices = nullptr;
+    const float *vals = nullptr;
+    const int32_t *cells = nullptr;   // [B] cell id per minibatch row (nullptr: identity)
+    int B = 0, D = 0;
+    int angular = 0;                  // 0: nb (Linear), 1: vmf (Angular + row L2 of log1p)
+    const float *W1T = nullptr;       // [D x h1]
+    int h1 = 0;
+    const float *inv_t = nullptr;     // [D]
+    const float *bias_eff = nullptr;  // [h1]
+    const float *col_scale = nullptr; // [h1] (angular)
+    int relu = 0;
+    float *H1 = nullptr;              // [B x h1]
+    const float *WnuT = nullptr;      // [D x H] (nb)
+    const float *bnu = nullptr;       // [H]
+    int H = 0;
+    const float *wdepth = nullptr;    // [D]
+    const float *bdepth = nullptr;    // [1]
+    float *Hnu = nullptr;             // [B x H]
+    float *dpre = nullptr;            // [B]
+    float *rownorm = nullptr;         // [B] (angular)
+};
+int launch_senc_fwd(const senc_args_t &a, cudaStream_t st);
+int launch_senc_bias(const float *W1T, const float *x_mean, const float *inv_t, const float *col_scale,
+                     float *bias_eff, int D, int h1, int angular, cudaStream_t st);
+
+struct batch_csc_args_t {
+    const int64_t *indptr = nullptr;
+    const int32_t *indices = nullptr;
+    const float *vals = nullptr;
+    const int32_t *cells = nullptr;
+    const float *rownorm = nullptr;   // vmf: entries are log1p(x) / ||log1p(x_i)||
+    int B = 0, D = 0;
+    int *counts = nullptr, *gene_ptr = nullptr, *cursor = nullptr;   // [D], [D+1], [D]
+    int *ent_row = nullptr;
+    float *ent_l = nullptr, *ent_x = nullptr;
+};
+int launch_batch_csc(const batch_csc_args_t &c, cudaStream_t st);
+
+struct senc_bwd_args_t {
+    const int *gene_ptr = nullptr, *ent_row = nullptr;
+    const float *ent_l = nullptr, *ent_x = nullptr;
+    int D = 0, h1 = 0, H = 0;
+    int angular = 0, accumulate = 1;
+    const float *delta = nullptr;     // [B x h1] dL/d(first-layer pre-activation)
+    const float *Delta = nullptr;     // [h1] column sums of delta
+    const float *W1T = nullptr, *col_scale = nullptr;
+    const float *inv_t = nullptr, *x_mean = nullptr, *ln_x_sd = nullptr;
+    float *dW1T = nullptr;            // [D x h1] gradient w.r.t. the EFFECTIVE weight
+    float *dx_mean = nullptr, *dln_x_sd = nullptr;
+    const float *dHnu = nullptr;      // [B x H]
+    const float *ddpre = nullptr;     // [B]
+    float *dWnuT = nullptr;           // [D x H]
+    float *dwdepth = nullptr;         // [D]
+};
+int launch_senc_bwd(const senc_bwd_args_t &a, cudaStream_t st);
+
+// ---- K4 NB likelihood (nb_likelihood.cu)
+struct nb_lik_args_t {
+    const float *G = nullptr;         // [B x D] last decoder layer output WITHOUT bias
+    const float *abias = nullptr;     // [D] mu_decoding.bias + covar_decoding.bias + mu_bias
+    const float *Wcd = nullptr;       // [D x C] covar_decoding.weight
+    const float *cov = nullptr;       // [n_cells x C] covariates (nullptr: ones)
+    const int64_t *indptr = nullptr;
+    const int32_t *indices = nullptr;
+    const float *vals = nullptr;
+    const int32_t *cells = nullptr;
+    const float *dpre = nullptr;      // [B] depth pre-activation
+    const float *znu = nullptr;       // [B x Rnu]
+    const float *Wnd = nullptr;       // [D x Rnu] nu_decoding.weight
+    const float *ubias = nullptr;     // [D] nu_decoding.bias - nu_bias
+    int B = 0, D = 0, C = 0, Rnu = 0;
+    float inv_B = 0.f;
+    float *dlogits = nullptr;         // [B x D]  (nullptr: forward only)
+    float *ddpre = nullptr;           // [B]
+    float *dznu = nullptr;            // [B x Rnu]
+    float *col_du = nullptr;          // [D]       += sum_i du_ij
+    float *col_duz = nullptr;         // [D x Rnu] += sum_i du_ij znu_ir
+    double *loss_acc = nullptr;       // += sum_ij nllik
+    float *recon_mu = nullptr, *recon_nu = nullptr;   // optional [B x D] (tests)
+    float *row_lse = nullptr;         // optional [B]
+};
+int launch_nb_likelihood(const nb_lik_args_t &a, int num_sms, cudaStream_t stream);
+
+// ---- K5 vMF likelihood (vmf_likelihood.cu)
+struct vmf_lik_args_t {
+    const float *G = nullptr;         // [B x D] last decoder layer output WITHOUT bias
+    const float *blast = nullptr;     // [D] decoding.bias
+    const float *Wcd = nullptr, *bcd = nullptr;   // covar_decoding_ [D x C], [D]
+    const float *cov = nullptr;
+    const int64_t *indptr = nullptr;
+    const int32_t *indices = nullptr;
+    const float *vals = nullptr;
+    const int32_t *cells = nullptr;
+    const float *kappa = nullptr;     // device scalar
+    int B = 0, D = 0, C = 0;
+    float inv_B = 0.f, eps_obs = 0.f;
+    float *dpre = nullptr;            // [B x D] (nullptr: forward only)
+    float *col_dq = nullptr;          // [D]
+    float *col_dqc = nullptr;         // [D x C]
+    double *t_acc = nullptr;          // += sum_i <yobs_i, recon_i>
+    float *recon = nullptr;           // optional [B x D]
+    float *row_t = nullptr;           // optional [B]
+};
+int launch_vmf_likelihood(const vmf_lik_args_t &a, int num_sms, cudaStream_t stream);
+
+struct vmf_scalar_args_t {
+    const float *kappa = nullptr, *ln_kappa = nullptr;
+    const double *t_acc = nullptr;
+    double *llik_sum = nullptr;
+    float *dln_kappa = nullptr;
+    int B = 0;                        // cells of THIS rank
+    float inv_B_global = 0.f, inv_ranks = 1.f;
+    float df = 0.f, eta = 0.f, kmin = 0.f, kmax = 0.f;
+    float c_eta_nu_log2 = 0.f, c_fasterlgamma = 0.f, c_half_log_2pi = 0.f, c_half_D_fasterlog_2pi = 0.f;
+};
+int launch_vmf_kappa(const float *ln_kappa, float kmin, float kmax, float *kappa, cudaStream_t st);
+int launch_vmf_scalar(const vmf_scalar_args_t &s, cudaStream_t st);
+
+// ---- K3 + helpers (elementwise.cu)
+int launch_gene_prep(const float *ln_x_sd, float eps, float *inv_t, int D, cudaStream_t st);
+int launch_vec_combine(const float *a, const float *b, const float *c, float sb, float sc, float *out, int n,
+                       cudaStream_t st);
+
+struct reparam_args_t {
+    const float *head = nullptr;      // [B x 2R] mean_raw | lnvar_raw
+    const float *Wce = nullptr, *bce = nullptr;   // covar_encoding [R x C], [R] (nullable)
+    const float *cov = nullptr;
+    const int32_t *cells = nullptr;
+    const float *eps = nullptr;       // [B x R] injected noise (nullptr: z = mean)
+    int B = 0, R = 0, C = 0;
+    float *mean = nullptr, *lnvar = nullptr, *z = nullptr;   // [B x R]
+    double *kl_acc = nullptr;
+    // backward
+    const float *dz = nullptr;
+    float *dhead = nullptr;
+    float kl_weight = 1.f, inv_B = 0.f;
+};
+int launch_reparam_fwd(const reparam_args_t &a, cudaStream_t st);
+int launch_reparam_bwd(const reparam_args_t &a, cudaStream_t st);
+
+struct colsum_args_t {
+    const float *X = nullptr;
+    int M = 0, N = 0, ldx = 0;
+    float *out_sum = nullptr, *out_sum2 = nullptr, *out_sum3 = nullptr;   // [N] each, +=
+    float *out_cov = nullptr;         // [N x C] += sum_i X[i, col] * cov[cell_i, c]
+    const float *cov = nullptr;
+    const int32_t *cells = nullptr;
+    int C = 0;
+    int rows_per_cta = 64;
+};
+int launch_colsum(colsum_args_t a, cudaStream_t st);
+int launch_relu_bwd(float *dX, const float *Y, size_t n, cudaStream_t st);
+
+// ---- Angular (angular.cu)
+int launch_angular_scale(const float *W, float *scale, int units, int inputs, size_t us, size_t is, cudaStream_t st);
+int launch_angular_materialize(const float *W, const float *scale, float *Wp, int units, int inputs, cudaStream_t st);
+int launch_angular_bwd(const float *W, const float *dWp, const float *scale, float *dot, float *dW,
+                       int units, int inputs, size_t us, size_t is, cudaStream_t st);
+
+// ---- K6 (optim.cu)
+int launch_sumsq(const float *g, size_t n, double *out, int num_sms, cudaStream_t st);
+struct adam_args_t {
+    float *param = nullptr, *grad = nullptr, *m = nullptr, *v = nullptr;
+    size_t n = 0;
+    const double *sumsq = nullptr;
+    float *norm_out = nullptr;
+    float max_norm = 1.f, weight_decay = 1e-4f, beta1 = 0.9f, beta2 = 0.999f, eps = 1e-8f;
+    float bc2_sqrt = 1.f, neg_step = 0.f;
+};
+int launch_adam(const adam_args_t &a, int num_sms, cudaStream_t st);
+
+} // namespace mmv

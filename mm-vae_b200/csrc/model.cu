@@ -1,0 +1,1157 @@
+// Model state + the minibatch ELBO step behind the C ABI (mmv_*_model_create,
+// mmv_step, mmv_encode, parameter access).
+//
+// Mirrors nbvae_tImpl (nb.hh:212-508) and vmf_vae_tImpl (vmf.hh:198-404) as a
+// flat fp32 parameter buffer + a table of named tensors (the reference's
+// named_parameters() keys), and train_vae_model's inner step
+// (mmvae_alg.hh:274-311) as a fixed sequence of kernel launches on one stream.
+#include "common.cuh"
+#include "internal.hh"
+
+#include <algorithm>
+#include <cmath>
+#include <map>
+#include <memory>
+
+using namespace mmv;
+
+namespace {
+
+struct tensor_t {
+    std::string name;
+    int64_t rows = 0, cols = 1;   // libtorch shape (vectors: rows = 1 or n, see `vec`)
+    size_t off = 0;               // offset (floats) in the flat buffers
+    bool registered = true;       // in model->parameters() of the reference
+    bool transposed = false;      // stored [cols x rows] (first-layer weights)
+    size_t numel() const { return (size_t)rows * cols; }
+};
+
+struct linear_t {
+    int in = 0, out = 0;
+    int w = -1, b = -1;           // tensor indices (b = -1: no bias)
+    bool angular = false;
+};
+
+struct dbuf_t {                    // device buffer that grows on demand
+    void *p = nullptr;
+    size_t bytes = 0;
+    int ensure(size_t need)
+    {
+        if (need <= bytes) return 0;
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+        MMV_CUDA(cudaMalloc(&p, need));
+        bytes = need;
+        return 0;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+    }
+    template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+// fastapprox scalars used as HOST constants by the reference's vmf loss
+// (fastlog.h:75-85, fastgamma.h:58-60) — same bit hack.
+float
+fasterlog_host(float x)
+{
+    union { float f; uint32_t i; } vx = { x };
+    float y = (float)vx.i;
+    y *= 8.2629582881927490e-8f;
+    return y - 87.989971088f;
+}
+
+float
+fasterlgamma_host(float x)
+{
+    return -0.0810614667f - x - fasterlog_host(x) + (0.5f + x) * fasterlog_host(1.0f + x);
+}
+
+struct rng_t {   // splitmix64 -> uniform; only the DISTRIBUTION matches libtorch's init
+    uint64_t s;
+    explicit rng_t(uint64_t seed) : s(seed * 0x9E3779B97F4A7C15ull + 0x1234567ull) { }
+    uint64_t next()
+    {
+        uint64_t z = (s += 0x9E3779B97F4A7C15ull);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        return z ^ (z >> 31);
+    }
+    float uniform(float lo, float hi) { return lo + (hi - lo) * (float)((next() >> 11) * (1.0 / 9007199254740992.0)); }
+};
+
+} // namespace
+
+struct mmv_model {
+    mmv_ctx *ctx = nullptr;
+    bool is_vmf = false;
+    int64_t D = 0, C = 1, R = 0, H = 0, Rnu = 0;
+    bool relu = false;
+    float kap_min = 0.1f, kap_max = 10.f;
+
+    std::vector<tensor_t> tensors;
+    std::map<std::string, int> by_name;
+    size_t n_reg = 0, n_all = 0;          // floats in the registered prefix / whole buffer
+    float *params = nullptr, *grads = nullptr, *adam_m = nullptr, *adam_v = nullptr;
+    int64_t adam_t = 0;
+
+    std::vector<linear_t> enc, dec;       // enc[0] = sparse first layer; dec.back() = layer onto D genes
+    int t_x_mean = -1, t_ln_x_sd = -1, t_mu_bias = -1, t_nu_bias = -1, t_ln_kappa = -1;
+    linear_t covar_enc, covar_dec, head_mu, head_nu, nu_enc, nu_dec, depth;   // head_* are the stacked [2R x h] heads
+    int t_head_mu_lv_w = -1, t_head_mu_lv_b = -1, t_head_nu_lv_w = -1, t_head_nu_lv_b = -1;
+
+    // options
+    float lr = 1e-3f, weight_decay = 1e-4f, grad_clip = 1.f;
+    bool train_all = false, frozen_grads = true, debug_outputs = false;
+    uint64_t seed = 0;
+
+    // workspace
+    int64_t cap_B = 0, cap_ent = 0;
+    int64_t last_B = 0;
+    std::map<std::string, dbuf_t> ws;
+    double *acc = nullptr;                // device: [0] nll/-, [1] kl_mu, [2] kl_nu, [3] sumsq, [4] t_acc, [5] llik_sum
+    float *fscal = nullptr;               // device: [0] kappa, [1] grad norm
+    double *h_acc = nullptr;              // pinned mirrors
+    float *h_fscal = nullptr;
+    int32_t *h_cells = nullptr;           // pinned staging
+    float *h_eps = nullptr;
+    size_t h_eps_cap = 0;
+    int64_t h_cells_cap = 0;
+
+    float *P(int t) const { return params + tensors[t].off; }
+    float *G(int t) const { return grads + tensors[t].off; }
+    float *W(const std::string &k, size_t bytes)
+    {
+        dbuf_t &b = ws[k];
+        if (b.ensure(bytes) != 0) return nullptr;
+        return b.as<float>();
+    }
+    bool optimised(int t) const { return train_all || tensors[t].registered; }
+    bool want_grad(int t) const { return optimised(t) || frozen_grads; }
+};
+
+namespace {
+
+int
+add_tensor(mmv_model *m, const std::string &name, int64_t rows, int64_t cols, bool registered, bool transposed = false)
+{
+    tensor_t t;
+    t.name = name;
+    t.rows = rows;
+    t.cols = cols;
+    t.registered = registered;
+    t.transposed = transposed;
+    m->tensors.push_back(t);
+    m->by_name[name] = (int)m->tensors.size() - 1;
+    return (int)m->tensors.size() - 1;
+}
+
+linear_t
+add_linear(mmv_model *m, const std::string &name, int in, int out, bool registered, bool bias = true,
+           bool transposed = false, bool angular = false)
+{
+    linear_t l;
+    l.in = in;
+    l.out = out;
+    l.angular = angular;
+    l.w = add_tensor(m, name + ".weight", out, in, registered, transposed);
+    if (bias) l.b = add_tensor(m, name + ".bias", 1, out, registered);
+    return l;
+}
+
+// Lay the tensors out: registered ones first (so "optimise the registered
+// parameters only" is one contiguous range), each start 4-float aligned except
+// the second half of a stacked head, which must follow its first half directly.
+int
+finalize_layout(mmv_model *m, const std::vector<std::pair<int, int>> &stacked)
+{
+    std::vector<int> order;
+    std::vector<char> placed(m->tensors.size(), 0), glue(m->tensors.size(), 0);
+    std::map<int, int> follower;
+    for (auto &p : stacked) {
+        follower[p.first] = p.second;
+        glue[p.second] = 1;
+    }
+    for (int pass = 0; pass < 2; ++pass)
+        for (int i = 0; i < (int)m->tensors.size(); ++i) {
+            if (placed[i] || glue[i] || m->tensors[i].registered != (pass == 0)) continue;
+            order.push_back(i);
+            placed[i] = 1;
+            auto it = follower.find(i);
+            if (it != follower.end()) {
+                MMV_CHECK(m->tensors[it->second].registered == m->tensors[i].registered, "layout: stacked pair split");
+                order.push_back(it->second);
+                placed[it->second] = 1;
+            }
+        }
+    size_t off = 0;
+    bool reg_done = false;
+    for (int i : order) {
+        tensor_t &t = m->tensors[i];
+        if (!t.registered && !reg_done) {
+            off = (off + 3) & ~(size_t)3;
+            m->n_reg = off;
+            reg_done = true;
+        }
+        if (!glue[i]) off = (off + 3) & ~(size_t)3;
+        t.off = off;
+        off += t.numel();
+    }
+    off = (off + 3) & ~(size_t)3;
+    if (!reg_done) m->n_reg = off;
+    m->n_all = off;
+    return 0;
+}
+
+int
+alloc_and_init(mmv_model *m)
+{
+    const size_t bytes = sizeof(float) * m->n_all;
+    MMV_CUDA(cudaSetDevice(m->ctx->device));
+    MMV_CUDA(cudaMalloc(&m->params, bytes));
+    MMV_CUDA(cudaMalloc(&m->grads, bytes));
+    MMV_CUDA(cudaMalloc(&m->adam_m, bytes));
+    MMV_CUDA(cudaMalloc(&m->adam_v, bytes));
+    MMV_CUDA(cudaMemset(m->grads, 0, bytes));
+    MMV_CUDA(cudaMemset(m->adam_m, 0, bytes));
+    MMV_CUDA(cudaMemset(m->adam_v, 0, bytes));
+    MMV_CUDA(cudaMalloc(&m->acc, sizeof(double) * 8));
+    MMV_CUDA(cudaMalloc(&m->fscal, sizeof(float) * 8));
+    MMV_CUDA(cudaMallocHost(&m->h_acc, sizeof(double) * 8));
+    MMV_CUDA(cudaMallocHost(&m->h_fscal, sizeof(float) * 8));
+
+    // libtorch default init: Linear/Angular weight kaiming_uniform_(a=sqrt 5) = U(+-1/sqrt(fan_in)),
+    // bias U(+-1/sqrt(fan_in)) (angular.hh:59-70); model-level vectors as in nb.hh:312-315, vmf.hh:321-323.
+    std::vector<float> h(m->n_all, 0.f);
+    rng_t rng(m->seed);
+    std::map<std::string, int> fan;   // layer name -> fan_in
+    for (auto &t : m->tensors)
+        if (t.name.size() > 7 && t.name.substr(t.name.size() - 7) == ".weight")
+            fan[t.name.substr(0, t.name.size() - 7)] = (int)t.cols;
+    for (auto &t : m->tensors) {
+        float *dst = h.data() + t.off;
+        const size_t n = t.numel();
+        const size_t dot = t.name.rfind('.');
+        const std::string layer = dot == std::string::npos ? "" : t.name.substr(0, dot);
+        if (fan.count(layer)) {
+            const float bound = 1.f / std::sqrt((float)fan[layer]);
+            for (size_t i = 0; i < n; ++i) dst[i] = rng.uniform(-bound, bound);
+        } else if (t.name == "ln_x_sd") {
+            for (size_t i = 0; i < n; ++i) dst[i] = 1.f;
+        } else if (t.name == "ln_kappa") {
+            dst[0] = std::log(m->kap_min);
+        }
+    }
+    MMV_CUDA(cudaMemcpy(m->params, h.data(), bytes, cudaMemcpyHostToDevice));
+    return 0;
+}
+
+} // namespace
+
+// ===========================================================================
+// construction
+// ===========================================================================
+extern "C" {
+
+int
+mmv_nb_model_create(mmv_ctx *ctx, const mmv_nb_dims *d, uint64_t seed, mmv_model **out)
+{
+    MMV_CHECK(ctx && d && out, "mmv_nb_model_create: NULL");
+    MMV_CHECK(d->x_dim > 0 && d->c_dim > 0 && d->mu_r_dim > 0 && d->nu_h_dim > 0 && d->nu_r_dim > 0,
+              "must be positive number");   // check_positive_t, check.hh:20-31
+    MMV_CHECK(d->n_enc >= 0 && d->n_enc <= MMV_MAX_LAYERS && d->n_dec >= 0 && d->n_dec <= MMV_MAX_LAYERS,
+              "mmv_nb_model_create: at most %d hidden layers", MMV_MAX_LAYERS);
+    MMV_CHECK(d->c_dim <= 8 && d->nu_r_dim <= 8, "mmv_nb_model_create: c_dim and nu_r_dim are limited to 8");
+    std::unique_ptr<mmv_model> m(new mmv_model());
+    m->ctx = ctx;
+    m->is_vmf = false;
+    m->D = d->x_dim; m->C = d->c_dim; m->R = d->mu_r_dim; m->H = d->nu_h_dim; m->Rnu = d->nu_r_dim;
+    m->relu = d->do_relu != 0;
+    m->seed = seed;
+    const int D = (int)m->D, C = (int)m->C, R = (int)m->R, H = (int)m->H, Rnu = (int)m->Rnu;
+
+    // registered tensors in named_parameters() order (nb.hh:318-322,351-400)
+    m->t_x_mean = add_tensor(m.get(), "x_mean", 1, D, true);
+    m->t_ln_x_sd = add_tensor(m.get(), "ln_x_sd", 1, D, true);
+    m->t_mu_bias = add_tensor(m.get(), "mu_bias", 1, D, true);
+    m->t_nu_bias = add_tensor(m.get(), "nu_bias", 1, D, true);
+    m->covar_enc = add_linear(m.get(), "covar_encoding", C, R, true);
+    int d_prev = D;   // width feeding the heads (nb.hh:331-349)
+    for (int l = 0; l < d->n_enc; ++l) {
+        MMV_CHECK(d->enc_dims[l] > 0, "must be positive number");
+        d_prev = (int)d->enc_dims[l];
+    }
+    if (d->n_enc < 1) d_prev = R;
+    linear_t hm = add_linear(m.get(), "mu_representation_mean", d_prev, R, true);
+    linear_t hv = add_linear(m.get(), "mu_representation_logvariance", d_prev, R, true);
+    m->covar_dec = add_linear(m.get(), "covar_decoding", C, D, true);
+    m->nu_enc = add_linear(m.get(), "nu_encoding", D, H, true, true, /*transposed=*/true);
+    linear_t nm = add_linear(m.get(), "nu_representation_mean", H, Rnu, true);
+    linear_t nv = add_linear(m.get(), "nu_representation_logvariance", H, Rnu, true);
+    m->nu_dec = add_linear(m.get(), "nu_decoding", Rnu, D, true);
+    m->depth = add_linear(m.get(), "depth", D, 1, true);
+
+    // unregistered Sequentials (nb.hh:331-349,366-379)
+    int prev = D;
+    for (int l = 0; l < d->n_enc; ++l) {
+        m->enc.push_back(add_linear(m.get(), "mu_encoding_" + std::to_string(l + 1), prev, (int)d->enc_dims[l],
+                                    false, true, /*transposed=*/l == 0));
+        prev = (int)d->enc_dims[l];
+    }
+    if (d->n_enc < 1) m->enc.push_back(add_linear(m.get(), "mu_encoding", D, R, false, true, true));
+    prev = R;
+    for (int l = 0; l < d->n_dec; ++l) {
+        MMV_CHECK(d->dec_dims[l] > 0, "must be positive number");
+        m->dec.push_back(add_linear(m.get(), "mu_decoding_" + std::to_string(l + 1), prev, (int)d->dec_dims[l], false));
+        prev = (int)d->dec_dims[l];
+    }
+    m->dec.push_back(add_linear(m.get(), "mu_decoding", prev, D, false));
+
+    m->head_mu = hm; m->head_mu.out = 2 * R;
+    m->t_head_mu_lv_w = hv.w; m->t_head_mu_lv_b = hv.b;
+    m->head_nu = nm; m->head_nu.out = 2 * Rnu;
+    m->t_head_nu_lv_w = nv.w; m->t_head_nu_lv_b = nv.b;
+    MMV_TRY(finalize_layout(m.get(), { { hm.w, hv.w }, { hm.b, hv.b }, { nm.w, nv.w }, { nm.b, nv.b } }));
+    MMV_TRY(alloc_and_init(m.get()));
+    *out = m.release();
+    return 0;
+}
+
+int
+mmv_vmf_model_create(mmv_ctx *ctx, const mmv_vmf_dims *d, uint64_t seed, mmv_model **out)
+{
+    MMV_CHECK(ctx && d && out, "mmv_vmf_model_create: NULL");
+    MMV_CHECK(d->x_dim > 0 && d->c_dim > 0 && d->z_dim > 0 && d->kappa_min > 0 && d->kappa_max > 0,
+              "must be positive number");
+    MMV_CHECK(std::isfinite(d->kappa_min) && std::isfinite(d->kappa_max), "must be finite number");
+    MMV_CHECK(d->n_enc >= 0 && d->n_enc <= MMV_MAX_LAYERS && d->n_dec >= 0 && d->n_dec <= MMV_MAX_LAYERS,
+              "mmv_vmf_model_create: at most %d hidden layers", MMV_MAX_LAYERS);
+    MMV_CHECK(d->c_dim <= 8, "mmv_vmf_model_create: c_dim is limited to 8");
+    std::unique_ptr<mmv_model> m(new mmv_model());
+    m->ctx = ctx;
+    m->is_vmf = true;
+    m->D = d->x_dim; m->C = d->c_dim; m->R = d->z_dim;
+    m->relu = d->do_relu != 0;
+    m->kap_min = d->kappa_min; m->kap_max = d->kappa_max;
+    m->seed = seed;
+    const int D = (int)m->D, C = (int)m->C, R = (int)m->R;
+
+    // registered (vmf.hh:325-327,357-388)
+    m->t_x_mean = add_tensor(m.get(), "x_mean", 1, D, true);
+    m->t_ln_x_sd = add_tensor(m.get(), "ln_x_sd", 1, D, true);
+    m->t_ln_kappa = add_tensor(m.get(), "ln_kappa", 1, 1, true);
+    m->covar_enc = add_linear(m.get(), "covar_encoding", C, R, true);
+    int d_prev = D;
+    for (int l = 0; l < d->n_enc; ++l) {
+        MMV_CHECK(d->enc_dims[l] > 0, "must be positive number");
+        d_prev = (int)d->enc_dims[l];
+    }
+    if (d->n_enc < 1) d_prev = R;
+    linear_t hm = add_linear(m.get(), "representation_mean", d_prev, R, true);
+    linear_t hv = add_linear(m.get(), "representation_logvariance", d_prev, R, true);
+    m->covar_dec = add_linear(m.get(), "covar_decoding_", C, D, true);   // trailing underscore: vmf.hh:388
+
+    // unregistered: Angular encoder (no bias, angular.hh:51-57), Linear decoder
+    int prev = D;
+    for (int l = 0; l < d->n_enc; ++l) {
+        m->enc.push_back(add_linear(m.get(), "encoding_" + std::to_string(l + 1), prev, (int)d->enc_dims[l], false,
+                                    /*bias=*/false, /*transposed=*/l == 0, /*angular=*/true));
+        prev = (int)d->enc_dims[l];
+    }
+    if (d->n_enc < 1)   // pushed unnamed -> key "0" (vmf.hh:350)
+        m->enc.push_back(add_linear(m.get(), "0", D, R, false, false, true, true));
+    prev = R;
+    for (int l = 0; l < d->n_dec; ++l) {
+        MMV_CHECK(d->dec_dims[l] > 0, "must be positive number");
+        m->dec.push_back(add_linear(m.get(), "decoding_" + std::to_string(l + 1), prev, (int)d->dec_dims[l], false));
+        prev = (int)d->dec_dims[l];
+    }
+    m->dec.push_back(add_linear(m.get(), "decoding", prev, D, false));
+
+    m->head_mu = hm; m->head_mu.out = 2 * R;
+    m->t_head_mu_lv_w = hv.w; m->t_head_mu_lv_b = hv.b;
+    MMV_TRY(finalize_layout(m.get(), { { hm.w, hv.w }, { hm.b, hv.b } }));
+    MMV_TRY(alloc_and_init(m.get()));
+    *out = m.release();
+    return 0;
+}
+
+int
+mmv_model_destroy(mmv_model *m)
+{
+    if (!m) return 0;
+    cudaSetDevice(m->ctx->device);
+    cudaStreamSynchronize(m->ctx->stream);
+    cudaFree(m->params); cudaFree(m->grads); cudaFree(m->adam_m); cudaFree(m->adam_v);
+    cudaFree(m->acc); cudaFree(m->fscal);
+    cudaFreeHost(m->h_acc); cudaFreeHost(m->h_fscal);
+    if (m->h_cells) cudaFreeHost(m->h_cells);
+    if (m->h_eps) cudaFreeHost(m->h_eps);
+    for (auto &kv : m->ws) kv.second.release();
+    delete m;
+    return 0;
+}
+
+int
+mmv_model_set_option(mmv_model *m, const char *key, double value)
+{
+    MMV_CHECK(m && key, "mmv_model_set_option: NULL");
+    const std::string k(key);
+    if (k == "lr") m->lr = (float)value;
+    else if (k == "weight_decay") m->weight_decay = (float)value;
+    else if (k == "grad_clip") m->grad_clip = (float)value;
+    else if (k == "train_all_layers") m->train_all = value != 0;
+    else if (k == "frozen_grads") m->frozen_grads = value != 0;
+    else if (k == "debug_outputs") m->debug_outputs = value != 0;
+    else if (k == "max_batch") { /* capacity hint; buffers grow on demand */ }
+    else MMV_CHECK(false, "mmv_model_set_option: unknown key '%s'", key);
+    return 0;
+}
+
+int
+mmv_model_num_params(mmv_model *m, int *out)
+{
+    MMV_CHECK(m && out, "mmv_model_num_params: NULL");
+    *out = (int)m->tensors.size();
+    return 0;
+}
+
+int
+mmv_model_param_info(mmv_model *m, int i, char name[MMV_NAME_LEN], int64_t *rows, int64_t *cols, int *registered)
+{
+    MMV_CHECK(m && i >= 0 && i < (int)m->tensors.size(), "mmv_model_param_info: index %d out of range", i);
+    const tensor_t &t = m->tensors[i];
+    if (name) snprintf(name, MMV_NAME_LEN, "%s", t.name.c_str());
+    if (rows) *rows = t.rows;
+    if (cols) *cols = t.cols;
+    if (registered) *registered = t.registered ? 1 : 0;
+    return 0;
+}
+
+static int
+copy_tensor(mmv_model *m, const char *name, float *host, const float *host_in, int64_t n, float *base)
+{
+    MMV_CHECK(m && name, "parameter access: NULL");
+    auto it = m->by_name.find(name);
+    MMV_CHECK(it != m->by_name.end(), "no parameter named '%s'", name);
+    const tensor_t &t = m->tensors[it->second];
+    MMV_CHECK((size_t)n == t.numel(), "parameter '%s' has %zu elements, got %ld", name, t.numel(), (long)n);
+    MMV_CUDA(cudaSetDevice(m->ctx->device));
+    MMV_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    std::vector<float> tmp;
+    if (host_in) {   // set
+        const float *src = host_in;
+        if (t.transposed) {   // libtorch [rows x cols] -> stored [cols x rows]
+            tmp.resize(n);
+            for (int64_t r = 0; r < t.rows; ++r)
+                for (int64_t c = 0; c < t.cols; ++c) tmp[c * t.rows + r] = host_in[r * t.cols + c];
+            src = tmp.data();
+        }
+        MMV_CUDA(cudaMemcpy(base + t.off, src, sizeof(float) * n, cudaMemcpyHostToDevice));
+    } else {
+        if (t.transposed) {
+            tmp.resize(n);
+            MMV_CUDA(cudaMemcpy(tmp.data(), base + t.off, sizeof(float) * n, cudaMemcpyDeviceToHost));
+            for (int64_t r = 0; r < t.rows; ++r)
+                for (int64_t c = 0; c < t.cols; ++c) host[r * t.cols + c] = tmp[c * t.rows + r];
+        } else {
+            MMV_CUDA(cudaMemcpy(host, base + t.off, sizeof(float) * n, cudaMemcpyDeviceToHost));
+        }
+    }
+    return 0;
+}
+
+int
+mmv_model_set_param(mmv_model *m, const char *name, const float *host, int64_t n)
+{
+    MMV_CHECK(host, "mmv_model_set_param: NULL data");
+    return copy_tensor(m, name, nullptr, host, n, m ? m->params : nullptr);
+}
+
+int
+mmv_model_get_param(mmv_model *m, const char *name, float *host, int64_t n)
+{
+    MMV_CHECK(host, "mmv_model_get_param: NULL data");
+    return copy_tensor(m, name, host, nullptr, n, m ? m->params : nullptr);
+}
+
+int
+mmv_model_get_grad(mmv_model *m, const char *name, float *host, int64_t n)
+{
+    MMV_CHECK(host, "mmv_model_get_grad: NULL data");
+    return copy_tensor(m, name, host, nullptr, n, m ? m->grads : nullptr);
+}
+
+} // extern "C"
+
+// ===========================================================================
+// the step
+// ===========================================================================
+namespace {
+
+__global__ void
+axpy_kernel(float *y, const float *x, float a, size_t n)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        y[i] = fmaf(a, x[i], y[i]);
+}
+
+int
+axpy(float *y, const float *x, float a, size_t n, cudaStream_t st)
+{
+    if (n == 0) return 0;
+    axpy_kernel<<<(int)min_sz((n + 255) / 256, 2048), 256, 0, st>>>(y, x, a, n);
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+struct step_t {
+    mmv_model *m;
+    mmv_csr *csr;
+    int B;
+    const int32_t *cells;   // device
+    const float *cov;       // device or nullptr (ones)
+    const float *eps_mu, *eps_nu;   // device or nullptr
+    float klw, inv_B;
+    bool bwd;
+    cudaStream_t st;
+};
+
+#define WS(name, count) m->W(name, sizeof(float) * (size_t)(count))
+#define NEED(ptr) MMV_CHECK((ptr) != nullptr, "out of device memory: %s", mmv::get_error())
+
+// Y = X W^T (+ b)
+int
+lin_fwd(const step_t &s, const float *X, int in, const float *W, const float *b, int out, float *Y, bool relu)
+{
+    gemm_args_t g;
+    g.A = X; g.lda = in; g.B = W; g.ldb = in; g.transB = 1;
+    g.C = Y; g.ldc = out; g.M = s.B; g.N = out; g.K = in; g.bias = b; g.relu = relu ? 1 : 0;
+    return launch_gemm_f32(g, s.st);
+}
+
+// dX = dY W
+int
+lin_bwd_data(const step_t &s, const float *dY, int out, const float *W, int in, float *dX)
+{
+    gemm_args_t g;
+    g.A = dY; g.lda = out; g.B = W; g.ldb = in;
+    g.C = dX; g.ldc = in; g.M = s.B; g.N = in; g.K = out;
+    return launch_gemm_f32(g, s.st);
+}
+
+// dW += dY^T X ; db += colsum(dY)
+int
+lin_bwd_weight(const step_t &s, const float *dY, int out, const float *X, int in, float *dW, float *db, float beta = 1.f)
+{
+    if (dW) {
+        gemm_args_t g;
+        g.A = dY; g.lda = out; g.transA = 1; g.B = X; g.ldb = in;
+        g.C = dW; g.ldc = in; g.M = out; g.N = in; g.K = s.B; g.beta = beta;
+        MMV_TRY(launch_gemm_f32(g, s.st));
+    }
+    if (db) {
+        colsum_args_t c;
+        c.X = dY; c.M = s.B; c.N = out; c.ldx = out; c.out_sum = db;
+        MMV_TRY(launch_colsum(c, s.st));
+    }
+    return 0;
+}
+
+// encoder tail shared by both models: hidden layers 1.., stacked heads, reparam.
+// Returns pointers through the workspace names "enc_act<l>", "head_mu", "mu_mean", "mu_lnvar", "z".
+int
+encoder_forward(const step_t &s, bool with_covar)
+{
+    mmv_model *m = s.m;
+    const int B = s.B, R = (int)m->R, C = (int)m->C;
+    const int k = (int)m->enc.size();
+    const float *h = m->ws["enc_act0"].as<float>();
+    for (int l = 1; l < k; ++l) {
+        const linear_t &L = m->enc[l];
+        float *y = WS("enc_act" + std::to_string(l), (size_t)B * L.out); NEED(y);
+        const float *Wl = m->P(L.w);
+        if (L.angular) {   // angular.hh:34-42
+            float *scale = WS("ang_scale" + std::to_string(l), L.out); NEED(scale);
+            float *Wp = WS("ang_wp" + std::to_string(l), (size_t)L.out * L.in); NEED(Wp);
+            MMV_TRY(launch_angular_scale(Wl, scale, L.out, L.in, L.in, 1, s.st));
+            MMV_TRY(launch_angular_materialize(Wl, scale, Wp, L.out, L.in, s.st));
+            Wl = Wp;
+        }
+        MMV_TRY(lin_fwd(s, h, L.in, Wl, L.b >= 0 ? m->P(L.b) : nullptr, L.out, y, m->relu));
+        h = y;
+    }
+    const linear_t &Hd = m->head_mu;
+    float *head = WS("head_mu", (size_t)B * 2 * R); NEED(head);
+    MMV_TRY(lin_fwd(s, h, Hd.in, m->P(Hd.w), m->P(Hd.b), 2 * R, head, false));
+    reparam_args_t r;
+    r.head = head; r.B = B; r.R = R; r.C = C;
+    if (with_covar) { r.Wce = m->P(m->covar_enc.w); r.bce = m->P(m->covar_enc.b); r.cov = s.cov; r.cells = s.cells; }
+    r.eps = s.eps_mu;
+    r.mean = WS("mu_mean", (size_t)B * R); r.lnvar = WS("mu_lnvar", (size_t)B * R); r.z = WS("z", (size_t)B * R);
+    NEED(r.mean); NEED(r.lnvar); NEED(r.z);
+    r.kl_acc = m->acc + 1;
+    return launch_reparam_fwd(r, s.st);
+}
+
+// decoder hidden layers + last layer (no bias: it is folded into K4/K5). Output "G" [B x D].
+int
+decoder_forward(const step_t &s)
+{
+    mmv_model *m = s.m;
+    const int B = s.B, D = (int)m->D;
+    const float *h = m->ws["z"].as<float>();
+    const int nd = (int)m->dec.size();
+    for (int l = 0; l + 1 < nd; ++l) {
+        const linear_t &L = m->dec[l];
+        float *y = WS("dec_act" + std::to_string(l), (size_t)B * L.out); NEED(y);
+        MMV_TRY(lin_fwd(s, h, L.in, m->P(L.w), m->P(L.b), L.out, y, m->relu));
+        h = y;
+    }
+    const linear_t &L = m->dec[nd - 1];
+    float *G = WS("G", (size_t)B * D); NEED(G);
+    return lin_fwd(s, h, L.in, m->P(L.w), nullptr, D, G, false);
+}
+
+// backward through the decoder given dG (in "G", in place) -> "dz"
+int
+decoder_backward(const step_t &s)
+{
+    mmv_model *m = s.m;
+    const int B = s.B, R = (int)m->R;
+    const int nd = (int)m->dec.size();
+    const float *dY = m->ws["G"].as<float>();
+    for (int l = nd - 1; l >= 0; --l) {
+        const linear_t &L = m->dec[l];
+        const float *X = l == 0 ? m->ws["z"].as<float>() : m->ws["dec_act" + std::to_string(l - 1)].as<float>();
+        const bool last = l == nd - 1;
+        // bias of the last layer is handled with the other per-gene sums by the caller
+        MMV_TRY(lin_bwd_weight(s, dY, L.out, X, L.in, m->want_grad(L.w) ? m->G(L.w) : nullptr,
+                               (!last && m->want_grad(L.b)) ? m->G(L.b) : nullptr));
+        float *dX = l == 0 ? WS("dz", (size_t)B * R) : WS("d_dec" + std::to_string(l - 1), (size_t)B * L.in);
+        NEED(dX);
+        MMV_TRY(lin_bwd_data(s, dY, L.out, m->P(L.w), L.in, dX));
+        if (l > 0 && m->relu) MMV_TRY(launch_relu_bwd(dX, X, (size_t)B * L.in, s.st));
+        dY = dX;
+    }
+    return 0;
+}
+
+// backward through reparam + heads + hidden encoder layers -> "d_enc0" (gradient
+// w.r.t. the first layer's output, ReLU mask applied) and "Delta" = its column sums
+int
+encoder_backward(const step_t &s, bool with_covar)
+{
+    mmv_model *m = s.m;
+    const int B = s.B, R = (int)m->R, C = (int)m->C;
+    const int k = (int)m->enc.size();
+    reparam_args_t r;
+    r.head = m->ws["head_mu"].as<float>(); r.B = B; r.R = R; r.C = C;
+    r.eps = s.eps_mu;
+    r.mean = m->ws["mu_mean"].as<float>(); r.lnvar = m->ws["mu_lnvar"].as<float>();
+    r.dz = m->ws["dz"].as<float>();
+    r.dhead = WS("dhead_mu", (size_t)B * 2 * R); NEED(r.dhead);
+    r.kl_weight = s.klw; r.inv_B = s.inv_B;
+    MMV_TRY(launch_reparam_bwd(r, s.st));
+    if (with_covar) {   // covar_encoding grads: dW_ce[r, c] = sum_i dmean_ir c_ic ; db_ce = sum_i dmean_ir
+        colsum_args_t c;
+        c.X = r.dhead; c.M = B; c.N = R; c.ldx = 2 * R;
+        c.out_sum = m->G(m->covar_enc.b); c.out_cov = m->G(m->covar_enc.w);
+        c.cov = s.cov; c.cells = s.cells; c.C = C;
+        MMV_TRY(launch_colsum(c, s.st));
+    }
+    const linear_t &Hd = m->head_mu;
+    const float *X = m->ws["enc_act" + std::to_string(k - 1)].as<float>();
+    MMV_TRY(lin_bwd_weight(s, r.dhead, 2 * R, X, Hd.in, m->G(Hd.w), m->G(Hd.b)));
+    float *dX = WS("d_enc" + std::to_string(k - 1), (size_t)B * Hd.in); NEED(dX);
+    MMV_TRY(lin_bwd_data(s, r.dhead, 2 * R, m->P(Hd.w), Hd.in, dX));
+    if (m->relu) MMV_TRY(launch_relu_bwd(dX, X, (size_t)B * Hd.in, s.st));
+    const float *dY = dX;
+    for (int l = k - 1; l >= 1; --l) {
+        const linear_t &L = m->enc[l];
+        const float *Xl = m->ws["enc_act" + std::to_string(l - 1)].as<float>();
+        const float *Wl = m->P(L.w);
+        if (L.angular) {
+            const float *scale = m->ws["ang_scale" + std::to_string(l)].as<float>();
+            Wl = m->ws["ang_wp" + std::to_string(l)].as<float>();
+            if (m->want_grad(L.w)) {
+                float *dWp = WS("ang_dwp", (size_t)L.out * L.in); NEED(dWp);
+                float *dot = WS("ang_dot", L.out); NEED(dot);
+                MMV_TRY(lin_bwd_weight(s, dY, L.out, Xl, L.in, dWp, nullptr, 0.f));
+                MMV_TRY(launch_angular_bwd(m->P(L.w), dWp, scale, dot, m->G(L.w), L.out, L.in, L.in, 1, s.st));
+            }
+        } else {
+            MMV_TRY(lin_bwd_weight(s, dY, L.out, Xl, L.in, m->want_grad(L.w) ? m->G(L.w) : nullptr,
+                                   (L.b >= 0 && m->want_grad(L.b)) ? m->G(L.b) : nullptr));
+        }
+        float *dXl = WS("d_enc" + std::to_string(l - 1), (size_t)B * L.in); NEED(dXl);
+        MMV_TRY(lin_bwd_data(s, dY, L.out, Wl, L.in, dXl));
+        if (m->relu) MMV_TRY(launch_relu_bwd(dXl, Xl, (size_t)B * L.in, s.st));
+        dY = dXl;
+    }
+    // column sums of delta: needed by the x_mean / ln_x_sd gradients and = grad of the first bias
+    const linear_t &L0 = m->enc[0];
+    float *Delta = WS("Delta", L0.out); NEED(Delta);
+    MMV_CUDA(cudaMemsetAsync(Delta, 0, sizeof(float) * L0.out, s.st));
+    colsum_args_t c;
+    c.X = dY; c.M = B; c.N = L0.out; c.ldx = L0.out; c.out_sum = Delta;
+    if (L0.b >= 0 && m->want_grad(L0.b)) c.out_sum2 = m->G(L0.b);
+    return launch_colsum(c, s.st);
+}
+
+int
+build_csc(const step_t &s, const float *rownorm)
+{
+    mmv_model *m = s.m;
+    const int D = (int)m->D;
+    const size_t cap = (size_t)s.B * (size_t)std::max<int64_t>(s.csr->max_row_nnz, 1);
+    batch_csc_args_t c;
+    c.indptr = s.csr->indptr; c.indices = s.csr->indices; c.vals = s.csr->vals; c.cells = s.cells;
+    c.rownorm = rownorm; c.B = s.B; c.D = D;
+    c.counts = (int *)WS("csc_counts", D); c.gene_ptr = (int *)WS("csc_ptr", D + 1); c.cursor = (int *)WS("csc_cursor", D);
+    c.ent_row = (int *)WS("csc_row", cap); c.ent_l = WS("csc_l", cap); c.ent_x = WS("csc_x", cap);
+    NEED(c.counts); NEED(c.gene_ptr); NEED(c.cursor); NEED(c.ent_row); NEED(c.ent_l); NEED(c.ent_x);
+    return launch_batch_csc(c, s.st);
+}
+
+} // namespace
+
+namespace {
+
+// ---------------------------------------------------------------------------
+// NB-VAE: forward (nb.hh:474-508) + loss (nb.hh:511-548) [+ backward]
+// ---------------------------------------------------------------------------
+int
+nb_forward_backward(const step_t &s)
+{
+    mmv_model *m = s.m;
+    const int B = s.B, D = (int)m->D, R = (int)m->R, H = (int)m->H, Rnu = (int)m->Rnu, C = (int)m->C;
+    (void)R;
+    const linear_t &L0 = m->enc[0];
+    const int h1 = L0.out;
+
+    float *inv_t = WS("inv_t", D); NEED(inv_t);
+    MMV_TRY(launch_gene_prep(m->P(m->t_ln_x_sd), 1e-4f, inv_t, D, s.st));            // nb.hh:406-410
+    float *bias_eff = WS("bias_eff", h1); NEED(bias_eff);
+    MMV_CUDA(cudaMemcpyAsync(bias_eff, m->P(L0.b), sizeof(float) * h1, cudaMemcpyDeviceToDevice, s.st));
+    MMV_TRY(launch_senc_bias(m->P(L0.w), m->P(m->t_x_mean), inv_t, nullptr, bias_eff, D, h1, 0, s.st));
+
+    senc_args_t e;
+    e.indptr = s.csr->indptr; e.indices = s.csr->indices; e.vals = s.csr->vals; e.cells = s.cells;
+    e.B = B; e.D = D; e.W1T = m->P(L0.w); e.h1 = h1; e.inv_t = inv_t; e.bias_eff = bias_eff; e.relu = m->relu;
+    e.H1 = WS("enc_act0", (size_t)B * h1); NEED(e.H1);
+    e.WnuT = m->P(m->nu_enc.w); e.bnu = m->P(m->nu_enc.b); e.H = H;
+    e.wdepth = m->P(m->depth.w); e.bdepth = m->P(m->depth.b);
+    e.Hnu = WS("Hnu", (size_t)B * H); e.dpre = WS("dpre", B); NEED(e.Hnu); NEED(e.dpre);
+    MMV_TRY(launch_senc_fwd(e, s.st));
+
+    MMV_TRY(encoder_forward(s, true));
+
+    // over-dispersion encoder heads (nb.hh:444-451) + reparam
+    const linear_t &Hn = m->head_nu;
+    float *head_nu = WS("head_nu", (size_t)B * 2 * Rnu); NEED(head_nu);
+    MMV_TRY(lin_fwd(s, e.Hnu, H, m->P(Hn.w), m->P(Hn.b), 2 * Rnu, head_nu, false));
+    reparam_args_t rn;
+    rn.head = head_nu; rn.B = B; rn.R = Rnu; rn.eps = s.eps_nu;
+    rn.mean = WS("nu_mean", (size_t)B * Rnu); rn.lnvar = WS("nu_lnvar", (size_t)B * Rnu); rn.z = WS("znu", (size_t)B * Rnu);
+    NEED(rn.mean); NEED(rn.lnvar); NEED(rn.z);
+    rn.kl_acc = m->acc + 2;
+    MMV_TRY(launch_reparam_fwd(rn, s.st));
+
+    MMV_TRY(decoder_forward(s));
+
+    const linear_t &Ld = m->dec.back();
+    float *abias = WS("abias", D), *ubias = WS("ubias", D); NEED(abias); NEED(ubias);
+    MMV_TRY(launch_vec_combine(m->P(Ld.b), m->P(m->covar_dec.b), m->P(m->t_mu_bias), 1.f, 1.f, abias, D, s.st));
+    MMV_TRY(launch_vec_combine(m->P(m->nu_dec.b), m->P(m->t_nu_bias), nullptr, -1.f, 0.f, ubias, D, s.st));
+
+    nb_lik_args_t k;
+    k.G = m->ws["G"].as<float>(); k.abias = abias; k.Wcd = m->P(m->covar_dec.w); k.cov = s.cov;
+    k.indptr = s.csr->indptr; k.indices = s.csr->indices; k.vals = s.csr->vals; k.cells = s.cells;
+    k.dpre = e.dpre; k.znu = rn.z; k.Wnd = m->P(m->nu_dec.w); k.ubias = ubias;
+    k.B = B; k.D = D; k.C = C; k.Rnu = Rnu; k.inv_B = s.inv_B;
+    k.loss_acc = m->acc + 0;
+    if (m->debug_outputs) {
+        k.recon_mu = WS("recon_mu", (size_t)B * D); k.recon_nu = WS("recon_nu", (size_t)B * D);
+        NEED(k.recon_mu); NEED(k.recon_nu);
+    }
+    if (s.bwd) {
+        k.dlogits = m->ws["G"].as<float>();   // in place: each row is staged in shared memory first
+        k.ddpre = WS("ddpre", B); k.dznu = WS("dznu", (size_t)B * Rnu);
+        k.col_du = WS("col_du", D); k.col_duz = WS("col_duz", (size_t)D * Rnu);
+        NEED(k.ddpre); NEED(k.dznu); NEED(k.col_du); NEED(k.col_duz);
+        MMV_CUDA(cudaMemsetAsync(k.col_du, 0, sizeof(float) * D, s.st));
+        MMV_CUDA(cudaMemsetAsync(k.col_duz, 0, sizeof(float) * D * Rnu, s.st));
+    }
+    MMV_TRY(launch_nb_likelihood(k, m->ctx->num_sms, s.st));
+    if (!s.bwd) return 0;
+
+    // per-gene sums of dlogits: mu_decoding.bias, covar_decoding.{bias,weight}, mu_bias
+    {
+        colsum_args_t c;
+        c.X = k.dlogits; c.M = B; c.N = D; c.ldx = D;
+        c.out_sum = m->want_grad(Ld.b) ? m->G(Ld.b) : nullptr;
+        c.out_sum2 = m->G(m->covar_dec.b); c.out_sum3 = m->G(m->t_mu_bias);
+        c.out_cov = m->G(m->covar_dec.w); c.cov = s.cov; c.cells = s.cells; c.C = C;
+        MMV_TRY(launch_colsum(c, s.st));
+    }
+    // nu decoder: u = W_nd znu + b_nd - nu_bias
+    MMV_TRY(axpy(m->G(m->nu_dec.b), k.col_du, 1.f, D, s.st));
+    MMV_TRY(axpy(m->G(m->t_nu_bias), k.col_du, -1.f, D, s.st));
+    MMV_TRY(axpy(m->G(m->nu_dec.w), k.col_duz, 1.f, (size_t)D * Rnu, s.st));
+
+    MMV_TRY(decoder_backward(s));
+    MMV_TRY(encoder_backward(s, true));
+
+    // nu encoder backward
+    rn.dz = k.dznu; rn.dhead = WS("dhead_nu", (size_t)B * 2 * Rnu); NEED(rn.dhead);
+    rn.kl_weight = s.klw; rn.inv_B = s.inv_B;
+    MMV_TRY(launch_reparam_bwd(rn, s.st));
+    MMV_TRY(lin_bwd_weight(s, rn.dhead, 2 * Rnu, e.Hnu, H, m->G(Hn.w), m->G(Hn.b)));
+    float *dHnu = WS("dHnu", (size_t)B * H); NEED(dHnu);
+    MMV_TRY(lin_bwd_data(s, rn.dhead, 2 * Rnu, m->P(Hn.w), H, dHnu));
+    {
+        colsum_args_t c;
+        c.X = dHnu; c.M = B; c.N = H; c.ldx = H; c.out_sum = m->G(m->nu_enc.b);
+        MMV_TRY(launch_colsum(c, s.st));
+        colsum_args_t c2;
+        c2.X = k.ddpre; c2.M = B; c2.N = 1; c2.ldx = 1; c2.out_sum = m->G(m->depth.b);
+        MMV_TRY(launch_colsum(c2, s.st));
+    }
+
+    MMV_TRY(build_csc(s, nullptr));
+    senc_bwd_args_t b;
+    b.gene_ptr = m->ws["csc_ptr"].as<int>(); b.ent_row = m->ws["csc_row"].as<int>();
+    b.ent_l = m->ws["csc_l"].as<float>(); b.ent_x = m->ws["csc_x"].as<float>();
+    b.D = D; b.h1 = h1; b.H = H; b.angular = 0; b.accumulate = 1;
+    b.delta = m->ws["d_enc0"].as<float>(); b.Delta = m->ws["Delta"].as<float>();
+    b.W1T = m->P(L0.w); b.inv_t = inv_t; b.x_mean = m->P(m->t_x_mean); b.ln_x_sd = m->P(m->t_ln_x_sd);
+    b.dW1T = m->want_grad(L0.w) ? m->G(L0.w) : nullptr;
+    b.dx_mean = m->G(m->t_x_mean); b.dln_x_sd = m->G(m->t_ln_x_sd);
+    b.dHnu = dHnu; b.ddpre = k.ddpre; b.dWnuT = m->G(m->nu_enc.w); b.dwdepth = m->G(m->depth.w);
+    return launch_senc_bwd(b, s.st);
+}
+
+// ---------------------------------------------------------------------------
+// vMF-VAE: forward (vmf.hh:292-304) + loss (vmf.hh:419-440) [+ backward]
+// ---------------------------------------------------------------------------
+int
+vmf_forward_backward(const step_t &s)
+{
+    mmv_model *m = s.m;
+    const int B = s.B, D = (int)m->D, C = (int)m->C;
+    const linear_t &L0 = m->enc[0];
+    const int h1 = L0.out;
+    const float eps_d = 1e-2f / (float)D;                                             // vmf.hh:253,422
+
+    float *inv_t = WS("inv_t", D); NEED(inv_t);
+    MMV_TRY(launch_gene_prep(m->P(m->t_ln_x_sd), eps_d, inv_t, D, s.st));             // vmf.hh:258
+    float *col_scale = WS("ang_scale0", h1); NEED(col_scale);
+    MMV_TRY(launch_angular_scale(m->P(L0.w), col_scale, h1, D, 1, (size_t)h1, s.st));
+    float *bias_eff = WS("bias_eff", h1); NEED(bias_eff);
+    MMV_CUDA(cudaMemsetAsync(bias_eff, 0, sizeof(float) * h1, s.st));                 // Angular has no bias
+    MMV_TRY(launch_senc_bias(m->P(L0.w), m->P(m->t_x_mean), inv_t, col_scale, bias_eff, D, h1, 1, s.st));
+
+    senc_args_t e;
+    e.indptr = s.csr->indptr; e.indices = s.csr->indices; e.vals = s.csr->vals; e.cells = s.cells;
+    e.B = B; e.D = D; e.angular = 1; e.W1T = m->P(L0.w); e.h1 = h1; e.inv_t = inv_t; e.bias_eff = bias_eff;
+    e.col_scale = col_scale; e.relu = m->relu;
+    e.H1 = WS("enc_act0", (size_t)B * h1); e.rownorm = WS("rownorm", B); NEED(e.H1); NEED(e.rownorm);
+    MMV_TRY(launch_senc_fwd(e, s.st));
+
+    MMV_TRY(encoder_forward(s, true));
+    MMV_TRY(decoder_forward(s));
+
+    float *kappa = m->fscal + 0;
+    MMV_TRY(launch_vmf_kappa(m->P(m->t_ln_kappa), m->kap_min, m->kap_max, kappa, s.st));
+
+    const linear_t &Ld = m->dec.back();
+    vmf_lik_args_t k;
+    k.G = m->ws["G"].as<float>(); k.blast = m->P(Ld.b); k.Wcd = m->P(m->covar_dec.w); k.bcd = m->P(m->covar_dec.b);
+    k.cov = s.cov; k.indptr = s.csr->indptr; k.indices = s.csr->indices; k.vals = s.csr->vals; k.cells = s.cells;
+    k.kappa = kappa; k.B = B; k.D = D; k.C = C; k.inv_B = s.inv_B; k.eps_obs = eps_d;
+    k.t_acc = m->acc + 4;
+    if (m->debug_outputs) { k.recon = WS("recon", (size_t)B * D); NEED(k.recon); }
+    if (s.bwd) {
+        k.dpre = m->ws["G"].as<float>();
+        k.col_dq = WS("col_dq", D); k.col_dqc = WS("col_dqc", (size_t)D * C); NEED(k.col_dq); NEED(k.col_dqc);
+        MMV_CUDA(cudaMemsetAsync(k.col_dq, 0, sizeof(float) * D, s.st));
+        MMV_CUDA(cudaMemsetAsync(k.col_dqc, 0, sizeof(float) * D * C, s.st));
+    }
+    MMV_TRY(launch_vmf_likelihood(k, m->ctx->num_sms, s.st));
+
+    // scalar part: loss constant, lbessel (operators.hh:49-101) and d ln_kappa (operators.hh:13-47)
+    vmf_scalar_args_t sc;
+    const float dd = (float)D;
+    const float df = (float)std::max(0.5 * dd - 1., 0.);                              // vmf.hh:429
+    const double nu = df;
+    const float eta = (float)((nu + 0.5) / (2. * (nu + 1.)));                         // operators.hh:69
+    sc.kappa = kappa; sc.ln_kappa = m->P(m->t_ln_kappa); sc.t_acc = m->acc + 4; sc.llik_sum = m->acc + 5;
+    sc.dln_kappa = s.bwd ? m->G(m->t_ln_kappa) : nullptr;
+    sc.B = B; sc.inv_B_global = s.inv_B; sc.inv_ranks = 1.f / (float)m->ctx->nranks;
+    sc.df = df; sc.eta = eta; sc.kmin = m->kap_min; sc.kmax = m->kap_max;
+    sc.c_eta_nu_log2 = (float)((eta + nu) * std::log(2.));
+    sc.c_fasterlgamma = fasterlgamma_host((float)(nu + 1));
+    sc.c_half_log_2pi = (float)(0.5 * std::log(2. * M_PI));
+    sc.c_half_D_fasterlog_2pi = (float)(0.5 * dd * fasterlog_host((float)(2. * M_PI)));   // vmf.hh:437
+    MMV_TRY(launch_vmf_scalar(sc, s.st));
+    if (!s.bwd) return 0;
+
+    {   // decoding.bias = column sums of dL/dpre ; covar_decoding_ from dL/dq
+        colsum_args_t c;
+        c.X = k.dpre; c.M = B; c.N = D; c.ldx = D; c.out_sum = m->want_grad(Ld.b) ? m->G(Ld.b) : nullptr;
+        if (c.out_sum) MMV_TRY(launch_colsum(c, s.st));
+    }
+    MMV_TRY(axpy(m->G(m->covar_dec.b), k.col_dq, 1.f, D, s.st));
+    MMV_TRY(axpy(m->G(m->covar_dec.w), k.col_dqc, 1.f, (size_t)D * C, s.st));
+
+    MMV_TRY(decoder_backward(s));
+    MMV_TRY(encoder_backward(s, true));
+
+    MMV_TRY(build_csc(s, e.rownorm));
+    float *dWeff = WS("dW1eff", (size_t)D * h1); NEED(dWeff);
+    float *dot = WS("ang_dot", std::max(h1, 1)); NEED(dot);
+    senc_bwd_args_t b;
+    b.gene_ptr = m->ws["csc_ptr"].as<int>(); b.ent_row = m->ws["csc_row"].as<int>();
+    b.ent_l = m->ws["csc_l"].as<float>(); b.ent_x = m->ws["csc_x"].as<float>();
+    b.D = D; b.h1 = h1; b.H = 0; b.angular = 1; b.accumulate = 0;
+    b.delta = m->ws["d_enc0"].as<float>(); b.Delta = m->ws["Delta"].as<float>();
+    b.W1T = m->P(L0.w); b.col_scale = col_scale; b.inv_t = inv_t;
+    b.x_mean = m->P(m->t_x_mean); b.ln_x_sd = m->P(m->t_ln_x_sd);
+    b.dW1T = dWeff; b.dx_mean = m->G(m->t_x_mean); b.dln_x_sd = m->G(m->t_ln_x_sd);
+    MMV_TRY(launch_senc_bwd(b, s.st));
+    if (m->want_grad(L0.w))
+        MMV_TRY(launch_angular_bwd(m->P(L0.w), dWeff, col_scale, dot, m->G(L0.w), h1, D, 1, (size_t)h1, s.st));
+    return 0;
+}
+
+} // namespace
+
+namespace {
+
+// counter-based N(0,1): one draw per element keyed on (seed, step, element).
+__device__ __forceinline__ uint32_t
+mix32(uint64_t z)
+{
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z = z ^ (z >> 31);
+    return (uint32_t)(z >> 16);
+}
+
+__global__ void
+normal_kernel(float *out, size_t n, uint64_t seed, uint64_t step)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const uint64_t key = seed * 0x9E3779B97F4A7C15ull + step * 0xD1B54A32D192ED03ull + i * 2;
+        const float u1 = ((float)mix32(key) + 1.f) * (1.f / 4294967808.f);          // (0, 1)
+        const float u2 = (float)mix32(key + 1) * (1.f / 4294967296.f);
+        out[i] = sqrtf(-2.f * logf(u1)) * cospif(2.f * u2);                          // Box-Muller
+    }
+}
+
+int
+stage_inputs(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int64_t *boot_idx,
+             const float *eps, int flags, step_t &s)
+{
+    cudaStream_t st = m->ctx->stream;
+    // staging buffers are reused: wait until the previous step's copies were consumed
+    MMV_CUDA(cudaStreamSynchronize(st));
+    if (m->h_cells_cap < B) {
+        if (m->h_cells) cudaFreeHost(m->h_cells);
+        MMV_CUDA(cudaMallocHost(&m->h_cells, sizeof(int32_t) * B));
+        m->h_cells_cap = B;
+    }
+    for (int64_t r = 0; r < B; ++r) {   // bootstrap = index composition (mmvae_alg.hh:292-301)
+        int64_t pos = r;
+        if (boot_idx) {
+            pos = boot_idx[r];
+            MMV_CHECK(pos >= 0 && pos < B, "mmv_step: boot_idx[%ld] = %ld out of range [0,%ld)", (long)r, (long)pos, (long)B);
+        }
+        const int64_t cell = cells ? cells[pos] : pos;
+        MMV_CHECK(cell >= 0 && cell < csr->n_cells, "mmv_step: cell id %ld out of range [0,%ld)", (long)cell,
+                  (long)csr->n_cells);
+        m->h_cells[r] = (int32_t)cell;
+    }
+    int32_t *d_cells = (int32_t *)m->W("cells", sizeof(int32_t) * B);
+    NEED(d_cells);
+    MMV_CUDA(cudaMemcpyAsync(d_cells, m->h_cells, sizeof(int32_t) * B, cudaMemcpyHostToDevice, st));
+    s.cells = d_cells;
+
+    const size_t n_mu = (size_t)B * m->R, n_nu = m->is_vmf ? 0 : (size_t)B * m->Rnu;
+    s.eps_mu = s.eps_nu = nullptr;
+    if (eps || (flags & MMV_EPS_PHILOX)) {
+        float *d_eps = m->W("eps", sizeof(float) * (n_mu + n_nu));
+        NEED(d_eps);
+        if (eps) {
+            if (m->h_eps_cap < n_mu + n_nu) {
+                if (m->h_eps) cudaFreeHost(m->h_eps);
+                MMV_CUDA(cudaMallocHost(&m->h_eps, sizeof(float) * (n_mu + n_nu)));
+                m->h_eps_cap = n_mu + n_nu;
+            }
+            memcpy(m->h_eps, eps, sizeof(float) * (n_mu + n_nu));
+            MMV_CUDA(cudaMemcpyAsync(d_eps, m->h_eps, sizeof(float) * (n_mu + n_nu), cudaMemcpyHostToDevice, st));
+        } else {
+            static uint64_t draw = 0;
+            normal_kernel<<<(int)min_sz((n_mu + n_nu + 255) / 256, 1024), 256, 0, st>>>(d_eps, n_mu + n_nu, m->seed + 77,
+                                                                                     ++draw);
+            MMV_CUDA(cudaGetLastError());
+        }
+        s.eps_mu = d_eps;
+        s.eps_nu = n_nu ? d_eps + n_mu : nullptr;
+    }
+    return 0;
+}
+
+} // namespace
+
+extern "C" {
+
+int
+mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int64_t *boot_idx, const float *eps,
+         float kl_weight, int flags, mmv_loss_terms *out)
+{
+    MMV_CHECK(m && csr, "mmv_step: NULL handle");
+    MMV_CHECK(m->ctx == csr->ctx, "mmv_step: model and data live in different contexts");
+    MMV_CHECK(B > 0 && B < (1LL << 30), "mmv_step: batch size %ld", (long)B);
+    MMV_CHECK(csr->n_genes == m->D, "mmv_step: data has %ld features, model expects %ld", (long)csr->n_genes, (long)m->D);
+    MMV_CHECK(!csr->has_cov || csr->c_dim == m->C, "mmv_step: covariate dim %ld != model c_dim %ld", (long)csr->c_dim,
+              (long)m->C);
+    MMV_CHECK((flags & MMV_FWD) || flags == MMV_OPTIM, "mmv_step: flags must include MMV_FWD (or be MMV_OPTIM alone)");
+    MMV_CHECK(!(flags & MMV_BWD) || (flags & MMV_FWD), "mmv_step: MMV_BWD needs MMV_FWD");
+    MMV_CUDA(cudaSetDevice(m->ctx->device));
+    cudaStream_t st = m->ctx->stream;
+    const int nranks = m->ctx->nranks;
+    const size_t n_opt = m->train_all ? m->n_all : m->n_reg;
+
+    if (flags & MMV_FWD) {
+        step_t s;
+        s.m = m; s.csr = csr; s.B = (int)B; s.cov = csr->has_cov ? csr->cov : nullptr;
+        s.klw = kl_weight; s.inv_B = 1.f / (float)(B * nranks); s.bwd = (flags & MMV_BWD) != 0; s.st = st;
+        MMV_TRY(stage_inputs(m, csr, cells, B, boot_idx, eps, flags, s));
+        m->last_B = B;
+        MMV_CUDA(cudaMemsetAsync(m->acc, 0, sizeof(double) * 8, st));
+        if (s.bwd)   // adam.zero_grad() reaches the optimiser's tensors only (mmvae_alg.hh:306)
+            MMV_CUDA(cudaMemsetAsync(m->grads, 0, sizeof(float) * n_opt, st));
+        MMV_TRY(m->is_vmf ? vmf_forward_backward(s) : nb_forward_backward(s));
+    } else {
+        MMV_CUDA(cudaMemsetAsync(m->acc + 3, 0, sizeof(double), st));
+    }
+
+    if (nranks > 1 && (flags & MMV_FWD)) MMV_TRY(comm_allreduce_f64(m->ctx, m->acc, 8));
+    if (flags & MMV_OPTIM) {
+        MMV_TRY(comm_allreduce_f32(m->ctx, m->grads, n_opt));
+        MMV_TRY(launch_sumsq(m->grads, n_opt, m->acc + 3, m->ctx->num_sms, st));
+        adam_args_t a;
+        m->adam_t += 1;
+        const double bc1 = 1. - std::pow(0.9, (double)m->adam_t), bc2 = 1. - std::pow(0.999, (double)m->adam_t);
+        a.param = m->params; a.grad = m->grads; a.m = m->adam_m; a.v = m->adam_v; a.n = n_opt;
+        a.sumsq = m->acc + 3; a.norm_out = m->fscal + 1;
+        a.max_norm = m->grad_clip; a.weight_decay = m->weight_decay;
+        a.bc2_sqrt = (float)std::sqrt(bc2); a.neg_step = (float)(-(double)m->lr / bc1);
+        MMV_TRY(launch_adam(a, m->ctx->num_sms, st));
+    }
+    if (!out) return 0;
+
+    MMV_CUDA(cudaMemcpyAsync(m->h_acc, m->acc, sizeof(double) * 8, cudaMemcpyDeviceToHost, st));
+    MMV_CUDA(cudaMemcpyAsync(m->h_fscal, m->fscal, sizeof(float) * 8, cudaMemcpyDeviceToHost, st));
+    MMV_CUDA(cudaStreamSynchronize(st));
+    const double n = (double)B * nranks;
+    if (m->is_vmf) {   // vmf.hh:439
+        out->recon = (float)m->h_acc[5];
+        out->kl_mu = (float)m->h_acc[1];
+        out->kl_nu = 0.f;
+        out->loss = (float)(m->h_acc[1] / n * kl_weight - m->h_acc[5] / n);
+    } else {           // nb.hh:542-547
+        out->recon = (float)m->h_acc[0];
+        out->kl_mu = (float)m->h_acc[1];
+        out->kl_nu = (float)m->h_acc[2];
+        out->loss = (float)((m->h_acc[0] + kl_weight * m->h_acc[1] + kl_weight * m->h_acc[2]) / n);
+    }
+    out->grad_norm = (flags & MMV_OPTIM) ? m->h_fscal[1] : 0.f;
+    return 0;
+}
+
+int
+mmv_get_output(mmv_model *m, const char *name, float *host, int64_t n)
+{
+    MMV_CHECK(m && name && host, "mmv_get_output: NULL");
+    const int64_t B = m->last_B;
+    std::string key = name;
+    int64_t want = 0;
+    const float *src = nullptr;
+    if (m->is_vmf) {
+        if (key == "mean") { key = "mu_mean"; want = B * m->R; }
+        else if (key == "lnvar") { key = "mu_lnvar"; want = B * m->R; }
+        else if (key == "recon") want = B * m->D;
+        else if (key == "kappa") { src = m->fscal; want = 1; }
+        else MMV_CHECK(false, "mmv_get_output: unknown output '%s'", name);
+    } else {
+        if (key == "mu_mean" || key == "mu_lnvar") want = B * m->R;
+        else if (key == "nu_mean" || key == "nu_lnvar") want = B * m->Rnu;
+        else if (key == "recon_mu" || key == "recon_nu") want = B * m->D;
+        else if (key == "recon_depth") { key = "dpre"; want = B; }
+        else MMV_CHECK(false, "mmv_get_output: unknown output '%s'", name);
+    }
+    MMV_CHECK(n == want, "mmv_get_output: '%s' has %ld elements, got %ld", name, (long)want, (long)n);
+    if (!src) {
+        auto it = m->ws.find(key);
+        MMV_CHECK(it != m->ws.end() && it->second.p, "mmv_get_output: '%s' not available (run a step; recon_* need debug_outputs)", name);
+        src = it->second.as<float>();
+    }
+    MMV_CUDA(cudaSetDevice(m->ctx->device));
+    MMV_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    MMV_CUDA(cudaMemcpy(host, src, sizeof(float) * n, cudaMemcpyDeviceToHost));
+    if (std::string(name) == "recon_depth")   // nb.hh:498: softplus of the pre-activation kept on device
+        for (int64_t i = 0; i < n; ++i) host[i] = host[i] > 20.f ? host[i] : std::log1p(std::exp(host[i]));
+    return 0;
+}
+
+int
+mmv_encode(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, float *mean, float *lnvar)
+{
+    MMV_CHECK(m && csr && mean && lnvar, "mmv_encode: NULL");
+    MMV_CHECK(m->ctx == csr->ctx, "mmv_encode: model and data live in different contexts");
+    MMV_CHECK(B > 0 && csr->n_genes == m->D, "mmv_encode: bad batch or feature count");
+    MMV_CUDA(cudaSetDevice(m->ctx->device));
+    cudaStream_t st = m->ctx->stream;
+    step_t s;
+    s.m = m; s.csr = csr; s.B = (int)B; s.cov = nullptr; s.klw = 0.f; s.inv_B = 1.f / (float)B; s.bwd = false; s.st = st;
+    MMV_TRY(stage_inputs(m, csr, cells, B, nullptr, nullptr, 0, s));
+    m->last_B = B;
+    const int D = (int)m->D;
+    const linear_t &L0 = m->enc[0];
+    const int h1 = L0.out;
+    float *inv_t = WS("inv_t", D); NEED(inv_t);
+    float *bias_eff = WS("bias_eff", h1); NEED(bias_eff);
+    senc_args_t e;
+    e.indptr = csr->indptr; e.indices = csr->indices; e.vals = csr->vals; e.cells = s.cells;
+    e.B = (int)B; e.D = D; e.W1T = m->P(L0.w); e.h1 = h1; e.inv_t = inv_t; e.bias_eff = bias_eff; e.relu = m->relu;
+    e.H1 = WS("enc_act0", (size_t)B * h1); NEED(e.H1);
+    if (m->is_vmf) {
+        MMV_TRY(launch_gene_prep(m->P(m->t_ln_x_sd), 1e-2f / (float)D, inv_t, D, st));
+        float *col_scale = WS("ang_scale0", h1); NEED(col_scale);
+        MMV_TRY(launch_angular_scale(m->P(L0.w), col_scale, h1, D, 1, (size_t)h1, st));
+        MMV_CUDA(cudaMemsetAsync(bias_eff, 0, sizeof(float) * h1, st));
+        MMV_TRY(launch_senc_bias(m->P(L0.w), m->P(m->t_x_mean), inv_t, col_scale, bias_eff, D, h1, 1, st));
+        e.angular = 1; e.col_scale = col_scale;
+        e.rownorm = WS("rownorm", B); NEED(e.rownorm);
+    } else {
+        MMV_TRY(launch_gene_prep(m->P(m->t_ln_x_sd), 1e-4f, inv_t, D, st));
+        MMV_CUDA(cudaMemcpyAsync(bias_eff, m->P(L0.b), sizeof(float) * h1, cudaMemcpyDeviceToDevice, st));
+        MMV_TRY(launch_senc_bias(m->P(L0.w), m->P(m->t_x_mean), inv_t, nullptr, bias_eff, D, h1, 0, st));
+    }
+    MMV_TRY(launch_senc_fwd(e, st));
+    MMV_CUDA(cudaMemsetAsync(m->acc, 0, sizeof(double) * 8, st));
+    MMV_TRY(encoder_forward(s, /*with_covar=*/false));   // recorder encodes WITHOUT covariates
+    MMV_CUDA(cudaMemcpyAsync(mean, m->ws["mu_mean"].p, sizeof(float) * B * m->R, cudaMemcpyDeviceToHost, st));
+    MMV_CUDA(cudaMemcpyAsync(lnvar, m->ws["mu_lnvar"].p, sizeof(float) * B * m->R, cudaMemcpyDeviceToHost, st));
+    MMV_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+} // extern "C"

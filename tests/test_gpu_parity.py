@@ -1,0 +1,146 @@
+"""Parity of the CUDA path (through the C ABI) against the golden vectors the
+reference itself produced (tests/golden/*.npz) and against the oracle.
+
+Tolerance (BASELINE.json north_star): per-step ELBO terms and gradients within
+1e-4 relative in fp32; measured here as |a-b|/|b| for scalars and relative
+Frobenius error per tensor.  Minibatch indexing (cells, bootstrap) is exact.
+"""
+import importlib
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import MODEL_CASES, Golden, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def mmv():
+    return importlib.import_module("mm-vae_b200")
+
+
+@pytest.fixture(scope="module")
+def ctx(mmv):
+    c = mmv.Context(0)
+    yield c
+    c.close()
+
+
+def build_model(mmv, ctx, g):
+    cfg = g.cfg
+    enc = [] if cfg["enc"] == "-" else [int(v) for v in cfg["enc"].split(",")]
+    dec = [] if cfg["dec"] == "-" else [int(v) for v in cfg["dec"].split(",")]
+    if cfg["model"] == "nb":
+        m = mmv.Model.nb(ctx, cfg["D"], cfg["C"], enc, dec, cfg["R"], cfg["H"], cfg["Rnu"])
+    else:
+        m = mmv.Model.vmf(ctx, cfg["D"], cfg["C"], cfg["R"], enc, dec,
+                          cfg.get("kappa_min", 0.1), cfg.get("kappa_max", 10.0))
+    m.set_params(g.params("init"))
+    m.set_option("train_all_layers", cfg.get("train_all", 0))
+    m.set_option("frozen_grads", 1)
+    m.set_option("debug_outputs", 1)
+    return m
+
+
+def scalar_close(a, b, tol=TOL):
+    return abs(a - b) <= tol * max(abs(b), 1e-6)
+
+
+@pytest.mark.parametrize("case", MODEL_CASES)
+def test_step_matches_reference(mmv, ctx, case):
+    g = Golden(case)
+    cfg = g.cfg
+    B, D = cfg["B"], cfg["D"]
+    csr = mmv.CSR.from_dense(ctx, g.a["x"], g.a["c"])
+    m = build_model(mmv, ctx, g)
+    info = m.param_info()
+    assert set(info) == set(g.params("init")), set(info) ^ set(g.params("init"))
+    worst = {}
+    for s in range(cfg["steps"]):
+        cells = g.a["ridx"][s]
+        eps = g.eps(s)
+        terms = m.step(csr, cells, eps=eps, kl_weight=cfg["kl"], flags=mmv.FWD | mmv.BWD)
+        ref = g.group(f"s{s}__out")
+        assert scalar_close(terms["loss"], float(ref["loss"][0])), (case, s, terms, float(ref["loss"][0]))
+        if cfg["model"] == "nb":
+            assert scalar_close(terms["recon"], float(ref["nllik"][0])), (case, s, "nllik", terms)
+            assert scalar_close(terms["kl_mu"], float(ref["kl_mu"][0]))
+            assert scalar_close(terms["kl_nu"], float(ref["kl_nu"][0]))
+            outs = {"mu_mean": B * cfg["R"], "mu_lnvar": B * cfg["R"], "nu_mean": B * cfg["Rnu"],
+                    "nu_lnvar": B * cfg["Rnu"], "recon_depth": B, "recon_mu": B * D, "recon_nu": B * D}
+        else:
+            assert scalar_close(terms["kl_mu"], float(ref["kl"][0]))
+            outs = {"mean": B * cfg["R"], "lnvar": B * cfg["R"], "kappa": 1, "recon": B * D}
+        for k, n in outs.items():
+            e = rel_err(m.output(k, n), ref[k])
+            worst[k] = max(worst.get(k, 0), e)
+            assert e < TOL, (case, s, "output", k, e)
+        gref = g.group(f"s{s}__grad")
+        for k, r in gref.items():
+            got = m.get_grad(k)
+            if np.linalg.norm(r) < 1e-12:
+                assert np.linalg.norm(got) < 1e-7, (case, s, "grad", k)
+                continue
+            e = rel_err(got, r)
+            worst["grad:" + k] = max(worst.get("grad:" + k, 0), e)
+            assert e < TOL, (case, s, "grad", k, e)
+        t2 = m.step(csr, cells, kl_weight=cfg["kl"], flags=mmv.OPTIM)
+        assert scalar_close(t2["grad_norm"], float(g.a[f"s{s}__gradnorm"][0])), (case, s, "gradnorm")
+        for k, r in g.params(f"s{s}").items():
+            e = rel_err(m.get_param(k), r)
+            assert e < TOL, (case, s, "param", k, e)
+    m.close()
+    csr.close()
+
+
+@pytest.mark.parametrize("case", MODEL_CASES)
+def test_encode_recorder_path(mmv, ctx, case):
+    """mmv_encode = eval-mode encoder without covariates (nb.hh:419-431, vmf.hh:267-281)."""
+    g = Golden(case)
+    csr = mmv.CSR.from_dense(ctx, g.a["x"], g.a["c"])
+    m = build_model(mmv, ctx, g)
+    mean, lnvar = m.encode(csr, np.arange(g.cfg["B0"]), g.cfg["R"])
+    assert rel_err(mean, g.a["enc__mean"]) < TOL
+    assert rel_err(lnvar, g.a["enc__lnvar"]) < TOL
+    m.close()
+    csr.close()
+
+
+def test_bootstrap_is_index_composition(mmv, ctx):
+    """step(cells, boot_idx) == step(cells[boot_idx]) bit for bit (mmvae_alg.hh:292-301)."""
+    g = Golden("nb_small")
+    csr = mmv.CSR.from_dense(ctx, g.a["x"], g.a["c"])
+    rng = np.random.default_rng(3)
+    cells = rng.permutation(g.cfg["B0"])[:10]
+    boot = rng.integers(0, 10, 10)
+    eps = [rng.normal(size=(10, g.cfg["R"])), rng.normal(size=(10, g.cfg["Rnu"]))]
+    out = []
+    for kw in (dict(cells=cells, boot_idx=boot), dict(cells=cells[boot])):
+        m = build_model(mmv, ctx, g)
+        t = m.step(csr, eps=eps, flags=mmv.FWD, **kw)
+        out.append((t, m.output("mu_mean", 10 * g.cfg["R"])))
+        m.close()
+    assert np.array_equal(out[0][1], out[1][1])
+    assert out[0][0]["kl_mu"] == out[1][0]["kl_mu"]
+    csr.close()
+
+
+def test_eval_mode_forward(mmv, ctx):
+    """eps=None -> z = mean (nb.hh:469-471): compare with the oracle."""
+    from oracle import model_oracle as mo
+    g = Golden("nb_deep")
+    csr = mmv.CSR.from_dense(ctx, g.a["x"], g.a["c"])
+    m = build_model(mmv, ctx, g)
+    cells = np.arange(g.cfg["B0"])
+    t = m.step(csr, cells, eps=None, kl_weight=0.7, flags=mmv.FWD)
+    P = {k: torch.from_numpy(v) for k, v in g.params("init").items()}
+    x, c = torch.from_numpy(g.a["x"]), torch.from_numpy(g.a["c"])
+    y = mo.nb_forward(P, x, c, None, None)
+    ref = mo.nb_loss(x, y, 0.7)
+    assert scalar_close(t["loss"], float(ref["loss"]))
+    assert scalar_close(t["recon"], float(ref["nllik"]))
+    m.close()
+    csr.close()
