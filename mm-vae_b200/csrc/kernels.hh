@@ -192,6 +192,8 @@ struct adam_args_t {
     const double *sumsq = nullptr;
     float *norm_out = nullptr;
     float max_norm = 1.f, weight_decay = 1e-4f, beta1 = 0.9f, beta2 = 0.999f, eps = 1e-8f;
+    // 1 - beta rounded from DOUBLE like libtorch's Scalar(1 - beta) (1.f - 0.999f is off by 1.3e-5)
+    float one_minus_beta1 = (float)(1.0 - 0.9), one_minus_beta2 = (float)(1.0 - 0.999);
     float bc2_sqrt = 1.f, neg_step = 0.f;
 };
 int launch_adam(const adam_args_t &a, int num_sms, cudaStream_t st);

@@ -42,8 +42,8 @@ adam_kernel(adam_args_t a)
         a.grad[i] = g;                       // clip_grad_norm_ scales .grad in place
         const float p = a.param[i];
         g = fmaf(a.weight_decay, p, g);
-        const float m = a.beta1 * a.m[i] + (1.f - a.beta1) * g;
-        const float v = a.beta2 * a.v[i] + ((1.f - a.beta2) * g) * g;
+        const float m = a.beta1 * a.m[i] + a.one_minus_beta1 * g;
+        const float v = a.beta2 * a.v[i] + (a.one_minus_beta2 * g) * g;
         a.m[i] = m;
         a.v[i] = v;
         const float denom = sqrtf(v) / a.bc2_sqrt + a.eps;

@@ -196,7 +196,9 @@ launch_vmf_likelihood(const vmf_lik_args_t &a, int num_sms, cudaStream_t stream)
 __global__ void
 vmf_kappa_kernel(const float *ln_kappa, float kmin, float kmax, float *kappa)
 {
-    const float e = expf(ln_kappa[0]);
+    // double exp, rounded once: at init ln_kappa = log(kappa_min) sits on the clamp edge and the
+    // reference's CPU expf lands just below kappa_min (grad masked)
+    const float e = (float)exp((double)ln_kappa[0]);
     kappa[0] = fminf(fmaxf(e, kmin), kmax);
 }
 
@@ -223,7 +225,7 @@ vmf_scalar_kernel(vmf_scalar_args_t s)
         // the data term is a per-cell sum (summed over ranks by the allreduce); the two
         // scalar terms are not, so each rank contributes its 1/nranks share
         const float dk = -(float)(tsum * (double)s.inv_B_global) + (-df / kappa + G) * s.inv_ranks;
-        const float ek = expf(s.ln_kappa[0]);
+        const float ek = (float)exp((double)s.ln_kappa[0]);
         const bool inside = ek >= s.kmin && ek <= s.kmax;
         s.dln_kappa[0] += inside ? dk * ek : 0.f;
     }
