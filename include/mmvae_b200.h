@@ -44,6 +44,8 @@ MMV_API const char *mmv_last_error(void);
 MMV_API int mmv_timer_start(mmv_ctx *ctx);
 MMV_API int mmv_timer_stop(mmv_ctx *ctx, float *elapsed_ms);   /* synchronises */
 MMV_API int mmv_ctx_num_sms(mmv_ctx *ctx, int *out);
+/* Number of kernels this library has launched in this process (bench accounting). */
+MMV_API int mmv_launch_count(int64_t *out);
 
 /* ---- resident sparse data: cells x genes CSR (+ dense covariates) ---------
  * replaces: mtx_data_block_t::read/torch_tensor/clear, mmvae_io.hh:81-88,208-256
@@ -61,6 +63,12 @@ MMV_API int mmv_csr_create(mmv_ctx *ctx, int64_t max_cells, int64_t max_nnz, int
                    mmv_csr **out);
 MMV_API int mmv_csr_update(mmv_csr *csr, int64_t n_cells, const int64_t *indptr, const int32_t *indices,
                    const float *values, const float *covar);
+/* Zero-copy: adopt CSR arrays that already live on the ctx's device (e.g. a shard
+ * generated or parsed there).  The arrays are BORROWED until mmv_csr_destroy.
+ * max_row_nnz = longest cell (sizes the per-step transpose workspace). */
+MMV_API int mmv_csr_wrap_device(mmv_ctx *ctx, int64_t n_cells, int64_t n_genes, int64_t nnz, int64_t max_row_nnz,
+                        const int64_t *d_indptr, const int32_t *d_indices, const float *d_values,
+                        const float *d_covar, int64_t c_dim, mmv_csr **out);
 MMV_API int mmv_csr_destroy(mmv_csr *csr);
 /* Pinned host allocation helpers for the streaming path. */
 MMV_API int mmv_host_alloc(void **out, int64_t bytes);
@@ -145,6 +153,12 @@ typedef struct {
 
 MMV_API int mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int64_t *boot_idx,
              const float *eps, float kl_weight, int flags, mmv_loss_terms *out);
+
+/* Per-kernel-group device times (CUDA events on the ctx stream), enabled with
+ * mmv_model_set_option(m, "profile", 1).  mmv_profile_read synchronises, returns the
+ * time and launch-group count accumulated for `name` since the last reset
+ * ("" resets everything).  Names: see DESIGN.md / bench.py. */
+MMV_API int mmv_profile_read(mmv_model *m, const char *name, float *total_ms, int *count);
 
 /* Forward outputs of the last step by name (tests / recorder): nb: "mu_mean",
  * "mu_lnvar", "nu_mean", "nu_lnvar", "recon_depth" and, with debug_outputs,

@@ -65,9 +65,11 @@ _PROTOS = {
     "mmv_timer_start": [_vp],
     "mmv_timer_stop": [_vp, C.POINTER(C.c_float)],
     "mmv_ctx_num_sms": [_vp, C.POINTER(C.c_int)],
+    "mmv_launch_count": [C.POINTER(_i64)],
     "mmv_csr_upload": [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _i64, C.POINTER(_vp)],
     "mmv_csr_create": [_vp, _i64, _i64, _i64, _i64, C.POINTER(_vp)],
     "mmv_csr_update": [_vp, _i64, _vp, _vp, _vp, _vp],
+    "mmv_csr_wrap_device": [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _i64, C.POINTER(_vp)],
     "mmv_csr_destroy": [_vp],
     "mmv_host_alloc": [C.POINTER(_vp), _i64],
     "mmv_host_free": [_vp],
@@ -81,6 +83,7 @@ _PROTOS = {
     "mmv_model_get_param": [_vp, C.c_char_p, _vp, _i64],
     "mmv_model_get_grad": [_vp, C.c_char_p, _vp, _i64],
     "mmv_step": [_vp, _vp, _vp, _i64, _vp, _vp, C.c_float, C.c_int, C.POINTER(LossTerms)],
+    "mmv_profile_read": [_vp, C.c_char_p, C.POINTER(C.c_float), C.POINTER(C.c_int)],
     "mmv_get_output": [_vp, C.c_char_p, _vp, _i64],
     "mmv_encode": [_vp, _vp, _vp, _i64, _vp, _vp],
     "mmv_comm_unique_id": [_vp],
@@ -147,6 +150,12 @@ class Context:
             self.h = C.c_void_p()
 
 
+def launch_count() -> int:
+    n = _i64()
+    _chk(lib.mmv_launch_count(C.byref(n)))
+    return int(n.value)
+
+
 def comm_unique_id() -> bytes:
     buf = (C.c_ubyte * 128)()
     _chk(lib.mmv_comm_unique_id(buf))
@@ -182,6 +191,15 @@ class CSR:
     def create(cls, ctx, max_cells, max_nnz, n_genes, c_dim=0):
         h = C.c_void_p()
         _chk(lib.mmv_csr_create(ctx.h, max_cells, max_nnz, n_genes, c_dim, C.byref(h)))
+        return cls(ctx, h)
+
+    @classmethod
+    def wrap_device(cls, ctx, n_cells, n_genes, nnz, max_row_nnz, d_indptr, d_indices, d_values, d_covar=0, c_dim=1):
+        """Adopt device arrays (raw pointers, e.g. torch tensor .data_ptr()); caller keeps them alive."""
+        h = C.c_void_p()
+        _chk(lib.mmv_csr_wrap_device(ctx.h, n_cells, n_genes, nnz, max_row_nnz, C.c_void_p(d_indptr),
+                                     C.c_void_p(d_indices), C.c_void_p(d_values),
+                                     C.c_void_p(d_covar) if d_covar else None, c_dim, C.byref(h)))
         return cls(ctx, h)
 
     def update(self, n_cells, indptr, indices, values, covar=None):
@@ -294,6 +312,11 @@ class Model:
         _chk(lib.mmv_step(self.h, csr.h, _ptr(cells), len(cells), _ptr(boot), _ptr(eps), kl_weight, flags,
                           C.byref(terms) if want_terms else None))
         return terms.as_dict() if want_terms else None
+
+    def profile_read(self, name: str = "") -> Tuple[float, int]:
+        ms, cnt = C.c_float(), C.c_int()
+        _chk(lib.mmv_profile_read(self.h, name.encode(), C.byref(ms), C.byref(cnt)))
+        return float(ms.value), int(cnt.value)
 
     def output(self, name: str, n: int) -> np.ndarray:
         out = np.empty(n, dtype=np.float32)

@@ -67,12 +67,12 @@ launch_angular_scale(const float *W, float *scale, int units, int inputs, size_t
     if (us == 1) {
         const int chunk = 256;
         dim3 grid(ceil_div(units, 128), ceil_div(inputs, chunk));
-        ang_reduce_units_kernel<0><<<grid, 128, 0, st>>>(W, nullptr, nullptr, scale, units, inputs, is, chunk);
+        ang_reduce_units_kernel<0><<<grid, 128, 0, st>>>(W, nullptr, nullptr, scale, units, inputs, is, chunk); ::mmv::count_launch();
     } else {
         MMV_CHECK(is == 1, "angular: unsupported weight strides");
-        ang_reduce_inputs_kernel<0><<<ceil_div(units, 4), 128, 0, st>>>(W, nullptr, nullptr, scale, units, inputs, us);
+        ang_reduce_inputs_kernel<0><<<ceil_div(units, 4), 128, 0, st>>>(W, nullptr, nullptr, scale, units, inputs, us); ::mmv::count_launch();
     }
-    ang_finish_scale_kernel<<<ceil_div(units, 128), 128, 0, st>>>(scale, units);
+    ang_finish_scale_kernel<<<ceil_div(units, 128), 128, 0, st>>>(scale, units); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -90,7 +90,7 @@ int
 launch_angular_materialize(const float *W, const float *scale, float *Wp, int units, int inputs, cudaStream_t st)
 {
     const size_t n = (size_t)units * inputs;
-    ang_materialize_kernel<<<(int)min_sz((n + 255) / 256, 2048), 256, 0, st>>>(W, scale, Wp, units, inputs);
+    ang_materialize_kernel<<<(int)min_sz((n + 255) / 256, 2048), 256, 0, st>>>(W, scale, Wp, units, inputs); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -122,14 +122,14 @@ launch_angular_bwd(const float *W, const float *dWp, const float *scale, float *
     if (us == 1) {
         const int chunk = 256;
         dim3 grid(ceil_div(units, 128), ceil_div(inputs, chunk));
-        ang_reduce_units_kernel<1><<<grid, 128, 0, st>>>(W, dWp, scale, dot, units, inputs, is, chunk);
+        ang_reduce_units_kernel<1><<<grid, 128, 0, st>>>(W, dWp, scale, dot, units, inputs, is, chunk); ::mmv::count_launch();
     } else {
         MMV_CHECK(is == 1, "angular: unsupported weight strides");
-        ang_reduce_inputs_kernel<1><<<ceil_div(units, 4), 128, 0, st>>>(W, dWp, scale, dot, units, inputs, us);
+        ang_reduce_inputs_kernel<1><<<ceil_div(units, 4), 128, 0, st>>>(W, dWp, scale, dot, units, inputs, us); ::mmv::count_launch();
     }
     const size_t n = (size_t)units * inputs;
     ang_bwd_apply_kernel<<<(int)min_sz((n + 255) / 256, 2048), 256, 0, st>>>(W, dWp, scale, dot, dW, units,
-                                                                               inputs, us, is);
+                                                                               inputs, us, is); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }

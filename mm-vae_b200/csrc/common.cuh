@@ -17,6 +17,8 @@ constexpr int kWarp = 32;
 // reference's "ELOG + EXIT_FAILURE" convention on the host side).
 // ---------------------------------------------------------------------------
 void set_error(const char *fmt, ...);
+void count_launch();          // one call per kernel launch (mmv_launch_count)
+long long launch_count();
 const char *get_error();
 
 #define MMV_CUDA(expr)                                                           \

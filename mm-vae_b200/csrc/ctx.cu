@@ -25,6 +25,20 @@ get_error()
     return g_err;
 }
 
+static long long g_launches = 0;
+
+void
+count_launch()
+{
+    ++g_launches;
+}
+
+long long
+launch_count()
+{
+    return g_launches;
+}
+
 } // namespace mmv
 
 using namespace mmv;
@@ -72,6 +86,14 @@ mmv_ctx_destroy(mmv_ctx *c)
     cudaEventDestroy(c->ev1);
     cudaStreamDestroy(c->stream);
     delete c;
+    return 0;
+}
+
+int
+mmv_launch_count(int64_t *out)
+{
+    MMV_CHECK(out, "mmv_launch_count: NULL");
+    *out = launch_count();
     return 0;
 }
 
@@ -228,15 +250,42 @@ mmv_csr_upload(mmv_ctx *ctx, int64_t n_cells, int64_t n_genes, const int64_t *in
 }
 
 int
+mmv_csr_wrap_device(mmv_ctx *ctx, int64_t n_cells, int64_t n_genes, int64_t nnz, int64_t max_row_nnz,
+                    const int64_t *d_indptr, const int32_t *d_indices, const float *d_values, const float *d_covar,
+                    int64_t c_dim, mmv_csr **out)
+{
+    MMV_CHECK(ctx && d_indptr && d_indices && d_values && out, "mmv_csr_wrap_device: NULL");
+    MMV_CHECK(n_cells > 0 && n_genes > 0 && n_genes < (1LL << 31) && nnz >= 0 && max_row_nnz >= 0,
+              "mmv_csr_wrap_device: bad sizes");
+    mmv_csr *s = new mmv_csr();
+    s->ctx = ctx;
+    s->borrowed = true;
+    s->n_cells = s->cap_cells = n_cells;
+    s->n_genes = n_genes;
+    s->nnz = s->cap_nnz = nnz;
+    s->max_row_nnz = max_row_nnz;
+    s->indptr = const_cast<int64_t *>(d_indptr);
+    s->indices = const_cast<int32_t *>(d_indices);
+    s->vals = const_cast<float *>(d_values);
+    s->cov = const_cast<float *>(d_covar);
+    s->has_cov = d_covar != nullptr;
+    s->c_dim = d_covar ? c_dim : (c_dim > 0 ? c_dim : 1);
+    *out = s;
+    return 0;
+}
+
+int
 mmv_csr_destroy(mmv_csr *s)
 {
     if (!s) return 0;
     cudaSetDevice(s->ctx->device);
     cudaStreamSynchronize(s->ctx->stream);
-    cudaFree(s->indptr);
-    cudaFree(s->indices);
-    cudaFree(s->vals);
-    cudaFree(s->cov);
+    if (!s->borrowed) {
+        cudaFree(s->indptr);
+        cudaFree(s->indices);
+        cudaFree(s->vals);
+        cudaFree(s->cov);
+    }
     delete s;
     return 0;
 }

@@ -29,7 +29,7 @@ vec_combine_kernel(const float *a, const float *b, const float *c, float sb, flo
 int
 launch_gene_prep(const float *ln_x_sd, float eps, float *inv_t, int D, cudaStream_t st)
 {
-    gene_prep_kernel<<<ceil_div(D, 256), 256, 0, st>>>(ln_x_sd, eps, inv_t, D);
+    gene_prep_kernel<<<ceil_div(D, 256), 256, 0, st>>>(ln_x_sd, eps, inv_t, D); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -38,7 +38,7 @@ int
 launch_vec_combine(const float *a, const float *b, const float *c, float sb, float sc, float *out, int n,
                    cudaStream_t st)
 {
-    vec_combine_kernel<<<ceil_div(n, 256), 256, 0, st>>>(a, b, c, sb, sc, out, n);
+    vec_combine_kernel<<<ceil_div(n, 256), 256, 0, st>>>(a, b, c, sb, sc, out, n); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -100,7 +100,7 @@ int
 launch_reparam_fwd(const reparam_args_t &a, cudaStream_t st)
 {
     const int n = a.B * a.R;
-    reparam_fwd_kernel<<<min(ceil_div(n, 256), 1024), 256, 0, st>>>(a);
+    reparam_fwd_kernel<<<min(ceil_div(n, 256), 1024), 256, 0, st>>>(a); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -109,7 +109,7 @@ int
 launch_reparam_bwd(const reparam_args_t &a, cudaStream_t st)
 {
     const int n = a.B * a.R;
-    reparam_bwd_kernel<<<min(ceil_div(n, 256), 1024), 256, 0, st>>>(a);
+    reparam_bwd_kernel<<<min(ceil_div(n, 256), 1024), 256, 0, st>>>(a); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -152,7 +152,7 @@ launch_colsum(colsum_args_t a, cudaStream_t st)
     MMV_CHECK(a.C <= 8, "colsum: covariate dim %d > 8 not supported", a.C);
     a.rows_per_cta = 64;
     dim3 grid(ceil_div(a.N, 128), ceil_div(a.M, a.rows_per_cta));
-    colsum_kernel<<<grid, 128, 0, st>>>(a);
+    colsum_kernel<<<grid, 128, 0, st>>>(a); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -169,7 +169,7 @@ int
 launch_relu_bwd(float *dX, const float *Y, size_t n, cudaStream_t st)
 {
     if (n == 0) return 0;
-    relu_bwd_kernel<<<(int)min_sz((n + 255) / 256, 4096), 256, 0, st>>>(dX, Y, n);
+    relu_bwd_kernel<<<(int)min_sz((n + 255) / 256, 4096), 256, 0, st>>>(dX, Y, n); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }

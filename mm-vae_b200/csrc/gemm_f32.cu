@@ -106,6 +106,7 @@ launch_gemm_f32(const gemm_args_t &g, cudaStream_t stream)
     else if (!g.transA && g.transB) gemm_f32_kernel<false, true><<<grid, GT, 0, stream>>>(g);
     else if (g.transA && !g.transB) gemm_f32_kernel<true, false><<<grid, GT, 0, stream>>>(g);
     else gemm_f32_kernel<true, true><<<grid, GT, 0, stream>>>(g);
+    ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }

@@ -28,6 +28,7 @@ struct mmv_csr {
     float *vals = nullptr;
     float *cov = nullptr;      // [n_cells x c_dim]; nullptr / !has_cov = all ones
     bool has_cov = false;
+    bool borrowed = false;     // device arrays owned by the caller (mmv_csr_wrap_device)
     size_t h2d_bytes = 0;      // bytes copied by the last update (bench accounting)
 };
 

@@ -122,6 +122,28 @@ struct mmv_model {
     size_t h_eps_cap = 0;
     int64_t h_cells_cap = 0;
 
+    // profiling (cudaEvent pairs per kernel group, read by mmv_profile_read)
+    bool profile = false;
+    struct prof_rec_t { int id; cudaEvent_t e0, e1; };
+    std::vector<std::string> prof_names;
+    std::vector<prof_rec_t> prof_recs;
+    std::vector<cudaEvent_t> prof_pool;
+    std::vector<double> prof_ms;
+    std::vector<int> prof_cnt;
+    cudaEvent_t prof_event()
+    {
+        cudaEvent_t e;
+        if (!prof_pool.empty()) { e = prof_pool.back(); prof_pool.pop_back(); return e; }
+        cudaEventCreate(&e);
+        return e;
+    }
+    int prof_id(const char *name)
+    {
+        for (size_t i = 0; i < prof_names.size(); ++i) if (prof_names[i] == name) return (int)i;
+        prof_names.push_back(name); prof_ms.push_back(0.); prof_cnt.push_back(0);
+        return (int)prof_names.size() - 1;
+    }
+
     float *P(int t) const { return params + tensors[t].off; }
     float *G(int t) const { return grads + tensors[t].off; }
     float *W(const std::string &k, size_t bytes)
@@ -407,6 +429,7 @@ mmv_model_set_option(mmv_model *m, const char *key, double value)
     else if (k == "train_all_layers") m->train_all = value != 0;
     else if (k == "frozen_grads") m->frozen_grads = value != 0;
     else if (k == "debug_outputs") m->debug_outputs = value != 0;
+    else if (k == "profile") m->profile = value != 0;
     else if (k == "max_batch") { /* capacity hint; buffers grow on demand */ }
     else MMV_CHECK(false, "mmv_model_set_option: unknown key '%s'", key);
     return 0;
@@ -504,10 +527,32 @@ int
 axpy(float *y, const float *x, float a, size_t n, cudaStream_t st)
 {
     if (n == 0) return 0;
-    axpy_kernel<<<(int)min_sz((n + 255) / 256, 2048), 256, 0, st>>>(y, x, a, n);
+    axpy_kernel<<<(int)min_sz((n + 255) / 256, 2048), 256, 0, st>>>(y, x, a, n); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }
+
+struct prof_scope_t {   // records a cudaEvent pair around a kernel group when profiling is on
+    mmv_model *m;
+    size_t idx = 0;
+    bool on;
+    prof_scope_t(mmv_model *m_, const char *name) : m(m_), on(m_->profile)
+    {
+        if (!on) return;
+        mmv_model::prof_rec_t r;
+        r.id = m->prof_id(name);
+        r.e0 = m->prof_event();
+        r.e1 = m->prof_event();
+        cudaEventRecord(r.e0, m->ctx->stream);
+        m->prof_recs.push_back(r);
+        idx = m->prof_recs.size() - 1;
+    }
+    ~prof_scope_t()
+    {
+        if (on) cudaEventRecord(m->prof_recs[idx].e1, m->ctx->stream);
+    }
+};
+#define PROF(name) prof_scope_t _prof_scope(m, name)
 
 struct step_t {
     mmv_model *m;
@@ -526,8 +571,11 @@ struct step_t {
 
 // Y = X W^T (+ b)
 int
-lin_fwd(const step_t &s, const float *X, int in, const float *W, const float *b, int out, float *Y, bool relu)
+lin_fwd(const step_t &s, const float *X, int in, const float *W, const float *b, int out, float *Y, bool relu,
+        const char *tag = "gemm_other")
 {
+    mmv_model *m = s.m;
+    PROF(tag);
     gemm_args_t g;
     g.A = X; g.lda = in; g.B = W; g.ldb = in; g.transB = 1;
     g.C = Y; g.ldc = out; g.M = s.B; g.N = out; g.K = in; g.bias = b; g.relu = relu ? 1 : 0;
@@ -536,8 +584,11 @@ lin_fwd(const step_t &s, const float *X, int in, const float *W, const float *b,
 
 // dX = dY W
 int
-lin_bwd_data(const step_t &s, const float *dY, int out, const float *W, int in, float *dX)
+lin_bwd_data(const step_t &s, const float *dY, int out, const float *W, int in, float *dX,
+             const char *tag = "gemm_other")
 {
+    mmv_model *m = s.m;
+    PROF(tag);
     gemm_args_t g;
     g.A = dY; g.lda = out; g.B = W; g.ldb = in;
     g.C = dX; g.ldc = in; g.M = s.B; g.N = in; g.K = out;
@@ -546,15 +597,19 @@ lin_bwd_data(const step_t &s, const float *dY, int out, const float *W, int in, 
 
 // dW += dY^T X ; db += colsum(dY)
 int
-lin_bwd_weight(const step_t &s, const float *dY, int out, const float *X, int in, float *dW, float *db, float beta = 1.f)
+lin_bwd_weight(const step_t &s, const float *dY, int out, const float *X, int in, float *dW, float *db, float beta = 1.f,
+               const char *tag = "gemm_other")
 {
+    mmv_model *m = s.m;
     if (dW) {
+        PROF(tag);
         gemm_args_t g;
         g.A = dY; g.lda = out; g.transA = 1; g.B = X; g.ldb = in;
         g.C = dW; g.ldc = in; g.M = out; g.N = in; g.K = s.B; g.beta = beta;
         MMV_TRY(launch_gemm_f32(g, s.st));
     }
     if (db) {
+        PROF("colsum");
         colsum_args_t c;
         c.X = dY; c.M = s.B; c.N = out; c.ldx = out; c.out_sum = db;
         MMV_TRY(launch_colsum(c, s.st));
@@ -614,7 +669,7 @@ decoder_forward(const step_t &s)
     }
     const linear_t &L = m->dec[nd - 1];
     float *G = WS("G", (size_t)B * D); NEED(G);
-    return lin_fwd(s, h, L.in, m->P(L.w), nullptr, D, G, false);
+    return lin_fwd(s, h, L.in, m->P(L.w), nullptr, D, G, false, "gemm_dec_last_fwd");
 }
 
 // backward through the decoder given dG (in "G", in place) -> "dz"
@@ -631,10 +686,11 @@ decoder_backward(const step_t &s)
         const bool last = l == nd - 1;
         // bias of the last layer is handled with the other per-gene sums by the caller
         MMV_TRY(lin_bwd_weight(s, dY, L.out, X, L.in, m->want_grad(L.w) ? m->G(L.w) : nullptr,
-                               (!last && m->want_grad(L.b)) ? m->G(L.b) : nullptr));
+                               (!last && m->want_grad(L.b)) ? m->G(L.b) : nullptr, 1.f,
+                               last ? "gemm_dec_last_dw" : "gemm_other"));
         float *dX = l == 0 ? WS("dz", (size_t)B * R) : WS("d_dec" + std::to_string(l - 1), (size_t)B * L.in);
         NEED(dX);
-        MMV_TRY(lin_bwd_data(s, dY, L.out, m->P(L.w), L.in, dX));
+        MMV_TRY(lin_bwd_data(s, dY, L.out, m->P(L.w), L.in, dX, last ? "gemm_dec_last_dx" : "gemm_other"));
         if (l > 0 && m->relu) MMV_TRY(launch_relu_bwd(dX, X, (size_t)B * L.in, s.st));
         dY = dX;
     }
@@ -747,7 +803,10 @@ nb_forward_backward(const step_t &s)
     e.WnuT = m->P(m->nu_enc.w); e.bnu = m->P(m->nu_enc.b); e.H = H;
     e.wdepth = m->P(m->depth.w); e.bdepth = m->P(m->depth.b);
     e.Hnu = WS("Hnu", (size_t)B * H); e.dpre = WS("dpre", B); NEED(e.Hnu); NEED(e.dpre);
-    MMV_TRY(launch_senc_fwd(e, s.st));
+    {
+        PROF("senc_fwd");
+        MMV_TRY(launch_senc_fwd(e, s.st));
+    }
 
     MMV_TRY(encoder_forward(s, true));
 
@@ -787,11 +846,15 @@ nb_forward_backward(const step_t &s)
         MMV_CUDA(cudaMemsetAsync(k.col_du, 0, sizeof(float) * D, s.st));
         MMV_CUDA(cudaMemsetAsync(k.col_duz, 0, sizeof(float) * D * Rnu, s.st));
     }
-    MMV_TRY(launch_nb_likelihood(k, m->ctx->num_sms, s.st));
+    {
+        PROF("nb_likelihood");
+        MMV_TRY(launch_nb_likelihood(k, m->ctx->num_sms, s.st));
+    }
     if (!s.bwd) return 0;
 
     // per-gene sums of dlogits: mu_decoding.bias, covar_decoding.{bias,weight}, mu_bias
     {
+        PROF("colsum_dlogits");
         colsum_args_t c;
         c.X = k.dlogits; c.M = B; c.N = D; c.ldx = D;
         c.out_sum = m->want_grad(Ld.b) ? m->G(Ld.b) : nullptr;
@@ -823,7 +886,10 @@ nb_forward_backward(const step_t &s)
         MMV_TRY(launch_colsum(c2, s.st));
     }
 
-    MMV_TRY(build_csc(s, nullptr));
+    {
+        PROF("batch_csc");
+        MMV_TRY(build_csc(s, nullptr));
+    }
     senc_bwd_args_t b;
     b.gene_ptr = m->ws["csc_ptr"].as<int>(); b.ent_row = m->ws["csc_row"].as<int>();
     b.ent_l = m->ws["csc_l"].as<float>(); b.ent_x = m->ws["csc_x"].as<float>();
@@ -833,6 +899,7 @@ nb_forward_backward(const step_t &s)
     b.dW1T = m->want_grad(L0.w) ? m->G(L0.w) : nullptr;
     b.dx_mean = m->G(m->t_x_mean); b.dln_x_sd = m->G(m->t_ln_x_sd);
     b.dHnu = dHnu; b.ddpre = k.ddpre; b.dWnuT = m->G(m->nu_enc.w); b.dwdepth = m->G(m->depth.w);
+    PROF("senc_bwd");
     return launch_senc_bwd(b, s.st);
 }
 
@@ -861,7 +928,10 @@ vmf_forward_backward(const step_t &s)
     e.B = B; e.D = D; e.angular = 1; e.W1T = m->P(L0.w); e.h1 = h1; e.inv_t = inv_t; e.bias_eff = bias_eff;
     e.col_scale = col_scale; e.relu = m->relu;
     e.H1 = WS("enc_act0", (size_t)B * h1); e.rownorm = WS("rownorm", B); NEED(e.H1); NEED(e.rownorm);
-    MMV_TRY(launch_senc_fwd(e, s.st));
+    {
+        PROF("senc_fwd");
+        MMV_TRY(launch_senc_fwd(e, s.st));
+    }
 
     MMV_TRY(encoder_forward(s, true));
     MMV_TRY(decoder_forward(s));
@@ -882,7 +952,10 @@ vmf_forward_backward(const step_t &s)
         MMV_CUDA(cudaMemsetAsync(k.col_dq, 0, sizeof(float) * D, s.st));
         MMV_CUDA(cudaMemsetAsync(k.col_dqc, 0, sizeof(float) * D * C, s.st));
     }
-    MMV_TRY(launch_vmf_likelihood(k, m->ctx->num_sms, s.st));
+    {
+        PROF("vmf_likelihood");
+        MMV_TRY(launch_vmf_likelihood(k, m->ctx->num_sms, s.st));
+    }
 
     // scalar part: loss constant, lbessel (operators.hh:49-101) and d ln_kappa (operators.hh:13-47)
     vmf_scalar_args_t sc;
@@ -912,7 +985,10 @@ vmf_forward_backward(const step_t &s)
     MMV_TRY(decoder_backward(s));
     MMV_TRY(encoder_backward(s, true));
 
-    MMV_TRY(build_csc(s, e.rownorm));
+    {
+        PROF("batch_csc");
+        MMV_TRY(build_csc(s, e.rownorm));
+    }
     float *dWeff = WS("dW1eff", (size_t)D * h1); NEED(dWeff);
     float *dot = WS("ang_dot", std::max(h1, 1)); NEED(dot);
     senc_bwd_args_t b;
@@ -923,7 +999,10 @@ vmf_forward_backward(const step_t &s)
     b.W1T = m->P(L0.w); b.col_scale = col_scale; b.inv_t = inv_t;
     b.x_mean = m->P(m->t_x_mean); b.ln_x_sd = m->P(m->t_ln_x_sd);
     b.dW1T = dWeff; b.dx_mean = m->G(m->t_x_mean); b.dln_x_sd = m->G(m->t_ln_x_sd);
-    MMV_TRY(launch_senc_bwd(b, s.st));
+    {
+        PROF("senc_bwd");
+        MMV_TRY(launch_senc_bwd(b, s.st));
+    }
     if (m->want_grad(L0.w))
         MMV_TRY(launch_angular_bwd(m->P(L0.w), dWeff, col_scale, dot, m->G(L0.w), h1, D, 1, (size_t)h1, s.st));
     return 0;
@@ -998,7 +1077,7 @@ stage_inputs(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const 
         } else {
             static uint64_t draw = 0;
             normal_kernel<<<(int)min_sz((n_mu + n_nu + 255) / 256, 1024), 256, 0, st>>>(d_eps, n_mu + n_nu, m->seed + 77,
-                                                                                     ++draw);
+                                                                                     ++draw); ::mmv::count_launch();
             MMV_CUDA(cudaGetLastError());
         }
         s.eps_mu = d_eps;
@@ -1044,7 +1123,11 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
 
     if (nranks > 1 && (flags & MMV_FWD)) MMV_TRY(comm_allreduce_f64(m->ctx, m->acc, 8));
     if (flags & MMV_OPTIM) {
-        MMV_TRY(comm_allreduce_f32(m->ctx, m->grads, n_opt));
+        {
+            PROF("allreduce");
+            MMV_TRY(comm_allreduce_f32(m->ctx, m->grads, n_opt));
+        }
+        PROF("clip_adam");
         MMV_TRY(launch_sumsq(m->grads, n_opt, m->acc + 3, m->ctx->num_sms, st));
         adam_args_t a;
         m->adam_t += 1;
@@ -1073,6 +1156,38 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         out->loss = (float)((m->h_acc[0] + kl_weight * m->h_acc[1] + kl_weight * m->h_acc[2]) / n);
     }
     out->grad_norm = (flags & MMV_OPTIM) ? m->h_fscal[1] : 0.f;
+    return 0;
+}
+
+int
+mmv_profile_read(mmv_model *m, const char *name, float *total_ms, int *count)
+{
+    MMV_CHECK(m && name, "mmv_profile_read: NULL");
+    MMV_CUDA(cudaSetDevice(m->ctx->device));
+    MMV_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    for (auto &r : m->prof_recs) {   // fold finished event pairs into the accumulators
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) {
+            m->prof_ms[r.id] += ms;
+            m->prof_cnt[r.id] += 1;
+        }
+        m->prof_pool.push_back(r.e0);
+        m->prof_pool.push_back(r.e1);
+    }
+    m->prof_recs.clear();
+    if (name[0] == 0) {
+        for (auto &v : m->prof_ms) v = 0.;
+        for (auto &v : m->prof_cnt) v = 0;
+        if (total_ms) *total_ms = 0.f;
+        if (count) *count = 0;
+        return 0;
+    }
+    double ms = 0.;
+    int cnt = 0;
+    for (size_t i = 0; i < m->prof_names.size(); ++i)
+        if (m->prof_names[i] == name) { ms = m->prof_ms[i]; cnt = m->prof_cnt[i]; }
+    if (total_ms) *total_ms = (float)ms;
+    if (count) *count = cnt;
     return 0;
 }
 

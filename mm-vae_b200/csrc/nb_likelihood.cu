@@ -296,6 +296,7 @@ launch_nb_likelihood(const nb_lik_args_t &a, int num_sms, cudaStream_t stream)
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     MMV_CUDA(cudaLaunchKernelEx(&cfg, kern, a, cs, Ds));
+    ::mmv::count_launch();
     return 0;
 }
 

@@ -25,7 +25,7 @@ launch_sumsq(const float *g, size_t n, double *out, int num_sms, cudaStream_t st
 {
     if (n == 0) return 0;
     const int grid = (int)min_sz((n + 1023) / 1024, (size_t)num_sms * 8);
-    sumsq_kernel<<<grid, 256, 0, st>>>(g, n, out);
+    sumsq_kernel<<<grid, 256, 0, st>>>(g, n, out); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -56,7 +56,7 @@ launch_adam(const adam_args_t &a, int num_sms, cudaStream_t st)
 {
     if (a.n == 0) return 0;
     const int grid = (int)min_sz((a.n + 255) / 256, (size_t)num_sms * 8);
-    adam_kernel<<<grid, 256, 0, st>>>(a);
+    adam_kernel<<<grid, 256, 0, st>>>(a); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }

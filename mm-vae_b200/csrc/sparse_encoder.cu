@@ -137,11 +137,11 @@ launch_fwd_t(const senc_args_t &a, int T, int nacc, cudaStream_t st)
 {
     const size_t smem = sizeof(float) * (2 * T + 64);
     switch (nacc) {
-    case 1: senc_fwd_kernel<1, ANG><<<a.B, T, smem, st>>>(a); break;
-    case 2: senc_fwd_kernel<2, ANG><<<a.B, T, smem, st>>>(a); break;
-    case 4: senc_fwd_kernel<4, ANG><<<a.B, T, smem, st>>>(a); break;
-    case 8: senc_fwd_kernel<8, ANG><<<a.B, T, smem, st>>>(a); break;
-    case 16: senc_fwd_kernel<16, ANG><<<a.B, T, smem, st>>>(a); break;
+    case 1: senc_fwd_kernel<1, ANG><<<a.B, T, smem, st>>>(a); ::mmv::count_launch(); break;
+    case 2: senc_fwd_kernel<2, ANG><<<a.B, T, smem, st>>>(a); ::mmv::count_launch(); break;
+    case 4: senc_fwd_kernel<4, ANG><<<a.B, T, smem, st>>>(a); ::mmv::count_launch(); break;
+    case 8: senc_fwd_kernel<8, ANG><<<a.B, T, smem, st>>>(a); ::mmv::count_launch(); break;
+    case 16: senc_fwd_kernel<16, ANG><<<a.B, T, smem, st>>>(a); ::mmv::count_launch(); break;
     default: MMV_CHECK(false, "sparse encoder: first layer width %d too large (max %d)", a.h1, 256 * kMaxAcc);
     }
     MMV_CUDA(cudaGetLastError());
@@ -180,7 +180,7 @@ launch_senc_bias(const float *W1T, const float *x_mean, const float *inv_t, cons
                  float *bias_eff, int D, int h1, int angular, cudaStream_t st)
 {
     const int gpc = 64;
-    senc_bias_kernel<<<ceil_div(D, gpc), 256, 0, st>>>(W1T, x_mean, inv_t, col_scale, bias_eff, D, h1, gpc, angular);
+    senc_bias_kernel<<<ceil_div(D, gpc), 256, 0, st>>>(W1T, x_mean, inv_t, col_scale, bias_eff, D, h1, gpc, angular); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -240,10 +240,10 @@ int
 launch_batch_csc(const batch_csc_args_t &c, cudaStream_t st)
 {
     MMV_CUDA(cudaMemsetAsync(c.counts, 0, sizeof(int) * c.D, st));
-    csc_count_kernel<<<c.B, 128, 0, st>>>(c.indptr, c.indices, c.cells, c.B, c.counts);
-    csc_scan_kernel<<<1, 1024, 0, st>>>(c.counts, c.gene_ptr, c.cursor, c.D);
+    csc_count_kernel<<<c.B, 128, 0, st>>>(c.indptr, c.indices, c.cells, c.B, c.counts); ::mmv::count_launch();
+    csc_scan_kernel<<<1, 1024, 0, st>>>(c.counts, c.gene_ptr, c.cursor, c.D); ::mmv::count_launch();
     csc_fill_kernel<<<c.B, 128, 0, st>>>(c.indptr, c.indices, c.vals, c.cells, c.rownorm, c.B, c.cursor,
-                                         c.ent_row, c.ent_l, c.ent_x);
+                                         c.ent_row, c.ent_l, c.ent_x); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -349,11 +349,11 @@ launch_senc_bwd(const senc_bwd_args_t &a, cudaStream_t st)
     int nacc, T = pick_threads(a.h1, &nacc);
     const size_t smem = sizeof(float) * (2 * T + 128);
     switch (nacc) {
-    case 1: senc_bwd_kernel<1><<<a.D, T, smem, st>>>(a); break;
-    case 2: senc_bwd_kernel<2><<<a.D, T, smem, st>>>(a); break;
-    case 4: senc_bwd_kernel<4><<<a.D, T, smem, st>>>(a); break;
-    case 8: senc_bwd_kernel<8><<<a.D, T, smem, st>>>(a); break;
-    case 16: senc_bwd_kernel<16><<<a.D, T, smem, st>>>(a); break;
+    case 1: senc_bwd_kernel<1><<<a.D, T, smem, st>>>(a); ::mmv::count_launch(); break;
+    case 2: senc_bwd_kernel<2><<<a.D, T, smem, st>>>(a); ::mmv::count_launch(); break;
+    case 4: senc_bwd_kernel<4><<<a.D, T, smem, st>>>(a); ::mmv::count_launch(); break;
+    case 8: senc_bwd_kernel<8><<<a.D, T, smem, st>>>(a); ::mmv::count_launch(); break;
+    case 16: senc_bwd_kernel<16><<<a.D, T, smem, st>>>(a); ::mmv::count_launch(); break;
     default: MMV_CHECK(false, "sparse encoder bwd: width %d too large", a.h1);
     }
     MMV_CUDA(cudaGetLastError());

@@ -188,6 +188,7 @@ launch_vmf_likelihood(const vmf_lik_args_t &a, int num_sms, cudaStream_t stream)
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     MMV_CUDA(cudaLaunchKernelEx(&cfg, vmf_likelihood_kernel, a, cs, Ds));
+    ::mmv::count_launch();
     return 0;
 }
 
@@ -219,12 +220,15 @@ vmf_scalar_kernel(vmf_scalar_args_t s)
     const float per_cell = df * logk - lb - s.c_half_D_fasterlog_2pi;
     s.llik_sum[0] = (double)kappa * tsum + (double)s.B * (double)per_cell;
     if (s.dln_kappa) {
-        const float lbq = sqrtf(kappa * kappa * df / (df + 1.f) + df * df);
-        const float ubq = sqrtf(kappa * kappa + df * df);
-        const float G = 0.5f * (lbq + ubq) / kappa;
+        // -df/kappa and G(kappa) ~ df/kappa cancel to O(1): evaluate in double (the reference's fp32
+        // autograd sum of these terms carries ~1e-3 relative noise at D = 20k; see tests)
+        const double kd = kappa, dfd = df;
+        const double lbq = sqrt(kd * kd * dfd / (dfd + 1.) + dfd * dfd);
+        const double ubq = sqrt(kd * kd + dfd * dfd);
+        const double G = 0.5 * (lbq + ubq) / kd;
         // the data term is a per-cell sum (summed over ranks by the allreduce); the two
         // scalar terms are not, so each rank contributes its 1/nranks share
-        const float dk = -(float)(tsum * (double)s.inv_B_global) + (-df / kappa + G) * s.inv_ranks;
+        const float dk = (float)(-tsum * (double)s.inv_B_global + (-dfd / kd + G) * (double)s.inv_ranks);
         const float ek = (float)exp((double)s.ln_kappa[0]);
         const bool inside = ek >= s.kmin && ek <= s.kmax;
         s.dln_kappa[0] += inside ? dk * ek : 0.f;
@@ -234,7 +238,7 @@ vmf_scalar_kernel(vmf_scalar_args_t s)
 int
 launch_vmf_kappa(const float *ln_kappa, float kmin, float kmax, float *kappa, cudaStream_t st)
 {
-    vmf_kappa_kernel<<<1, 1, 0, st>>>(ln_kappa, kmin, kmax, kappa);
+    vmf_kappa_kernel<<<1, 1, 0, st>>>(ln_kappa, kmin, kmax, kappa); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -242,7 +246,7 @@ launch_vmf_kappa(const float *ln_kappa, float kmin, float kmax, float *kappa, cu
 int
 launch_vmf_scalar(const vmf_scalar_args_t &s, cudaStream_t st)
 {
-    vmf_scalar_kernel<<<1, 1, 0, st>>>(s);
+    vmf_scalar_kernel<<<1, 1, 0, st>>>(s); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }

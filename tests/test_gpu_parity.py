@@ -158,3 +158,67 @@ def test_eval_mode_forward(mmv, ctx):
     assert scalar_close(t["recon"], float(ref["nllik"]))
     m.close()
     csr.close()
+
+
+# ---------------------------------------------------------------------------
+# BASELINE-sized feature axes (D = 20k / 30k): exercises the multi-CTA cluster
+# + DSMEM paths of K4/K5 that the small golden cases never reach.  Oracle =
+# torch CPU restatement on the same seeded inputs; parameters come from the
+# library's own initialiser.
+# ---------------------------------------------------------------------------
+def synth_batch(rng, n, D, density):
+    x = np.zeros((n, D), dtype=np.float32)
+    for i in range(n):
+        k = max(1, rng.binomial(D, density))
+        cols = rng.choice(D, size=k, replace=False)
+        x[i, cols] = 1 + rng.poisson(1.5, size=k)
+    return x
+
+
+@pytest.mark.parametrize("model,D,B,C", [("nb", 20000, 40, 1), ("nb", 30000, 24, 2), ("nb", 2000, 300, 1),
+                                         ("vmf", 20000, 40, 1), ("vmf", 30000, 24, 3), ("vmf", 2000, 300, 1)])
+def test_large_feature_axis_vs_oracle(mmv, ctx, model, D, B, C):
+    rng = np.random.default_rng(D + B)
+    x = synth_batch(rng, B, D, 0.05)
+    c = np.ones((B, 1), np.float32) if C == 1 else rng.normal(size=(B, C)).astype(np.float32)
+    csr = mmv.CSR.from_dense(ctx, x, c)
+    if model == "nb":
+        m = mmv.Model.nb(ctx, D, C, [96], [80], mu_r=8, nu_h=2, nu_r=2, seed=5)
+        eps = [rng.normal(size=(B, 8)).astype(np.float32), rng.normal(size=(B, 2)).astype(np.float32)]
+    else:
+        m = mmv.Model.vmf(ctx, D, C, 8, [96], [80], seed=5)
+        m.set_param("ln_kappa", np.array([0.4], np.float32))
+        eps = [rng.normal(size=(B, 8)).astype(np.float32)]
+    m.set_option("train_all_layers", 1)
+    # move the data-standardisation parameters off their symmetric init
+    m.set_param("x_mean", rng.normal(scale=0.05, size=D).astype(np.float32))
+    m.set_param("ln_x_sd", (1 + rng.normal(scale=0.1, size=D)).astype(np.float32))
+    info = m.param_info()
+    P = {k: torch.from_numpy(m.get_param(k).reshape((r, cc) if k.endswith("weight") else
+                                                    ((1, cc) if k in ("x_mean", "ln_x_sd", "mu_bias", "nu_bias") else (cc,))))
+         for k, (r, cc, _) in info.items()}
+    cells = rng.permutation(B)
+    terms = m.step(csr, cells, eps=eps, kl_weight=0.8, flags=mmv.FWD | mmv.BWD)
+    torch.set_num_threads(8)
+    ref, _, grads = mo.run_step(model, P, torch.from_numpy(x[cells]), torch.from_numpy(c[cells]),
+                                [torch.from_numpy(e) for e in eps], 0.8)
+    assert scalar_close(terms["loss"], float(ref["loss"])), (terms, float(ref["loss"]))
+    worst = {}
+    for k, gr in grads.items():
+        r = gr.numpy()
+        if np.linalg.norm(r) < 1e-12:
+            continue
+        worst[k] = rel_err(m.get_grad(k), r)
+    print(model, D, {k: f"{v:.1e}" for k, v in sorted(worst.items(), key=lambda kv: -kv[1])[:3]})
+    if model == "vmf":
+        # d ln_kappa = -sum t/B - df/kappa + G(kappa): the last two (~ +-D/2) cancel to O(1), so the
+        # reference's own fp32 value is only good to ~1e-3 at D = 20k; pin ours against fp64 instead.
+        P64 = {k: v.double() for k, v in P.items()}
+        _, _, g64 = mo.run_step(model, P64, torch.from_numpy(x[cells]).double(), torch.from_numpy(c[cells]).double(),
+                                [torch.from_numpy(e).double() for e in eps], 0.8)
+        assert rel_err(m.get_grad("ln_kappa"), g64["ln_kappa"].numpy()) < TOL
+        assert worst.pop("ln_kappa") < 2e-2
+    bad = {k: v for k, v in worst.items() if v >= TOL}
+    assert not bad, bad
+    m.close()
+    csr.close()
