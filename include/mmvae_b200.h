@@ -169,6 +169,14 @@ MMV_API int mmv_get_output(mmv_model *m, const char *name, float *host, int64_t 
  * replaces: encode_mu(x) nb.hh:419-431,627-628 ; encode(x) vmf.hh:267-281,517 */
 MMV_API int mmv_encode(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, float *mean, float *lnvar);
 
+/* ---- kernel-level entry for the unit tests --------------------------------------
+ * C[M x N] = op(A) op(B) (+ bias) (+ beta C) (ReLU) with host fp32 operands, on the
+ * bf16 tcgen05 path (use_tc = 1; operands rounded to bf16 on the device) or the fp32
+ * FFMA path (use_tc = 0).  a_mn / b_mn: operand stored [K x M] / [K x N] (MN-major)
+ * instead of [M x K] / [N x K] (K-major).  C is in/out. */
+MMV_API int mmv_test_gemm(mmv_ctx *ctx, int use_tc, int M, int N, int K, int a_mn, int b_mn, const float *A,
+                  const float *B, const float *bias, float beta, int relu, float *C);
+
 /* ---- data-parallel gradient exchange (no reference counterpart) ----
  * One process per GPU.  Rank 0 creates the id, the host program broadcasts the
  * 128 bytes, every rank calls mmv_comm_init.  After it, mmv_step sum-reduces the

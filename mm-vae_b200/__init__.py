@@ -86,6 +86,7 @@ _PROTOS = {
     "mmv_profile_read": [_vp, C.c_char_p, C.POINTER(C.c_float), C.POINTER(C.c_int)],
     "mmv_get_output": [_vp, C.c_char_p, _vp, _i64],
     "mmv_encode": [_vp, _vp, _vp, _i64, _vp, _vp],
+    "mmv_test_gemm": [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, C.c_float, C.c_int, _vp],
     "mmv_comm_unique_id": [_vp],
     "mmv_comm_init": [_vp, C.c_int, C.c_int, _vp],
     "mmv_comm_destroy": [_vp],
@@ -148,6 +149,19 @@ class Context:
         if self.h:
             lib.mmv_ctx_destroy(self.h)
             self.h = C.c_void_p()
+
+
+def test_gemm(ctx, A, B, a_mn=False, b_mn=False, bias=None, beta=0.0, relu=False, C_in=None, use_tc=True):
+    """Unit-test entry: A is [M,K] (or [K,M] if a_mn), B is [N,K] (or [K,N] if b_mn); returns C [M,N]."""
+    A = _arr(A, np.float32)
+    B = _arr(B, np.float32)
+    M, K = (A.shape[1], A.shape[0]) if a_mn else A.shape
+    N = B.shape[1] if b_mn else B.shape[0]
+    out = np.zeros((M, N), np.float32) if C_in is None else np.array(C_in, dtype=np.float32, order="C")
+    bias = _arr(bias, np.float32)
+    _chk(lib.mmv_test_gemm(ctx.h, int(use_tc), M, N, K, int(a_mn), int(b_mn), _ptr(A), _ptr(B), _ptr(bias),
+                           float(beta), int(relu), _ptr(out)))
+    return out
 
 
 def launch_count() -> int:

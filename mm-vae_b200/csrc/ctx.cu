@@ -291,3 +291,46 @@ mmv_csr_destroy(mmv_csr *s)
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------- unit-test entry
+extern "C" int
+mmv_test_gemm(mmv_ctx *ctx, int use_tc, int M, int N, int K, int a_mn, int b_mn, const float *A, const float *B,
+              const float *bias, float beta, int relu, float *C)
+{
+    MMV_CHECK(ctx && A && B && C && M > 0 && N > 0 && K > 0, "mmv_test_gemm: bad arguments");
+    MMV_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const size_t na = (size_t)M * K, nb = (size_t)N * K, nc = (size_t)M * N;
+    float *dA = nullptr, *dB = nullptr, *dC = nullptr, *dbias = nullptr;
+    void *bA = nullptr, *bB = nullptr;
+    MMV_CUDA(cudaMalloc(&dA, na * 4)); MMV_CUDA(cudaMalloc(&dB, nb * 4)); MMV_CUDA(cudaMalloc(&dC, nc * 4));
+    MMV_CUDA(cudaMemcpyAsync(dA, A, na * 4, cudaMemcpyHostToDevice, st));
+    MMV_CUDA(cudaMemcpyAsync(dB, B, nb * 4, cudaMemcpyHostToDevice, st));
+    MMV_CUDA(cudaMemcpyAsync(dC, C, nc * 4, cudaMemcpyHostToDevice, st));
+    if (bias) {
+        MMV_CUDA(cudaMalloc(&dbias, (size_t)N * 4));
+        MMV_CUDA(cudaMemcpyAsync(dbias, bias, (size_t)N * 4, cudaMemcpyHostToDevice, st));
+    }
+    int rc = 0;
+    if (use_tc) {
+        MMV_CUDA(cudaMalloc(&bA, na * 2)); MMV_CUDA(cudaMalloc(&bB, nb * 2));
+        rc = launch_to_bf16(dA, bA, na, st);
+        if (!rc) rc = launch_to_bf16(dB, bB, nb, st);
+        gemm_tc_args_t g;
+        g.A = bA; g.B = bB; g.a_mn = a_mn; g.b_mn = b_mn; g.lda = a_mn ? M : K; g.ldb = b_mn ? N : K;
+        g.C = dC; g.ldc = N; g.bias = dbias; g.M = M; g.N = N; g.K = K; g.beta = beta; g.relu = relu;
+        if (!rc) rc = launch_gemm_tc(g, st);
+    } else {
+        gemm_args_t g;
+        g.A = dA; g.B = dB; g.transA = a_mn; g.transB = !b_mn; g.lda = a_mn ? M : K; g.ldb = b_mn ? N : K;
+        g.C = dC; g.ldc = N; g.bias = dbias; g.M = M; g.N = N; g.K = K; g.beta = beta; g.relu = relu;
+        rc = launch_gemm_f32(g, st);
+    }
+    if (!rc) {
+        cudaError_t e = cudaMemcpyAsync(C, dC, nc * 4, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) { set_error("mmv_test_gemm: %s", cudaGetErrorString(e)); rc = 1; }
+    }
+    cudaFree(dA); cudaFree(dB); cudaFree(dC); cudaFree(dbias); cudaFree(bA); cudaFree(bB);
+    return rc;
+}

@@ -1,0 +1,359 @@
+// K2 (throughput mode) — bf16 GEMM on the 5th-gen tensor cores.
+//
+//   C[M x N] (fp32, + optional bf16 copy) = op(A) op(B) (+ bias[N]) (+ beta C) (ReLU optional)
+// A and B are bf16 and may each be K-major or MN-major, so the three products
+// of a Linear layer (nb.hh:335-394, vmf.hh:357-388 + autograd) need no
+// transposed copies:
+//   forward  Y  = X W^T : A = X  [M x K]  K-major , B = W [N x K]  K-major
+//   dX       dX = dY W  : A = dY [M x K]  K-major , B = W [K x N]  MN-major
+//   dW       dW = dY^T X: A = dY [K x M]  MN-major, B = X [K x N]  MN-major
+//
+// One CTA per 128 x 128 output tile, warp-specialised:
+//   warp 0   TMA producer  (cp.async.bulk.tensor.2d, SWIZZLE_128B, mbarrier tx-count)
+//   warp 1   MMA issuer    (one elected thread: tcgen05.mma.cta_group::1.kind::f16, D in TMEM)
+//   warp 2   TMEM allocator
+//   warps 4-7 epilogue     (tcgen05.ld 32x32b -> registers -> shared transpose -> coalesced stores)
+// 3-stage shared-memory ring (full/empty mbarriers); two CTAs are co-resident per
+// SM so one tile's epilogue overlaps the other's MMAs.  Out-of-range parts of
+// edge tiles are zero-filled by TMA, so no padding of M, N or K is needed
+// (leading dimensions must be multiples of 8 elements = 16 bytes).
+#include "common.cuh"
+#include "kernels.hh"
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+namespace mmv {
+
+namespace tc {
+
+constexpr int BLOCK_M = 128, BLOCK_N = 128, BLOCK_K = 64, UMMA_K = 16;
+constexpr int STAGES = 3;
+constexpr int THREADS = 256;
+constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2, B_BYTES = BLOCK_N * BLOCK_K * 2;
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int TMEM_COLS = 128;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+
+__device__ __forceinline__ uint32_t
+smem_u32(const void *p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+__device__ __forceinline__ void
+mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+
+__device__ __forceinline__ void
+mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void
+mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+
+__device__ __forceinline__ void
+tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+
+__device__ __forceinline__ void
+umma_commit(uint32_t bar)   // arrives on `bar` when all previously issued MMAs have completed
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void
+umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+// Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start address, leading /
+// stride byte offsets in 16-byte units, version 1 (Blackwell), SWIZZLE_128B.
+__device__ __forceinline__ uint64_t
+make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;   // version
+    d |= (uint64_t)2 << 61;   // LayoutType::SWIZZLE_128B
+    return d;
+}
+
+// Instruction descriptor (cute::UMMA::InstrDescriptor), kind::f16: D fp32, A/B bf16.
+__host__ __device__ constexpr uint32_t
+make_idesc(bool a_mn, bool b_mn)
+{
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) |
+        ((uint32_t)(BLOCK_N >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
+}
+
+struct params_t {
+    float *C;
+    __nv_bfloat16 *Cb;
+    const float *bias;
+    int M, N, K, ldc, ldcb;
+    float beta;
+    int relu;
+};
+
+template <bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(THREADS, 2)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, params_t p)
+{
+    extern __shared__ uint8_t smem_raw[];
+    // SWIZZLE_128B operands need 1024-byte alignment
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + STAGES * STAGE_BYTES);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * STAGES + 1);
+    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + STAGES), tfull = smem_u32(bars + 2 * STAGES);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.y * BLOCK_M, n0 = blockIdx.x * BLOCK_N;
+    const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(full0 + 8 * s, 1);
+            mbar_init(empty0 + 8 * s, 1);
+        }
+        mbar_init(tfull, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"(smem_u32(tmem_slot)), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================= TMA producer =================
+        if (lane == 0) {
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % STAGES;
+                const uint32_t ph = (kb / STAGES) & 1;
+                mbar_wait(empty0 + 8 * s, ph ^ 1);
+                const uint32_t sa = smem_u32(smem + s * STAGE_BYTES), sb = sa + A_BYTES;
+                const uint32_t fb = full0 + 8 * s;
+                mbar_expect_tx(fb, STAGE_BYTES);
+                const int k0 = kb * BLOCK_K;
+                if (A_MN) {     // tensor dims {MN, K}: two [64 k x 64 m] boxes
+                    tma_load_2d(sa, &tmA, fb, m0, k0);
+                    tma_load_2d(sa + A_BYTES / 2, &tmA, fb, m0 + 64, k0);
+                } else {        // tensor dims {K, MN}: one [128 m x 64 k] box
+                    tma_load_2d(sa, &tmA, fb, k0, m0);
+                }
+                if (B_MN) {
+                    tma_load_2d(sb, &tmB, fb, n0, k0);
+                    tma_load_2d(sb + B_BYTES / 2, &tmB, fb, n0 + 64, k0);
+                } else {
+                    tma_load_2d(sb, &tmB, fb, k0, n0);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc(A_MN, B_MN);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % STAGES;
+                const uint32_t ph = (kb / STAGES) & 1;
+                mbar_wait(full0 + 8 * s, ph);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t sa = smem_u32(smem + s * STAGE_BYTES), sb = sa + A_BYTES;
+#pragma unroll
+                for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                    // K-major  : rows of 128 B, 8-row groups 1024 B apart; a K step of 16 = +32 B
+                    // MN-major : [k][64 mn] rows of 128 B, 8-k groups 1024 B apart (SBO), 64-mn
+                    //            chunks 8192 B apart (LBO); a K step of 16 = 2 groups = +2048 B
+                    const uint64_t ad = A_MN ? make_desc(sa + k * 2048, A_BYTES / 2, 1024)
+                                             : make_desc(sa + k * 32, 16, 1024);
+                    const uint64_t bd = B_MN ? make_desc(sb + k * 2048, B_BYTES / 2, 1024)
+                                             : make_desc(sb + k * 32, 16, 1024);
+                    umma_bf16(tmem_base, ad, bd, idesc, (kb | k) != 0);
+                }
+                umma_commit(empty0 + 8 * s);          // frees the smem stage when these MMAs finish
+            }
+            umma_commit(tfull);                        // accumulator complete
+        }
+    } else if (warp >= 4) {
+        // ================= epilogue =================
+        mbar_wait(tfull, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int e = warp - 4;                         // TMEM lanes [32e, 32e+32) = tile rows
+        float *tile = reinterpret_cast<float *>(smem) + e * (32 * 33);   // operand stages are free now
+        for (int c = 0; c < BLOCK_N / 32; ++c) {
+            uint32_t v[32];
+            const uint32_t taddr = tmem_base + ((uint32_t)(32 * e) << 16) + (uint32_t)(32 * c);
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                  "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                  "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = __uint_as_float(v[j]);
+            __syncwarp();
+            const int col = n0 + 32 * c + lane;
+            const float bv = (p.bias && col < p.N) ? p.bias[col] : 0.f;
+#pragma unroll 4
+            for (int r = 0; r < 32; ++r) {
+                const int row = m0 + 32 * e + r;
+                if (row < p.M && col < p.N) {
+                    float x = tile[r * 33 + lane] + bv;
+                    if (p.beta != 0.f) x = fmaf(p.beta, p.C[(size_t)row * p.ldc + col], x);
+                    if (p.relu) x = fmaxf(x, 0.f);
+                    if (p.C) p.C[(size_t)row * p.ldc + col] = x;
+                    if (p.Cb) p.Cb[(size_t)row * p.ldcb + col] = __float2bfloat16(x);
+                }
+            }
+            __syncwarp();
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+
+    __syncthreads();
+    if (warp == 2) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    }
+}
+
+} // namespace tc
+
+// ---------------------------------------------------------------------------
+// host side: tensor maps + launch
+// ---------------------------------------------------------------------------
+namespace {
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+encode_tiled_fn
+get_encode()
+{
+    static encode_tiled_fn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (encode_tiled_fn)p;
+    }
+    return fn;
+}
+
+// bf16 matrix stored row-major [outer x inner] with leading dimension ld (elements)
+int
+make_map(CUtensorMap *map, const void *base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+         uint32_t box_outer)
+{
+    encode_tiled_fn enc = get_encode();
+    MMV_CHECK(enc, "gemm_tc: cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t dims[2] = { inner, outer };
+    cuuint64_t strides[1] = { ld * 2 };
+    cuuint32_t box[2] = { box_inner, box_outer };
+    cuuint32_t estr[2] = { 1, 1 };
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    MMV_CHECK(r == CUDA_SUCCESS, "gemm_tc: cuTensorMapEncodeTiled failed (%d): inner=%lu outer=%lu ld=%lu", (int)r,
+              (unsigned long)inner, (unsigned long)outer, (unsigned long)ld);
+    return 0;
+}
+
+} // namespace
+
+bool
+gemm_tc_supported(const gemm_tc_args_t &g)
+{
+    auto al16 = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+    return g.M > 0 && g.N > 0 && g.K > 0 && g.lda % 8 == 0 && g.ldb % 8 == 0 && al16(g.A) && al16(g.B);
+}
+
+int
+launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
+{
+    using namespace tc;
+    MMV_CHECK(gemm_tc_supported(g), "gemm_tc: operands must be 16-byte aligned with leading dimensions %% 8 == 0");
+    CUtensorMap ta, tb;
+    if (g.a_mn) MMV_TRY(make_map(&ta, g.A, g.M, g.K, g.lda, 64, BLOCK_K));
+    else MMV_TRY(make_map(&ta, g.A, g.K, g.M, g.lda, BLOCK_K, BLOCK_M));
+    if (g.b_mn) MMV_TRY(make_map(&tb, g.B, g.N, g.K, g.ldb, 64, BLOCK_K));
+    else MMV_TRY(make_map(&tb, g.B, g.K, g.N, g.ldb, BLOCK_K, BLOCK_N));
+    params_t p;
+    p.C = g.C; p.Cb = reinterpret_cast<__nv_bfloat16 *>(g.Cb); p.bias = g.bias;
+    p.M = g.M; p.N = g.N; p.K = g.K; p.ldc = g.ldc; p.ldcb = g.ldcb; p.beta = g.beta; p.relu = g.relu;
+    dim3 grid(ceil_div(g.N, BLOCK_N), ceil_div(g.M, BLOCK_M));
+    void (*kern)(const CUtensorMap, const CUtensorMap, params_t) =
+        g.a_mn ? (g.b_mn ? gemm_tc_kernel<true, true> : gemm_tc_kernel<true, false>)
+               : (g.b_mn ? gemm_tc_kernel<false, true> : gemm_tc_kernel<false, false>);
+    static bool attr_set[4] = { false, false, false, false };
+    const int vi = (g.a_mn ? 2 : 0) + (g.b_mn ? 1 : 0);
+    if (!attr_set[vi]) {
+        MMV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        attr_set[vi] = true;
+    }
+    kern<<<grid, THREADS, SMEM_BYTES, stream>>>(ta, tb, p);
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// fp32 -> bf16 (activations entering a tensor-core GEMM)
+__global__ void
+to_bf16_kernel(const float *x, __nv_bfloat16 *y, size_t n)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        y[i] = __float2bfloat16(x[i]);
+}
+
+int
+launch_to_bf16(const float *x, void *y, size_t n, cudaStream_t st)
+{
+    if (n == 0) return 0;
+    to_bf16_kernel<<<(int)min_sz((n + 255) / 256, 4096), 256, 0, st>>>(x, reinterpret_cast<__nv_bfloat16 *>(y), n);
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+} // namespace mmv

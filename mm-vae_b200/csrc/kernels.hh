@@ -22,6 +22,24 @@ struct gemm_args_t {
 };
 int launch_gemm_f32(const gemm_args_t &g, cudaStream_t stream);
 
+// ---- K2 bf16 tcgen05 GEMM (gemm_tc.cu).  A, B are bf16 (device), each K-major or MN-major:
+//   a_mn = 0: A stored [M x K] (lda) ; a_mn = 1: A stored [K x M] (lda)
+//   b_mn = 0: B stored [N x K] (ldb) ; b_mn = 1: B stored [K x N] (ldb)
+struct gemm_tc_args_t {
+    const void *A = nullptr, *B = nullptr;
+    int a_mn = 0, b_mn = 0, lda = 0, ldb = 0;
+    float *C = nullptr;            // fp32 output (may be nullptr if only Cb is wanted)
+    void *Cb = nullptr;            // optional bf16 copy of the output
+    int ldc = 0, ldcb = 0;
+    const float *bias = nullptr;
+    int M = 0, N = 0, K = 0;
+    float beta = 0.f;
+    int relu = 0;
+};
+bool gemm_tc_supported(const gemm_tc_args_t &g);
+int launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream);
+int launch_to_bf16(const float *x, void *y, size_t n, cudaStream_t st);
+
 // ---- K1 sparse encoder (sparse_encoder.cu)
 struct senc_args_t {
     const int64_t *indptr = nullptr;
