@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument("--genes", type=int, default=WORKLOAD["genes"])
     ap.add_argument("--batch", type=int, default=WORKLOAD["batch"], help="cells per step per GPU")
     ap.add_argument("--model", default="nb", choices=["nb", "vmf"])
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"],
+                    help="GEMM operand type: bf16 = tcgen05 tensor cores (fp32 accumulate), f32 = FFMA parity mode")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the CPU baseline sample")
     return ap.parse_args()
@@ -302,6 +304,7 @@ def run_own(args):
         model = mmv.Model.nb(ctx, D, 1, w["enc"], w["dec"], w["latent"], w["nu_h"], w["nu_r"], seed=7)
     else:
         model = mmv.Model.vmf(ctx, D, 1, w["latent"], w["enc"], w["dec"], seed=7)
+    model.set_option("dtype", 1 if args.dtype == "bf16" else 0)
     model.set_option("train_all_layers", 1)    # train every layer (the reference's unregistered-Sequential
     model.set_option("profile", 1)             # bug freezes them; its autograd still computes their grads)
     rng = np.random.default_rng(11 + rank)
@@ -336,7 +339,7 @@ def run_own(args):
         t, c = model.profile_read(name)
         if c:
             prof[name] = (t, c)
-    for name in ("batch_csc", "clip_adam", "allreduce", "colsum"):
+    for name in ("batch_csc", "clip_adam", "allreduce", "colsum", "to_bf16"):
         t, c = model.profile_read(name)
         if c:
             prof[name] = (t, c)
@@ -414,7 +417,7 @@ def run_own(args):
                   else "train cells/sec (vMF-VAE ELBO fwd+bwd)",
         "value": round(world * B * args.steps / (ms * 1e-3), 1), "unit": "cells/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": f"{w['model']}_vae {w['cells']} cells x {D} genes, {w['density']:.0%} density "
                                f"(SURVEY cfg 4), cells sharded over {world} GPU(s), {n_local} resident per GPU",
                    "batch_per_gpu": B, "global_batch": B * world, "encoder": w["enc"], "decoder": w["dec"],

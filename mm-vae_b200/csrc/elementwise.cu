@@ -9,6 +9,8 @@
 #include "common.cuh"
 #include "kernels.hh"
 
+#include <cuda_bf16.h>
+
 namespace mmv {
 
 // inv_t[j] = 1 / (softplus(ln_x_sd_j) + eps);  out = a + b + c (nullable) element-wise
@@ -129,7 +131,8 @@ colsum_kernel(colsum_args_t a)
 #pragma unroll
     for (int c = 0; c < 8; ++c) sc[c] = 0.f;
     for (int i = r0; i < r1; ++i) {
-        const float v = a.X[(size_t)i * a.ldx + col];
+        const float v = a.Xb ? __bfloat162float(reinterpret_cast<const __nv_bfloat16 *>(a.Xb)[(size_t)i * a.ldx + col])
+                             : a.X[(size_t)i * a.ldx + col];
         s += v;
         if (a.out_cov) {
             const int64_t cell = a.cells ? (int64_t)a.cells[i] : (int64_t)i;

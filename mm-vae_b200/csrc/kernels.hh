@@ -115,7 +115,8 @@ struct nb_lik_args_t {
     const float *ubias = nullptr;     // [D] nu_decoding.bias - nu_bias
     int B = 0, D = 0, C = 0, Rnu = 0;
     float inv_B = 0.f;
-    float *dlogits = nullptr;         // [B x D]  (nullptr: forward only)
+    float *dlogits = nullptr;         // [B x D]  (nullptr: forward only unless dlogits_bf16)
+    void *dlogits_bf16 = nullptr;     // [B x D] bf16 instead of fp32 (tensor-core mode)
     float *ddpre = nullptr;           // [B]
     float *dznu = nullptr;            // [B x Rnu]
     float *col_du = nullptr;          // [D]       += sum_i du_ij
@@ -185,6 +186,7 @@ int launch_reparam_bwd(const reparam_args_t &a, cudaStream_t st);
 
 struct colsum_args_t {
     const float *X = nullptr;
+    const void *Xb = nullptr;         // bf16 input instead of X
     int M = 0, N = 0, ldx = 0;
     float *out_sum = nullptr, *out_sum2 = nullptr, *out_sum3 = nullptr;   // [N] each, +=
     float *out_cov = nullptr;         // [N x C] += sum_i X[i, col] * cov[cell_i, c]
@@ -206,6 +208,7 @@ int launch_angular_bwd(const float *W, const float *dWp, const float *scale, flo
 int launch_sumsq(const float *g, size_t n, double *out, int num_sms, cudaStream_t st);
 struct adam_args_t {
     float *param = nullptr, *grad = nullptr, *m = nullptr, *v = nullptr;
+    void *param_bf16 = nullptr;       // optional bf16 mirror refreshed in the same pass
     size_t n = 0;
     const double *sumsq = nullptr;
     float *norm_out = nullptr;

@@ -12,6 +12,7 @@
 #include <cmath>
 #include <map>
 #include <memory>
+#include <set>
 
 using namespace mmv;
 
@@ -107,6 +108,11 @@ struct mmv_model {
     // options
     float lr = 1e-3f, weight_decay = 1e-4f, grad_clip = 1.f;
     bool train_all = false, frozen_grads = true, debug_outputs = false;
+    bool use_tc = false;                  // "dtype" option: bf16 tcgen05 GEMMs (fp32 accumulate) vs fp32 FFMA
+    void *params_bf16 = nullptr;          // bf16 mirror of `params` (same offsets), GEMM B operands
+    bool bf16_dirty = true;
+    bool top_grad_bf16 = false;           // K4 wrote the B x D gradient as bf16 into "dG.bf" this step
+    std::map<const float *, const void *> bf_cache;   // activations already converted in this step
     uint64_t seed = 0;
 
     // workspace
@@ -186,7 +192,8 @@ add_linear(mmv_model *m, const std::string &name, int in, int out, bool register
 }
 
 // Lay the tensors out: registered ones first (so "optimise the registered
-// parameters only" is one contiguous range), each start 4-float aligned except
+// parameters only" is one contiguous range), each start 8-float aligned (16 bytes in the
+// bf16 mirror, as TMA requires) except
 // the second half of a stacked head, which must follow its first half directly.
 int
 finalize_layout(mmv_model *m, const std::vector<std::pair<int, int>> &stacked)
@@ -215,15 +222,15 @@ finalize_layout(mmv_model *m, const std::vector<std::pair<int, int>> &stacked)
     for (int i : order) {
         tensor_t &t = m->tensors[i];
         if (!t.registered && !reg_done) {
-            off = (off + 3) & ~(size_t)3;
+            off = (off + 7) & ~(size_t)7;
             m->n_reg = off;
             reg_done = true;
         }
-        if (!glue[i]) off = (off + 3) & ~(size_t)3;
+        if (!glue[i]) off = (off + 7) & ~(size_t)7;
         t.off = off;
         off += t.numel();
     }
-    off = (off + 3) & ~(size_t)3;
+    off = (off + 7) & ~(size_t)7;
     if (!reg_done) m->n_reg = off;
     m->n_all = off;
     return 0;
@@ -238,6 +245,7 @@ alloc_and_init(mmv_model *m)
     MMV_CUDA(cudaMalloc(&m->grads, bytes));
     MMV_CUDA(cudaMalloc(&m->adam_m, bytes));
     MMV_CUDA(cudaMalloc(&m->adam_v, bytes));
+    MMV_CUDA(cudaMalloc(&m->params_bf16, bytes / 2));
     MMV_CUDA(cudaMemset(m->grads, 0, bytes));
     MMV_CUDA(cudaMemset(m->adam_m, 0, bytes));
     MMV_CUDA(cudaMemset(m->adam_v, 0, bytes));
@@ -409,7 +417,7 @@ mmv_model_destroy(mmv_model *m)
     cudaSetDevice(m->ctx->device);
     cudaStreamSynchronize(m->ctx->stream);
     cudaFree(m->params); cudaFree(m->grads); cudaFree(m->adam_m); cudaFree(m->adam_v);
-    cudaFree(m->acc); cudaFree(m->fscal);
+    cudaFree(m->acc); cudaFree(m->fscal); cudaFree(m->params_bf16);
     cudaFreeHost(m->h_acc); cudaFreeHost(m->h_fscal);
     if (m->h_cells) cudaFreeHost(m->h_cells);
     if (m->h_eps) cudaFreeHost(m->h_eps);
@@ -430,6 +438,7 @@ mmv_model_set_option(mmv_model *m, const char *key, double value)
     else if (k == "frozen_grads") m->frozen_grads = value != 0;
     else if (k == "debug_outputs") m->debug_outputs = value != 0;
     else if (k == "profile") m->profile = value != 0;
+    else if (k == "dtype") m->use_tc = value != 0;   // 0 = fp32 (parity mode), 1 = bf16 tensor-core GEMMs
     else if (k == "max_batch") { /* capacity hint; buffers grow on demand */ }
     else MMV_CHECK(false, "mmv_model_set_option: unknown key '%s'", key);
     return 0;
@@ -475,6 +484,7 @@ copy_tensor(mmv_model *m, const char *name, float *host, const float *host_in, i
             src = tmp.data();
         }
         MMV_CUDA(cudaMemcpy(base + t.off, src, sizeof(float) * n, cudaMemcpyHostToDevice));
+        m->bf16_dirty = true;
     } else {
         if (t.transposed) {
             tmp.resize(n);
@@ -569,12 +579,51 @@ struct step_t {
 #define WS(name, count) m->W(name, sizeof(float) * (size_t)(count))
 #define NEED(ptr) MMV_CHECK((ptr) != nullptr, "out of device memory: %s", mmv::get_error())
 
+// bf16 view of an fp32 device array for the tensor-core GEMMs: parameters come from the
+// mirror kept by the Adam kernel, activations are converted once per step into "<name>.bf".
+int
+bf16_of(const step_t &s, const float *p, size_t n, const void **out)
+{
+    mmv_model *m = s.m;
+    if (p >= m->params && p < m->params + m->n_all) {
+        *out = reinterpret_cast<const uint16_t *>(m->params_bf16) + (p - m->params);
+        return 0;
+    }
+    auto it = m->bf_cache.find(p);
+    if (it != m->bf_cache.end()) { *out = it->second; return 0; }
+    std::string name = "anon";
+    for (auto &kv : m->ws) if (kv.second.p == (const void *)p) { name = kv.first; break; }
+    void *buf = m->W(name + ".bf", n * 2);
+    MMV_CHECK(buf, "out of device memory: %s", mmv::get_error());
+    {
+        PROF("to_bf16");
+        MMV_TRY(launch_to_bf16(p, buf, n, s.st));
+    }
+    m->bf_cache[p] = buf;
+    *out = buf;
+    return 0;
+}
+
+bool
+tc_ok(const step_t &s, int64_t M, int64_t N, int64_t K, int lda, int ldb)
+{
+    return s.m->use_tc && lda % 8 == 0 && ldb % 8 == 0 && N >= 16 && M * N * K >= (1LL << 21);
+}
+
 // Y = X W^T (+ b)
 int
 lin_fwd(const step_t &s, const float *X, int in, const float *W, const float *b, int out, float *Y, bool relu,
         const char *tag = "gemm_other")
 {
     mmv_model *m = s.m;
+    if (tc_ok(s, s.B, out, in, in, in)) {
+        gemm_tc_args_t t;
+        MMV_TRY(bf16_of(s, X, (size_t)s.B * in, &t.A));
+        MMV_TRY(bf16_of(s, W, (size_t)out * in, &t.B));
+        t.lda = in; t.ldb = in; t.C = Y; t.ldc = out; t.bias = b; t.M = s.B; t.N = out; t.K = in; t.relu = relu ? 1 : 0;
+        PROF(tag);
+        return launch_gemm_tc(t, s.st);
+    }
     PROF(tag);
     gemm_args_t g;
     g.A = X; g.lda = in; g.B = W; g.ldb = in; g.transB = 1;
@@ -585,9 +634,18 @@ lin_fwd(const step_t &s, const float *X, int in, const float *W, const float *b,
 // dX = dY W
 int
 lin_bwd_data(const step_t &s, const float *dY, int out, const float *W, int in, float *dX,
-             const char *tag = "gemm_other")
+             const char *tag = "gemm_other", const void *dY_bf = nullptr)
 {
     mmv_model *m = s.m;
+    if (tc_ok(s, s.B, in, out, out, in)) {
+        gemm_tc_args_t t;
+        if (dY_bf) t.A = dY_bf; else MMV_TRY(bf16_of(s, dY, (size_t)s.B * out, &t.A));
+        MMV_TRY(bf16_of(s, W, (size_t)out * in, &t.B));
+        t.lda = out; t.b_mn = 1; t.ldb = in; t.C = dX; t.ldc = in; t.M = s.B; t.N = in; t.K = out;
+        PROF(tag);
+        return launch_gemm_tc(t, s.st);
+    }
+    MMV_CHECK(dY != nullptr, "lin_bwd_data: fp32 path needs an fp32 gradient");
     PROF(tag);
     gemm_args_t g;
     g.A = dY; g.lda = out; g.B = W; g.ldb = in;
@@ -598,10 +656,19 @@ lin_bwd_data(const step_t &s, const float *dY, int out, const float *W, int in, 
 // dW += dY^T X ; db += colsum(dY)
 int
 lin_bwd_weight(const step_t &s, const float *dY, int out, const float *X, int in, float *dW, float *db, float beta = 1.f,
-               const char *tag = "gemm_other")
+               const char *tag = "gemm_other", const void *dY_bf = nullptr)
 {
     mmv_model *m = s.m;
-    if (dW) {
+    if (dW && tc_ok(s, out, in, s.B, out, in)) {
+        gemm_tc_args_t t;
+        if (dY_bf) t.A = dY_bf; else MMV_TRY(bf16_of(s, dY, (size_t)s.B * out, &t.A));
+        MMV_TRY(bf16_of(s, X, (size_t)s.B * in, &t.B));
+        t.a_mn = 1; t.lda = out; t.b_mn = 1; t.ldb = in; t.C = dW; t.ldc = in; t.M = out; t.N = in; t.K = s.B;
+        t.beta = beta;
+        PROF(tag);
+        MMV_TRY(launch_gemm_tc(t, s.st));
+    } else if (dW) {
+        MMV_CHECK(dY != nullptr, "lin_bwd_weight: fp32 path needs an fp32 gradient");
         PROF(tag);
         gemm_args_t g;
         g.A = dY; g.lda = out; g.transA = 1; g.B = X; g.ldb = in;
@@ -611,7 +678,7 @@ lin_bwd_weight(const step_t &s, const float *dY, int out, const float *X, int in
     if (db) {
         PROF("colsum");
         colsum_args_t c;
-        c.X = dY; c.M = s.B; c.N = out; c.ldx = out; c.out_sum = db;
+        c.X = dY; c.Xb = dY ? nullptr : dY_bf; c.M = s.B; c.N = out; c.ldx = out; c.out_sum = db;
         MMV_TRY(launch_colsum(c, s.st));
     }
     return 0;
@@ -679,7 +746,9 @@ decoder_backward(const step_t &s)
     mmv_model *m = s.m;
     const int B = s.B, R = (int)m->R;
     const int nd = (int)m->dec.size();
-    const float *dY = m->ws["G"].as<float>();
+    const bool bf_top = m->top_grad_bf16;
+    const float *dY = bf_top ? nullptr : m->ws["G"].as<float>();
+    const void *dY_bf = bf_top ? m->ws["dG.bf"].p : nullptr;
     for (int l = nd - 1; l >= 0; --l) {
         const linear_t &L = m->dec[l];
         const float *X = l == 0 ? m->ws["z"].as<float>() : m->ws["dec_act" + std::to_string(l - 1)].as<float>();
@@ -687,10 +756,11 @@ decoder_backward(const step_t &s)
         // bias of the last layer is handled with the other per-gene sums by the caller
         MMV_TRY(lin_bwd_weight(s, dY, L.out, X, L.in, m->want_grad(L.w) ? m->G(L.w) : nullptr,
                                (!last && m->want_grad(L.b)) ? m->G(L.b) : nullptr, 1.f,
-                               last ? "gemm_dec_last_dw" : "gemm_other"));
+                               last ? "gemm_dec_last_dw" : "gemm_other", dY_bf));
         float *dX = l == 0 ? WS("dz", (size_t)B * R) : WS("d_dec" + std::to_string(l - 1), (size_t)B * L.in);
         NEED(dX);
-        MMV_TRY(lin_bwd_data(s, dY, L.out, m->P(L.w), L.in, dX, last ? "gemm_dec_last_dx" : "gemm_other"));
+        MMV_TRY(lin_bwd_data(s, dY, L.out, m->P(L.w), L.in, dX, last ? "gemm_dec_last_dx" : "gemm_other", dY_bf));
+        dY_bf = nullptr;
         if (l > 0 && m->relu) MMV_TRY(launch_relu_bwd(dX, X, (size_t)B * L.in, s.st));
         dY = dX;
     }
@@ -838,8 +908,13 @@ nb_forward_backward(const step_t &s)
         k.recon_mu = WS("recon_mu", (size_t)B * D); k.recon_nu = WS("recon_nu", (size_t)B * D);
         NEED(k.recon_mu); NEED(k.recon_nu);
     }
-    if (s.bwd) {
+    m->top_grad_bf16 = s.bwd && tc_ok(s, D, Ld.in, B, D, Ld.in) && tc_ok(s, B, Ld.in, D, D, Ld.in);
+    if (m->top_grad_bf16) {
+        k.dlogits_bf16 = m->W("dG.bf", (size_t)B * D * 2); NEED(k.dlogits_bf16);
+    } else if (s.bwd) {
         k.dlogits = m->ws["G"].as<float>();   // in place: each row is staged in shared memory first
+    }
+    if (s.bwd) {
         k.ddpre = WS("ddpre", B); k.dznu = WS("dznu", (size_t)B * Rnu);
         k.col_du = WS("col_du", D); k.col_duz = WS("col_duz", (size_t)D * Rnu);
         NEED(k.ddpre); NEED(k.dznu); NEED(k.col_du); NEED(k.col_duz);
@@ -856,7 +931,7 @@ nb_forward_backward(const step_t &s)
     {
         PROF("colsum_dlogits");
         colsum_args_t c;
-        c.X = k.dlogits; c.M = B; c.N = D; c.ldx = D;
+        c.X = k.dlogits; c.Xb = k.dlogits_bf16; c.M = B; c.N = D; c.ldx = D;
         c.out_sum = m->want_grad(Ld.b) ? m->G(Ld.b) : nullptr;
         c.out_sum2 = m->G(m->covar_dec.b); c.out_sum3 = m->G(m->t_mu_bias);
         c.out_cov = m->G(m->covar_dec.w); c.cov = s.cov; c.cells = s.cells; c.C = C;
@@ -946,6 +1021,7 @@ vmf_forward_backward(const step_t &s)
     k.kappa = kappa; k.B = B; k.D = D; k.C = C; k.inv_B = s.inv_B; k.eps_obs = eps_d;
     k.t_acc = m->acc + 4;
     if (m->debug_outputs) { k.recon = WS("recon", (size_t)B * D); NEED(k.recon); }
+    m->top_grad_bf16 = false;
     if (s.bwd) {
         k.dpre = m->ws["G"].as<float>();
         k.col_dq = WS("col_dq", D); k.col_dqc = WS("col_dqc", (size_t)D * C); NEED(k.col_dq); NEED(k.col_dqc);
@@ -1113,6 +1189,11 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         s.klw = kl_weight; s.inv_B = 1.f / (float)(B * nranks); s.bwd = (flags & MMV_BWD) != 0; s.st = st;
         MMV_TRY(stage_inputs(m, csr, cells, B, boot_idx, eps, flags, s));
         m->last_B = B;
+        m->bf_cache.clear();
+        if (m->use_tc && m->bf16_dirty) {
+            MMV_TRY(launch_to_bf16(m->params, m->params_bf16, m->n_all, st));
+            m->bf16_dirty = false;
+        }
         MMV_CUDA(cudaMemsetAsync(m->acc, 0, sizeof(double) * 8, st));
         if (s.bwd)   // adam.zero_grad() reaches the optimiser's tensors only (mmvae_alg.hh:306)
             MMV_CUDA(cudaMemsetAsync(m->grads, 0, sizeof(float) * n_opt, st));
@@ -1134,6 +1215,8 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         const double bc1 = 1. - std::pow(0.9, (double)m->adam_t), bc2 = 1. - std::pow(0.999, (double)m->adam_t);
         a.param = m->params; a.grad = m->grads; a.m = m->adam_m; a.v = m->adam_v; a.n = n_opt;
         a.sumsq = m->acc + 3; a.norm_out = m->fscal + 1;
+        if (m->use_tc && !m->bf16_dirty) a.param_bf16 = m->params_bf16;
+        else m->bf16_dirty = true;
         a.max_norm = m->grad_clip; a.weight_decay = m->weight_decay;
         a.bc2_sqrt = (float)std::sqrt(bc2); a.neg_step = (float)(-(double)m->lr / bc1);
         MMV_TRY(launch_adam(a, m->ctx->num_sms, st));
@@ -1238,6 +1321,11 @@ mmv_encode(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, float *m
     s.m = m; s.csr = csr; s.B = (int)B; s.cov = nullptr; s.klw = 0.f; s.inv_B = 1.f / (float)B; s.bwd = false; s.st = st;
     MMV_TRY(stage_inputs(m, csr, cells, B, nullptr, nullptr, 0, s));
     m->last_B = B;
+    m->bf_cache.clear();
+    if (m->use_tc && m->bf16_dirty) {
+        MMV_TRY(launch_to_bf16(m->params, m->params_bf16, m->n_all, st));
+        m->bf16_dirty = false;
+    }
     const int D = (int)m->D;
     const linear_t &L0 = m->enc[0];
     const int h1 = L0.out;

@@ -19,6 +19,7 @@
 #include "kernels.hh"
 
 #include <cooperative_groups.h>
+#include <cuda_bf16.h>
 
 namespace cg = cooperative_groups;
 
@@ -94,7 +95,7 @@ nb_likelihood_kernel(nb_lik_args_t a, int cs, int Ds)
     const int D = a.D, C = a.C, R = a.Rnu;
     const int j0 = rank * Ds;
     const int nj = max(0, min(D - j0, Ds));
-    const bool grad = a.dlogits != nullptr;
+    const bool grad = a.dlogits != nullptr || a.dlogits_bf16 != nullptr;
 
     extern __shared__ __align__(16) float smem[];
     float *sa = smem;                    // [Ds] logits -> exp -> p
@@ -230,9 +231,15 @@ nb_likelihood_kernel(nb_lik_args_t a, int cs, int Ds)
             const float s = red[0];
             // ---- pass 4: dL/dlogit_j = (d_i / B) p_j (g_j - s_i)
             const float coef = depth * a.inv_B;
-            float *drow = a.dlogits + (size_t)row * D + j0;
-            for (int jj = tid; jj < nj; jj += kNbThreads)
-                drow[jj] = coef * sa[jj] * (sg[jj] - s);
+            if (a.dlogits_bf16) {
+                __nv_bfloat16 *drow = reinterpret_cast<__nv_bfloat16 *>(a.dlogits_bf16) + (size_t)row * D + j0;
+                for (int jj = tid; jj < nj; jj += kNbThreads)
+                    drow[jj] = __float2bfloat16(coef * sa[jj] * (sg[jj] - s));
+            } else {
+                float *drow = a.dlogits + (size_t)row * D + j0;
+                for (int jj = tid; jj < nj; jj += kNbThreads)
+                    drow[jj] = coef * sa[jj] * (sg[jj] - s);
+            }
             if (rank == 0 && tid == 0) {
                 const float dp = a.dpre[row];
                 a.ddpre[row] = s * a.inv_B * (dp > 20.f ? 1.f : sigmoid_f(dp));

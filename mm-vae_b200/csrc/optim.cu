@@ -6,6 +6,8 @@
 #include "common.cuh"
 #include "kernels.hh"
 
+#include <cuda_bf16.h>
+
 namespace mmv {
 
 __global__ void
@@ -47,7 +49,9 @@ adam_kernel(adam_args_t a)
         a.m[i] = m;
         a.v[i] = v;
         const float denom = sqrtf(v) / a.bc2_sqrt + a.eps;
-        a.param[i] = p + (a.neg_step * m) / denom;
+        const float pn = p + (a.neg_step * m) / denom;
+        a.param[i] = pn;
+        if (a.param_bf16) reinterpret_cast<__nv_bfloat16 *>(a.param_bf16)[i] = __float2bfloat16(pn);
     }
 }
 

@@ -175,9 +175,12 @@ def synth_batch(rng, n, D, density):
     return x
 
 
+@pytest.mark.parametrize("dtype", ["f32", "bf16"])
 @pytest.mark.parametrize("model,D,B,C", [("nb", 20000, 40, 1), ("nb", 30000, 24, 2), ("nb", 2000, 300, 1),
                                          ("vmf", 20000, 40, 1), ("vmf", 30000, 24, 3), ("vmf", 2000, 300, 1)])
-def test_large_feature_axis_vs_oracle(mmv, ctx, model, D, B, C):
+def test_large_feature_axis_vs_oracle(mmv, ctx, model, D, B, C, dtype):
+    """fp32 mode: 1e-4; bf16 mode (tcgen05 GEMMs, bf16 operands, fp32 accumulate): 1e-2 (north_star)."""
+    TOL = 1e-4 if dtype == "f32" else 1e-2
     rng = np.random.default_rng(D + B)
     x = synth_batch(rng, B, D, 0.05)
     c = np.ones((B, 1), np.float32) if C == 1 else rng.normal(size=(B, C)).astype(np.float32)
@@ -190,6 +193,7 @@ def test_large_feature_axis_vs_oracle(mmv, ctx, model, D, B, C):
         m.set_param("ln_kappa", np.array([0.4], np.float32))
         eps = [rng.normal(size=(B, 8)).astype(np.float32)]
     m.set_option("train_all_layers", 1)
+    m.set_option("dtype", 1 if dtype == "bf16" else 0)
     # move the data-standardisation parameters off their symmetric init
     m.set_param("x_mean", rng.normal(scale=0.05, size=D).astype(np.float32))
     m.set_param("ln_x_sd", (1 + rng.normal(scale=0.1, size=D)).astype(np.float32))
@@ -202,14 +206,14 @@ def test_large_feature_axis_vs_oracle(mmv, ctx, model, D, B, C):
     torch.set_num_threads(8)
     ref, _, grads = mo.run_step(model, P, torch.from_numpy(x[cells]), torch.from_numpy(c[cells]),
                                 [torch.from_numpy(e) for e in eps], 0.8)
-    assert scalar_close(terms["loss"], float(ref["loss"])), (terms, float(ref["loss"]))
+    assert scalar_close(terms["loss"], float(ref["loss"]), TOL), (terms, float(ref["loss"]))
     worst = {}
     for k, gr in grads.items():
         r = gr.numpy()
         if np.linalg.norm(r) < 1e-12:
             continue
         worst[k] = rel_err(m.get_grad(k), r)
-    print(model, D, {k: f"{v:.1e}" for k, v in sorted(worst.items(), key=lambda kv: -kv[1])[:3]})
+    print(model, D, dtype, {k: f"{v:.1e}" for k, v in sorted(worst.items(), key=lambda kv: -kv[1])[:3]})
     if model == "vmf":
         # d ln_kappa = -sum t/B - df/kappa + G(kappa): the last two (~ +-D/2) cancel to O(1), so the
         # reference's own fp32 value is only good to ~1e-3 at D = 20k; pin ours against fp64 instead.
@@ -217,7 +221,7 @@ def test_large_feature_axis_vs_oracle(mmv, ctx, model, D, B, C):
         _, _, g64 = mo.run_step(model, P64, torch.from_numpy(x[cells]).double(), torch.from_numpy(c[cells]).double(),
                                 [torch.from_numpy(e).double() for e in eps], 0.8)
         assert rel_err(m.get_grad("ln_kappa"), g64["ln_kappa"].numpy()) < TOL
-        assert worst.pop("ln_kappa") < 2e-2
+        assert worst.pop("ln_kappa") < 2e-2 + TOL
     bad = {k: v for k, v in worst.items() if v >= TOL}
     assert not bad, bad
     m.close()
