@@ -124,7 +124,10 @@ struct nb_lik_args_t {
     double *loss_acc = nullptr;       // += sum_ij nllik
     float *recon_mu = nullptr, *recon_nu = nullptr;   // optional [B x D] (tests)
     float *row_lse = nullptr;         // optional [B]
+    int allow_fast = 1;               // use the tuned Rnu = 1 / all-ones-covariate kernel when eligible
 };
+bool nb_likelihood_fast_eligible(const nb_lik_args_t &a);
+int launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stream);
 int launch_nb_likelihood(const nb_lik_args_t &a, int num_sms, cudaStream_t stream);
 
 // ---- K5 vMF likelihood (vmf_likelihood.cu)

@@ -108,6 +108,7 @@ struct mmv_model {
     // options
     float lr = 1e-3f, weight_decay = 1e-4f, grad_clip = 1.f;
     bool train_all = false, frozen_grads = true, debug_outputs = false;
+    bool nb_fast = true;                  // "nb_fast" option: tuned K4 kernel when eligible
     bool use_tc = false;                  // "dtype" option: bf16 tcgen05 GEMMs (fp32 accumulate) vs fp32 FFMA
     void *params_bf16 = nullptr;          // bf16 mirror of `params` (same offsets), GEMM B operands
     bool bf16_dirty = true;
@@ -438,6 +439,7 @@ mmv_model_set_option(mmv_model *m, const char *key, double value)
     else if (k == "frozen_grads") m->frozen_grads = value != 0;
     else if (k == "debug_outputs") m->debug_outputs = value != 0;
     else if (k == "profile") m->profile = value != 0;
+    else if (k == "nb_fast") m->nb_fast = value != 0;
     else if (k == "dtype") m->use_tc = value != 0;   // 0 = fp32 (parity mode), 1 = bf16 tensor-core GEMMs
     else if (k == "max_batch") { /* capacity hint; buffers grow on demand */ }
     else MMV_CHECK(false, "mmv_model_set_option: unknown key '%s'", key);
@@ -904,6 +906,7 @@ nb_forward_backward(const step_t &s)
     k.dpre = e.dpre; k.znu = rn.z; k.Wnd = m->P(m->nu_dec.w); k.ubias = ubias;
     k.B = B; k.D = D; k.C = C; k.Rnu = Rnu; k.inv_B = s.inv_B;
     k.loss_acc = m->acc + 0;
+    k.allow_fast = m->nb_fast ? 1 : 0;
     if (m->debug_outputs) {
         k.recon_mu = WS("recon_mu", (size_t)B * D); k.recon_nu = WS("recon_nu", (size_t)B * D);
         NEED(k.recon_mu); NEED(k.recon_nu);

@@ -18,49 +18,15 @@
 #include "common.cuh"
 #include "kernels.hh"
 
-#include <cooperative_groups.h>
-#include <cuda_bf16.h>
+#include "cluster_reduce.cuh"
 
-namespace cg = cooperative_groups;
+#include <cuda_bf16.h>
 
 namespace mmv {
 
 constexpr int kNbThreads = 512;
 constexpr float kEps = 1e-4f;  // nb.hh:514
 constexpr float kNuMin = 1e-4f, kNuMax = 1e4f;  // nb.hh:252,459
-
-// Sum N per-thread values over the block, then over the cluster (DSMEM).
-template <int N>
-__device__ __forceinline__ void
-cluster_sum(float (&v)[N], float *slot, float *scratch, cg::cluster_group &cluster, int cs)
-{
-    block_sum<N>(v, scratch);
-    if (cs == 1) return;
-    if (threadIdx.x == 0) {
-#pragma unroll
-        for (int k = 0; k < N; ++k) slot[k] = v[k];
-    }
-    cluster.sync();
-#pragma unroll
-    for (int k = 0; k < N; ++k) v[k] = 0.f;
-    for (int r = 0; r < cs; ++r) {
-        const float *remote = cluster.map_shared_rank(slot, r);
-#pragma unroll
-        for (int k = 0; k < N; ++k) v[k] += remote[k];
-    }
-}
-
-__device__ __forceinline__ float
-cluster_max(float v, float *slot, float *scratch, cg::cluster_group &cluster, int cs)
-{
-    v = block_max(v, scratch);
-    if (cs == 1) return v;
-    if (threadIdx.x == 0) slot[0] = v;
-    cluster.sync();
-    float m = -INFINITY;
-    for (int r = 0; r < cs; ++r) m = fmaxf(m, cluster.map_shared_rank(slot, r)[0]);
-    return m;
-}
 
 struct nb_elem_t {
     float m, nu, l1p, sig_mask, inv_mnu;
@@ -273,6 +239,7 @@ nb_smem_bytes(int Ds, int rmax)
 int
 launch_nb_likelihood(const nb_lik_args_t &a, int num_sms, cudaStream_t stream)
 {
+    if (a.allow_fast && nb_likelihood_fast_eligible(a)) return launch_nb_likelihood_fast(a, num_sms, stream);
     MMV_CHECK(a.Rnu >= 1 && a.Rnu <= 8, "nb_likelihood: overdispersion latent dim %d not in [1,8]", a.Rnu);
     const int rmax = a.Rnu == 1 ? 1 : (a.Rnu <= 4 ? 4 : 8);
     const size_t budget = 200 * 1024;

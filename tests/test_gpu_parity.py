@@ -177,6 +177,8 @@ def synth_batch(rng, n, D, density):
 
 @pytest.mark.parametrize("dtype", ["f32", "bf16"])
 @pytest.mark.parametrize("model,D,B,C", [("nb", 20000, 40, 1), ("nb", 30000, 24, 2), ("nb", 2000, 300, 1),
+                                         ("nb1", 20000, 200, 1), ("nb1", 30000, 160, 1), ("nb1", 2000, 300, 1),
+                                         ("nb1", 4000, 33, 1),
                                          ("vmf", 20000, 40, 1), ("vmf", 30000, 24, 3), ("vmf", 2000, 300, 1)])
 def test_large_feature_axis_vs_oracle(mmv, ctx, model, D, B, C, dtype):
     """fp32 mode: 1e-4; bf16 mode (tcgen05 GEMMs, bf16 operands, fp32 accumulate): 1e-2 (north_star)."""
@@ -185,7 +187,11 @@ def test_large_feature_axis_vs_oracle(mmv, ctx, model, D, B, C, dtype):
     x = synth_batch(rng, B, D, 0.05)
     c = np.ones((B, 1), np.float32) if C == 1 else rng.normal(size=(B, C)).astype(np.float32)
     csr = mmv.CSR.from_dense(ctx, x, c)
-    if model == "nb":
+    if model == "nb1":   # default over-dispersion dims (nu_h = nu_r = 1): the tuned K4 kernel
+        m = mmv.Model.nb(ctx, D, C, [96], [80], mu_r=8, nu_h=1, nu_r=1, seed=5)
+        eps = [rng.normal(size=(B, 8)).astype(np.float32), rng.normal(size=(B, 1)).astype(np.float32)]
+        model = "nb"
+    elif model == "nb":
         m = mmv.Model.nb(ctx, D, C, [96], [80], mu_r=8, nu_h=2, nu_r=2, seed=5)
         eps = [rng.normal(size=(B, 8)).astype(np.float32), rng.normal(size=(B, 2)).astype(np.float32)]
     else:
