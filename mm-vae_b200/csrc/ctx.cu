@@ -150,6 +150,37 @@ mmv_host_free(void *p)
 }
 
 // ------------------------------------------------------------------ CSR
+// One warp per cell: raises *flag when gene ids are not strictly increasing inside a cell.
+// The K4/K5 kernels bisect a cell's nonzeros by gene slice when the flag stays 0.
+__global__ void
+csr_check_sorted_kernel(const int64_t *indptr, const int32_t *indices, int64_t n_cells, int *flag)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarp = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    bool bad = false;
+    for (int64_t i = warp; i < n_cells; i += nwarp) {
+        const int64_t b = indptr[i], e = indptr[i + 1];
+        for (int64_t q = b + 1 + lane; q < e; q += 32) bad |= indices[q] <= indices[q - 1];
+    }
+    if (__any_sync(0xffffffffu, bad) && lane == 0) *flag = 1;
+}
+
+static int
+csr_check_sorted(mmv_csr *s)
+{
+    cudaStream_t st = s->ctx->stream;
+    if (!s->d_unsorted) MMV_CUDA(cudaMalloc(&s->d_unsorted, sizeof(int)));
+    MMV_CUDA(cudaMemsetAsync(s->d_unsorted, 0, sizeof(int), st));
+    if (s->nnz == 0) return 0;
+    const int64_t want = (s->n_cells * 32 + 255) / 256;
+    const int grid = (int)(want < 1 ? 1 : (want > 148 * 16 ? 148 * 16 : want));
+    csr_check_sorted_kernel<<<grid, 256, 0, st>>>(s->indptr, s->indices, s->n_cells, s->d_unsorted);
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
 static int
 csr_validate(int64_t n_cells, int64_t n_genes, const int64_t *indptr, const int32_t *indices, int64_t *max_row,
              bool check_indices)
@@ -218,7 +249,7 @@ csr_update_impl(mmv_csr *s, int64_t n_cells, const int64_t *indptr, const int32_
     s->nnz = nnz;
     if (mx > s->max_row_nnz) s->max_row_nnz = mx;
     s->h2d_bytes = sizeof(int64_t) * (n_cells + 1) + 8 * nnz + (covar ? sizeof(float) * n_cells * s->c_dim : 0);
-    return 0;
+    return csr_check_sorted(s);
 }
 
 // Streaming path: gene ids are range-checked once per resident upload only; a
@@ -270,6 +301,11 @@ mmv_csr_wrap_device(mmv_ctx *ctx, int64_t n_cells, int64_t n_genes, int64_t nnz,
     s->cov = const_cast<float *>(d_covar);
     s->has_cov = d_covar != nullptr;
     s->c_dim = d_covar ? c_dim : (c_dim > 0 ? c_dim : 1);
+    MMV_CUDA(cudaSetDevice(ctx->device));
+    if (csr_check_sorted(s) != 0) {
+        delete s;
+        return 1;
+    }
     *out = s;
     return 0;
 }
@@ -286,6 +322,7 @@ mmv_csr_destroy(mmv_csr *s)
         cudaFree(s->vals);
         cudaFree(s->cov);
     }
+    cudaFree(s->d_unsorted);
     delete s;
     return 0;
 }

@@ -30,6 +30,8 @@ struct mmv_csr {
     bool has_cov = false;
     bool borrowed = false;     // device arrays owned by the caller (mmv_csr_wrap_device)
     size_t h2d_bytes = 0;      // bytes copied by the last update (bench accounting)
+    int *d_unsorted = nullptr; // device flag: 1 if some cell's gene ids are not strictly increasing (set on the
+                               // ctx stream by every upload / update / wrap; kernels that bisect rows read it)
 };
 
 namespace mmv {

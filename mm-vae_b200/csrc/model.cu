@@ -907,6 +907,7 @@ nb_forward_backward(const step_t &s)
     k.B = B; k.D = D; k.C = C; k.Rnu = Rnu; k.inv_B = s.inv_B;
     k.loss_acc = m->acc + 0;
     k.allow_fast = m->nb_fast ? 1 : 0;
+    k.unsorted = s.csr->d_unsorted;
     if (m->debug_outputs) {
         k.recon_mu = WS("recon_mu", (size_t)B * D); k.recon_nu = WS("recon_nu", (size_t)B * D);
         NEED(k.recon_mu); NEED(k.recon_nu);

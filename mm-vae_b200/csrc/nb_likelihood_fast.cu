@@ -92,6 +92,32 @@ bar_wait(uint32_t bar, uint32_t parity)
         "}\n" ::"r"(bar), "r"(parity) : "memory");
 }
 
+// lgamma(nu) - lgamma(nu + x) + lgamma(x + 1) and digamma(nu) - digamma(nu + x) for a count x.
+// Small integer counts (the bulk of single-cell data) use the exact product forms
+//   lgamma(nu + x) - lgamma(nu) = log prod_{k<x} (nu + k),  digamma(nu + x) - digamma(nu) = P'(nu) / P(nu)
+// on the FMA pipe with one lg2 and one rcp; anything else falls back to libdevice.
+__constant__ float kLogFact[9] = { 0.f, 0.f, 0.6931471806f, 1.7917594692f, 3.1780538303f, 4.7874917428f,
+                                   6.5792512120f, 8.5251613611f, 10.6046029027f };
+
+__device__ __forceinline__ void
+count_terms(float nu, float x, float &lg_terms, float &dig_diff)
+{
+    const int xi = (int)x;
+    if ((float)xi == x && xi >= 1 && xi <= 8) {
+        float P = nu, dP = 1.f;
+        for (int k = 1; k < xi; ++k) {
+            const float f = nu + (float)k;
+            dP = fmaf(dP, f, P);
+            P *= f;
+        }
+        lg_terms = kLogFact[xi] - __logf(P);
+        dig_diff = -dP * rcp_f(P);
+    } else {
+        lg_terms = lgammaf(nu) + lgammaf(x + 1.f) - lgammaf(nu + x);
+        dig_diff = digamma_f(nu) - digamma_f(nu + x);
+    }
+}
+
 template <int EPT>
 __global__ void __launch_bounds__(kT, 1)
 nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
@@ -99,9 +125,11 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = cs > 1 ? (int)cluster.block_rank() : 0;
     const int cluster_id = blockIdx.x / cs, n_clusters = gridDim.x / cs;
-    const int tid = threadIdx.x, D = a.D;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, D = a.D;
+    constexpr int NW = kT / 32;
     const int j0 = rank * Ds, nj = max(0, min(D - j0, Ds));
     const bool grad = a.dlogits != nullptr || a.dlogits_bf16 != nullptr;
+    const bool sorted = a.unsorted != nullptr && *a.unsorted == 0;
 
     extern __shared__ __align__(16) float smem[];
     float *sG0 = smem, *sG1 = sG0 + Ds;          // TMA landing buffers (raw decoder output)
@@ -109,8 +137,9 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
     float *s_ub = s_ab + Ds;                     // nu_decoding.bias - nu_bias
     float *s_wn = s_ub + Ds;                     // nu_decoding.weight[:, 0]
     float *scratch = s_wn + Ds;                  // [2 * 32]
-    float *slots = scratch + 64;                 // [2][3][2]
-    uint64_t *bars = reinterpret_cast<uint64_t *>(slots + 16);   // [2], 8-byte aligned (Ds % 4 == 0)
+    float *slots = scratch + 64;                 // [2][2 + 2] cluster exchange, double buffered by row parity
+    float *wstat = slots + 8;                    // [2][NW][4] per-warp (max, sumexp, n_lo, n_hi)
+    uint64_t *bars = reinterpret_cast<uint64_t *>(wstat + 2 * NW * 4);   // [2], 8-byte aligned (Ds % 4 == 0)
     const uint32_t bar0 = smem_addr(bars), bar1 = bar0 + 8;
 
     if (tid == 0) {
@@ -140,7 +169,8 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
     for (int it = 0; row < a.B; row += n_clusters, ++it) {
         const int cur = it & 1;
         const float *sG = cur ? sG1 : sG0;
-        float *slot = slots + cur * 6;
+        float *slot = slots + cur * 4;
+        float *ws = wstat + cur * NW * 4;
         const int next = row + n_clusters;
         if (tid == 0 && next < a.B && nj > 0)   // stream the next row while this one is processed
             bulk_load(smem_addr(cur ? sG0 : sG1), a.G + (size_t)next * D + j0, row_bytes, cur ? bar0 : bar1);
@@ -151,38 +181,89 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         const float zn = a.znu[row];
         const int64_t nz_beg = a.indptr[cell], nz_end = a.indptr[cell + 1];
 
+        // position of this CTA's gene slice inside the (sorted) nonzeros of the cell
+        int n_lo = 0, n_hi = 0;
+        if (sorted)
+            for (int64_t q = nz_beg + tid; q < nz_end; q += kT) {
+                const int j = a.indices[q];
+                n_lo += j < j0;
+                n_hi += j < j0 + nj;
+            }
+
         if (nj > 0) bar_wait(cur ? bar1 : bar0, (uint32_t)(it >> 1) & 1u);
 
-        // ---- pass 1: logits into registers, row max
+        // ---- pass 1: logits into registers; softmax numerators against the WARP max, so one
+        //      block hop + one cluster hop give max and sum together (online-softmax merge)
         float v[EPT];
-        float mx = -INFINITY;
+        float wm = -INFINITY;
 #pragma unroll
         for (int k = 0; k < EPT; ++k) {
             const int jj = tid + k * kT;
             v[k] = jj < nj ? sG[jj] + s_ab[jj] : -INFINITY;
-            mx = fmaxf(mx, v[k]);
+            wm = fmaxf(wm, v[k]);
         }
-        mx = cluster_max(mx, slot + 0, scratch, cluster, cs);
-
-        // ---- pass 2: softmax numerators
-        float se[1] = { 0.f };
+        wm = warp_max(wm);
+        float wsum = 0.f;
+        if (wm > -INFINITY) {
 #pragma unroll
-        for (int k = 0; k < EPT; ++k) {
-            v[k] = __expf(v[k] - mx);          // exp(-inf) = 0 for the padding lanes
-            se[0] += v[k];
+            for (int k = 0; k < EPT; ++k) {
+                v[k] = __expf(v[k] - wm);          // exp(-inf) = 0 for the padding lanes
+                wsum += v[k];
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < EPT; ++k) v[k] = 0.f;
         }
-        cluster_sum<1>(se, slot + 2, scratch, cluster, cs);
-        const float inv_sum = 1.f / se[0];
-        if (a.row_lse && rank == 0 && tid == 0) a.row_lse[row] = mx + logf(se[0]);
+        wsum = warp_sum(wsum);
+        n_lo = __reduce_add_sync(0xffffffffu, n_lo);
+        n_hi = __reduce_add_sync(0xffffffffu, n_hi);
+        if (lane == 0) {
+            ws[warp * 4 + 0] = wm;
+            ws[warp * 4 + 1] = wsum;
+            ws[warp * 4 + 2] = __int_as_float(n_lo);
+            ws[warp * 4 + 3] = __int_as_float(n_hi);
+        }
+        __syncthreads();
+        float bm = lane < NW ? ws[lane * 4 + 0] : -INFINITY;
+        const float bs_in = lane < NW ? ws[lane * 4 + 1] : 0.f;
+        int c_lo = lane < NW ? __float_as_int(ws[lane * 4 + 2]) : 0;
+        int c_hi = lane < NW ? __float_as_int(ws[lane * 4 + 3]) : 0;
+        const float bmax = warp_max(bm);
+        float bsum = warp_sum(bm > -INFINITY ? bs_in * __expf(bm - bmax) : 0.f);
+        c_lo = __reduce_add_sync(0xffffffffu, c_lo);
+        c_hi = __reduce_add_sync(0xffffffffu, c_hi);
+        float gmax = bmax, gsum = bsum;
+        if (cs > 1) {
+            if (tid == 0) { slot[0] = bmax; slot[1] = bsum; }
+            cluster.sync();
+            gmax = -INFINITY;
+            float rm[8], rs[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                rm[r] = -INFINITY; rs[r] = 0.f;
+                if (r < cs) {
+                    const float *remote = cluster.map_shared_rank(slot, r);
+                    rm[r] = remote[0]; rs[r] = remote[1];
+                }
+                gmax = fmaxf(gmax, rm[r]);
+            }
+            gsum = 0.f;
+#pragma unroll
+            for (int r = 0; r < 8; ++r) gsum += rm[r] > -INFINITY ? rs[r] * __expf(rm[r] - gmax) : 0.f;
+        }
+        const float inv_sum = 1.f / gsum;
+        const float scale = wm > -INFINITY ? __expf(wm - gmax) * inv_sum : 0.f;
+        if (a.row_lse && rank == 0 && tid == 0) a.row_lse[row] = gmax + logf(gsum);
+        const int64_t q_lo = sorted ? nz_beg + c_lo : nz_beg, q_hi = sorted ? nz_beg + c_hi : nz_end;
 
-        // ---- pass 3: dense sweep assuming x = 0 (lgammas cancel, no digamma)
+        // ---- pass 2: dense sweep assuming x = 0 (lgammas cancel, no digamma)
         float g[EPT];
         float red[2] = { 0.f, 0.f };           // s = sum g p ; d znu
 #pragma unroll
         for (int k = 0; k < EPT; ++k) {
             const int jj = tid + k * kT;
             if (jj < nj) {
-                const float p = v[k] * inv_sum;
+                const float p = v[k] * scale;
                 const float wn = s_wn[jj];
                 const elem_t e = elem_fast(p, depth, fmaf(zn, wn, s_ub[jj]));
                 nll_acc = fmaf(e.nu, e.l1p, nll_acc);
@@ -198,22 +279,24 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
             }
         }
 
-        // ---- pass 3b: compact loop over this cell's nonzeros that fall in the slice
-        for (int64_t q = nz_beg + tid; q < nz_end; q += kT) {
+        // ---- pass 2b: compact loop over this cell's nonzeros that fall in the slice
+        for (int64_t q = q_lo + tid; q < q_hi; q += kT) {
             const int j = a.indices[q];
             const int jj = j - j0;
             const float x = a.vals[q];
             if (jj < 0 || jj >= nj || x == 0.f) continue;
-            const float p = __expf(sG[jj] + s_ab[jj] - mx) * inv_sum;
+            const float p = __expf(sG[jj] + s_ab[jj] - gmax) * inv_sum;
             const float wn = s_wn[jj];
             const elem_t e = elem_fast(p, depth, fmaf(zn, wn, s_ub[jj]));
             const float L = __logf(e.m + e.nu);
+            float lg_terms, dig_diff;
+            count_terms(e.nu, x, lg_terms, dig_diff);
             // nb.hh:522-528 minus the x = 0 value already counted
-            nll_acc += lgammaf(e.nu) + lgammaf(x + 1.f) - lgammaf(e.nu + x) + x * (L - __logf(e.m));
+            nll_acc += lg_terms + x * (L - __logf(e.m));
             if (grad) {
                 const float gx = (e.nu + x) * e.inv_mnu - x * rcp_f(e.m);
                 red[0] = fmaf(gx - e.nu * e.inv_mnu, p, red[0]);
-                const float ddnu = digamma_f(e.nu) - digamma_f(e.nu + x) + x * e.inv_mnu;   // dnu_x - dnu_0
+                const float ddnu = dig_diff + x * e.inv_mnu;   // dnu_x - dnu_0
                 const float ddu = ddnu * e.sig_mask * a.inv_B;
                 atomicAdd(a.col_du + j, ddu);
                 atomicAdd(a.col_duz + j, ddu * zn);
@@ -222,10 +305,10 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         }
 
         if (grad) {
-            cluster_sum<2>(red, slot + 4, scratch, cluster, cs);
+            cluster_sum<2>(red, slot + 2, scratch, cluster, cs);
             const float s = red[0];
             const float coef = depth * a.inv_B;
-            // ---- pass 4: dL/dlogit_j = (d_i / B) p_j (g_j - s_i), coalesced
+            // ---- pass 3: dL/dlogit_j = (d_i / B) p_j (g_j - s_i), coalesced
             if (a.dlogits_bf16) {
                 __nv_bfloat16 *drow = reinterpret_cast<__nv_bfloat16 *>(a.dlogits_bf16) + (size_t)row * D + j0;
 #pragma unroll
@@ -246,13 +329,13 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
                 a.dznu[row] = red[1];
             }
             __syncthreads();   // dense stores of this block are visible before the patches below
-            // ---- pass 4b: patch the entries of the nonzeros
-            for (int64_t q = nz_beg + tid; q < nz_end; q += kT) {
+            // ---- pass 3b: patch the entries of the nonzeros
+            for (int64_t q = q_lo + tid; q < q_hi; q += kT) {
                 const int j = a.indices[q];
                 const int jj = j - j0;
                 const float x = a.vals[q];
                 if (jj < 0 || jj >= nj || x == 0.f) continue;
-                const float p = __expf(sG[jj] + s_ab[jj] - mx) * inv_sum;
+                const float p = __expf(sG[jj] + s_ab[jj] - gmax) * inv_sum;
                 const elem_t e = elem_fast(p, depth, fmaf(zn, s_wn[jj], s_ub[jj]));
                 const float gx = (e.nu + x) * e.inv_mnu - x * rcp_f(e.m);
                 const float dl = coef * p * (gx - s);
@@ -284,7 +367,7 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
 size_t
 fast_smem_bytes(int Ds)
 {
-    return sizeof(float) * ((size_t)5 * Ds + 64 + 16) + 16;
+    return sizeof(float) * ((size_t)5 * Ds + 64 + 8 + 2 * (kT / 32) * 4) + 16;
 }
 
 } // namespace
@@ -311,11 +394,8 @@ launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stre
         : ept <= 8 ? nb_likelihood_fast_kernel<8> : ept <= 12 ? nb_likelihood_fast_kernel<12> : nb_likelihood_fast_kernel<16>;
     const size_t smem = fast_smem_bytes(Ds);
     MMV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int n_clusters = num_sms / cs;
-    if (n_clusters > a.B) n_clusters = a.B;
-    if (n_clusters < 1) n_clusters = 1;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(n_clusters * cs);
+    cfg.gridDim = dim3(num_sms / cs * cs);
     cfg.blockDim = dim3(kT);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
@@ -326,6 +406,17 @@ launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stre
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    // persistent clusters: exactly one wave.  A GPC holds fewer whole clusters than SMs / cs
+    // (148 SMs take 33 clusters of 4, not 37), and a second wave would double the kernel time.
+    int n_clusters = num_sms / cs;
+    if (cs > 1) {
+        int fit = 0;
+        MMV_CUDA(cudaOccupancyMaxActiveClusters(&fit, kern, &cfg));
+        if (fit > 0 && fit < n_clusters) n_clusters = fit;
+    }
+    if (n_clusters > a.B) n_clusters = a.B;
+    if (n_clusters < 1) n_clusters = 1;
+    cfg.gridDim = dim3(n_clusters * cs);
     MMV_CUDA(cudaLaunchKernelEx(&cfg, kern, a, cs, Ds));
     ::mmv::count_launch();
     return 0;
