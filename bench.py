@@ -339,7 +339,7 @@ def run_own(args):
         t, c = model.profile_read(name)
         if c:
             prof[name] = (t, c)
-    for name in ("batch_csc", "clip_adam", "allreduce", "colsum", "to_bf16"):
+    for name in ("panel_build", "batch_csc", "clip_adam", "allreduce", "colsum", "to_bf16"):
         t, c = model.profile_read(name)
         if c:
             prof[name] = (t, c)

@@ -19,6 +19,7 @@
 // (leading dimensions must be multiples of 8 elements = 16 bytes).
 #include "common.cuh"
 #include "kernels.hh"
+#include "tc_ptx.cuh"
 
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -34,84 +35,6 @@ constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2, B_BYTES = BLOCK_N * BLOCK_K * 2;
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int TMEM_COLS = 128;
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
-
-__device__ __forceinline__ uint32_t
-smem_u32(const void *p)
-{
-    return (uint32_t)__cvta_generic_to_shared(p);
-}
-
-__device__ __forceinline__ void
-mbar_init(uint32_t bar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-
-__device__ __forceinline__ void
-mbar_expect_tx(uint32_t bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-
-__device__ __forceinline__ void
-mbar_wait(uint32_t bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra WAIT_DONE;\n"
-        "bra WAIT_LOOP;\n"
-        "WAIT_DONE:\n"
-        "}\n" ::"r"(bar), "r"(parity) : "memory");
-}
-
-__device__ __forceinline__ void
-tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1)
-{
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-                 ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
-}
-
-__device__ __forceinline__ void
-umma_commit(uint32_t bar)   // arrives on `bar` when all previously issued MMAs have completed
-{
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-
-__device__ __forceinline__ void
-umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
-{
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
-        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-
-// Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start address, leading /
-// stride byte offsets in 16-byte units, version 1 (Blackwell), SWIZZLE_128B.
-__device__ __forceinline__ uint64_t
-make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes)
-{
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
-    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
-    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
-    d |= (uint64_t)1 << 46;   // version
-    d |= (uint64_t)2 << 61;   // LayoutType::SWIZZLE_128B
-    return d;
-}
-
-// Instruction descriptor (cute::UMMA::InstrDescriptor), kind::f16: D fp32, A/B bf16.
-__host__ __device__ constexpr uint32_t
-make_idesc(bool a_mn, bool b_mn)
-{
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) |
-        ((uint32_t)(BLOCK_N >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
-}
 
 struct params_t {
     float *C;
@@ -187,7 +110,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else if (warp == 1) {
         // ================= MMA issuer =================
         if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc(A_MN, B_MN);
+            constexpr uint32_t idesc = make_idesc(A_MN, B_MN, BLOCK_M, BLOCK_N);
             for (int kb = 0; kb < num_kb; ++kb) {
                 const int s = kb % STAGES;
                 const uint32_t ph = (kb / STAGES) & 1;
@@ -301,6 +224,13 @@ make_map(CUtensorMap *map, const void *base, uint64_t inner, uint64_t outer, uin
 }
 
 } // namespace
+
+int
+make_tma_map_bf16(void *map, const void *base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+                  uint32_t box_outer)
+{
+    return make_map(reinterpret_cast<CUtensorMap *>(map), base, inner, outer, ld, box_inner, box_outer);
+}
 
 bool
 gemm_tc_supported(const gemm_tc_args_t &g)

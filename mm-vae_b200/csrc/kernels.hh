@@ -39,6 +39,9 @@ struct gemm_tc_args_t {
 bool gemm_tc_supported(const gemm_tc_args_t &g);
 int launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream);
 int launch_to_bf16(const float *x, void *y, size_t n, cudaStream_t st);
+// SWIZZLE_128B tiled map over a row-major bf16 matrix [outer x inner] (leading dimension ld elements); map = CUtensorMap*
+int make_tma_map_bf16(void *map, const void *base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+                      uint32_t box_outer);
 
 // ---- K1 sparse encoder (sparse_encoder.cu)
 struct senc_args_t {
@@ -98,6 +101,56 @@ struct senc_bwd_args_t {
     float *dwdepth = nullptr;         // [D]
 };
 int launch_senc_bwd(const senc_bwd_args_t &a, cudaStream_t st);
+
+// ---- K1 tensor-core path (senc_tc.cu): per-minibatch tiled-COO "panel" + densify-in-smem tcgen05 GEMMs
+// Panel: the minibatch's nonzeros bucketed by (tile of 64 batch rows, chunk of 64 genes); bucket (T, k) is
+// the run [bucket_ptr[T * (nK + 1) + k], bucket_ptr[T * (nK + 1) + k + 1]) of `ent` / `xraw`.
+// ent = row_in_tile << 26 | gene_in_chunk << 20 | bf16(log1p(x) [/ ||log1p x_i||] / t_gene).
+struct panel_args_t {
+    const int64_t *indptr = nullptr;
+    const int32_t *indices = nullptr;
+    const float *vals = nullptr;
+    const int32_t *cells = nullptr;
+    int B = 0, D = 0, angular = 0;
+    const float *inv_t = nullptr;
+    const float *WnuT = nullptr, *bnu = nullptr;       // nb: nu encoder + depth on raw counts (nullable)
+    int H = 0;
+    const float *wdepth = nullptr, *bdepth = nullptr;
+    float *Hnu = nullptr, *dpre = nullptr, *rownorm = nullptr;
+    int *rowptr = nullptr;                             // [B + 1] workspace
+    int *bucket_ptr = nullptr;                         // [nT * (nK + 1)]
+    uint32_t *ent = nullptr;                           // [nnz of the minibatch]
+    float *xraw = nullptr;                             // [nnz of the minibatch] raw counts, same order
+};
+inline int panel_tiles(int B) { return (B + 63) / 64; }
+inline int panel_chunks(int D) { return (D + 63) / 64; }
+int launch_panel_build(const panel_args_t &p, cudaStream_t st);
+
+struct senc_tc_args_t {
+    const int *bucket_ptr = nullptr;
+    const uint32_t *ent = nullptr;
+    int B = 0, D = 0, h1 = 0;
+    const void *dense_bf16 = nullptr;   // fwd: effective W1^T [D x h1] bf16 ; bwd: delta [B x h1] bf16
+    // forward epilogue: H1 = acc + bias_eff (ReLU optional), fp32 + bf16 copies
+    const float *bias_eff = nullptr;
+    int relu = 0;
+    float *H1 = nullptr;
+    void *H1_bf16 = nullptr;
+    // backward epilogue (see senc_bwd_args_t for the formulas)
+    const float *W1T = nullptr, *col_scale = nullptr, *Delta = nullptr, *inv_t = nullptr, *x_mean = nullptr;
+    int angular = 0, accumulate = 1;
+    float *dW1T = nullptr;
+    float *dot0 = nullptr, *dot1 = nullptr;   // [D] each, zeroed by the caller
+};
+bool senc_tc_supported(int h1);
+int launch_senc_tc_fwd(const senc_tc_args_t &a, cudaStream_t st);
+int launch_senc_tc_bwd(const senc_tc_args_t &a, cudaStream_t st);
+// d x_mean, d ln_x_sd from the per-gene dots; dWnu / dw_depth from the panel's raw counts
+int launch_senc_tc_finish(const float *dot0, const float *dot1, const float *inv_t, const float *x_mean,
+                          const float *ln_x_sd, float *dx_mean, float *dln_x_sd, int D, cudaStream_t st);
+int launch_panel_aux_bwd(const int *bucket_ptr, const uint32_t *ent, const float *xraw, int B, int D, int H,
+                         const float *dHnu, const float *ddpre, float *dWnuT, float *dwdepth, cudaStream_t st);
+int launch_w1eff_bf16(const float *W1T, const float *col_scale, void *out, int D, int h1, cudaStream_t st);
 
 // ---- K4 NB likelihood (nb_likelihood.cu)
 struct nb_lik_args_t {

@@ -846,6 +846,71 @@ build_csc(const step_t &s, const float *rownorm)
     return launch_batch_csc(c, s.st);
 }
 
+// K1 tensor-core path: is it usable for this model / step?
+bool
+senc_tc_ok(const step_t &s)
+{
+    const mmv_model *m = s.m;
+    return m->use_tc && senc_tc_supported(m->enc[0].out) && m->H <= 128 && (m->D % 8 == 0 || true);
+}
+
+// Re-bucket the minibatch into the tiled-COO panel ("pan_*" workspaces) and run the densify GEMM
+// H1 = A W1eff^T + bias_eff.  Also produces Hnu / dpre (nb) or rownorm (vmf).
+int
+senc_tc_forward(const step_t &s, const senc_args_t &e, const void *w1eff_bf16)
+{
+    mmv_model *m = s.m;
+    const int B = s.B, D = (int)m->D, h1 = e.h1;
+    const size_t cap = (size_t)B * (size_t)std::max<int64_t>(s.csr->max_row_nnz, 1);
+    const int nT = panel_tiles(B), nK = panel_chunks(D);
+    panel_args_t p;
+    p.indptr = e.indptr; p.indices = e.indices; p.vals = e.vals; p.cells = e.cells;
+    p.B = B; p.D = D; p.angular = e.angular; p.inv_t = e.inv_t;
+    p.WnuT = e.WnuT; p.bnu = e.bnu; p.H = e.angular ? 0 : e.H; p.wdepth = e.wdepth; p.bdepth = e.bdepth;
+    p.Hnu = e.Hnu; p.dpre = e.dpre; p.rownorm = e.rownorm;
+    p.rowptr = (int *)WS("pan_rowptr", B + 1); p.bucket_ptr = (int *)WS("pan_bptr", (size_t)nT * (nK + 1));
+    p.ent = (uint32_t *)WS("pan_ent", cap); p.xraw = WS("pan_x", cap);
+    NEED(p.rowptr); NEED(p.bucket_ptr); NEED(p.ent); NEED(p.xraw);
+    {
+        PROF("panel_build");
+        MMV_TRY(launch_panel_build(p, s.st));
+    }
+    senc_tc_args_t a;
+    a.bucket_ptr = p.bucket_ptr; a.ent = p.ent; a.B = B; a.D = D; a.h1 = h1;
+    a.dense_bf16 = w1eff_bf16; a.bias_eff = e.bias_eff; a.relu = e.relu; a.H1 = e.H1;
+    a.H1_bf16 = m->W("enc_act0.bf", (size_t)B * h1 * 2); NEED(a.H1_bf16);
+    {
+        PROF("senc_fwd");
+        MMV_TRY(launch_senc_tc_fwd(a, s.st));
+    }
+    m->bf_cache[e.H1] = a.H1_bf16;
+    return 0;
+}
+
+// dW1 (effective), d x_mean, d ln_x_sd (+ dWnu, dw_depth for nb) from the panel.
+int
+senc_tc_backward(const step_t &s, const senc_bwd_args_t &b)
+{
+    mmv_model *m = s.m;
+    const int B = s.B, D = (int)m->D, h1 = b.h1;
+    senc_tc_args_t a;
+    a.bucket_ptr = m->ws["pan_bptr"].as<int>(); a.ent = m->ws["pan_ent"].as<uint32_t>();
+    a.B = B; a.D = D; a.h1 = h1;
+    MMV_TRY(bf16_of(s, b.delta, (size_t)B * h1, &a.dense_bf16));
+    a.W1T = b.W1T; a.col_scale = b.col_scale; a.Delta = b.Delta; a.inv_t = b.inv_t; a.x_mean = b.x_mean;
+    a.angular = b.angular; a.accumulate = b.accumulate; a.dW1T = b.dW1T;
+    float *dots = WS("pan_dots", 2 * (size_t)D); NEED(dots);
+    a.dot0 = dots; a.dot1 = dots + D;
+    MMV_CUDA(cudaMemsetAsync(dots, 0, sizeof(float) * 2 * D, s.st));
+    PROF("senc_bwd");
+    MMV_TRY(launch_senc_tc_bwd(a, s.st));
+    MMV_TRY(launch_senc_tc_finish(a.dot0, a.dot1, b.inv_t, b.x_mean, b.ln_x_sd, b.dx_mean, b.dln_x_sd, D, s.st));
+    if (!b.angular && b.dWnuT)
+        MMV_TRY(launch_panel_aux_bwd(a.bucket_ptr, a.ent, m->ws["pan_x"].as<float>(), B, D, b.H, b.dHnu, b.ddpre,
+                                     b.dWnuT, b.dwdepth, s.st));
+    return 0;
+}
+
 } // namespace
 
 namespace {
@@ -875,7 +940,12 @@ nb_forward_backward(const step_t &s)
     e.WnuT = m->P(m->nu_enc.w); e.bnu = m->P(m->nu_enc.b); e.H = H;
     e.wdepth = m->P(m->depth.w); e.bdepth = m->P(m->depth.b);
     e.Hnu = WS("Hnu", (size_t)B * H); e.dpre = WS("dpre", B); NEED(e.Hnu); NEED(e.dpre);
-    {
+    const bool tc_senc = senc_tc_ok(s);
+    if (tc_senc) {
+        const void *w1b = nullptr;
+        MMV_TRY(bf16_of(s, m->P(L0.w), (size_t)D * h1, &w1b));
+        MMV_TRY(senc_tc_forward(s, e, w1b));
+    } else {
         PROF("senc_fwd");
         MMV_TRY(launch_senc_fwd(e, s.st));
     }
@@ -965,19 +1035,22 @@ nb_forward_backward(const step_t &s)
         MMV_TRY(launch_colsum(c2, s.st));
     }
 
-    {
+    if (!tc_senc) {
         PROF("batch_csc");
         MMV_TRY(build_csc(s, nullptr));
     }
     senc_bwd_args_t b;
-    b.gene_ptr = m->ws["csc_ptr"].as<int>(); b.ent_row = m->ws["csc_row"].as<int>();
-    b.ent_l = m->ws["csc_l"].as<float>(); b.ent_x = m->ws["csc_x"].as<float>();
+    if (!tc_senc) {
+        b.gene_ptr = m->ws["csc_ptr"].as<int>(); b.ent_row = m->ws["csc_row"].as<int>();
+        b.ent_l = m->ws["csc_l"].as<float>(); b.ent_x = m->ws["csc_x"].as<float>();
+    }
     b.D = D; b.h1 = h1; b.H = H; b.angular = 0; b.accumulate = 1;
     b.delta = m->ws["d_enc0"].as<float>(); b.Delta = m->ws["Delta"].as<float>();
     b.W1T = m->P(L0.w); b.inv_t = inv_t; b.x_mean = m->P(m->t_x_mean); b.ln_x_sd = m->P(m->t_ln_x_sd);
     b.dW1T = m->want_grad(L0.w) ? m->G(L0.w) : nullptr;
     b.dx_mean = m->G(m->t_x_mean); b.dln_x_sd = m->G(m->t_ln_x_sd);
     b.dHnu = dHnu; b.ddpre = k.ddpre; b.dWnuT = m->G(m->nu_enc.w); b.dwdepth = m->G(m->depth.w);
+    if (tc_senc) return senc_tc_backward(s, b);
     PROF("senc_bwd");
     return launch_senc_bwd(b, s.st);
 }
@@ -1007,7 +1080,12 @@ vmf_forward_backward(const step_t &s)
     e.B = B; e.D = D; e.angular = 1; e.W1T = m->P(L0.w); e.h1 = h1; e.inv_t = inv_t; e.bias_eff = bias_eff;
     e.col_scale = col_scale; e.relu = m->relu;
     e.H1 = WS("enc_act0", (size_t)B * h1); e.rownorm = WS("rownorm", B); NEED(e.H1); NEED(e.rownorm);
-    {
+    const bool tc_senc = senc_tc_ok(s);
+    if (tc_senc) {   // B operand = (relu(W) + 1e-4) * col_scale, materialised in bf16 once per step
+        void *w1b = m->W("w1eff.bf", (size_t)D * h1 * 2); NEED(w1b);
+        MMV_TRY(launch_w1eff_bf16(m->P(L0.w), col_scale, w1b, D, h1, s.st));
+        MMV_TRY(senc_tc_forward(s, e, w1b));
+    } else {
         PROF("senc_fwd");
         MMV_TRY(launch_senc_fwd(e, s.st));
     }
@@ -1065,21 +1143,25 @@ vmf_forward_backward(const step_t &s)
     MMV_TRY(decoder_backward(s));
     MMV_TRY(encoder_backward(s, true));
 
-    {
+    if (!tc_senc) {
         PROF("batch_csc");
         MMV_TRY(build_csc(s, e.rownorm));
     }
     float *dWeff = WS("dW1eff", (size_t)D * h1); NEED(dWeff);
     float *dot = WS("ang_dot", std::max(h1, 1)); NEED(dot);
     senc_bwd_args_t b;
-    b.gene_ptr = m->ws["csc_ptr"].as<int>(); b.ent_row = m->ws["csc_row"].as<int>();
-    b.ent_l = m->ws["csc_l"].as<float>(); b.ent_x = m->ws["csc_x"].as<float>();
+    if (!tc_senc) {
+        b.gene_ptr = m->ws["csc_ptr"].as<int>(); b.ent_row = m->ws["csc_row"].as<int>();
+        b.ent_l = m->ws["csc_l"].as<float>(); b.ent_x = m->ws["csc_x"].as<float>();
+    }
     b.D = D; b.h1 = h1; b.H = 0; b.angular = 1; b.accumulate = 0;
     b.delta = m->ws["d_enc0"].as<float>(); b.Delta = m->ws["Delta"].as<float>();
     b.W1T = m->P(L0.w); b.col_scale = col_scale; b.inv_t = inv_t;
     b.x_mean = m->P(m->t_x_mean); b.ln_x_sd = m->P(m->t_ln_x_sd);
     b.dW1T = dWeff; b.dx_mean = m->G(m->t_x_mean); b.dln_x_sd = m->G(m->t_ln_x_sd);
-    {
+    if (tc_senc) {
+        MMV_TRY(senc_tc_backward(s, b));
+    } else {
         PROF("senc_bwd");
         MMV_TRY(launch_senc_bwd(b, s.st));
     }

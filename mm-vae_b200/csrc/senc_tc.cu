@@ -1,0 +1,578 @@
+// K1, tensor-core path — sparse x dense first encoder layer and its weight gradient on tcgen05.
+//
+// Replaces (same math as sparse_encoder.cu, which stays as the fp32 parity path):
+//   encode_mu first Linear            nb.hh:406-411   h1 = ((log1p x - x_mean) / t) W1^T + b1
+//   encode first Angular              vmf.hh:253-260, angular.hh:34-42
+//   nu_enc(x), depth(x) on raw counts nb.hh:448,498
+//   their autograd backward (dW1, d x_mean, d ln_x_sd, dW_nu, dw_depth)
+//
+// At 5 % density a gather formulation moves nnz x h1 weight elements through L2 (12.6 GB per
+// minibatch at cfg 4) and runs on the FMA pipe; the dense product is 20x more flops but the
+// tensor pipe is >20x faster and the weight tile is read once per 128 cells.  So the minibatch is
+// re-bucketed once per step into a tiled COO "panel" (tiles of 64 cells x 64 genes, packed 32-bit
+// entries), and the GEMM kernels DENSIFY one [128 x 64] bf16 operand tile per pipeline stage
+// directly in shared memory (SWIZZLE_128B K-major layout, written with st.shared, published to the
+// async proxy with fence.proxy.async) while TMA streams the dense operand; tcgen05.mma accumulates
+// in TMEM.  The same panel serves forward (rows = cells, K = genes) and backward (rows = genes,
+// K = cells) — only the scatter coordinates swap.
+#include "common.cuh"
+#include "kernels.hh"
+#include "tc_ptx.cuh"
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+namespace mmv {
+
+namespace {
+
+// ===========================================================================
+// panel build
+// ===========================================================================
+__global__ void
+batch_rowptr_kernel(const int64_t *indptr, const int32_t *cells, int B, int *rowptr)
+{
+    __shared__ int s_part[1024];
+    const int tid = threadIdx.x, T = blockDim.x;
+    const int per = (B + T - 1) / T;
+    const int r0 = min(B, tid * per), r1 = min(B, r0 + per);
+    int sum = 0;
+    for (int r = r0; r < r1; ++r) {
+        const int64_t c = cells ? (int64_t)cells[r] : (int64_t)r;
+        sum += (int)(indptr[c + 1] - indptr[c]);
+    }
+    s_part[tid] = sum;
+    __syncthreads();
+    for (int off = 1; off < T; off <<= 1) {   // Hillis-Steele inclusive scan
+        const int v = tid >= off ? s_part[tid - off] : 0;
+        __syncthreads();
+        s_part[tid] += v;
+        __syncthreads();
+    }
+    int run = s_part[tid] - sum;
+    for (int r = r0; r < r1; ++r) {
+        rowptr[r] = run;
+        const int64_t c = cells ? (int64_t)cells[r] : (int64_t)r;
+        run += (int)(indptr[c + 1] - indptr[c]);
+    }
+    if (tid == T - 1) rowptr[B] = s_part[T - 1];
+}
+
+constexpr int kPanelThreads = 512;
+
+__global__ void __launch_bounds__(kPanelThreads)
+panel_build_kernel(panel_args_t p, int nK)
+{
+    extern __shared__ int s_int[];
+    int *s_off = s_int;               // [nK + 1] exclusive offsets of the buckets of this tile
+    int *s_cur = s_int + nK + 1;      // [nK] fill cursors
+    __shared__ int s_scan[kPanelThreads];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = kPanelThreads / 32;
+    const int T = blockIdx.x, r0 = T * 64, nrows = min(64, p.B - r0);
+
+    for (int k = tid; k < nK; k += kPanelThreads) s_cur[k] = 0;
+    __syncthreads();
+    // ---- pass 1: bucket sizes
+    for (int r = warp; r < nrows; r += NW) {
+        const int64_t c = p.cells ? (int64_t)p.cells[r0 + r] : (int64_t)(r0 + r);
+        const int64_t beg = p.indptr[c], end = p.indptr[c + 1];
+        for (int64_t q = beg + lane; q < end; q += 32) atomicAdd(&s_cur[p.indices[q] >> 6], 1);
+    }
+    __syncthreads();
+    // ---- exclusive scan over the chunks (each thread owns a contiguous span)
+    const int per = (nK + kPanelThreads - 1) / kPanelThreads;
+    const int k0 = min(nK, tid * per), k1 = min(nK, k0 + per);
+    int sum = 0;
+    for (int k = k0; k < k1; ++k) sum += s_cur[k];
+    s_scan[tid] = sum;
+    __syncthreads();
+    for (int off = 1; off < kPanelThreads; off <<= 1) {
+        const int v = tid >= off ? s_scan[tid - off] : 0;
+        __syncthreads();
+        s_scan[tid] += v;
+        __syncthreads();
+    }
+    const int base = p.rowptr[r0];
+    int run = s_scan[tid] - sum;
+    for (int k = k0; k < k1; ++k) {
+        const int n = s_cur[k];
+        s_off[k] = run;
+        run += n;
+    }
+    if (tid == kPanelThreads - 1) s_off[nK] = s_scan[kPanelThreads - 1];
+    __syncthreads();
+    int *bp = p.bucket_ptr + (size_t)T * (nK + 1);
+    for (int k = tid; k <= nK; k += kPanelThreads) {
+        bp[k] = base + s_off[k];
+        if (k < nK) s_cur[k] = s_off[k];
+    }
+    __syncthreads();
+    // ---- pass 2: emit packed entries; per-row scalars on the way
+    for (int r = warp; r < nrows; r += NW) {
+        const int64_t c = p.cells ? (int64_t)p.cells[r0 + r] : (int64_t)(r0 + r);
+        const int64_t beg = p.indptr[c], end = p.indptr[c + 1];
+        float rs = 1.f;
+        if (p.angular) {   // vmf.hh:255: row L2 norm of log1p(x), F::normalize eps 1e-12
+            float sq = 0.f;
+            for (int64_t q = beg + lane; q < end; q += 32) {
+                const float l = log1pf(p.vals[q]);
+                sq = fmaf(l, l, sq);
+            }
+            sq = warp_sum(sq);
+            const float nrm = fmaxf(sqrtf(sq), 1e-12f);
+            rs = 1.f / nrm;
+            if (lane == 0 && p.rownorm) p.rownorm[r0 + r] = nrm;
+        }
+        float depth = 0.f;
+        for (int64_t q = beg + lane; q < end; q += 32) {
+            const int j = p.indices[q];
+            const float x = p.vals[q];
+            const float v = log1pf(x) * rs * p.inv_t[j];
+            const int pos = base + atomicAdd(&s_cur[j >> 6], 1);
+            const uint32_t bits = (uint32_t)__bfloat16_as_ushort(__float2bfloat16(v));
+            p.ent[pos] = ((uint32_t)r << 26) | ((uint32_t)(j & 63) << 20) | bits;
+            p.xraw[pos] = x;
+            if (p.wdepth) depth = fmaf(x, p.wdepth[j], depth);
+        }
+        if (p.wdepth) {   // nb.hh:498 (raw counts)
+            depth = warp_sum(depth);
+            if (lane == 0) p.dpre[r0 + r] = depth + p.bdepth[0];
+        }
+        for (int h = 0; h < p.H; ++h) {   // nb.hh:448 (raw counts); H = 1 by default
+            float s = 0.f;
+            for (int64_t q = beg + lane; q < end; q += 32)
+                s = fmaf(p.vals[q], p.WnuT[(size_t)p.indices[q] * p.H + h], s);
+            s = warp_sum(s);
+            if (lane == 0) p.Hnu[(size_t)(r0 + r) * p.H + h] = s + p.bnu[h];
+        }
+    }
+}
+
+} // namespace
+
+int
+launch_panel_build(const panel_args_t &p, cudaStream_t st)
+{
+    const int nT = panel_tiles(p.B), nK = panel_chunks(p.D);
+    const size_t smem = sizeof(int) * (2 * (size_t)nK + 2);
+    MMV_CHECK(smem <= 200 * 1024, "panel_build: %d genes exceed the shared-memory bucket table", p.D);
+    static bool attr = false;
+    if (!attr) {
+        MMV_CUDA(cudaFuncSetAttribute(panel_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr = true;
+    }
+    batch_rowptr_kernel<<<1, 1024, 0, st>>>(p.indptr, p.cells, p.B, p.rowptr);
+    ::mmv::count_launch();
+    panel_build_kernel<<<nT, kPanelThreads, smem, st>>>(p, nK);
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+
+// ===========================================================================
+// densify-in-smem tcgen05 GEMM:  C[128 x BN] += A_panel[128 x 64] * Dense[64 x BN]  per stage
+//   forward : rows = cells (2 tiles of 64), K = genes  (one chunk per stage),  Dense = W1eff^T [D x h1]
+//   backward: rows = genes (2 chunks of 64), K = cells (one tile per stage),   Dense = delta    [B x h1]
+// Warp roles: 0 = TMA producer (dense operand), 1 = MMA issuer, 2 = TMEM allocator,
+//             4-7 = panel densifiers during the main loop, epilogue afterwards.
+// ===========================================================================
+namespace {
+
+using namespace tc;
+
+constexpr int BM = 128, BK = 64, UK = 16, STG = 4, TCT = 256;
+constexpr int A_TILE = BM * BK * 2;   // 16 KB
+constexpr int PF = 4;                 // entries prefetched per densifier thread per stage (fast path)
+
+template <int BN>
+struct tc_cfg {
+    static constexpr int B_TILE = BN * BK * 2;
+    static constexpr int STAGE = A_TILE + B_TILE;
+    static constexpr int SMEM = STG * STAGE + 1024 + 256;
+};
+
+struct run2_t {   // the two bucket runs of one stage
+    int b0, n0, b1, n1;
+};
+
+template <bool BWD>
+__device__ __forceinline__ run2_t
+stage_runs(const int *__restrict__ bp, int kb, int tile, int nT, int nK)
+{
+    run2_t r;
+    if (!BWD) {   // cell tiles 2*tile, 2*tile+1 ; gene chunk kb
+        const int T0 = 2 * tile, T1 = T0 + 1;
+        const int *p0 = bp + (size_t)T0 * (nK + 1) + kb;
+        r.b0 = p0[0]; r.n0 = p0[1] - r.b0;
+        if (T1 < nT) {
+            const int *p1 = bp + (size_t)T1 * (nK + 1) + kb;
+            r.b1 = p1[0]; r.n1 = p1[1] - r.b1;
+        } else { r.b1 = 0; r.n1 = 0; }
+    } else {      // cell tile kb ; gene chunks 2*tile, 2*tile+1 (adjacent runs)
+        const int *p0 = bp + (size_t)kb * (nK + 1) + 2 * tile;
+        r.b0 = p0[0]; r.n0 = p0[1] - r.b0;
+        r.b1 = p0[1];
+        r.n1 = (2 * tile + 1 < nK) ? p0[2] - r.b1 : 0;
+    }
+    return r;
+}
+
+template <bool BWD>
+__device__ __forceinline__ void
+scatter_entry(uint8_t *tileA, uint32_t e, int rowbase)
+{
+    const int r6 = (int)(e >> 26), c6 = (int)((e >> 20) & 63);
+    const int trow = rowbase + (BWD ? c6 : r6), tcol = BWD ? r6 : c6;
+    // K-major SWIZZLE_128B: row = 128 B, 16-byte chunk index XOR (row & 7)
+    const int off = trow * 128 + ((((tcol >> 3) ^ (trow & 7))) << 4) + (tcol & 7) * 2;
+    *reinterpret_cast<uint16_t *>(tileA + off) = (uint16_t)(e & 0xFFFFu);
+}
+
+template <int BN, bool BWD>
+__global__ void __launch_bounds__(TCT, 1)
+senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, senc_tc_args_t a, int nT, int nK)
+{
+    using cfg = tc_cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + STG * cfg::STAGE);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 3 * STG + 1);
+    const uint32_t fulla0 = smem_u32(bars), fullb0 = smem_u32(bars + STG), empty0 = smem_u32(bars + 2 * STG),
+                   tfull = smem_u32(bars + 3 * STG);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = blockIdx.y, n0 = blockIdx.x * BN;
+    const int num_kb = BWD ? nT : nK;
+
+    if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmD) : "memory");
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < STG; ++s) {
+            mbar_init(fulla0 + 8 * s, 128);
+            mbar_init(fullb0 + 8 * s, 1);
+            mbar_init(empty0 + 8 * s, 1);
+        }
+        mbar_init(tfull, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"(smem_u32(tmem_slot)), "r"(BN) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================= TMA producer: dense operand, [64 k x 64 n] boxes =================
+        if (lane == 0) {
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % STG;
+                mbar_wait(empty0 + 8 * s, ((kb / STG) & 1) ^ 1);
+                const uint32_t sb = smem_u32(smem + s * cfg::STAGE + A_TILE);
+                const uint32_t fb = fullb0 + 8 * s;
+                mbar_expect_tx(fb, cfg::B_TILE);
+#pragma unroll
+                for (int i = 0; i < BN / 64; ++i) tma_load_2d(sb + i * 8192, &tmD, fb, n0 + 64 * i, kb * BK);
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc(false, true, BM, BN);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % STG;
+                const uint32_t ph = (kb / STG) & 1;
+                mbar_wait(fullb0 + 8 * s, ph);
+                mbar_wait(fulla0 + 8 * s, ph);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t sa = smem_u32(smem + s * cfg::STAGE), sb = sa + A_TILE;
+#pragma unroll
+                for (int k = 0; k < BK / UK; ++k) {
+                    const uint64_t ad = make_desc(sa + k * 32, 16, 1024);        // K-major, SW128
+                    const uint64_t bd = make_desc(sb + k * 2048, 8192, 1024);    // MN-major, SW128
+                    umma_bf16(tmem_base, ad, bd, idesc, (kb | k) != 0);
+                }
+                umma_commit(empty0 + 8 * s);
+            }
+            umma_commit(tfull);
+        }
+    } else if (warp >= 4) {
+        // ================= densifiers =================
+        const int t = threadIdx.x - 128;   // 0..127
+        const int *__restrict__ bp = a.bucket_ptr;
+        const uint32_t *__restrict__ ent = a.ent;
+        uint32_t cur[PF], nxt[PF];
+        run2_t rc = stage_runs<BWD>(bp, 0, tile, nT, nK), rn = rc, rnn = rc;
+        if (num_kb > 1) rn = stage_runs<BWD>(bp, 1, tile, nT, nK);
+#pragma unroll
+        for (int i = 0; i < PF; ++i) {
+            const int e = t + 128 * i;
+            cur[i] = e < rc.n0 ? ent[rc.b0 + e] : (e < rc.n0 + rc.n1 ? ent[rc.b1 + e - rc.n0] : 0u);
+        }
+        for (int kb = 0; kb < num_kb; ++kb) {
+            const int s = kb % STG;
+            // prefetch: entries of stage kb+1, bucket pointers of stage kb+2
+            if (kb + 2 < num_kb) rnn = stage_runs<BWD>(bp, kb + 2, tile, nT, nK);
+            if (kb + 1 < num_kb) {
+#pragma unroll
+                for (int i = 0; i < PF; ++i) {
+                    const int e = t + 128 * i;
+                    nxt[i] = e < rn.n0 ? ent[rn.b0 + e] : (e < rn.n0 + rn.n1 ? ent[rn.b1 + e - rn.n0] : 0u);
+                }
+            }
+            mbar_wait(empty0 + 8 * s, ((kb / STG) & 1) ^ 1);
+            uint8_t *tileA = smem + s * cfg::STAGE;
+            {
+                uint4 z = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+                for (int i = 0; i < A_TILE / (128 * 16); ++i) reinterpret_cast<uint4 *>(tileA)[t + 128 * i] = z;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+            for (int i = 0; i < PF; ++i) {
+                const int e = t + 128 * i;
+                if (e < rc.n0 + rc.n1) scatter_entry<BWD>(tileA, cur[i], e < rc.n0 ? 0 : 64);
+            }
+            for (int e = t + 128 * PF; e < rc.n0 + rc.n1; e += 128) {   // dense buckets: slow path
+                const uint32_t v = e < rc.n0 ? ent[rc.b0 + e] : ent[rc.b1 + e - rc.n0];
+                scatter_entry<BWD>(tileA, v, e < rc.n0 ? 0 : 64);
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(fulla0 + 8 * s) : "memory");
+#pragma unroll
+            for (int i = 0; i < PF; ++i) cur[i] = nxt[i];
+            rc = rn; rn = rnn;
+        }
+
+        // ================= epilogue =================
+        mbar_wait(tfull, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int e4 = warp - 4;                       // TMEM lanes [32 e4, 32 e4 + 32)
+        const int trow = 32 * e4 + lane;
+        if (!BWD) {
+            const int row = tile * BM + trow;
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(32 * e4) << 16) + (uint32_t)(32 * c), v);
+                const int col0 = n0 + 32 * c;
+                if (row < a.B) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 8) {
+                        if (col0 + j < a.h1) {   // h1 % 8 == 0
+                            float f[8];
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) {
+                                f[q] = __uint_as_float(v[j + q]) + a.bias_eff[col0 + j + q];
+                                if (a.relu) f[q] = fmaxf(f[q], 0.f);
+                            }
+                            float4 *dst = reinterpret_cast<float4 *>(a.H1 + (size_t)row * a.h1 + col0 + j);
+                            dst[0] = make_float4(f[0], f[1], f[2], f[3]);
+                            dst[1] = make_float4(f[4], f[5], f[6], f[7]);
+                            if (a.H1_bf16) {
+                                __nv_bfloat162 b0 = __floats2bfloat162_rn(f[0], f[1]), b1 = __floats2bfloat162_rn(f[2], f[3]);
+                                __nv_bfloat162 b2 = __floats2bfloat162_rn(f[4], f[5]), b3 = __floats2bfloat162_rn(f[6], f[7]);
+                                uint4 pk;
+                                pk.x = *reinterpret_cast<uint32_t *>(&b0); pk.y = *reinterpret_cast<uint32_t *>(&b1);
+                                pk.z = *reinterpret_cast<uint32_t *>(&b2); pk.w = *reinterpret_cast<uint32_t *>(&b3);
+                                *reinterpret_cast<uint4 *>(reinterpret_cast<__nv_bfloat16 *>(a.H1_bf16) +
+                                                           (size_t)row * a.h1 + col0 + j) = pk;
+                            }
+                        }
+                    }
+                }
+            }
+        } else {
+            const int g = tile * BM + trow;
+            const bool live = g < a.D;
+            const float xmit = live ? a.x_mean[g] * a.inv_t[g] : 0.f;
+            float d0 = 0.f, d1 = 0.f;
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(32 * e4) << 16) + (uint32_t)(32 * c), v);
+                const int col0 = n0 + 32 * c;
+                if (live) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        if (col0 + j < a.h1) {   // h1 % 8 == 0
+                            const float4 w4 = *reinterpret_cast<const float4 *>(a.W1T + (size_t)g * a.h1 + col0 + j);
+                            const float4 dl4 = *reinterpret_cast<const float4 *>(a.Delta + col0 + j);
+                            float w[4] = { w4.x, w4.y, w4.z, w4.w };
+                            const float dl[4] = { dl4.x, dl4.y, dl4.z, dl4.w };
+                            float o[4];
+                            if (a.angular) {
+                                const float4 cs4 = *reinterpret_cast<const float4 *>(a.col_scale + col0 + j);
+                                const float cs[4] = { cs4.x, cs4.y, cs4.z, cs4.w };
+#pragma unroll
+                                for (int q = 0; q < 4; ++q) w[q] = (fmaxf(w[q], 0.f) + 1e-4f) * cs[q];
+                            }
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const float acc = __uint_as_float(v[j + q]);
+                                d0 = fmaf(w[q], acc, d0);
+                                d1 = fmaf(w[q], dl[q], d1);
+                                o[q] = fmaf(-xmit, dl[q], acc);
+                            }
+                            if (a.dW1T) {
+                                float4 *dst = reinterpret_cast<float4 *>(a.dW1T + (size_t)g * a.h1 + col0 + j);
+                                if (a.accumulate) {
+                                    const float4 old = *dst;
+                                    o[0] += old.x; o[1] += old.y; o[2] += old.z; o[3] += old.w;
+                                }
+                                *dst = make_float4(o[0], o[1], o[2], o[3]);
+                            }
+                        }
+                    }
+                }
+            }
+            if (live) {
+                atomicAdd(a.dot0 + g, d0);
+                atomicAdd(a.dot1 + g, d1);
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+
+    __syncthreads();
+    if (warp == 2) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(BN) : "memory");
+    }
+}
+
+} // namespace
+
+namespace {
+
+template <int BN, bool BWD>
+int
+launch_tc(const senc_tc_args_t &a, cudaStream_t st)
+{
+    using cfg = tc_cfg<BN>;
+    const int nT = panel_tiles(a.B), nK = panel_chunks(a.D);
+    CUtensorMap tm;
+    // dense operand: rows = K index (genes fwd / cells bwd), h1 contiguous
+    MMV_TRY(make_tma_map_bf16(&tm, a.dense_bf16, (uint64_t)a.h1, (uint64_t)(BWD ? a.B : a.D), (uint64_t)a.h1, 64, BK));
+    auto kern = senc_tc_kernel<BN, BWD>;
+    static bool attr = false;
+    if (!attr) {
+        MMV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, cfg::SMEM));
+        attr = true;
+    }
+    dim3 grid(ceil_div(a.h1, BN), BWD ? ceil_div(a.D, BM) : ceil_div(a.B, BM));
+    kern<<<grid, TCT, cfg::SMEM, st>>>(tm, a, nT, nK);
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+__global__ void
+senc_tc_finish_kernel(const float *dot0, const float *dot1, const float *inv_t, const float *x_mean,
+                      const float *ln_x_sd, float *dx_mean, float *dln_x_sd, int D)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= D) return;
+    // dot0 = W_eff[j,:] . S'[j,:] with S' = S / t (the panel values carry 1/t) ; dot1 = W_eff[j,:] . Delta
+    const float it = inv_t[j], xm = x_mean[j];
+    dx_mean[j] += -dot1[j] * it;
+    const float dt = -(dot0[j] - xm * it * dot1[j]) * it;
+    dln_x_sd[j] += dt * sigmoid_f(ln_x_sd[j]);   // d softplus
+}
+
+// dWnuT[j, h] += sum_e x_e dHnu[row_e, h] ; dwdepth[j] += sum_e x_e ddpre[row_e].  One CTA per gene chunk.
+__global__ void __launch_bounds__(256)
+panel_aux_bwd_kernel(const int *bp, const uint32_t *ent, const float *xraw, int nT, int nK, int H,
+                     const float *dHnu, const float *ddpre, float *dWnuT, float *dwdepth, int D)
+{
+    extern __shared__ float s_acc[];   // [64 x (H + 1)]
+    const int k = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int W = H + 1;
+    for (int i = tid; i < 64 * W; i += 256) s_acc[i] = 0.f;
+    __syncthreads();
+    for (int T = warp; T < nT; T += 8) {
+        const int *p = bp + (size_t)T * (nK + 1) + k;
+        const int b = p[0], e = p[1];
+        for (int q = b + lane; q < e; q += 32) {
+            const uint32_t v = ent[q];
+            const float x = xraw[q];
+            const int r = T * 64 + (int)(v >> 26), c = (int)((v >> 20) & 63);
+            atomicAdd(&s_acc[c * W + H], x * ddpre[r]);
+            for (int h = 0; h < H; ++h) atomicAdd(&s_acc[c * W + h], x * dHnu[(size_t)r * H + h]);
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < 64 * W; i += 256) {
+        const int c = i / W, h = i % W, j = k * 64 + c;
+        if (j >= D) continue;
+        if (h == H) dwdepth[j] += s_acc[i];
+        else dWnuT[(size_t)j * H + h] += s_acc[i];
+    }
+}
+
+__global__ void
+w1eff_bf16_kernel(const float *W1T, const float *col_scale, __nv_bfloat16 *out, size_t n, int h1)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = __float2bfloat16((fmaxf(W1T[i], 0.f) + 1e-4f) * col_scale[i % h1]);   // angular.hh:38-40
+}
+
+} // namespace
+
+bool
+senc_tc_supported(int h1)
+{
+    return h1 >= 16 && h1 % 8 == 0;
+}
+
+int
+launch_senc_tc_fwd(const senc_tc_args_t &a, cudaStream_t st)
+{
+    MMV_CHECK(senc_tc_supported(a.h1), "senc_tc: first-layer width %d must be a multiple of 8", a.h1);
+    return a.h1 > 128 ? launch_tc<256, false>(a, st) : launch_tc<128, false>(a, st);
+}
+
+int
+launch_senc_tc_bwd(const senc_tc_args_t &a, cudaStream_t st)
+{
+    MMV_CHECK(senc_tc_supported(a.h1), "senc_tc: first-layer width %d must be a multiple of 8", a.h1);
+    return a.h1 > 128 ? launch_tc<256, true>(a, st) : launch_tc<128, true>(a, st);
+}
+
+int
+launch_senc_tc_finish(const float *dot0, const float *dot1, const float *inv_t, const float *x_mean,
+                      const float *ln_x_sd, float *dx_mean, float *dln_x_sd, int D, cudaStream_t st)
+{
+    senc_tc_finish_kernel<<<ceil_div(D, 256), 256, 0, st>>>(dot0, dot1, inv_t, x_mean, ln_x_sd, dx_mean, dln_x_sd, D);
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int
+launch_panel_aux_bwd(const int *bucket_ptr, const uint32_t *ent, const float *xraw, int B, int D, int H,
+                     const float *dHnu, const float *ddpre, float *dWnuT, float *dwdepth, cudaStream_t st)
+{
+    const size_t smem = sizeof(float) * 64 * (size_t)(H + 1);
+    MMV_CHECK(smem <= 48 * 1024, "panel_aux_bwd: nu hidden width %d too large", H);
+    panel_aux_bwd_kernel<<<panel_chunks(D), 256, smem, st>>>(bucket_ptr, ent, xraw, panel_tiles(B), panel_chunks(D), H,
+                                                             dHnu, ddpre, dWnuT, dwdepth, D);
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int
+launch_w1eff_bf16(const float *W1T, const float *col_scale, void *out, int D, int h1, cudaStream_t st)
+{
+    const size_t n = (size_t)D * h1;
+    w1eff_bf16_kernel<<<(int)min_sz((n + 255) / 256, 148 * 16), 256, 0, st>>>(W1T, col_scale,
+                                                                            reinterpret_cast<__nv_bfloat16 *>(out), n, h1);
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+} // namespace mmv
