@@ -148,11 +148,67 @@ colsum_kernel(colsum_args_t a)
         for (int c = 0; c < a.C; ++c) atomicAdd(a.out_cov + (size_t)col * a.C + c, sc[c]);
 }
 
+// bf16 input, all-ones covariates, N % 8 == 0: each thread owns 8 adjacent columns (one 16-byte load
+// per row), 4 rows in flight; a CTA covers 256 columns x rows_per_cta rows.
+__global__ void __launch_bounds__(256)
+colsum_bf16x8_kernel(colsum_args_t a)
+{
+    __shared__ float s_part[8][32 * 8 + 1];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int col = (blockIdx.x * 32 + lane) * 8;
+    const int r0 = blockIdx.y * a.rows_per_cta, r1 = min(a.M, r0 + a.rows_per_cta);
+    float s[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) s[q] = 0.f;
+    if (col < a.N) {
+        const __nv_bfloat16 *X = reinterpret_cast<const __nv_bfloat16 *>(a.Xb) + col;
+        for (int i = r0 + warp; i < r1; i += 32) {
+            uint4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                v[u] = i + 8 * u < r1 ? *reinterpret_cast<const uint4 *>(X + (size_t)(i + 8 * u) * a.ldx)
+                                      : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t w[4] = { v[u].x, v[u].y, v[u].z, v[u].w };
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    s[2 * q] += __uint_as_float(w[q] << 16);
+                    s[2 * q + 1] += __uint_as_float(w[q] & 0xFFFF0000u);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < 8; ++q) s_part[warp][lane * 8 + q] = s[q];
+    __syncthreads();
+    const int c = threadIdx.x;   // 256 threads = 256 columns of the CTA
+    float tot = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) tot += s_part[w][c];
+    const int gc = blockIdx.x * 256 + c;
+    if (gc < a.N) {
+        if (a.out_sum) atomicAdd(a.out_sum + gc, tot);
+        if (a.out_sum2) atomicAdd(a.out_sum2 + gc, tot);
+        if (a.out_sum3) atomicAdd(a.out_sum3 + gc, tot);
+        if (a.out_cov)
+            for (int k = 0; k < a.C; ++k) atomicAdd(a.out_cov + (size_t)gc * a.C + k, tot);
+    }
+}
+
 int
 launch_colsum(colsum_args_t a, cudaStream_t st)
 {
     if (a.M <= 0 || a.N <= 0) return 0;
     MMV_CHECK(a.C <= 8, "colsum: covariate dim %d > 8 not supported", a.C);
+    if (a.Xb && a.cov == nullptr && a.N % 8 == 0 && a.ldx % 8 == 0 && (reinterpret_cast<uintptr_t>(a.Xb) & 15) == 0 &&
+        a.N >= 256) {
+        a.rows_per_cta = 256;
+        dim3 grid(ceil_div(a.N, 256), ceil_div(a.M, a.rows_per_cta));
+        colsum_bf16x8_kernel<<<grid, 256, 0, st>>>(a); ::mmv::count_launch();
+        MMV_CUDA(cudaGetLastError());
+        return 0;
+    }
     a.rows_per_cta = 64;
     dim3 grid(ceil_div(a.N, 128), ceil_div(a.M, a.rows_per_cta));
     colsum_kernel<<<grid, 128, 0, st>>>(a); ::mmv::count_launch();

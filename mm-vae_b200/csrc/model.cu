@@ -1044,7 +1044,8 @@ nb_forward_backward(const step_t &s)
         b.gene_ptr = m->ws["csc_ptr"].as<int>(); b.ent_row = m->ws["csc_row"].as<int>();
         b.ent_l = m->ws["csc_l"].as<float>(); b.ent_x = m->ws["csc_x"].as<float>();
     }
-    b.D = D; b.h1 = h1; b.H = H; b.angular = 0; b.accumulate = 1;
+    b.D = D; b.h1 = h1; b.H = H; b.angular = 0;
+    b.accumulate = m->optimised(L0.w) ? 0 : 1;   // zero_grad reaches the optimiser's tensors only: frozen ones accumulate
     b.delta = m->ws["d_enc0"].as<float>(); b.Delta = m->ws["Delta"].as<float>();
     b.W1T = m->P(L0.w); b.inv_t = inv_t; b.x_mean = m->P(m->t_x_mean); b.ln_x_sd = m->P(m->t_ln_x_sd);
     b.dW1T = m->want_grad(L0.w) ? m->G(L0.w) : nullptr;

@@ -59,6 +59,7 @@ batch_rowptr_kernel(const int64_t *indptr, const int32_t *cells, int B, int *row
 }
 
 constexpr int kPanelThreads = 512;
+constexpr int kUn = 8;
 
 __global__ void __launch_bounds__(kPanelThreads)
 panel_build_kernel(panel_args_t p, int nK)
@@ -77,7 +78,17 @@ panel_build_kernel(panel_args_t p, int nK)
     for (int r = warp; r < nrows; r += NW) {
         const int64_t c = p.cells ? (int64_t)p.cells[r0 + r] : (int64_t)(r0 + r);
         const int64_t beg = p.indptr[c], end = p.indptr[c + 1];
-        for (int64_t q = beg + lane; q < end; q += 32) atomicAdd(&s_cur[p.indices[q] >> 6], 1);
+        for (int64_t q0 = beg; q0 < end; q0 += 32 * kUn) {   // kUn independent loads in flight per lane
+            int j[kUn];
+#pragma unroll
+            for (int u = 0; u < kUn; ++u) {
+                const int64_t q = q0 + lane + 32 * u;
+                j[u] = q < end ? p.indices[q] : -1;
+            }
+#pragma unroll
+            for (int u = 0; u < kUn; ++u)
+                if (j[u] >= 0) atomicAdd(&s_cur[j[u] >> 6], 1);
+        }
     }
     __syncthreads();
     // ---- exclusive scan over the chunks (each thread owns a contiguous span)
@@ -124,22 +135,45 @@ panel_build_kernel(panel_args_t p, int nK)
             rs = 1.f / nrm;
             if (lane == 0 && p.rownorm) p.rownorm[r0 + r] = nrm;
         }
-        float depth = 0.f;
-        for (int64_t q = beg + lane; q < end; q += 32) {
-            const int j = p.indices[q];
-            const float x = p.vals[q];
-            const float v = log1pf(x) * rs * p.inv_t[j];
-            const int pos = base + atomicAdd(&s_cur[j >> 6], 1);
-            const uint32_t bits = (uint32_t)__bfloat16_as_ushort(__float2bfloat16(v));
-            p.ent[pos] = ((uint32_t)r << 26) | ((uint32_t)(j & 63) << 20) | bits;
-            p.xraw[pos] = x;
-            if (p.wdepth) depth = fmaf(x, p.wdepth[j], depth);
+        float depth = 0.f, hn0 = 0.f;
+        const bool h_inline = p.H == 1;
+        for (int64_t q0 = beg; q0 < end; q0 += 32 * kUn) {
+            int j[kUn];
+            float x[kUn], it[kUn], wd[kUn], wn[kUn];
+#pragma unroll
+            for (int u = 0; u < kUn; ++u) {
+                const int64_t q = q0 + lane + 32 * u;
+                j[u] = q < end ? p.indices[q] : -1;
+                x[u] = q < end ? p.vals[q] : 0.f;
+            }
+#pragma unroll
+            for (int u = 0; u < kUn; ++u) {
+                const int jj = max(j[u], 0);
+                it[u] = p.inv_t[jj];
+                wd[u] = p.wdepth ? p.wdepth[jj] : 0.f;
+                wn[u] = h_inline ? p.WnuT[jj] : 0.f;
+            }
+#pragma unroll
+            for (int u = 0; u < kUn; ++u) {
+                if (j[u] < 0) continue;
+                const float v = log1pf(x[u]) * rs * it[u];
+                const int pos = base + atomicAdd(&s_cur[j[u] >> 6], 1);
+                const uint32_t bits = (uint32_t)__bfloat16_as_ushort(__float2bfloat16(v));
+                p.ent[pos] = ((uint32_t)r << 26) | ((uint32_t)(j[u] & 63) << 20) | bits;
+                p.xraw[pos] = x[u];
+                depth = fmaf(x[u], wd[u], depth);
+                hn0 = fmaf(x[u], wn[u], hn0);
+            }
+        }
+        if (h_inline) {   // nb.hh:448 (raw counts), default H = 1
+            hn0 = warp_sum(hn0);
+            if (lane == 0) p.Hnu[r0 + r] = hn0 + p.bnu[0];
         }
         if (p.wdepth) {   // nb.hh:498 (raw counts)
             depth = warp_sum(depth);
             if (lane == 0) p.dpre[r0 + r] = depth + p.bdepth[0];
         }
-        for (int h = 0; h < p.H; ++h) {   // nb.hh:448 (raw counts); H = 1 by default
+        for (int h = 0; h < p.H && !h_inline; ++h) {   // nb.hh:448 (raw counts), general H
             float s = 0.f;
             for (int64_t q = beg + lane; q < end; q += 32)
                 s = fmaf(p.vals[q], p.WnuT[(size_t)p.indices[q] * p.H + h], s);
@@ -176,13 +210,14 @@ launch_panel_build(const panel_args_t &p, cudaStream_t st)
 //   forward : rows = cells (2 tiles of 64), K = genes  (one chunk per stage),  Dense = W1eff^T [D x h1]
 //   backward: rows = genes (2 chunks of 64), K = cells (one tile per stage),   Dense = delta    [B x h1]
 // Warp roles: 0 = TMA producer (dense operand), 1 = MMA issuer, 2 = TMEM allocator,
-//             4-7 = panel densifiers during the main loop, epilogue afterwards.
+//             4-11 = panel densifiers (two groups alternating stages) during the main loop, epilogue afterwards.
 // ===========================================================================
 namespace {
 
 using namespace tc;
 
-constexpr int BM = 128, BK = 64, UK = 16, STG = 4, TCT = 256;
+constexpr int BM = 128, BK = 64, UK = 16, STG = 4, TCT = 384;
+constexpr int RT = 256;                // run-table entries cached in shared memory per densifier group
 constexpr int A_TILE = BM * BK * 2;   // 16 KB
 constexpr int PF = 4;                 // entries prefetched per densifier thread per stage (fast path)
 
@@ -190,7 +225,7 @@ template <int BN>
 struct tc_cfg {
     static constexpr int B_TILE = BN * BK * 2;
     static constexpr int STAGE = A_TILE + B_TILE;
-    static constexpr int SMEM = STG * STAGE + 1024 + 256;
+    static constexpr int SMEM = STG * STAGE + 1024 + 256 + 2 * RT * 16;
 };
 
 struct run2_t {   // the two bucket runs of one stage
@@ -249,7 +284,7 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, senc_tc_args_t a, int nT
     if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmD) : "memory");
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STG; ++s) {
-            mbar_init(fulla0 + 8 * s, 128);
+            mbar_init(fulla0 + 8 * s, 128);   // one densifier group per stage
             mbar_init(fullb0 + 8 * s, 1);
             mbar_init(empty0 + 8 * s, 1);
         }
@@ -301,61 +336,77 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, senc_tc_args_t a, int nT
             umma_commit(tfull);
         }
     } else if (warp >= 4) {
-        // ================= densifiers =================
-        const int t = threadIdx.x - 128;   // 0..127
+        // ================= densifiers: two groups of 4 warps, alternating stages =================
+        const int grp = (warp - 4) >> 2;
+        const int t = threadIdx.x - 128 - 128 * grp;   // 0..127 inside the group
         const int *__restrict__ bp = a.bucket_ptr;
         const uint32_t *__restrict__ ent = a.ent;
-        uint32_t cur[PF], nxt[PF];
-        run2_t rc = stage_runs<BWD>(bp, 0, tile, nT, nK), rn = rc, rnn = rc;
-        if (num_kb > 1) rn = stage_runs<BWD>(bp, 1, tile, nT, nK);
-#pragma unroll
-        for (int i = 0; i < PF; ++i) {
-            const int e = t + 128 * i;
-            cur[i] = e < rc.n0 ? ent[rc.b0 + e] : (e < rc.n0 + rc.n1 ? ent[rc.b1 + e - rc.n0] : 0u);
-        }
-        for (int kb = 0; kb < num_kb; ++kb) {
-            const int s = kb % STG;
-            // prefetch: entries of stage kb+1, bucket pointers of stage kb+2
-            if (kb + 2 < num_kb) rnn = stage_runs<BWD>(bp, kb + 2, tile, nT, nK);
-            if (kb + 1 < num_kb) {
-#pragma unroll
-                for (int i = 0; i < PF; ++i) {
-                    const int e = t + 128 * i;
-                    nxt[i] = e < rn.n0 ? ent[rn.b0 + e] : (e < rn.n0 + rn.n1 ? ent[rn.b1 + e - rn.n0] : 0u);
+        int4 *rtab = reinterpret_cast<int4 *>(smem + STG * cfg::STAGE + 256) + grp * RT;   // run table of this group
+        const int n_own = (num_kb - grp + 1) / 2;      // stages grp, grp + 2, ...
+
+        auto refill = [&](int i0) {                    // own-stage indices [i0, i0 + RT)
+            asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
+            for (int i = t; i < RT; i += 128)
+                if (i0 + i < n_own) {
+                    const run2_t r = stage_runs<BWD>(bp, grp + 2 * (i0 + i), tile, nT, nK);
+                    rtab[i] = make_int4(r.b0, r.n0, r.b1, r.n1);
                 }
+            asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
+        };
+        auto load = [&](uint32_t (&e)[PF], int i) {
+            const int4 r = rtab[i % RT];
+#pragma unroll
+            for (int q = 0; q < PF; ++q) {
+                const int x = t + 128 * q;
+                e[q] = x < r.y ? ent[r.x + x] : (x < r.y + r.w ? ent[r.z + x - r.y] : 0u);
             }
+        };
+        auto build = [&](const uint32_t (&e)[PF], int i) {
+            const int kb = grp + 2 * i, s = kb % STG;
+            const int4 r = rtab[i % RT];
+            const int n = r.y + r.w;
             mbar_wait(empty0 + 8 * s, ((kb / STG) & 1) ^ 1);
             uint8_t *tileA = smem + s * cfg::STAGE;
-            {
-                uint4 z = make_uint4(0u, 0u, 0u, 0u);
+            const uint4 z = make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
-                for (int i = 0; i < A_TILE / (128 * 16); ++i) reinterpret_cast<uint4 *>(tileA)[t + 128 * i] = z;
-            }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            for (int q = 0; q < A_TILE / (128 * 16); ++q) reinterpret_cast<uint4 *>(tileA)[t + 128 * q] = z;
+            asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
 #pragma unroll
-            for (int i = 0; i < PF; ++i) {
-                const int e = t + 128 * i;
-                if (e < rc.n0 + rc.n1) scatter_entry<BWD>(tileA, cur[i], e < rc.n0 ? 0 : 64);
+            for (int q = 0; q < PF; ++q) {
+                const int x = t + 128 * q;
+                if (x < n) scatter_entry<BWD>(tileA, e[q], x < r.y ? 0 : 64);
             }
-            for (int e = t + 128 * PF; e < rc.n0 + rc.n1; e += 128) {   // dense buckets: slow path
-                const uint32_t v = e < rc.n0 ? ent[rc.b0 + e] : ent[rc.b1 + e - rc.n0];
-                scatter_entry<BWD>(tileA, v, e < rc.n0 ? 0 : 64);
+            for (int x = t + 128 * PF; x < n; x += 128) {   // dense buckets: slow path
+                const uint32_t v = x < r.y ? ent[r.x + x] : ent[r.z + x - r.y];
+                scatter_entry<BWD>(tileA, v, x < r.y ? 0 : 64);
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(fulla0 + 8 * s) : "memory");
-#pragma unroll
-            for (int i = 0; i < PF; ++i) cur[i] = nxt[i];
-            rc = rn; rn = rnn;
+        };
+
+        uint32_t ea[PF], eb[PF];
+        for (int i0 = 0; i0 < n_own; i0 += RT) {
+            refill(i0);
+            const int i1 = min(n_own, i0 + RT);
+            load(ea, i0);
+            for (int i = i0; i < i1; i += 2) {          // ping-pong register sets: no moves of in-flight loads
+                if (i + 1 < i1) load(eb, i + 1);
+                build(ea, i);
+                if (i + 1 >= i1) break;
+                if (i + 2 < i1) load(ea, i + 2);
+                build(eb, i + 1);
+            }
         }
 
         // ================= epilogue =================
         mbar_wait(tfull, 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const int e4 = warp - 4;                       // TMEM lanes [32 e4, 32 e4 + 32)
+        const int e4 = (warp - 4) & 3;                 // TMEM lanes [32 e4, 32 e4 + 32) (= warp % 4)
         const int trow = 32 * e4 + lane;
+        const int c_beg = grp * (BN / 64), c_end = c_beg + BN / 64;   // each group drains half of the columns
         if (!BWD) {
             const int row = tile * BM + trow;
-            for (int c = 0; c < BN / 32; ++c) {
+            for (int c = c_beg; c < c_end; ++c) {
                 uint32_t v[32];
                 tmem_ld32(tmem_base + ((uint32_t)(32 * e4) << 16) + (uint32_t)(32 * c), v);
                 const int col0 = n0 + 32 * c;
@@ -390,7 +441,7 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, senc_tc_args_t a, int nT
             const bool live = g < a.D;
             const float xmit = live ? a.x_mean[g] * a.inv_t[g] : 0.f;
             float d0 = 0.f, d1 = 0.f;
-            for (int c = 0; c < BN / 32; ++c) {
+            for (int c = c_beg; c < c_end; ++c) {
                 uint32_t v[32];
                 tmem_ld32(tmem_base + ((uint32_t)(32 * e4) << 16) + (uint32_t)(32 * c), v);
                 const int col0 = n0 + 32 * c;
