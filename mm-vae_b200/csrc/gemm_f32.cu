@@ -36,14 +36,18 @@ gemm_f32_kernel(gemm_args_t g)
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
 
-    for (int k0 = 0; k0 < K; k0 += BK) {
+    // split-K: blockIdx.z owns a K range and adds its partial product atomically (dW-type products
+    // with few output tiles and a long batch dimension would otherwise run on a handful of SMs)
+    const int k_per = ((K + (int)gridDim.z - 1) / (int)gridDim.z + BK - 1) / BK * BK;
+    const int k_beg = blockIdx.z * k_per, k_end = min(K, k_beg + k_per);
+    for (int k0 = k_beg; k0 < k_end; k0 += BK) {
         // ---- stage A tile (BM x BK) as As[k][m]
         for (int idx = tid; idx < BM * BK; idx += GT) {
             int m, k;
             if (TA) { k = idx / BM; m = idx % BM; } else { m = idx / BK; k = idx % BK; }
             const int gm = m0 + m, gk = k0 + k;
             float v = 0.f;
-            if (gm < M && gk < K)
+            if (gm < M && gk < k_end)
                 v = TA ? g.A[(size_t)gk * g.lda + gm] : g.A[(size_t)gm * g.lda + gk];
             As[k][m] = v;
         }
@@ -53,7 +57,7 @@ gemm_f32_kernel(gemm_args_t g)
             if (TB) { n = idx / BK; k = idx % BK; } else { k = idx / BN; n = idx % BN; }
             const int gn = n0 + n, gk = k0 + k;
             float v = 0.f;
-            if (gn < N && gk < K)
+            if (gn < N && gk < k_end)
                 v = TB ? g.B[(size_t)gn * g.ldb + gk] : g.B[(size_t)gk * g.ldb + gn];
             Bs[k][n] = v;
         }
@@ -87,8 +91,13 @@ gemm_f32_kernel(gemm_args_t g)
             const int gn = n0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
             if (gn >= N) continue;
             float v = g.alpha * acc[i][j];
-            if (g.bias) v += g.bias[gn];
             float *c = g.C + (size_t)gm * g.ldc + gn;
+            if (gridDim.z > 1) {   // C already holds beta * C (launcher); bias once
+                if (g.bias && blockIdx.z == 0) v += g.bias[gn];
+                atomicAdd(c, v);
+                continue;
+            }
+            if (g.bias) v += g.bias[gn];
             if (g.beta != 0.f) v = fmaf(g.beta, *c, v);
             if (g.relu) v = fmaxf(v, 0.f);
             *c = v;
@@ -102,6 +111,19 @@ launch_gemm_f32(const gemm_args_t &g, cudaStream_t stream)
     if (g.M <= 0 || g.N <= 0) return 0;
     MMV_CHECK(g.K > 0, "gemm_f32: K=%d", g.K);
     dim3 grid(ceil_div(g.N, BN), ceil_div(g.M, BM));
+    const int tiles = (int)(grid.x * grid.y);
+    if (tiles <= 32 && g.K >= 1024 && !g.relu && (g.beta == 1.f || (g.beta == 0.f && g.ldc == g.N))) {
+        int splits = g.K / 256;
+        if (splits > 128 / tiles) splits = 128 / tiles;
+        if (splits > 1) {
+            const int per = ceil_div(ceil_div(g.K, splits), BK) * BK;
+            splits = ceil_div(g.K, per);
+        }
+        if (splits > 1) {
+            grid.z = splits;
+            if (g.beta == 0.f) MMV_CUDA(cudaMemsetAsync(g.C, 0, sizeof(float) * (size_t)g.M * g.N, stream));
+        }
+    }
     if (!g.transA && !g.transB) gemm_f32_kernel<false, false><<<grid, GT, 0, stream>>>(g);
     else if (!g.transA && g.transB) gemm_f32_kernel<false, true><<<grid, GT, 0, stream>>>(g);
     else if (g.transA && !g.transB) gemm_f32_kernel<true, false><<<grid, GT, 0, stream>>>(g);

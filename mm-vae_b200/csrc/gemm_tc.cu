@@ -58,7 +58,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.y * BLOCK_M, n0 = blockIdx.x * BLOCK_N;
-    const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+    // split-K (gridDim.z > 1): this CTA owns k-blocks [kb0, kb0 + num_kb) and adds its partial tile atomically
+    const int total_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+    const int kb_per = (total_kb + (int)gridDim.z - 1) / (int)gridDim.z;
+    const int kb0 = blockIdx.z * kb_per;
+    const int num_kb = max(0, min(total_kb - kb0, kb_per));
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
@@ -92,7 +96,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const uint32_t sa = smem_u32(smem + s * STAGE_BYTES), sb = sa + A_BYTES;
                 const uint32_t fb = full0 + 8 * s;
                 mbar_expect_tx(fb, STAGE_BYTES);
-                const int k0 = kb * BLOCK_K;
+                const int k0 = (kb0 + kb) * BLOCK_K;
                 if (A_MN) {     // tensor dims {MN, K}: two [64 k x 64 m] boxes
                     tma_load_2d(sa, &tmA, fb, m0, k0);
                     tma_load_2d(sa + A_BYTES / 2, &tmA, fb, m0 + 64, k0);
@@ -155,12 +159,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = __uint_as_float(v[j]);
             __syncwarp();
             const int col = n0 + 32 * c + lane;
-            const float bv = (p.bias && col < p.N) ? p.bias[col] : 0.f;
+            const float bv = (p.bias && col < p.N && blockIdx.z == 0) ? p.bias[col] : 0.f;
 #pragma unroll 4
             for (int r = 0; r < 32; ++r) {
                 const int row = m0 + 32 * e + r;
                 if (row < p.M && col < p.N) {
                     float x = tile[r * 33 + lane] + bv;
+                    if (gridDim.z > 1) {   // C already holds beta * C (launcher)
+                        atomicAdd(p.C + (size_t)row * p.ldc + col, x);
+                        continue;
+                    }
                     if (p.beta != 0.f) x = fmaf(p.beta, p.C[(size_t)row * p.ldc + col], x);
                     if (p.relu) x = fmaxf(x, 0.f);
                     if (p.C) p.C[(size_t)row * p.ldc + col] = x;
@@ -253,6 +261,19 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
     p.C = g.C; p.Cb = reinterpret_cast<__nv_bfloat16 *>(g.Cb); p.bias = g.bias;
     p.M = g.M; p.N = g.N; p.K = g.K; p.ldc = g.ldc; p.ldcb = g.ldcb; p.beta = g.beta; p.relu = g.relu;
     dim3 grid(ceil_div(g.N, BLOCK_N), ceil_div(g.M, BLOCK_M));
+    const int tiles = (int)(grid.x * grid.y), total_kb = ceil_div(g.K, BLOCK_K);
+    if (tiles <= 64 && total_kb >= 16 && !g.relu && !g.Cb && g.C && (g.beta == 1.f || (g.beta == 0.f && g.ldc == g.N))) {
+        int splits = total_kb / 4;                 // at least 4 k-blocks per CTA
+        if (splits > 256 / tiles) splits = 256 / tiles;
+        if (splits > 1) {
+            const int per = ceil_div(total_kb, splits);
+            splits = ceil_div(total_kb, per);      // every split owns at least one k-block
+        }
+        if (splits > 1) {
+            grid.z = splits;
+            if (g.beta == 0.f) MMV_CUDA(cudaMemsetAsync(g.C, 0, sizeof(float) * (size_t)g.M * g.N, stream));
+        }
+    }
     void (*kern)(const CUtensorMap, const CUtensorMap, params_t) =
         g.a_mn ? (g.b_mn ? gemm_tc_kernel<true, true> : gemm_tc_kernel<true, false>)
                : (g.b_mn ? gemm_tc_kernel<false, true> : gemm_tc_kernel<false, false>);
