@@ -179,6 +179,7 @@ struct nb_lik_args_t {
     float *row_lse = nullptr;         // optional [B]
     int allow_fast = 1;               // use the tuned Rnu = 1 / all-ones-covariate kernel when eligible
     const int *unsorted = nullptr;    // device flag (mmv_csr::d_unsorted); nullptr = treat rows as unsorted
+    int64_t *slice_bounds = nullptr;  // workspace [B x 9] for the tuned kernel (per-row CSR offsets of the gene slices)
 };
 bool nb_likelihood_fast_eligible(const nb_lik_args_t &a);
 int launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stream);

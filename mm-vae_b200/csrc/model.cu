@@ -978,6 +978,7 @@ nb_forward_backward(const step_t &s)
     k.loss_acc = m->acc + 0;
     k.allow_fast = m->nb_fast ? 1 : 0;
     k.unsorted = s.csr->d_unsorted;
+    k.slice_bounds = (int64_t *)WS("k4_bounds", (size_t)B * 9 * 2); NEED(k.slice_bounds);
     if (m->debug_outputs) {
         k.recon_mu = WS("recon_mu", (size_t)B * D); k.recon_nu = WS("recon_nu", (size_t)B * D);
         NEED(k.recon_mu); NEED(k.recon_nu);

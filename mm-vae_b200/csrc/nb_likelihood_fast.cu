@@ -1,29 +1,37 @@
-// K4, tuned path (default overdispersion latent Rnu = 1, all-ones covariate) — same math
-// and cluster mapping as nb_likelihood.cu, reorganised after the first ncu capture
-// (profiles/r01_step1_*: 41 % long-scoreboard stalls on one in-flight LDG per thread,
-// 16 warps/SM, ~180 libdevice instructions per element):
-//   * the row slice of the decoder output is brought in by the TMA unit
-//     (cp.async.bulk 1D + mbarrier tx-count), double buffered: row r+1 streams from HBM
-//     while row r is being processed, so no warp ever waits on a global load;
-//   * the per-gene constants of the slice (bias, nu bias, nu weight) are staged in shared
-//     memory once per CTA instead of being re-read from L2 for every row;
-//   * p, g and the per-gene column sums of the nu gradient live in REGISTERS
-//     (each thread owns genes tid, tid+512, ... of the slice; EPT is a template constant);
-//   * MUFU ex2/lg2/rcp with FMA-pipe polynomials where the MUFU form loses accuracy
-//     (log1p of small arguments); 7 MUFU per element;
-//   * the nonzeros are handled by a compact second loop (all lanes busy) that corrects
-//     the row sums, sends its column-sum deltas straight to red.global.add and, after the
-//     dense store, patches its dL/dlogit entries in place.
-#include "cluster_reduce.cuh"
+// K4, tuned path (default overdispersion latent Rnu = 1, all-ones covariate) — same math as
+// nb_likelihood.cu (nb.hh:433-460,511-531 + autograd), organised around what the ncu captures
+// under profiles/ showed (r01 step 1-3: stalls on cluster.sync's MEMBAR.GPU + L1 invalidate, on
+// serial global-load chains at the head of every row and on the recomputing patch pass):
+//   * a thread-block cluster owns whole rows, each CTA a fixed gene slice for the entire kernel:
+//     per-gene constants staged in shared memory once, per-gene column sums of the nu gradient
+//     in registers; two CTAs (of different clusters) share an SM so one computes while the other
+//     waits on a hop;
+//   * rows arrive through a double-buffered cp.async.bulk + mbarrier ring (row r+1 streams from
+//     HBM while row r is processed);
+//   * the two row reductions (softmax max/sum merged by the online-softmax identity; sum g p and
+//     d znu) cross the cluster with st.async into every peer's slot + a remote mbarrier
+//     complete_tx — no cluster barrier, no memory fence, no L1 invalidate;
+//   * a pre-kernel bisects every cell's CSR run by gene slice, so the nonzero fix-up touches only
+//     its own entries; its indices/values are prefetched one row ahead;
+//   * g lives in shared memory: the nonzero loop overwrites the entries it corrects before the
+//     single coalesced dL/dlogit store (bf16x2 or float2 per thread) — no patch pass;
+//   * dense sweep is branch-free (padded slices), 7 MUFU per element, log1p polynomials on the
+//     FMA pipe; small integer counts use product forms of lgamma / digamma.
+#include "common.cuh"
 #include "kernels.hh"
 
+#include <cooperative_groups.h>
 #include <cuda_bf16.h>
 
 namespace mmv {
 
+namespace cg = cooperative_groups;
+
 namespace {
 
-constexpr int kT = 512;
+constexpr int kT = 256;
+constexpr int NW = kT / 32;
+constexpr int NZP = 2;                                         // nonzeros prefetched per thread per row
 constexpr float kEps = 1e-4f, kNuMin = 1e-4f, kNuMax = 1e4f;   // nb.hh:514,252,459
 
 __device__ __forceinline__ float
@@ -64,6 +72,32 @@ elem_fast(float p, float depth, float u)
     return e;
 }
 
+// lgamma(nu) - lgamma(nu + x) + lgamma(x + 1) and digamma(nu) - digamma(nu + x) for a count x.
+// Small integer counts (the bulk of single-cell data) use the exact product forms
+//   lgamma(nu + x) - lgamma(nu) = log prod_{k<x} (nu + k),  digamma(nu + x) - digamma(nu) = P'(nu) / P(nu)
+// on the FMA pipe with one lg2 and one rcp; anything else falls back to libdevice.
+__constant__ float kLogFact[9] = { 0.f, 0.f, 0.6931471806f, 1.7917594692f, 3.1780538303f, 4.7874917428f,
+                                   6.5792512120f, 8.5251613611f, 10.6046029027f };
+
+__device__ __forceinline__ void
+count_terms(float nu, float x, float &lg_terms, float &dig_diff)
+{
+    const int xi = (int)x;
+    if ((float)xi == x && xi >= 1 && xi <= 8) {
+        float P = nu, dP = 1.f;
+        for (int k = 1; k < xi; ++k) {
+            const float f = nu + (float)k;
+            dP = fmaf(dP, f, P);
+            P *= f;
+        }
+        lg_terms = kLogFact[xi] - __logf(P);
+        dig_diff = -dP * rcp_f(P);
+    } else {
+        lg_terms = lgammaf(nu) + lgammaf(x + 1.f) - lgammaf(nu + x);
+        dig_diff = digamma_f(nu) - digamma_f(nu + x);
+    }
+}
+
 __device__ __forceinline__ uint32_t
 smem_addr(const void *p)
 {
@@ -92,70 +126,104 @@ bar_wait(uint32_t bar, uint32_t parity)
         "}\n" ::"r"(bar), "r"(parity) : "memory");
 }
 
-// lgamma(nu) - lgamma(nu + x) + lgamma(x + 1) and digamma(nu) - digamma(nu + x) for a count x.
-// Small integer counts (the bulk of single-cell data) use the exact product forms
-//   lgamma(nu + x) - lgamma(nu) = log prod_{k<x} (nu + k),  digamma(nu + x) - digamma(nu) = P'(nu) / P(nu)
-// on the FMA pipe with one lg2 and one rcp; anything else falls back to libdevice.
-__constant__ float kLogFact[9] = { 0.f, 0.f, 0.6931471806f, 1.7917594692f, 3.1780538303f, 4.7874917428f,
-                                   6.5792512120f, 8.5251613611f, 10.6046029027f };
-
+// One thread publishes (a, b) into slot[my_rank] of every CTA of the cluster and signals that CTA's
+// mbarrier with the 8 bytes written (st.async ... complete_tx): the data and the signal travel together.
 __device__ __forceinline__ void
-count_terms(float nu, float x, float &lg_terms, float &dig_diff)
+xchg_send(uint32_t slot_local, uint32_t bar_local, int cs, float a, float b)
 {
-    const int xi = (int)x;
-    if ((float)xi == x && xi >= 1 && xi <= 8) {
-        float P = nu, dP = 1.f;
-        for (int k = 1; k < xi; ++k) {
-            const float f = nu + (float)k;
-            dP = fmaf(dP, f, P);
-            P *= f;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_local), "r"(8u * (uint32_t)cs) : "memory");
+    for (int r = 0; r < cs; ++r) {
+        uint32_t rslot, rbar;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rslot) : "r"(slot_local), "r"(r));
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rbar) : "r"(bar_local), "r"(r));
+        asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];"
+                     ::"r"(rslot), "f"(a), "f"(b), "r"(rbar) : "memory");
+    }
+}
+
+// ---------------------------------------------------------------------------
+// pre-kernel: for every minibatch row, the absolute CSR offsets at which each gene slice begins
+// (bounds[row * (cs + 1) + c]); one warp per row.  Unsorted rows get the whole run for every slice
+// (the kernel's range test filters).
+// ---------------------------------------------------------------------------
+__global__ void
+slice_bounds_kernel(const int64_t *indptr, const int32_t *indices, const int32_t *cells, const int *unsorted, int B,
+                    int cs, int Ds, int64_t *bounds)
+{
+    const int lane = threadIdx.x & 31;
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (row >= B) return;
+    const int64_t cell = cells ? (int64_t)cells[row] : (int64_t)row;
+    const int64_t beg = indptr[cell], end = indptr[cell + 1];
+    const bool sorted = unsorted != nullptr && *unsorted == 0;
+    int cnt[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) cnt[c] = 0;
+    if (sorted)
+        for (int64_t q = beg + lane; q < end; q += 32) {
+            const int j = indices[q];
+#pragma unroll
+            for (int c = 1; c < 8; ++c) cnt[c] += (c < cs && j < c * Ds) ? 1 : 0;
         }
-        lg_terms = kLogFact[xi] - __logf(P);
-        dig_diff = -dP * rcp_f(P);
-    } else {
-        lg_terms = lgammaf(nu) + lgammaf(x + 1.f) - lgammaf(nu + x);
-        dig_diff = digamma_f(nu) - digamma_f(nu + x);
+#pragma unroll
+    for (int c = 1; c < 8; ++c) cnt[c] = __reduce_add_sync(0xffffffffu, cnt[c]);
+    if (lane == 0) {
+        int64_t *b = bounds + (size_t)row * (cs + 1);
+#pragma unroll
+        for (int c = 0; c <= 8; ++c) {
+            if (c > cs) break;
+            int64_t v = c == 0 ? beg : end;                  // unsorted: every slice scans the whole run
+            if (sorted && c > 0 && c < cs) v = beg + cnt[c < 8 ? c : 7];
+            b[c] = v;
+        }
     }
 }
 
 template <int EPT>
-__global__ void __launch_bounds__(kT, 1)
+__global__ void __launch_bounds__(kT, 2)
 nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
 {
+    static_assert(EPT % 2 == 0, "threads own adjacent gene pairs");
+    constexpr int HP = EPT / 2;                  // pairs per thread
+    constexpr int Dp = EPT * kT;                 // padded slice length (>= Ds)
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = cs > 1 ? (int)cluster.block_rank() : 0;
     const int cluster_id = blockIdx.x / cs, n_clusters = gridDim.x / cs;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, D = a.D;
-    constexpr int NW = kT / 32;
     const int j0 = rank * Ds, nj = max(0, min(D - j0, Ds));
     const bool grad = a.dlogits != nullptr || a.dlogits_bf16 != nullptr;
     const bool sorted = a.unsorted != nullptr && *a.unsorted == 0;
 
     extern __shared__ __align__(16) float smem[];
-    float *sG0 = smem, *sG1 = sG0 + Ds;          // TMA landing buffers (raw decoder output)
-    float *s_ab = sG1 + Ds;                      // bias: mu_decoding.bias + covar_decoding.bias + mu_bias + sum_c Wcd
-    float *s_ub = s_ab + Ds;                     // nu_decoding.bias - nu_bias
-    float *s_wn = s_ub + Ds;                     // nu_decoding.weight[:, 0]
-    float *scratch = s_wn + Ds;                  // [2 * 32]
-    float *slots = scratch + 64;                 // [2][2 + 2] cluster exchange, double buffered by row parity
-    float *wstat = slots + 8;                    // [2][NW][4] per-warp (max, sumexp, n_lo, n_hi)
-    uint64_t *bars = reinterpret_cast<uint64_t *>(wstat + 2 * NW * 4);   // [2], 8-byte aligned (Ds % 4 == 0)
-    const uint32_t bar0 = smem_addr(bars), bar1 = bar0 + 8;
+    float *sG0 = smem, *sG1 = sG0 + Dp;          // TMA landing buffers (raw decoder output)
+    float *s_ab = sG1 + Dp;                      // bias: mu_decoding.bias + covar_decoding.bias + mu_bias + sum_c Wcd
+    float *s_ub = s_ab + Dp;                     // nu_decoding.bias - nu_bias
+    float *s_wn = s_ub + Dp;                     // nu_decoding.weight[:, 0]
+    float *s_g = s_wn + Dp;                      // g = dl/dm of the current row (dense value, nonzeros overwritten)
+    float *wstat = s_g + Dp;                     // [2 parity][NW][4] per-warp partials of the two reductions
+    float *xslot = wstat + 2 * NW * 4;           // [2 parity][2 exchanges][8 ranks][2]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(xslot + 64);   // [2] row ring + [2 parity][2 exchanges]
+    const uint32_t bar0 = smem_addr(bars), bar1 = bar0 + 8, xbar0 = bar0 + 16;
 
     if (tid == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar1));
+        for (int i = 0; i < 6; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8 * i));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int jj = tid; jj < nj; jj += kT) {
+    for (int jj = tid; jj < Dp; jj += kT) {
         const int j = j0 + jj;
-        float ab = a.abias[j];
-        for (int c = 0; c < a.C; ++c) ab += a.Wcd[(size_t)j * a.C + c];   // covariates are all ones on this path
+        float ab = 0.f, ub = 0.f, wn = 0.f;
+        if (jj < nj) {
+            ab = a.abias[j];
+            for (int c = 0; c < a.C; ++c) ab += a.Wcd[(size_t)j * a.C + c];   // covariates are all ones on this path
+            ub = a.ubias[j];
+            wn = a.Wnd[j];
+        }
         s_ab[jj] = ab;
-        s_ub[jj] = a.ubias[j];
-        s_wn[jj] = a.Wnd[j];
+        s_ub[jj] = ub;
+        s_wn[jj] = wn;
+        if (jj >= nj) sG0[jj] = sG1[jj] = 0.f;   // the padding of the landing buffers is never written by TMA
     }
-    __syncthreads();
+    if (cs > 1) cluster.sync(); else __syncthreads();   // barriers initialised cluster-wide before any remote signal
 
     const uint32_t row_bytes = (uint32_t)nj * 4u;
     int row = cluster_id;
@@ -166,85 +234,84 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
     for (int k = 0; k < EPT; ++k) cdu[k] = cduz[k] = 0.f;
     float nll_acc = 0.f;
 
+    // per-row metadata, one row ahead: scalars, the slice's CSR range, the first NZP nonzeros per thread
+    const int bstride = cs + 1;
+    float dp_n = 0.f, zn_n = 0.f;
+    int64_t qlo_n = 0, qhi_n = 0;
+    int pj[NZP];
+    float px[NZP];
+    if (row < a.B) {
+        dp_n = a.dpre[row]; zn_n = a.znu[row];
+        qlo_n = a.slice_bounds[(size_t)row * bstride + (sorted ? rank : 0)];
+        qhi_n = a.slice_bounds[(size_t)row * bstride + (sorted ? rank + 1 : cs)];
+#pragma unroll
+        for (int i = 0; i < NZP; ++i) {
+            const int64_t q = qlo_n + tid + i * kT;
+            pj[i] = q < qhi_n ? a.indices[q] : -1;
+            px[i] = q < qhi_n ? a.vals[q] : 0.f;
+        }
+    }
+
     for (int it = 0; row < a.B; row += n_clusters, ++it) {
         const int cur = it & 1;
+        const uint32_t ph = (uint32_t)(it >> 1) & 1u;
         const float *sG = cur ? sG1 : sG0;
-        float *slot = slots + cur * 4;
         float *ws = wstat + cur * NW * 4;
+        float *xs = xslot + cur * 32;
+        const uint32_t xb = xbar0 + cur * 16;
         const int next = row + n_clusters;
         if (tid == 0 && next < a.B && nj > 0)   // stream the next row while this one is processed
             bulk_load(smem_addr(cur ? sG0 : sG1), a.G + (size_t)next * D + j0, row_bytes, cur ? bar0 : bar1);
 
-        const int64_t cell = a.cells ? (int64_t)a.cells[row] : (int64_t)row;
-        const float dp = a.dpre[row];
+        const float dp = dp_n, zn = zn_n;
+        const int64_t q_lo = qlo_n, q_hi = qhi_n;
         const float depth = dp > 20.f ? dp : log1pf(expf(dp));       // nb.hh:498 (once per row: exact)
-        const float zn = a.znu[row];
-        const int64_t nz_beg = a.indptr[cell], nz_end = a.indptr[cell + 1];
+        if (next < a.B) {                        // next row's scalars and CSR range (consumed next iteration)
+            dp_n = a.dpre[next]; zn_n = a.znu[next];
+            qlo_n = a.slice_bounds[(size_t)next * bstride + (sorted ? rank : 0)];
+            qhi_n = a.slice_bounds[(size_t)next * bstride + (sorted ? rank + 1 : cs)];
+        }
 
-        // position of this CTA's gene slice inside the (sorted) nonzeros of the cell
-        int n_lo = 0, n_hi = 0;
-        if (sorted)
-            for (int64_t q = nz_beg + tid; q < nz_end; q += kT) {
-                const int j = a.indices[q];
-                n_lo += j < j0;
-                n_hi += j < j0 + nj;
-            }
-
-        if (nj > 0) bar_wait(cur ? bar1 : bar0, (uint32_t)(it >> 1) & 1u);
+        if (nj > 0) bar_wait(cur ? bar1 : bar0, ph);
 
         // ---- pass 1: logits into registers; softmax numerators against the WARP max, so one
         //      block hop + one cluster hop give max and sum together (online-softmax merge)
         float v[EPT];
         float wm = -INFINITY;
 #pragma unroll
-        for (int k = 0; k < EPT; ++k) {
-            const int jj = tid + k * kT;
-            v[k] = jj < nj ? sG[jj] + s_ab[jj] : -INFINITY;
-            wm = fmaxf(wm, v[k]);
+        for (int h = 0; h < HP; ++h) {
+            const int jj = 2 * tid + h * 2 * kT;
+            const float2 gq = *reinterpret_cast<const float2 *>(sG + jj);
+            const float2 ab = *reinterpret_cast<const float2 *>(s_ab + jj);
+            v[2 * h] = jj < nj ? gq.x + ab.x : -INFINITY;            // nj is even: a pair is valid or not as a whole
+            v[2 * h + 1] = jj < nj ? gq.y + ab.y : -INFINITY;
+            wm = fmaxf(wm, fmaxf(v[2 * h], v[2 * h + 1]));
         }
         wm = warp_max(wm);
+        const float wm_safe = wm > -INFINITY ? wm : 0.f;
         float wsum = 0.f;
-        if (wm > -INFINITY) {
 #pragma unroll
-            for (int k = 0; k < EPT; ++k) {
-                v[k] = __expf(v[k] - wm);          // exp(-inf) = 0 for the padding lanes
-                wsum += v[k];
-            }
-        } else {
-#pragma unroll
-            for (int k = 0; k < EPT; ++k) v[k] = 0.f;
+        for (int k = 0; k < EPT; ++k) {
+            v[k] = __expf(v[k] - wm_safe);         // exp(-inf) = 0 on the padding
+            wsum += v[k];
         }
         wsum = warp_sum(wsum);
-        n_lo = __reduce_add_sync(0xffffffffu, n_lo);
-        n_hi = __reduce_add_sync(0xffffffffu, n_hi);
-        if (lane == 0) {
-            ws[warp * 4 + 0] = wm;
-            ws[warp * 4 + 1] = wsum;
-            ws[warp * 4 + 2] = __int_as_float(n_lo);
-            ws[warp * 4 + 3] = __int_as_float(n_hi);
-        }
+        if (lane == 0) { ws[warp * 4 + 0] = wm; ws[warp * 4 + 1] = wsum; }
         __syncthreads();
-        float bm = lane < NW ? ws[lane * 4 + 0] : -INFINITY;
+        const float bm = lane < NW ? ws[lane * 4 + 0] : -INFINITY;
         const float bs_in = lane < NW ? ws[lane * 4 + 1] : 0.f;
-        int c_lo = lane < NW ? __float_as_int(ws[lane * 4 + 2]) : 0;
-        int c_hi = lane < NW ? __float_as_int(ws[lane * 4 + 3]) : 0;
         const float bmax = warp_max(bm);
-        float bsum = warp_sum(bm > -INFINITY ? bs_in * __expf(bm - bmax) : 0.f);
-        c_lo = __reduce_add_sync(0xffffffffu, c_lo);
-        c_hi = __reduce_add_sync(0xffffffffu, c_hi);
+        const float bsum = warp_sum(bm > -INFINITY ? bs_in * __expf(bm - bmax) : 0.f);
         float gmax = bmax, gsum = bsum;
         if (cs > 1) {
-            if (tid == 0) { slot[0] = bmax; slot[1] = bsum; }
-            cluster.sync();
+            if (tid == 0) xchg_send(smem_addr(xs + rank * 2), xb, cs, bmax, bsum);
+            bar_wait(xb, ph);
             gmax = -INFINITY;
             float rm[8], rs[8];
 #pragma unroll
             for (int r = 0; r < 8; ++r) {
                 rm[r] = -INFINITY; rs[r] = 0.f;
-                if (r < cs) {
-                    const float *remote = cluster.map_shared_rank(slot, r);
-                    rm[r] = remote[0]; rs[r] = remote[1];
-                }
+                if (r < cs) { rm[r] = xs[r * 2]; rs[r] = xs[r * 2 + 1]; }
                 gmax = fmaxf(gmax, rm[r]);
             }
             gsum = 0.f;
@@ -254,120 +321,138 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         const float inv_sum = 1.f / gsum;
         const float scale = wm > -INFINITY ? __expf(wm - gmax) * inv_sum : 0.f;
         if (a.row_lse && rank == 0 && tid == 0) a.row_lse[row] = gmax + logf(gsum);
-        const int64_t q_lo = sorted ? nz_beg + c_lo : nz_beg, q_hi = sorted ? nz_beg + c_hi : nz_end;
 
-        // ---- pass 2: dense sweep assuming x = 0 (lgammas cancel, no digamma)
-        float g[EPT];
+        // ---- pass 2: dense sweep assuming x = 0 (lgammas cancel, no digamma).  Branch-free: the
+        //      out-of-range lanes compute on the padding and are masked at the accumulations.
         float red[2] = { 0.f, 0.f };           // s = sum g p ; d znu
 #pragma unroll
-        for (int k = 0; k < EPT; ++k) {
-            const int jj = tid + k * kT;
-            if (jj < nj) {
-                const float p = v[k] * scale;
-                const float wn = s_wn[jj];
-                const elem_t e = elem_fast(p, depth, fmaf(zn, wn, s_ub[jj]));
-                nll_acc = fmaf(e.nu, e.l1p, nll_acc);
+        for (int h = 0; h < HP; ++h) {
+            const int jj = 2 * tid + h * 2 * kT;
+            const float ok = jj < nj ? 1.f : 0.f;
+            const float2 wn2 = *reinterpret_cast<const float2 *>(s_wn + jj);
+            const float2 ub2 = *reinterpret_cast<const float2 *>(s_ub + jj);
+            float gg[2];
+#pragma unroll
+            for (int e2 = 0; e2 < 2; ++e2) {
+                const int k = 2 * h + e2;
+                const float wn = e2 ? wn2.y : wn2.x, ub = e2 ? ub2.y : ub2.x;
+                const float p = v[k] * scale;  // 0 on the padding
+                const elem_t e = elem_fast(p, depth, fmaf(zn, wn, ub));
+                nll_acc = fmaf(e.nu * ok, e.l1p, nll_acc);
                 v[k] = p;
-                g[k] = e.nu * e.inv_mnu;
-                red[0] = fmaf(g[k], p, red[0]);
-                const float du = (e.l1p - e.m * e.inv_mnu) * e.sig_mask * a.inv_B;
+                gg[e2] = e.nu * e.inv_mnu;
+                red[0] = fmaf(gg[e2], p, red[0]);
+                const float du = (e.l1p - e.m * e.inv_mnu) * e.sig_mask * (a.inv_B * ok);
                 cdu[k] += du;
                 cduz[k] = fmaf(du, zn, cduz[k]);
                 red[1] = fmaf(du, wn, red[1]);
-            } else {
-                g[k] = 0.f;
             }
+            *reinterpret_cast<float2 *>(s_g + jj) = make_float2(gg[0], gg[1]);
         }
+        __syncthreads();                       // s_g complete before the nonzero loop overwrites entries
 
-        // ---- pass 2b: compact loop over this cell's nonzeros that fall in the slice
-        for (int64_t q = q_lo + tid; q < q_hi; q += kT) {
-            const int j = a.indices[q];
+        // ---- pass 2b: this cell's nonzeros that fall in the slice (prefetched; overflow from global)
+        auto fix = [&](int j, float x) {
             const int jj = j - j0;
-            const float x = a.vals[q];
-            if (jj < 0 || jj >= nj || x == 0.f) continue;
+            if (jj < 0 || jj >= nj || x == 0.f) return;
             const float p = __expf(sG[jj] + s_ab[jj] - gmax) * inv_sum;
             const float wn = s_wn[jj];
             const elem_t e = elem_fast(p, depth, fmaf(zn, wn, s_ub[jj]));
             const float L = __logf(e.m + e.nu);
             float lg_terms, dig_diff;
             count_terms(e.nu, x, lg_terms, dig_diff);
-            // nb.hh:522-528 minus the x = 0 value already counted
-            nll_acc += lg_terms + x * (L - __logf(e.m));
+            nll_acc += lg_terms + x * (L - __logf(e.m));   // nb.hh:522-528 minus the x = 0 value already counted
             if (grad) {
                 const float gx = (e.nu + x) * e.inv_mnu - x * rcp_f(e.m);
                 red[0] = fmaf(gx - e.nu * e.inv_mnu, p, red[0]);
-                const float ddnu = dig_diff + x * e.inv_mnu;   // dnu_x - dnu_0
-                const float ddu = ddnu * e.sig_mask * a.inv_B;
+                s_g[jj] = gx;
+                const float ddu = (dig_diff + x * e.inv_mnu) * e.sig_mask * a.inv_B;   // dnu_x - dnu_0
                 atomicAdd(a.col_du + j, ddu);
                 atomicAdd(a.col_duz + j, ddu * zn);
                 red[1] = fmaf(ddu, wn, red[1]);
             }
+        };
+#pragma unroll
+        for (int i = 0; i < NZP; ++i)
+            if (pj[i] >= 0) fix(pj[i], px[i]);
+        for (int64_t q = q_lo + tid + NZP * kT; q < q_hi; q += kT) fix(a.indices[q], a.vals[q]);
+        if (next < a.B) {                      // prefetch the next row's nonzeros (its range arrived long ago)
+#pragma unroll
+            for (int i = 0; i < NZP; ++i) {
+                const int64_t q = qlo_n + tid + i * kT;
+                pj[i] = q < qhi_n ? a.indices[q] : -1;
+                px[i] = q < qhi_n ? a.vals[q] : 0.f;
+            }
         }
 
         if (grad) {
-            cluster_sum<2>(red, slot + 2, scratch, cluster, cs);
-            const float s = red[0];
+            // ---- second reduction: s = sum g p, d znu
+            red[0] = warp_sum(red[0]);
+            red[1] = warp_sum(red[1]);
+            if (lane == 0) { ws[warp * 4 + 2] = red[0]; ws[warp * 4 + 3] = red[1]; }
+            __syncthreads();                   // also: every s_g fix is visible
+            float s = warp_sum(lane < NW ? ws[lane * 4 + 2] : 0.f);
+            float dz = warp_sum(lane < NW ? ws[lane * 4 + 3] : 0.f);
+            if (cs > 1) {
+                if (tid == 0) xchg_send(smem_addr(xs + 16 + rank * 2), xb + 8, cs, s, dz);
+                bar_wait(xb + 8, ph);
+                s = 0.f; dz = 0.f;
+#pragma unroll
+                for (int r = 0; r < 8; ++r)
+                    if (r < cs) { s += xs[16 + r * 2]; dz += xs[16 + r * 2 + 1]; }
+            }
             const float coef = depth * a.inv_B;
-            // ---- pass 3: dL/dlogit_j = (d_i / B) p_j (g_j - s_i), coalesced
-            if (a.dlogits_bf16) {
-                __nv_bfloat16 *drow = reinterpret_cast<__nv_bfloat16 *>(a.dlogits_bf16) + (size_t)row * D + j0;
+            // ---- pass 3: dL/dlogit_j = (d_i / B) p_j (g_j - s_i), one coalesced store per pair
 #pragma unroll
-                for (int k = 0; k < EPT; ++k) {
-                    const int jj = tid + k * kT;
-                    if (jj < nj) drow[jj] = __float2bfloat16(coef * v[k] * (g[k] - s));
-                }
-            } else {
-                float *drow = a.dlogits + (size_t)row * D + j0;
-#pragma unroll
-                for (int k = 0; k < EPT; ++k) {
-                    const int jj = tid + k * kT;
-                    if (jj < nj) drow[jj] = coef * v[k] * (g[k] - s);
+            for (int h = 0; h < HP; ++h) {
+                const int jj = 2 * tid + h * 2 * kT;
+                if (jj < nj) {
+                    const float2 gq = *reinterpret_cast<const float2 *>(s_g + jj);
+                    const float o0 = coef * v[2 * h] * (gq.x - s), o1 = coef * v[2 * h + 1] * (gq.y - s);
+                    if (a.dlogits_bf16) {
+                        const __nv_bfloat162 b = __floats2bfloat162_rn(o0, o1);
+                        *reinterpret_cast<__nv_bfloat162 *>(reinterpret_cast<__nv_bfloat16 *>(a.dlogits_bf16) +
+                                                            (size_t)row * D + j0 + jj) = b;
+                    } else {
+                        *reinterpret_cast<float2 *>(a.dlogits + (size_t)row * D + j0 + jj) = make_float2(o0, o1);
+                    }
                 }
             }
             if (rank == 0 && tid == 0) {
                 a.ddpre[row] = s * a.inv_B * (dp > 20.f ? 1.f : 1.f / (1.f + expf(-dp)));
-                a.dznu[row] = red[1];
-            }
-            __syncthreads();   // dense stores of this block are visible before the patches below
-            // ---- pass 3b: patch the entries of the nonzeros
-            for (int64_t q = q_lo + tid; q < q_hi; q += kT) {
-                const int j = a.indices[q];
-                const int jj = j - j0;
-                const float x = a.vals[q];
-                if (jj < 0 || jj >= nj || x == 0.f) continue;
-                const float p = __expf(sG[jj] + s_ab[jj] - gmax) * inv_sum;
-                const elem_t e = elem_fast(p, depth, fmaf(zn, s_wn[jj], s_ub[jj]));
-                const float gx = (e.nu + x) * e.inv_mnu - x * rcp_f(e.m);
-                const float dl = coef * p * (gx - s);
-                if (a.dlogits_bf16)
-                    reinterpret_cast<__nv_bfloat16 *>(a.dlogits_bf16)[(size_t)row * D + j] = __float2bfloat16(dl);
-                else
-                    a.dlogits[(size_t)row * D + j] = dl;
+                a.dznu[row] = dz;
             }
         }
-        __syncthreads();       // everyone is done with sG[cur] before the TMA unit refills it
+        __syncthreads();       // everyone is done with sG[cur] / s_g before the TMA unit and the next row refill them
     }
 
-    float nl[1] = { nll_acc };
-    block_sum<1>(nl, scratch);
-    if (tid == 0 && nl[0] != 0.f) atomicAdd(a.loss_acc, (double)nl[0]);
+    nll_acc = warp_sum(nll_acc);
+    if (lane == 0 && nll_acc != 0.f) atomicAdd(a.loss_acc, (double)nll_acc);
     if (grad) {
 #pragma unroll
-        for (int k = 0; k < EPT; ++k) {
-            const int jj = tid + k * kT;
+        for (int h = 0; h < HP; ++h) {
+            const int jj = 2 * tid + h * 2 * kT;
             if (jj < nj) {
-                atomicAdd(a.col_du + j0 + jj, cdu[k]);
-                atomicAdd(a.col_duz + j0 + jj, cduz[k]);
+                atomicAdd(a.col_du + j0 + jj, cdu[2 * h]);
+                atomicAdd(a.col_du + j0 + jj + 1, cdu[2 * h + 1]);
+                atomicAdd(a.col_duz + j0 + jj, cduz[2 * h]);
+                atomicAdd(a.col_duz + j0 + jj + 1, cduz[2 * h + 1]);
             }
         }
     }
-    if (cs > 1) cluster.sync();
+    if (cs > 1) cluster.sync();   // no CTA exits while a peer may still signal its barriers
 }
 
 size_t
-fast_smem_bytes(int Ds)
+fast_smem_bytes(int ept)
 {
-    return sizeof(float) * ((size_t)5 * Ds + 64 + 8 + 2 * (kT / 32) * 4) + 16;
+    return sizeof(float) * ((size_t)6 * ept * kT + 2 * NW * 4 + 64) + 6 * 8 + 16;
+}
+
+int
+ept_class(int ept)
+{
+    return ept <= 4 ? 4 : ept <= 8 ? 8 : ept <= 12 ? 12 : 16;
 }
 
 } // namespace
@@ -375,24 +460,32 @@ fast_smem_bytes(int Ds)
 bool
 nb_likelihood_fast_eligible(const nb_lik_args_t &a)
 {
-    return a.Rnu == 1 && a.cov == nullptr && a.D % 4 == 0 && a.recon_mu == nullptr && a.recon_nu == nullptr &&
-        (reinterpret_cast<uintptr_t>(a.G) & 15) == 0;
+    return a.Rnu == 1 && a.cov == nullptr && a.D % 4 == 0 && a.D <= 8 * 16 * kT - 32 && a.recon_mu == nullptr &&
+        a.recon_nu == nullptr && a.slice_bounds != nullptr && (reinterpret_cast<uintptr_t>(a.G) & 15) == 0 &&
+        (a.dlogits == nullptr || (reinterpret_cast<uintptr_t>(a.dlogits) & 7) == 0);
 }
 
 int
 launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stream)
 {
-    const size_t budget = 200 * 1024;
+    const size_t budget = 110 * 1024;   // two CTAs per SM
     int cs = 1, Ds = 0, ept = 0;
     for (;; cs *= 2) {
         Ds = ((a.D + cs - 1) / cs + 3) & ~3;
         ept = (Ds + kT - 1) / kT;
-        if (fast_smem_bytes(Ds) <= budget && ept <= 16) break;
+        if (ept <= 16 && fast_smem_bytes(ept_class(ept)) <= budget) break;
         MMV_CHECK(cs < 8, "nb_likelihood: D=%d does not fit a cluster of 8 CTAs", a.D);
+    }
+    {
+        const int warps_per_cta = 8;
+        slice_bounds_kernel<<<ceil_div(a.B, warps_per_cta), 32 * warps_per_cta, 0, stream>>>(
+            a.indptr, a.indices, a.cells, a.unsorted, a.B, cs, Ds, a.slice_bounds);
+        ::mmv::count_launch();
+        MMV_CUDA(cudaGetLastError());
     }
     void (*kern)(nb_lik_args_t, int, int) = ept <= 4 ? nb_likelihood_fast_kernel<4>
         : ept <= 8 ? nb_likelihood_fast_kernel<8> : ept <= 12 ? nb_likelihood_fast_kernel<12> : nb_likelihood_fast_kernel<16>;
-    const size_t smem = fast_smem_bytes(Ds);
+    const size_t smem = fast_smem_bytes(ept_class(ept));
     MMV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(num_sms / cs * cs);
@@ -406,9 +499,8 @@ launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stre
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    // persistent clusters: exactly one wave.  A GPC holds fewer whole clusters than SMs / cs
-    // (148 SMs take 33 clusters of 4, not 37), and a second wave would double the kernel time.
-    int n_clusters = num_sms / cs;
+    // persistent clusters: exactly one wave (a second wave would double the kernel time)
+    int n_clusters = 2 * num_sms / cs;
     if (cs > 1) {
         int fit = 0;
         MMV_CUDA(cudaOccupancyMaxActiveClusters(&fit, kern, &cfg));
