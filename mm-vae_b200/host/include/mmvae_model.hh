@@ -1,0 +1,183 @@
+// Model handles with the reference's constructor arguments, over the C ABI (include/mmvae_b200.h):
+//   mmvae::nb::nbvae_t    <- nbvae_tImpl ctor   include/models/nb.hh:214-221,299-401
+//   mmvae::vmf::vmf_vae_t <- vmf_vae_tImpl ctor include/models/vmf.hh:200-207,307-389
+// and the recorder visitors (update_on_batch / update_on_epoch, nb.hh:569-662, vmf.hh:457-551) reduced to
+// what the hot path needs: the per-cell latent mean / log-variance table through mmv_encode (eval mode,
+// no covariates, nb.hh:627-628) written as gz text at the recording epochs.
+#ifndef MMVAE_B200_MODEL_HH_
+#define MMVAE_B200_MODEL_HH_
+
+#include "../../../include/mmvae_b200.h"
+#include "mmvae_io.hh"
+#include "mmvae_options.hh"
+
+#include <memory>
+#include <zlib.h>
+
+namespace mmvae {
+
+struct device_t {   // one context + the resident data of a run
+    mmv_ctx *ctx = nullptr;
+    mmv_csr *csr = nullptr;
+    ~device_t()
+    {
+        if (csr) mmv_csr_destroy(csr);
+        if (ctx) mmv_ctx_destroy(ctx);
+    }
+    // upload the counts (cells x genes CSR) and the covariates (dense [N x C], or none = all ones)
+    int upload(int device, const mtx_data_block_t &data, const std::vector<float> *covar, int64_t c_dim)
+    {
+        MMV_OK(mmv_ctx_create(device, &ctx));
+        MMV_OK(mmv_csr_upload(ctx, data.ntot(), data.nfeature(), data.indptr.data(), data.indices.data(),
+                              data.values.data(), covar ? covar->data() : nullptr, c_dim, &csr));
+        return EXIT_SUCCESS;
+    }
+};
+
+class model_base_t {
+public:
+    ~model_base_t() { if (m_) mmv_model_destroy(m_); }
+    mmv_model *get() const { return m_; }
+    int configure(const training_options_t &opt)
+    {
+        MMV_OK(mmv_model_set_option(m_, "lr", opt.lr));
+        MMV_OK(mmv_model_set_option(m_, "grad_clip", opt.grad_clip));
+        MMV_OK(mmv_model_set_option(m_, "weight_decay", 1e-4));   // mmvae_alg.hh:236
+        MMV_OK(mmv_model_set_option(m_, "dtype", opt.bf16 ? 1 : 0));
+        MMV_OK(mmv_model_set_option(m_, "train_all_layers", opt.train_all_layers ? 1 : 0));
+        MMV_OK(mmv_model_set_option(m_, "frozen_grads", 0));      // never read on this path: skip the dead work
+        return EXIT_SUCCESS;
+    }
+    void pretty_print(std::ostream &os) const
+    {
+        int n = 0;
+        mmv_model_num_params(m_, &n);
+        for (int i = 0; i < n; ++i) {
+            char name[MMV_NAME_LEN];
+            int64_t r, c;
+            int reg;
+            mmv_model_param_info(m_, i, name, &r, &c, &reg);
+            os << "  " << name << " [" << r << " x " << c << "]" << (reg ? "" : " (not registered: frozen unless --train_all_layers)") << "\n";
+        }
+    }
+    int64_t latent_dim = 0;
+
+protected:
+    mmv_model *m_ = nullptr;
+};
+
+namespace nb {
+
+class nbvae_t : public model_base_t {
+public:
+    nbvae_t(mmv_ctx *ctx, int64_t data_dim, int64_t covar_dim, const std::vector<int64_t> &mu_enc_h,
+            const std::vector<int64_t> &mu_dec_h, int64_t mu_r_dim, int64_t nu_h_dim, int64_t nu_r_dim, bool do_relu,
+            uint64_t seed)
+    {
+        mmv_nb_dims d;
+        std::memset(&d, 0, sizeof(d));
+        d.x_dim = data_dim; d.c_dim = covar_dim;
+        ASSERT(mu_enc_h.size() <= MMV_MAX_LAYERS && mu_dec_h.size() <= MMV_MAX_LAYERS, "too many layers");
+        d.n_enc = (int32_t)mu_enc_h.size();
+        for (size_t i = 0; i < mu_enc_h.size(); ++i) d.enc_dims[i] = mu_enc_h[i];
+        d.n_dec = (int32_t)mu_dec_h.size();
+        for (size_t i = 0; i < mu_dec_h.size(); ++i) d.dec_dims[i] = mu_dec_h[i];
+        d.mu_r_dim = mu_r_dim; d.nu_h_dim = nu_h_dim; d.nu_r_dim = nu_r_dim; d.do_relu = do_relu ? 1 : 0;
+        MMV_OK_EXIT(mmv_nb_model_create(ctx, &d, seed, &m_));
+        latent_dim = mu_r_dim;
+    }
+};
+
+} // namespace nb
+
+namespace vmf {
+
+class vmf_vae_t : public model_base_t {
+public:
+    vmf_vae_t(mmv_ctx *ctx, int64_t data_dim, int64_t covar_dim, int64_t z_dim, const std::vector<int64_t> &enc_h,
+              const std::vector<int64_t> &dec_h, float kappa_min, float kappa_max, bool do_relu, uint64_t seed)
+    {
+        mmv_vmf_dims d;
+        std::memset(&d, 0, sizeof(d));
+        d.x_dim = data_dim; d.c_dim = covar_dim; d.z_dim = z_dim;
+        ASSERT(enc_h.size() <= MMV_MAX_LAYERS && dec_h.size() <= MMV_MAX_LAYERS, "too many layers");
+        d.n_enc = (int32_t)enc_h.size();
+        for (size_t i = 0; i < enc_h.size(); ++i) d.enc_dims[i] = enc_h[i];
+        d.n_dec = (int32_t)dec_h.size();
+        for (size_t i = 0; i < dec_h.size(); ++i) d.dec_dims[i] = dec_h[i];
+        d.kappa_min = kappa_min; d.kappa_max = kappa_max; d.do_relu = do_relu ? 1 : 0;
+        MMV_OK_EXIT(mmv_vmf_model_create(ctx, &d, seed, &m_));
+        latent_dim = z_dim;
+    }
+};
+
+} // namespace vmf
+
+// VISITOR concept (mmvae_alg.hh:316,332).  Writes ${out}.latent_mean_${epoch}.gz / latent_lnvar at the
+// recording epochs: one line per data point, R columns (ostream default precision like io.hh:308-331).
+class latent_recorder_t {
+public:
+    latent_recorder_t(const std::string &out, int64_t max_epoch, device_t &dev) : out_(out), max_epoch_(max_epoch), dev_(dev) { }
+
+    template <typename MODEL, typename DATA_BLOCK>
+    void update_on_batch(MODEL &model, DATA_BLOCK &data, const std::vector<typename DATA_BLOCK::Index> &batch)
+    {
+        const int64_t R = model.latent_dim, B = (int64_t)batch.size();
+        if (mean_.empty()) {
+            mean_.assign((size_t)(data.ntot() * R), 0.f);
+            lnvar_.assign((size_t)(data.ntot() * R), 0.f);
+        }
+        std::vector<int64_t> cells(batch.begin(), batch.end());
+        std::vector<float> mu((size_t)(B * R)), lv((size_t)(B * R));
+        MMV_OK_EXIT(mmv_encode(model.get(), dev_.csr, cells.data(), B, mu.data(), lv.data()));
+        for (int64_t j = 0; j < B; ++j) {
+            std::copy(mu.begin() + j * R, mu.begin() + (j + 1) * R, mean_.begin() + cells[(size_t)j] * R);
+            std::copy(lv.begin() + j * R, lv.begin() + (j + 1) * R, lnvar_.begin() + cells[(size_t)j] * R);
+        }
+    }
+
+    template <typename MODEL>
+    void update_on_epoch(MODEL &model, int64_t epoch)
+    {
+        const std::string tag = zeropad(epoch + 1, max_epoch_);
+        write(out_ + ".latent_mean_" + tag + ".gz", mean_, model.latent_dim);
+        write(out_ + ".latent_lnvar_" + tag + ".gz", lnvar_, model.latent_dim);
+    }
+
+private:
+    static void write(const std::string &path, const std::vector<float> &v, int64_t R)
+    {
+        if (v.empty() || R <= 0) return;
+        gzFile g = gzopen(path.c_str(), "wb");
+        if (!g) { ELOG("unable to write " << path); return; }
+        std::ostringstream os;
+        for (size_t i = 0; i < v.size(); ++i) {
+            os << v[i] << (((int64_t)(i + 1) % R == 0) ? "\n" : " ");
+            if (os.tellp() > (1 << 20)) { const std::string s = os.str(); gzwrite(g, s.data(), (unsigned)s.size()); os.str(""); }
+        }
+        const std::string s = os.str();
+        gzwrite(g, s.data(), (unsigned)s.size());
+        gzclose(g);
+    }
+    std::string out_;
+    int64_t max_epoch_;
+    device_t &dev_;
+    std::vector<float> mean_, lnvar_;
+};
+
+// io.hh:308-331 write_vector_file: one value per line, gz
+inline int
+write_vector_file(const std::string &path, const std::vector<float> &v)
+{
+    gzFile g = gzopen(path.c_str(), "wb");
+    ERR_RET(!g, "unable to write " << path);
+    std::ostringstream os;
+    for (float x : v) os << x << "\n";
+    const std::string s = os.str();
+    gzwrite(g, s.data(), (unsigned)s.size());
+    gzclose(g);
+    return EXIT_SUCCESS;
+}
+
+} // namespace mmvae
+#endif

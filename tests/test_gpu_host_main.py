@@ -1,0 +1,63 @@
+"""The C++ mains (mm-vae_b200/host/bin/nb_vae, vmf_vae) end to end on a B200: reference command line,
+bgzf-indexed Matrix Market input, resident CSR, the epoch / batch / bootstrap schedule of
+mmvae_alg.hh:254-334 through the C ABI, ${out}.scores.gz and the latent tables out."""
+import gzip
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+HOST = os.path.join(ROOT, "mm-vae_b200", "host")
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def bins():
+    subprocess.run(["make", "-C", os.path.join(ROOT, "mm-vae_b200")], check=True, stdout=subprocess.DEVNULL)
+    subprocess.run(["make", "-C", HOST], check=True, stdout=subprocess.DEVNULL)
+    return os.path.join(HOST, "bin")
+
+
+def scores(path):
+    return np.array([float(v) for v in gzip.open(path, "rt").read().split()], dtype=np.float64)
+
+
+@pytest.mark.parametrize("dtype", ["f32", "bf16"])
+def test_nb_vae_main_trains(bins, tmp_path, dtype):
+    out = tmp_path / "nb"
+    idx = tmp_path / "b.index"
+    cmd = [os.path.join(bins, "nb_vae"), "--mtx", os.path.join(GOLDEN, "reader_b.mtx.gz"), "--idx", str(idx), "--out", str(out),
+           "--batch_size", "100", "--mean_encoding", "64", "--mean_decoding", "64", "--mean_latent", "8", "--max_epoch", "6",
+           "--recording", "3", "--nboot", "2", "--seed", "5", "--dtype", dtype, "--train_all_layers", "--lr", "0.01"]
+    p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr[-2000:]
+    assert idx.exists()                                  # built on demand like nb_vae_main.cc:56-57
+    s = scores(str(out) + ".scores.gz")
+    assert s.shape == (6,) and np.all(np.isfinite(s)) and s[-1] < s[0]
+    for tag in ("3", "6"):
+        m = np.loadtxt(gzip.open(f"{out}.latent_mean_{tag}.gz", "rt"))
+        lv = np.loadtxt(gzip.open(f"{out}.latent_lnvar_{tag}.gz", "rt"))
+        assert m.shape == (500, 8) and lv.shape == (500, 8) and np.all(np.isfinite(m))
+        assert np.all(lv >= -4.0001) and np.all(lv <= 4.0001)          # clamp of nb.hh:415
+
+
+def test_vmf_vae_main_trains(bins, tmp_path):
+    out = tmp_path / "vmf"
+    cmd = [os.path.join(bins, "vmf_vae"), "--mtx", os.path.join(GOLDEN, "reader_b.mtx.gz"), "--idx", str(tmp_path / "b.index"),
+           "--out", str(out), "--batch", "128", "--encoding", "32", "--decoding", "32", "--latent", "4", "--epoch", "4",
+           "--recording", "4", "--seed", "3", "--train_all_layers"]
+    p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr[-2000:]
+    s = scores(str(out) + ".scores.gz")
+    assert s.shape == (4,) and np.all(np.isfinite(s)) and s[-1] <= s[0]
+    assert np.loadtxt(gzip.open(f"{out}.latent_mean_4.gz", "rt")).shape == (500, 4)
+
+
+def test_main_fails_like_reference_without_out(bins):
+    p = subprocess.run([os.path.join(bins, "nb_vae"), "--mtx", os.path.join(GOLDEN, "reader_b.mtx.gz")],
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=60)
+    assert p.returncode == 1 and "need output file header" in p.stderr

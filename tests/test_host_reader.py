@@ -1,0 +1,143 @@
+"""Host C++ surface (mm-vae_b200/host): reader + option parsers, CPU only.
+
+The tool's output is compared bit for bit with tests/golden/reader_golden.npz, i.e. with what the
+REFERENCE reader (mmutil_index.hh, mmutil_bgzf_util.hh, strbuf.hh, bgzf.c compiled verbatim by
+oracle/_ref/ref_reader_harness) produced on the same files — the same fixtures the Python oracle is
+pinned to in test_oracle_golden.py.
+"""
+import gzip
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+HOST = os.path.join(ROOT, "mm-vae_b200", "host")
+TOOL = os.path.join(HOST, "bin", "mmv_reader_tool")
+FILES = {"a": "reader_a.mtx.gz", "b": "reader_b.mtx.gz", "ones": "reader_ones.mtx.gz"}
+
+
+@pytest.fixture(scope="module")
+def tool():
+    subprocess.run(["make", "-C", HOST, "bin/mmv_reader_tool"], check=True, stdout=subprocess.DEVNULL)
+    return TOOL
+
+
+@pytest.fixture(scope="module")
+def rg():
+    z = np.load(os.path.join(GOLDEN, "reader_golden.npz"))
+    return {k: z[k] for k in z.files}
+
+
+def run(tool, *args):
+    return subprocess.run([tool, *map(str, args)], check=True, stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                          text=True).stdout
+
+
+def test_take_float_bit_exact(tool, rg):
+    toks = bytes(rg["float_tokens"]).decode().split("\n")
+    got = [int(v) for v in run(tool, "floats", *toks).split()]
+    assert got == rg["float_values"].view(np.uint32).tolist()
+
+
+@pytest.mark.parametrize("tag", list(FILES))
+def test_header_index_table(tool, rg, tag, tmp_path):
+    path = os.path.join(GOLDEN, FILES[tag])
+    out = run(tool, "header", path).split("\n")
+    assert [int(v) for v in out[0].split()] == rg[f"{tag}__header"].tolist()
+    assert out[1] == "is_bgzf 1"
+    assert run(tool, "scan", path).encode() == bytes(rg[f"{tag}__index_text"])
+    idx = tmp_path / "t.index"
+    tab = [int(v) for v in run(tool, "table", path, idx).split()]
+    assert gzip.open(idx, "rb").read() == bytes(rg[f"{tag}__index_text"])   # same index FILE format
+    assert tab == rg[f"{tag}__table"].tolist()
+
+
+@pytest.mark.parametrize("tag", list(FILES))
+@pytest.mark.parametrize("blk", ["all", "mid"])
+def test_block_triplets(tool, rg, tag, blk):
+    path = os.path.join(GOLDEN, FILES[tag])
+    beg, end = rg[f"{tag}__block_{blk}_range"].tolist()
+    rows = np.array([[int(v) for v in ln.split()] for ln in run(tool, "block", path, beg, end).splitlines()], dtype=np.int64)
+    assert rows[:, 0].tolist() == rg[f"{tag}__block_{blk}_rows"].tolist()
+    assert rows[:, 1].tolist() == rg[f"{tag}__block_{blk}_cols"].tolist()
+    assert rows[:, 2].tolist() == rg[f"{tag}__block_{blk}_vals"].view(np.uint32).tolist()
+
+
+@pytest.mark.parametrize("tag", list(FILES))
+def test_dense_minibatches_indexed_and_csr(tool, rg, tag, tmp_path):
+    """Minibatch indexing is bit-exact both through the reference's index/block route and through the
+    parse-once CSR the device path uses (wrap-around batches, duplicate cells included)."""
+    path = os.path.join(GOLDEN, FILES[tag])
+    idx = tmp_path / "t.index"
+    run(tool, "table", path, idx)
+    D = int(rg[f"{tag}__header"][0])
+    for cols, dense in zip(rg[f"{tag}__batches"], rg[f"{tag}__dense"]):
+        out = tmp_path / "d.bin"
+        run(tool, "dense", path, idx, out, *cols.tolist())
+        got = np.fromfile(out, dtype=np.float32).reshape(2, len(cols), D)
+        assert np.array_equal(got[0].view(np.uint32), dense.view(np.uint32))
+        assert np.array_equal(got[1].view(np.uint32), dense.view(np.uint32))
+
+
+def test_csr_rows_sorted_and_complete(tool, rg, tmp_path):
+    path = os.path.join(GOLDEN, FILES["b"])
+    idx = tmp_path / "t.index"
+    run(tool, "table", path, idx)
+    D, N, nnz = [int(v) for v in run(tool, "csr", path, idx, tmp_path / "c").split()]
+    indptr = np.fromfile(str(tmp_path / "c") + ".indptr", dtype=np.int64)
+    indices = np.fromfile(str(tmp_path / "c") + ".indices", dtype=np.int32)
+    values = np.fromfile(str(tmp_path / "c") + ".values", dtype=np.float32)
+    assert [D, N] == rg["b__header"][:2].tolist() and indptr.shape == (N + 1,) and indptr[-1] == nnz == len(indices)
+    for c in range(N):
+        seg = indices[indptr[c]:indptr[c + 1]]
+        assert np.all(np.diff(seg) > 0) and (len(seg) == 0 or (seg[0] >= 0 and seg[-1] < D))
+    # every triplet of the full-file block is in the CSR (last duplicate wins)
+    last = {}
+    for r, c, v in zip(rg["b__block_all_rows"], rg["b__block_all_cols"], rg["b__block_all_vals"]):
+        last[(int(c), int(r))] = v
+    assert len(last) == nnz
+    for (c, r), v in list(last.items())[::37]:
+        seg = indices[indptr[c]:indptr[c + 1]]
+        k = int(np.searchsorted(seg, r))
+        assert seg[k] == r and values[indptr[c] + k].view(np.uint32) == np.float32(v).view(np.uint32)
+
+
+def test_bgzf_writer_roundtrip(tool, rg, tmp_path):
+    txt = tmp_path / "m.mtx"
+    lines = ["%%MatrixMarket matrix coordinate integer general", "3 5 5", "1 1 2", "3 1 1", "2 3 7", "1 4 1.5e1", "3 5 4"]
+    txt.write_text("\n".join(lines) + "\n")
+    gz = tmp_path / "m.mtx.gz"
+    run(tool, "write", txt, gz)
+    assert gzip.open(gz, "rb").read().decode() == txt.read_text()           # valid multi-member gzip
+    assert run(tool, "header", gz).split("\n")[0] == "3 5 5"
+    # column 2 (0-based 1) is empty: the gap fill gives it the next column's offset (mmutil_index.hh:219-224)
+    tab = [int(v) for v in run(tool, "table", gz, tmp_path / "m.index").split()]
+    assert len(tab) == 5 and tab[1] == tab[2] and tab[0] < tab[2] < tab[3] < tab[4]
+
+
+def test_option_defaults_and_aliases(tool, tmp_path):
+    mtx = os.path.join(GOLDEN, FILES["a"])
+    kv = dict(ln.split(" ", 1) if " " in ln else (ln, "") for ln in run(tool, "opts", "--mtx", mtx, "--out", "o").splitlines())
+    # defaults: mmvae.hh:36-39, mmvae_alg.hh:19-23, nb.hh:58-61, vmf.hh:59-62
+    assert kv["rc"] == "0" and kv["idx"] == mtx + ".index" and kv["batch_size"] == "100"
+    assert (kv["kl_discount"], kv["kl_min"], kv["kl_max"]) == ("0.1", "0.01", "1")
+    assert (kv["lr"], kv["grad_clip"], kv["nboot"], kv["max_epoch"], kv["recording"]) == ("0.001", "1", "3", "101", "10")
+    assert (kv["mean_latent"], kv["overdispersion_encoding"], kv["overdispersion_latent"], kv["nb_relu"]) == ("2", "1", "1", "0")
+    assert (kv["latent"], kv["kappa_min"], kv["kappa_max"], kv["vmf_relu"]) == ("2", "0.1", "10", "0")
+    kv = dict(ln.split(" ", 1) if " " in ln else (ln, "") for ln in run(
+        tool, "opts", "--mtx", mtx, "--output", "o", "--batch", "64", "--cov", "c.mtx.gz", "--kl_min", "0.5",
+        "--learning_rate", "0.01", "--bootstrap", "5", "--epoch", "7", "--mean-encoding", "128,64", "--mean_decoding", "32",
+        "--mean_latent", "10", "--overdisp-encoding", "3", "--overdispersion-latent", "2", "--relu", "--encoding", "16,8",
+        "--latent", "4", "--kappa-max", "20", "--seed", "9", "--dtype", "bf16", "--train_all_layers").splitlines())
+    assert kv["out"] == "o" and kv["batch_size"] == "64" and kv["covar_mtx"] == "c.mtx.gz" and kv["covar_idx"] == "c.mtx.gz.index"
+    assert kv["kl_min"] == "0.5" and kv["lr"] == "0.01" and kv["nboot"] == "5" and kv["max_epoch"] == "7"
+    assert kv["mean_encoding"] == "128,64" and kv["mean_decoding"] == "32" and kv["mean_latent"] == "10"
+    assert kv["overdispersion_encoding"] == "3" and kv["overdispersion_latent"] == "2" and kv["nb_relu"] == "1"
+    assert kv["encoding"] == "16,8" and kv["latent"] == "4" and kv["kappa_max"] == "20" and kv["vmf_relu"] == "1"
+    assert kv["seed"] == "9" and kv["bf16"] == "1" and kv["train_all_layers"] == "1"
+    # missing --out fails like the reference (ERR_RET "need output file header")
+    p = subprocess.run([tool, "opts", "--mtx", mtx], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    assert "rc 1" in p.stdout and "need output file header" in p.stderr
