@@ -43,11 +43,13 @@ struct params_t {
     int M, N, K, ldc, ldcb;
     float beta;
     int relu;
+    int tma_epi;   // 0: register epilogue ; 1: TMA tile store ; 2: TMA reduce-add (beta = 1 or split-K)
 };
 
 template <bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(THREADS, 2)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, params_t p)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmC, params_t p)
 {
     extern __shared__ uint8_t smem_raw[];
     // SWIZZLE_128B operands need 1024-byte alignment
@@ -67,6 +69,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+        if (p.tma_epi) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmC) : "memory");
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) {
@@ -141,20 +144,51 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_wait(tfull, 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int e = warp - 4;                         // TMEM lanes [32e, 32e+32) = tile rows
+        if (p.tma_epi) {
+            // TMEM -> registers -> [32 x 32] fp32 boxes in shared memory (SWIZZLE_128B: conflict-free
+            // 16-byte stores) -> TMA tile store, or TMA reduce-add when the product accumulates
+            // (beta = 1, split-K): the read-modify-write happens in L2, no thread waits on a load.
+            uint8_t *boxes = smem + e * (BLOCK_N / 32) * 4096;      // operand stages are free now
+            for (int c = 0; c < BLOCK_N / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(32 * e) << 16) + (uint32_t)(32 * c), v);
+                uint8_t *box = boxes + c * 4096;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float f[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int col = n0 + 32 * c + 4 * j + q;
+                        f[q] = __uint_as_float(v[4 * j + q]);
+                        if (p.bias && blockIdx.z == 0 && col < p.N) f[q] += p.bias[col];
+                        if (p.relu) f[q] = fmaxf(f[q], 0.f);
+                    }
+                    *reinterpret_cast<float4 *>(box + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_float4(f[0], f[1], f[2], f[3]);
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+                for (int c = 0; c < BLOCK_N / 32; ++c) {
+                    const uint32_t src = smem_u32(boxes + c * 4096);
+                    const int c0 = n0 + 32 * c, c1 = m0 + 32 * e;
+                    if (c0 >= p.N || c1 >= p.M) continue;
+                    if (p.tma_epi == 2)
+                        asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%1, %2}], [%3];"
+                                     ::"l"(&tmC), "r"(c0), "r"(c1), "r"(src) : "memory");
+                    else
+                        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%1, %2}], [%3];"
+                                     ::"l"(&tmC), "r"(c0), "r"(c1), "r"(src) : "memory");
+                }
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            }
+            __syncwarp();
+        } else {
         float *tile = reinterpret_cast<float *>(smem) + e * (32 * 33);   // operand stages are free now
         for (int c = 0; c < BLOCK_N / 32; ++c) {
             uint32_t v[32];
-            const uint32_t taddr = tmem_base + ((uint32_t)(32 * e) << 16) + (uint32_t)(32 * c);
-            asm volatile(
-                "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-                  "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-                  "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                : "r"(taddr));
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            tmem_ld32(tmem_base + ((uint32_t)(32 * e) << 16) + (uint32_t)(32 * c), v);
 #pragma unroll
             for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = __uint_as_float(v[j]);
             __syncwarp();
@@ -176,6 +210,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
             }
             __syncwarp();
+        }
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
@@ -215,15 +250,15 @@ get_encode()
 // bf16 matrix stored row-major [outer x inner] with leading dimension ld (elements)
 int
 make_map(CUtensorMap *map, const void *base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
-         uint32_t box_outer)
+         uint32_t box_outer, bool f32 = false)
 {
     encode_tiled_fn enc = get_encode();
     MMV_CHECK(enc, "gemm_tc: cuTensorMapEncodeTiled is not available from this driver");
     cuuint64_t dims[2] = { inner, outer };
-    cuuint64_t strides[1] = { ld * 2 };
+    cuuint64_t strides[1] = { ld * (f32 ? 4 : 2) };
     cuuint32_t box[2] = { box_inner, box_outer };
     cuuint32_t estr[2] = { 1, 1 };
-    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
+    CUresult r = enc(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     MMV_CHECK(r == CUDA_SUCCESS, "gemm_tc: cuTensorMapEncodeTiled failed (%d): inner=%lu outer=%lu ld=%lu", (int)r,
@@ -274,7 +309,15 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
             if (g.beta == 0.f) MMV_CUDA(cudaMemsetAsync(g.C, 0, sizeof(float) * (size_t)g.M * g.N, stream));
         }
     }
-    void (*kern)(const CUtensorMap, const CUtensorMap, params_t) =
+    // epilogue through TMA when C can be described by a tensor map and no bf16 copy is wanted
+    CUtensorMap tc_map = ta;
+    p.tma_epi = 0;
+    if (g.C && !g.Cb && g.ldc % 4 == 0 && (reinterpret_cast<uintptr_t>(g.C) & 15) == 0 &&
+        (g.beta == 0.f || g.beta == 1.f) && !(g.relu && (g.beta == 1.f || grid.z > 1))) {
+        MMV_TRY(make_map(&tc_map, g.C, g.N, g.M, g.ldc, 32, 32, true));
+        p.tma_epi = (g.beta == 1.f || grid.z > 1) ? 2 : 1;
+    }
+    void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, params_t) =
         g.a_mn ? (g.b_mn ? gemm_tc_kernel<true, true> : gemm_tc_kernel<true, false>)
                : (g.b_mn ? gemm_tc_kernel<false, true> : gemm_tc_kernel<false, false>);
     static bool attr_set[4] = { false, false, false, false };
@@ -283,7 +326,7 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
         MMV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         attr_set[vi] = true;
     }
-    kern<<<grid, THREADS, SMEM_BYTES, stream>>>(ta, tb, p);
+    kern<<<grid, THREADS, SMEM_BYTES, stream>>>(ta, tb, tc_map, p);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
