@@ -69,6 +69,7 @@ mmv_ctx_create(int device, mmv_ctx **out)
     c->device = device;
     c->num_sms = prop.multiProcessorCount;
     MMV_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    MMV_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     MMV_CUDA(cudaEventCreate(&c->ev0));
     MMV_CUDA(cudaEventCreate(&c->ev1));
     *out = c;
@@ -85,6 +86,7 @@ mmv_ctx_destroy(mmv_ctx *c)
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
     cudaStreamDestroy(c->stream);
+    cudaStreamDestroy(c->copy_stream);
     delete c;
     return 0;
 }
@@ -102,6 +104,7 @@ mmv_ctx_sync(mmv_ctx *c)
 {
     MMV_CHECK(c, "mmv_ctx_sync: NULL ctx");
     MMV_CUDA(cudaSetDevice(c->device));
+    MMV_CUDA(cudaStreamSynchronize(c->copy_stream));
     MMV_CUDA(cudaStreamSynchronize(c->stream));
     return 0;
 }
@@ -167,9 +170,8 @@ csr_check_sorted_kernel(const int64_t *indptr, const int32_t *indices, int64_t n
 }
 
 static int
-csr_check_sorted(mmv_csr *s)
+csr_check_sorted(mmv_csr *s, cudaStream_t st)
 {
-    cudaStream_t st = s->ctx->stream;
     if (!s->d_unsorted) MMV_CUDA(cudaMalloc(&s->d_unsorted, sizeof(int)));
     MMV_CUDA(cudaMemsetAsync(s->d_unsorted, 0, sizeof(int), st));
     if (s->nnz == 0) return 0;
@@ -233,8 +235,19 @@ csr_update_impl(mmv_csr *s, int64_t n_cells, const int64_t *indptr, const int32_
     MMV_CHECK(nnz <= s->cap_nnz, "mmv_csr_update: %ld nonzeros exceed capacity %ld", (long)nnz, (long)s->cap_nnz);
     int64_t mx = 0;
     MMV_TRY(csr_validate(n_cells, s->n_genes, indptr, indices, &mx, check_indices));
-    cudaStream_t st = s->ctx->stream;
+    // streaming updates (mmv_csr_update) go through the copy stream: they wait for the last step that
+    // read this slot and overlap whatever the ctx stream is running on another slot
+    const bool streaming = !check_indices;
+    cudaStream_t st = streaming ? s->ctx->copy_stream : s->ctx->stream;
     MMV_CUDA(cudaSetDevice(s->ctx->device));
+    if (streaming) {
+        if (!s->ev_ready) {
+            MMV_CUDA(cudaEventCreateWithFlags(&s->ev_ready, cudaEventDisableTiming));
+            MMV_CUDA(cudaEventCreateWithFlags(&s->ev_consumed, cudaEventDisableTiming));
+            MMV_CUDA(cudaEventRecord(s->ev_consumed, s->ctx->stream));
+        }
+        MMV_CUDA(cudaStreamWaitEvent(st, s->ev_consumed, 0));
+    }
     MMV_CUDA(cudaMemcpyAsync(s->indptr, indptr, sizeof(int64_t) * (n_cells + 1), cudaMemcpyHostToDevice, st));
     if (nnz > 0) {
         MMV_CUDA(cudaMemcpyAsync(s->indices, indices, sizeof(int32_t) * nnz, cudaMemcpyHostToDevice, st));
@@ -249,7 +262,9 @@ csr_update_impl(mmv_csr *s, int64_t n_cells, const int64_t *indptr, const int32_
     s->nnz = nnz;
     if (mx > s->max_row_nnz) s->max_row_nnz = mx;
     s->h2d_bytes = sizeof(int64_t) * (n_cells + 1) + 8 * nnz + (covar ? sizeof(float) * n_cells * s->c_dim : 0);
-    return csr_check_sorted(s);
+    MMV_TRY(csr_check_sorted(s, st));
+    if (streaming) MMV_CUDA(cudaEventRecord(s->ev_ready, st));
+    return 0;
 }
 
 // Streaming path: gene ids are range-checked once per resident upload only; a
@@ -302,7 +317,7 @@ mmv_csr_wrap_device(mmv_ctx *ctx, int64_t n_cells, int64_t n_genes, int64_t nnz,
     s->has_cov = d_covar != nullptr;
     s->c_dim = d_covar ? c_dim : (c_dim > 0 ? c_dim : 1);
     MMV_CUDA(cudaSetDevice(ctx->device));
-    if (csr_check_sorted(s) != 0) {
+    if (csr_check_sorted(s, ctx->stream) != 0) {
         delete s;
         return 1;
     }
@@ -315,6 +330,7 @@ mmv_csr_destroy(mmv_csr *s)
 {
     if (!s) return 0;
     cudaSetDevice(s->ctx->device);
+    cudaStreamSynchronize(s->ctx->copy_stream);
     cudaStreamSynchronize(s->ctx->stream);
     if (!s->borrowed) {
         cudaFree(s->indptr);
@@ -323,6 +339,8 @@ mmv_csr_destroy(mmv_csr *s)
         cudaFree(s->cov);
     }
     cudaFree(s->d_unsorted);
+    if (s->ev_ready) cudaEventDestroy(s->ev_ready);
+    if (s->ev_consumed) cudaEventDestroy(s->ev_consumed);
     delete s;
     return 0;
 }

@@ -14,6 +14,7 @@ struct mmv_ctx {
     int num_sms = 148;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaStream_t copy_stream = nullptr;   // mmv_csr_update copies here, so minibatch k+1 uploads while step k runs
     // NCCL data-parallel state (comm.cu)
     void *nccl_comm = nullptr;
     int nranks = 1, rank = 0;
@@ -30,6 +31,8 @@ struct mmv_csr {
     bool has_cov = false;
     bool borrowed = false;     // device arrays owned by the caller (mmv_csr_wrap_device)
     size_t h2d_bytes = 0;      // bytes copied by the last update (bench accounting)
+    cudaEvent_t ev_ready = nullptr;     // streamed slot: recorded on the copy stream after an update
+    cudaEvent_t ev_consumed = nullptr;  // recorded on the ctx stream after the last step that read the slot
     int *d_unsorted = nullptr; // device flag: 1 if some cell's gene ids are not strictly increasing (set on the
                                // ctx stream by every upload / update / wrap; kernels that bisect rows read it)
 };

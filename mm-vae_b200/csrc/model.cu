@@ -1276,6 +1276,7 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         s.m = m; s.csr = csr; s.B = (int)B; s.cov = csr->has_cov ? csr->cov : nullptr;
         s.klw = kl_weight; s.inv_B = 1.f / (float)(B * nranks); s.bwd = (flags & MMV_BWD) != 0; s.st = st;
         MMV_TRY(stage_inputs(m, csr, cells, B, boot_idx, eps, flags, s));
+        if (csr->ev_ready) MMV_CUDA(cudaStreamWaitEvent(st, csr->ev_ready, 0));   // streamed slot: its upload is done
         m->last_B = B;
         m->bf_cache.clear();
         if (m->use_tc && m->bf16_dirty) {
@@ -1286,6 +1287,7 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         if (s.bwd)   // adam.zero_grad() reaches the optimiser's tensors only (mmvae_alg.hh:306)
             MMV_CUDA(cudaMemsetAsync(m->grads, 0, sizeof(float) * n_opt, st));
         MMV_TRY(m->is_vmf ? vmf_forward_backward(s) : nb_forward_backward(s));
+        if (csr->ev_consumed) MMV_CUDA(cudaEventRecord(csr->ev_consumed, st));   // the slot may be refilled from here on
     } else {
         MMV_CUDA(cudaMemsetAsync(m->acc + 3, 0, sizeof(double), st));
     }
@@ -1408,6 +1410,7 @@ mmv_encode(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, float *m
     step_t s;
     s.m = m; s.csr = csr; s.B = (int)B; s.cov = nullptr; s.klw = 0.f; s.inv_B = 1.f / (float)B; s.bwd = false; s.st = st;
     MMV_TRY(stage_inputs(m, csr, cells, B, nullptr, nullptr, 0, s));
+    if (csr->ev_ready) MMV_CUDA(cudaStreamWaitEvent(st, csr->ev_ready, 0));
     m->last_B = B;
     m->bf_cache.clear();
     if (m->use_tc && m->bf16_dirty) {
