@@ -75,6 +75,25 @@ comm_allreduce_f32(mmv_ctx *ctx, float *buf, size_t n)
 }
 
 int
+comm_allreduce_f32_async(mmv_ctx *ctx, float *buf, size_t n)
+{
+    if (ctx->nranks <= 1 || n == 0) return 0;
+    MMV_CUDA(cudaEventRecord(ctx->ev_fork, ctx->stream));
+    MMV_CUDA(cudaStreamWaitEvent(ctx->comm_stream, ctx->ev_fork, 0));
+    MMV_NCCL(g_nccl.AllReduce(buf, buf, n, ncclFloat32, ncclSum, (ncclComm_t)ctx->nccl_comm, ctx->comm_stream));
+    MMV_CUDA(cudaEventRecord(ctx->ev_join, ctx->comm_stream));
+    return 0;
+}
+
+int
+comm_join(mmv_ctx *ctx)
+{
+    if (ctx->nranks <= 1) return 0;
+    MMV_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
+    return 0;
+}
+
+int
 comm_allreduce_f64(mmv_ctx *ctx, double *buf, size_t n)
 {
     if (ctx->nranks <= 1 || n == 0) return 0;
@@ -111,6 +130,10 @@ mmv_comm_init(mmv_ctx *ctx, int nranks, int rank, const unsigned char id[128])
     ncclComm_t comm = nullptr;
     MMV_NCCL(g_nccl.CommInitRank(&comm, nranks, u, rank));
     ctx->nccl_comm = comm;
+    MMV_CUDA(cudaStreamCreateWithFlags(&ctx->comm_stream, cudaStreamNonBlocking));
+    MMV_CUDA(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+    MMV_CUDA(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+    MMV_CUDA(cudaEventRecord(ctx->ev_join, ctx->comm_stream));
     ctx->nranks = nranks;
     ctx->rank = rank;
     return 0;
@@ -122,7 +145,12 @@ mmv_comm_destroy(mmv_ctx *ctx)
     if (!ctx || !ctx->nccl_comm) return 0;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    cudaStreamSynchronize(ctx->comm_stream);
     g_nccl.CommDestroy((ncclComm_t)ctx->nccl_comm);
+    cudaStreamDestroy(ctx->comm_stream);
+    cudaEventDestroy(ctx->ev_fork);
+    cudaEventDestroy(ctx->ev_join);
+    ctx->comm_stream = nullptr;
     ctx->nccl_comm = nullptr;
     ctx->nranks = 1;
     ctx->rank = 0;

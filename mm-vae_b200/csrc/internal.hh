@@ -17,6 +17,8 @@ struct mmv_ctx {
     cudaStream_t copy_stream = nullptr;   // mmv_csr_update copies here, so minibatch k+1 uploads while step k runs
     // NCCL data-parallel state (comm.cu)
     void *nccl_comm = nullptr;
+    cudaStream_t comm_stream = nullptr;          // early gradient buckets are reduced here, under the rest of backward
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int nranks = 1, rank = 0;
 };
 
@@ -42,5 +44,9 @@ namespace mmv {
 // comm.cu: sum-reduce over ranks on the ctx stream (no-ops when nranks == 1)
 int comm_allreduce_f32(mmv_ctx *ctx, float *buf, size_t n);
 int comm_allreduce_f64(mmv_ctx *ctx, double *buf, size_t n);
+// bucketed overlap: reduce buf[0, n) on the comm stream once everything queued so far on the ctx stream
+// has finished; comm_join makes the ctx stream wait for it
+int comm_allreduce_f32_async(mmv_ctx *ctx, float *buf, size_t n);
+int comm_join(mmv_ctx *ctx);
 
 } // namespace mmv

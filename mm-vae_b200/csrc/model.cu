@@ -99,6 +99,7 @@ struct mmv_model {
     size_t n_reg = 0, n_all = 0;          // floats in the registered prefix / whole buffer
     float *params = nullptr, *grads = nullptr, *adam_m = nullptr, *adam_v = nullptr;
     int64_t adam_t = 0;
+    size_t early_off = 0, early_n = 0;   // gradient range already handed to the comm stream this step
 
     std::vector<linear_t> enc, dec;       // enc[0] = sparse first layer; dec.back() = layer onto D genes
     int t_x_mean = -1, t_ln_x_sd = -1, t_mu_bias = -1, t_nu_bias = -1, t_ln_kappa = -1;
@@ -575,6 +576,7 @@ struct step_t {
     const float *eps_mu, *eps_nu;   // device or nullptr
     float klw, inv_B;
     bool bwd;
+    bool optim = false;     // this step ends with allreduce + clip + Adam
     cudaStream_t st;
 };
 
@@ -759,6 +761,12 @@ decoder_backward(const step_t &s)
         MMV_TRY(lin_bwd_weight(s, dY, L.out, X, L.in, m->want_grad(L.w) ? m->G(L.w) : nullptr,
                                (!last && m->want_grad(L.b)) ? m->G(L.b) : nullptr, 1.f,
                                last ? "gemm_dec_last_dw" : "gemm_other", dY_bf));
+        if (last && s.optim && m->ctx->nranks > 1 && m->optimised(L.w)) {
+            // first bucket: the largest gradient is complete long before backward ends — reduce it under the rest
+            m->early_off = m->tensors[L.w].off;
+            m->early_n = m->tensors[L.w].numel();
+            MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + m->early_off, m->early_n));
+        }
         float *dX = l == 0 ? WS("dz", (size_t)B * R) : WS("d_dec" + std::to_string(l - 1), (size_t)B * L.in);
         NEED(dX);
         MMV_TRY(lin_bwd_data(s, dY, L.out, m->P(L.w), L.in, dX, last ? "gemm_dec_last_dx" : "gemm_other", dY_bf));
@@ -1275,6 +1283,8 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         step_t s;
         s.m = m; s.csr = csr; s.B = (int)B; s.cov = csr->has_cov ? csr->cov : nullptr;
         s.klw = kl_weight; s.inv_B = 1.f / (float)(B * nranks); s.bwd = (flags & MMV_BWD) != 0; s.st = st;
+        s.optim = (flags & MMV_OPTIM) != 0;
+        m->early_off = m->early_n = 0;
         MMV_TRY(stage_inputs(m, csr, cells, B, boot_idx, eps, flags, s));
         if (csr->ev_ready) MMV_CUDA(cudaStreamWaitEvent(st, csr->ev_ready, 0));   // streamed slot: its upload is done
         m->last_B = B;
@@ -1296,7 +1306,15 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
     if (flags & MMV_OPTIM) {
         {
             PROF("allreduce");
-            MMV_TRY(comm_allreduce_f32(m->ctx, m->grads, n_opt));
+            if (m->early_n > 0) {   // everything but the bucket already in flight, then wait for it
+                MMV_TRY(comm_allreduce_f32(m->ctx, m->grads, m->early_off));
+                const size_t tail = m->early_off + m->early_n;
+                if (tail < n_opt) MMV_TRY(comm_allreduce_f32(m->ctx, m->grads + tail, n_opt - tail));
+                MMV_TRY(comm_join(m->ctx));
+                m->early_off = m->early_n = 0;
+            } else {
+                MMV_TRY(comm_allreduce_f32(m->ctx, m->grads, n_opt));
+            }
         }
         PROF("clip_adam");
         MMV_TRY(launch_sumsq(m->grads, n_opt, m->acc + 3, m->ctx->num_sms, st));

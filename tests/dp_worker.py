@@ -1,0 +1,106 @@
+"""Data-parallel worker (launched by torchrun from test_gpu_multi.py, or with --cpu from test_dist_cpu.py).
+
+GPU mode: rank r steps on ITS shard of a global batch with injected noise; with the NCCL allreduce inside
+mmv_step the post-Adam parameters of every rank must equal a single-GPU step on the concatenated batch
+(SURVEY 8e pin: sum-order tolerance), and the replicas must be bit-identical to each other.
+CPU mode (--cpu, gloo): only the host-side plumbing bench.py uses for N > 1 — cell sharding, unique-id
+broadcast, max-over-ranks timing — no compute.
+"""
+import importlib
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def shard_range(n_cells, world, rank):
+    """Contiguous cell range of a rank: [rank * n / world, (rank + 1) * n / world)."""
+    return rank * n_cells // world, (rank + 1) * n_cells // world
+
+
+def main_cpu():
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    box = [bytes(range(128)) if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    assert box[0] == bytes(range(128))
+    lo, hi = shard_range(1001, world, rank)
+    cover = [None] * world
+    dist.all_gather_object(cover, (lo, hi))
+    assert cover[0][0] == 0 and cover[-1][1] == 1001 and all(cover[i][1] == cover[i + 1][0] for i in range(world - 1))
+    t = torch.tensor([1.0 + rank, 10.0 - rank])
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    assert t.tolist() == [float(world), 10.0]
+    dist.barrier()
+    dist.destroy_process_group()
+    print(f"rank {rank} ok")
+
+
+def main_gpu():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    mmv = importlib.import_module("mm-vae_b200")
+    D, Bl, R = 512, 96, 8
+    B = Bl * world
+    rng = np.random.default_rng(5)                       # same global data on every rank
+    x = (rng.random((B, D)) < 0.08) * rng.integers(1, 6, (B, D))
+    x = x.astype(np.float32)
+    x[:, 0] = 1.0
+    eps_mu, eps_nu = rng.standard_normal((B, R)).astype(np.float32), rng.standard_normal((B, 1)).astype(np.float32)
+
+    def make(ctx):
+        m = mmv.Model.nb(ctx, D, 1, [64], [64], R, 1, 1, seed=3)
+        m.set_option("train_all_layers", 1)
+        m.set_option("dtype", int(os.environ.get("DP_BF16", "0")))
+        return m
+
+    flags = mmv.FWD | mmv.BWD | mmv.OPTIM
+    # ---- distributed: this rank's rows
+    ctx = mmv.Context(local)
+    box = [mmv.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    ctx.comm_init(world, rank, box[0])
+    lo, hi = shard_range(B, world, rank)
+    csr = mmv.CSR.from_dense(ctx, x[lo:hi], None)
+    m = make(ctx)
+    for _ in range(3):
+        eps = np.concatenate([eps_mu[lo:hi].ravel(), eps_nu[lo:hi].ravel()])
+        terms = m.step(csr, np.arange(hi - lo), eps=eps, kl_weight=0.7, flags=flags)
+    names = list(m.param_info())
+    dist_params = {k: m.get_param(k) for k in names}
+    # replicas bit-identical
+    for k in ("mu_decoding.weight", "mu_encoding_1.weight", "x_mean"):
+        t = torch.from_numpy(dist_params[k].copy()).cuda()
+        ref = t.clone()
+        dist.broadcast(ref, src=0)
+        assert torch.equal(t, ref), f"replicas diverged on {k}"
+    # ---- single GPU on the concatenated batch (own context without a communicator)
+    ctx1 = mmv.Context(local)
+    csr1 = mmv.CSR.from_dense(ctx1, x, None)
+    m1 = make(ctx1)
+    for _ in range(3):
+        eps = np.concatenate([eps_mu.ravel(), eps_nu.ravel()])
+        terms1 = m1.step(csr1, np.arange(B), eps=eps, kl_weight=0.7, flags=flags)
+    tol = 2e-2 if os.environ.get("DP_BF16", "0") == "1" else 2e-5
+    assert abs(terms["loss"] - terms1["loss"]) <= tol * abs(terms1["loss"]), (terms, terms1)
+    worst = 0.0
+    for k in names:
+        a, b = dist_params[k], m1.get_param(k)
+        den = np.linalg.norm(b) + 1e-12
+        worst = max(worst, float(np.linalg.norm(a - b) / den))
+    assert worst <= tol, f"data-parallel parameters differ from the single-GPU step: {worst}"
+    dist.barrier()
+    if rank == 0:
+        print(f"dp ok: world {world}, loss {terms['loss']:.6f} vs {terms1['loss']:.6f}, worst rel param diff {worst:.2e}")
+    m.close(); m1.close(); csr.close(); csr1.close(); ctx.close(); ctx1.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main_cpu() if "--cpu" in sys.argv else main_gpu()
