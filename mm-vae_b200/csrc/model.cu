@@ -125,10 +125,13 @@ struct mmv_model {
     float *fscal = nullptr;               // device: [0] kappa, [1] grad norm
     double *h_acc = nullptr;              // pinned mirrors
     float *h_fscal = nullptr;
-    int32_t *h_cells = nullptr;           // pinned staging
-    float *h_eps = nullptr;
-    size_t h_eps_cap = 0;
-    int64_t h_cells_cap = 0;
+    // pinned staging, two slots: the host prepares step k+1 while step k runs (no stream sync per step)
+    int32_t *h_cells[2] = { nullptr, nullptr };
+    float *h_eps[2] = { nullptr, nullptr };
+    size_t h_eps_cap[2] = { 0, 0 };
+    int64_t h_cells_cap[2] = { 0, 0 };
+    cudaEvent_t ev_stage[2] = { nullptr, nullptr };
+    unsigned stage_i = 0;
 
     // profiling (cudaEvent pairs per kernel group, read by mmv_profile_read)
     bool profile = false;
@@ -421,8 +424,11 @@ mmv_model_destroy(mmv_model *m)
     cudaFree(m->params); cudaFree(m->grads); cudaFree(m->adam_m); cudaFree(m->adam_v);
     cudaFree(m->acc); cudaFree(m->fscal); cudaFree(m->params_bf16);
     cudaFreeHost(m->h_acc); cudaFreeHost(m->h_fscal);
-    if (m->h_cells) cudaFreeHost(m->h_cells);
-    if (m->h_eps) cudaFreeHost(m->h_eps);
+    for (int i = 0; i < 2; ++i) {
+        if (m->h_cells[i]) cudaFreeHost(m->h_cells[i]);
+        if (m->h_eps[i]) cudaFreeHost(m->h_eps[i]);
+        if (m->ev_stage[i]) cudaEventDestroy(m->ev_stage[i]);
+    }
     for (auto &kv : m->ws) kv.second.release();
     delete m;
     return 0;
@@ -1210,13 +1216,16 @@ stage_inputs(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const 
              const float *eps, int flags, step_t &s)
 {
     cudaStream_t st = m->ctx->stream;
-    // staging buffers are reused: wait until the previous step's copies were consumed
-    MMV_CUDA(cudaStreamSynchronize(st));
-    if (m->h_cells_cap < B) {
-        if (m->h_cells) cudaFreeHost(m->h_cells);
-        MMV_CUDA(cudaMallocHost(&m->h_cells, sizeof(int32_t) * B));
-        m->h_cells_cap = B;
+    // staging slot: reused every second step; wait only for the copies issued from it two steps ago
+    const int slot = (int)(m->stage_i++ & 1u);
+    if (!m->ev_stage[slot]) MMV_CUDA(cudaEventCreateWithFlags(&m->ev_stage[slot], cudaEventDisableTiming));
+    else MMV_CUDA(cudaEventSynchronize(m->ev_stage[slot]));
+    if (m->h_cells_cap[slot] < B) {
+        if (m->h_cells[slot]) cudaFreeHost(m->h_cells[slot]);
+        MMV_CUDA(cudaMallocHost(&m->h_cells[slot], sizeof(int32_t) * B));
+        m->h_cells_cap[slot] = B;
     }
+    int32_t *h_cells = m->h_cells[slot];
     for (int64_t r = 0; r < B; ++r) {   // bootstrap = index composition (mmvae_alg.hh:292-301)
         int64_t pos = r;
         if (boot_idx) {
@@ -1226,11 +1235,11 @@ stage_inputs(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const 
         const int64_t cell = cells ? cells[pos] : pos;
         MMV_CHECK(cell >= 0 && cell < csr->n_cells, "mmv_step: cell id %ld out of range [0,%ld)", (long)cell,
                   (long)csr->n_cells);
-        m->h_cells[r] = (int32_t)cell;
+        h_cells[r] = (int32_t)cell;
     }
     int32_t *d_cells = (int32_t *)m->W("cells", sizeof(int32_t) * B);
     NEED(d_cells);
-    MMV_CUDA(cudaMemcpyAsync(d_cells, m->h_cells, sizeof(int32_t) * B, cudaMemcpyHostToDevice, st));
+    MMV_CUDA(cudaMemcpyAsync(d_cells, h_cells, sizeof(int32_t) * B, cudaMemcpyHostToDevice, st));
     s.cells = d_cells;
 
     const size_t n_mu = (size_t)B * m->R, n_nu = m->is_vmf ? 0 : (size_t)B * m->Rnu;
@@ -1239,13 +1248,13 @@ stage_inputs(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const 
         float *d_eps = m->W("eps", sizeof(float) * (n_mu + n_nu));
         NEED(d_eps);
         if (eps) {
-            if (m->h_eps_cap < n_mu + n_nu) {
-                if (m->h_eps) cudaFreeHost(m->h_eps);
-                MMV_CUDA(cudaMallocHost(&m->h_eps, sizeof(float) * (n_mu + n_nu)));
-                m->h_eps_cap = n_mu + n_nu;
+            if (m->h_eps_cap[slot] < n_mu + n_nu) {
+                if (m->h_eps[slot]) cudaFreeHost(m->h_eps[slot]);
+                MMV_CUDA(cudaMallocHost(&m->h_eps[slot], sizeof(float) * (n_mu + n_nu)));
+                m->h_eps_cap[slot] = n_mu + n_nu;
             }
-            memcpy(m->h_eps, eps, sizeof(float) * (n_mu + n_nu));
-            MMV_CUDA(cudaMemcpyAsync(d_eps, m->h_eps, sizeof(float) * (n_mu + n_nu), cudaMemcpyHostToDevice, st));
+            memcpy(m->h_eps[slot], eps, sizeof(float) * (n_mu + n_nu));
+            MMV_CUDA(cudaMemcpyAsync(d_eps, m->h_eps[slot], sizeof(float) * (n_mu + n_nu), cudaMemcpyHostToDevice, st));
         } else {
             static uint64_t draw = 0;
             normal_kernel<<<(int)min_sz((n_mu + n_nu + 255) / 256, 1024), 256, 0, st>>>(d_eps, n_mu + n_nu, m->seed + 77,
@@ -1255,6 +1264,7 @@ stage_inputs(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const 
         s.eps_mu = d_eps;
         s.eps_nu = n_nu ? d_eps + n_mu : nullptr;
     }
+    MMV_CUDA(cudaEventRecord(m->ev_stage[slot], st));
     return 0;
 }
 

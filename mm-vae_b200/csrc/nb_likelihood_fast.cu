@@ -150,33 +150,24 @@ __global__ void
 slice_bounds_kernel(const int64_t *indptr, const int32_t *indices, const int32_t *cells, const int *unsorted, int B,
                     int cs, int Ds, int64_t *bounds)
 {
-    const int lane = threadIdx.x & 31;
-    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    // one thread per (row, boundary): lower_bound of c * Ds in the cell's sorted gene ids
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int row = t / (cs + 1), c = t % (cs + 1);
     if (row >= B) return;
     const int64_t cell = cells ? (int64_t)cells[row] : (int64_t)row;
     const int64_t beg = indptr[cell], end = indptr[cell + 1];
     const bool sorted = unsorted != nullptr && *unsorted == 0;
-    int cnt[8];
-#pragma unroll
-    for (int c = 0; c < 8; ++c) cnt[c] = 0;
-    if (sorted)
-        for (int64_t q = beg + lane; q < end; q += 32) {
-            const int j = indices[q];
-#pragma unroll
-            for (int c = 1; c < 8; ++c) cnt[c] += (c < cs && j < c * Ds) ? 1 : 0;
+    int64_t v = c == 0 ? beg : end;                          // unsorted: every slice scans the whole run
+    if (sorted && c > 0 && c < cs) {
+        const int key = c * Ds;
+        int64_t lo = beg, hi = end;
+        while (lo < hi) {
+            const int64_t mid = (lo + hi) >> 1;
+            if (indices[mid] < key) lo = mid + 1; else hi = mid;
         }
-#pragma unroll
-    for (int c = 1; c < 8; ++c) cnt[c] = __reduce_add_sync(0xffffffffu, cnt[c]);
-    if (lane == 0) {
-        int64_t *b = bounds + (size_t)row * (cs + 1);
-#pragma unroll
-        for (int c = 0; c <= 8; ++c) {
-            if (c > cs) break;
-            int64_t v = c == 0 ? beg : end;                  // unsorted: every slice scans the whole run
-            if (sorted && c > 0 && c < cs) v = beg + cnt[c < 8 ? c : 7];
-            b[c] = v;
-        }
+        v = lo;
     }
+    bounds[(size_t)row * (cs + 1) + c] = v;
 }
 
 template <int EPT>
@@ -477,8 +468,7 @@ launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stre
         MMV_CHECK(cs < 8, "nb_likelihood: D=%d does not fit a cluster of 8 CTAs", a.D);
     }
     {
-        const int warps_per_cta = 8;
-        slice_bounds_kernel<<<ceil_div(a.B, warps_per_cta), 32 * warps_per_cta, 0, stream>>>(
+        slice_bounds_kernel<<<ceil_div((int64_t)a.B * (cs + 1), 256), 256, 0, stream>>>(
             a.indptr, a.indices, a.cells, a.unsorted, a.B, cs, Ds, a.slice_bounds);
         ::mmv::count_launch();
         MMV_CUDA(cudaGetLastError());
