@@ -42,12 +42,31 @@ rcp_f(float x)
     return r;
 }
 
-// log(1 + y), y >= 0: Taylor polynomial on the FMA pipe below 1/16, MUFU lg2 above
+constexpr float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
+
+__device__ __forceinline__ float
+ex2_f(float x)
+{
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+__device__ __forceinline__ float
+lg2_f(float x)
+{
+    float r;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// log(1 + y), y >= 0: Taylor polynomial on the FMA pipe below 1/16 (where log1p(y) - y / (1 + y)
+// cancels and lg2.approx's absolute error near 1 would dominate), MUFU lg2 above
 __device__ __forceinline__ float
 log1p_fast(float y)
 {
-    const float poly = y * (1.f - y * (0.5f - y * (0.33333334f - y * (0.25f - y * (0.2f - y * 0.16666667f)))));
-    const float big = __logf(1.f + y);
+    const float poly = y * (1.f - y * (0.5f - y * (0.33333334f - y * (0.25f - y * 0.2f))));
+    const float big = lg2_f(1.f + y) * kLn2;
     return y < 0.0625f ? poly : big;
 }
 
@@ -55,20 +74,27 @@ struct elem_t {
     float m, nu, l1p, inv_mnu, sig_mask;
 };
 
+// u2 = u * log2(e): the per-gene nu weights are staged pre-scaled so that exp(u) is one ex2.
+// 6 MUFU: ex2, rcp(1 + t), lg2(1 + t), rcp(nu (m + nu)), lg2(1 + m / nu) (+ the softmax ex2 outside).
 __device__ __forceinline__ elem_t
-elem_fast(float p, float depth, float u)
+elem_fast(float p, float depth, float u2)
 {
     elem_t e;
     e.m = fmaf(p, depth, kEps);                                  // nb.hh:519
-    const float uc = fminf(u, 20.f);
-    const float t = __expf(uc);
-    const float sp = u > 20.f ? u : log1p_fast(t);               // softplus, threshold 20 (nb.hh:458)
+    const bool big = u2 > 20.f * kLog2e;                         // softplus threshold 20 (nb.hh:458)
+    const float t = ex2_f(fminf(u2, 20.f * kLog2e));
+    const float w = 1.f + t, rw = rcp_f(w);
+    // log1p(t) = log(w) + (t - (w - 1)) / w : the second term restores what rounding 1 + t lost
+    float sp = fmaf(lg2_f(w), kLn2, (t - (w - 1.f)) * rw);
+    sp = big ? u2 * kLn2 : sp;
     const float r = fminf(fmaxf(sp, kNuMin), kNuMax);            // nb.hh:459
     e.nu = r + kEps;                                             // nb.hh:518
-    const float sig = u > 20.f ? 1.f : 1.f - rcp_f(1.f + t);     // d softplus / du
-    e.sig_mask = (sp >= kNuMin && sp <= kNuMax) ? sig : 0.f;     // clamp passes the gradient inside
-    e.l1p = log1p_fast(e.m * rcp_f(e.nu));                       // log(m + nu) - log(nu)
-    e.inv_mnu = rcp_f(e.m + e.nu);
+    const float sig = big ? 1.f : t * rw;                        // d softplus / du
+    e.sig_mask = r == sp ? sig : 0.f;                            // clamp passes the gradient inside [min, max]
+    const float mnu = e.m + e.nu;
+    const float q = rcp_f(e.nu * mnu);                           // one MUFU for both reciprocals
+    e.inv_mnu = q * e.nu;
+    e.l1p = log1p_fast(e.m * (q * mnu));                         // log(m + nu) - log(nu)
     return e;
 }
 
@@ -206,8 +232,8 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         if (jj < nj) {
             ab = a.abias[j];
             for (int c = 0; c < a.C; ++c) ab += a.Wcd[(size_t)j * a.C + c];   // covariates are all ones on this path
-            ub = a.ubias[j];
-            wn = a.Wnd[j];
+            ub = a.ubias[j] * kLog2e;   // pre-scaled: u * log2(e) = zn * wn' + ub'
+            wn = a.Wnd[j] * kLog2e;
         }
         s_ab[jj] = ab;
         s_ub[jj] = ub;
@@ -383,7 +409,7 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
             if (lane == 0) { ws[warp * 4 + 2] = red[0]; ws[warp * 4 + 3] = red[1]; }
             __syncthreads();                   // also: every s_g fix is visible
             float s = warp_sum(lane < NW ? ws[lane * 4 + 2] : 0.f);
-            float dz = warp_sum(lane < NW ? ws[lane * 4 + 3] : 0.f);
+            float dz = warp_sum(lane < NW ? ws[lane * 4 + 3] : 0.f) * kLn2;   // red[1] was accumulated against wn * log2(e)
             if (cs > 1) {
                 if (tid == 0) xchg_send(smem_addr(xs + 16 + rank * 2), xb + 8, cs, s, dz);
                 bar_wait(xb + 8, ph);
