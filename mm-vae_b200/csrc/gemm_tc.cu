@@ -164,6 +164,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         if (p.relu) f[q] = fmaxf(f[q], 0.f);
                     }
                     *reinterpret_cast<float4 *>(box + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_float4(f[0], f[1], f[2], f[3]);
+                    if (p.Cb) {   // bf16 copy for the next tensor-core GEMM, straight from the registers
+                        const int row = m0 + 32 * e + lane, col = n0 + 32 * c + 4 * j;
+                        if (row < p.M && col < p.N) {   // N % 4 == 0 (launcher)
+                            const __nv_bfloat162 lo = __floats2bfloat162_rn(f[0], f[1]), hi = __floats2bfloat162_rn(f[2], f[3]);
+                            uint2 pk;
+                            pk.x = *reinterpret_cast<const uint32_t *>(&lo);
+                            pk.y = *reinterpret_cast<const uint32_t *>(&hi);
+                            *reinterpret_cast<uint2 *>(p.Cb + (size_t)row * p.ldcb + col) = pk;
+                        }
+                    }
                 }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -275,6 +285,13 @@ make_tma_map_bf16(void *map, const void *base, uint64_t inner, uint64_t outer, u
     return make_map(reinterpret_cast<CUtensorMap *>(map), base, inner, outer, ld, box_inner, box_outer);
 }
 
+int
+make_tma_map_f32(void *map, const void *base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+                 uint32_t box_outer)
+{
+    return make_map(reinterpret_cast<CUtensorMap *>(map), base, inner, outer, ld, box_inner, box_outer, true);
+}
+
 bool
 gemm_tc_supported(const gemm_tc_args_t &g)
 {
@@ -312,7 +329,9 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
     // epilogue through TMA when C can be described by a tensor map and no bf16 copy is wanted
     CUtensorMap tc_map = ta;
     p.tma_epi = 0;
-    if (g.C && !g.Cb && g.ldc % 4 == 0 && (reinterpret_cast<uintptr_t>(g.C) & 15) == 0 &&
+    const bool cb_ok = !g.Cb || (g.beta == 0.f && grid.z == 1 && g.N % 4 == 0 && g.ldcb % 4 == 0 &&
+                                 (reinterpret_cast<uintptr_t>(g.Cb) & 7) == 0);
+    if (g.C && cb_ok && g.ldc % 4 == 0 && (reinterpret_cast<uintptr_t>(g.C) & 15) == 0 &&
         (g.beta == 0.f || g.beta == 1.f) && !(g.relu && (g.beta == 1.f || grid.z > 1))) {
         MMV_TRY(make_map(&tc_map, g.C, g.N, g.M, g.ldc, 32, 32, true));
         p.tma_epi = (g.beta == 1.f || grid.z > 1) ? 2 : 1;

@@ -42,6 +42,8 @@ int launch_to_bf16(const float *x, void *y, size_t n, cudaStream_t st);
 // SWIZZLE_128B tiled map over a row-major bf16 matrix [outer x inner] (leading dimension ld elements); map = CUtensorMap*
 int make_tma_map_bf16(void *map, const void *base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
                       uint32_t box_outer);
+int make_tma_map_f32(void *map, const void *base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+                     uint32_t box_outer);
 
 // ---- K1 sparse encoder (sparse_encoder.cu)
 struct senc_args_t {
@@ -140,14 +142,14 @@ struct senc_tc_args_t {
     const float *W1T = nullptr, *col_scale = nullptr, *Delta = nullptr, *inv_t = nullptr, *x_mean = nullptr;
     int angular = 0, accumulate = 1;
     float *dW1T = nullptr;
-    float *dot0 = nullptr, *dot1 = nullptr;   // [D] each, zeroed by the caller
+    float *S = nullptr;                 // [D x h1] raw product A^T delta (may alias dW1T when accumulate = 0)
 };
 bool senc_tc_supported(int h1);
 int launch_senc_tc_fwd(const senc_tc_args_t &a, cudaStream_t st);
 int launch_senc_tc_bwd(const senc_tc_args_t &a, cudaStream_t st);
-// d x_mean, d ln_x_sd from the per-gene dots; dWnu / dw_depth from the panel's raw counts
-int launch_senc_tc_finish(const float *dot0, const float *dot1, const float *inv_t, const float *x_mean,
-                          const float *ln_x_sd, float *dx_mean, float *dln_x_sd, int D, cudaStream_t st);
+// row pass after launch_senc_tc_bwd: rank-1 correction of dW1, d x_mean, d ln_x_sd (formulas in senc_tc.cu)
+int launch_senc_row_pass(const senc_tc_args_t &a, const float *ln_x_sd, float *dx_mean, float *dln_x_sd, cudaStream_t st);
+// dWnu / dw_depth from the panel's raw counts
 int launch_panel_aux_bwd(const int *bucket_ptr, const uint32_t *ent, const float *xraw, int B, int D, int H,
                          const float *dHnu, const float *ddpre, float *dWnuT, float *dwdepth, cudaStream_t st);
 int launch_w1eff_bf16(const float *W1T, const float *col_scale, void *out, int D, int h1, cudaStream_t st);

@@ -614,6 +614,20 @@ bf16_of(const step_t &s, const float *p, size_t n, const void **out)
     return 0;
 }
 
+// "<name>.bf" twin of an fp32 workspace array, registered so bf16_of() finds it without a cast kernel:
+// the GEMM that produces the fp32 array writes the twin from its epilogue registers.
+void *
+bf16_twin(const step_t &s, const float *p, size_t n)
+{
+    mmv_model *m = s.m;
+    std::string name;
+    for (auto &kv : m->ws) if (kv.second.p == (const void *)p) { name = kv.first; break; }
+    if (name.empty()) return nullptr;
+    void *buf = m->W(name + ".bf", n * 2);
+    if (buf) m->bf_cache[p] = buf;
+    return buf;
+}
+
 bool
 tc_ok(const step_t &s, int64_t M, int64_t N, int64_t K, int lda, int ldb)
 {
@@ -623,7 +637,7 @@ tc_ok(const step_t &s, int64_t M, int64_t N, int64_t K, int lda, int ldb)
 // Y = X W^T (+ b)
 int
 lin_fwd(const step_t &s, const float *X, int in, const float *W, const float *b, int out, float *Y, bool relu,
-        const char *tag = "gemm_other")
+        const char *tag = "gemm_other", bool want_twin = true)
 {
     mmv_model *m = s.m;
     if (tc_ok(s, s.B, out, in, in, in)) {
@@ -631,6 +645,10 @@ lin_fwd(const step_t &s, const float *X, int in, const float *W, const float *b,
         MMV_TRY(bf16_of(s, X, (size_t)s.B * in, &t.A));
         MMV_TRY(bf16_of(s, W, (size_t)out * in, &t.B));
         t.lda = in; t.ldb = in; t.C = Y; t.ldc = out; t.bias = b; t.M = s.B; t.N = out; t.K = in; t.relu = relu ? 1 : 0;
+        if (want_twin && out % 8 == 0 && (size_t)s.B * out <= ((size_t)1 << 25)) {   // hidden activations feed the next GEMM
+            t.Cb = bf16_twin(s, Y, (size_t)s.B * out);
+            t.ldcb = out;
+        }
         PROF(tag);
         return launch_gemm_tc(t, s.st);
     }
@@ -652,6 +670,10 @@ lin_bwd_data(const step_t &s, const float *dY, int out, const float *W, int in, 
         if (dY_bf) t.A = dY_bf; else MMV_TRY(bf16_of(s, dY, (size_t)s.B * out, &t.A));
         MMV_TRY(bf16_of(s, W, (size_t)out * in, &t.B));
         t.lda = out; t.b_mn = 1; t.ldb = in; t.C = dX; t.ldc = in; t.M = s.B; t.N = in; t.K = out;
+        if (in % 8 == 0 && !s.m->relu) {   // (a ReLU mask is applied to dX afterwards: the twin would be stale)
+            t.Cb = bf16_twin(s, dX, (size_t)s.B * in);
+            t.ldcb = in;
+        }
         PROF(tag);
         return launch_gemm_tc(t, s.st);
     }
@@ -746,7 +768,8 @@ decoder_forward(const step_t &s)
     }
     const linear_t &L = m->dec[nd - 1];
     float *G = WS("G", (size_t)B * D); NEED(G);
-    return lin_fwd(s, h, L.in, m->P(L.w), nullptr, D, G, false, "gemm_dec_last_fwd");
+    // no bf16 twin of the logits: K4 / K5 read them in fp32 and overwrite the buffer with the gradient
+    return lin_fwd(s, h, L.in, m->P(L.w), nullptr, D, G, false, "gemm_dec_last_fwd", /*want_twin=*/false);
 }
 
 // backward through the decoder given dG (in "G", in place) -> "dz"
@@ -913,12 +936,12 @@ senc_tc_backward(const step_t &s, const senc_bwd_args_t &b)
     MMV_TRY(bf16_of(s, b.delta, (size_t)B * h1, &a.dense_bf16));
     a.W1T = b.W1T; a.col_scale = b.col_scale; a.Delta = b.Delta; a.inv_t = b.inv_t; a.x_mean = b.x_mean;
     a.angular = b.angular; a.accumulate = b.accumulate; a.dW1T = b.dW1T;
-    float *dots = WS("pan_dots", 2 * (size_t)D); NEED(dots);
-    a.dot0 = dots; a.dot1 = dots + D;
-    MMV_CUDA(cudaMemsetAsync(dots, 0, sizeof(float) * 2 * D, s.st));
+    // raw product straight into the gradient when it is overwritten anyway, else into a scratch buffer
+    if (a.dW1T && !a.accumulate) a.S = a.dW1T;
+    else { a.S = WS("pan_S", (size_t)D * h1); NEED(a.S); }
     PROF("senc_bwd");
     MMV_TRY(launch_senc_tc_bwd(a, s.st));
-    MMV_TRY(launch_senc_tc_finish(a.dot0, a.dot1, b.inv_t, b.x_mean, b.ln_x_sd, b.dx_mean, b.dln_x_sd, D, s.st));
+    MMV_TRY(launch_senc_row_pass(a, b.ln_x_sd, b.dx_mean, b.dln_x_sd, s.st));
     if (!b.angular && b.dWnuT)
         MMV_TRY(launch_panel_aux_bwd(a.bucket_ptr, a.ent, m->ws["pan_x"].as<float>(), B, D, b.H, b.dHnu, b.ddpre,
                                      b.dWnuT, b.dwdepth, s.st));
@@ -1014,6 +1037,7 @@ nb_forward_backward(const step_t &s)
         PROF("nb_likelihood");
         MMV_TRY(launch_nb_likelihood(k, m->ctx->num_sms, s.st));
     }
+    m->bf_cache.erase(k.G);   // G may now hold the gradient (in-place fp32 mode)
     if (!s.bwd) return 0;
 
     // per-gene sums of dlogits: mu_decoding.bias, covar_decoding.{bias,weight}, mu_bias
@@ -1130,6 +1154,7 @@ vmf_forward_backward(const step_t &s)
         PROF("vmf_likelihood");
         MMV_TRY(launch_vmf_likelihood(k, m->ctx->num_sms, s.st));
     }
+    m->bf_cache.erase(k.G);   // G now holds dL/dpre
 
     // scalar part: loss constant, lbessel (operators.hh:49-101) and d ln_kappa (operators.hh:13-47)
     vmf_scalar_args_t sc;

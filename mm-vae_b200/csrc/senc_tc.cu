@@ -267,7 +267,8 @@ scatter_entry(uint8_t *tileA, uint32_t e, int rowbase)
 
 template <int BN, bool BWD>
 __global__ void __launch_bounds__(TCT, 1)
-senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, senc_tc_args_t a, int nT, int nK)
+senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmS, senc_tc_args_t a, int nT,
+               int nK)
 {
     using cfg = tc_cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
@@ -384,15 +385,28 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, senc_tc_args_t a, int nT
             asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(fulla0 + 8 * s) : "memory");
         };
 
+        // pull the runs of a later stage into L2 (backward walks the panel tile by tile: every stage is a
+        // first touch of DRAM otherwise, and the register prefetch is only one own-stage deep)
+        auto l2_prefetch = [&](int i, int i1) {
+            if (i >= i1) return;
+            const int4 r = rtab[i % RT];
+            if (t * 32 < r.y) asm volatile("prefetch.global.L2 [%0];" ::"l"(ent + r.x + t * 32));
+            if (t * 32 < r.w) asm volatile("prefetch.global.L2 [%0];" ::"l"(ent + r.z + t * 32));
+        };
+        constexpr int L2D = 4;                           // own-stages ahead (8 pipeline stages)
+
         uint32_t ea[PF], eb[PF];
         for (int i0 = 0; i0 < n_own; i0 += RT) {
             refill(i0);
             const int i1 = min(n_own, i0 + RT);
+            for (int i = i0 + 1; i < i0 + L2D; ++i) l2_prefetch(i, i1);
             load(ea, i0);
             for (int i = i0; i < i1; i += 2) {          // ping-pong register sets: no moves of in-flight loads
+                l2_prefetch(i + L2D, i1);
                 if (i + 1 < i1) load(eb, i + 1);
                 build(ea, i);
                 if (i + 1 >= i1) break;
+                l2_prefetch(i + 1 + L2D, i1);
                 if (i + 2 < i1) load(ea, i + 2);
                 build(eb, i + 1);
             }
@@ -437,52 +451,34 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, senc_tc_args_t a, int nT
                 }
             }
         } else {
-            const int g = tile * BM + trow;
-            const bool live = g < a.D;
-            const float xmit = live ? a.x_mean[g] * a.inv_t[g] : 0.f;
-            float d0 = 0.f, d1 = 0.f;
+            // S' = A^T delta tile -> [32 x 32] fp32 boxes in shared memory (SWIZZLE_128B) -> TMA tile store into
+            // the S buffer.  The rank-1 correction, the per-gene dots and the x_mean / ln_x_sd gradients are
+            // a coalesced row pass afterwards (senc_row_pass_kernel): a thread-per-row epilogue here would
+            // touch 32 different lines per request.
+            uint8_t *boxes = smem + (size_t)(warp - 4) * (BN / 64) * 4096;   // operand stages are free now
             for (int c = c_beg; c < c_end; ++c) {
                 uint32_t v[32];
                 tmem_ld32(tmem_base + ((uint32_t)(32 * e4) << 16) + (uint32_t)(32 * c), v);
-                const int col0 = n0 + 32 * c;
-                if (live) {
+                uint8_t *box = boxes + (size_t)(c - c_beg) * 4096;
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        if (col0 + j < a.h1) {   // h1 % 8 == 0
-                            const float4 w4 = *reinterpret_cast<const float4 *>(a.W1T + (size_t)g * a.h1 + col0 + j);
-                            const float4 dl4 = *reinterpret_cast<const float4 *>(a.Delta + col0 + j);
-                            float w[4] = { w4.x, w4.y, w4.z, w4.w };
-                            const float dl[4] = { dl4.x, dl4.y, dl4.z, dl4.w };
-                            float o[4];
-                            if (a.angular) {
-                                const float4 cs4 = *reinterpret_cast<const float4 *>(a.col_scale + col0 + j);
-                                const float cs[4] = { cs4.x, cs4.y, cs4.z, cs4.w };
-#pragma unroll
-                                for (int q = 0; q < 4; ++q) w[q] = (fmaxf(w[q], 0.f) + 1e-4f) * cs[q];
-                            }
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) {
-                                const float acc = __uint_as_float(v[j + q]);
-                                d0 = fmaf(w[q], acc, d0);
-                                d1 = fmaf(w[q], dl[q], d1);
-                                o[q] = fmaf(-xmit, dl[q], acc);
-                            }
-                            if (a.dW1T) {
-                                float4 *dst = reinterpret_cast<float4 *>(a.dW1T + (size_t)g * a.h1 + col0 + j);
-                                if (a.accumulate) {
-                                    const float4 old = *dst;
-                                    o[0] += old.x; o[1] += old.y; o[2] += old.z; o[3] += old.w;
-                                }
-                                *dst = make_float4(o[0], o[1], o[2], o[3]);
-                            }
-                        }
-                    }
+                for (int j = 0; j < 8; ++j)
+                    *reinterpret_cast<uint4 *>(box + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                        make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+                for (int c = c_beg; c < c_end; ++c) {
+                    const int c0 = n0 + 32 * c, c1 = tile * BM + 32 * e4;
+                    if (c0 >= a.h1 || c1 >= a.D) continue;
+                    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%1, %2}], [%3];"
+                                 ::"l"(&tmS), "r"(c0), "r"(c1), "r"(smem_u32(boxes + (size_t)(c - c_beg) * 4096)) : "memory");
                 }
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             }
-            if (live) {
-                atomicAdd(a.dot0 + g, d0);
-                atomicAdd(a.dot1 + g, d1);
-            }
+            __syncwarp();
+            (void)trow;
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
@@ -507,6 +503,8 @@ launch_tc(const senc_tc_args_t &a, cudaStream_t st)
     CUtensorMap tm;
     // dense operand: rows = K index (genes fwd / cells bwd), h1 contiguous
     MMV_TRY(make_tma_map_bf16(&tm, a.dense_bf16, (uint64_t)a.h1, (uint64_t)(BWD ? a.B : a.D), (uint64_t)a.h1, 64, BK));
+    CUtensorMap ts = tm;
+    if (BWD) MMV_TRY(make_tma_map_f32(&ts, a.S, (uint64_t)a.h1, (uint64_t)a.D, (uint64_t)a.h1, 32, 32));
     auto kern = senc_tc_kernel<BN, BWD>;
     static bool attr = false;
     if (!attr) {
@@ -514,23 +512,57 @@ launch_tc(const senc_tc_args_t &a, cudaStream_t st)
         attr = true;
     }
     dim3 grid(ceil_div(a.h1, BN), BWD ? ceil_div(a.D, BM) : ceil_div(a.B, BM));
-    kern<<<grid, TCT, cfg::SMEM, st>>>(tm, a, nT, nK);
+    kern<<<grid, TCT, cfg::SMEM, st>>>(tm, ts, a, nT, nK);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }
 
-__global__ void
-senc_tc_finish_kernel(const float *dot0, const float *dot1, const float *inv_t, const float *x_mean,
-                      const float *ln_x_sd, float *dx_mean, float *dln_x_sd, int D)
+// Row pass after the backward GEMM: one warp per gene j, coalesced over the h1 columns.
+//   S'[j, :] = sum_i (l_ij / t_j) delta_i   (the panel values carry 1 / t_j)
+//   dW1eff[j, :] (+)= S'[j, :] - (x_mean_j / t_j) Delta          nb.hh:406-411 backward, see sparse_encoder.cu
+//   d x_mean_j   += -(W_eff[j, :] . Delta) / t_j
+//   d t_j         = -(W_eff[j, :] . S' - (x_mean_j / t_j) W_eff[j, :] . Delta) / t_j ; d ln_x_sd_j += d t_j sigmoid(ln_x_sd_j)
+__global__ void __launch_bounds__(256)
+senc_row_pass_kernel(senc_tc_args_t a, const float *ln_x_sd, float *dx_mean, float *dln_x_sd)
 {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= D) return;
-    // dot0 = W_eff[j,:] . S'[j,:] with S' = S / t (the panel values carry 1/t) ; dot1 = W_eff[j,:] . Delta
-    const float it = inv_t[j], xm = x_mean[j];
-    dx_mean[j] += -dot1[j] * it;
-    const float dt = -(dot0[j] - xm * it * dot1[j]) * it;
-    dln_x_sd[j] += dt * sigmoid_f(ln_x_sd[j]);   // d softplus
+    const int lane = threadIdx.x & 31;
+    const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (j >= a.D) return;
+    const float it = a.inv_t[j], xm = a.x_mean[j], xmit = xm * it;
+    const float4 *S4 = reinterpret_cast<const float4 *>(a.S + (size_t)j * a.h1);
+    const float4 *W4 = reinterpret_cast<const float4 *>(a.W1T + (size_t)j * a.h1);
+    const float4 *D4 = reinterpret_cast<const float4 *>(a.Delta);
+    const float4 *C4 = reinterpret_cast<const float4 *>(a.col_scale);
+    float4 *O4 = a.dW1T ? reinterpret_cast<float4 *>(a.dW1T + (size_t)j * a.h1) : nullptr;
+    float d0 = 0.f, d1 = 0.f;
+    for (int n = lane; n < a.h1 / 4; n += 32) {      // h1 % 8 == 0
+        const float4 s4 = S4[n], dl = D4[n];
+        float4 w = W4[n];
+        if (a.angular) {                              // angular.hh:38-40
+            const float4 cs = C4[n];
+            w.x = (fmaxf(w.x, 0.f) + 1e-4f) * cs.x; w.y = (fmaxf(w.y, 0.f) + 1e-4f) * cs.y;
+            w.z = (fmaxf(w.z, 0.f) + 1e-4f) * cs.z; w.w = (fmaxf(w.w, 0.f) + 1e-4f) * cs.w;
+        }
+        d0 += w.x * s4.x + w.y * s4.y + w.z * s4.z + w.w * s4.w;
+        d1 += w.x * dl.x + w.y * dl.y + w.z * dl.z + w.w * dl.w;
+        if (O4) {
+            float4 o = make_float4(fmaf(-xmit, dl.x, s4.x), fmaf(-xmit, dl.y, s4.y), fmaf(-xmit, dl.z, s4.z),
+                                   fmaf(-xmit, dl.w, s4.w));
+            if (a.accumulate) {
+                const float4 old = O4[n];
+                o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+            }
+            O4[n] = o;
+        }
+    }
+    d0 = warp_sum(d0);
+    d1 = warp_sum(d1);
+    if (lane == 0) {
+        dx_mean[j] += -d1 * it;
+        const float dt = -(d0 - xmit * d1) * it;
+        dln_x_sd[j] += dt * sigmoid_f(ln_x_sd[j]);   // d softplus
+    }
 }
 
 // dWnuT[j, h] += sum_e x_e dHnu[row_e, h] ; dwdepth[j] += sum_e x_e ddpre[row_e].  One CTA per gene chunk.
@@ -593,10 +625,9 @@ launch_senc_tc_bwd(const senc_tc_args_t &a, cudaStream_t st)
 }
 
 int
-launch_senc_tc_finish(const float *dot0, const float *dot1, const float *inv_t, const float *x_mean,
-                      const float *ln_x_sd, float *dx_mean, float *dln_x_sd, int D, cudaStream_t st)
+launch_senc_row_pass(const senc_tc_args_t &a, const float *ln_x_sd, float *dx_mean, float *dln_x_sd, cudaStream_t st)
 {
-    senc_tc_finish_kernel<<<ceil_div(D, 256), 256, 0, st>>>(dot0, dot1, inv_t, x_mean, ln_x_sd, dx_mean, dln_x_sd, D);
+    senc_row_pass_kernel<<<ceil_div((int64_t)a.D * 32, 256), 256, 0, st>>>(a, ln_x_sd, dx_mean, dln_x_sd);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
