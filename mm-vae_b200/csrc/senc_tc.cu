@@ -565,7 +565,11 @@ senc_row_pass_kernel(senc_tc_args_t a, const float *ln_x_sd, float *dx_mean, flo
     }
 }
 
-// dWnuT[j, h] += sum_e x_e dHnu[row_e, h] ; dwdepth[j] += sum_e x_e ddpre[row_e].  One CTA per gene chunk.
+// dWnuT[j, h] += sum_e x_e dHnu[row_e, h] ; dwdepth[j] += sum_e x_e ddpre[row_e].
+// Grid = gene chunks x kAuxSplit slices of the cell tiles; a CTA accumulates its 64 genes in shared
+// memory (one warp per cell tile, lanes over the bucket) and adds them to the gradient once.
+constexpr int kAuxSplit = 8;
+
 __global__ void __launch_bounds__(256)
 panel_aux_bwd_kernel(const int *bp, const uint32_t *ent, const float *xraw, int nT, int nK, int H,
                      const float *dHnu, const float *ddpre, float *dWnuT, float *dwdepth, int D)
@@ -575,7 +579,7 @@ panel_aux_bwd_kernel(const int *bp, const uint32_t *ent, const float *xraw, int 
     const int W = H + 1;
     for (int i = tid; i < 64 * W; i += 256) s_acc[i] = 0.f;
     __syncthreads();
-    for (int T = warp; T < nT; T += 8) {
+    for (int T = blockIdx.y * 8 + warp; T < nT; T += 8 * kAuxSplit) {
         const int *p = bp + (size_t)T * (nK + 1) + k;
         const int b = p[0], e = p[1];
         for (int q = b + lane; q < e; q += 32) {
@@ -589,9 +593,9 @@ panel_aux_bwd_kernel(const int *bp, const uint32_t *ent, const float *xraw, int 
     __syncthreads();
     for (int i = tid; i < 64 * W; i += 256) {
         const int c = i / W, h = i % W, j = k * 64 + c;
-        if (j >= D) continue;
-        if (h == H) dwdepth[j] += s_acc[i];
-        else dWnuT[(size_t)j * H + h] += s_acc[i];
+        if (j >= D || s_acc[i] == 0.f) continue;
+        if (h == H) atomicAdd(dwdepth + j, s_acc[i]);
+        else atomicAdd(dWnuT + (size_t)j * H + h, s_acc[i]);
     }
 }
 
@@ -639,7 +643,7 @@ launch_panel_aux_bwd(const int *bucket_ptr, const uint32_t *ent, const float *xr
 {
     const size_t smem = sizeof(float) * 64 * (size_t)(H + 1);
     MMV_CHECK(smem <= 48 * 1024, "panel_aux_bwd: nu hidden width %d too large", H);
-    panel_aux_bwd_kernel<<<panel_chunks(D), 256, smem, st>>>(bucket_ptr, ent, xraw, panel_tiles(B), panel_chunks(D), H,
+    panel_aux_bwd_kernel<<<dim3(panel_chunks(D), kAuxSplit), 256, smem, st>>>(bucket_ptr, ent, xraw, panel_tiles(B), panel_chunks(D), H,
                                                              dHnu, ddpre, dWnuT, dwdepth, D);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
