@@ -114,6 +114,8 @@ struct panel_args_t {
     const float *vals = nullptr;
     const int32_t *cells = nullptr;
     int B = 0, D = 0, angular = 0;
+    const int *unsorted = nullptr;                     // device flag: 0 = every CSR row has ascending gene ids
+    int num_sms = 0;
     const float *inv_t = nullptr;
     const float *WnuT = nullptr, *bnu = nullptr;       // nb: nu encoder + depth on raw counts (nullable)
     int H = 0;

@@ -903,6 +903,7 @@ senc_tc_forward(const step_t &s, const senc_args_t &e, const void *w1eff_bf16)
     panel_args_t p;
     p.indptr = e.indptr; p.indices = e.indices; p.vals = e.vals; p.cells = e.cells;
     p.B = B; p.D = D; p.angular = e.angular; p.inv_t = e.inv_t;
+    p.unsorted = s.csr->d_unsorted; p.num_sms = m->ctx->num_sms;
     p.WnuT = e.WnuT; p.bnu = e.bnu; p.H = e.angular ? 0 : e.H; p.wdepth = e.wdepth; p.bdepth = e.bdepth;
     p.Hnu = e.Hnu; p.dpre = e.dpre; p.rownorm = e.rownorm;
     p.rowptr = (int *)WS("pan_rowptr", B + 1); p.bucket_ptr = (int *)WS("pan_bptr", (size_t)nT * (nK + 1));

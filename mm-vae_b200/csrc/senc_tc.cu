@@ -22,6 +22,8 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <algorithm>
+
 namespace mmv {
 
 namespace {
@@ -30,16 +32,20 @@ namespace {
 // panel build
 // ===========================================================================
 __global__ void
-batch_rowptr_kernel(const int64_t *indptr, const int32_t *cells, int B, int *rowptr)
+batch_rowptr_kernel(panel_args_t p)
 {
+    // minibatch-local CSR offsets (exclusive scan of the selected cells' run lengths) and the row
+    // scalars' bias terms (panel_build adds its per-split partial sums on top)
     __shared__ int s_part[1024];
-    const int tid = threadIdx.x, T = blockDim.x;
+    const int tid = threadIdx.x, T = blockDim.x, B = p.B;
     const int per = (B + T - 1) / T;
     const int r0 = min(B, tid * per), r1 = min(B, r0 + per);
     int sum = 0;
     for (int r = r0; r < r1; ++r) {
-        const int64_t c = cells ? (int64_t)cells[r] : (int64_t)r;
-        sum += (int)(indptr[c + 1] - indptr[c]);
+        const int64_t c = p.cells ? (int64_t)p.cells[r] : (int64_t)r;
+        sum += (int)(p.indptr[c + 1] - p.indptr[c]);
+        if (p.wdepth) p.dpre[r] = p.bdepth[0];
+        for (int h = 0; h < p.H; ++h) p.Hnu[(size_t)r * p.H + h] = p.bnu[h];
     }
     s_part[tid] = sum;
     __syncthreads();
@@ -51,33 +57,66 @@ batch_rowptr_kernel(const int64_t *indptr, const int32_t *cells, int B, int *row
     }
     int run = s_part[tid] - sum;
     for (int r = r0; r < r1; ++r) {
-        rowptr[r] = run;
-        const int64_t c = cells ? (int64_t)cells[r] : (int64_t)r;
-        run += (int)(indptr[c + 1] - indptr[c]);
+        p.rowptr[r] = run;
+        const int64_t c = p.cells ? (int64_t)p.cells[r] : (int64_t)r;
+        run += (int)(p.indptr[c + 1] - p.indptr[c]);
     }
-    if (tid == T - 1) rowptr[B] = s_part[T - 1];
+    if (tid == T - 1) p.rowptr[B] = s_part[T - 1];
 }
 
 constexpr int kPanelThreads = 512;
-constexpr int kUn = 8;
+constexpr int kUn = 4;
 
+// One CTA per (cell tile T, gene split s): the tile's 64 rows are cut at the split's chunk range
+// [k_lo, k_hi) by bisection of the sorted gene ids, so every CTA owns its buckets outright and the
+// grid covers the machine even at 64 cell tiles.  Unsorted rows: the whole run is scanned and filtered.
 __global__ void __launch_bounds__(kPanelThreads)
-panel_build_kernel(panel_args_t p, int nK)
+panel_build_kernel(panel_args_t p, int nK, int nS)
 {
     extern __shared__ int s_int[];
-    int *s_off = s_int;               // [nK + 1] exclusive offsets of the buckets of this tile
-    int *s_cur = s_int + nK + 1;      // [nK] fill cursors
     __shared__ int s_scan[kPanelThreads];
+    __shared__ int64_t s_qlo[64], s_qhi[64];
+    __shared__ int s_before;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = kPanelThreads / 32;
-    const int T = blockIdx.x, r0 = T * 64, nrows = min(64, p.B - r0);
+    const int T = blockIdx.x, sp = blockIdx.y, r0 = T * 64, nrows = min(64, p.B - r0);
+    const int k_lo = (int)((int64_t)nK * sp / nS), k_hi = (int)((int64_t)nK * (sp + 1) / nS), nKl = k_hi - k_lo;
+    int *s_off = s_int;               // [nKl + 1] exclusive offsets of this CTA's buckets
+    int *s_cur = s_int + nKl + 1;     // [nKl] fill cursors
+    const bool sorted = p.unsorted != nullptr && *p.unsorted == 0;
+    const bool filter = !sorted && nS > 1;
 
-    for (int k = tid; k < nK; k += kPanelThreads) s_cur[k] = 0;
+    for (int k = tid; k < nKl; k += kPanelThreads) s_cur[k] = 0;
+    if (tid == 0) s_before = 0;
+    __syncthreads();
+    if (tid < 128) {                  // per row: where the split's gene range starts / ends in the run
+        const int r = tid >> 1, which = tid & 1;
+        if (r < nrows) {
+            const int64_t c = p.cells ? (int64_t)p.cells[r0 + r] : (int64_t)(r0 + r);
+            const int64_t beg = p.indptr[c], end = p.indptr[c + 1];
+            const int kk = which ? k_hi : k_lo;
+            int64_t v = which ? end : beg;
+            if (sorted && kk > 0 && kk < nK) {
+                const int key = kk * 64;
+                int64_t lo = beg, hi = end;
+                while (lo < hi) {
+                    const int64_t mid = (lo + hi) >> 1;
+                    if (p.indices[mid] < key) lo = mid + 1; else hi = mid;
+                }
+                v = lo;
+            }
+            if (which) s_qhi[r] = v;
+            else {
+                s_qlo[r] = v;
+                if (sorted && v > beg) atomicAdd(&s_before, (int)(v - beg));   // entries of earlier splits
+            }
+        }
+    }
     __syncthreads();
     // ---- pass 1: bucket sizes
+    int before_unsorted = 0;          // unsorted rows: count the entries that belong to earlier splits
     for (int r = warp; r < nrows; r += NW) {
-        const int64_t c = p.cells ? (int64_t)p.cells[r0 + r] : (int64_t)(r0 + r);
-        const int64_t beg = p.indptr[c], end = p.indptr[c + 1];
+        const int64_t beg = s_qlo[r], end = s_qhi[r];
         for (int64_t q0 = beg; q0 < end; q0 += 32 * kUn) {   // kUn independent loads in flight per lane
             int j[kUn];
 #pragma unroll
@@ -86,14 +125,21 @@ panel_build_kernel(panel_args_t p, int nK)
                 j[u] = q < end ? p.indices[q] : -1;
             }
 #pragma unroll
-            for (int u = 0; u < kUn; ++u)
-                if (j[u] >= 0) atomicAdd(&s_cur[j[u] >> 6], 1);
+            for (int u = 0; u < kUn; ++u) {
+                const int k = (j[u] >> 6) - k_lo;
+                if (j[u] >= 0 && k >= 0 && k < nKl) atomicAdd(&s_cur[k], 1);
+                else if (filter && j[u] >= 0 && k < 0) ++before_unsorted;
+            }
         }
+    }
+    if (filter) {
+        before_unsorted = warp_sum(before_unsorted);
+        if (lane == 0 && before_unsorted) atomicAdd(&s_before, before_unsorted);
     }
     __syncthreads();
     // ---- exclusive scan over the chunks (each thread owns a contiguous span)
-    const int per = (nK + kPanelThreads - 1) / kPanelThreads;
-    const int k0 = min(nK, tid * per), k1 = min(nK, k0 + per);
+    const int per = (nKl + kPanelThreads - 1) / kPanelThreads;
+    const int k0 = min(nKl, tid * per), k1 = min(nKl, k0 + per);
     int sum = 0;
     for (int k = k0; k < k1; ++k) sum += s_cur[k];
     s_scan[tid] = sum;
@@ -104,36 +150,36 @@ panel_build_kernel(panel_args_t p, int nK)
         s_scan[tid] += v;
         __syncthreads();
     }
-    const int base = p.rowptr[r0];
+    const int base = p.rowptr[r0] + s_before;
     int run = s_scan[tid] - sum;
     for (int k = k0; k < k1; ++k) {
         const int n = s_cur[k];
         s_off[k] = run;
         run += n;
     }
-    if (tid == kPanelThreads - 1) s_off[nK] = s_scan[kPanelThreads - 1];
+    if (tid == kPanelThreads - 1) s_off[nKl] = s_scan[kPanelThreads - 1];
     __syncthreads();
-    int *bp = p.bucket_ptr + (size_t)T * (nK + 1);
-    for (int k = tid; k <= nK; k += kPanelThreads) {
-        bp[k] = base + s_off[k];
-        if (k < nK) s_cur[k] = s_off[k];
+    int *bp = p.bucket_ptr + (size_t)T * (nK + 1) + k_lo;
+    for (int k = tid; k <= nKl; k += kPanelThreads) {
+        if (k < nKl || sp == nS - 1) bp[k] = base + s_off[k];   // bp[k_hi] belongs to the next split
+        if (k < nKl) s_cur[k] = s_off[k];
     }
     __syncthreads();
-    // ---- pass 2: emit packed entries; per-row scalars on the way
+    // ---- pass 2: emit packed entries; partial row scalars on the way
     for (int r = warp; r < nrows; r += NW) {
-        const int64_t c = p.cells ? (int64_t)p.cells[r0 + r] : (int64_t)(r0 + r);
-        const int64_t beg = p.indptr[c], end = p.indptr[c + 1];
+        const int64_t beg = s_qlo[r], end = s_qhi[r];
         float rs = 1.f;
-        if (p.angular) {   // vmf.hh:255: row L2 norm of log1p(x), F::normalize eps 1e-12
+        if (p.angular) {   // vmf.hh:255: row L2 norm of log1p(x) over the WHOLE row, F::normalize eps 1e-12
+            const int64_t c = p.cells ? (int64_t)p.cells[r0 + r] : (int64_t)(r0 + r);
             float sq = 0.f;
-            for (int64_t q = beg + lane; q < end; q += 32) {
+            for (int64_t q = p.indptr[c] + lane, e = p.indptr[c + 1]; q < e; q += 32) {
                 const float l = log1pf(p.vals[q]);
                 sq = fmaf(l, l, sq);
             }
             sq = warp_sum(sq);
             const float nrm = fmaxf(sqrtf(sq), 1e-12f);
             rs = 1.f / nrm;
-            if (lane == 0 && p.rownorm) p.rownorm[r0 + r] = nrm;
+            if (lane == 0 && sp == 0 && p.rownorm) p.rownorm[r0 + r] = nrm;
         }
         float depth = 0.f, hn0 = 0.f;
         const bool h_inline = p.H == 1;
@@ -145,6 +191,8 @@ panel_build_kernel(panel_args_t p, int nK)
                 const int64_t q = q0 + lane + 32 * u;
                 j[u] = q < end ? p.indices[q] : -1;
                 x[u] = q < end ? p.vals[q] : 0.f;
+                const int k = (j[u] >> 6) - k_lo;
+                if (k < 0 || k >= nKl) j[u] = -1;      // (unsorted rows) another split's entry
             }
 #pragma unroll
             for (int u = 0; u < kUn; ++u) {
@@ -157,7 +205,7 @@ panel_build_kernel(panel_args_t p, int nK)
             for (int u = 0; u < kUn; ++u) {
                 if (j[u] < 0) continue;
                 const float v = log1pf(x[u]) * rs * it[u];
-                const int pos = base + atomicAdd(&s_cur[j[u] >> 6], 1);
+                const int pos = base + atomicAdd(&s_cur[(j[u] >> 6) - k_lo], 1);
                 const uint32_t bits = (uint32_t)__bfloat16_as_ushort(__float2bfloat16(v));
                 p.ent[pos] = ((uint32_t)r << 26) | ((uint32_t)(j[u] & 63) << 20) | bits;
                 p.xraw[pos] = x[u];
@@ -167,18 +215,20 @@ panel_build_kernel(panel_args_t p, int nK)
         }
         if (h_inline) {   // nb.hh:448 (raw counts), default H = 1
             hn0 = warp_sum(hn0);
-            if (lane == 0) p.Hnu[r0 + r] = hn0 + p.bnu[0];
+            if (lane == 0) atomicAdd(p.Hnu + r0 + r, hn0);
         }
         if (p.wdepth) {   // nb.hh:498 (raw counts)
             depth = warp_sum(depth);
-            if (lane == 0) p.dpre[r0 + r] = depth + p.bdepth[0];
+            if (lane == 0) atomicAdd(p.dpre + r0 + r, depth);
         }
         for (int h = 0; h < p.H && !h_inline; ++h) {   // nb.hh:448 (raw counts), general H
             float s = 0.f;
-            for (int64_t q = beg + lane; q < end; q += 32)
-                s = fmaf(p.vals[q], p.WnuT[(size_t)p.indices[q] * p.H + h], s);
+            for (int64_t q = beg + lane; q < end; q += 32) {
+                const int j = p.indices[q], k = (j >> 6) - k_lo;
+                if (k >= 0 && k < nKl) s = fmaf(p.vals[q], p.WnuT[(size_t)j * p.H + h], s);
+            }
             s = warp_sum(s);
-            if (lane == 0) p.Hnu[(size_t)(r0 + r) * p.H + h] = s + p.bnu[h];
+            if (lane == 0) atomicAdd(p.Hnu + (size_t)(r0 + r) * p.H + h, s);
         }
     }
 }
@@ -189,16 +239,20 @@ int
 launch_panel_build(const panel_args_t &p, cudaStream_t st)
 {
     const int nT = panel_tiles(p.B), nK = panel_chunks(p.D);
-    const size_t smem = sizeof(int) * (2 * (size_t)nK + 2);
+    // enough gene splits per cell tile for two CTAs per SM
+    int nS = (2 * std::max(p.num_sms, 1) + nT - 1) / nT;
+    nS = std::max(1, std::min(std::min(nS, 8), nK));
+    const int nKl = (nK + nS - 1) / nS + 1;
+    const size_t smem = sizeof(int) * (2 * (size_t)nKl + 2);
     MMV_CHECK(smem <= 200 * 1024, "panel_build: %d genes exceed the shared-memory bucket table", p.D);
     static bool attr = false;
     if (!attr) {
         MMV_CUDA(cudaFuncSetAttribute(panel_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr = true;
     }
-    batch_rowptr_kernel<<<1, 1024, 0, st>>>(p.indptr, p.cells, p.B, p.rowptr);
+    batch_rowptr_kernel<<<1, 1024, 0, st>>>(p);
     ::mmv::count_launch();
-    panel_build_kernel<<<nT, kPanelThreads, smem, st>>>(p, nK);
+    panel_build_kernel<<<dim3(nT, nS), kPanelThreads, smem, st>>>(p, nK, nS);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
