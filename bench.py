@@ -277,8 +277,9 @@ def kernel_work(w, B, bf16=True):
                     ("hbm", 8 * nnz + 4.0 * B * (h1 + H + 1) + 8.0 * D * h1 + 16.0 * D),
         "colsum_dlogits": ("hbm", (2.0 if bf16 else 4.0) * B * D),
         "panel_build": ("hbm", 8 * nnz + 8 * nnz + 8 * (B + 1)),
-        # K6: P ~ D (h1 + d_last) parameters; sumsq reads 4 B, Adam reads 16 + writes 16 + bf16 mirror 2
-        "clip_adam": ("hbm", 38.0 * D * (h1 + dl)),
+        # K6: P ~ D (h1 + d_last) parameters; sumsq reads 4 B, Adam reads 16 + writes 12 (p, m, v; the clip
+        # scale of .grad is applied when the gradient is read) + bf16 mirror 2
+        "clip_adam": ("hbm", 34.0 * D * (h1 + dl)),
     }
 
 

@@ -278,7 +278,10 @@ struct adam_args_t {
     // 1 - beta rounded from DOUBLE like libtorch's Scalar(1 - beta) (1.f - 0.999f is off by 1.3e-5)
     float one_minus_beta1 = (float)(1.0 - 0.9), one_minus_beta2 = (float)(1.0 - 0.999);
     float bc2_sqrt = 1.f, neg_step = 0.f;
+    int write_grad = 1;               // 0: leave .grad unscaled; the caller applies *coef_out when it is read
+    float *coef_out = nullptr;        // clip coefficient min(1, max_norm / (||g|| + 1e-6))
 };
 int launch_adam(const adam_args_t &a, int num_sms, cudaStream_t st);
+int launch_scale_by(float *x, size_t n, const float *coef, cudaStream_t st);
 
 } // namespace mmv

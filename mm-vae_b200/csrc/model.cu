@@ -122,7 +122,9 @@ struct mmv_model {
     int64_t last_B = 0;
     std::map<std::string, dbuf_t> ws;
     double *acc = nullptr;                // device: [0] nll/-, [1] kl_mu, [2] kl_nu, [3] sumsq, [4] t_acc, [5] llik_sum
-    float *fscal = nullptr;               // device: [0] kappa, [1] grad norm
+    float *fscal = nullptr;               // device: [0] kappa, [1] grad norm, [2] clip coefficient
+    bool grad_lazy = false;               // the clip scale of the last fused step is still to be applied to .grad
+    size_t grad_lazy_n = 0;               //   ... over grads[0, grad_lazy_n)
     double *h_acc = nullptr;              // pinned mirrors
     float *h_fscal = nullptr;
     // pinned staging, two slots: the host prepares step k+1 while step k runs (no stream sync per step)
@@ -525,7 +527,16 @@ int
 mmv_model_get_grad(mmv_model *m, const char *name, float *host, int64_t n)
 {
     MMV_CHECK(host, "mmv_model_get_grad: NULL data");
-    return copy_tensor(m, name, host, nullptr, n, m ? m->grads : nullptr);
+    MMV_TRY(copy_tensor(m, name, host, nullptr, n, m ? m->grads : nullptr));
+    if (m->grad_lazy) {   // clip_grad_norm_ scaled .grad in place (mmvae_alg.hh:308): apply the pending coefficient
+        const tensor_t &t = m->tensors[m->by_name.find(name)->second];
+        if (t.off + t.numel() <= m->grad_lazy_n) {
+            float coef = 1.f;
+            MMV_CUDA(cudaMemcpy(&coef, m->fscal + 2, sizeof(float), cudaMemcpyDeviceToHost));
+            for (int64_t i = 0; i < n; ++i) host[i] *= coef;
+        }
+    }
+    return 0;
 }
 
 } // extern "C"
@@ -788,7 +799,8 @@ decoder_backward(const step_t &s)
         const bool last = l == nd - 1;
         // bias of the last layer is handled with the other per-gene sums by the caller
         MMV_TRY(lin_bwd_weight(s, dY, L.out, X, L.in, m->want_grad(L.w) ? m->G(L.w) : nullptr,
-                               (!last && m->want_grad(L.b)) ? m->G(L.b) : nullptr, 1.f,
+                               (!last && m->want_grad(L.b)) ? m->G(L.b) : nullptr,
+                               (last && m->optimised(L.w)) ? 0.f : 1.f,   // mmv_step leaves this one un-zeroed
                                last ? "gemm_dec_last_dw" : "gemm_other", dY_bf));
         if (last && s.optim && m->ctx->nranks > 1 && m->optimised(L.w)) {
             // first bucket: the largest gradient is complete long before backward ends — reduce it under the rest
@@ -1330,8 +1342,28 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
             m->bf16_dirty = false;
         }
         MMV_CUDA(cudaMemsetAsync(m->acc, 0, sizeof(double) * 8, st));
-        if (s.bwd)   // adam.zero_grad() reaches the optimiser's tensors only (mmvae_alg.hh:306)
-            MMV_CUDA(cudaMemsetAsync(m->grads, 0, sizeof(float) * n_opt, st));
+        if (s.bwd) m->grad_lazy = false;
+        if (s.bwd) {   // adam.zero_grad() reaches the optimiser's tensors only (mmvae_alg.hh:306)
+            // the two D x h weight gradients are OVERWRITTEN by their producers (decoder-last dW GEMM with
+            // beta = 0, first-layer row pass with accumulate = 0): zero everything around them
+            size_t skip[2][2];
+            int ns = 0;
+            auto add_skip = [&](int t) {
+                if (t >= 0 && m->optimised(t) && m->tensors[t].off + m->tensors[t].numel() <= n_opt) {
+                    skip[ns][0] = m->tensors[t].off; skip[ns][1] = m->tensors[t].off + m->tensors[t].numel();
+                    ++ns;
+                }
+            };
+            if (!m->is_vmf) add_skip(m->enc[0].w);
+            add_skip(m->dec.back().w);
+            if (ns == 2 && skip[1][0] < skip[0][0]) { std::swap(skip[0][0], skip[1][0]); std::swap(skip[0][1], skip[1][1]); }
+            size_t pos = 0;
+            for (int i = 0; i <= ns; ++i) {
+                const size_t end = i < ns ? skip[i][0] : n_opt;
+                if (end > pos) MMV_CUDA(cudaMemsetAsync(m->grads + pos, 0, sizeof(float) * (end - pos), st));
+                if (i < ns) pos = skip[i][1];
+            }
+        }
         MMV_TRY(m->is_vmf ? vmf_forward_backward(s) : nb_forward_backward(s));
         if (csr->ev_consumed) MMV_CUDA(cudaEventRecord(csr->ev_consumed, st));   // the slot may be refilled from here on
     } else {
@@ -1340,6 +1372,10 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
 
     if (nranks > 1 && (flags & MMV_FWD)) MMV_TRY(comm_allreduce_f64(m->ctx, m->acc, 8));
     if (flags & MMV_OPTIM) {
+        if (m->grad_lazy) {   // an optimiser-only call on gradients whose previous clip is still pending
+            MMV_TRY(launch_scale_by(m->grads, m->grad_lazy_n, m->fscal + 2, st));
+            m->grad_lazy = false;
+        }
         {
             PROF("allreduce");
             if (m->early_n > 0) {   // everything but the bucket already in flight, then wait for it
@@ -1358,7 +1394,11 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         m->adam_t += 1;
         const double bc1 = 1. - std::pow(0.9, (double)m->adam_t), bc2 = 1. - std::pow(0.999, (double)m->adam_t);
         a.param = m->params; a.grad = m->grads; a.m = m->adam_m; a.v = m->adam_v; a.n = n_opt;
-        a.sumsq = m->acc + 3; a.norm_out = m->fscal + 1;
+        a.sumsq = m->acc + 3; a.norm_out = m->fscal + 1; a.coef_out = m->fscal + 2;
+        if ((flags & MMV_FWD) && (flags & MMV_BWD)) {   // fused step: nothing reads .grad before get_grad
+            a.write_grad = 0;
+            m->grad_lazy = true; m->grad_lazy_n = n_opt;
+        }
         if (m->use_tc && !m->bf16_dirty) a.param_bf16 = m->params_bf16;
         else m->bf16_dirty = true;
         a.max_norm = m->grad_clip; a.weight_decay = m->weight_decay;

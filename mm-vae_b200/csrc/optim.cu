@@ -50,7 +50,10 @@ adam_kernel(adam_args_t a)
     const float total = (float)sqrt(*a.sumsq);
     float coef = a.max_norm / (total + 1e-6f);
     coef = fminf(coef, 1.f);
-    if (blockIdx.x == 0 && threadIdx.x == 0 && a.norm_out) *a.norm_out = total;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (a.norm_out) *a.norm_out = total;
+        if (a.coef_out) *a.coef_out = coef;
+    }
     // 4 elements per thread per trip (the flat buffers are 16-byte aligned and n is a multiple of 8)
     const bool vec = ((reinterpret_cast<uintptr_t>(a.grad) | reinterpret_cast<uintptr_t>(a.param) |
                        reinterpret_cast<uintptr_t>(a.m) | reinterpret_cast<uintptr_t>(a.v)) & 15) == 0 && a.n % 4 == 0;
@@ -62,7 +65,7 @@ adam_kernel(adam_args_t a)
         float g[4] = { g4.x * coef, g4.y * coef, g4.z * coef, g4.w * coef };
         const float p[4] = { p4.x, p4.y, p4.z, p4.w };
         float m[4] = { m4.x, m4.y, m4.z, m4.w }, v[4] = { v4.x, v4.y, v4.z, v4.w }, pn[4];
-        reinterpret_cast<float4 *>(a.grad)[i] = make_float4(g[0], g[1], g[2], g[3]);   // clip scales .grad in place
+        if (a.write_grad) reinterpret_cast<float4 *>(a.grad)[i] = make_float4(g[0], g[1], g[2], g[3]);   // clip scales .grad in place
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             const float gw = fmaf(a.weight_decay, p[q], g[q]);
@@ -84,7 +87,7 @@ adam_kernel(adam_args_t a)
     }
     for (size_t i = n4 * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += (size_t)gridDim.x * blockDim.x) {
         float g = a.grad[i] * coef;
-        a.grad[i] = g;                       // clip_grad_norm_ scales .grad in place
+        if (a.write_grad) a.grad[i] = g;     // clip_grad_norm_ scales .grad in place
         const float p = a.param[i];
         g = fmaf(a.weight_decay, p, g);
         const float m = a.beta1 * a.m[i] + a.one_minus_beta1 * g;
@@ -104,6 +107,23 @@ launch_adam(const adam_args_t &a, int num_sms, cudaStream_t st)
     if (a.n == 0) return 0;
     const int grid = (int)min_sz((a.n / 4 + 255) / 256 + 1, (size_t)num_sms * 8);
     adam_kernel<<<grid, 256, 0, st>>>(a); ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+__global__ void
+scale_by_kernel(float *x, size_t n, const float *coef)
+{
+    const float c = *coef;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) x[i] *= c;
+}
+
+// materialise a clip scale that launch_adam (write_grad = 0) left pending
+int
+launch_scale_by(float *x, size_t n, const float *coef, cudaStream_t st)
+{
+    if (n == 0) return 0;
+    scale_by_kernel<<<(int)min_sz((n + 255) / 256, 2048), 256, 0, st>>>(x, n, coef); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
 }

@@ -271,3 +271,34 @@ def test_unsorted_rows_equal_sorted(mmv, ctx, model, dtype):
     assert scalar_close(l0, l1, TOL), (l0, l1)
     bad = {k: rel_err(g1[k], g0[k]) for k in g0 if np.linalg.norm(g0[k]) > 1e-12 and rel_err(g1[k], g0[k]) >= TOL}
     assert not bad, bad
+
+
+@pytest.mark.parametrize("dtype", ["f32", "bf16"])
+def test_fused_step_equals_split_step(mmv, ctx, dtype):
+    """FWD|BWD|OPTIM in one call (clip scale applied lazily to .grad, overwritten gradients not
+    zero-filled) must leave the same parameters and the same clipped gradients as FWD|BWD followed by
+    an optimiser-only call (clip_grad_norm_ + adam.step, mmvae_alg.hh:306-310)."""
+    D, B = 6000, 96
+    rng = np.random.default_rng(11)
+    x = synth_batch(rng, B, D, 0.05)
+    csr = mmv.CSR.from_dense(ctx, x)
+    eps = [rng.normal(size=(B, 8)).astype(np.float32), rng.normal(size=(B, 1)).astype(np.float32)]
+    res = []
+    for fused in (False, True):
+        m = mmv.Model.nb(ctx, D, 1, [96], [80], mu_r=8, nu_h=1, nu_r=1, seed=5)
+        m.set_option("train_all_layers", 1)
+        m.set_option("dtype", 1 if dtype == "bf16" else 0)
+        m.set_option("grad_clip", 0.05)          # well below the gradient norm: the clip is active
+        for it in range(2):                      # second round: stale gradients from round one are around
+            if fused:
+                t = m.step(csr, np.arange(B), eps=eps, kl_weight=0.5, flags=mmv.FWD | mmv.BWD | mmv.OPTIM)
+            else:
+                m.step(csr, np.arange(B), eps=eps, kl_weight=0.5, flags=mmv.FWD | mmv.BWD)
+                t = m.step(csr, np.arange(B), flags=mmv.OPTIM)
+        assert t["grad_norm"] > 0.05
+        res.append(({k: m.get_grad(k).copy() for k in m.param_info()}, {k: m.get_param(k).copy() for k in m.param_info()}))
+        m.close()
+    csr.close()
+    for k in res[0][0]:
+        assert rel_err(res[1][0][k], res[0][0][k]) < 1e-5, ("grad", k)
+        assert rel_err(res[1][1][k], res[0][1][k]) < 1e-4, ("param", k)
