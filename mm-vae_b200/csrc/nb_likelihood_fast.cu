@@ -70,9 +70,122 @@ log1p_fast(float y)
     return y < 0.0625f ? poly : big;
 }
 
+// ---- packed fp32 pairs (sm_100 FFMA2 / FMUL2 / FADD2): the dense sweep is issue-bound, and every
+//      thread owns adjacent gene pairs, so the FMA-pipe arithmetic is issued two lanes at a time
+typedef unsigned long long f2_t;
+
+__device__ __forceinline__ f2_t
+pk2(float a, float b)
+{
+    f2_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+
+__device__ __forceinline__ f2_t
+bc2(float a)
+{
+    return pk2(a, a);
+}
+
+__device__ __forceinline__ void
+up2(f2_t r, float &a, float &b)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(r));
+}
+
+__device__ __forceinline__ f2_t
+fma2(f2_t a, f2_t b, f2_t c)
+{
+    f2_t r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+
+__device__ __forceinline__ f2_t
+mul2(f2_t a, f2_t b)
+{
+    f2_t r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
+__device__ __forceinline__ f2_t
+add2(f2_t a, f2_t b)
+{
+    f2_t r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
 struct elem_t {
     float m, nu, l1p, inv_mnu, sig_mask;
 };
+
+// Dense sweep of one adjacent gene pair assuming x = 0 (same formulas as elem_fast, two lanes per
+// FMA-pipe instruction).  v = softmax numerators, u = (zn wn + ub) log2(e).  Outputs: p (softmax),
+// g = dl/dm = nu / (m + nu), nl = nu log1p(m / nu), du = (log1p(m / nu) - m / (m + nu)) dnu/du
+// (NOT yet divided by B: the row / column sums are scaled once at the end).
+struct pair_t {
+    f2_t p, g, nl, du;
+};
+
+__device__ __forceinline__ pair_t
+pair_fast(f2_t v, f2_t scale, f2_t depth, f2_t u)
+{
+    const f2_t one = bc2(1.f), neg1 = bc2(-1.f), ln2 = bc2(kLn2), eps = bc2(kEps);
+    constexpr float c20 = 20.f * kLog2e;                              // softplus threshold 20 (nb.hh:458)
+    pair_t o;
+    o.p = mul2(v, scale);
+    const f2_t m = fma2(o.p, depth, eps);                             // nb.hh:519
+    float u0, u1;
+    up2(u, u0, u1);
+    const float t0 = ex2_f(fminf(u0, c20)), t1 = ex2_f(fminf(u1, c20));
+    const f2_t t = pk2(t0, t1);
+    const f2_t w = add2(t, one);
+    float w0, w1;
+    up2(w, w0, w1);
+    const f2_t rw = pk2(rcp_f(w0), rcp_f(w1));
+    const f2_t lw = pk2(lg2_f(w0), lg2_f(w1));
+    // log1p(t) = log(w) + (t - (w - 1)) / w ; beyond the threshold softplus(u) = u = log1p(e^20) + (u - 20)
+    const f2_t comp = mul2(fma2(add2(w, neg1), neg1, t), rw);
+    f2_t sp = fma2(lw, ln2, comp);
+    const f2_t over = add2(u, bc2(-c20));
+    float v0, v1;
+    up2(over, v0, v1);
+    sp = fma2(pk2(fmaxf(v0, 0.f), fmaxf(v1, 0.f)), ln2, sp);
+    float s0, s1;
+    up2(sp, s0, s1);
+    const float r0 = fminf(fmaxf(s0, kNuMin), kNuMax), r1 = fminf(fmaxf(s1, kNuMin), kNuMax);   // nb.hh:459
+    const f2_t nu = add2(pk2(r0, r1), eps);                           // nb.hh:518
+    const f2_t sig = mul2(t, rw);                                     // d softplus / du (-> 1 beyond the threshold)
+    float g0, g1;
+    up2(sig, g0, g1);
+    const f2_t sigm = pk2(r0 == s0 ? g0 : 0.f, r1 == s1 ? g1 : 0.f);  // clamp passes the gradient inside [min, max]
+    const f2_t mnu = add2(m, nu);
+    float q0, q1;
+    up2(mul2(nu, mnu), q0, q1);
+    const f2_t q = pk2(rcp_f(q0), rcp_f(q1));                         // one MUFU for both reciprocals
+    const f2_t minv = mul2(m, mul2(q, nu));                           // m / (m + nu)
+    const f2_t y = mul2(m, mul2(q, mnu));                             // m / nu
+    // log1p(y): Taylor polynomial below 1/16, MUFU lg2 above (see log1p_fast)
+    const f2_t ny = mul2(y, neg1);
+    f2_t poly = fma2(ny, bc2(0.2f), bc2(0.25f));
+    poly = fma2(ny, poly, bc2(0.33333334f));
+    poly = fma2(ny, poly, bc2(0.5f));
+    poly = fma2(ny, poly, one);
+    poly = mul2(y, poly);
+    float y0, y1, z0, z1, p0, p1, b0, b1;
+    up2(y, y0, y1);
+    up2(add2(y, one), z0, z1);
+    up2(poly, p0, p1);
+    up2(mul2(pk2(lg2_f(z0), lg2_f(z1)), ln2), b0, b1);
+    const f2_t l1p = pk2(y0 < 0.0625f ? p0 : b0, y1 < 0.0625f ? p1 : b1);
+    o.g = fma2(minv, neg1, one);                                      // nu / (m + nu)
+    o.nl = mul2(nu, l1p);
+    o.du = mul2(fma2(minv, neg1, l1p), sigm);
+    return o;
+}
 
 // u2 = u * log2(e): the per-gene nu weights are staged pre-scaled so that exp(u) is one ex2.
 // 6 MUFU: ex2, rcp(1 + t), lg2(1 + t), rcp(nu (m + nu)), lg2(1 + m / nu) (+ the softmax ex2 outside).
@@ -228,9 +341,11 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
     }
     for (int jj = tid; jj < Dp; jj += kT) {
         const int j = j0 + jj;
-        float ab = 0.f, ub = 0.f, wn = 0.f;
+        // padding: logit -inf (softmax numerator 0), u -> -inf (nu clamped, gradient masked), weight 0
+        float ab = -INFINITY, ub = -1e30f, wn = 0.f;
         if (jj < nj) {
-            ab = a.abias[j];
+            ab = 0.f;
+            ab += a.abias[j];
             for (int c = 0; c < a.C; ++c) ab += a.Wcd[(size_t)j * a.C + c];   // covariates are all ones on this path
             ub = a.ubias[j] * kLog2e;   // pre-scaled: u * log2(e) = zn * wn' + ub'
             wn = a.Wnd[j] * kLog2e;
@@ -246,9 +361,10 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
     int row = cluster_id;
     if (tid == 0 && row < a.B && nj > 0) bulk_load(smem_addr(sG0), a.G + (size_t)row * D + j0, row_bytes, bar0);
 
-    float cdu[EPT], cduz[EPT];
+    f2_t cdu[HP], cduz[HP];            // per-gene column sums of d nu-logit (x zn), un-normalised (1/B at the end)
 #pragma unroll
-    for (int k = 0; k < EPT; ++k) cdu[k] = cduz[k] = 0.f;
+    for (int h = 0; h < HP; ++h) cdu[h] = cduz[h] = 0ull;
+    f2_t nll2 = 0ull;
     float nll_acc = 0.f;
 
     // per-row metadata, one row ahead: scalars, the slice's CSR range, the first NZP nonzeros per thread
@@ -293,32 +409,40 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
 
         // ---- pass 1: logits into registers; softmax numerators against the WARP max, so one
         //      block hop + one cluster hop give max and sum together (online-softmax merge)
-        float v[EPT];
+        // (log2 domain: every shift is the SAME rounded number wherever it is used, so the merges are exact)
+        f2_t vp[HP];
         float wm = -INFINITY;
 #pragma unroll
         for (int h = 0; h < HP; ++h) {
             const int jj = 2 * tid + h * 2 * kT;
-            const float2 gq = *reinterpret_cast<const float2 *>(sG + jj);
-            const float2 ab = *reinterpret_cast<const float2 *>(s_ab + jj);
-            v[2 * h] = jj < nj ? gq.x + ab.x : -INFINITY;            // nj is even: a pair is valid or not as a whole
-            v[2 * h + 1] = jj < nj ? gq.y + ab.y : -INFINITY;
-            wm = fmaxf(wm, fmaxf(v[2 * h], v[2 * h + 1]));
+            vp[h] = add2(*reinterpret_cast<const f2_t *>(sG + jj), *reinterpret_cast<const f2_t *>(s_ab + jj));
+            float x0, x1;
+            up2(vp[h], x0, x1);
+            wm = fmaxf(wm, fmaxf(x0, x1));
         }
         wm = warp_max(wm);
-        const float wm_safe = wm > -INFINITY ? wm : 0.f;
-        float wsum = 0.f;
+        const float cw = wm > -INFINITY ? wm * kLog2e : 0.f;
+        const f2_t l2e = bc2(kLog2e), ncw = bc2(-cw);
+        f2_t ws2 = 0ull;
 #pragma unroll
-        for (int k = 0; k < EPT; ++k) {
-            v[k] = __expf(v[k] - wm_safe);         // exp(-inf) = 0 on the padding
-            wsum += v[k];
+        for (int h = 0; h < HP; ++h) {
+            float y0, y1;
+            up2(fma2(vp[h], l2e, ncw), y0, y1);
+            vp[h] = pk2(ex2_f(y0), ex2_f(y1));      // ex2(-inf) = 0 on the padding
+            ws2 = add2(ws2, vp[h]);
         }
-        wsum = warp_sum(wsum);
-        if (lane == 0) { ws[warp * 4 + 0] = wm; ws[warp * 4 + 1] = wsum; }
+        float wsum;
+        {
+            float s0, s1;
+            up2(ws2, s0, s1);
+            wsum = warp_sum(s0 + s1);
+        }
+        if (lane == 0) { ws[warp * 4 + 0] = wm > -INFINITY ? cw : -INFINITY; ws[warp * 4 + 1] = wsum; }
         __syncthreads();
         const float bm = lane < NW ? ws[lane * 4 + 0] : -INFINITY;
         const float bs_in = lane < NW ? ws[lane * 4 + 1] : 0.f;
         const float bmax = warp_max(bm);
-        const float bsum = warp_sum(bm > -INFINITY ? bs_in * __expf(bm - bmax) : 0.f);
+        const float bsum = warp_sum(bm > -INFINITY ? bs_in * ex2_f(bm - bmax) : 0.f);
         float gmax = bmax, gsum = bsum;
         if (cs > 1) {
             if (tid == 0) xchg_send(smem_addr(xs + rank * 2), xb, cs, bmax, bsum);
@@ -333,38 +457,32 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
             }
             gsum = 0.f;
 #pragma unroll
-            for (int r = 0; r < 8; ++r) gsum += rm[r] > -INFINITY ? rs[r] * __expf(rm[r] - gmax) : 0.f;
+            for (int r = 0; r < 8; ++r) gsum += rm[r] > -INFINITY ? rs[r] * ex2_f(rm[r] - gmax) : 0.f;
         }
         const float inv_sum = 1.f / gsum;
-        const float scale = wm > -INFINITY ? __expf(wm - gmax) * inv_sum : 0.f;
-        if (a.row_lse && rank == 0 && tid == 0) a.row_lse[row] = gmax + logf(gsum);
+        const float scale = wm > -INFINITY ? ex2_f(cw - gmax) * inv_sum : 0.f;
+        if (a.row_lse && rank == 0 && tid == 0) a.row_lse[row] = gmax * kLn2 + logf(gsum);
 
         // ---- pass 2: dense sweep assuming x = 0 (lgammas cancel, no digamma).  Branch-free: the
         //      out-of-range lanes compute on the padding and are masked at the accumulations.
-        float red[2] = { 0.f, 0.f };           // s = sum g p ; d znu
+        float red[2] = { 0.f, 0.f };           // s = sum g p ; d znu (un-normalised)
+        f2_t red0 = 0ull, red1 = 0ull;
+        {
+            const f2_t scale2 = bc2(scale), depth2 = bc2(depth), zn2 = bc2(zn);
 #pragma unroll
-        for (int h = 0; h < HP; ++h) {
-            const int jj = 2 * tid + h * 2 * kT;
-            const float ok = jj < nj ? 1.f : 0.f;
-            const float2 wn2 = *reinterpret_cast<const float2 *>(s_wn + jj);
-            const float2 ub2 = *reinterpret_cast<const float2 *>(s_ub + jj);
-            float gg[2];
-#pragma unroll
-            for (int e2 = 0; e2 < 2; ++e2) {
-                const int k = 2 * h + e2;
-                const float wn = e2 ? wn2.y : wn2.x, ub = e2 ? ub2.y : ub2.x;
-                const float p = v[k] * scale;  // 0 on the padding
-                const elem_t e = elem_fast(p, depth, fmaf(zn, wn, ub));
-                nll_acc = fmaf(e.nu * ok, e.l1p, nll_acc);
-                v[k] = p;
-                gg[e2] = e.nu * e.inv_mnu;
-                red[0] = fmaf(gg[e2], p, red[0]);
-                const float du = (e.l1p - e.m * e.inv_mnu) * e.sig_mask * (a.inv_B * ok);
-                cdu[k] += du;
-                cduz[k] = fmaf(du, zn, cduz[k]);
-                red[1] = fmaf(du, wn, red[1]);
+            for (int h = 0; h < HP; ++h) {
+                const int jj = 2 * tid + h * 2 * kT;
+                const f2_t wn2 = *reinterpret_cast<const f2_t *>(s_wn + jj);
+                const f2_t ub2 = *reinterpret_cast<const f2_t *>(s_ub + jj);
+                const pair_t e = pair_fast(vp[h], scale2, depth2, fma2(zn2, wn2, ub2));
+                nll2 = fma2(e.nl, bc2(jj < nj ? 1.f : 0.f), nll2);
+                vp[h] = e.p;
+                red0 = fma2(e.g, e.p, red0);
+                cdu[h] = add2(cdu[h], e.du);
+                cduz[h] = fma2(e.du, zn2, cduz[h]);
+                red1 = fma2(e.du, wn2, red1);
+                *reinterpret_cast<f2_t *>(s_g + jj) = e.g;
             }
-            *reinterpret_cast<float2 *>(s_g + jj) = make_float2(gg[0], gg[1]);
         }
         __syncthreads();                       // s_g complete before the nonzero loop overwrites entries
 
@@ -372,7 +490,7 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         auto fix = [&](int j, float x) {
             const int jj = j - j0;
             if (jj < 0 || jj >= nj || x == 0.f) return;
-            const float p = __expf(sG[jj] + s_ab[jj] - gmax) * inv_sum;
+            const float p = ex2_f(fmaf(sG[jj] + s_ab[jj], kLog2e, -gmax)) * inv_sum;
             const float wn = s_wn[jj];
             const elem_t e = elem_fast(p, depth, fmaf(zn, wn, s_ub[jj]));
             const float L = __logf(e.m + e.nu);
@@ -383,9 +501,9 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
                 const float gx = (e.nu + x) * e.inv_mnu - x * rcp_f(e.m);
                 red[0] = fmaf(gx - e.nu * e.inv_mnu, p, red[0]);
                 s_g[jj] = gx;
-                const float ddu = (dig_diff + x * e.inv_mnu) * e.sig_mask * a.inv_B;   // dnu_x - dnu_0
-                atomicAdd(a.col_du + j, ddu);
-                atomicAdd(a.col_duz + j, ddu * zn);
+                const float ddu = (dig_diff + x * e.inv_mnu) * e.sig_mask;   // dnu_x - dnu_0 (un-normalised)
+                atomicAdd(a.col_du + j, ddu * a.inv_B);
+                atomicAdd(a.col_duz + j, ddu * zn * a.inv_B);
                 red[1] = fmaf(ddu, wn, red[1]);
             }
         };
@@ -404,12 +522,18 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
 
         if (grad) {
             // ---- second reduction: s = sum g p, d znu
-            red[0] = warp_sum(red[0]);
-            red[1] = warp_sum(red[1]);
+            {
+                float a0, a1, b0, b1;
+                up2(red0, a0, a1);
+                up2(red1, b0, b1);
+                red[0] = warp_sum(red[0] + a0 + a1);
+                red[1] = warp_sum(red[1] + b0 + b1);
+            }
             if (lane == 0) { ws[warp * 4 + 2] = red[0]; ws[warp * 4 + 3] = red[1]; }
             __syncthreads();                   // also: every s_g fix is visible
             float s = warp_sum(lane < NW ? ws[lane * 4 + 2] : 0.f);
-            float dz = warp_sum(lane < NW ? ws[lane * 4 + 3] : 0.f) * kLn2;   // red[1] was accumulated against wn * log2(e)
+            // red[1] was accumulated against wn * log2(e) and without the 1 / B
+            float dz = warp_sum(lane < NW ? ws[lane * 4 + 3] : 0.f) * (kLn2 * a.inv_B);
             if (cs > 1) {
                 if (tid == 0) xchg_send(smem_addr(xs + 16 + rank * 2), xb + 8, cs, s, dz);
                 bar_wait(xb + 8, ph);
@@ -420,12 +544,14 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
             }
             const float coef = depth * a.inv_B;
             // ---- pass 3: dL/dlogit_j = (d_i / B) p_j (g_j - s_i), one coalesced store per pair
+            const f2_t coef2 = bc2(coef), ns2 = bc2(-s);
 #pragma unroll
             for (int h = 0; h < HP; ++h) {
                 const int jj = 2 * tid + h * 2 * kT;
                 if (jj < nj) {
-                    const float2 gq = *reinterpret_cast<const float2 *>(s_g + jj);
-                    const float o0 = coef * v[2 * h] * (gq.x - s), o1 = coef * v[2 * h + 1] * (gq.y - s);
+                    const f2_t gq = *reinterpret_cast<const f2_t *>(s_g + jj);
+                    float o0, o1;
+                    up2(mul2(mul2(vp[h], coef2), add2(gq, ns2)), o0, o1);
                     if (a.dlogits_bf16) {
                         const __nv_bfloat162 b = __floats2bfloat162_rn(o0, o1);
                         *reinterpret_cast<__nv_bfloat162 *>(reinterpret_cast<__nv_bfloat16 *>(a.dlogits_bf16) +
@@ -443,17 +569,24 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         __syncthreads();       // everyone is done with sG[cur] / s_g before the TMA unit and the next row refill them
     }
 
-    nll_acc = warp_sum(nll_acc);
+    {
+        float n0, n1;
+        up2(nll2, n0, n1);
+        nll_acc = warp_sum(nll_acc + n0 + n1);
+    }
     if (lane == 0 && nll_acc != 0.f) atomicAdd(a.loss_acc, (double)nll_acc);
     if (grad) {
 #pragma unroll
         for (int h = 0; h < HP; ++h) {
             const int jj = 2 * tid + h * 2 * kT;
             if (jj < nj) {
-                atomicAdd(a.col_du + j0 + jj, cdu[2 * h]);
-                atomicAdd(a.col_du + j0 + jj + 1, cdu[2 * h + 1]);
-                atomicAdd(a.col_duz + j0 + jj, cduz[2 * h]);
-                atomicAdd(a.col_duz + j0 + jj + 1, cduz[2 * h + 1]);
+                float c0, c1, z0, z1;
+                up2(cdu[h], c0, c1);
+                up2(cduz[h], z0, z1);
+                atomicAdd(a.col_du + j0 + jj, c0 * a.inv_B);
+                atomicAdd(a.col_du + j0 + jj + 1, c1 * a.inv_B);
+                atomicAdd(a.col_duz + j0 + jj, z0 * a.inv_B);
+                atomicAdd(a.col_duz + j0 + jj + 1, z1 * a.inv_B);
             }
         }
     }
