@@ -24,6 +24,9 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <algorithm>
+#include <cstdlib>
+
 namespace mmv {
 
 namespace tc {
@@ -232,6 +235,182 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
 }
 
+// ---------------------------------------------------------------------------
+// Persistent variant for many-tile products (the decoder's last layer: 4096 x 30000 x 1024).
+// One CTA per SM walks 128 x 256 tiles (half the operand traffic per flop of a 128 x 128 tile);
+// the TMA producer and the MMA issuer run ahead across tile boundaries (the 4-stage ring never
+// drains), and the accumulator is double-buffered in TMEM (2 x 256 columns) so the epilogue warps
+// drain tile i through TMA tile stores while tile i + 1 is being multiplied.
+// ---------------------------------------------------------------------------
+constexpr int P_BLOCK_N = 256, P_STAGES = 4;
+constexpr int P_B_BYTES = P_BLOCK_N * BLOCK_K * 2, P_STAGE_BYTES = A_BYTES + P_B_BYTES;
+constexpr int P_BOX_BYTES = 4 * 2 * 4096;        // 4 epilogue warps x 2 staging boxes of [32 x 32] fp32
+constexpr int P_SMEM_BYTES = P_STAGES * P_STAGE_BYTES + P_BOX_BYTES + 1024 + 256;
+
+template <bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(THREADS, 1)
+gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                       const __grid_constant__ CUtensorMap tmC, params_t p)
+{
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t *boxes_all = smem + P_STAGES * P_STAGE_BYTES;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(boxes_all + P_BOX_BYTES);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * P_STAGES + 4);
+    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + P_STAGES);
+    const uint32_t tfull0 = smem_u32(bars + 2 * P_STAGES), tempty0 = tfull0 + 16;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tiles_m = (p.M + BLOCK_M - 1) / BLOCK_M, tiles_n = (p.N + P_BLOCK_N - 1) / P_BLOCK_N;
+    const int num_tiles = tiles_m * tiles_n;
+    const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmC) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < P_STAGES; ++s) {
+            mbar_init(full0 + 8 * s, 1);
+            mbar_init(empty0 + 8 * s, 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(tfull0 + 8 * b, 1);
+            mbar_init(tempty0 + 8 * b, 4);            // one arrival per epilogue warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================= TMA producer (runs ahead across tiles) =================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                const int m0 = (t % tiles_m) * BLOCK_M, n0 = (t / tiles_m) * P_BLOCK_N;   // m fastest: concurrent CTAs share B
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const uint32_t s = it % P_STAGES, ph = (it / P_STAGES) & 1;
+                    mbar_wait(empty0 + 8 * s, ph ^ 1);
+                    const uint32_t sa = smem_u32(smem + s * P_STAGE_BYTES), sb = sa + A_BYTES;
+                    const uint32_t fb = full0 + 8 * s;
+                    mbar_expect_tx(fb, P_STAGE_BYTES);
+                    const int k0 = kb * BLOCK_K;
+                    if (A_MN) {
+                        tma_load_2d(sa, &tmA, fb, m0, k0);
+                        tma_load_2d(sa + A_BYTES / 2, &tmA, fb, m0 + 64, k0);
+                    } else {
+                        tma_load_2d(sa, &tmA, fb, k0, m0);
+                    }
+                    if (B_MN) {
+#pragma unroll
+                        for (int q = 0; q < P_BLOCK_N / 64; ++q) tma_load_2d(sb + q * 8192, &tmB, fb, n0 + 64 * q, k0);
+                    } else {
+                        tma_load_2d(sb, &tmB, fb, k0, n0);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc(A_MN, B_MN, BLOCK_M, P_BLOCK_N);
+            uint32_t it = 0, lt = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++lt) {
+                const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
+                mbar_wait(tempty0 + 8 * acc, aph ^ 1);              // epilogue has drained this accumulator
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t d_tmem = tmem_base + acc * P_BLOCK_N;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const uint32_t s = it % P_STAGES, ph = (it / P_STAGES) & 1;
+                    mbar_wait(full0 + 8 * s, ph);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sa = smem_u32(smem + s * P_STAGE_BYTES), sb = sa + A_BYTES;
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                        const uint64_t ad = A_MN ? make_desc(sa + k * 2048, A_BYTES / 2, 1024)
+                                                 : make_desc(sa + k * 32, 16, 1024);
+                        const uint64_t bd = B_MN ? make_desc(sb + k * 2048, 8192, 1024)
+                                                 : make_desc(sb + k * 32, 16, 1024);
+                        umma_bf16(d_tmem, ad, bd, idesc, (kb | k) != 0);
+                    }
+                    umma_commit(empty0 + 8 * s);
+                }
+                umma_commit(tfull0 + 8 * acc);
+            }
+        }
+    } else if (warp >= 4) {
+        // ================= epilogue (overlaps the next tile's MMAs) =================
+        const int e = warp - 4;
+        uint8_t *boxes = boxes_all + e * 2 * 4096;
+        uint32_t lt = 0, nstore = 0;
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++lt) {
+            const int m0 = (t % tiles_m) * BLOCK_M, n0 = (t / tiles_m) * P_BLOCK_N;
+            const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
+            mbar_wait(tfull0 + 8 * acc, aph);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            for (int c = 0; c < P_BLOCK_N / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(32 * e) << 16) + acc * P_BLOCK_N + (uint32_t)(32 * c), v);
+                if (c == P_BLOCK_N / 32 - 1) {   // accumulator fully read: hand it back to the MMA warp
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
+                }
+                uint8_t *box = boxes + (nstore & 1) * 4096;
+                if (nstore >= 2) {               // the store issued two chunks ago has finished reading this box
+                    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                    __syncwarp();
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float f[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int col = n0 + 32 * c + 4 * j + q;
+                        f[q] = __uint_as_float(v[4 * j + q]);
+                        if (p.bias && col < p.N) f[q] += p.bias[col];
+                        if (p.relu) f[q] = fmaxf(f[q], 0.f);
+                    }
+                    *reinterpret_cast<float4 *>(box + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_float4(f[0], f[1], f[2], f[3]);
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) {
+                    const int c0 = n0 + 32 * c, c1 = m0 + 32 * e;
+                    if (c0 < p.N && c1 < p.M) {
+                        if (p.tma_epi == 2)
+                            asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%1, %2}], [%3];"
+                                         ::"l"(&tmC), "r"(c0), "r"(c1), "r"(smem_u32(box)) : "memory");
+                        else
+                            asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%1, %2}], [%3];"
+                                         ::"l"(&tmC), "r"(c0), "r"(c1), "r"(smem_u32(box)) : "memory");
+                    }
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");   // (possibly empty) group: keeps the count in step
+                }
+                ++nstore;
+            }
+        }
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+
+    __syncthreads();
+    if (warp == 2) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+    }
+}
+
 } // namespace tc
 
 // ---------------------------------------------------------------------------
@@ -335,6 +514,32 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
         (g.beta == 0.f || g.beta == 1.f) && !(g.relu && (g.beta == 1.f || grid.z > 1))) {
         MMV_TRY(make_map(&tc_map, g.C, g.N, g.M, g.ldc, 32, 32, true));
         p.tma_epi = (g.beta == 1.f || grid.z > 1) ? 2 : 1;
+    }
+    // many-tile products: persistent 128 x 256 kernel (operand ring never drains, epilogue overlapped)
+    static int num_sms = 0, persist_mode = -1;
+    if (num_sms == 0) {
+        int dev = 0;
+        MMV_CUDA(cudaGetDevice(&dev));
+        MMV_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+        const char *e = getenv("MMV_GEMM_PERSIST");
+        persist_mode = e ? atoi(e) : 1;
+    }
+    const int ptiles = ceil_div(g.M, BLOCK_M) * ceil_div(g.N, P_BLOCK_N);
+    if (persist_mode > 0 && p.tma_epi && !g.Cb && grid.z == 1 && ptiles >= 4 * num_sms) {
+        if (!g.b_mn) MMV_TRY(make_map(&tb, g.B, g.K, g.N, g.ldb, BLOCK_K, P_BLOCK_N));
+        void (*pk)(const CUtensorMap, const CUtensorMap, const CUtensorMap, params_t) =
+            g.a_mn ? (g.b_mn ? gemm_tc_persist_kernel<true, true> : gemm_tc_persist_kernel<true, false>)
+                   : (g.b_mn ? gemm_tc_persist_kernel<false, true> : gemm_tc_persist_kernel<false, false>);
+        static bool pattr[4] = { false, false, false, false };
+        const int pvi = (g.a_mn ? 2 : 0) + (g.b_mn ? 1 : 0);
+        if (!pattr[pvi]) {
+            MMV_CUDA(cudaFuncSetAttribute(pk, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM_BYTES));
+            pattr[pvi] = true;
+        }
+        pk<<<std::min(ptiles, num_sms), THREADS, P_SMEM_BYTES, stream>>>(ta, tb, tc_map, p);
+        ::mmv::count_launch();
+        MMV_CUDA(cudaGetLastError());
+        return 0;
     }
     void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, params_t) =
         g.a_mn ? (g.b_mn ? gemm_tc_kernel<true, true> : gemm_tc_kernel<true, false>)

@@ -414,6 +414,8 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         float wm = -INFINITY;
 #pragma unroll
         for (int h = 0; h < HP; ++h) {
+            vp[h] = 0ull;
+            if (h * 2 * kT + warp * 64 >= nj) continue;   // warp-uniform: the whole warp sits on the padding
             const int jj = 2 * tid + h * 2 * kT;
             vp[h] = add2(*reinterpret_cast<const f2_t *>(sG + jj), *reinterpret_cast<const f2_t *>(s_ab + jj));
             float x0, x1;
@@ -426,6 +428,7 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         f2_t ws2 = 0ull;
 #pragma unroll
         for (int h = 0; h < HP; ++h) {
+            if (h * 2 * kT + warp * 64 >= nj) continue;
             float y0, y1;
             up2(fma2(vp[h], l2e, ncw), y0, y1);
             vp[h] = pk2(ex2_f(y0), ex2_f(y1));      // ex2(-inf) = 0 on the padding
@@ -471,6 +474,7 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
             const f2_t scale2 = bc2(scale), depth2 = bc2(depth), zn2 = bc2(zn);
 #pragma unroll
             for (int h = 0; h < HP; ++h) {
+                if (h * 2 * kT + warp * 64 >= nj) continue;
                 const int jj = 2 * tid + h * 2 * kT;
                 const f2_t wn2 = *reinterpret_cast<const f2_t *>(s_wn + jj);
                 const f2_t ub2 = *reinterpret_cast<const f2_t *>(s_ub + jj);
@@ -545,20 +549,23 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
             const float coef = depth * a.inv_B;
             // ---- pass 3: dL/dlogit_j = (d_i / B) p_j (g_j - s_i), one coalesced store per pair
             const f2_t coef2 = bc2(coef), ns2 = bc2(-s);
+            if (a.dlogits_bf16) {
+                __nv_bfloat16 *orow = reinterpret_cast<__nv_bfloat16 *>(a.dlogits_bf16) + (size_t)row * D + j0 + 2 * tid;
 #pragma unroll
-            for (int h = 0; h < HP; ++h) {
-                const int jj = 2 * tid + h * 2 * kT;
-                if (jj < nj) {
-                    const f2_t gq = *reinterpret_cast<const f2_t *>(s_g + jj);
+                for (int h = 0; h < HP; ++h) {
+                    const int jj = 2 * tid + h * 2 * kT;
                     float o0, o1;
-                    up2(mul2(mul2(vp[h], coef2), add2(gq, ns2)), o0, o1);
-                    if (a.dlogits_bf16) {
-                        const __nv_bfloat162 b = __floats2bfloat162_rn(o0, o1);
-                        *reinterpret_cast<__nv_bfloat162 *>(reinterpret_cast<__nv_bfloat16 *>(a.dlogits_bf16) +
-                                                            (size_t)row * D + j0 + jj) = b;
-                    } else {
-                        *reinterpret_cast<float2 *>(a.dlogits + (size_t)row * D + j0 + jj) = make_float2(o0, o1);
-                    }
+                    up2(mul2(mul2(vp[h], coef2), add2(*reinterpret_cast<const f2_t *>(s_g + jj), ns2)), o0, o1);
+                    if (jj < nj) *reinterpret_cast<__nv_bfloat162 *>(orow + h * 2 * kT) = __floats2bfloat162_rn(o0, o1);
+                }
+            } else {
+                float *orow = a.dlogits + (size_t)row * D + j0 + 2 * tid;
+#pragma unroll
+                for (int h = 0; h < HP; ++h) {
+                    const int jj = 2 * tid + h * 2 * kT;
+                    float o0, o1;
+                    up2(mul2(mul2(vp[h], coef2), add2(*reinterpret_cast<const f2_t *>(s_g + jj), ns2)), o0, o1);
+                    if (jj < nj) *reinterpret_cast<float2 *>(orow + h * 2 * kT) = make_float2(o0, o1);
                 }
             }
             if (rank == 0 && tid == 0) {

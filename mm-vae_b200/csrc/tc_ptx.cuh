@@ -28,6 +28,12 @@ mbar_expect_tx(uint32_t bar, uint32_t bytes)
 }
 
 __device__ __forceinline__ void
+mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void
 mbar_wait(uint32_t bar, uint32_t parity)
 {
     asm volatile(

@@ -59,3 +59,23 @@ def test_gemm_f32(mmv, ctx, M, N, K, a_mn, b_mn):
     ref = A.astype(np.float64) @ B.astype(np.float64).T
     got = mmv.test_gemm(ctx, A.T.copy() if a_mn else A, B.T.copy() if b_mn else B, a_mn, b_mn, use_tc=False)
     assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-5
+
+
+@pytest.mark.parametrize("M,N,K", [(1000, 20008, 200), (1152, 17000, 136)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("beta", [0.0, 1.0])
+def test_gemm_tc_persistent(mmv, ctx, M, N, K, a_mn, b_mn, beta):
+    """Many-tile products take the persistent 128 x 256 kernel (double-buffered TMEM accumulator, TMA
+    store / reduce-add epilogue overlapped with the next tile): edge tiles in M and N, every layout."""
+    if (a_mn and M % 8) or (b_mn and N % 8) or (not a_mn and K % 8) or (not b_mn and K % 8):
+        pytest.skip("leading dimension not a multiple of 8")
+    rng = np.random.default_rng(M + N + K)
+    A = rng.normal(size=(M, K)).astype(np.float32)
+    B = rng.normal(size=(N, K)).astype(np.float32)
+    bias = rng.normal(size=N).astype(np.float32)
+    C0 = rng.normal(size=(M, N)).astype(np.float32)
+    ref = bf16_round(A) @ bf16_round(B).T + bias[None, :] + beta * C0
+    got = mmv.test_gemm(ctx, A.T.copy() if a_mn else A, B.T.copy() if b_mn else B, a_mn, b_mn, bias=bias,
+                        beta=beta, C_in=C0)
+    err = np.abs(got - ref).max() / np.abs(ref).max()
+    assert err < 1e-5, err
