@@ -130,22 +130,36 @@ colsum_kernel(colsum_args_t a)
     float sc[8];
 #pragma unroll
     for (int c = 0; c < 8; ++c) sc[c] = 0.f;
-    for (int i = r0; i < r1; ++i) {
-        const float v = a.Xb ? __bfloat162float(reinterpret_cast<const __nv_bfloat16 *>(a.Xb)[(size_t)i * a.ldx + col])
-                             : a.X[(size_t)i * a.ldx + col];
-        s += v;
-        if (a.out_cov) {
-            const int64_t cell = a.cells ? (int64_t)a.cells[i] : (int64_t)i;
+    const bool gather = a.out_cov != nullptr && a.cov != nullptr;
+    for (int ib = r0; ib < r1; ib += 8) {      // 8 rows in flight
+        float v[8];
+        int64_t cell[8];
 #pragma unroll
-            for (int c = 0; c < 8; ++c)
-                if (c < a.C) sc[c] = fmaf(v, a.cov ? a.cov[cell * a.C + c] : 1.f, sc[c]);
+        for (int u = 0; u < 8; ++u) {
+            const int i = ib + u;
+            v[u] = 0.f;
+            cell[u] = 0;
+            if (i < r1) {
+                v[u] = a.Xb ? __bfloat162float(reinterpret_cast<const __nv_bfloat16 *>(a.Xb)[(size_t)i * a.ldx + col])
+                            : a.X[(size_t)i * a.ldx + col];
+                if (gather) cell[u] = a.cells ? (int64_t)a.cells[i] : (int64_t)i;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            s += v[u];
+            if (gather) {
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    if (c < a.C) sc[c] = fmaf(v[u], a.cov[cell[u] * a.C + c], sc[c]);
+            }
         }
     }
     if (a.out_sum) atomicAdd(a.out_sum + col, s);
     if (a.out_sum2) atomicAdd(a.out_sum2 + col, s);
     if (a.out_sum3) atomicAdd(a.out_sum3 + col, s);
-    if (a.out_cov)
-        for (int c = 0; c < a.C; ++c) atomicAdd(a.out_cov + (size_t)col * a.C + c, sc[c]);
+    if (a.out_cov)   // all-ones covariates (cov == nullptr): every covariate column sees the plain sum
+        for (int c = 0; c < a.C; ++c) atomicAdd(a.out_cov + (size_t)col * a.C + c, gather ? sc[c] : s);
 }
 
 // bf16 input, all-ones covariates, N % 8 == 0: each thread owns 8 adjacent columns (one 16-byte load

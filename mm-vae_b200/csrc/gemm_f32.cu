@@ -113,8 +113,8 @@ launch_gemm_f32(const gemm_args_t &g, cudaStream_t stream)
     dim3 grid(ceil_div(g.N, BN), ceil_div(g.M, BM));
     const int tiles = (int)(grid.x * grid.y);
     if (tiles <= 32 && g.K >= 1024 && !g.relu && (g.beta == 1.f || (g.beta == 0.f && g.ldc == g.N))) {
-        int splits = g.K / 256;
-        if (splits > 128 / tiles) splits = 128 / tiles;
+        int splits = g.K / 64;                      // few output tiles, long K: spread K over the machine
+        if (splits > 256 / tiles) splits = 256 / tiles;
         if (splits > 1) {
             const int per = ceil_div(ceil_div(g.K, splits), BK) * BK;
             splits = ceil_div(g.K, per);

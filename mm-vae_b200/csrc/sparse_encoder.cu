@@ -163,6 +163,37 @@ senc_bias_kernel(const float *W1T, const float *x_mean, const float *inv_t, cons
                  float *bias_eff, int D, int h1, int genes_per_cta, int angular)
 {
     const int j0 = blockIdx.x * genes_per_cta, j1 = min(D, j0 + genes_per_cta);
+    if (h1 % 4 == 0 && (reinterpret_cast<uintptr_t>(W1T) & 15) == 0) {
+        // 16-byte loads, 8 genes in flight per thread: the [D x h1] weight is read once at HBM speed
+        for (int c4 = threadIdx.x; c4 < h1 / 4; c4 += blockDim.x) {
+            float s[4] = { 0.f, 0.f, 0.f, 0.f };
+            for (int jb = j0; jb < j1; jb += 8) {
+                float4 w[8];
+                float f[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int j = min(jb + u, j1 - 1);
+                    w[u] = *reinterpret_cast<const float4 *>(W1T + (size_t)j * h1 + 4 * c4);
+                    f[u] = jb + u < j1 ? x_mean[j] * inv_t[j] : 0.f;
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    float v[4] = { w[u].x, w[u].y, w[u].z, w[u].w };
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        if (angular) v[q] = fmaxf(v[q], 0.f) + 1e-4f;
+                        s[q] = fmaf(f[u], v[q], s[q]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (angular) s[q] *= col_scale[4 * c4 + q];
+                if (s[q] != 0.f) atomicAdd(bias_eff + 4 * c4 + q, -s[q]);
+            }
+        }
+        return;
+    }
     for (int col = threadIdx.x; col < h1; col += blockDim.x) {
         float s = 0.f;
         for (int j = j0; j < j1; ++j) {
@@ -179,7 +210,7 @@ int
 launch_senc_bias(const float *W1T, const float *x_mean, const float *inv_t, const float *col_scale,
                  float *bias_eff, int D, int h1, int angular, cudaStream_t st)
 {
-    const int gpc = 64;
+    const int gpc = 32;
     senc_bias_kernel<<<ceil_div(D, gpc), 256, 0, st>>>(W1T, x_mean, inv_t, col_scale, bias_eff, D, h1, gpc, angular); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
