@@ -249,7 +249,7 @@ def cpu_reference_run(w, model, steps=None, warmup=1, budget_s=20.0, B=256):
 # ---------------------------------------------------------------------------
 # algorithmic work per kernel group (restated in DESIGN.md)
 # ---------------------------------------------------------------------------
-def kernel_work(w, B, bf16=True):
+def kernel_work(w, B, bf16=True, n_gpus=1):
     D, h1, R, H, Rn = w["genes"], w["enc"][0], w["latent"], w["nu_h"], w["nu_r"]
     dl = w["dec"][-1]
     nnz = w["density"] * D * B
@@ -277,9 +277,10 @@ def kernel_work(w, B, bf16=True):
                     ("hbm", 8 * nnz + 4.0 * B * (h1 + H + 1) + 8.0 * D * h1 + 16.0 * D),
         "colsum_dlogits": ("hbm", (2.0 if bf16 else 4.0) * B * D),
         "panel_build": ("hbm", 8 * nnz + 8 * nnz + 8 * (B + 1)),
-        # K6: P ~ D (h1 + d_last) parameters; sumsq reads 4 B, Adam reads 16 + writes 12 (p, m, v; the clip
-        # scale of .grad is applied when the gradient is read) + bf16 mirror 2
-        "clip_adam": ("hbm", 34.0 * D * (h1 + dl)),
+        # K6: P ~ D (h1 + d_last) parameters; Adam reads 16 + writes 12 (p, m, v; the clip scale of .grad is
+        # applied when the gradient is read) + bf16 mirror 2; the two D x h gradients' ||g||^2 comes from
+        # their producing kernels (1 GPU), so the separate sumsq pass only reads the small tensors
+        "clip_adam": ("hbm", (30.0 if n_gpus == 1 else 34.0) * D * (h1 + dl)),
     }
 
 
@@ -411,7 +412,7 @@ def run_own(args):
         return
 
     pk = peaks()
-    work = kernel_work(w, B, args.dtype == "bf16")
+    work = kernel_work(w, B, args.dtype == "bf16", world)
     kernels = {}
     for name, (t, c) in prof.items():
         per = t / c

@@ -164,7 +164,17 @@ csr_check_sorted_kernel(const int64_t *indptr, const int32_t *indices, int64_t n
     bool bad = false;
     for (int64_t i = warp; i < n_cells; i += nwarp) {
         const int64_t b = indptr[i], e = indptr[i + 1];
-        for (int64_t q = b + 1 + lane; q < e; q += 32) bad |= indices[q] <= indices[q - 1];
+        for (int64_t q0 = b + 1; q0 < e; q0 += 32 * 8) {   // 8 independent loads in flight per lane
+            int cur[8], prev[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int64_t q = q0 + lane + 32 * u;
+                cur[u] = q < e ? indices[q] : 0x7fffffff;
+                prev[u] = q < e ? indices[q - 1] : -1;
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) bad |= cur[u] <= prev[u];
+        }
     }
     if (__any_sync(0xffffffffu, bad) && lane == 0) *flag = 1;
 }

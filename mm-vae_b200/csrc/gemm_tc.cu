@@ -32,12 +32,11 @@ namespace mmv {
 namespace tc {
 
 constexpr int BLOCK_M = 128, BLOCK_N = 128, BLOCK_K = 64, UMMA_K = 16;
-constexpr int STAGES = 3;
 constexpr int THREADS = 256;
 constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2, B_BYTES = BLOCK_N * BLOCK_K * 2;
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int TMEM_COLS = 128;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int smem_bytes(int stages) { return stages * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/; }
 
 struct params_t {
     float *C;
@@ -47,10 +46,13 @@ struct params_t {
     float beta;
     int relu;
     int tma_epi;   // 0: register epilogue ; 1: TMA tile store ; 2: TMA reduce-add (beta = 1 or split-K)
+    double *sumsq; // persistent store epilogue: += sum of squares of the product
 };
 
-template <bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(THREADS, 2)
+// STAGES = 3: two CTAs per SM (many-tile grids) ; STAGES = 6: one CTA per SM with a deeper ring, for
+// single-wave grids whose short K loop is bound by the TMA round trip
+template <bool A_MN, bool B_MN, int STAGES>
+__global__ void __launch_bounds__(THREADS, STAGES <= 3 ? 2 : 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmC, params_t p)
 {
@@ -352,6 +354,7 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         const int e = warp - 4;
         uint8_t *boxes = boxes_all + e * 2 * 4096;
         uint32_t lt = 0, nstore = 0;
+        float ss = 0.f;
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++lt) {
             const int m0 = (t % tiles_m) * BLOCK_M, n0 = (t / tiles_m) * P_BLOCK_N;
             const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
@@ -380,6 +383,7 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                         if (p.bias && col < p.N) f[q] += p.bias[col];
                         if (p.relu) f[q] = fmaxf(f[q], 0.f);
                     }
+                    ss += f[0] * f[0] + f[1] * f[1] + f[2] * f[2] + f[3] * f[3];   // out-of-range parts of edge tiles are zero (no bias: launcher)
                     *reinterpret_cast<float4 *>(box + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_float4(f[0], f[1], f[2], f[3]);
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -401,6 +405,10 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         }
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         __syncwarp();
+        if (p.sumsq) {
+            ss = warp_sum(ss);
+            if (lane == 0) atomicAdd(p.sumsq, (double)ss);
+        }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
 
@@ -491,6 +499,8 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
     params_t p;
     p.C = g.C; p.Cb = reinterpret_cast<__nv_bfloat16 *>(g.Cb); p.bias = g.bias;
     p.M = g.M; p.N = g.N; p.K = g.K; p.ldc = g.ldc; p.ldcb = g.ldcb; p.beta = g.beta; p.relu = g.relu;
+    p.sumsq = nullptr;
+    if (g.sumsq_done) *g.sumsq_done = 0;
     dim3 grid(ceil_div(g.N, BLOCK_N), ceil_div(g.M, BLOCK_M));
     const int tiles = (int)(grid.x * grid.y), total_kb = ceil_div(g.K, BLOCK_K);
     if (tiles <= 64 && total_kb >= 16 && !g.relu && !g.Cb && g.C && (g.beta == 1.f || (g.beta == 0.f && g.ldc == g.N))) {
@@ -527,6 +537,10 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
     const int ptiles = ceil_div(g.M, BLOCK_M) * ceil_div(g.N, P_BLOCK_N);
     if (persist_mode > 0 && p.tma_epi && !g.Cb && grid.z == 1 && ptiles >= 4 * num_sms) {
         if (!g.b_mn) MMV_TRY(make_map(&tb, g.B, g.K, g.N, g.ldb, BLOCK_K, P_BLOCK_N));
+        if (g.sumsq && p.tma_epi == 1 && !g.bias) {
+            p.sumsq = g.sumsq;
+            if (g.sumsq_done) *g.sumsq_done = 1;
+        }
         void (*pk)(const CUtensorMap, const CUtensorMap, const CUtensorMap, params_t) =
             g.a_mn ? (g.b_mn ? gemm_tc_persist_kernel<true, true> : gemm_tc_persist_kernel<true, false>)
                    : (g.b_mn ? gemm_tc_persist_kernel<false, true> : gemm_tc_persist_kernel<false, false>);
@@ -541,16 +555,22 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
         MMV_CUDA(cudaGetLastError());
         return 0;
     }
-    void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, params_t) =
-        g.a_mn ? (g.b_mn ? gemm_tc_kernel<true, true> : gemm_tc_kernel<true, false>)
-               : (g.b_mn ? gemm_tc_kernel<false, true> : gemm_tc_kernel<false, false>);
-    static bool attr_set[4] = { false, false, false, false };
-    const int vi = (g.a_mn ? 2 : 0) + (g.b_mn ? 1 : 0);
+    const bool deep = (int)(grid.x * grid.y * grid.z) <= num_sms && ceil_div(total_kb, (int)grid.z) >= 6;
+    void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, params_t);
+    if (deep)
+        kern = g.a_mn ? (g.b_mn ? gemm_tc_kernel<true, true, 6> : gemm_tc_kernel<true, false, 6>)
+                      : (g.b_mn ? gemm_tc_kernel<false, true, 6> : gemm_tc_kernel<false, false, 6>);
+    else
+        kern = g.a_mn ? (g.b_mn ? gemm_tc_kernel<true, true, 3> : gemm_tc_kernel<true, false, 3>)
+                      : (g.b_mn ? gemm_tc_kernel<false, true, 3> : gemm_tc_kernel<false, false, 3>);
+    static bool attr_set[8] = { false, false, false, false, false, false, false, false };
+    const int vi = (deep ? 4 : 0) + (g.a_mn ? 2 : 0) + (g.b_mn ? 1 : 0);
+    const int smem = smem_bytes(deep ? 6 : 3);
     if (!attr_set[vi]) {
-        MMV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        MMV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_set[vi] = true;
     }
-    kern<<<grid, THREADS, SMEM_BYTES, stream>>>(ta, tb, tc_map, p);
+    kern<<<grid, THREADS, smem, stream>>>(ta, tb, tc_map, p);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;

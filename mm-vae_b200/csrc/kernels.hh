@@ -35,6 +35,10 @@ struct gemm_tc_args_t {
     int M = 0, N = 0, K = 0;
     float beta = 0.f;
     int relu = 0;
+    // optional: add sum(C^2) of the finished product to *sumsq (global-norm clip without a second pass);
+    // *sumsq_done is set to 1 when the chosen kernel did it (persistent store epilogue), else 0
+    double *sumsq = nullptr;
+    int *sumsq_done = nullptr;
 };
 bool gemm_tc_supported(const gemm_tc_args_t &g);
 int launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream);
@@ -145,6 +149,7 @@ struct senc_tc_args_t {
     int angular = 0, accumulate = 1;
     float *dW1T = nullptr;
     float *S = nullptr;                 // [D x h1] raw product A^T delta (may alias dW1T when accumulate = 0)
+    double *sumsq = nullptr;            // row pass: += sum(dW1T^2) (accumulate = 0 only)
 };
 bool senc_tc_supported(int h1);
 int launch_senc_tc_fwd(const senc_tc_args_t &a, cudaStream_t st);

@@ -123,6 +123,7 @@ struct mmv_model {
     std::map<std::string, dbuf_t> ws;
     double *acc = nullptr;                // device: [0] nll/-, [1] kl_mu, [2] kl_nu, [3] sumsq, [4] t_acc, [5] llik_sum
     float *fscal = nullptr;               // device: [0] kappa, [1] grad norm, [2] clip coefficient
+    std::vector<std::pair<size_t, size_t>> ss_done;   // gradient ranges whose sum of squares a producer already added to acc[3]
     bool grad_lazy = false;               // the clip scale of the last fused step is still to be applied to .grad
     size_t grad_lazy_n = 0;               //   ... over grads[0, grad_lazy_n)
     double *h_acc = nullptr;              // pinned mirrors
@@ -699,7 +700,7 @@ lin_bwd_data(const step_t &s, const float *dY, int out, const float *W, int in, 
 // dW += dY^T X ; db += colsum(dY)
 int
 lin_bwd_weight(const step_t &s, const float *dY, int out, const float *X, int in, float *dW, float *db, float beta = 1.f,
-               const char *tag = "gemm_other", const void *dY_bf = nullptr)
+               const char *tag = "gemm_other", const void *dY_bf = nullptr, double *sumsq = nullptr, int *sumsq_done = nullptr)
 {
     mmv_model *m = s.m;
     if (dW && tc_ok(s, out, in, s.B, out, in)) {
@@ -707,7 +708,7 @@ lin_bwd_weight(const step_t &s, const float *dY, int out, const float *X, int in
         if (dY_bf) t.A = dY_bf; else MMV_TRY(bf16_of(s, dY, (size_t)s.B * out, &t.A));
         MMV_TRY(bf16_of(s, X, (size_t)s.B * in, &t.B));
         t.a_mn = 1; t.lda = out; t.b_mn = 1; t.ldb = in; t.C = dW; t.ldc = in; t.M = out; t.N = in; t.K = s.B;
-        t.beta = beta;
+        t.beta = beta; t.sumsq = sumsq; t.sumsq_done = sumsq_done;
         PROF(tag);
         MMV_TRY(launch_gemm_tc(t, s.st));
     } else if (dW) {
@@ -798,10 +799,14 @@ decoder_backward(const step_t &s)
         const float *X = l == 0 ? m->ws["z"].as<float>() : m->ws["dec_act" + std::to_string(l - 1)].as<float>();
         const bool last = l == nd - 1;
         // bias of the last layer is handled with the other per-gene sums by the caller
+        // single GPU, optimiser step in the same call: the overwriting GEMM also adds ||dW||^2 to the clip norm
+        const bool fuse_ss = last && s.optim && m->ctx->nranks == 1 && m->optimised(L.w);
+        int ss_ok = 0;
         MMV_TRY(lin_bwd_weight(s, dY, L.out, X, L.in, m->want_grad(L.w) ? m->G(L.w) : nullptr,
                                (!last && m->want_grad(L.b)) ? m->G(L.b) : nullptr,
                                (last && m->optimised(L.w)) ? 0.f : 1.f,   // mmv_step leaves this one un-zeroed
-                               last ? "gemm_dec_last_dw" : "gemm_other", dY_bf));
+                               last ? "gemm_dec_last_dw" : "gemm_other", dY_bf, fuse_ss ? m->acc + 3 : nullptr, &ss_ok));
+        if (ss_ok) m->ss_done.emplace_back(m->tensors[L.w].off, m->tensors[L.w].off + m->tensors[L.w].numel());
         if (last && s.optim && m->ctx->nranks > 1 && m->optimised(L.w)) {
             // first bucket: the largest gradient is complete long before backward ends — reduce it under the rest
             m->early_off = m->tensors[L.w].off;
@@ -952,6 +957,11 @@ senc_tc_backward(const step_t &s, const senc_bwd_args_t &b)
     // raw product straight into the gradient when it is overwritten anyway, else into a scratch buffer
     if (a.dW1T && !a.accumulate) a.S = a.dW1T;
     else { a.S = WS("pan_S", (size_t)D * h1); NEED(a.S); }
+    const linear_t &L0 = m->enc[0];
+    if (!b.angular && a.dW1T && !a.accumulate && s.optim && m->ctx->nranks == 1 && m->optimised(L0.w)) {
+        a.sumsq = m->acc + 3;   // the row pass writes the final gradient: it adds ||dW1||^2 to the clip norm on the way
+        m->ss_done.emplace_back(m->tensors[L0.w].off, m->tensors[L0.w].off + m->tensors[L0.w].numel());
+    }
     PROF("senc_bwd");
     MMV_TRY(launch_senc_tc_bwd(a, s.st));
     MMV_TRY(launch_senc_row_pass(a, b.ln_x_sd, b.dx_mean, b.dln_x_sd, s.st));
@@ -1333,6 +1343,7 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         s.klw = kl_weight; s.inv_B = 1.f / (float)(B * nranks); s.bwd = (flags & MMV_BWD) != 0; s.st = st;
         s.optim = (flags & MMV_OPTIM) != 0;
         m->early_off = m->early_n = 0;
+        m->ss_done.clear();
         MMV_TRY(stage_inputs(m, csr, cells, B, boot_idx, eps, flags, s));
         if (csr->ev_ready) MMV_CUDA(cudaStreamWaitEvent(st, csr->ev_ready, 0));   // streamed slot: its upload is done
         m->last_B = B;
@@ -1389,7 +1400,17 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
             }
         }
         PROF("clip_adam");
-        MMV_TRY(launch_sumsq(m->grads, n_opt, m->acc + 3, m->ctx->num_sms, st));
+        if (!(flags & MMV_FWD)) m->ss_done.clear();   // acc[3] was re-zeroed: nothing carried over
+        std::sort(m->ss_done.begin(), m->ss_done.end());
+        {
+            size_t pos = 0;
+            for (size_t i = 0; i <= m->ss_done.size(); ++i) {
+                const size_t end = i < m->ss_done.size() ? std::min(m->ss_done[i].first, n_opt) : n_opt;
+                if (end > pos) MMV_TRY(launch_sumsq(m->grads + pos, end - pos, m->acc + 3, m->ctx->num_sms, st));
+                if (i < m->ss_done.size()) pos = std::max(pos, std::min(m->ss_done[i].second, n_opt));
+            }
+            m->ss_done.clear();
+        }
         adam_args_t a;
         m->adam_t += 1;
         const double bc1 = 1. - std::pow(0.9, (double)m->adam_t), bc2 = 1. - std::pow(0.999, (double)m->adam_t);

@@ -580,9 +580,11 @@ launch_tc(const senc_tc_args_t &a, cudaStream_t st)
 __global__ void __launch_bounds__(256)
 senc_row_pass_kernel(senc_tc_args_t a, const float *ln_x_sd, float *dx_mean, float *dln_x_sd)
 {
+    __shared__ float s_ss[8];
     const int lane = threadIdx.x & 31;
     const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (j >= a.D) return;
+    float ss = 0.f;
+    if (j < a.D) {
     const float it = a.inv_t[j], xm = a.x_mean[j], xmit = xm * it;
     const float4 *S4 = reinterpret_cast<const float4 *>(a.S + (size_t)j * a.h1);
     const float4 *W4 = reinterpret_cast<const float4 *>(a.W1T + (size_t)j * a.h1);
@@ -608,6 +610,7 @@ senc_row_pass_kernel(senc_tc_args_t a, const float *ln_x_sd, float *dx_mean, flo
                 o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
             }
             O4[n] = o;
+            ss += o.x * o.x + o.y * o.y + o.z * o.z + o.w * o.w;
         }
     }
     d0 = warp_sum(d0);
@@ -616,6 +619,17 @@ senc_row_pass_kernel(senc_tc_args_t a, const float *ln_x_sd, float *dx_mean, flo
         dx_mean[j] += -d1 * it;
         const float dt = -(d0 - xmit * d1) * it;
         dln_x_sd[j] += dt * sigmoid_f(ln_x_sd[j]);   // d softplus
+    }
+    }
+    if (a.sumsq) {   // global-norm clip: this gradient's share of ||g||^2, one atomic per CTA
+        ss = warp_sum(ss);
+        if (lane == 0) s_ss[threadIdx.x >> 5] = ss;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float t = 0.f;
+            for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += s_ss[w];
+            atomicAdd(a.sumsq, (double)t);
+        }
     }
 }
 

@@ -300,5 +300,6 @@ def test_fused_step_equals_split_step(mmv, ctx, dtype):
         m.close()
     csr.close()
     for k in res[0][0]:
-        assert rel_err(res[1][0][k], res[0][0][k]) < 1e-5, ("grad", k)
+        # (the fused step adds ||dW||^2 from the producing kernels: a different fp32 summation order for the clip norm)
+        assert rel_err(res[1][0][k], res[0][0][k]) < 1e-4, ("grad", k)
         assert rel_err(res[1][1][k], res[0][1][k]) < 1e-4, ("param", k)
