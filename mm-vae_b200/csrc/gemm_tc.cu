@@ -535,7 +535,7 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
         persist_mode = e ? atoi(e) : 1;
     }
     const int ptiles = ceil_div(g.M, BLOCK_M) * ceil_div(g.N, P_BLOCK_N);
-    if (persist_mode > 0 && p.tma_epi && !g.Cb && grid.z == 1 && ptiles >= 4 * num_sms) {
+    if (persist_mode > 0 && p.tma_epi && !g.Cb && grid.z == 1 && ptiles >= 2 * num_sms) {
         if (!g.b_mn) MMV_TRY(make_map(&tb, g.B, g.K, g.N, g.ldb, BLOCK_K, P_BLOCK_N));
         if (g.sumsq && p.tma_epi == 1 && !g.bias) {
             p.sumsq = g.sumsq;

@@ -150,6 +150,7 @@ struct senc_tc_args_t {
     float *dW1T = nullptr;
     float *S = nullptr;                 // [D x h1] raw product A^T delta (may alias dW1T when accumulate = 0)
     double *sumsq = nullptr;            // row pass: += sum(dW1T^2) (accumulate = 0 only)
+    int tile0 = 0, ntiles = 0;          // backward + row pass: restrict to 128-gene tiles [tile0, tile0 + ntiles) (0 = all)
 };
 bool senc_tc_supported(int h1);
 int launch_senc_tc_fwd(const senc_tc_args_t &a, cudaStream_t st);

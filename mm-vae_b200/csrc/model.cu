@@ -8,6 +8,8 @@
 #include "common.cuh"
 #include "internal.hh"
 
+#include <cuda_bf16.h>
+
 #include <algorithm>
 #include <cmath>
 #include <map>
@@ -99,7 +101,7 @@ struct mmv_model {
     size_t n_reg = 0, n_all = 0;          // floats in the registered prefix / whole buffer
     float *params = nullptr, *grads = nullptr, *adam_m = nullptr, *adam_v = nullptr;
     int64_t adam_t = 0;
-    size_t early_off = 0, early_n = 0;   // gradient range already handed to the comm stream this step
+    std::vector<std::pair<size_t, size_t>> ar_done;   // gradient ranges already handed to the comm stream this step
 
     std::vector<linear_t> enc, dec;       // enc[0] = sparse first layer; dec.back() = layer onto D genes
     int t_x_mean = -1, t_ln_x_sd = -1, t_mu_bias = -1, t_nu_bias = -1, t_ln_kappa = -1;
@@ -784,6 +786,18 @@ decoder_forward(const step_t &s)
     return lin_fwd(s, h, L.in, m->P(L.w), nullptr, D, G, false, "gemm_dec_last_fwd", /*want_twin=*/false);
 }
 
+// hand a finished gradient range to the comm stream (multi-GPU, optimiser step in this call)
+int
+allreduce_grad_async(const step_t &s, int t)
+{
+    mmv_model *m = s.m;
+    if (!(s.optim && m->ctx->nranks > 1 && m->optimised(t))) return 0;
+    const size_t off = m->tensors[t].off, n = m->tensors[t].numel();
+    MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off, n));
+    m->ar_done.emplace_back(off, off + n);
+    return 0;
+}
+
 // backward through the decoder given dG (in "G", in place) -> "dz"
 int
 decoder_backward(const step_t &s)
@@ -806,13 +820,9 @@ decoder_backward(const step_t &s)
                                (!last && m->want_grad(L.b)) ? m->G(L.b) : nullptr,
                                (last && m->optimised(L.w)) ? 0.f : 1.f,   // mmv_step leaves this one un-zeroed
                                last ? "gemm_dec_last_dw" : "gemm_other", dY_bf, fuse_ss ? m->acc + 3 : nullptr, &ss_ok));
+        // multi GPU, first bucket: the largest gradient is final long before backward ends — reduce it under the rest
+        if (last && m->want_grad(L.w)) MMV_TRY(allreduce_grad_async(s, L.w));
         if (ss_ok) m->ss_done.emplace_back(m->tensors[L.w].off, m->tensors[L.w].off + m->tensors[L.w].numel());
-        if (last && s.optim && m->ctx->nranks > 1 && m->optimised(L.w)) {
-            // first bucket: the largest gradient is complete long before backward ends — reduce it under the rest
-            m->early_off = m->tensors[L.w].off;
-            m->early_n = m->tensors[L.w].numel();
-            MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + m->early_off, m->early_n));
-        }
         float *dX = l == 0 ? WS("dz", (size_t)B * R) : WS("d_dec" + std::to_string(l - 1), (size_t)B * L.in);
         NEED(dX);
         MMV_TRY(lin_bwd_data(s, dY, L.out, m->P(L.w), L.in, dX, last ? "gemm_dec_last_dx" : "gemm_other", dY_bf));
@@ -963,8 +973,27 @@ senc_tc_backward(const step_t &s, const senc_bwd_args_t &b)
         m->ss_done.emplace_back(m->tensors[L0.w].off, m->tensors[L0.w].off + m->tensors[L0.w].numel());
     }
     PROF("senc_bwd");
-    MMV_TRY(launch_senc_tc_bwd(a, s.st));
-    MMV_TRY(launch_senc_row_pass(a, b.ln_x_sd, b.dx_mean, b.dln_x_sd, s.st));
+    const bool split_ar = !b.angular && a.dW1T && !a.accumulate && s.optim && m->ctx->nranks > 1 && m->optimised(L0.w);
+    const int tiles = (D + 127) / 128, cols = (h1 + 255) / 256;
+    const int waves = (tiles * cols + m->ctx->num_sms - 1) / m->ctx->num_sms;
+    if (split_ar && waves >= 3) {
+        // multi GPU: the gene tiles in two parts of whole waves; the first part's rows of dW1 are all-reduced
+        // on the comm stream while the second part is multiplied (only the smaller second all-reduce is exposed)
+        const int t1 = std::min(tiles - 1, (int)((int64_t)((waves + 1) / 2) * m->ctx->num_sms / cols));
+        const size_t off = m->tensors[L0.w].off;
+        a.tile0 = 0; a.ntiles = t1;
+        MMV_TRY(launch_senc_tc_bwd(a, s.st));
+        MMV_TRY(launch_senc_row_pass(a, b.ln_x_sd, b.dx_mean, b.dln_x_sd, s.st));
+        const size_t n1 = (size_t)std::min(D, t1 * 128) * h1;
+        MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off, n1));
+        m->ar_done.emplace_back(off, off + n1);
+        a.tile0 = t1; a.ntiles = tiles - t1;
+        MMV_TRY(launch_senc_tc_bwd(a, s.st));
+        MMV_TRY(launch_senc_row_pass(a, b.ln_x_sd, b.dx_mean, b.dln_x_sd, s.st));
+    } else {
+        MMV_TRY(launch_senc_tc_bwd(a, s.st));
+        MMV_TRY(launch_senc_row_pass(a, b.ln_x_sd, b.dx_mean, b.dln_x_sd, s.st));
+    }
     if (!b.angular && b.dWnuT)
         MMV_TRY(launch_panel_aux_bwd(a.bucket_ptr, a.ent, m->ws["pan_x"].as<float>(), B, D, b.H, b.dHnu, b.ddpre,
                                      b.dWnuT, b.dwdepth, s.st));
@@ -1113,9 +1142,13 @@ nb_forward_backward(const step_t &s)
     b.dW1T = m->want_grad(L0.w) ? m->G(L0.w) : nullptr;
     b.dx_mean = m->G(m->t_x_mean); b.dln_x_sd = m->G(m->t_ln_x_sd);
     b.dHnu = dHnu; b.ddpre = k.ddpre; b.dWnuT = m->G(m->nu_enc.w); b.dwdepth = m->G(m->depth.w);
-    if (tc_senc) return senc_tc_backward(s, b);
-    PROF("senc_bwd");
-    return launch_senc_bwd(b, s.st);
+    if (tc_senc) {
+        MMV_TRY(senc_tc_backward(s, b));
+    } else {
+        PROF("senc_bwd");
+        MMV_TRY(launch_senc_bwd(b, s.st));
+    }
+    return 0;
 }
 
 // ---------------------------------------------------------------------------
@@ -1229,8 +1262,10 @@ vmf_forward_backward(const step_t &s)
         PROF("senc_bwd");
         MMV_TRY(launch_senc_bwd(b, s.st));
     }
-    if (m->want_grad(L0.w))
+    if (m->want_grad(L0.w)) {
         MMV_TRY(launch_angular_bwd(m->P(L0.w), dWeff, col_scale, dot, m->G(L0.w), h1, D, 1, (size_t)h1, s.st));
+        MMV_TRY(allreduce_grad_async(s, L0.w));
+    }
     return 0;
 }
 
@@ -1342,7 +1377,7 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         s.m = m; s.csr = csr; s.B = (int)B; s.cov = csr->has_cov ? csr->cov : nullptr;
         s.klw = kl_weight; s.inv_B = 1.f / (float)(B * nranks); s.bwd = (flags & MMV_BWD) != 0; s.st = st;
         s.optim = (flags & MMV_OPTIM) != 0;
-        m->early_off = m->early_n = 0;
+        m->ar_done.clear();
         m->ss_done.clear();
         MMV_TRY(stage_inputs(m, csr, cells, B, boot_idx, eps, flags, s));
         if (csr->ev_ready) MMV_CUDA(cudaStreamWaitEvent(st, csr->ev_ready, 0));   // streamed slot: its upload is done
@@ -1389,15 +1424,17 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         }
         {
             PROF("allreduce");
-            if (m->early_n > 0) {   // everything but the bucket already in flight, then wait for it
-                MMV_TRY(comm_allreduce_f32(m->ctx, m->grads, m->early_off));
-                const size_t tail = m->early_off + m->early_n;
-                if (tail < n_opt) MMV_TRY(comm_allreduce_f32(m->ctx, m->grads + tail, n_opt - tail));
-                MMV_TRY(comm_join(m->ctx));
-                m->early_off = m->early_n = 0;
-            } else {
-                MMV_TRY(comm_allreduce_f32(m->ctx, m->grads, n_opt));
+            // everything not yet handed to the comm stream follows the buckets there, then the step waits
+            if (!(flags & MMV_FWD)) m->ar_done.clear();
+            std::sort(m->ar_done.begin(), m->ar_done.end());
+            size_t pos = 0;
+            for (size_t i = 0; i <= m->ar_done.size(); ++i) {
+                const size_t end = i < m->ar_done.size() ? std::min(m->ar_done[i].first, n_opt) : n_opt;
+                if (end > pos) MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + pos, end - pos));
+                if (i < m->ar_done.size()) pos = std::max(pos, std::min(m->ar_done[i].second, n_opt));
             }
+            m->ar_done.clear();
+            MMV_TRY(comm_join(m->ctx));
         }
         PROF("clip_adam");
         if (!(flags & MMV_FWD)) m->ss_done.clear();   // acc[3] was re-zeroed: nothing carried over

@@ -333,7 +333,7 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ 
                    tfull = smem_u32(bars + 3 * STG);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int tile = blockIdx.y, n0 = blockIdx.x * BN;
+    const int tile = blockIdx.y + (BWD ? a.tile0 : 0), n0 = blockIdx.x * BN;
     const int num_kb = BWD ? nT : nK;
 
     if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmD) : "memory");
@@ -565,7 +565,7 @@ launch_tc(const senc_tc_args_t &a, cudaStream_t st)
         MMV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, cfg::SMEM));
         attr = true;
     }
-    dim3 grid(ceil_div(a.h1, BN), BWD ? ceil_div(a.D, BM) : ceil_div(a.B, BM));
+    dim3 grid(ceil_div(a.h1, BN), BWD ? (a.ntiles > 0 ? a.ntiles : ceil_div(a.D, BM)) : ceil_div(a.B, BM));
     kern<<<grid, TCT, cfg::SMEM, st>>>(tm, ts, a, nT, nK);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
@@ -582,9 +582,10 @@ senc_row_pass_kernel(senc_tc_args_t a, const float *ln_x_sd, float *dx_mean, flo
 {
     __shared__ float s_ss[8];
     const int lane = threadIdx.x & 31;
-    const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int j = a.tile0 * 128 + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const int j_end = a.ntiles > 0 ? min(a.D, (a.tile0 + a.ntiles) * 128) : a.D;
     float ss = 0.f;
-    if (j < a.D) {
+    if (j < j_end) {
     const float it = a.inv_t[j], xm = a.x_mean[j], xmit = xm * it;
     const float4 *S4 = reinterpret_cast<const float4 *>(a.S + (size_t)j * a.h1);
     const float4 *W4 = reinterpret_cast<const float4 *>(a.W1T + (size_t)j * a.h1);
@@ -699,7 +700,8 @@ launch_senc_tc_bwd(const senc_tc_args_t &a, cudaStream_t st)
 int
 launch_senc_row_pass(const senc_tc_args_t &a, const float *ln_x_sd, float *dx_mean, float *dln_x_sd, cudaStream_t st)
 {
-    senc_row_pass_kernel<<<ceil_div((int64_t)a.D * 32, 256), 256, 0, st>>>(a, ln_x_sd, dx_mean, dln_x_sd);
+    const int64_t genes = a.ntiles > 0 ? std::min<int64_t>(a.D - (int64_t)a.tile0 * 128, (int64_t)a.ntiles * 128) : a.D;
+    senc_row_pass_kernel<<<ceil_div(genes * 32, 256), 256, 0, st>>>(a, ln_x_sd, dx_mean, dln_x_sd);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
