@@ -47,6 +47,7 @@ struct params_t {
     int relu;
     int tma_epi;   // 0: register epilogue ; 1: TMA tile store ; 2: TMA reduce-add (beta = 1 or split-K)
     double *sumsq; // persistent store epilogue: += sum of squares of the product
+    int n_fast;    // persistent tile order: 1 = consecutive tiles walk N (A tile reused from L2), 0 = walk M (B tile reused)
 };
 
 // STAGES = 3: two CTAs per SM (many-tile grids) ; STAGES = 6: one CTA per SM with a deeper ring, for
@@ -298,7 +299,9 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         if (lane == 0) {
             uint32_t it = 0;
             for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const int m0 = (t % tiles_m) * BLOCK_M, n0 = (t / tiles_m) * P_BLOCK_N;   // m fastest: concurrent CTAs share B
+                // concurrent CTAs share the operand that is walked slowly; the LARGER operand must be the one reused
+                // back to back, or it is streamed from HBM once per tile of the other dimension
+                const int m0 = (p.n_fast ? t / tiles_n : t % tiles_m) * BLOCK_M, n0 = (p.n_fast ? t % tiles_n : t / tiles_m) * P_BLOCK_N;
                 for (int kb = 0; kb < num_kb; ++kb, ++it) {
                     const uint32_t s = it % P_STAGES, ph = (it / P_STAGES) & 1;
                     mbar_wait(empty0 + 8 * s, ph ^ 1);
@@ -356,7 +359,7 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         uint32_t lt = 0, nstore = 0;
         float ss = 0.f;
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++lt) {
-            const int m0 = (t % tiles_m) * BLOCK_M, n0 = (t / tiles_m) * P_BLOCK_N;
+            const int m0 = (p.n_fast ? t / tiles_n : t % tiles_m) * BLOCK_M, n0 = (p.n_fast ? t % tiles_n : t / tiles_m) * P_BLOCK_N;
             const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
             mbar_wait(tfull0 + 8 * acc, aph);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -500,6 +503,7 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
     p.C = g.C; p.Cb = reinterpret_cast<__nv_bfloat16 *>(g.Cb); p.bias = g.bias;
     p.M = g.M; p.N = g.N; p.K = g.K; p.ldc = g.ldc; p.ldcb = g.ldcb; p.beta = g.beta; p.relu = g.relu;
     p.sumsq = nullptr;
+    p.n_fast = g.M > g.N ? 1 : 0;
     if (g.sumsq_done) *g.sumsq_done = 0;
     dim3 grid(ceil_div(g.N, BLOCK_N), ceil_div(g.M, BLOCK_M));
     const int tiles = (int)(grid.x * grid.y), total_kb = ceil_div(g.K, BLOCK_K);
