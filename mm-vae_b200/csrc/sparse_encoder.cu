@@ -14,6 +14,8 @@
 #include "common.cuh"
 #include "kernels.hh"
 
+#include <algorithm>
+
 namespace mmv {
 
 constexpr int kMaxAcc = 16;
@@ -210,7 +212,9 @@ int
 launch_senc_bias(const float *W1T, const float *x_mean, const float *inv_t, const float *col_scale,
                  float *bias_eff, int D, int h1, int angular, cudaStream_t st)
 {
-    const int gpc = 32;
+    // ~2 CTAs per SM, each walking a contiguous gene range with register accumulators: the per-column
+    // atomics at the end (h1 per CTA, all CTAs on the same h1 addresses) stay a small part of the pass
+    const int gpc = std::max(8, (ceil_div(D, 296) + 7) / 8 * 8);
     senc_bias_kernel<<<ceil_div(D, gpc), 256, 0, st>>>(W1T, x_mean, inv_t, col_scale, bias_eff, D, h1, gpc, angular); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
