@@ -112,7 +112,15 @@ load_inputs(const mmvae_options_t &main_options, run_inputs_t &in)
         in.c_dim = covar_block.nfeature();
         in.has_covar = true;
     } else {
-        TLOG("No covariate file is given. So we use a single all-ones covariate");
+        // nb_vae_main.cc:67-73: the reference writes a 1 x N all-ones Matrix Market file next to the outputs,
+        // indexes it and reads it back; the same two files are produced here (create_ones_like), while the
+        // device path keeps the all-ones covariate implicit (no B x 1 tensor, K4's tuned kernel stays eligible)
+        if (main_options.out.size() > 0) {
+            const std::string covar_mtx = main_options.out + ".covar.mtx.gz";
+            CHK(mmvae::create_ones_like(in.data->ntot(), covar_mtx));
+            TLOG("No covariate file is given. So we use this: " << covar_mtx);
+            CHK(mmutil::index::build_mmutil_index(covar_mtx, covar_mtx + ".index"));
+        }
     }
     return EXIT_SUCCESS;
 }

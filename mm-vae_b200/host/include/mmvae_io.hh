@@ -312,5 +312,22 @@ private:
     std::vector<int64_t> batch_;
 };
 
+// create_ones_like (mmvae_io.hh:292-310) + write_matrix_market_stream (io.hh:191-226): a 1 x ntot sparse
+// matrix of ones as bgzf Matrix Market text, triplets "1 <col> 1" sorted by column (1-based).
+inline int
+create_ones_like(int64_t ntot, const std::string &out_file)
+{
+    std::string text = "%%MatrixMarket matrix coordinate integer general\n";
+    text += "1 " + std::to_string(ntot) + " " + std::to_string(ntot) + "\n";
+    text.reserve(text.size() + (size_t)ntot * 12);
+    for (int64_t j = 0; j < ntot; ++j) {
+        text += "1 ";
+        text += std::to_string(j + 1);
+        text += " 1\n";
+    }
+    ERR_RET(!bgzf_write_file(out_file, text), "unable to write " << out_file);
+    return EXIT_SUCCESS;
+}
+
 } // namespace mmvae
 #endif

@@ -11,7 +11,11 @@
 #include "mmvae_io.hh"
 #include "mmvae_options.hh"
 
+#include <cstdio>
+#include <cstring>
 #include <memory>
+#include <string>
+#include <vector>
 #include <zlib.h>
 
 namespace mmvae {
@@ -115,9 +119,19 @@ public:
 
 // VISITOR concept (mmvae_alg.hh:316,332).  Writes ${out}.latent_mean_${epoch}.gz / latent_lnvar at the
 // recording epochs: one line per data point, R columns (ostream default precision like io.hh:308-331).
+// nbvae_recorder_t (nb.hh:569-662) / vmf_vae_recorder_t (vmf.hh:457-551): per recorded epoch
+//   ${out}_${zeropad(epoch)}.mu_mean.gz / .mu_lnvar.gz        (nb)
+//   ${out}_${zeropad(epoch)}.latent_mean.gz / .latent_lnvar.gz (vmf)
+//   ${out}_${zeropad(epoch)}_${parameter key}.gz              every named parameter, as write_tensor
+// (mmvae_io.hh:11-28) writes it: a 2-D tensor one row per line, a 1-D tensor one value per line, values
+// space-separated with the ostream default format (%g, 6 significant digits; io.hh:522-534).
+// The latent tables come from mmv_encode (eval mode, no covariate term: nb.hh:627-628, vmf.hh:516-517).
 class latent_recorder_t {
 public:
-    latent_recorder_t(const std::string &out, int64_t max_epoch, device_t &dev) : out_(out), max_epoch_(max_epoch), dev_(dev) { }
+    latent_recorder_t(const std::string &out, int64_t max_epoch, device_t &dev, bool is_vmf = false, bool write_params = true)
+        : out_(out), max_epoch_(max_epoch), dev_(dev), is_vmf_(is_vmf), write_params_(write_params)
+    {
+    }
 
     template <typename MODEL, typename DATA_BLOCK>
     void update_on_batch(MODEL &model, DATA_BLOCK &data, const std::vector<typename DATA_BLOCK::Index> &batch)
@@ -139,29 +153,52 @@ public:
     template <typename MODEL>
     void update_on_epoch(MODEL &model, int64_t epoch)
     {
-        const std::string tag = zeropad(epoch + 1, max_epoch_);
-        write(out_ + ".latent_mean_" + tag + ".gz", mean_, model.latent_dim);
-        write(out_ + ".latent_lnvar_" + tag + ".gz", lnvar_, model.latent_dim);
+        const std::string tag = out_ + "_" + zeropad((int)epoch, (int)max_epoch_);   // nb.hh:590
+        const int64_t R = model.latent_dim;
+        write_matrix(tag + (is_vmf_ ? ".latent_mean.gz" : ".mu_mean.gz"), mean_.data(), R > 0 ? (int64_t)mean_.size() / R : 0, R);
+        write_matrix(tag + (is_vmf_ ? ".latent_lnvar.gz" : ".mu_lnvar.gz"), lnvar_.data(), R > 0 ? (int64_t)lnvar_.size() / R : 0, R);
+        if (!write_params_) return;
+        int n = 0;
+        MMV_OK_EXIT(mmv_model_num_params(model.get(), &n));
+        std::vector<float> host;
+        for (int i = 0; i < n; ++i) {   // nb.hh:599-615: mu_enc, mu_dec, then every registered parameter
+            char name[MMV_NAME_LEN];
+            int64_t r = 0, c = 0;
+            int reg = 0;
+            MMV_OK_EXIT(mmv_model_param_info(model.get(), i, name, &r, &c, &reg));
+            host.resize((size_t)(r * c));
+            MMV_OK_EXIT(mmv_model_get_param(model.get(), name, host.data(), r * c));
+            const std::string key(name);
+            const bool one_d = key.size() > 5 && key.compare(key.size() - 5, 5, ".bias") == 0;   // torch 1-D tensor -> Eigen column vector
+            if (one_d) write_matrix(tag + "_" + key + ".gz", host.data(), r * c, 1);
+            else write_matrix(tag + "_" + key + ".gz", host.data(), r, c);
+        }
+    }
+
+    // row-major [rows x cols] -> gz text, "%g" (= operator<< of a float at the default precision)
+    static void write_matrix(const std::string &path, const float *v, int64_t rows, int64_t cols)
+    {
+        if (rows <= 0 || cols <= 0) return;
+        gzFile g = gzopen(path.c_str(), "wb");
+        if (!g) { ELOG("unable to write " << path); return; }
+        std::vector<char> buf((size_t)1 << 20);
+        size_t used = 0;
+        for (int64_t i = 0; i < rows; ++i) {
+            for (int64_t j = 0; j < cols; ++j) {
+                if (used + 32 > buf.size()) { gzwrite(g, buf.data(), (unsigned)used); used = 0; }
+                used += (size_t)std::snprintf(buf.data() + used, 24, "%g", (double)v[i * cols + j]);
+                buf[used++] = j + 1 == cols ? '\n' : ' ';
+            }
+        }
+        gzwrite(g, buf.data(), (unsigned)used);
+        gzclose(g);
     }
 
 private:
-    static void write(const std::string &path, const std::vector<float> &v, int64_t R)
-    {
-        if (v.empty() || R <= 0) return;
-        gzFile g = gzopen(path.c_str(), "wb");
-        if (!g) { ELOG("unable to write " << path); return; }
-        std::ostringstream os;
-        for (size_t i = 0; i < v.size(); ++i) {
-            os << v[i] << (((int64_t)(i + 1) % R == 0) ? "\n" : " ");
-            if (os.tellp() > (1 << 20)) { const std::string s = os.str(); gzwrite(g, s.data(), (unsigned)s.size()); os.str(""); }
-        }
-        const std::string s = os.str();
-        gzwrite(g, s.data(), (unsigned)s.size());
-        gzclose(g);
-    }
     std::string out_;
     int64_t max_epoch_;
     device_t &dev_;
+    bool is_vmf_, write_params_;
     std::vector<float> mean_, lnvar_;
 };
 

@@ -113,7 +113,7 @@ parse_mmvae_options(const int argc, const char *argv[], mmvae_options_t &options
 struct training_options_t {
     explicit training_options_t()
         : lr(1e-3f), grad_clip(1.f), nboot(3), max_epoch(101), recording(10), device(0), seed(0), bf16(false),
-          train_all_layers(false)
+          train_all_layers(false), record_params(true)
     {
     }
     float lr;          // 1e-3
@@ -125,6 +125,7 @@ struct training_options_t {
     uint64_t seed;             // 0 = std::random_device like the reference (mmvae_alg.hh:242-243)
     bool bf16;                 // --dtype bf16: tcgen05 GEMMs (1e-2 tolerance); default fp32 (1e-4)
     bool train_all_layers;     // default off = the reference's frozen unregistered Sequentials
+    bool record_params;        // default on = the reference's per-parameter text dumps at every recorded epoch (nb.hh:599-615)
 };
 
 inline int
@@ -136,7 +137,7 @@ parse_training_options(const int argc, const char *argv[], training_options_t &o
                         "--nboot      : #bootstrapped gradients (default: 3)\n"
                         "--max_epoch  : maximum #epoch (default: 101)\n"
                         "--recording  : recording interval (default: 10)\n"
-                        "--seed, --device, --dtype {f32,bf16}, --train_all_layers : B200 build additions\n\n";
+                        "--seed, --device, --dtype {f32,bf16}, --train_all_layers, --skip_param_record : B200 build additions\n\n";
     const option long_opts[] = { { "lr", required_argument, nullptr, 'L' },         { "learning", required_argument, nullptr, 'L' },
                                  { "learn_rate", required_argument, nullptr, 'L' }, { "learning_rate", required_argument, nullptr, 'L' },
                                  { "rate", required_argument, nullptr, 'L' },       { "grad_clip", required_argument, nullptr, 'G' },
@@ -145,6 +146,7 @@ parse_training_options(const int argc, const char *argv[], training_options_t &o
                                  { "epoch", required_argument, nullptr, 'E' },      { "recording", required_argument, nullptr, 'R' },
                                  { "seed", required_argument, nullptr, 1001 },      { "device", required_argument, nullptr, 1002 },
                                  { "dtype", required_argument, nullptr, 1003 },     { "train_all_layers", no_argument, nullptr, 1004 },
+                                 { "skip_param_record", no_argument, nullptr, 1005 },
                                  { "help", no_argument, nullptr, 'h' },             { nullptr, no_argument, nullptr, 0 } };
     bool help = false;
     mmvae_detail::scan_options(argc, argv, "L:G:B:E:R:h", long_opts, [&](int opt, const char *arg) {
@@ -158,6 +160,7 @@ parse_training_options(const int argc, const char *argv[], training_options_t &o
         case 1002: options.device = std::stoi(arg); break;
         case 1003: options.bf16 = std::strcmp(arg, "bf16") == 0; break;
         case 1004: options.train_all_layers = true; break;
+        case 1005: options.record_params = false; break;
         case 'h': help = true; break;
         default: break;
         }

@@ -24,7 +24,7 @@ main(const int argc, const char *argv[])
                              nb_opt.overdispersion_latent, nb_opt.do_relu, train_opt.seed + 7);
 
     TLOG("Training the model...");
-    mmvae::latent_recorder_t recorder(main_options.out, train_opt.max_epoch, dev);
+    mmvae::latent_recorder_t recorder(main_options.out, train_opt.max_epoch, dev, /*is_vmf=*/false, train_opt.record_params);
     nb_loss_t loss;
     loss.min_rate = main_options.kl_min;
     loss.max_rate = main_options.kl_max;

@@ -18,7 +18,7 @@ write_raw(const std::string &path, const void *p, size_t bytes)
 int
 main(const int argc, const char *argv[])
 {
-    if (argc < 2) { std::cerr << "usage: mmv_reader_tool <header|scan|table|block|dense|csr|floats|write|opts> ..." << std::endl; return 2; }
+    if (argc < 2) { std::cerr << "usage: mmv_reader_tool <header|scan|table|block|dense|csr|floats|write|ones|opts> ..." << std::endl; return 2; }
     const std::string cmd = argv[1];
     using mmutil::index::Index;
     if (cmd == "header" && argc == 3) {
@@ -73,6 +73,9 @@ main(const int argc, const char *argv[])
         while ((n = std::fread(buf, 1, sizeof(buf), f)) > 0) data.append(buf, n);
         std::fclose(f);
         ERR_RET(!mmvae::bgzf_write_file(argv[3], data), "cannot write " << argv[3]);
+    } else if (cmd == "ones" && argc == 4) {          // ones <N> <out.mtx.gz>: create_ones_like + its index
+        CHK(mmvae::create_ones_like(std::stoll(argv[2]), argv[3]));
+        CHK(mmutil::index::build_mmutil_index(argv[3], std::string(argv[3]) + ".index"));
     } else if (cmd == "opts") {                       // parsed option values, one "key value" per line
         mmvae_options_t mo;
         training_options_t to;

@@ -24,7 +24,7 @@ main(const int argc, const char *argv[])
                                 train_opt.seed + 7);
 
     TLOG("Training the model...");
-    mmvae::latent_recorder_t recorder(main_options.out, train_opt.max_epoch, dev);
+    mmvae::latent_recorder_t recorder(main_options.out, train_opt.max_epoch, dev, /*is_vmf=*/true, train_opt.record_params);
     vmf_loss_t loss;
     loss.min_rate = main_options.kl_min;
     loss.max_rate = main_options.kl_max;

@@ -38,23 +38,35 @@ def test_nb_vae_main_trains(bins, tmp_path, dtype):
     assert idx.exists()                                  # built on demand like nb_vae_main.cc:56-57
     s = scores(str(out) + ".scores.gz")
     assert s.shape == (6,) and np.all(np.isfinite(s)) and s[-1] < s[0]
-    for tag in ("3", "6"):
-        m = np.loadtxt(gzip.open(f"{out}.latent_mean_{tag}.gz", "rt"))
-        lv = np.loadtxt(gzip.open(f"{out}.latent_lnvar_{tag}.gz", "rt"))
+    for tag in ("2", "5"):   # update_on_epoch(model, epoch) with the 0-based epoch, zero-padded to len("6") (nb.hh:590)
+        m = np.loadtxt(gzip.open(f"{out}_{tag}.mu_mean.gz", "rt"))
+        lv = np.loadtxt(gzip.open(f"{out}_{tag}.mu_lnvar.gz", "rt"))
         assert m.shape == (500, 8) and lv.shape == (500, 8) and np.all(np.isfinite(m))
         assert np.all(lv >= -4.0001) and np.all(lv <= 4.0001)          # clamp of nb.hh:415
+    # per-parameter dumps (nb.hh:599-615 through write_tensor, mmvae_io.hh:11-28): 2-D one row per line, biases one value per line
+    D = 300
+    w1 = np.loadtxt(gzip.open(f"{out}_5_mu_encoding_1.weight.gz", "rt"))
+    assert w1.shape == (64, D) and np.all(np.isfinite(w1))
+    b1 = np.loadtxt(gzip.open(f"{out}_5_mu_encoding_1.bias.gz", "rt"))
+    assert b1.shape == (64,)
+    xm = np.loadtxt(gzip.open(f"{out}_5_x_mean.gz", "rt"), ndmin=2)
+    assert xm.shape == (1, D)
+    wd = np.loadtxt(gzip.open(f"{out}_5_mu_decoding.weight.gz", "rt"))
+    assert wd.shape == (D, 64)
+    assert not np.allclose(np.loadtxt(gzip.open(f"{out}_2_mu_decoding.weight.gz", "rt")), wd)   # training moved it
 
 
 def test_vmf_vae_main_trains(bins, tmp_path):
     out = tmp_path / "vmf"
     cmd = [os.path.join(bins, "vmf_vae"), "--mtx", os.path.join(GOLDEN, "reader_b.mtx.gz"), "--idx", str(tmp_path / "b.index"),
            "--out", str(out), "--batch", "128", "--encoding", "32", "--decoding", "32", "--latent", "4", "--epoch", "4",
-           "--recording", "4", "--seed", "3", "--train_all_layers"]
+           "--recording", "4", "--seed", "3", "--train_all_layers", "--skip_param_record"]
     p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
     assert p.returncode == 0, p.stderr[-2000:]
     s = scores(str(out) + ".scores.gz")
     assert s.shape == (4,) and np.all(np.isfinite(s)) and s[-1] <= s[0]
-    assert np.loadtxt(gzip.open(f"{out}.latent_mean_4.gz", "rt")).shape == (500, 4)
+    assert np.loadtxt(gzip.open(f"{out}_3.latent_mean.gz", "rt")).shape == (500, 4)
+    assert not os.path.exists(f"{out}_3_z_decoding.weight.gz")          # --skip_param_record
 
 
 def test_main_fails_like_reference_without_out(bins):

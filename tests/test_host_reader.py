@@ -141,3 +141,25 @@ def test_option_defaults_and_aliases(tool, tmp_path):
     # missing --out fails like the reference (ERR_RET "need output file header")
     p = subprocess.run([tool, "opts", "--mtx", mtx], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
     assert "rc 1" in p.stdout and "need output file header" in p.stderr
+
+
+def test_covar_ones_matrix_writer(tool, tmp_path):
+    """No --covar: the reference writes ${out}.covar.mtx.gz, a 1 x N matrix of ones as bgzf Matrix Market text
+    sorted by column, and indexes it (nb_vae_main.cc:67-73, mmvae_io.hh:292-310, io.hh:191-226).  The file
+    must read back through the same reader: N columns, each holding the single triplet (row 0, value 1)."""
+    N = 70000   # more than one 64 KB bgzf block of text
+    path = tmp_path / "run.covar.mtx.gz"
+    run(tool, "ones", N, path)
+    text = gzip.open(path, "rt").read().split("\n")
+    assert text[0] == "%%MatrixMarket matrix coordinate integer general"
+    assert text[1] == f"1 {N} {N}"
+    assert text[2] == "1 1 1" and text[N + 1] == f"1 {N} 1" and text[N + 2] == ""
+    assert [int(v) for v in run(tool, "header", path).split("\n")[0].split()] == [1, N, N]
+    idx = [l.split() for l in gzip.open(str(path) + ".index", "rt").read().strip().split("\n")]
+    assert len(idx) == N and [int(r[0]) for r in idx] == list(range(N))
+    prefix = tmp_path / "ones"
+    dims = [int(v) for v in run(tool, "csr", path, str(path) + ".index", prefix).split()]
+    assert dims == [1, N, N]
+    assert np.array_equal(np.fromfile(str(prefix) + ".indptr", np.int64), np.arange(N + 1))
+    assert not np.fromfile(str(prefix) + ".indices", np.int32).any()
+    assert np.all(np.fromfile(str(prefix) + ".values", np.float32) == 1.0)
