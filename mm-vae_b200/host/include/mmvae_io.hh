@@ -17,8 +17,12 @@
 #include "mmvae_util.hh"
 
 #include <algorithm>
+#include <chrono>
 #include <tuple>
 #include <unordered_map>
+#include <cstdlib>
+#include <functional>
+#include <thread>
 
 namespace mmutil {
 namespace index {
@@ -200,7 +204,8 @@ public:
         ASSERT(mmutil::index::read_mmutil_index(idx_file, index_tab_) == EXIT_SUCCESS, "failed to read " << idx_file);
         ASSERT(parse_all() == EXIT_SUCCESS, "failed to parse " << mtx_file);
         TLOG("Read " << mtx_file << ": " << D_ << " features x " << N_ << " data points, " << indices.size()
-                     << " nonzeros resident as CSR");
+                     << " nonzeros resident as CSR (" << ingest_threads_ << " reader threads: parse " << parse_seconds_
+                     << " s, merge " << merge_seconds_ << " s)");
     }
 
     Index ntot() const { return N_; }
@@ -264,6 +269,11 @@ public:
     std::vector<float> values;
 
 private:
+    // One pass over the file into CSR.  The text is split at column boundaries taken from the index table
+    // (bgzf virtual offsets, mmutil_index.hh:138-228) into one range per host thread; every thread inflates
+    // and parses its own range with its own reader (mmutil_bgzf_util.hh:53-151 semantics), and the triplets
+    // are merged in FILE order, so duplicates resolve exactly as in a sequential read (the last one wins,
+    // mmvae_io.hh:127-130).  MMV_INGEST_THREADS overrides the thread count (1 = the sequential reader).
     int parse_all()
     {
         // start right after the header line (not at voffset 0: the header itself has three fields)
@@ -279,33 +289,109 @@ private:
             }
             start = fp.tell();
         }
-        struct ent_t { int32_t g; float w; };
-        std::vector<std::vector<ent_t>> rows((size_t)N_);
-        bool bad = false;
-        const Index D = D_, N = N_;
-        CHK(mmutil::index::visit_bgzf_block(mtx_file_, start, 0, [&](Index r, Index c, float w) {
-            // the reference does not range-check rows (mmutil_bgzf_util.hh:139 -> out-of-bounds write); we fail
-            if (r < 0 || r >= D || c < 0 || c >= N) { bad = true; return; }
-            rows[(size_t)c].push_back(ent_t{ (int32_t)r, w });
-        }));
-        ERR_RET(bad, "matrix market entry outside the " << D_ << " x " << N_ << " header shape in " << mtx_file_);
-        indptr.assign((size_t)N_ + 1, 0);
-        indices.clear();
-        values.clear();
-        for (Index c = 0; c < N_; ++c) {
-            auto &v = rows[(size_t)c];
-            std::stable_sort(v.begin(), v.end(), [](const ent_t &a, const ent_t &b) { return a.g < b.g; });
-            for (size_t i = 0; i < v.size(); ++i) {
-                if (i + 1 < v.size() && v[i + 1].g == v[i].g) continue;   // duplicates: the last one wins (:127-130)
-                indices.push_back(v[i].g);
-                values.push_back(v[i].w);
-            }
-            indptr[(size_t)c + 1] = (int64_t)indices.size();
-            std::vector<ent_t>().swap(v);
+        int T = (int)std::thread::hardware_concurrency();
+        if (const char *e = std::getenv("MMV_INGEST_THREADS")) T = std::atoi(e);
+        T = std::max(1, std::min(T, 64));
+        // range boundaries: strictly increasing, valid (non-zero) offsets of evenly spaced columns
+        std::vector<int64_t> cut{ start };
+        for (int t = 1; t < T; ++t) {
+            Index c = (Index)((int64_t)N_ * t / T);
+            while (c < N_ && (int64_t)index_tab_[(size_t)c] <= cut.back()) ++c;   // skips MISSING_POS = 0 and gap-filled repeats
+            if (c >= N_) break;
+            cut.push_back((int64_t)index_tab_[(size_t)c]);
         }
+        const int R = (int)cut.size();
+        const auto t_begin = std::chrono::steady_clock::now();
+        struct trip_t { Index c; int32_t g; float w; };
+        std::vector<std::vector<trip_t>> part((size_t)R);
+        std::vector<int> rc((size_t)R, EXIT_SUCCESS), bad((size_t)R, 0);
+        const Index D = D_, N = N_;
+        auto parse_range = [&](int t) {
+            std::vector<trip_t> &out = part[(size_t)t];
+            int &b = bad[(size_t)t];
+            rc[(size_t)t] = mmutil::index::visit_bgzf_block(mtx_file_, cut[(size_t)t], t + 1 < R ? cut[(size_t)t + 1] : 0,
+                                                            [&out, &b, D, N](Index r, Index c, float w) {
+                // the reference does not range-check rows (mmutil_bgzf_util.hh:139 -> out-of-bounds write); we fail
+                if (r < 0 || r >= D || c < 0 || c >= N) { b = 1; return; }
+                out.push_back(trip_t{ c, (int32_t)r, w });
+            });
+        };
+        if (R == 1) parse_range(0);
+        else {
+            std::vector<std::thread> th;
+            for (int t = 0; t < R; ++t) th.emplace_back(parse_range, t);
+            for (auto &x : th) x.join();
+        }
+        for (int t = 0; t < R; ++t) {
+            if (rc[(size_t)t] != EXIT_SUCCESS) return rc[(size_t)t];
+            ERR_RET(bad[(size_t)t], "matrix market entry outside the " << D_ << " x " << N_ << " header shape in " << mtx_file_);
+        }
+        const auto t_parsed = std::chrono::steady_clock::now();
+        // bucket by data point in file order (counting sort: stable)
+        std::vector<int64_t> cnt((size_t)N_ + 1, 0);
+        for (auto &p : part)
+            for (auto &e : p) ++cnt[(size_t)e.c + 1];
+        for (Index c = 0; c < N_; ++c) cnt[(size_t)c + 1] += cnt[(size_t)c];
+        struct ent_t { int32_t g; float w; };
+        std::vector<ent_t> all((size_t)cnt[(size_t)N_]);
+        {
+            std::vector<int64_t> cur(cnt.begin(), cnt.end() - 1);
+            for (auto &p : part) {
+                for (auto &e : p) all[(size_t)cur[(size_t)e.c]++] = ent_t{ e.g, e.w };
+                std::vector<trip_t>().swap(p);
+            }
+        }
+        // per data point: sort by gene (stable), duplicates keep the last; column ranges in parallel
+        std::vector<int64_t> kept((size_t)N_ + 1, 0);
+        auto tidy = [&](Index c0, Index c1) {
+            for (Index c = c0; c < c1; ++c) {
+                ent_t *v = all.data() + cnt[(size_t)c];
+                const size_t n = (size_t)(cnt[(size_t)c + 1] - cnt[(size_t)c]);
+                std::stable_sort(v, v + n, [](const ent_t &a, const ent_t &b) { return a.g < b.g; });
+                size_t k = 0;
+                for (size_t i = 0; i < n; ++i) {
+                    if (i + 1 < n && v[i + 1].g == v[i].g) continue;
+                    v[k++] = v[i];
+                }
+                kept[(size_t)c + 1] = (int64_t)k;
+            }
+        };
+        auto for_ranges = [&](const std::function<void(Index, Index)> &f) {
+            if (T == 1 || N_ < 1024) { f(0, N_); return; }
+            std::vector<std::thread> th;
+            for (int t = 0; t < T; ++t) th.emplace_back(f, (Index)((int64_t)N_ * t / T), (Index)((int64_t)N_ * (t + 1) / T));
+            for (auto &x : th) x.join();
+        };
+        for_ranges(tidy);
+        indptr.assign((size_t)N_ + 1, 0);
+        for (Index c = 0; c < N_; ++c) indptr[(size_t)c + 1] = indptr[(size_t)c] + kept[(size_t)c + 1];
+        indices.resize((size_t)indptr[(size_t)N_]);
+        values.resize((size_t)indptr[(size_t)N_]);
+        for_ranges([&](Index c0, Index c1) {
+            for (Index c = c0; c < c1; ++c) {
+                const ent_t *v = all.data() + cnt[(size_t)c];
+                int64_t q = indptr[(size_t)c];
+                for (int64_t i = 0; i < kept[(size_t)c + 1]; ++i, ++q) {
+                    indices[(size_t)q] = v[i].g;
+                    values[(size_t)q] = v[i].w;
+                }
+            }
+        });
+        ingest_threads_ = R;
+        const auto t_end = std::chrono::steady_clock::now();
+        parse_seconds_ = std::chrono::duration<double>(t_parsed - t_begin).count();
+        merge_seconds_ = std::chrono::duration<double>(t_end - t_parsed).count();
         return EXIT_SUCCESS;
     }
 
+public:
+    int ingest_threads() const { return ingest_threads_; }
+    double parse_seconds() const { return parse_seconds_; }   // inflate + text parse (parallel part)
+    double merge_seconds() const { return merge_seconds_; }   // bucket + sort + CSR assembly
+
+private:
+    int ingest_threads_ = 1;
+    double parse_seconds_ = 0., merge_seconds_ = 0.;
     std::string mtx_file_, idx_file_;
     Index B_ = 0, D_ = 0, N_ = 0;
     std::vector<Index> index_tab_;

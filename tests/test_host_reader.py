@@ -163,3 +163,21 @@ def test_covar_ones_matrix_writer(tool, tmp_path):
     assert np.array_equal(np.fromfile(str(prefix) + ".indptr", np.int64), np.arange(N + 1))
     assert not np.fromfile(str(prefix) + ".indices", np.int32).any()
     assert np.all(np.fromfile(str(prefix) + ".values", np.float32) == 1.0)
+
+
+@pytest.mark.parametrize("tag", list(FILES))
+def test_parallel_ingest_equals_sequential(tool, tag, tmp_path):
+    """The one-off ingest splits the text at column boundaries of the index table and parses the ranges on
+    several host threads; merging in file order must give byte-identical CSR arrays to the 1-thread read
+    (duplicates: last one wins; unsorted rows inside a column: sorted by gene)."""
+    path = os.path.join(GOLDEN, FILES[tag])
+    idx = tmp_path / "t.index"
+    run(tool, "table", path, idx)
+    outs = []
+    for threads in ("1", "3", "8"):
+        prefix = tmp_path / f"csr{threads}"
+        env = dict(os.environ, MMV_INGEST_THREADS=threads)
+        subprocess.run([tool, "csr", path, str(idx), str(prefix)], check=True, stdout=subprocess.PIPE, env=env)
+        outs.append([open(str(prefix) + ext, "rb").read() for ext in (".indptr", ".indices", ".values")])
+    assert outs[0] == outs[1] == outs[2]
+    assert len(outs[0][1]) > 0
