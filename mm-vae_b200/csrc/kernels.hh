@@ -209,6 +209,10 @@ struct vmf_lik_args_t {
     int B = 0, D = 0, C = 0;
     float inv_B = 0.f, eps_obs = 0.f;
     float *dpre = nullptr;            // [B x D] (nullptr: forward only)
+    void *dpre_bf16 = nullptr;        // tuned kernel only: the gradient as bf16 instead (feeds the tensor-core GEMMs)
+    const int *unsorted = nullptr;    // device flag: 0 = every CSR row has ascending gene ids
+    int64_t *slice_bounds = nullptr;  // [B x 9] workspace of the tuned kernel
+    int allow_fast = 1;
     float *col_dq = nullptr;          // [D]
     float *col_dqc = nullptr;         // [D x C]
     double *t_acc = nullptr;          // += sum_i <yobs_i, recon_i>
@@ -216,6 +220,8 @@ struct vmf_lik_args_t {
     float *row_t = nullptr;           // optional [B]
 };
 int launch_vmf_likelihood(const vmf_lik_args_t &a, int num_sms, cudaStream_t stream);
+bool vmf_likelihood_fast_eligible(const vmf_lik_args_t &a);
+int launch_vmf_likelihood_fast(const vmf_lik_args_t &a, int num_sms, cudaStream_t stream);
 
 struct vmf_scalar_args_t {
     const float *kappa = nullptr, *ln_kappa = nullptr;

@@ -1199,9 +1199,15 @@ vmf_forward_backward(const step_t &s)
     k.kappa = kappa; k.B = B; k.D = D; k.C = C; k.inv_B = s.inv_B; k.eps_obs = eps_d;
     k.t_acc = m->acc + 4;
     if (m->debug_outputs) { k.recon = WS("recon", (size_t)B * D); NEED(k.recon); }
-    m->top_grad_bf16 = false;
+    k.allow_fast = m->nb_fast ? 1 : 0;
+    k.unsorted = s.csr->d_unsorted;
+    k.slice_bounds = (int64_t *)WS("k4_bounds", (size_t)B * 9 * 2); NEED(k.slice_bounds);
+    // tuned kernel + tensor-core GEMMs behind it: the B x D gradient leaves K5 as bf16
+    m->top_grad_bf16 = s.bwd && k.allow_fast && vmf_likelihood_fast_eligible(k) && tc_ok(s, D, Ld.in, B, D, Ld.in) &&
+        tc_ok(s, B, Ld.in, D, D, Ld.in);
     if (s.bwd) {
-        k.dpre = m->ws["G"].as<float>();
+        if (m->top_grad_bf16) { k.dpre_bf16 = m->W("dG.bf", (size_t)B * D * 2); NEED(k.dpre_bf16); }
+        else k.dpre = m->ws["G"].as<float>();
         k.col_dq = WS("col_dq", D); k.col_dqc = WS("col_dqc", (size_t)D * C); NEED(k.col_dq); NEED(k.col_dqc);
         MMV_CUDA(cudaMemsetAsync(k.col_dq, 0, sizeof(float) * D, s.st));
         MMV_CUDA(cudaMemsetAsync(k.col_dqc, 0, sizeof(float) * D * C, s.st));
@@ -1231,7 +1237,8 @@ vmf_forward_backward(const step_t &s)
 
     {   // decoding.bias = column sums of dL/dpre ; covar_decoding_ from dL/dq
         colsum_args_t c;
-        c.X = k.dpre; c.M = B; c.N = D; c.ldx = D; c.out_sum = m->want_grad(Ld.b) ? m->G(Ld.b) : nullptr;
+        PROF("colsum_dlogits");
+        c.X = k.dpre; c.Xb = k.dpre_bf16; c.M = B; c.N = D; c.ldx = D; c.out_sum = m->want_grad(Ld.b) ? m->G(Ld.b) : nullptr;
         if (c.out_sum) MMV_TRY(launch_colsum(c, s.st));
     }
     MMV_TRY(axpy(m->G(m->covar_dec.b), k.col_dq, 1.f, D, s.st));

@@ -19,6 +19,7 @@
 //     FMA pipe; small integer counts use product forms of lgamma / digamma.
 #include "common.cuh"
 #include "kernels.hh"
+#include "rowstream.cuh"
 
 #include <cooperative_groups.h>
 #include <cuda_bf16.h>
@@ -29,36 +30,12 @@ namespace cg = cooperative_groups;
 
 namespace {
 
+using namespace rowstream;
+
 constexpr int kT = 256;
 constexpr int NW = kT / 32;
 constexpr int NZP = 2;                                         // nonzeros prefetched per thread per row
 constexpr float kEps = 1e-4f, kNuMin = 1e-4f, kNuMax = 1e4f;   // nb.hh:514,252,459
-
-__device__ __forceinline__ float
-rcp_f(float x)
-{
-    float r;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
-}
-
-constexpr float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
-
-__device__ __forceinline__ float
-ex2_f(float x)
-{
-    float r;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
-}
-
-__device__ __forceinline__ float
-lg2_f(float x)
-{
-    float r;
-    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
-}
 
 // log(1 + y), y >= 0: Taylor polynomial on the FMA pipe below 1/16 (where log1p(y) - y / (1 + y)
 // cancels and lg2.approx's absolute error near 1 would dominate), MUFU lg2 above
@@ -68,54 +45,6 @@ log1p_fast(float y)
     const float poly = y * (1.f - y * (0.5f - y * (0.33333334f - y * (0.25f - y * 0.2f))));
     const float big = lg2_f(1.f + y) * kLn2;
     return y < 0.0625f ? poly : big;
-}
-
-// ---- packed fp32 pairs (sm_100 FFMA2 / FMUL2 / FADD2): the dense sweep is issue-bound, and every
-//      thread owns adjacent gene pairs, so the FMA-pipe arithmetic is issued two lanes at a time
-typedef unsigned long long f2_t;
-
-__device__ __forceinline__ f2_t
-pk2(float a, float b)
-{
-    f2_t r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
-    return r;
-}
-
-__device__ __forceinline__ f2_t
-bc2(float a)
-{
-    return pk2(a, a);
-}
-
-__device__ __forceinline__ void
-up2(f2_t r, float &a, float &b)
-{
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(r));
-}
-
-__device__ __forceinline__ f2_t
-fma2(f2_t a, f2_t b, f2_t c)
-{
-    f2_t r;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-    return r;
-}
-
-__device__ __forceinline__ f2_t
-mul2(f2_t a, f2_t b)
-{
-    f2_t r;
-    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-    return r;
-}
-
-__device__ __forceinline__ f2_t
-add2(f2_t a, f2_t b)
-{
-    f2_t r;
-    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-    return r;
 }
 
 struct elem_t {
@@ -236,50 +165,6 @@ count_terms(float nu, float x, float &lg_terms, float &dig_diff)
         dig_diff = digamma_f(nu) - digamma_f(nu + x);
     }
 }
-
-__device__ __forceinline__ uint32_t
-smem_addr(const void *p)
-{
-    return (uint32_t)__cvta_generic_to_shared(p);
-}
-
-__device__ __forceinline__ void
-bulk_load(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-
-__device__ __forceinline__ void
-bar_wait(uint32_t bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "NBW_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra NBW_DONE;\n"
-        "bra NBW_LOOP;\n"
-        "NBW_DONE:\n"
-        "}\n" ::"r"(bar), "r"(parity) : "memory");
-}
-
-// One thread publishes (a, b) into slot[my_rank] of every CTA of the cluster and signals that CTA's
-// mbarrier with the 8 bytes written (st.async ... complete_tx): the data and the signal travel together.
-__device__ __forceinline__ void
-xchg_send(uint32_t slot_local, uint32_t bar_local, int cs, float a, float b)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_local), "r"(8u * (uint32_t)cs) : "memory");
-    for (int r = 0; r < cs; ++r) {
-        uint32_t rslot, rbar;
-        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rslot) : "r"(slot_local), "r"(r));
-        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rbar) : "r"(bar_local), "r"(r));
-        asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];"
-                     ::"r"(rslot), "f"(a), "f"(b), "r"(rbar) : "memory");
-    }
-}
-
 // ---------------------------------------------------------------------------
 // pre-kernel: for every minibatch row, the absolute CSR offsets at which each gene slice begins
 // (bounds[row * (cs + 1) + c]); one warp per row.  Unsorted rows get the whole run for every slice
@@ -614,6 +499,16 @@ ept_class(int ept)
 
 } // namespace
 
+int
+launch_slice_bounds(const int64_t *indptr, const int32_t *indices, const int32_t *cells, const int *unsorted, int B, int cs,
+                    int Ds, int64_t *bounds, cudaStream_t stream)
+{
+    slice_bounds_kernel<<<ceil_div((int64_t)B * (cs + 1), 256), 256, 0, stream>>>(indptr, indices, cells, unsorted, B, cs, Ds, bounds);
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
 bool
 nb_likelihood_fast_eligible(const nb_lik_args_t &a)
 {
@@ -633,12 +528,7 @@ launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stre
         if (ept <= 16 && fast_smem_bytes(ept_class(ept)) <= budget) break;
         MMV_CHECK(cs < 8, "nb_likelihood: D=%d does not fit a cluster of 8 CTAs", a.D);
     }
-    {
-        slice_bounds_kernel<<<ceil_div((int64_t)a.B * (cs + 1), 256), 256, 0, stream>>>(
-            a.indptr, a.indices, a.cells, a.unsorted, a.B, cs, Ds, a.slice_bounds);
-        ::mmv::count_launch();
-        MMV_CUDA(cudaGetLastError());
-    }
+    MMV_TRY(launch_slice_bounds(a.indptr, a.indices, a.cells, a.unsorted, a.B, cs, Ds, a.slice_bounds, stream));
     void (*kern)(nb_lik_args_t, int, int) = ept <= 4 ? nb_likelihood_fast_kernel<4>
         : ept <= 8 ? nb_likelihood_fast_kernel<8> : ept <= 12 ? nb_likelihood_fast_kernel<12> : nb_likelihood_fast_kernel<16>;
     const size_t smem = fast_smem_bytes(ept_class(ept));

@@ -163,6 +163,8 @@ int
 launch_vmf_likelihood(const vmf_lik_args_t &a, int num_sms, cudaStream_t stream)
 {
     MMV_CHECK(a.C >= 1 && a.C <= kVmfCMax, "vmf_likelihood: covariate dim %d not in [1,%d]", a.C, kVmfCMax);
+    if (a.allow_fast && vmf_likelihood_fast_eligible(a)) return launch_vmf_likelihood_fast(a, num_sms, stream);
+    MMV_CHECK(a.dpre_bf16 == nullptr, "vmf_likelihood: the general kernel writes fp32 gradients only");
     const size_t budget = 200 * 1024;
     int cs = 1, Ds = 0;
     for (;; cs *= 2) {
