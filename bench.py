@@ -42,6 +42,9 @@ def parse_args():
     ap.add_argument("--genes", type=int, default=WORKLOAD["genes"])
     ap.add_argument("--batch", type=int, default=WORKLOAD["batch"], help="cells per step per GPU")
     ap.add_argument("--model", default="nb", choices=["nb", "vmf"])
+    ap.add_argument("--enc", default=None, help="encoder widths, comma separated (default: SURVEY cfg 4)")
+    ap.add_argument("--dec", default=None, help="decoder widths, comma separated")
+    ap.add_argument("--latent", type=int, default=None)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"],
                     help="GEMM operand type: bf16 = tcgen05 tensor cores (fp32 accumulate), f32 = FFMA parity mode")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -296,6 +299,12 @@ def run_own(args):
         dist.init_process_group("nccl", device_id=dev)
     mmv = importlib.import_module("mm-vae_b200")
     w = dict(WORKLOAD, cells=args.cells, genes=args.genes, batch=args.batch, model=args.model)
+    if args.enc:
+        w["enc"] = [int(v) for v in args.enc.split(",")]
+    if args.dec:
+        w["dec"] = [int(v) for v in args.dec.split(",")]
+    if args.latent:
+        w["latent"] = args.latent
     B, D = w["batch"], w["genes"]
     ctx = mmv.Context(local)
     if world > 1:
@@ -495,6 +504,12 @@ def run_reference(args):
     if rank != 0:
         return
     w = dict(WORKLOAD, cells=args.cells, genes=args.genes, batch=args.batch, model=args.model)
+    if args.enc:
+        w["enc"] = [int(v) for v in args.enc.split(",")]
+    if args.dec:
+        w["dec"] = [int(v) for v in args.dec.split(",")]
+    if args.latent:
+        w["latent"] = args.latent
     cb = cpu_reference_run(w, w["model"], steps=args.steps, warmup=args.warmup)
     out = {"impl": "reference",
            "metric": "train cells/sec (NB-VAE ELBO fwd+bwd, 1M x 30k sparse)", "value": round(cb["value"], 2),
