@@ -296,6 +296,9 @@ def run_own(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # the library pins its gradient all-reduces to NCCL's ring (comm.cu: measured faster under backward); NCCL
+        # reads the variable once per process, so it has to be in place before torch creates its own communicator
+        os.environ.setdefault("NCCL_ALGO", "Ring")
         dist.init_process_group("nccl", device_id=dev)
     mmv = importlib.import_module("mm-vae_b200")
     w = dict(WORKLOAD, cells=args.cells, genes=args.genes, batch=args.batch, model=args.model)

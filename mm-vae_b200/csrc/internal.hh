@@ -20,6 +20,12 @@ struct mmv_ctx {
     cudaStream_t comm_stream = nullptr;          // early gradient buckets are reduced here, under the rest of backward
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int nranks = 1, rank = 0;
+    bool in_group = false;
+    // MMV_COMM_TRACE=<k>: timed marks on both streams for the k-th optimiser step, printed by rank 0 (comm.cu)
+    int trace_step = -1, trace_seen = 0;
+    bool trace_on = false;
+    struct mark_t { std::string name; cudaEvent_t ev; int comm; };
+    std::vector<mark_t> marks;
 };
 
 struct mmv_csr {
@@ -48,5 +54,16 @@ int comm_allreduce_f64(mmv_ctx *ctx, double *buf, size_t n);
 // has finished; comm_join makes the ctx stream wait for it
 int comm_allreduce_f32_async(mmv_ctx *ctx, float *buf, size_t n);
 int comm_join(mmv_ctx *ctx);
+// reductions queued between begin and end go out as one NCCL launch on the comm stream
+int comm_group_begin(mmv_ctx *ctx);
+int comm_allreduce_f64_async(mmv_ctx *ctx, double *buf, size_t n);
+int comm_group_end(mmv_ctx *ctx);
+// gradient buffer: a registered symmetric NCCL window when data-parallel (see comm.cu)
+int comm_alloc_grads(mmv_ctx *ctx, size_t bytes, float **ptr, void **win, bool *nccl_owned);
+void comm_free_grads(mmv_ctx *ctx, float *ptr, void *win, bool nccl_owned);
+// timeline marks (no-ops unless this step is traced)
+void trace_begin(mmv_ctx *ctx);
+void trace_mark(mmv_ctx *ctx, const char *name, bool on_comm = false);
+void trace_end(mmv_ctx *ctx);
 
 } // namespace mmv

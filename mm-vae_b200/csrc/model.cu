@@ -100,6 +100,8 @@ struct mmv_model {
     std::map<std::string, int> by_name;
     size_t n_reg = 0, n_all = 0;          // floats in the registered prefix / whole buffer
     float *params = nullptr, *grads = nullptr, *adam_m = nullptr, *adam_v = nullptr;
+    void *grads_win = nullptr;   // NCCL symmetric window over grads (data-parallel), else nullptr
+    bool grads_nccl = false;     // grads came from ncclMemAlloc
     int64_t adam_t = 0;
     std::vector<std::pair<size_t, size_t>> ar_done;   // gradient ranges already handed to the comm stream this step
 
@@ -252,7 +254,7 @@ alloc_and_init(mmv_model *m)
     const size_t bytes = sizeof(float) * m->n_all;
     MMV_CUDA(cudaSetDevice(m->ctx->device));
     MMV_CUDA(cudaMalloc(&m->params, bytes));
-    MMV_CUDA(cudaMalloc(&m->grads, bytes));
+    MMV_TRY(comm_alloc_grads(m->ctx, bytes, &m->grads, &m->grads_win, &m->grads_nccl));
     MMV_CUDA(cudaMalloc(&m->adam_m, bytes));
     MMV_CUDA(cudaMalloc(&m->adam_v, bytes));
     MMV_CUDA(cudaMalloc(&m->params_bf16, bytes / 2));
@@ -426,7 +428,8 @@ mmv_model_destroy(mmv_model *m)
     if (!m) return 0;
     cudaSetDevice(m->ctx->device);
     cudaStreamSynchronize(m->ctx->stream);
-    cudaFree(m->params); cudaFree(m->grads); cudaFree(m->adam_m); cudaFree(m->adam_v);
+    cudaFree(m->params); cudaFree(m->adam_m); cudaFree(m->adam_v);
+    comm_free_grads(m->ctx, m->grads, m->grads_win, m->grads_nccl);
     cudaFree(m->acc); cudaFree(m->fscal); cudaFree(m->params_bf16);
     cudaFreeHost(m->h_acc); cudaFreeHost(m->h_fscal);
     for (int i = 0; i < 2; ++i) {
@@ -821,6 +824,7 @@ decoder_backward(const step_t &s)
                                (last && m->optimised(L.w)) ? 0.f : 1.f,   // mmv_step leaves this one un-zeroed
                                last ? "gemm_dec_last_dw" : "gemm_other", dY_bf, fuse_ss ? m->acc + 3 : nullptr, &ss_ok));
         // multi GPU, first bucket: the largest gradient is final long before backward ends — reduce it under the rest
+        if (last) trace_mark(m->ctx, "decoder-last dW done");
         if (last && m->want_grad(L.w)) MMV_TRY(allreduce_grad_async(s, L.w));
         if (ss_ok) m->ss_done.emplace_back(m->tensors[L.w].off, m->tensors[L.w].off + m->tensors[L.w].numel());
         float *dX = l == 0 ? WS("dz", (size_t)B * R) : WS("d_dec" + std::to_string(l - 1), (size_t)B * L.in);
@@ -977,19 +981,23 @@ senc_tc_backward(const step_t &s, const senc_bwd_args_t &b)
     const int tiles = (D + 127) / 128, cols = (h1 + 255) / 256;
     const int waves = (tiles * cols + m->ctx->num_sms - 1) / m->ctx->num_sms;
     if (split_ar && waves >= 3) {
-        // multi GPU: the gene tiles in two parts of whole waves; the first part's rows of dW1 are all-reduced
-        // on the comm stream while the second part is multiplied (only the smaller second all-reduce is exposed)
-        const int t1 = std::min(tiles - 1, (int)((int64_t)((waves + 1) / 2) * m->ctx->num_sms / cols));
+        // multi GPU: the gene tiles in up to four parts of whole waves; each part's rows of dW1 are all-reduced on
+        // the comm stream while the next part is multiplied.  dW1 is produced about as fast as NVLink reduces it, so
+        // only the last (partial-wave) part's reduction is left over, and that one runs under the aux kernel below
+        const int per = std::max(1, (int)((int64_t)((waves + 3) / 4) * m->ctx->num_sms / cols));
         const size_t off = m->tensors[L0.w].off;
-        a.tile0 = 0; a.ntiles = t1;
-        MMV_TRY(launch_senc_tc_bwd(a, s.st));
-        MMV_TRY(launch_senc_row_pass(a, b.ln_x_sd, b.dx_mean, b.dln_x_sd, s.st));
-        const size_t n1 = (size_t)std::min(D, t1 * 128) * h1;
-        MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off, n1));
-        m->ar_done.emplace_back(off, off + n1);
-        a.tile0 = t1; a.ntiles = tiles - t1;
-        MMV_TRY(launch_senc_tc_bwd(a, s.st));
-        MMV_TRY(launch_senc_row_pass(a, b.ln_x_sd, b.dx_mean, b.dln_x_sd, s.st));
+        for (int t0 = 0; t0 < tiles; t0 += per) {
+            const int t1 = std::min(tiles, t0 + per);
+            a.tile0 = t0; a.ntiles = t1 - t0;
+            MMV_TRY(launch_senc_tc_bwd(a, s.st));
+            MMV_TRY(launch_senc_row_pass(a, b.ln_x_sd, b.dx_mean, b.dln_x_sd, s.st));
+            const size_t r0 = (size_t)std::min(D, t0 * 128) * h1, r1 = (size_t)std::min(D, t1 * 128) * h1;
+            trace_mark(m->ctx, "first-layer dW part done");
+            // a small last part is not worth a launch of its own: it goes with the step's grouped leftovers
+            if (t1 == tiles && t0 > 0 && (r1 - r0) * sizeof(float) < ((size_t)16 << 20)) break;
+            MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off + r0, r1 - r0));
+            m->ar_done.emplace_back(off + r0, off + r1);
+        }
     } else {
         MMV_TRY(launch_senc_tc_bwd(a, s.st));
         MMV_TRY(launch_senc_row_pass(a, b.ln_x_sd, b.dx_mean, b.dln_x_sd, s.st));
@@ -1052,7 +1060,9 @@ nb_forward_backward(const step_t &s)
     rn.kl_acc = m->acc + 2;
     MMV_TRY(launch_reparam_fwd(rn, s.st));
 
+    trace_mark(m->ctx, "encoder forward done");
     MMV_TRY(decoder_forward(s));
+    trace_mark(m->ctx, "decoder forward done");
 
     const linear_t &Ld = m->dec.back();
     float *abias = WS("abias", D), *ubias = WS("ubias", D); NEED(abias); NEED(ubias);
@@ -1107,7 +1117,9 @@ nb_forward_backward(const step_t &s)
     MMV_TRY(axpy(m->G(m->t_nu_bias), k.col_du, -1.f, D, s.st));
     MMV_TRY(axpy(m->G(m->nu_dec.w), k.col_duz, 1.f, (size_t)D * Rnu, s.st));
 
+    trace_mark(m->ctx, "likelihood + column sums done");
     MMV_TRY(decoder_backward(s));
+    trace_mark(m->ctx, "decoder backward done");
     MMV_TRY(encoder_backward(s, true));
 
     // nu encoder backward
@@ -1142,12 +1154,14 @@ nb_forward_backward(const step_t &s)
     b.dW1T = m->want_grad(L0.w) ? m->G(L0.w) : nullptr;
     b.dx_mean = m->G(m->t_x_mean); b.dln_x_sd = m->G(m->t_ln_x_sd);
     b.dHnu = dHnu; b.ddpre = k.ddpre; b.dWnuT = m->G(m->nu_enc.w); b.dwdepth = m->G(m->depth.w);
+    trace_mark(m->ctx, "encoder backward (dense part) done");
     if (tc_senc) {
         MMV_TRY(senc_tc_backward(s, b));
     } else {
         PROF("senc_bwd");
         MMV_TRY(launch_senc_bwd(b, s.st));
     }
+    trace_mark(m->ctx, "first-layer backward done");
     return 0;
 }
 
@@ -1386,6 +1400,7 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         s.optim = (flags & MMV_OPTIM) != 0;
         m->ar_done.clear();
         m->ss_done.clear();
+        if (s.optim && s.bwd) trace_begin(m->ctx);
         MMV_TRY(stage_inputs(m, csr, cells, B, boot_idx, eps, flags, s));
         if (csr->ev_ready) MMV_CUDA(cudaStreamWaitEvent(st, csr->ev_ready, 0));   // streamed slot: its upload is done
         m->last_B = B;
@@ -1423,7 +1438,10 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         MMV_CUDA(cudaMemsetAsync(m->acc + 3, 0, sizeof(double), st));
     }
 
-    if (nranks > 1 && (flags & MMV_FWD)) MMV_TRY(comm_allreduce_f64(m->ctx, m->acc, 8));
+    if (nranks > 1 && (flags & MMV_FWD) && !(flags & MMV_OPTIM)) {
+        PROF("allreduce");
+        MMV_TRY(comm_allreduce_f64(m->ctx, m->acc, 8));
+    }
     if (flags & MMV_OPTIM) {
         if (m->grad_lazy) {   // an optimiser-only call on gradients whose previous clip is still pending
             MMV_TRY(launch_scale_by(m->grads, m->grad_lazy_n, m->fscal + 2, st));
@@ -1434,6 +1452,8 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
             // everything not yet handed to the comm stream follows the buckets there, then the step waits
             if (!(flags & MMV_FWD)) m->ar_done.clear();
             std::sort(m->ar_done.begin(), m->ar_done.end());
+            MMV_TRY(comm_group_begin(m->ctx));   // the loss sums ride along: one launch for all the leftovers
+            if (flags & MMV_FWD) MMV_TRY(comm_allreduce_f64_async(m->ctx, m->acc, 8));
             size_t pos = 0;
             for (size_t i = 0; i <= m->ar_done.size(); ++i) {
                 const size_t end = i < m->ar_done.size() ? std::min(m->ar_done[i].first, n_opt) : n_opt;
@@ -1441,7 +1461,9 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
                 if (i < m->ar_done.size()) pos = std::max(pos, std::min(m->ar_done[i].second, n_opt));
             }
             m->ar_done.clear();
+            MMV_TRY(comm_group_end(m->ctx));
             MMV_TRY(comm_join(m->ctx));
+            trace_mark(m->ctx, "joined the comm stream");
         }
         PROF("clip_adam");
         if (!(flags & MMV_FWD)) m->ss_done.clear();   // acc[3] was re-zeroed: nothing carried over
@@ -1469,6 +1491,7 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         a.max_norm = m->grad_clip; a.weight_decay = m->weight_decay;
         a.bc2_sqrt = (float)std::sqrt(bc2); a.neg_step = (float)(-(double)m->lr / bc1);
         MMV_TRY(launch_adam(a, m->ctx->num_sms, st));
+        trace_end(m->ctx);
     }
     if (!out) return 0;
 
