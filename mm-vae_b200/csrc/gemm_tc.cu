@@ -538,6 +538,14 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
         const char *e = getenv("MMV_GEMM_PERSIST");
         persist_mode = e ? atoi(e) : 1;
     }
+    static int log_left = -1;   // MMV_GEMM_LOG=<n>: print the first n launches' shapes
+    if (log_left < 0) { const char *e = getenv("MMV_GEMM_LOG"); log_left = e ? atoi(e) : 0; }
+    if (log_left > 0) {
+        --log_left;
+        fprintf(stderr, "[gemm_tc] M=%d N=%d K=%d a_mn=%d b_mn=%d lda=%d ldb=%d ldc=%d beta=%g bias=%d relu=%d Cb=%d epi=%d grid=(%u,%u,%u) A=%p B=%p C=%p\n",
+                g.M, g.N, g.K, g.a_mn, g.b_mn, g.lda, g.ldb, g.ldc, g.beta, g.bias != nullptr, g.relu, g.Cb != nullptr, p.tma_epi,
+                grid.x, grid.y, grid.z, g.A, g.B, (void *)g.C);
+    }
     const int ptiles = ceil_div(g.M, BLOCK_M) * ceil_div(g.N, P_BLOCK_N);
     if (persist_mode > 0 && p.tma_epi && !g.Cb && grid.z == 1 && ptiles >= 2 * num_sms) {
         if (!g.b_mn) MMV_TRY(make_map(&tb, g.B, g.K, g.N, g.ldb, BLOCK_K, P_BLOCK_N));
