@@ -258,6 +258,19 @@ struct reparam_args_t {
 int launch_reparam_fwd(const reparam_args_t &a, cudaStream_t st);
 int launch_reparam_bwd(const reparam_args_t &a, cudaStream_t st);
 
+// ---- true vMF latent (vmf_latent.cu; SURVEY 8 f4, opt-in, no reference counterpart): same head / outputs as
+// the Gaussian block above — mean = unit direction, lnvar = -log kappa broadcast, z on the sphere, kl_acc += KL
+struct vmf_latent_args_t {
+    reparam_args_t r;
+    uint64_t seed = 0, draw = 0;      // Philox key: any (seed, draw, row) is reproducible on its own
+    float kappa_max = 1e4f;
+    double lgamma_half_d = 0.;        // lgamma(R / 2)
+    float *w = nullptr;               // [B] sampled cosine <z, mu>: written forward, read backward
+    int *attempts = nullptr;          // [B] proposals used (nullable)
+};
+int launch_vmf_latent_fwd(const vmf_latent_args_t &a, cudaStream_t st);
+int launch_vmf_latent_bwd(const vmf_latent_args_t &a, cudaStream_t st);
+
 struct colsum_args_t {
     const float *X = nullptr;
     const void *Xb = nullptr;         // bf16 input instead of X

@@ -120,6 +120,9 @@ struct mmv_model {
     bool top_grad_bf16 = false;           // K4 wrote the B x D gradient as bf16 into "dG.bf" this step
     std::map<const float *, const void *> bf_cache;   // activations already converted in this step
     uint64_t seed = 0;
+    bool vmf_latent = false;              // "vmf_latent" option: Wood sampler + Householder + Bessel KL (vmf_latent.cu)
+    uint64_t vmf_draw = 0;                // Philox draw counter of the next sampled forward pass
+    float vmf_kappa_max = 1e4f;
 
     // workspace
     int64_t cap_B = 0, cap_ent = 0;
@@ -461,6 +464,12 @@ mmv_model_set_option(mmv_model *m, const char *key, double value)
     else if (k == "nb_fast") m->nb_fast = value != 0;
     else if (k == "dtype") m->use_tc = value != 0;   // 0 = fp32 (parity mode), 1 = bf16 tensor-core GEMMs
     else if (k == "max_batch") { /* capacity hint; buffers grow on demand */ }
+    else if (k == "vmf_latent") {
+        MMV_CHECK(value == 0 || (m->is_vmf && m->R >= 3), "mmv_model_set_option: vmf_latent needs a vmf model with latent dim >= 3");
+        m->vmf_latent = value != 0;
+    }
+    else if (k == "vmf_latent_draw") m->vmf_draw = (uint64_t)value;
+    else if (k == "vmf_kappa_max") m->vmf_kappa_max = (float)value;
     else MMV_CHECK(false, "mmv_model_set_option: unknown key '%s'", key);
     return 0;
 }
@@ -770,6 +779,16 @@ encoder_forward(const step_t &s, bool with_covar)
     r.mean = WS("mu_mean", (size_t)B * R); r.lnvar = WS("mu_lnvar", (size_t)B * R); r.z = WS("z", (size_t)B * R);
     NEED(r.mean); NEED(r.lnvar); NEED(r.z);
     r.kl_acc = m->acc + 1;
+    if (m->vmf_latent) {
+        vmf_latent_args_t v;
+        v.r = r;
+        v.seed = m->seed + 0x5eed + 0x9E3779B97F4A7C15ull * (uint64_t)m->ctx->rank; v.draw = m->vmf_draw;   // ranks draw independently
+        if (r.eps) ++m->vmf_draw;
+        v.kappa_max = m->vmf_kappa_max; v.lgamma_half_d = std::lgamma(0.5 * (double)R);
+        v.w = WS("vmf_w", B); NEED(v.w);
+        v.attempts = (int *)WS("vmf_attempts", B); NEED(v.attempts);
+        return launch_vmf_latent_fwd(v, s.st);
+    }
     return launch_reparam_fwd(r, s.st);
 }
 
@@ -856,7 +875,16 @@ encoder_backward(const step_t &s, bool with_covar)
     r.dz = m->ws["dz"].as<float>();
     r.dhead = WS("dhead_mu", (size_t)B * 2 * R); NEED(r.dhead);
     r.kl_weight = s.klw; r.inv_B = s.inv_B;
-    MMV_TRY(launch_reparam_bwd(r, s.st));
+    if (m->vmf_latent) {
+        vmf_latent_args_t v;
+        v.r = r;
+        if (with_covar) { v.r.Wce = m->P(m->covar_enc.w); v.r.bce = m->P(m->covar_enc.b); v.r.cov = s.cov; v.r.cells = s.cells; }
+        v.kappa_max = m->vmf_kappa_max; v.lgamma_half_d = std::lgamma(0.5 * (double)R);
+        v.w = m->ws["vmf_w"].as<float>();
+        MMV_TRY(launch_vmf_latent_bwd(v, s.st));
+    } else {
+        MMV_TRY(launch_reparam_bwd(r, s.st));
+    }
     if (with_covar) {   // covar_encoding grads: dW_ce[r, c] = sum_i dmean_ir c_ic ; db_ce = sum_i dmean_ir
         colsum_args_t c;
         c.X = r.dhead; c.M = B; c.N = R; c.ldx = 2 * R;
@@ -1563,6 +1591,9 @@ mmv_get_output(mmv_model *m, const char *name, float *host, int64_t n)
         else if (key == "lnvar") { key = "mu_lnvar"; want = B * m->R; }
         else if (key == "recon") want = B * m->D;
         else if (key == "kappa") { src = m->fscal; want = 1; }
+        else if (key == "z" || key == "dz") want = B * m->R;
+        else if (key == "dhead_mu" || key == "head_mu") want = B * 2 * m->R;
+        else if (key == "vmf_w" || key == "vmf_attempts") want = B;   // attempts: int32 bit patterns
         else MMV_CHECK(false, "mmv_get_output: unknown output '%s'", name);
     } else {
         if (key == "mu_mean" || key == "mu_lnvar") want = B * m->R;

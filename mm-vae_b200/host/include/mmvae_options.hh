@@ -231,11 +231,12 @@ parse_nbvae_options(const int argc, const char *argv[], nbvae_options_t &options
 namespace vmf {
 
 struct vmf_options_t {
-    explicit vmf_options_t() : latent(2), kappa_min(.1f), kappa_max(10.f), do_relu(false) { }
+    explicit vmf_options_t() : latent(2), kappa_min(.1f), kappa_max(10.f), do_relu(false), vmf_latent(false) { }
     std::vector<int64_t> encoding_layers, decoding_layers;
     int64_t latent;
     float kappa_min, kappa_max;
     bool do_relu;
+    bool vmf_latent;   // NOT in the reference: true vMF latent (Wood sampler, Householder, Bessel KL), long option only
 };
 
 inline int
@@ -248,8 +249,11 @@ parse_vmf_options(const int argc, const char *argv[], vmf_options_t &options)
                         "--kappa_min : minimum concentration (default: 0.1)\n"
                         "--kappa_max : maximum concentration (default: 10)\n"
                         "--no_relu   : remove ReLU between layers (default)\n"
-                        "--relu      : add ReLU between layers\n\n";
+                        "--relu      : add ReLU between layers\n"
+                        "--vmf_latent: von Mises-Fisher latent instead of the Gaussian one (needs --latent >= 3;\n"
+                        "              not in the reference: Wood sampler, Householder reflection, Bessel KL)\n\n";
     const option long_opts[] = { { "encoding", required_argument, nullptr, 'E' },  { "decoding", required_argument, nullptr, 'D' },
+                                 { "vmf_latent", no_argument, nullptr, 1001 },     { "vmf-latent", no_argument, nullptr, 1001 },
                                  { "latent", required_argument, nullptr, 'L' },    { "kappa_min", required_argument, nullptr, 'k' },
                                  { "kappa-min", required_argument, nullptr, 'k' }, { "kappa_max", required_argument, nullptr, 'K' },
                                  { "kappa-max", required_argument, nullptr, 'K' }, { "relu", no_argument, nullptr, 'R' },
@@ -265,6 +269,7 @@ parse_vmf_options(const int argc, const char *argv[], vmf_options_t &options)
         case 'L': options.latent = std::stol(arg); break;
         case 'k': options.kappa_min = std::stof(arg); break;
         case 'K': options.kappa_max = std::stof(arg); break;
+        case 1001: options.vmf_latent = true; break;
         case 'h': help = true; break;
         default: break;
         }

@@ -22,6 +22,10 @@ main(const int argc, const char *argv[])
     mmvae::vmf::vmf_vae_t model(dev.ctx, in.data->nfeature(), in.c_dim, vmf_opt.latent, vmf_opt.encoding_layers,
                                 vmf_opt.decoding_layers, vmf_opt.kappa_min, vmf_opt.kappa_max, vmf_opt.do_relu,
                                 train_opt.seed + 7);
+    if (vmf_opt.vmf_latent) {
+        ASSERT(vmf_opt.latent >= 3, "--vmf_latent needs --latent >= 3");
+        MMV_OK_EXIT(mmv_model_set_option(model.get(), "vmf_latent", 1));
+    }
 
     TLOG("Training the model...");
     mmvae::latent_recorder_t recorder(main_options.out, train_opt.max_epoch, dev, /*is_vmf=*/true, train_opt.record_params);

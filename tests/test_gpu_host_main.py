@@ -69,6 +69,22 @@ def test_vmf_vae_main_trains(bins, tmp_path):
     assert not os.path.exists(f"{out}_3_z_decoding.weight.gz")          # --skip_param_record
 
 
+def test_vmf_vae_main_with_vmf_latent(bins, tmp_path):
+    """--vmf_latent (not in the reference): the latent table holds unit vectors, the second table -log kappa."""
+    out = tmp_path / "vmfl"
+    cmd = [os.path.join(bins, "vmf_vae"), "--mtx", os.path.join(GOLDEN, "reader_b.mtx.gz"), "--idx", str(tmp_path / "b.index"),
+           "--out", str(out), "--batch", "128", "--encoding", "32", "--decoding", "32", "--latent", "6", "--epoch", "4",
+           "--recording", "4", "--seed", "3", "--train_all_layers", "--skip_param_record", "--vmf_latent"]
+    p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr[-2000:]
+    s = scores(str(out) + ".scores.gz")
+    assert s.shape == (4,) and np.all(np.isfinite(s))
+    mu = np.loadtxt(gzip.open(f"{out}_3.latent_mean.gz", "rt"))
+    lv = np.loadtxt(gzip.open(f"{out}_3.latent_lnvar.gz", "rt"))
+    assert mu.shape == (500, 6) and np.abs(np.linalg.norm(mu, axis=1) - 1).max() < 1e-4
+    assert np.all(lv <= 0) and np.abs(lv - lv[:, :1]).max() == 0          # -log kappa, kappa >= 1, one value per cell
+
+
 def test_main_fails_like_reference_without_out(bins):
     p = subprocess.run([os.path.join(bins, "nb_vae"), "--mtx", os.path.join(GOLDEN, "reader_b.mtx.gz")],
                        stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=60)
