@@ -73,13 +73,22 @@ def make_model(mmv, ctx, model, D, enc, dec, R, dtype, rng):
     return m, neps
 
 
-def check_vs_oracle(mmv, m, model, csr, x, cells, eps, tol, klw=0.8):
+_ORACLE_CACHE = {}
+
+
+def check_vs_oracle(mmv, m, model, csr, x, cells, eps, tol, klw=0.8, cache_key=None):
     terms = m.step(csr, cells, eps=eps, kl_weight=klw, flags=mmv.FWD | mmv.BWD)
-    P = oracle_params(m)
-    c = np.ones((len(cells), 1), np.float32)
-    torch.set_num_threads(max(1, min(16, torch.get_num_threads())))
-    ref, _, grads = mo.run_step("nb" if model.startswith("nb") else "vmf", P, torch.from_numpy(x[cells]), torch.from_numpy(c),
-                                [torch.from_numpy(e) for e in eps], klw)
+    if cache_key is not None and cache_key in _ORACLE_CACHE:       # same seeded parameters / inputs: one oracle run
+        ref, grads = _ORACLE_CACHE[cache_key]
+    else:
+        P = oracle_params(m)
+        c = np.ones((len(cells), 1), np.float32)
+        ref, _, grads = mo.run_step("nb" if model.startswith("nb") else "vmf", P, torch.from_numpy(x[cells]), torch.from_numpy(c),
+                                    [torch.from_numpy(e) for e in eps], klw)
+        ref = {"loss": float(ref["loss"])}
+        grads = {k: v.detach().clone() for k, v in grads.items()}
+        if cache_key is not None:
+            _ORACLE_CACHE[cache_key] = (ref, grads)
     assert np.isfinite(terms["loss"])
     assert abs(terms["loss"] - float(ref["loss"])) <= tol * abs(float(ref["loss"])), (terms, float(ref["loss"]))
     worst = {}
@@ -164,7 +173,7 @@ def full_batch():
     rng = np.random.default_rng(20201)
     D, B = FULL["D"], FULL["B"]
     # library sizes / gene propensities as SURVEY 8d, drawn with numpy (the bench draws them on the device)
-    lib = np.exp(rng.normal(np.log(0.05 * D * 3), 0.5, size=B))
+    lib = np.exp(rng.normal(np.log(0.05 * D * 1.05), 0.5, size=B))   # realised density ~5 %
     pi = rng.gamma(0.3, 1.0, size=D)
     pi /= pi.sum()
     x = np.zeros((B, D), dtype=np.float32)
@@ -184,7 +193,7 @@ def test_full_size_minibatch_vs_oracle(mmv, ctx, full_batch, dtype):
     csr = mmv.CSR.from_dense(ctx, x)
     m, neps = make_model(mmv, ctx, "nb1", D, FULL["enc"], FULL["dec"], FULL["R"], dtype, rng)
     eps = [rng.normal(size=(B, n)).astype(np.float32) for n in neps]
-    terms, worst = check_vs_oracle(mmv, m, "nb1", csr, x, np.arange(B), eps, tol, klw=1.0)
+    terms, worst = check_vs_oracle(mmv, m, "nb1", csr, x, np.arange(B), eps, tol, klw=1.0, cache_key="full")
     print(dtype, "density", float((x > 0).mean()), "loss", terms["loss"],
           {k: f"{v:.1e}" for k, v in sorted(worst.items(), key=lambda kv: -kv[1])[:4]})
     m.close()
