@@ -116,7 +116,16 @@ MMV_API int mmv_model_destroy(mmv_model *m);
  *   "frozen_grads" (1): compute the gradients of the non-optimised tensors
  *        (what the reference's autograd does); 0 skips that dead work.
  *   "max_batch" : capacity hint (cells per step), grows on demand.
- *   "debug_outputs" (0): keep recon_mu / recon_nu / recon for mmv_get_output. */
+ *   "debug_outputs" (0): keep recon_mu / recon_nu / recon for mmv_get_output.
+ *   "vmf_latent" (0): vmf models only, z_dim >= 3.  NOT in the reference (its vmf_vae reparameterises a
+ *        Gaussian, vmf.hh:394-404, and uses kl_loss_normal, vmf.hh:410-414); this is the latent the north star
+ *        names.  1 = the stacked head is read as a von Mises-Fisher posterior instead: mean direction
+ *        mu = normalise(mean head + covar_enc(c)), concentration kappa = min(1 + softplus(mean_r of the second
+ *        head), "vmf_kappa_max" (1e4)); z ~ vMF(mu, kappa) by Wood's rejection sampler (Philox keyed on the model
+ *        seed, the draw counter "vmf_latent_draw" and the row; the cell's eps[1:] gives the tangent direction) and
+ *        a Householder reflection; kl_mu = sum_i KL(vMF(mu_i, kappa_i) || uniform sphere); gradients flow
+ *        through the reflection and, for kappa, the implicit-reparameterisation derivative of the sampled cosine.
+ *        mmv_encode / the recorder then return mu (unit vectors) and -log kappa. */
 MMV_API int mmv_model_set_option(mmv_model *m, const char *key, double value);
 
 /* Parameters by the reference's named_parameters() keys ("x_mean",
