@@ -22,6 +22,7 @@
 #include "rowstream.cuh"
 
 #include <cooperative_groups.h>
+#include <type_traits>
 #include <cuda_bf16.h>
 
 namespace mmv {
@@ -59,6 +60,9 @@ struct pair_t {
     f2_t p, g, nl, du;
 };
 
+// CLAMPS = false: the caller has shown that every u of the row lies inside (log(expm1(1e-4)), 20), so the
+// softplus threshold, the clamp of nb.hh:459 and its gradient mask cannot act (they cost ~15 of ~70 instructions).
+template <bool CLAMPS>
 __device__ __forceinline__ pair_t
 pair_fast(f2_t v, f2_t scale, f2_t depth, f2_t u)
 {
@@ -69,7 +73,7 @@ pair_fast(f2_t v, f2_t scale, f2_t depth, f2_t u)
     const f2_t m = fma2(o.p, depth, eps);                             // nb.hh:519
     float u0, u1;
     up2(u, u0, u1);
-    const float t0 = ex2_f(fminf(u0, c20)), t1 = ex2_f(fminf(u1, c20));
+    const float t0 = ex2_f(CLAMPS ? fminf(u0, c20) : u0), t1 = ex2_f(CLAMPS ? fminf(u1, c20) : u1);
     const f2_t t = pk2(t0, t1);
     const f2_t w = add2(t, one);
     float w0, w1;
@@ -79,18 +83,24 @@ pair_fast(f2_t v, f2_t scale, f2_t depth, f2_t u)
     // log1p(t) = log(w) + (t - (w - 1)) / w ; beyond the threshold softplus(u) = u = log1p(e^20) + (u - 20)
     const f2_t comp = mul2(fma2(add2(w, neg1), neg1, t), rw);
     f2_t sp = fma2(lw, ln2, comp);
-    const f2_t over = add2(u, bc2(-c20));
-    float v0, v1;
-    up2(over, v0, v1);
-    sp = fma2(pk2(fmaxf(v0, 0.f), fmaxf(v1, 0.f)), ln2, sp);
-    float s0, s1;
-    up2(sp, s0, s1);
-    const float r0 = fminf(fmaxf(s0, kNuMin), kNuMax), r1 = fminf(fmaxf(s1, kNuMin), kNuMax);   // nb.hh:459
-    const f2_t nu = add2(pk2(r0, r1), eps);                           // nb.hh:518
+    f2_t nu, sigm;
     const f2_t sig = mul2(t, rw);                                     // d softplus / du (-> 1 beyond the threshold)
-    float g0, g1;
-    up2(sig, g0, g1);
-    const f2_t sigm = pk2(r0 == s0 ? g0 : 0.f, r1 == s1 ? g1 : 0.f);  // clamp passes the gradient inside [min, max]
+    if (CLAMPS) {
+        const f2_t over = add2(u, bc2(-c20));
+        float v0, v1;
+        up2(over, v0, v1);
+        sp = fma2(pk2(fmaxf(v0, 0.f), fmaxf(v1, 0.f)), ln2, sp);
+        float s0, s1;
+        up2(sp, s0, s1);
+        const float r0 = fminf(fmaxf(s0, kNuMin), kNuMax), r1 = fminf(fmaxf(s1, kNuMin), kNuMax);   // nb.hh:459
+        nu = add2(pk2(r0, r1), eps);                                  // nb.hh:518
+        float g0, g1;
+        up2(sig, g0, g1);
+        sigm = pk2(r0 == s0 ? g0 : 0.f, r1 == s1 ? g1 : 0.f);        // clamp passes the gradient inside [min, max]
+    } else {
+        nu = add2(sp, eps);
+        sigm = sig;
+    }
     const f2_t mnu = add2(m, nu);
     float q0, q1;
     up2(mul2(nu, mnu), q0, q1);
@@ -147,6 +157,17 @@ elem_fast(float p, float depth, float u2)
 __constant__ float kLogFact[9] = { 0.f, 0.f, 0.6931471806f, 1.7917594692f, 3.1780538303f, 4.7874917428f,
                                    6.5792512120f, 8.5251613611f, 10.6046029027f };
 
+// lgamma(z) and digamma(z) for z >= 8 by Stirling's series (error < 3e-8 / 2e-9 relative to the leading terms):
+//   lgamma(z) = (z - 1/2) ln z - z + ln(2 pi)/2 + 1/(12 z) - 1/(360 z^3) + 1/(1260 z^5)
+//   psi(z)    = ln z - 1/(2 z) - 1/(12 z^2) + 1/(120 z^4) - 1/(252 z^6)
+__device__ __forceinline__ void
+stirling(float z, float &lg, float &dg)
+{
+    const float lz = logf(z), r = rcp_f(z), r2 = r * r;   // accurate log: (z - 1/2) ln z is ~1e4 for counts in the thousands
+    lg = fmaf(z - 0.5f, lz, -z) + 0.9189385332f + r * (0.0833333333f - r2 * (0.00277777778f - r2 * 0.000793650794f));
+    dg = lz - 0.5f * r - r2 * (0.0833333333f - r2 * (0.00833333333f - r2 * 0.00396825397f));
+}
+
 __device__ __forceinline__ void
 count_terms(float nu, float x, float &lg_terms, float &dig_diff)
 {
@@ -160,7 +181,28 @@ count_terms(float nu, float x, float &lg_terms, float &dig_diff)
         }
         lg_terms = kLogFact[xi] - __logf(P);
         dig_diff = -dP * rcp_f(P);
-    } else {
+    } else if (x > 8.f) {
+        // larger counts (a warp meets one almost every row): nu is shifted up by 8 with the product form
+        // (lgamma(nu) = lgamma(nu + 8) - ln prod_{k<8}(nu + k), same for digamma), nu + x and x + 1 are >= 9,
+        // so all three lgammas and both digammas are Stirling series: ~70 instructions instead of five libdevice calls
+        float P = 1.f, dP = 0.f, z = nu;
+        if (nu < 8.f) {
+            P = nu; dP = 1.f;
+#pragma unroll
+            for (int k = 1; k < 8; ++k) {
+                const float f = nu + (float)k;
+                dP = fmaf(dP, f, P);
+                P *= f;
+            }
+            z = nu + 8.f;
+        }
+        float lg_n, dg_n, lg_nx, dg_nx, lg_x1, dg_x1;
+        stirling(z, lg_n, dg_n);
+        stirling(nu + x, lg_nx, dg_nx);
+        stirling(x + 1.f, lg_x1, dg_x1);
+        lg_terms = (lg_n - lg2_f(P) * kLn2) - lg_nx + lg_x1;
+        dig_diff = (dg_n - dP * rcp_f(P)) - dg_nx;
+    } else {   // non-integer value below 8 (the reference's reader accepts decimals): libdevice
         lg_terms = lgammaf(nu) + lgammaf(x + 1.f) - lgammaf(nu + x);
         dig_diff = digamma_f(nu) - digamma_f(nu + x);
     }
@@ -224,6 +266,9 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         for (int i = 0; i < 6; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8 * i));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    // extremes of the slice's nu-decoder constants: a row whose u = zn wn + ub provably stays inside
+    // (log(expm1(1e-4)), 20) takes the sweep without softplus threshold / clamp / gradient mask
+    float wlo = INFINITY, whi = -INFINITY, blo = INFINITY, bhi = -INFINITY;
     for (int jj = tid; jj < Dp; jj += kT) {
         const int j = j0 + jj;
         // padding: logit -inf (softmax numerator 0), u -> -inf (nu clamped, gradient masked), weight 0
@@ -234,13 +279,22 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
             for (int c = 0; c < a.C; ++c) ab += a.Wcd[(size_t)j * a.C + c];   // covariates are all ones on this path
             ub = a.ubias[j] * kLog2e;   // pre-scaled: u * log2(e) = zn * wn' + ub'
             wn = a.Wnd[j] * kLog2e;
+            wlo = fminf(wlo, wn); whi = fmaxf(whi, wn);
+            blo = fminf(blo, ub); bhi = fmaxf(bhi, ub);
         }
         s_ab[jj] = ab;
         s_ub[jj] = ub;
         s_wn[jj] = wn;
         if (jj >= nj) sG0[jj] = sG1[jj] = 0.f;   // the padding of the landing buffers is never written by TMA
     }
+    wlo = -warp_max(-wlo); whi = warp_max(whi); blo = -warp_max(-blo); bhi = warp_max(bhi);
+    if (lane == 0) { wstat[warp * 4 + 0] = wlo; wstat[warp * 4 + 1] = whi; wstat[warp * 4 + 2] = blo; wstat[warp * 4 + 3] = bhi; }
     if (cs > 1) cluster.sync(); else __syncthreads();   // barriers initialised cluster-wide before any remote signal
+    for (int w8 = 0; w8 < NW; ++w8) {
+        wlo = fminf(wlo, wstat[w8 * 4 + 0]); whi = fmaxf(whi, wstat[w8 * 4 + 1]);
+        blo = fminf(blo, wstat[w8 * 4 + 2]); bhi = fmaxf(bhi, wstat[w8 * 4 + 3]);
+    }
+    __syncthreads();                                     // wstat is reused by the row loop
 
     const uint32_t row_bytes = (uint32_t)nj * 4u;
     int row = cluster_id;
@@ -357,21 +411,27 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         f2_t red0 = 0ull, red1 = 0ull;
         {
             const f2_t scale2 = bc2(scale), depth2 = bc2(depth), zn2 = bc2(zn);
+            // u' = u log2(e) over the slice lies in [ulo, uhi] (interval arithmetic on zn wn' + ub')
+            const float ulo = fminf(zn * wlo, zn * whi) + blo, uhi = fmaxf(zn * wlo, zn * whi) + bhi;
+            const bool plain = ulo > -13.f && uhi < 28.5f;    // log2(e) * (-9.21, 20) = (-13.29, 28.85), with margin
+            auto sweep = [&](auto clamps) {
 #pragma unroll
-            for (int h = 0; h < HP; ++h) {
-                if (h * 2 * kT + warp * 64 >= nj) continue;
-                const int jj = 2 * tid + h * 2 * kT;
-                const f2_t wn2 = *reinterpret_cast<const f2_t *>(s_wn + jj);
-                const f2_t ub2 = *reinterpret_cast<const f2_t *>(s_ub + jj);
-                const pair_t e = pair_fast(vp[h], scale2, depth2, fma2(zn2, wn2, ub2));
-                nll2 = fma2(e.nl, bc2(jj < nj ? 1.f : 0.f), nll2);
-                vp[h] = e.p;
-                red0 = fma2(e.g, e.p, red0);
-                cdu[h] = add2(cdu[h], e.du);
-                cduz[h] = fma2(e.du, zn2, cduz[h]);
-                red1 = fma2(e.du, wn2, red1);
-                *reinterpret_cast<f2_t *>(s_g + jj) = e.g;
-            }
+                for (int h = 0; h < HP; ++h) {
+                    if (h * 2 * kT + warp * 64 >= nj) continue;
+                    const int jj = 2 * tid + h * 2 * kT;
+                    const f2_t wn2 = *reinterpret_cast<const f2_t *>(s_wn + jj);
+                    const f2_t ub2 = *reinterpret_cast<const f2_t *>(s_ub + jj);
+                    const pair_t e = pair_fast<decltype(clamps)::value>(vp[h], scale2, depth2, fma2(zn2, wn2, ub2));
+                    nll2 = fma2(e.nl, bc2(jj < nj ? 1.f : 0.f), nll2);
+                    vp[h] = e.p;
+                    red0 = fma2(e.g, e.p, red0);
+                    cdu[h] = add2(cdu[h], e.du);
+                    cduz[h] = fma2(e.du, zn2, cduz[h]);
+                    red1 = fma2(e.du, wn2, red1);
+                    *reinterpret_cast<f2_t *>(s_g + jj) = e.g;
+                }
+            };
+            if (plain) sweep(std::false_type{}); else sweep(std::true_type{});
         }
         __syncthreads();                       // s_g complete before the nonzero loop overwrites entries
 
