@@ -9,8 +9,10 @@ A "step" = one pass of the hot path over one minibatch of B cells per GPU:
 forward, loss, backward, (allreduce when N > 1,) global-norm clip, Adam —
 mmvae_alg.hh:303-310 of the reference.  `value` times it with the matrix
 resident in HBM as CSR; `e2e` times the same step fed with HOST buffers through
-the C ABI (pinned minibatch CSR -> H2D -> step -> loss terms D2H), the call the
-reference-side binding makes.  Cells are sharded over ranks (weak scaling: B per
+the C ABI (pinned minibatch CSR -> H2D -> step -> loss terms D2H every step, read
+one step late through MMV_TERMS_DEFERRED so the host stays ahead of the device;
+--e2e-sync waits for each step's terms instead), the call the reference-side
+binding makes.  Cells are sharded over ranks (weak scaling: B per
 GPU fixed), gradients summed with ncclAllReduce inside mmv_step.
 """
 import argparse
@@ -48,6 +50,9 @@ def parse_args():
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"],
                     help="GEMM operand type: bf16 = tcgen05 tensor cores (fp32 accumulate), f32 = FFMA parity mode")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-order", default="step", choices=["update", "step"],
+                    help="e2e loop: issue the next minibatch's upload before (update) or after (step) the step call")
+    ap.add_argument("--e2e-sync", action="store_true", help="e2e loop waits for each step's loss terms before issuing the next step")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the CPU baseline sample")
     return ap.parse_args()
 
@@ -400,18 +405,50 @@ def run_own(args):
     slots = [mmv.CSR.create(ctx, B, cap, D, 0), mmv.CSR.create(ctx, B, cap, D, 0)]
     ar = np.arange(B, dtype=np.int64)
     h2d = int(np.mean([8 * (B + 1) + 8 * h[3] for h in host])) + 4 * B
+    # every step's loss terms ARE read on the host, one step late (MMV_TERMS_DEFERRED: the D2H copy of step k is
+    # waited for by the call that issues step k + 1, so the host stays one step ahead of the device); the last
+    # step's terms are collected inside the timed region.  The next minibatch's upload is issued AFTER the step call
+    # (--e2e-order step): issued before it, the step's own 16 KB cell-list DMA queues behind the 50 MB upload on the
+    # H2D engine.  Measured (65 k resident cells, ms/step): deferred + step-first 2.865, per-step sync 2.96,
+    # deferred + update-first 3.39; CSR resident in HBM 2.79.
     last = None
+    eflags = flags | (0 if args.e2e_sync else mmv.TERMS_DEFERRED)
     slots[0].update(B, *host[0][:3])
     for k in range(2):
         slots[(k + 1) % 2].update(B, *host[(k + 1) % n_host][:3])
-        last = model.step(slots[k % 2], ar, kl_weight=1.0, flags=flags)
+        last = model.step(slots[k % 2], ar, kl_weight=1.0, flags=eflags)
+    if not args.e2e_sync:
+        last = model.collect()
+    if os.environ.get("BENCH_DEBUG"):
+        model.set_option("profile", 1)
+        model.profile_read("")
     barrier()
     t0 = time.perf_counter()
     ctx.timer_start()
+    seen = 0
     for k in range(args.steps):
-        slots[(k + 1) % 2].update(B, *host[(k + 3) % n_host][:3])
-        last = model.step(slots[k % 2], ar, kl_weight=1.0, flags=flags)
-    ms_e2e = max(ctx.timer_stop(), 1e3 * (time.perf_counter() - t0))
+        if args.e2e_order == "update":
+            slots[(k + 1) % 2].update(B, *host[(k + 3) % n_host][:3])
+        t = model.step(slots[k % 2], ar, kl_weight=1.0, flags=eflags)
+        if args.e2e_order == "step":
+            slots[(k + 1) % 2].update(B, *host[(k + 3) % n_host][:3])
+        if k > 0 or args.e2e_sync:
+            assert np.isfinite(t["loss"])
+            seen += 1
+            last = t
+    if not args.e2e_sync:
+        last = model.collect()
+        seen += 1
+    assert seen == args.steps and np.isfinite(last["loss"])
+    ms_dev, ms_wall = ctx.timer_stop(), 1e3 * (time.perf_counter() - t0)
+    ms_e2e = max(ms_dev, ms_wall)
+    if os.environ.get("BENCH_DEBUG"):
+        print(f"[e2e] sync={args.e2e_sync} device {ms_dev / args.steps:.4f} ms/step, wall {ms_wall / args.steps:.4f} ms/step", file=sys.stderr)
+        for name in list(kernel_work(w, B, args.dtype == "bf16")) + ["allreduce", "colsum", "to_bf16"]:
+            t, c = model.profile_read(name)
+            if c:
+                print(f"[e2e]   {name:22s} {t / args.steps:.4f} ms/step ({c} groups)", file=sys.stderr)
+        model.set_option("profile", 0)
     barrier()
 
     # ---- secondary: unique cells/s under the reference's own schedule — per minibatch one

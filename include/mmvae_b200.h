@@ -150,7 +150,7 @@ MMV_API int mmv_model_get_grad(mmv_model *m, const char *name, float *host, int6
  *   kl_weight    : max(kl_max * exp(-kl_discount * epoch), kl_min), nb_vae_main.cc:27-32
  *   flags        : MMV_FWD | MMV_BWD | MMV_OPTIM
  *   out          : loss terms, written when the call returns (synchronises) unless NULL. */
-enum { MMV_FWD = 1, MMV_BWD = 2, MMV_OPTIM = 4, MMV_EPS_PHILOX = 8 };
+enum { MMV_FWD = 1, MMV_BWD = 2, MMV_OPTIM = 4, MMV_EPS_PHILOX = 8, MMV_TERMS_DEFERRED = 16 };
 
 typedef struct {
     float loss;       /* nb.hh:539-548 / vmf.hh:439: (recon + w*KL...) / B        */
@@ -162,6 +162,12 @@ typedef struct {
 
 MMV_API int mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int64_t *boot_idx,
              const float *eps, float kl_weight, int flags, mmv_loss_terms *out);
+
+/* MMV_TERMS_DEFERRED (with out != NULL): the call does not wait for the device.  The step's sums are copied to
+ * pinned memory behind an event and `out` receives the terms of the PREVIOUS deferred step (loss = NaN if none):
+ * the epoch loss of mmvae_alg.hh:281,324 is a sum, so the host loop can stay one step ahead of the device instead
+ * of paying the `.item()` round trip per batch.  mmv_step_collect waits for and returns the last pending terms. */
+MMV_API int mmv_step_collect(mmv_model *m, mmv_loss_terms *out);
 
 /* Per-kernel-group device times (CUDA events on the ctx stream), enabled with
  * mmv_model_set_option(m, "profile", 1).  mmv_profile_read synchronises, returns the

@@ -31,7 +31,7 @@ lib = C.CDLL(LIB_PATH)
 
 MMV_MAX_LAYERS = 8
 MMV_NAME_LEN = 96
-FWD, BWD, OPTIM, EPS_PHILOX = 1, 2, 4, 8
+FWD, BWD, OPTIM, EPS_PHILOX, TERMS_DEFERRED = 1, 2, 4, 8, 16
 
 
 class NbDims(C.Structure):
@@ -83,6 +83,7 @@ _PROTOS = {
     "mmv_model_get_param": [_vp, C.c_char_p, _vp, _i64],
     "mmv_model_get_grad": [_vp, C.c_char_p, _vp, _i64],
     "mmv_step": [_vp, _vp, _vp, _i64, _vp, _vp, C.c_float, C.c_int, C.POINTER(LossTerms)],
+    "mmv_step_collect": [_vp, C.POINTER(LossTerms)],
     "mmv_profile_read": [_vp, C.c_char_p, C.POINTER(C.c_float), C.POINTER(C.c_int)],
     "mmv_get_output": [_vp, C.c_char_p, _vp, _i64],
     "mmv_encode": [_vp, _vp, _vp, _i64, _vp, _vp],
@@ -326,6 +327,12 @@ class Model:
         _chk(lib.mmv_step(self.h, csr.h, _ptr(cells), len(cells), _ptr(boot), _ptr(eps), kl_weight, flags,
                           C.byref(terms) if want_terms else None))
         return terms.as_dict() if want_terms else None
+
+    def collect(self) -> dict:
+        """Terms of the last step issued with TERMS_DEFERRED (a step call with that flag returns the PREVIOUS one's)."""
+        terms = LossTerms()
+        _chk(lib.mmv_step_collect(self.h, C.byref(terms)))
+        return terms.as_dict()
 
     def profile_read(self, name: str = "") -> Tuple[float, int]:
         ms, cnt = C.c_float(), C.c_int()

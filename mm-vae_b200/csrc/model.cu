@@ -135,6 +135,17 @@ struct mmv_model {
     size_t grad_lazy_n = 0;               //   ... over grads[0, grad_lazy_n)
     double *h_acc = nullptr;              // pinned mirrors
     float *h_fscal = nullptr;
+    // MMV_TERMS_DEFERRED: two pinned slots; a step's sums are copied asynchronously and handed out by the next call
+    struct deferred_t {
+        double *acc = nullptr;
+        float *fscal = nullptr;
+        cudaEvent_t ev = nullptr;
+        double n = 1.;
+        float klw = 0.f;
+        int flags = 0;
+    } def[2];
+    unsigned def_i = 0;
+    int def_pending = -1;
     // pinned staging, two slots: the host prepares step k+1 while step k runs (no stream sync per step)
     int32_t *h_cells[2] = { nullptr, nullptr };
     float *h_eps[2] = { nullptr, nullptr };
@@ -439,6 +450,11 @@ mmv_model_destroy(mmv_model *m)
     comm_free_grads(m->ctx, m->grads, m->grads_win, m->grads_nccl);
     cudaFree(m->acc); cudaFree(m->fscal); cudaFree(m->params_bf16);
     cudaFreeHost(m->h_acc); cudaFreeHost(m->h_fscal);
+    for (auto &d : m->def) {
+        if (d.acc) cudaFreeHost(d.acc);
+        if (d.fscal) cudaFreeHost(d.fscal);
+        if (d.ev) cudaEventDestroy(d.ev);
+    }
     for (int i = 0; i < 2; ++i) {
         if (m->h_cells[i]) cudaFreeHost(m->h_cells[i]);
         if (m->h_eps[i]) cudaFreeHost(m->h_eps[i]);
@@ -1375,6 +1391,9 @@ stage_inputs(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const 
     }
     int32_t *d_cells = (int32_t *)m->W("cells", sizeof(int32_t) * B);
     NEED(d_cells);
+    // NB: this small DMA shares the H2D copy engine with mmv_csr_update's 50 MB minibatch upload.  A caller that
+    // streams minibatches should issue the NEXT upload after this call, not before it (bench.py --e2e-order): queued
+    // behind the upload, this copy holds the whole step back (3.39 vs 2.87 ms/step measured)
     MMV_CUDA(cudaMemcpyAsync(d_cells, h_cells, sizeof(int32_t) * B, cudaMemcpyHostToDevice, st));
     s.cells = d_cells;
 
@@ -1402,6 +1421,24 @@ stage_inputs(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const 
     }
     MMV_CUDA(cudaEventRecord(m->ev_stage[slot], st));
     return 0;
+}
+
+// loss terms from the device sums (nb.hh:542-547 / vmf.hh:439)
+void
+fill_terms(const mmv_model *m, const double *acc, const float *fscal, double n, float kl_weight, int flags, mmv_loss_terms *out)
+{
+    if (m->is_vmf) {   // vmf.hh:439
+        out->recon = (float)acc[5];
+        out->kl_mu = (float)acc[1];
+        out->kl_nu = 0.f;
+        out->loss = (float)(acc[1] / n * kl_weight - acc[5] / n);
+    } else {           // nb.hh:542-547
+        out->recon = (float)acc[0];
+        out->kl_mu = (float)acc[1];
+        out->kl_nu = (float)acc[2];
+        out->loss = (float)((acc[0] + kl_weight * acc[1] + kl_weight * acc[2]) / n);
+    }
+    out->grad_norm = (flags & MMV_OPTIM) ? fscal[1] : 0.f;
 }
 
 } // namespace
@@ -1527,22 +1564,47 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
     }
     if (!out) return 0;
 
+    const double n = (double)B * nranks;
+    if (flags & MMV_TERMS_DEFERRED) {
+        // no host wait on this step: its sums go to a pinned slot behind an event, and `out` gets the terms of the
+        // previous deferred step (NaN loss when there is none); mmv_step_collect drains the last one
+        mmv_model::deferred_t &d = m->def[m->def_i++ & 1u];
+        if (!d.acc) {
+            MMV_CUDA(cudaMallocHost(&d.acc, sizeof(double) * 8));
+            MMV_CUDA(cudaMallocHost(&d.fscal, sizeof(float) * 8));
+            MMV_CUDA(cudaEventCreateWithFlags(&d.ev, cudaEventDisableTiming));
+        }
+        const int prev = m->def_pending;
+        if (prev >= 0) {
+            MMV_CUDA(cudaEventSynchronize(m->def[prev].ev));
+            fill_terms(m, m->def[prev].acc, m->def[prev].fscal, m->def[prev].n, m->def[prev].klw, m->def[prev].flags, out);
+        } else {
+            std::memset(out, 0, sizeof(*out));
+            out->loss = NAN;
+        }
+        MMV_CUDA(cudaMemcpyAsync(d.acc, m->acc, sizeof(double) * 8, cudaMemcpyDeviceToHost, st));
+        MMV_CUDA(cudaMemcpyAsync(d.fscal, m->fscal, sizeof(float) * 8, cudaMemcpyDeviceToHost, st));
+        MMV_CUDA(cudaEventRecord(d.ev, st));
+        d.n = n; d.klw = kl_weight; d.flags = flags;
+        m->def_pending = (int)(&d - m->def);
+        return 0;
+    }
     MMV_CUDA(cudaMemcpyAsync(m->h_acc, m->acc, sizeof(double) * 8, cudaMemcpyDeviceToHost, st));
     MMV_CUDA(cudaMemcpyAsync(m->h_fscal, m->fscal, sizeof(float) * 8, cudaMemcpyDeviceToHost, st));
     MMV_CUDA(cudaStreamSynchronize(st));
-    const double n = (double)B * nranks;
-    if (m->is_vmf) {   // vmf.hh:439
-        out->recon = (float)m->h_acc[5];
-        out->kl_mu = (float)m->h_acc[1];
-        out->kl_nu = 0.f;
-        out->loss = (float)(m->h_acc[1] / n * kl_weight - m->h_acc[5] / n);
-    } else {           // nb.hh:542-547
-        out->recon = (float)m->h_acc[0];
-        out->kl_mu = (float)m->h_acc[1];
-        out->kl_nu = (float)m->h_acc[2];
-        out->loss = (float)((m->h_acc[0] + kl_weight * m->h_acc[1] + kl_weight * m->h_acc[2]) / n);
-    }
-    out->grad_norm = (flags & MMV_OPTIM) ? m->h_fscal[1] : 0.f;
+    fill_terms(m, m->h_acc, m->h_fscal, n, kl_weight, flags, out);
+    return 0;
+}
+
+int
+mmv_step_collect(mmv_model *m, mmv_loss_terms *out)
+{
+    MMV_CHECK(m && out, "mmv_step_collect: NULL");
+    MMV_CHECK(m->def_pending >= 0, "mmv_step_collect: no deferred step is pending");
+    mmv_model::deferred_t &d = m->def[m->def_pending];
+    MMV_CUDA(cudaEventSynchronize(d.ev));
+    fill_terms(m, d.acc, d.fscal, d.n, d.klw, d.flags, out);
+    m->def_pending = -1;
     return 0;
 }
 

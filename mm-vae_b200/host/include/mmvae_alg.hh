@@ -61,12 +61,16 @@ train_vae_model(MODEL &model, VISITOR &visitor, DATA_BLOCK &data_block, mmvae::d
             data_block.read(batch);
             const std::vector<int64_t> &cells = data_block.batch();
 
-            {   // reported loss: forward in train mode
+            {   // reported loss: forward in train mode.  Deferred: this call hands back the terms of the previous
+                // batch's evaluation, so the host never waits for the device inside the epoch (the reference pays
+                // one .item() round trip per batch, mmvae_alg.hh:281); the last batch is collected after the loop
                 mmv_loss_terms terms;
                 MMV_OK_EXIT(mmv_step(model.get(), dev.csr, cells.data(), batch_size, nullptr, nullptr, kl_weight,
-                                     MMV_FWD | MMV_EPS_PHILOX, &terms));
-                _loss_epoch += terms.loss * batch_size;
-                std::cerr << "\r[" << std::setw(20) << (b + 1) << "] " << std::setw(20) << terms.loss;
+                                     MMV_FWD | MMV_EPS_PHILOX | MMV_TERMS_DEFERRED, &terms));
+                if (b > 0) {
+                    _loss_epoch += terms.loss * batch_size;
+                    std::cerr << "\r[" << std::setw(20) << b << "] " << std::setw(20) << terms.loss;
+                }
             }
             for (int64_t boot = 0; boot < opt.nboot; ++boot) {
                 for (size_t r = 0; r < ridx.size(); ++r) ridx[r] = rboot(rng);
@@ -75,6 +79,11 @@ train_vae_model(MODEL &model, VISITOR &visitor, DATA_BLOCK &data_block, mmvae::d
             }
             if ((epoch + 1) % opt.recording == 0) visitor.update_on_batch(model, data_block, batch);
             data_block.clear();
+        }
+        {
+            mmv_loss_terms terms;
+            MMV_OK_EXIT(mmv_step_collect(model.get(), &terms));
+            _loss_epoch += terms.loss * batch_size;
         }
         std::cerr << "\r";
         _loss_epoch /= batch_size * nbatch;

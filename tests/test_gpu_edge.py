@@ -224,3 +224,27 @@ def test_full_size_properties(mmv, ctx, full_batch):
         assert rel_err(0.5 * (halves[0][1][k] + halves[1][1][k]), g) < 5e-3, k    # bf16 dlogits round per cell
     m.close()
     csr.close()
+
+
+def test_deferred_terms_are_the_previous_steps(mmv, ctx):
+    """MMV_TERMS_DEFERRED: no host wait; step k + 1 hands back exactly what a synchronous step k reported."""
+    D, B = 3000, 64
+    rng = np.random.default_rng(13)
+    x = synth(rng, 3 * B, D)
+    csr = mmv.CSR.from_dense(ctx, x)
+    eps = [[rng.normal(size=(B, n)).astype(np.float32) for n in (8, 1)] for _ in range(3)]
+    out = []
+    for deferred in (False, True):
+        m, _ = make_model(mmv, ctx, "nb1", D, [96], [80], 8, "f32", np.random.default_rng(3))
+        fl = mmv.FWD | mmv.BWD | mmv.OPTIM | (mmv.TERMS_DEFERRED if deferred else 0)
+        ts = [m.step(csr, np.arange(k * B, (k + 1) * B), eps=eps[k], kl_weight=0.5, flags=fl) for k in range(3)]
+        if deferred:
+            assert np.isnan(ts[0]["loss"])
+            ts = ts[1:] + [m.collect()]
+            with pytest.raises(mmv.MMVError):
+                m.collect()                      # nothing pending any more
+        out.append(ts)
+        m.close()
+    for a, b in zip(*out):
+        assert a == b, (a, b)
+    csr.close()
