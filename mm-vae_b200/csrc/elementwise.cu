@@ -223,7 +223,10 @@ launch_colsum(colsum_args_t a, cudaStream_t st)
         MMV_CUDA(cudaGetLastError());
         return 0;
     }
+    // narrow matrices (bias gradients of the hidden layers: N = 64 ... 1024): the pass is a chain of dependent row
+    // loads, so fewer rows per CTA (more CTAs, more atomics) until the grid covers the machine about four times
     a.rows_per_cta = 64;
+    while (a.rows_per_cta > 8 && (int64_t)ceil_div(a.N, 128) * ceil_div(a.M, a.rows_per_cta) < 592) a.rows_per_cta /= 2;
     dim3 grid(ceil_div(a.N, 128), ceil_div(a.M, a.rows_per_cta));
     colsum_kernel<<<grid, 128, 0, st>>>(a); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());

@@ -35,33 +35,68 @@ __global__ void
 batch_rowptr_kernel(panel_args_t p)
 {
     // minibatch-local CSR offsets (exclusive scan of the selected cells' run lengths) and the row
-    // scalars' bias terms (panel_build adds its per-split partial sums on top)
-    __shared__ int s_part[1024];
-    const int tid = threadIdx.x, T = blockDim.x, B = p.B;
+    // scalars' bias terms (panel_build adds its per-split partial sums on top).  One CTA, on the critical
+    // path of every step: a thread's rows are gathered with all their loads in flight (up to 8 rows per
+    // thread stay in registers for the second pass), the scan is two levels of warp shuffles.
+    __shared__ int s_warp[32];
+    const int tid = threadIdx.x, T = blockDim.x, B = p.B, lane = tid & 31, warp = tid >> 5;
     const int per = (B + T - 1) / T;
     const int r0 = min(B, tid * per), r1 = min(B, r0 + per);
+    constexpr int KEEP = 8;
+    int len[KEEP];
     int sum = 0;
-    for (int r = r0; r < r1; ++r) {
+#pragma unroll
+    for (int u = 0; u < KEEP; ++u) {
+        len[u] = 0;
+        const int r = r0 + u;
+        if (r < r1) {
+            const int64_t c = p.cells ? (int64_t)p.cells[r] : (int64_t)r;
+            len[u] = (int)(p.indptr[c + 1] - p.indptr[c]);
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < KEEP; ++u) sum += len[u];
+    for (int r = r0 + KEEP; r < r1; ++r) {
         const int64_t c = p.cells ? (int64_t)p.cells[r] : (int64_t)r;
         sum += (int)(p.indptr[c + 1] - p.indptr[c]);
+    }
+    for (int r = r0; r < r1; ++r) {
         if (p.wdepth) p.dpre[r] = p.bdepth[0];
         for (int h = 0; h < p.H; ++h) p.Hnu[(size_t)r * p.H + h] = p.bnu[h];
     }
-    s_part[tid] = sum;
-    __syncthreads();
-    for (int off = 1; off < T; off <<= 1) {   // Hillis-Steele inclusive scan
-        const int v = tid >= off ? s_part[tid - off] : 0;
-        __syncthreads();
-        s_part[tid] += v;
-        __syncthreads();
+    int inc = sum;                              // inclusive scan inside the warp
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
     }
-    int run = s_part[tid] - sum;
-    for (int r = r0; r < r1; ++r) {
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int w = lane < (T >> 5) ? s_warp[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += v;
+        }
+        s_warp[lane] = w;                       // inclusive totals of the warps
+    }
+    __syncthreads();
+    int run = inc - sum + (warp > 0 ? s_warp[warp - 1] : 0);
+#pragma unroll
+    for (int u = 0; u < KEEP; ++u) {
+        const int r = r0 + u;
+        if (r < r1) {
+            p.rowptr[r] = run;
+            run += len[u];
+        }
+    }
+    for (int r = r0 + KEEP; r < r1; ++r) {
         p.rowptr[r] = run;
         const int64_t c = p.cells ? (int64_t)p.cells[r] : (int64_t)r;
         run += (int)(p.indptr[c + 1] - p.indptr[c]);
     }
-    if (tid == T - 1) p.rowptr[B] = s_part[T - 1];
+    if (tid == T - 1) p.rowptr[B] = s_warp[(T >> 5) - 1];
 }
 
 constexpr int kPanelThreads = 512;
