@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--latent", type=int, default=None)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"],
                     help="GEMM operand type: bf16 = tcgen05 tensor cores (fp32 accumulate), f32 = FFMA parity mode")
+    ap.add_argument("--vmf-latent", action="store_true",
+                    help="vmf model with the true von Mises-Fisher latent (not in the reference; DESIGN K8)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-order", default="step", choices=["update", "step"],
                     help="e2e loop: issue the next minibatch's upload before (update) or after (step) the step call")
@@ -332,6 +334,8 @@ def run_own(args):
     else:
         model = mmv.Model.vmf(ctx, D, 1, w["latent"], w["enc"], w["dec"], seed=7)
     model.set_option("dtype", 1 if args.dtype == "bf16" else 0)
+    if args.vmf_latent:
+        model.set_option("vmf_latent", 1)
     # train every layer (the reference's unregistered-Sequential bug freezes them; its autograd still
     # computes their gradients, so this is the superset of the reference's per-step work)
     model.set_option("train_all_layers", 1)
@@ -377,7 +381,7 @@ def run_own(args):
         t, c = model.profile_read(name)
         if c:
             prof[name] = (t, c)
-    for name in ("batch_csc", "allreduce", "colsum", "to_bf16"):
+    for name in ("batch_csc", "allreduce", "colsum", "to_bf16", "vmf_latent"):
         t, c = model.profile_read(name)
         if c:
             prof[name] = (t, c)

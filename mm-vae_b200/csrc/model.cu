@@ -803,6 +803,7 @@ encoder_forward(const step_t &s, bool with_covar)
         v.kappa_max = m->vmf_kappa_max; v.lgamma_half_d = std::lgamma(0.5 * (double)R);
         v.w = WS("vmf_w", B); NEED(v.w);
         v.attempts = (int *)WS("vmf_attempts", B); NEED(v.attempts);
+        PROF("vmf_latent");
         return launch_vmf_latent_fwd(v, s.st);
     }
     return launch_reparam_fwd(r, s.st);
@@ -897,6 +898,7 @@ encoder_backward(const step_t &s, bool with_covar)
         if (with_covar) { v.r.Wce = m->P(m->covar_enc.w); v.r.bce = m->P(m->covar_enc.b); v.r.cov = s.cov; v.r.cells = s.cells; }
         v.kappa_max = m->vmf_kappa_max; v.lgamma_half_d = std::lgamma(0.5 * (double)R);
         v.w = m->ws["vmf_w"].as<float>();
+        PROF("vmf_latent");
         MMV_TRY(launch_vmf_latent_bwd(v, s.st));
     } else {
         MMV_TRY(launch_reparam_bwd(r, s.st));
