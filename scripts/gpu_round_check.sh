@@ -14,4 +14,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --
 timeout 300 python bench.py --model vmf --cells 16384 --steps 3 --warmup 3 --no-cpu-baseline > $O/${TAG}_bench_vmf_plain.log 2>&1 &&
 timeout 600 ncu --set full --import-source on --clock-control none -k regex:"vmf_likelihood_fast|nb_likelihood_fast" -s 4 -c 1 -f -o $O/${TAG}_vmf_full \
     python bench.py --model vmf --cells 16384 --steps 3 --warmup 3 --no-cpu-baseline > $O/${TAG}_ncu_vmf.log 2>&1
+timeout 600 ncu --set full --import-source on --clock-control none -k regex:"nb_likelihood_fast" -s 4 -c 1 -f -o $O/${TAG}_k4_full \
+    python bench.py --cells 16384 --steps 3 --warmup 3 --no-cpu-baseline > $O/${TAG}_ncu_k4.log 2>&1
+( time timeout 300 python bench.py --impl reference --steps 3 --warmup 1 ) > $O/${TAG}_bench_reference.log 2>&1; tail -c 400 $O/${TAG}_bench_reference.log
 ls -la $O | tail -20
