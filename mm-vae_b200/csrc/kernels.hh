@@ -267,6 +267,7 @@ struct vmf_latent_args_t {
     double lgamma_half_d = 0.;        // lgamma(R / 2)
     float *w = nullptr;               // [B] sampled cosine <z, mu>: written forward, read backward
     int *attempts = nullptr;          // [B] proposals used (nullable)
+    double *kl_aux = nullptr;         // [B x 2] A_d(kappa) and dKL/dkappa: written forward, read backward
 };
 int launch_vmf_latent_fwd(const vmf_latent_args_t &a, cudaStream_t st);
 int launch_vmf_latent_bwd(const vmf_latent_args_t &a, cudaStream_t st);

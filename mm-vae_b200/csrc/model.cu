@@ -803,6 +803,7 @@ encoder_forward(const step_t &s, bool with_covar)
         v.kappa_max = m->vmf_kappa_max; v.lgamma_half_d = std::lgamma(0.5 * (double)R);
         v.w = WS("vmf_w", B); NEED(v.w);
         v.attempts = (int *)WS("vmf_attempts", B); NEED(v.attempts);
+        v.kl_aux = (double *)WS("vmf_kl_aux", (size_t)4 * B); NEED(v.kl_aux);   // 2 doubles per cell
         PROF("vmf_latent");
         return launch_vmf_latent_fwd(v, s.st);
     }
@@ -898,6 +899,7 @@ encoder_backward(const step_t &s, bool with_covar)
         if (with_covar) { v.r.Wce = m->P(m->covar_enc.w); v.r.bce = m->P(m->covar_enc.b); v.r.cov = s.cov; v.r.cells = s.cells; }
         v.kappa_max = m->vmf_kappa_max; v.lgamma_half_d = std::lgamma(0.5 * (double)R);
         v.w = m->ws["vmf_w"].as<float>();
+        v.kl_aux = (double *)m->ws["vmf_kl_aux"].as<float>();
         PROF("vmf_latent");
         MMV_TRY(launch_vmf_latent_bwd(v, s.st));
     } else {

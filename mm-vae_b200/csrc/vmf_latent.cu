@@ -100,6 +100,7 @@ vmf_latent_fwd_kernel(vmf_latent_args_t A)
         double kl, dkl, Ab;
         kl_vmf_uniform(R, (double)r.kappa, A.lgamma_half_d, kl, dkl, Ab);
         if (a.kl_acc) atomicAdd(a.kl_acc, kl);
+        if (A.kl_aux) { A.kl_aux[2 * i] = Ab; A.kl_aux[2 * i + 1] = dkl; }   // the backward pass skips the recurrence
     }
     if (!a.eps) {                              // eval mode: z = mu (as reparameterize() returns the mean, vmf.hh:401)
         for (int k = lane; k < R; k += 32) z[k] = mu[k];
@@ -172,7 +173,8 @@ vmf_latent_bwd_kernel(vmf_latent_args_t A)
     const float *mu = a.mean + (size_t)i * R, *gz = a.dz + (size_t)i * R;
     float *dm = a.dhead + (size_t)i * 2 * R, *dk = dm + R;
     double kl, dkl, Ab;
-    kl_vmf_uniform(R, (double)r.kappa, A.lgamma_half_d, kl, dkl, Ab);   // every lane: A feeds the quadrature
+    if (A.kl_aux) { Ab = A.kl_aux[2 * i]; dkl = A.kl_aux[2 * i + 1]; }   // saved by the forward pass
+    else kl_vmf_uniform(R, (double)r.kappa, A.lgamma_half_d, kl, dkl, Ab);
     double dkappa = (double)(a.kl_weight * a.inv_B) * dkl;
     if (!a.eps) {                              // z = mu
         float pm = 0.f;

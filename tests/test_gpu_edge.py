@@ -157,7 +157,7 @@ def test_streamed_minibatch_is_bit_identical_to_resident(mmv, ctx, model):
         m.close()
         csr.close()
     (t0, g0), (t1, g1) = res
-    assert t0["loss"] == t1["loss"]
+    assert abs(t0["loss"] - t1["loss"]) <= 1e-6 * abs(t0["loss"])      # same rows, same order; sums use atomics
     # every gradient whose accumulation order does not depend on where the rows sit in memory is bit-equal;
     # float atomics (column sums) may differ in the last bits
     for k in g0:
@@ -245,6 +245,6 @@ def test_deferred_terms_are_the_previous_steps(mmv, ctx):
                 m.collect()                      # nothing pending any more
         out.append(ts)
         m.close()
-    for a, b in zip(*out):
-        assert a == b, (a, b)
+    for a, b in zip(*out):      # two separately built models: equal up to the atomic summation order of the fp32 GEMMs
+        assert all(abs(a[k] - b[k]) <= 1e-5 * max(abs(b[k]), 1e-6) for k in a), (a, b)
     csr.close()

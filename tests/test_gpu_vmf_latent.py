@@ -106,8 +106,11 @@ def test_draws_are_reproducible_and_distinct(mmv, ctx):
     a, _, _, _ = run(mmv, ctx, 2000, 64, 16, draw=5)
     b, _, _, _ = run(mmv, ctx, 2000, 64, 16, draw=5)
     c, _, _, _ = run(mmv, ctx, 2000, 64, 16, draw=6)
-    assert np.array_equal(a["z"], b["z"]) and np.array_equal(a["vmf_w"], b["vmf_w"])
-    assert not np.array_equal(a["vmf_w"], c["vmf_w"])
+    # same Philox stream -> same sample, up to the last bits of the encoder output (its fp32 split-K GEMMs add
+    # with atomics, so kappa and mu are reproducible to rounding only)
+    assert np.abs(a["vmf_w"] - b["vmf_w"]).max() < 1e-5 and np.abs(a["z"] - b["z"]).max() < 1e-4
+    assert np.array_equal(a["attempts"], b["attempts"])
+    assert np.abs(a["vmf_w"] - c["vmf_w"]).mean() > 1e-2
 
 
 @pytest.mark.parametrize("R,shift", [(32, 30.0), (128, 150.0)])
