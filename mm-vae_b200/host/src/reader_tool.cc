@@ -95,7 +95,8 @@ main(const int argc, const char *argv[])
                   << no.mean_latent << "\noverdispersion_encoding " << no.overdispersion_encoding << "\noverdispersion_latent "
                   << no.overdispersion_latent << "\nnb_relu " << no.do_relu << "\nencoding " << join(vo.encoding_layers)
                   << "\ndecoding " << join(vo.decoding_layers) << "\nlatent " << vo.latent << "\nkappa_min " << vo.kappa_min
-                  << "\nkappa_max " << vo.kappa_max << "\nvmf_relu " << vo.do_relu << std::endl;
+                  << "\nkappa_max " << vo.kappa_max << "\nvmf_relu " << vo.do_relu << "\nvmf_latent " << vo.vmf_latent
+                  << std::endl;
     } else {
         std::cerr << "bad command" << std::endl;
         return 2;

@@ -127,17 +127,18 @@ def test_option_defaults_and_aliases(tool, tmp_path):
     assert (kv["lr"], kv["grad_clip"], kv["nboot"], kv["max_epoch"], kv["recording"]) == ("0.001", "1", "3", "101", "10")
     assert (kv["mean_latent"], kv["overdispersion_encoding"], kv["overdispersion_latent"], kv["nb_relu"]) == ("2", "1", "1", "0")
     assert (kv["latent"], kv["kappa_min"], kv["kappa_max"], kv["vmf_relu"]) == ("2", "0.1", "10", "0")
+    assert kv["vmf_latent"] == "0"                      # the one option the reference does not have: off by default
     kv = dict(ln.split(" ", 1) if " " in ln else (ln, "") for ln in run(
         tool, "opts", "--mtx", mtx, "--output", "o", "--batch", "64", "--cov", "c.mtx.gz", "--kl_min", "0.5",
         "--learning_rate", "0.01", "--bootstrap", "5", "--epoch", "7", "--mean-encoding", "128,64", "--mean_decoding", "32",
         "--mean_latent", "10", "--overdisp-encoding", "3", "--overdispersion-latent", "2", "--relu", "--encoding", "16,8",
-        "--latent", "4", "--kappa-max", "20", "--seed", "9", "--dtype", "bf16", "--train_all_layers").splitlines())
+        "--latent", "4", "--kappa-max", "20", "--seed", "9", "--dtype", "bf16", "--train_all_layers", "--vmf_latent").splitlines())
     assert kv["out"] == "o" and kv["batch_size"] == "64" and kv["covar_mtx"] == "c.mtx.gz" and kv["covar_idx"] == "c.mtx.gz.index"
     assert kv["kl_min"] == "0.5" and kv["lr"] == "0.01" and kv["nboot"] == "5" and kv["max_epoch"] == "7"
     assert kv["mean_encoding"] == "128,64" and kv["mean_decoding"] == "32" and kv["mean_latent"] == "10"
     assert kv["overdispersion_encoding"] == "3" and kv["overdispersion_latent"] == "2" and kv["nb_relu"] == "1"
     assert kv["encoding"] == "16,8" and kv["latent"] == "4" and kv["kappa_max"] == "20" and kv["vmf_relu"] == "1"
-    assert kv["seed"] == "9" and kv["bf16"] == "1" and kv["train_all_layers"] == "1"
+    assert kv["seed"] == "9" and kv["bf16"] == "1" and kv["train_all_layers"] == "1" and kv["vmf_latent"] == "1"
     # missing --out fails like the reference (ERR_RET "need output file header")
     p = subprocess.run([tool, "opts", "--mtx", mtx], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
     assert "rc 1" in p.stdout and "need output file header" in p.stderr
