@@ -111,7 +111,7 @@ load_inputs(const mmvae_options_t &main_options, run_inputs_t &in)
 {
     if (!file_exists(main_options.mtx)) return EXIT_FAILURE;
     if (!file_exists(main_options.idx)) CHK(mmutil::index::build_mmutil_index(main_options.mtx, main_options.idx));
-    in.data.reset(new mmvae::mtx_data_block_t(main_options.mtx, main_options.idx, main_options.batch_size));
+    in.data.reset(new mmvae::mtx_data_block_t(main_options.mtx, main_options.idx, main_options.batch_size, main_options.csr_cache));
     if (file_exists(main_options.covar_mtx)) {
         if (!file_exists(main_options.covar_idx))
             CHK(mmutil::index::build_mmutil_index(main_options.covar_mtx, main_options.covar_idx));

@@ -22,6 +22,7 @@
 #include <unordered_map>
 #include <cstdlib>
 #include <functional>
+#include <sys/stat.h>
 #include <thread>
 
 namespace mmutil {
@@ -194,7 +195,9 @@ public:
     using Index = std::ptrdiff_t;
 
     // Reads the header and the index, then parses the whole file once into CSR.
-    mtx_data_block_t(const std::string &mtx_file, const std::string &idx_file, const Index batch_size)
+    // csr_cache (or MMV_CSR_CACHE=1): keep the parsed CSR as ${idx_file}.csr beside the index, so that a later run
+    // on the same, unchanged mtx file maps three arrays instead of inflating and parsing the text again.
+    mtx_data_block_t(const std::string &mtx_file, const std::string &idx_file, const Index batch_size, bool csr_cache = false)
         : mtx_file_(mtx_file), idx_file_(idx_file), B_(batch_size)
     {
         mmutil::index::mtx_header_t h;
@@ -202,7 +205,14 @@ public:
         D_ = h.max_row;   // rows = features, columns = data points (mmvae_io.hh:264-267)
         N_ = h.max_col;
         ASSERT(mmutil::index::read_mmutil_index(idx_file, index_tab_) == EXIT_SUCCESS, "failed to read " << idx_file);
+        if (const char *e = std::getenv("MMV_CSR_CACHE")) csr_cache = csr_cache || std::atoi(e) != 0;
+        if (csr_cache && load_cache()) {
+            TLOG("Read " << idx_file_ << ".csr: " << D_ << " features x " << N_ << " data points, " << indices.size()
+                         << " nonzeros (binary CSR cache of " << mtx_file << ")");
+            return;
+        }
         ASSERT(parse_all() == EXIT_SUCCESS, "failed to parse " << mtx_file);
+        if (csr_cache && !save_cache()) WLOG("could not write " << idx_file_ << ".csr");
         TLOG("Read " << mtx_file << ": " << D_ << " features x " << N_ << " data points, " << indices.size()
                      << " nonzeros resident as CSR (" << ingest_threads_ << " reader threads: parse " << parse_seconds_
                      << " s, merge " << merge_seconds_ << " s)");
@@ -268,7 +278,71 @@ public:
     std::vector<int32_t> indices;   // gene ids, increasing inside a cell
     std::vector<float> values;
 
+    bool from_cache() const { return from_cache_; }
+
 private:
+    // ---- binary CSR cache: header {magic, D, N, nnz, mtx size, mtx mtime (ns), index-table checksum}, then
+    //      indptr int64[N + 1], indices int32[nnz], values fp32[nnz].  Valid only for the byte-identical mtx file.
+    struct cache_header_t {
+        char magic[8];
+        int64_t D, N, nnz, mtx_size, mtx_mtime_ns;
+        uint64_t index_sum;
+    };
+    bool cache_key(cache_header_t &k) const
+    {
+        struct stat st;
+        if (::stat(mtx_file_.c_str(), &st) != 0) return false;
+        std::memset(&k, 0, sizeof(k));
+        std::memcpy(k.magic, "MMVCSR1", 8);
+        k.D = (int64_t)D_; k.N = (int64_t)N_; k.nnz = 0;
+        k.mtx_size = (int64_t)st.st_size;
+        k.mtx_mtime_ns = (int64_t)st.st_mtim.tv_sec * 1000000000LL + (int64_t)st.st_mtim.tv_nsec;
+        uint64_t hsh = 1469598103934665603ull;                       // FNV-1a over the index table
+        for (Index v : index_tab_) { hsh ^= (uint64_t)v; hsh *= 1099511628211ull; }
+        k.index_sum = hsh;
+        return true;
+    }
+    bool load_cache()
+    {
+        cache_header_t want, got;
+        if (!cache_key(want)) return false;
+        FILE *f = std::fopen((idx_file_ + ".csr").c_str(), "rb");
+        if (!f) return false;
+        bool ok = std::fread(&got, sizeof(got), 1, f) == 1 && std::memcmp(got.magic, want.magic, 8) == 0 && got.D == want.D &&
+            got.N == want.N && got.mtx_size == want.mtx_size && got.mtx_mtime_ns == want.mtx_mtime_ns &&
+            got.index_sum == want.index_sum && got.nnz >= 0;
+        if (ok) {
+            indptr.resize((size_t)N_ + 1); indices.resize((size_t)got.nnz); values.resize((size_t)got.nnz);
+            ok = std::fread(indptr.data(), 8, indptr.size(), f) == indptr.size() &&
+                std::fread(indices.data(), 4, indices.size(), f) == indices.size() &&
+                std::fread(values.data(), 4, values.size(), f) == values.size() && std::fgetc(f) == EOF;
+            ok = ok && indptr.front() == 0 && indptr.back() == got.nnz;
+            for (size_t c = 0; ok && c < (size_t)N_; ++c) ok = indptr[c] <= indptr[c + 1];
+            for (size_t q = 0; ok && q < indices.size(); ++q) ok = indices[q] >= 0 && indices[q] < (int32_t)D_;
+        }
+        std::fclose(f);
+        if (!ok) { indptr.clear(); indices.clear(); values.clear(); }
+        from_cache_ = ok;
+        return ok;
+    }
+    bool save_cache() const
+    {
+        cache_header_t k;
+        if (!cache_key(k)) return false;
+        k.nnz = (int64_t)indices.size();
+        const std::string path = idx_file_ + ".csr", tmp = path + ".tmp";
+        FILE *f = std::fopen(tmp.c_str(), "wb");
+        if (!f) return false;
+        bool ok = std::fwrite(&k, sizeof(k), 1, f) == 1 && std::fwrite(indptr.data(), 8, indptr.size(), f) == indptr.size() &&
+            std::fwrite(indices.data(), 4, indices.size(), f) == indices.size() &&
+            std::fwrite(values.data(), 4, values.size(), f) == values.size();
+        ok = (std::fclose(f) == 0) && ok;
+        if (ok) ok = std::rename(tmp.c_str(), path.c_str()) == 0;   // readers never see a half-written cache
+        if (!ok) std::remove(tmp.c_str());
+        return ok;
+    }
+    bool from_cache_ = false;
+
     // One pass over the file into CSR.  The text is split at column boundaries taken from the index table
     // (bgzf virtual offsets, mmutil_index.hh:138-228) into one range per host thread; every thread inflates
     // and parses its own range with its own reader (mmutil_bgzf_util.hh:53-151 semantics), and the triplets

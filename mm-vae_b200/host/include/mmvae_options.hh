@@ -45,11 +45,12 @@ scan_options(int argc, const char *argv[], const char *short_opts, const option 
 } // namespace mmvae_detail
 
 struct mmvae_options_t {
-    explicit mmvae_options_t() : batch_size(100), kl_discount(.1f), kl_min(1e-2f), kl_max(1.f) { }
+    explicit mmvae_options_t() : batch_size(100), kl_discount(.1f), kl_min(1e-2f), kl_max(1.f), csr_cache(false) { }
     std::string mtx, idx, out, row, col, annot;
     std::string covar_mtx, covar_idx;
     int64_t batch_size;
     float kl_discount, kl_min, kl_max;
+    bool csr_cache;   // NOT in the reference (long option only): keep the parsed CSR as ${idx}.csr for the next run
 };
 
 inline int
@@ -64,7 +65,8 @@ parse_mmvae_options(const int argc, const char *argv[], mmvae_options_t &options
                         "--out         : output file header\n"
                         "--covar       : a separate matrix market mtx for other covariates\n"
                         "--covar_idx   : an index file for the covar mtx (default: ${covar}.index)\n"
-                        "--batch_size  : #samples in each batch (default: 100)\n\n"
+                        "--batch_size  : #samples in each batch (default: 100)\n"
+                        "--csr_cache   : keep the parsed counts as ${idx}.csr and reuse it while the mtx file is unchanged\n\n"
                         "--kl_discount : KL divergence discount (default: 0)\n"
                         "              : Loss = likelihood_loss + beta * KL_loss\n"
                         "              : where beta = exp(- ${discount} * epoch)\n"
@@ -79,6 +81,7 @@ parse_mmvae_options(const int argc, const char *argv[], mmvae_options_t &options
                                  { "annotation", required_argument, nullptr, 'a' }, { "batch_size", required_argument, nullptr, 'b' },
                                  { "batch", required_argument, nullptr, 'b' },      { "kl_discount", required_argument, nullptr, 'K' },
                                  { "kl_max", required_argument, nullptr, 'L' },     { "kl_min", required_argument, nullptr, 'l' },
+                                 { "csr_cache", no_argument, nullptr, 1002 },       { "csr-cache", no_argument, nullptr, 1002 },
                                  { "help", no_argument, nullptr, 'h' },             { nullptr, no_argument, nullptr, 0 } };
     bool help = false;
     mmvae_detail::scan_options(argc, argv, "M:I:O:V:J:r:c:a:b:K:L:l:h?", long_opts, [&](int opt, const char *arg) {
@@ -95,6 +98,7 @@ parse_mmvae_options(const int argc, const char *argv[], mmvae_options_t &options
         case 'K': options.kl_discount = std::stof(arg); break;
         case 'l': options.kl_min = std::stof(arg); break;
         case 'L': options.kl_max = std::stof(arg); break;
+        case 1002: options.csr_cache = true; break;
         case 'h': help = true; break;
         default: break;
         }

@@ -51,12 +51,13 @@ main(const int argc, const char *argv[])
         a.insert(a.end(), b.begin(), b.end());
         write_raw(argv[4], a.data(), a.size() * 4);
         std::printf("%ld %ld %ld\n", (long)blk.nfeature(), (long)blk.ntot(), (long)blk.indices.size());
-    } else if (cmd == "csr" && argc == 5) {           // csr <mtx> <idx> <out prefix>
-        mmvae::mtx_data_block_t blk(argv[2], argv[3], 1);
+    } else if (cmd == "csr" && (argc == 5 || argc == 6)) {   // csr <mtx> <idx> <out prefix> [cache]: last line says where it came from
+        mmvae::mtx_data_block_t blk(argv[2], argv[3], 1, argc == 6);
         write_raw(std::string(argv[4]) + ".indptr", blk.indptr.data(), blk.indptr.size() * 8);
         write_raw(std::string(argv[4]) + ".indices", blk.indices.data(), blk.indices.size() * 4);
         write_raw(std::string(argv[4]) + ".values", blk.values.data(), blk.values.size() * 4);
         std::printf("%ld %ld %ld\n", (long)blk.nfeature(), (long)blk.ntot(), (long)blk.indices.size());
+        if (argc == 6) std::printf("%s\n", blk.from_cache() ? "cache" : "parsed");
     } else if (cmd == "floats") {                     // take_float of each argument -> bits
         for (int i = 2; i < argc; ++i) {
             const float w = mmvae::take_float(argv[i], std::strlen(argv[i]));
@@ -95,7 +96,7 @@ main(const int argc, const char *argv[])
                   << no.mean_latent << "\noverdispersion_encoding " << no.overdispersion_encoding << "\noverdispersion_latent "
                   << no.overdispersion_latent << "\nnb_relu " << no.do_relu << "\nencoding " << join(vo.encoding_layers)
                   << "\ndecoding " << join(vo.decoding_layers) << "\nlatent " << vo.latent << "\nkappa_min " << vo.kappa_min
-                  << "\nkappa_max " << vo.kappa_max << "\nvmf_relu " << vo.do_relu << "\nvmf_latent " << vo.vmf_latent
+                  << "\nkappa_max " << vo.kappa_max << "\nvmf_relu " << vo.do_relu << "\nvmf_latent " << vo.vmf_latent << "\ncsr_cache " << mo.csr_cache
                   << std::endl;
     } else {
         std::cerr << "bad command" << std::endl;

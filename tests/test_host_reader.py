@@ -127,18 +127,19 @@ def test_option_defaults_and_aliases(tool, tmp_path):
     assert (kv["lr"], kv["grad_clip"], kv["nboot"], kv["max_epoch"], kv["recording"]) == ("0.001", "1", "3", "101", "10")
     assert (kv["mean_latent"], kv["overdispersion_encoding"], kv["overdispersion_latent"], kv["nb_relu"]) == ("2", "1", "1", "0")
     assert (kv["latent"], kv["kappa_min"], kv["kappa_max"], kv["vmf_relu"]) == ("2", "0.1", "10", "0")
-    assert kv["vmf_latent"] == "0"                      # the one option the reference does not have: off by default
+    assert kv["vmf_latent"] == "0" and kv["csr_cache"] == "0"   # options the reference does not have: off by default
     kv = dict(ln.split(" ", 1) if " " in ln else (ln, "") for ln in run(
         tool, "opts", "--mtx", mtx, "--output", "o", "--batch", "64", "--cov", "c.mtx.gz", "--kl_min", "0.5",
         "--learning_rate", "0.01", "--bootstrap", "5", "--epoch", "7", "--mean-encoding", "128,64", "--mean_decoding", "32",
         "--mean_latent", "10", "--overdisp-encoding", "3", "--overdispersion-latent", "2", "--relu", "--encoding", "16,8",
-        "--latent", "4", "--kappa-max", "20", "--seed", "9", "--dtype", "bf16", "--train_all_layers", "--vmf_latent").splitlines())
+        "--latent", "4", "--kappa-max", "20", "--seed", "9", "--dtype", "bf16", "--train_all_layers", "--vmf_latent", "--csr_cache").splitlines())
     assert kv["out"] == "o" and kv["batch_size"] == "64" and kv["covar_mtx"] == "c.mtx.gz" and kv["covar_idx"] == "c.mtx.gz.index"
     assert kv["kl_min"] == "0.5" and kv["lr"] == "0.01" and kv["nboot"] == "5" and kv["max_epoch"] == "7"
     assert kv["mean_encoding"] == "128,64" and kv["mean_decoding"] == "32" and kv["mean_latent"] == "10"
     assert kv["overdispersion_encoding"] == "3" and kv["overdispersion_latent"] == "2" and kv["nb_relu"] == "1"
     assert kv["encoding"] == "16,8" and kv["latent"] == "4" and kv["kappa_max"] == "20" and kv["vmf_relu"] == "1"
     assert kv["seed"] == "9" and kv["bf16"] == "1" and kv["train_all_layers"] == "1" and kv["vmf_latent"] == "1"
+    assert kv["csr_cache"] == "1"
     # missing --out fails like the reference (ERR_RET "need output file header")
     p = subprocess.run([tool, "opts", "--mtx", mtx], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
     assert "rc 1" in p.stdout and "need output file header" in p.stderr
@@ -182,3 +183,43 @@ def test_parallel_ingest_equals_sequential(tool, tag, tmp_path):
         outs.append([open(str(prefix) + ext, "rb").read() for ext in (".indptr", ".indices", ".values")])
     assert outs[0] == outs[1] == outs[2]
     assert len(outs[0][1]) > 0
+
+
+def test_binary_csr_cache(tool, tmp_path):
+    """--csr_cache (not in the reference): ${idx}.csr holds the parsed CSR; it is used only while the
+    mtx file is byte-identical (size, mtime, index table), and gives byte-identical arrays."""
+    import shutil
+    import time
+    src = os.path.join(GOLDEN, FILES["b"])
+    mtx = tmp_path / "m.mtx.gz"
+    shutil.copy(src, mtx)
+    idx = tmp_path / "m.index"
+    run(tool, "table", mtx, idx)
+    arrays = lambda p: [np.fromfile(str(tmp_path / p) + s, dtype=np.uint8) for s in (".indptr", ".indices", ".values")]
+    run(tool, "csr", mtx, idx, tmp_path / "plain")
+    out = run(tool, "csr", mtx, idx, tmp_path / "first", "cache").split("\n")
+    assert out[1] == "parsed" and os.path.exists(str(idx) + ".csr") and not os.path.exists(str(idx) + ".csr.tmp")
+    out2 = run(tool, "csr", mtx, idx, tmp_path / "second", "cache").split("\n")
+    assert out2[1] == "cache" and out2[0] == out[0]
+    for a, b, c in zip(arrays("plain"), arrays("first"), arrays("second")):
+        assert np.array_equal(a, b) and np.array_equal(a, c)
+    # the environment variable turns it on without the option
+    env = dict(os.environ, MMV_CSR_CACHE="1")
+    p = subprocess.run([tool, "csr", str(mtx), str(idx), str(tmp_path / "env")], check=True, env=env, stdout=subprocess.PIPE,
+                       stderr=subprocess.PIPE, text=True)
+    assert "binary CSR cache" in p.stderr
+    # a touched file (same bytes, new mtime) and a different file both invalidate it
+    time.sleep(0.01)
+    os.utime(mtx, ns=(time.time_ns(), time.time_ns()))
+    assert run(tool, "csr", mtx, idx, tmp_path / "third", "cache").split("\n")[1] == "parsed"
+    assert run(tool, "csr", mtx, idx, tmp_path / "fourth", "cache").split("\n")[1] == "cache"
+    shutil.copy(os.path.join(GOLDEN, FILES["a"]), mtx)
+    run(tool, "table", mtx, idx)
+    out5 = run(tool, "csr", mtx, idx, tmp_path / "fifth", "cache").split("\n")
+    assert out5[1] == "parsed" and out5[0] != out[0]
+    # a truncated cache is rejected, not trusted
+    blob = open(str(idx) + ".csr", "rb").read()
+    open(str(idx) + ".csr", "wb").write(blob[:-3])
+    assert run(tool, "csr", mtx, idx, tmp_path / "sixth", "cache").split("\n")[1] == "parsed"
+    for a, b in zip(arrays("fifth"), arrays("sixth")):
+        assert np.array_equal(a, b)
