@@ -85,6 +85,25 @@ def test_vmf_vae_main_with_vmf_latent(bins, tmp_path):
     assert np.all(lv <= 0) and np.abs(lv - lv[:, :1]).max() == 0          # -log kappa, kappa >= 1, one value per cell
 
 
+def test_nb_vae_main_with_csr_cache(bins, tmp_path):
+    """--csr_cache: the second run trains from ${idx}.csr instead of the text and reports the same epoch losses."""
+    import shutil
+    mtx = tmp_path / "b.mtx.gz"
+    shutil.copy(os.path.join(GOLDEN, "reader_b.mtx.gz"), mtx)
+    res = []
+    for k in range(2):
+        out = tmp_path / f"run{k}"
+        cmd = [os.path.join(bins, "nb_vae"), "--mtx", str(mtx), "--out", str(out), "--batch_size", "100", "--mean_encoding", "32",
+               "--mean_decoding", "32", "--mean_latent", "4", "--max_epoch", "3", "--recording", "3", "--nboot", "1", "--seed", "5",
+               "--skip_param_record", "--csr_cache"]
+        p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
+        assert p.returncode == 0, p.stderr[-2000:]
+        assert ("binary CSR cache" in p.stderr) == (k == 1)
+        res.append(scores(str(out) + ".scores.gz"))
+    assert os.path.exists(str(mtx) + ".index.csr")
+    assert np.allclose(res[0], res[1], rtol=1e-4)
+
+
 def test_main_fails_like_reference_without_out(bins):
     p = subprocess.run([os.path.join(bins, "nb_vae"), "--mtx", os.path.join(GOLDEN, "reader_b.mtx.gz")],
                        stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=60)
