@@ -63,11 +63,35 @@ visit_bgzf_block(const std::string &mtx_file, const int64_t beg_pos, const int64
     ERR_RET(!fp.open(mtx_file), "unable to open " << mtx_file);
     fp.seek(beg_pos);
     std::string line, tok[3];
+    auto is_space = [](char c) { return c == ' ' || (c >= 9 && c <= 13); };
+    auto is_digit = [](char c) { return c >= '0' && c <= '9'; };
     while (fp.getline(line) >= 0) {
         if (line.empty() || line[0] == '%') continue;
-        if (mmvae::split_triplet_line(line, tok) < 3) continue;
-        fun((Index)mmvae::take_uint64(tok[0].data(), tok[0].size()) - 1,
-            (Index)mmvae::take_uint64(tok[1].data(), tok[1].size()) - 1, mmvae::take_float(tok[2].data(), tok[2].size()));
+        // the shape every writer produces — "digits SP digits SP token", nothing else on the line — is split in
+        // place (same three tokens the state machine below would cut, no copies); any other line takes the
+        // reference's whitespace state machine
+        const char *p = line.data(), *const e = p + line.size();
+        const char *t0 = p;
+        while (p < e && is_digit(*p)) ++p;
+        const char *t0e = p, *t1 = nullptr, *t1e = nullptr, *t2 = nullptr;
+        if (p > t0 && p < e && *p == ' ') {
+            t1 = ++p;
+            while (p < e && is_digit(*p)) ++p;
+            t1e = p;
+            if (p > t1 && p < e && *p == ' ') {
+                t2 = ++p;
+                while (p < e && !is_space(*p)) ++p;
+                if (p != e || p == t2) t2 = nullptr;
+            }
+        }
+        if (t2) {
+            fun((Index)mmvae::take_uint64(t0, (size_t)(t0e - t0)) - 1, (Index)mmvae::take_uint64(t1, (size_t)(t1e - t1)) - 1,
+                mmvae::take_float(t2, (size_t)(e - t2)));
+        } else {
+            if (mmvae::split_triplet_line(line, tok) < 3) continue;
+            fun((Index)mmvae::take_uint64(tok[0].data(), tok[0].size()) - 1,
+                (Index)mmvae::take_uint64(tok[1].data(), tok[1].size()) - 1, mmvae::take_float(tok[2].data(), tok[2].size()));
+        }
         if (end_pos != 0 && fp.tell() >= end_pos) break;
     }
     return EXIT_SUCCESS;
