@@ -106,3 +106,23 @@ def test_vmf_vae_schedule_and_vmf_latent_option(stub, tmp_path):
     # without the flag the option is never touched: the default path is the reference's
     calls2, _ = run_main(stub, tmp_path, "vmf_vae", "--batch", 250, "--epoch", 1, "--latent", 4, "--skip_param_record")
     assert "vmf_latent" not in {c[1]["key"] for c in calls2 if c[0] == "set_option"}
+
+
+def test_covariate_file_reaches_the_abi(stub, tmp_path):
+    """--covar: a C x N Matrix Market file is read through the same reader, uploaded as the dense
+    covariate block, and the model is built with c_dim = C (nb_vae_main.cc:65-82)."""
+    from oracle import bgzf_mtx
+    rng = np.random.default_rng(3)
+    C = 2
+    lines = [f"%%MatrixMarket matrix coordinate real general\n{C} {N} {C * N}\n"]
+    for c in range(N):
+        for r in range(C):
+            lines.append(f"{r + 1} {c + 1} {rng.normal():.4f}\n")
+    cov = tmp_path / "cov.mtx.gz"
+    bgzf_mtx.bgzf_write(str(cov), "".join(lines).encode())
+    calls, _ = run_main(stub, tmp_path, "nb_vae", "--covar", cov, "--batch_size", 250, "--max_epoch", 1, "--nboot", 1,
+                        "--skip_param_record")
+    up = [c[1] for c in calls if c[0] == "csr_upload"][0]
+    mdl = [c[1] for c in calls if c[0] == "nb_model"][0]
+    assert (up["covar"], up["c_dim"], mdl["c"]) == ("1", str(C), str(C))
+    assert os.path.exists(str(cov) + ".index")                      # built on demand like the data index
