@@ -343,7 +343,7 @@ def kernel_work(w, B, bf16=True, n_gpus=1):
         "gemm_dec_last_dw": ("tensor", gemm_last), "gemm_other": ("tensor", other),
         # K4/K5: logits read as fp32, gradient written as bf16 in tensor-core mode
         "nb_likelihood": ("hbm", (6.0 if bf16 else 8.0) * B * D + 8 * nnz + 4.0 * D * (2 + 2 * Rn) + 16 * B),
-        "vmf_likelihood": ("hbm", 8.0 * B * D + 8 * nnz + 4.0 * D * w["c_dim"] + 16 * B),
+        "vmf_likelihood": ("hbm", (6.0 if bf16 else 8.0) * B * D + 8 * nnz + 4.0 * D * w["c_dim"] + 16 * B),
         # K1: in tensor-core mode the first layer is a densify-in-smem tcgen05 GEMM, judged on the
         # dense-equivalent flops; in fp32 mode it is the gather kernel, judged on compulsory HBM bytes
         "senc_fwd": ("tensor", 2.0 * B * D * h1) if bf16 else
