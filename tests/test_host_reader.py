@@ -223,3 +223,32 @@ def test_binary_csr_cache(tool, tmp_path):
     assert run(tool, "csr", mtx, idx, tmp_path / "sixth", "cache").split("\n")[1] == "parsed"
     for a, b in zip(arrays("fifth"), arrays("sixth")):
         assert np.array_equal(a, b)
+
+
+def test_synthetic_shard_roundtrip_through_mtx(tool, tmp_path):
+    """a subsample of the benchmark's synthetic NB counts (bench.gen_shard, cfg-3 feature count) written as
+    bgzf Matrix Market, indexed and read back by the host reader gives the identical CSR — the device-generated
+    shards and the file path index cells and genes the same way."""
+    import importlib.util
+    import torch
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    n, D = 400, 20_000
+    indptr, indices, values, longest = bench.gen_shard(n, D, 0.05, 7, torch.device("cpu"), chunk=128)
+    indptr, indices, values = indptr.numpy(), indices.numpy(), values.numpy()
+    assert 0.04 < len(indices) / (n * D) < 0.06 and (np.diff(indptr) >= 1).all() and longest == np.diff(indptr).max()
+    cell = np.repeat(np.arange(n), np.diff(indptr))
+    txt = tmp_path / "s.mtx"
+    with open(txt, "w") as f:
+        f.write(f"%%MatrixMarket matrix coordinate integer general\n{D} {n} {len(indices)}\n")
+        f.write("\n".join(f"{g + 1} {c + 1} {int(v)}" for g, c, v in zip(indices.tolist(), cell.tolist(), values.tolist())))
+        f.write("\n")
+    gz, idx = tmp_path / "s.mtx.gz", tmp_path / "s.index"
+    run(tool, "write", txt, gz)
+    run(tool, "table", gz, idx)
+    Dn, Nn, nnz = [int(v) for v in run(tool, "csr", gz, idx, tmp_path / "c").split()]
+    assert (Dn, Nn, nnz) == (D, n, len(indices))
+    assert np.array_equal(np.fromfile(str(tmp_path / "c") + ".indptr", dtype=np.int64), indptr)
+    assert np.array_equal(np.fromfile(str(tmp_path / "c") + ".indices", dtype=np.int32), indices)
+    assert np.array_equal(np.fromfile(str(tmp_path / "c") + ".values", dtype=np.float32), values)
