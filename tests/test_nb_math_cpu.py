@@ -50,7 +50,7 @@ def count_terms(nu, x):
 def test_zero_count_shortcut():
     rng = np.random.default_rng(0)
     m, nu = rng.uniform(1e-4, 50, 1000), rng.uniform(2e-4, 1e4, 1000)
-    assert np.allclose(nll_full(0.0, m, nu), nu * np.log1p(m / nu), rtol=1e-9, atol=1e-12)   # the full form cancels log(m + nu) - log(nu)
+    assert np.allclose(nll_full(0.0, m, nu), nu * np.log1p(m / nu), rtol=1e-8, atol=1e-12)   # the full form cancels log(m + nu) - log(nu)
 
 
 def test_count_terms_match_gammaln_digamma():
