@@ -117,3 +117,30 @@ def test_plain_row_interval_test_is_sound():
         u = u2 / l2e
         spv = np.log1p(np.exp(u))
         assert u < 20 and 1e-4 <= spv <= 1e4
+
+
+def test_vmf_data_term_gradient_vs_finite_differences():
+    """K5 (vmf.hh:283-290,419-440): recon = normalise(q), q = exp(pre) + cv; t = <yobs, recon>; per-cell loss -kappa t / B.
+    Hand-derived: dL/dq = -kappa (yobs - recon t) / (B ||q||), dL/dpre = dL/dq exp(pre)."""
+    rng = np.random.default_rng(4)
+    D, B, kappa = 40, 7.0, 2.3
+    pre, cv = rng.normal(size=D), rng.uniform(0, 0.3, size=D)
+    x = rng.poisson(0.4, size=D).astype(float)
+    yobs = np.log1p(x) + 1e-2 / D
+    yobs /= np.linalg.norm(yobs)
+
+    def loss(pre):
+        q = np.exp(pre) + cv
+        return -kappa * (yobs @ (q / np.linalg.norm(q))) / B
+
+    q = np.exp(pre) + cv
+    qn = np.linalg.norm(q)
+    t = yobs @ (q / qn)
+    dq = -kappa * (yobs - (q / qn) * t) / (B * qn)
+    dpre = dq * np.exp(pre)
+    assert abs(dq @ q) < 1e-12                      # the gradient is tangent to the sphere
+    for k in range(0, D, 5):
+        e = np.zeros(D)
+        e[k] = 1e-6
+        fd = (loss(pre + e) - loss(pre - e)) / 2e-6
+        assert abs(dpre[k] - fd) <= 1e-7 * max(1e-3, abs(fd))
