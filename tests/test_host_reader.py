@@ -252,3 +252,29 @@ def test_synthetic_shard_roundtrip_through_mtx(tool, tmp_path):
     assert np.array_equal(np.fromfile(str(tmp_path / "c") + ".indptr", dtype=np.int64), indptr)
     assert np.array_equal(np.fromfile(str(tmp_path / "c") + ".indices", dtype=np.int32), indices)
     assert np.array_equal(np.fromfile(str(tmp_path / "c") + ".values", dtype=np.float32), values)
+
+
+def test_reader_under_sanitizers(rg, tmp_path):
+    """The host reader (bgzf inflate, in-place line split, index, parallel ingest, CSR cache, dense views) built with
+    AddressSanitizer + UBSan: any finding aborts the tool and fails the call."""
+    if subprocess.run(["make", "-C", HOST, "bin/mmv_reader_tool_asan"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL).returncode != 0:
+        pytest.skip("no sanitizer runtime for the host compiler on this machine")
+    asan = os.path.join(HOST, "bin", "mmv_reader_tool_asan")
+    env = dict(os.environ, ASAN_OPTIONS="detect_leaks=0", UBSAN_OPTIONS="halt_on_error=1")
+
+    def go(*args, **extra):
+        return subprocess.run([asan, *map(str, args)], check=True, env=dict(env, **extra), stdout=subprocess.PIPE,
+                              stderr=subprocess.PIPE, text=True).stdout
+    for tag in ("a", "b"):
+        gz = os.path.join(GOLDEN, FILES[tag])
+        idx = tmp_path / f"{tag}.index"
+        go("table", gz, idx)
+        go("block", gz, 0, 0)
+        for th in ("1", "5"):
+            go("csr", gz, idx, tmp_path / f"c{tag}{th}", MMV_INGEST_THREADS=th)
+        go("csr", gz, idx, tmp_path / "cc", "cache")
+        assert go("csr", gz, idx, tmp_path / "cc", "cache").split("\n")[1] == "cache"
+        n = int(rg[f"{tag}__header"][1])
+        go("dense", gz, idx, tmp_path / "d.bin", 0, n - 1, n // 2, 0)
+    go("floats", "1.5e1", "-3.25", "7", "1e-3", "00012.5000", ".5", "abc")
+    go("ones", 37, tmp_path / "ones.mtx.gz")
