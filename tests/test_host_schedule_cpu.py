@@ -126,3 +126,27 @@ def test_covariate_file_reaches_the_abi(stub, tmp_path):
     mdl = [c[1] for c in calls if c[0] == "nb_model"][0]
     assert (up["covar"], up["c_dim"], mdl["c"]) == ("1", str(C), str(C))
     assert os.path.exists(str(cov) + ".index")                      # built on demand like the data index
+
+
+def test_mains_under_sanitizers(stub, tmp_path):
+    """train_vae_model, the option parsers, the covariate loader and the recorders' gz writers built with
+    AddressSanitizer + UBSan and run against the test double: any finding aborts the program."""
+    exe = {}
+    for prog in ("nb_vae", "vmf_vae"):
+        exe[prog] = str(tmp_path / (prog + "_asan"))
+        cmd = ["/usr/bin/g++", "-O1", "-g", "-std=c++17", "-fsanitize=address,undefined", "-fno-omit-frame-pointer", "-pthread",
+               "-I" + os.path.join(HOST, "include"), os.path.join(HOST, "src", prog + "_main.cc"), "-o", exe[prog],
+               "-L" + str(stub), "-lmmvae_b200", "-lz"]
+        if subprocess.run(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL).returncode != 0:
+            pytest.skip("no sanitizer runtime for the host compiler on this machine")
+    env = dict(os.environ, LD_LIBRARY_PATH=str(stub), MMV_STUB_LOG=str(tmp_path / "log"), ASAN_OPTIONS="detect_leaks=0",
+               UBSAN_OPTIONS="halt_on_error=1")
+    mtx = os.path.join(GOLDEN, "reader_b.mtx.gz")
+    for prog, extra in (("nb_vae", ["--mean_encoding", "16,8", "--mean_decoding", "8", "--mean_latent", "3", "--csr_cache"]),
+                        ("nb_vae", ["--mean_latent", "3", "--csr_cache"]),
+                        ("vmf_vae", ["--latent", "4", "--vmf_latent"])):
+        p = subprocess.run([exe[prog], "--mtx", mtx, "--idx", str(tmp_path / "b.index"), "--out", str(tmp_path / "o"), "--batch_size",
+                            "96", "--max_epoch", "3", "--recording", "1", "--nboot", "2", *extra],
+                           env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
+        assert p.returncode == 0, p.stderr[-3000:]
+    assert "binary CSR cache" in p.stderr or os.path.exists(str(tmp_path / "b.index") + ".csr")
