@@ -278,3 +278,17 @@ def test_reader_under_sanitizers(rg, tmp_path):
         go("dense", gz, idx, tmp_path / "d.bin", 0, n - 1, n // 2, 0)
     go("floats", "1.5e1", "-3.25", "7", "1e-3", "00012.5000", ".5", "abc")
     go("ones", 37, tmp_path / "ones.mtx.gz")
+
+
+def test_parallel_ingest_under_thread_sanitizer(tmp_path):
+    """The multi-threaded one-off ingest (ranges parsed by separate readers, parallel tidy / CSR assembly) under TSan."""
+    if subprocess.run(["make", "-C", HOST, "bin/mmv_reader_tool_tsan"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL).returncode != 0:
+        pytest.skip("no TSan runtime for the host compiler on this machine")
+    tsan = os.path.join(HOST, "bin", "mmv_reader_tool_tsan")
+    gz = os.path.join(GOLDEN, FILES["b"])
+    env = dict(os.environ, MMV_INGEST_THREADS="6", TSAN_OPTIONS="halt_on_error=1 exitcode=66")
+    subprocess.run([tsan, "table", gz, str(tmp_path / "b.index")], check=True, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    p = subprocess.run([tsan, "csr", gz, str(tmp_path / "b.index"), str(tmp_path / "c")], env=env, stdout=subprocess.PIPE,
+                       stderr=subprocess.PIPE, text=True)
+    assert p.returncode == 0 and "ThreadSanitizer" not in p.stderr, p.stderr[-2000:]
+    assert "6 reader threads" in p.stderr or "reader threads" in p.stderr
