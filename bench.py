@@ -35,8 +35,42 @@ WORKLOAD = dict(model="nb", cells=1_000_000, genes=30_000, density=0.05, batch=4
                 enc=[1024, 256], dec=[256, 1024], latent=32, nu_h=1, nu_r=1, c_dim=1)
 
 
+# BASELINE.json configs (shapes: SURVEY.md section 8 table).  cfg 4 is the default / headline workload.
+CONFIGS = {
+    1: dict(model="nb", cells=10_000, genes=2_000, batch=1024, enc=[128], dec=[128], latent=10, dtype="f32"),
+    2: dict(model="vmf", cells=10_000, genes=2_000, batch=1024, enc=[128], dec=[128], latent=10, dtype="f32"),
+    3: dict(model="nb", cells=200_000, genes=20_000, batch=4096, enc=[1024, 256], dec=[256, 1024], latent=32, dtype="bf16"),
+    4: dict(model="nb", cells=1_000_000, genes=30_000, batch=4096, enc=[1024, 256], dec=[256, 1024], latent=32, dtype="bf16"),
+    5: dict(model="vmf", cells=1_000_000, genes=30_000, batch=4096, enc=[2048, 512], dec=[512, 2048], latent=128, dtype="bf16"),
+}
+
+
+def apply_config(args):
+    """--config N fills in every shape option that was not given explicitly."""
+    args.cfg_name = "SURVEY cfg 4"
+    if args.config is None:
+        return args
+    c = CONFIGS[args.config]
+    args.cfg_name = f"SURVEY cfg {args.config}"
+    args.model = c["model"]
+    if args.cells == WORKLOAD["cells"]:
+        args.cells = c["cells"]
+    if args.genes == WORKLOAD["genes"]:
+        args.genes = c["genes"]
+    if args.batch == WORKLOAD["batch"]:
+        args.batch = c["batch"]
+    args.enc = args.enc or ",".join(map(str, c["enc"]))
+    args.dec = args.dec or ",".join(map(str, c["dec"]))
+    args.latent = args.latent or c["latent"]
+    if args.dtype is None:
+        args.dtype = c["dtype"]
+    return args
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--config", type=int, default=None, choices=sorted(CONFIGS),
+                    help="BASELINE.json config preset (model, N x D, batch, layer widths, dtype); default = cfg 4")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
@@ -48,7 +82,7 @@ def parse_args():
     ap.add_argument("--enc", default=None, help="encoder widths, comma separated (default: SURVEY cfg 4)")
     ap.add_argument("--dec", default=None, help="decoder widths, comma separated")
     ap.add_argument("--latent", type=int, default=None)
-    ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"],
+    ap.add_argument("--dtype", default=None, choices=["bf16", "f32"],
                     help="GEMM operand type: bf16 = tcgen05 tensor cores (fp32 accumulate), f32 = FFMA parity mode")
     ap.add_argument("--vmf-latent", action="store_true",
                     help="vmf model with the true von Mises-Fisher latent (not in the reference; DESIGN K8)")
@@ -57,7 +91,12 @@ def parse_args():
                     help="e2e loop: issue the next minibatch's upload before (update) or after (step) the step call")
     ap.add_argument("--e2e-sync", action="store_true", help="e2e loop waits for each step's loss terms before issuing the next step")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the CPU baseline sample")
-    return ap.parse_args()
+    ap.add_argument("--cpu-batch", type=int, default=1024, help="cells per step of the CPU reference arm (BASELINE.md section 3)")
+    ap.add_argument("--no-dp-check", action="store_true", help="N > 1: skip the gradient / replica check after the timed regions")
+    args = apply_config(ap.parse_args())
+    if args.dtype is None:
+        args.dtype = "bf16"
+    return args
 
 
 def peaks():
@@ -230,31 +269,24 @@ def _port_step_time(w, model, B, steps, warmup, threads):
     return {"ms_per_step": 1e3 * sec / steps, "cells_per_s": B * steps / sec, "threads": threads}
 
 
-def cpu_reference_run(w, model, steps=None, warmup=1, budget_s=20.0, B=256):
+def cpu_reference_run(w, model, steps=None, warmup=1, budget_s=20.0, B=1024):
     """Times the reference's CPU implementation of the step on a bounded sample of the workload
-    (B cells per step, full D and layer widths).  Returns the cpu_baseline object."""
+    (B cells per step, full D and layer widths) with ALL host cores (at::set_num_threads(nproc), BASELINE.md
+    section 3; a fixed, stated thread count: the denominator of a GPU / CPU ratio must not depend on a probe).
+    Returns the cpu_baseline object."""
     ncpu = os.cpu_count() or 1
     have_ref = os.path.exists(HARNESS)
     run = (lambda th, st, wu: _run_harness(w, model, B, st, wu, th)) if have_ref else \
           (lambda th, st, wu: _port_step_time(w, model, B, st, wu, th))
-    cands = sorted({1, min(8, ncpu), max(1, ncpu // 2), ncpu}, reverse=True)
-    best, best_th = None, 1
-    for th in cands:                      # pick the thread count the host actually scales to
-        try:
-            r = run(th, 1, 1)
-        except Exception:
-            continue
-        if best is None or r["ms_per_step"] < best:
-            best, best_th = r["ms_per_step"], th
-    if best is None:
-        raise RuntimeError("CPU reference could not run")
+    threads = ncpu
     if steps is None:
-        steps = int(max(3, min(50, budget_s * 1e3 / best)))
-    r = run(best_th, steps, warmup)
-    return {"value": r["cells_per_s"], "unit": "cells/s", "cores": best_th, "host_cpus": ncpu,
-            "kind": "reference" if have_ref else "port", "ms_per_step": r["ms_per_step"],
+        probe = run(threads, 1, 1)["ms_per_step"]
+        steps = int(max(3, min(50, budget_s * 1e3 / probe)))
+    r = run(threads, steps, warmup)
+    return {"value": r["cells_per_s"], "unit": "cells/s", "cores": threads, "host_cpus": ncpu,
+            "kind": "reference" if have_ref else "port", "ms_per_step": r["ms_per_step"], "batch": B,
             "sample": f"{steps} timed steps (+{warmup} warm-up) of {B} cells x {w['genes']} genes, same layers, "
-                      f"dense fp32 libtorch CPU step (fwd+loss+bwd+clip+Adam), reader excluded"}
+                      f"dense fp32 libtorch CPU step (fwd+loss+bwd+clip+Adam) on {threads} threads, reader excluded"}
 
 
 READER_REF = os.path.join(ROOT, "oracle", "_ref", "ref_reader_harness")
@@ -357,6 +389,110 @@ def kernel_work(w, B, bf16=True, n_gpus=1):
         # their producing kernels (1 GPU), so the separate sumsq pass only reads the small tensors
         "clip_adam": ("hbm", (30.0 if n_gpus == 1 else 34.0) * D * (h1 + dl)),
     }
+
+
+def k1_contract_bytes(w, B, bf16=True):
+    """SURVEY 8d's CONTRACT figures for K1 (compulsory HBM bytes of the sparse formulation).  In tensor-core mode the
+    first layer runs as a densify-in-smem tcgen05 GEMM judged on dense-equivalent flops (kernel_work); these byte
+    figures are printed beside it as `frac_hbm_contract` so that the credit taken for multiplying the zeros is visible."""
+    D, h1, H = w["genes"], w["enc"][0], w["nu_h"]
+    nnz = w["density"] * D * B
+    e = 2.0 if bf16 else 4.0
+    return {"senc_fwd": 8 * nnz + 8 * (B + 1) + e * D * h1 + 4.0 * D * (2 + H + 1) + 4.0 * B * (h1 + H + 1),
+            "senc_bwd": 8 * nnz + 4.0 * B * (h1 + H + 1) + 4.0 * D * h1 + e * D * h1 + 16.0 * D}
+
+
+def src_sha(*names):
+    """sha1 over kernel source files: profiles/traffic.json entries carry the hash of the source they were captured on,
+    and a stale entry (the kernel changed since the ncu capture) is dropped instead of being reported."""
+    import hashlib
+    h = hashlib.sha1()
+    for n in names:
+        with open(os.path.join(ROOT, "mm-vae_b200", "csrc", n), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+KERNEL_SOURCES = {"nb_likelihood": ("nb_likelihood_fast.cu",), "vmf_likelihood": ("vmf_likelihood_fast.cu",),
+                  "senc_fwd": ("senc_tc.cu",), "senc_bwd": ("senc_tc.cu",), "panel_build": ("senc_tc.cu",),
+                  "gemm_dec_last_fwd": ("gemm_tc.cu",), "gemm_dec_last_dx": ("gemm_tc.cu",), "gemm_dec_last_dw": ("gemm_tc.cu",),
+                  "clip_adam": ("optim.cu",)}
+
+
+def measured_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture, or None when
+    there is none for the CURRENT source of that kernel (scripts/ncu_traffic.sh refreshes the file)."""
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(tpath) or kernel not in KERNEL_SOURCES:
+        return None, "no capture"
+    ent = json.load(open(tpath)).get(kernel)
+    if not isinstance(ent, dict):
+        return None, "no capture"
+    if ent.get("src_sha") != src_sha(*KERNEL_SOURCES[kernel]):
+        return None, f"stale: captured on {ent.get('commit', '?')}, kernel source changed since"
+    return ent.get("dram_bytes"), f"ncu --set full, {ent.get('capture', '?')} ({ent.get('commit', '?')})"
+
+
+def run_dp_check(mmv, model, ctx, csr, w, args, indptr, indices, values, rank, world, local, dev, B_chk=512):
+    """Outside every timed region, N > 1 only: the data-parallel step of THIS run (same model object, same communicator,
+    same kernels and bucket schedule as the timed loop) against a single-GPU step on the concatenated global batch.
+    One fixed-seed minibatch of B_chk cells per rank with injected eps: every rank steps its own rows through the N-rank
+    path; rank 0 gathers all ranks' rows and steps them on its own un-communicated context from the same parameters.
+    Reports the worst relative gradient error over all tensors and whether the replicas' parameters are bit-identical
+    after the step (sha1 of every tensor on every rank)."""
+    import hashlib
+    import torch
+    import torch.distributed as dist
+    D, R = w["genes"], w["latent"]
+    n_eps = [R] + ([w["nu_r"]] if w["model"] == "nb" else [])
+    names = list(model.param_info())
+    P0 = {k: model.get_param(k) for k in names} if rank == 0 else None
+    # this rank's rows: the first B_chk cells of its shard, as host CSR
+    ip = indptr[:B_chk + 1].cpu().numpy()
+    nn = int(ip[-1])
+    ix, vv = indices[:nn].cpu().numpy(), values[:nn].cpu().numpy()
+    parts = [None] * world if rank == 0 else None
+    dist.gather_object((ip, ix, vv), parts, dst=0)
+    erng = np.random.default_rng(4242)
+    eps_all = [erng.standard_normal((world * B_chk, n)).astype(np.float32) for n in n_eps]
+    ref = None
+    if rank == 0:
+        ctx1 = mmv.Context(local)
+        gip = np.concatenate([[0]] + [p[0][1:] + off for p, off in zip(parts, np.cumsum([0] + [int(p[0][-1]) for p in parts[:-1]]))]).astype(np.int64)
+        csr1 = mmv.CSR.upload(ctx1, gip, np.concatenate([p[1] for p in parts]), np.concatenate([p[2] for p in parts]), D)
+        if w["model"] == "nb":
+            m1 = mmv.Model.nb(ctx1, D, 1, w["enc"], w["dec"], w["latent"], w["nu_h"], w["nu_r"], seed=7)
+        else:
+            m1 = mmv.Model.vmf(ctx1, D, 1, w["latent"], w["enc"], w["dec"], seed=7)
+        m1.set_option("dtype", 1 if args.dtype == "bf16" else 0)
+        m1.set_option("train_all_layers", 1)
+        m1.set_params(P0)
+        t1 = m1.step(csr1, np.arange(world * B_chk), eps=eps_all, kl_weight=1.0, flags=mmv.FWD | mmv.BWD | mmv.OPTIM)
+        ref = (t1, {k: m1.get_grad(k) for k in names})
+        m1.close(); csr1.close(); ctx1.close()
+    lo = rank * B_chk
+    t = model.step(csr, np.arange(B_chk), eps=[e[lo:lo + B_chk] for e in eps_all], kl_weight=1.0,
+                   flags=mmv.FWD | mmv.BWD | mmv.OPTIM)
+    h = hashlib.sha1()
+    for k in names:
+        h.update(model.get_param(k).tobytes())
+    digests = [None] * world
+    dist.all_gather_object(digests, h.hexdigest())
+    if rank != 0:
+        return None
+    worst, wk = 0.0, ""
+    for k in names:
+        a, b = model.get_grad(k).astype(np.float64), ref[1][k].astype(np.float64)
+        if np.linalg.norm(b) < 1e-12:
+            continue
+        e = float(np.linalg.norm(a - b) / np.linalg.norm(b))
+        if e > worst:
+            worst, wk = e, k
+    return {"replicas_identical": len(set(digests)) == 1, "worst_grad_rel_err": float(f"{worst:.3e}"), "worst_tensor": wk,
+            "loss_rel_err": float(f"{abs(t['loss'] - ref[0]['loss']) / abs(ref[0]['loss']):.3e}"),
+            "grad_norm": [t["grad_norm"], ref[0]["grad_norm"]], "cells_per_gpu": B_chk, "tensors": len(names),
+            "what": f"{world}-rank step (this run's communicator) vs 1-GPU step on the concatenated {world * B_chk}-cell batch, "
+                    f"{args.dtype} mode, injected eps"}
 
 
 def run_own(args):
@@ -548,6 +684,9 @@ def run_own(args):
         t = torch.tensor([ms, ms_e2e], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, ms_e2e = float(t[0]), float(t[1])
+    dp_check = None
+    if world > 1 and not args.no_dp_check:
+        dp_check = run_dp_check(mmv, model, ctx, csr, w, args, indptr, indices, values, rank, world, local, dev)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -555,6 +694,7 @@ def run_own(args):
 
     pk = peaks()
     work = kernel_work(w, B, args.dtype == "bf16", world)
+    k1c = k1_contract_bytes(w, B, args.dtype == "bf16")
     kernels = {}
     for name, (t, c) in prof.items():
         per = t / c
@@ -567,15 +707,16 @@ def run_own(args):
             else:
                 ent.update(bound="tensor", achieved=round(amount / (per * 1e-3) / 1e12, 2), unit="TFLOP/s")
                 ent["frac"] = round(ent["achieved"] / pk["tc_sustained"], 4)
+        if name in k1c and args.dtype == "bf16":   # K1: the dense-equivalent tensor figure AND SURVEY 8d's contract bytes
+            ent["basis"] = "dense-equivalent flops 2 B D h1 (the densified zeros are multiplied too)"
+            ent["hbm_contract_bytes"] = k1c[name]
+            ent["frac_hbm_contract"] = round(k1c[name] / (per * 1e-3) / 1e9 / pk["hbm"], 4)
         kernels[name] = ent
     dom = max((n for n in kernels if "frac" in kernels[n]), key=lambda n: kernels[n]["share"])
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get(dom)
+    traffic, traffic_src = measured_traffic(dom)
     roof = {"kernel": dom, "bound": kernels[dom]["bound"], "achieved": kernels[dom]["achieved"],
             "peak": pk["hbm"] if kernels[dom]["bound"] == "hbm" else pk["tc_sustained"],
-            "unit": kernels[dom]["unit"], "frac": kernels[dom]["frac"], "traffic": traffic,
+            "unit": kernels[dom]["unit"], "frac": kernels[dom]["frac"], "traffic": traffic, "traffic_source": traffic_src,
             "peak_source": pk["src"] + (", sustained bf16 figure (kernel timed inside a long step)"
                                         if kernels[dom]["bound"] == "tensor" else "")}
     out = {
@@ -585,7 +726,7 @@ def run_own(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": f"{w['model']}_vae {w['cells']} cells x {D} genes, {w['density']:.0%} density "
-                               f"(SURVEY cfg 4), cells sharded over {world} GPU(s), {n_local} resident per GPU",
+                               f"({args.cfg_name}), cells sharded over {world} GPU(s), {n_local} resident per GPU",
                    "batch_per_gpu": B, "global_batch": B * world, "encoder": w["enc"], "decoder": w["dec"],
                    "latent": w["latent"], "train_all_layers": True, "nnz_resident_per_gpu": nnz,
                    "l2_policy": "inputs larger than L2 (new cells every step; B x D activations = "
@@ -598,9 +739,11 @@ def run_own(args):
                       "ms_per_minibatch": round(ms_sched / n_sched, 4)},
         "last_loss": last["loss"] if last else None,
     }
+    if dp_check is not None:
+        out["dp_check"] = dp_check
     if not args.no_cpu_baseline and world == 1:
         try:
-            out["cpu_baseline"] = cpu_reference_run(w, w["model"], budget_s=args.cpu_seconds)
+            out["cpu_baseline"] = cpu_reference_run(w, w["model"], budget_s=args.cpu_seconds, B=args.cpu_batch)
         except Exception as e:   # the baseline is reported, never required
             out["cpu_baseline"] = {"value": None, "error": str(e)[:200]}
         try:
@@ -623,7 +766,7 @@ def run_reference(args):
         w["dec"] = [int(v) for v in args.dec.split(",")]
     if args.latent:
         w["latent"] = args.latent
-    cb = cpu_reference_run(w, w["model"], steps=args.steps, warmup=args.warmup)
+    cb = cpu_reference_run(w, w["model"], steps=args.steps, warmup=args.warmup, B=args.cpu_batch)
     out = {"impl": "reference",
            "metric": "train cells/sec (NB-VAE ELBO fwd+bwd, 1M x 30k sparse)", "value": round(cb["value"], 2),
            "unit": "cells/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,

@@ -36,6 +36,9 @@ typedef struct mmv_model mmv_model;
 
 /* ---- device context ------------------------------------------------------
  * replaces: training_options_t::device + model->to(device), mmvae_alg.hh:17,237 */
+/* Number of CUDA devices this process can see (the multi-GPU mains shard the cells over them; the reference is
+ * single device: training_options_t::device, mmvae_alg.hh:16-17). */
+MMV_API int mmv_device_count(int *out);
 MMV_API int mmv_ctx_create(int device, mmv_ctx **out);
 MMV_API int mmv_ctx_destroy(mmv_ctx *ctx);
 MMV_API int mmv_ctx_sync(mmv_ctx *ctx);
@@ -193,8 +196,9 @@ MMV_API int mmv_test_gemm(mmv_ctx *ctx, int use_tc, int M, int N, int K, int a_m
                   const float *B, const float *bias, float beta, int relu, float *C);
 
 /* ---- data-parallel gradient exchange (no reference counterpart) ----
- * One process per GPU.  Rank 0 creates the id, the host program broadcasts the
- * 128 bytes, every rank calls mmv_comm_init.  After it, mmv_step sum-reduces the
+ * One rank per GPU: separate processes (bench.py under torchrun) or the host threads of one process
+ * (nb_vae / vmf_vae --ngpu G), each with its own mmv_ctx.  Rank 0 creates the id, the host program hands
+ * the 128 bytes to every rank, every rank calls mmv_comm_init (concurrently: the call is collective).  After it, mmv_step sum-reduces the
  * flat gradient buffer (and the loss terms) over ranks with ncclAllReduce before
  * clip + Adam; each rank must scale by its share (the step divides by the GLOBAL
  * batch = B * nranks). */

@@ -59,6 +59,7 @@ class LossTerms(C.Structure):
 
 _vp, _i64, _f32p = C.c_void_p, C.c_int64, C.POINTER(C.c_float)
 _PROTOS = {
+    "mmv_device_count": [C.POINTER(C.c_int)],
     "mmv_ctx_create": [C.c_int, C.POINTER(_vp)],
     "mmv_ctx_destroy": [_vp],
     "mmv_ctx_sync": [_vp],
@@ -163,6 +164,12 @@ def test_gemm(ctx, A, B, a_mn=False, b_mn=False, bias=None, beta=0.0, relu=False
     _chk(lib.mmv_test_gemm(ctx.h, int(use_tc), M, N, K, int(a_mn), int(b_mn), _ptr(A), _ptr(B), _ptr(bias),
                            float(beta), int(relu), _ptr(out)))
     return out
+
+
+def device_count() -> int:
+    n = C.c_int()
+    _chk(lib.mmv_device_count(C.byref(n)))
+    return int(n.value)
 
 
 def launch_count() -> int:

@@ -9,6 +9,7 @@
 #include "internal.hh"
 
 #include <dlfcn.h>
+#include <mutex>
 
 namespace {
 
@@ -38,9 +39,12 @@ struct nccl_api_t {
 
 nccl_api_t g_nccl;
 
+std::mutex g_nccl_mu;   // the ranks of a one-process / multi-thread host initialise concurrently
+
 int
 load_nccl()
 {
+    std::lock_guard<std::mutex> lk(g_nccl_mu);
     if (g_nccl.lib) return 0;
     const char *names[] = { "libnccl.so.2", "libnccl.so" };
     void *lib = nullptr;

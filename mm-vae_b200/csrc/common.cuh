@@ -20,6 +20,10 @@ void set_error(const char *fmt, ...);
 void count_launch();          // one call per kernel launch (mmv_launch_count)
 long long launch_count();
 const char *get_error();
+// per-DEVICE launch state (function attributes and the SM count belong to a device, not to the process: one
+// process may hold a context per GPU, mmv_ctx_create(device)).  Both act on the CURRENT device.
+int dev_num_sms(int *out);                          // SM count, cached per ordinal
+int dev_set_smem(const void *func, int bytes);      // MaxDynamicSharedMemorySize once per (device, kernel)
 
 #define MMV_CUDA(expr)                                                           \
     do {                                                                         \

@@ -3,7 +3,10 @@
 #include "common.cuh"
 #include "internal.hh"
 
+#include <atomic>
 #include <cstdarg>
+#include <map>
+#include <mutex>
 #include <vector>
 
 namespace mmv {
@@ -25,18 +28,52 @@ get_error()
     return g_err;
 }
 
-static long long g_launches = 0;
+static std::atomic<long long> g_launches{0};   // host threads of a multi-GPU process launch concurrently
 
 void
 count_launch()
 {
-    ++g_launches;
+    g_launches.fetch_add(1, std::memory_order_relaxed);
 }
 
 long long
 launch_count()
 {
-    return g_launches;
+    return g_launches.load(std::memory_order_relaxed);
+}
+
+static std::mutex g_dev_mu;
+static std::map<int, int> g_dev_sms;
+static std::map<std::pair<int, const void *>, int> g_dev_smem;
+
+int
+dev_num_sms(int *out)
+{
+    int dev = 0;
+    MMV_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_dev_mu);
+    auto it = g_dev_sms.find(dev);
+    if (it == g_dev_sms.end()) {
+        int n = 0;
+        MMV_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+        it = g_dev_sms.emplace(dev, n).first;
+    }
+    *out = it->second;
+    return 0;
+}
+
+int
+dev_set_smem(const void *func, int bytes)
+{
+    int dev = 0;
+    MMV_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_dev_mu);
+    int &have = g_dev_smem[std::make_pair(dev, func)];
+    if (have < bytes) {
+        MMV_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        have = bytes;
+    }
+    return 0;
 }
 
 } // namespace mmv
@@ -49,6 +86,17 @@ const char *
 mmv_last_error(void)
 {
     return get_error();
+}
+
+int
+mmv_device_count(int *out)
+{
+    MMV_CHECK(out != nullptr, "mmv_device_count: out is NULL");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    MMV_CHECK(e == cudaSuccess, "mmv_device_count: %s", cudaGetErrorString(e));
+    *out = ndev;
+    return 0;
 }
 
 int
@@ -153,17 +201,28 @@ mmv_host_free(void *p)
 }
 
 // ------------------------------------------------------------------ CSR
-// One warp per cell: raises *flag when gene ids are not strictly increasing inside a cell.
-// The K4/K5 kernels bisect a cell's nonzeros by gene slice when the flag stays 0.
+// One warp per cell.  flag[0] is raised when gene ids are not strictly increasing inside a cell (the K4/K5
+// kernels bisect a cell's nonzeros by gene slice when it stays 0); flag[1] when a gene id lies outside
+// [0, n_genes) — K1/K4/K5 index weight rows, shared-memory slices and column sums with it.  With `sanitize`
+// (arrays owned by the library: the streamed-minibatch slot) such an entry is neutralised in place (gene 0,
+// value 0: it contributes nothing) so no kernel can go out of bounds; the flag still fails the step.
 __global__ void
-csr_check_sorted_kernel(const int64_t *indptr, const int32_t *indices, int64_t n_cells, int *flag)
+csr_check_sorted_kernel(const int64_t *indptr, int32_t *indices, float *vals, int64_t n_cells, int32_t n_genes, int sanitize,
+                        int *flag)
 {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarp = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    bool bad = false;
+    bool bad = false, oob = false;
     for (int64_t i = warp; i < n_cells; i += nwarp) {
         const int64_t b = indptr[i], e = indptr[i + 1];
+        if (lane == 0 && e > b) {                          // the row's first entry has no predecessor
+            const int j = indices[b];
+            if (j < 0 || j >= n_genes) {
+                oob = true;
+                if (sanitize) { indices[b] = 0; vals[b] = 0.f; }
+            }
+        }
         for (int64_t q0 = b + 1; q0 < e; q0 += 32 * 8) {   // 8 independent loads in flight per lane
             int cur[8], prev[8];
 #pragma unroll
@@ -173,21 +232,30 @@ csr_check_sorted_kernel(const int64_t *indptr, const int32_t *indices, int64_t n
                 prev[u] = q < e ? indices[q - 1] : -1;
             }
 #pragma unroll
-            for (int u = 0; u < 8; ++u) bad |= cur[u] <= prev[u];
+            for (int u = 0; u < 8; ++u) {
+                const int64_t q = q0 + lane + 32 * u;
+                bad |= cur[u] <= prev[u];
+                if (q < e && (cur[u] < 0 || cur[u] >= n_genes)) {
+                    oob = true;
+                    if (sanitize) { indices[q] = 0; vals[q] = 0.f; }
+                }
+            }
         }
     }
-    if (__any_sync(0xffffffffu, bad) && lane == 0) *flag = 1;
+    if (__any_sync(0xffffffffu, bad) && lane == 0) flag[0] = 1;
+    if (__any_sync(0xffffffffu, oob) && lane == 0) { flag[0] = 1; flag[1] = 1; }   // (a neutralised row is no longer sorted)
 }
 
 static int
 csr_check_sorted(mmv_csr *s, cudaStream_t st)
 {
-    if (!s->d_unsorted) MMV_CUDA(cudaMalloc(&s->d_unsorted, sizeof(int)));
-    MMV_CUDA(cudaMemsetAsync(s->d_unsorted, 0, sizeof(int), st));
+    if (!s->d_unsorted) MMV_CUDA(cudaMalloc(&s->d_unsorted, 2 * sizeof(int)));
+    MMV_CUDA(cudaMemsetAsync(s->d_unsorted, 0, 2 * sizeof(int), st));
     if (s->nnz == 0) return 0;
     const int64_t want = (s->n_cells * 32 + 255) / 256;
     const int grid = (int)(want < 1 ? 1 : (want > 148 * 16 ? 148 * 16 : want));
-    csr_check_sorted_kernel<<<grid, 256, 0, st>>>(s->indptr, s->indices, s->n_cells, s->d_unsorted);
+    csr_check_sorted_kernel<<<grid, 256, 0, st>>>(s->indptr, s->indices, s->vals, s->n_cells, (int32_t)s->n_genes,
+                                                 s->borrowed ? 0 : 1, s->d_unsorted);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
@@ -277,8 +345,9 @@ csr_update_impl(mmv_csr *s, int64_t n_cells, const int64_t *indptr, const int32_
     return 0;
 }
 
-// Streaming path: gene ids are range-checked once per resident upload only; a
-// per-minibatch host scan of the nonzeros would cost more than the step itself.
+// Streaming path: no per-minibatch host scan of the nonzeros (it would cost more than the step itself) — the
+// device-side check that already reads every gene id for the sortedness flag also range-checks them,
+// neutralises offenders in the slot and raises a flag that fails the step which consumes the slot.
 int
 mmv_csr_update(mmv_csr *s, int64_t n_cells, const int64_t *indptr, const int32_t *indices, const float *values,
                const float *covar)
@@ -327,7 +396,12 @@ mmv_csr_wrap_device(mmv_ctx *ctx, int64_t n_cells, int64_t n_genes, int64_t nnz,
     s->has_cov = d_covar != nullptr;
     s->c_dim = d_covar ? c_dim : (c_dim > 0 ? c_dim : 1);
     MMV_CUDA(cudaSetDevice(ctx->device));
-    if (csr_check_sorted(s, ctx->stream) != 0) {
+    int flags[2] = { 0, 0 };   // adopted arrays cannot be repaired: a one-off synchronous range check instead
+    if (csr_check_sorted(s, ctx->stream) != 0 ||
+        cudaMemcpyAsync(flags, s->d_unsorted, sizeof(flags), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+        cudaStreamSynchronize(ctx->stream) != cudaSuccess || flags[1] != 0) {
+        if (flags[1]) set_error("csr: gene index out of range [0,%ld) in the adopted device arrays", (long)n_genes);
+        cudaFree(s->d_unsorted);
         delete s;
         return 1;
     }

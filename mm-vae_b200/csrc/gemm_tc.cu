@@ -25,6 +25,7 @@
 #include <cuda_bf16.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstdlib>
 
 namespace mmv {
@@ -436,14 +437,14 @@ typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32
 encode_tiled_fn
 get_encode()
 {
-    static encode_tiled_fn fn = nullptr;
-    if (!fn) {
+    static const encode_tiled_fn fn = [] {   // thread-safe one-time lookup
         void *p = nullptr;
         cudaDriverEntryPointQueryResult q;
         if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
             q == cudaDriverEntryPointSuccess)
-            fn = (encode_tiled_fn)p;
-    }
+            return (encode_tiled_fn)p;
+        return (encode_tiled_fn) nullptr;
+    }();
     return fn;
 }
 
@@ -530,18 +531,11 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
         p.tma_epi = (g.beta == 1.f || grid.z > 1) ? 2 : 1;
     }
     // many-tile products: persistent 128 x 256 kernel (operand ring never drains, epilogue overlapped)
-    static int num_sms = 0, persist_mode = -1;
-    if (num_sms == 0) {
-        int dev = 0;
-        MMV_CUDA(cudaGetDevice(&dev));
-        MMV_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-        const char *e = getenv("MMV_GEMM_PERSIST");
-        persist_mode = e ? atoi(e) : 1;
-    }
-    static int log_left = -1;   // MMV_GEMM_LOG=<n>: print the first n launches' shapes
-    if (log_left < 0) { const char *e = getenv("MMV_GEMM_LOG"); log_left = e ? atoi(e) : 0; }
-    if (log_left > 0) {
-        --log_left;
+    int num_sms = 0;
+    MMV_TRY(dev_num_sms(&num_sms));
+    static const int persist_mode = [] { const char *e = getenv("MMV_GEMM_PERSIST"); return e ? atoi(e) : 1; }();
+    static std::atomic<int> log_left{ [] { const char *e = getenv("MMV_GEMM_LOG"); return e ? atoi(e) : 0; }() };   // MMV_GEMM_LOG=<n>: print the first n launches' shapes
+    if (log_left.load(std::memory_order_relaxed) > 0 && log_left.fetch_sub(1) > 0) {
         fprintf(stderr, "[gemm_tc] M=%d N=%d K=%d a_mn=%d b_mn=%d lda=%d ldb=%d ldc=%d beta=%g bias=%d relu=%d Cb=%d epi=%d grid=(%u,%u,%u) A=%p B=%p C=%p\n",
                 g.M, g.N, g.K, g.a_mn, g.b_mn, g.lda, g.ldb, g.ldc, g.beta, g.bias != nullptr, g.relu, g.Cb != nullptr, p.tma_epi,
                 grid.x, grid.y, grid.z, g.A, g.B, (void *)g.C);
@@ -556,12 +550,7 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
         void (*pk)(const CUtensorMap, const CUtensorMap, const CUtensorMap, params_t) =
             g.a_mn ? (g.b_mn ? gemm_tc_persist_kernel<true, true> : gemm_tc_persist_kernel<true, false>)
                    : (g.b_mn ? gemm_tc_persist_kernel<false, true> : gemm_tc_persist_kernel<false, false>);
-        static bool pattr[4] = { false, false, false, false };
-        const int pvi = (g.a_mn ? 2 : 0) + (g.b_mn ? 1 : 0);
-        if (!pattr[pvi]) {
-            MMV_CUDA(cudaFuncSetAttribute(pk, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM_BYTES));
-            pattr[pvi] = true;
-        }
+        MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(pk), P_SMEM_BYTES));
         pk<<<std::min(ptiles, num_sms), THREADS, P_SMEM_BYTES, stream>>>(ta, tb, tc_map, p);
         ::mmv::count_launch();
         MMV_CUDA(cudaGetLastError());
@@ -575,13 +564,8 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
     else
         kern = g.a_mn ? (g.b_mn ? gemm_tc_kernel<true, true, 3> : gemm_tc_kernel<true, false, 3>)
                       : (g.b_mn ? gemm_tc_kernel<false, true, 3> : gemm_tc_kernel<false, false, 3>);
-    static bool attr_set[8] = { false, false, false, false, false, false, false, false };
-    const int vi = (deep ? 4 : 0) + (g.a_mn ? 2 : 0) + (g.b_mn ? 1 : 0);
     const int smem = smem_bytes(deep ? 6 : 3);
-    if (!attr_set[vi]) {
-        MMV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr_set[vi] = true;
-    }
+    MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(kern), smem));
     kern<<<grid, THREADS, smem, stream>>>(ta, tb, tc_map, p);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());

@@ -122,6 +122,7 @@ struct mmv_model {
     uint64_t seed = 0;
     bool vmf_latent = false;              // "vmf_latent" option: Wood sampler + Householder + Bessel KL (vmf_latent.cu)
     uint64_t vmf_draw = 0;                // Philox draw counter of the next sampled forward pass
+    uint64_t eps_draw = 0;                // draw counter of the library's own Gaussian noise (MMV_EPS_PHILOX)
     float vmf_kappa_max = 1e4f;
 
     // workspace
@@ -135,6 +136,7 @@ struct mmv_model {
     size_t grad_lazy_n = 0;               //   ... over grads[0, grad_lazy_n)
     double *h_acc = nullptr;              // pinned mirrors
     float *h_fscal = nullptr;
+    int *h_oob = nullptr;                 // pinned: [0..1] sync path, [2..3] / [4..5] the two deferred slots (csr range flag)
     // MMV_TERMS_DEFERRED: two pinned slots; a step's sums are copied asynchronously and handed out by the next call
     struct deferred_t {
         double *acc = nullptr;
@@ -143,6 +145,7 @@ struct mmv_model {
         double n = 1.;
         float klw = 0.f;
         int flags = 0;
+        bool has_oob = false;
     } def[2];
     unsigned def_i = 0;
     int def_pending = -1;
@@ -283,6 +286,8 @@ alloc_and_init(mmv_model *m)
     MMV_CUDA(cudaMalloc(&m->fscal, sizeof(float) * 8));
     MMV_CUDA(cudaMallocHost(&m->h_acc, sizeof(double) * 8));
     MMV_CUDA(cudaMallocHost(&m->h_fscal, sizeof(float) * 8));
+    MMV_CUDA(cudaMallocHost(&m->h_oob, sizeof(int) * 6));
+    std::memset(m->h_oob, 0, sizeof(int) * 6);
 
     // libtorch default init: Linear/Angular weight kaiming_uniform_(a=sqrt 5) = U(+-1/sqrt(fan_in)),
     // bias U(+-1/sqrt(fan_in)) (angular.hh:59-70); model-level vectors as in nb.hh:312-315, vmf.hh:321-323.
@@ -449,7 +454,7 @@ mmv_model_destroy(mmv_model *m)
     cudaFree(m->params); cudaFree(m->adam_m); cudaFree(m->adam_v);
     comm_free_grads(m->ctx, m->grads, m->grads_win, m->grads_nccl);
     cudaFree(m->acc); cudaFree(m->fscal); cudaFree(m->params_bf16);
-    cudaFreeHost(m->h_acc); cudaFreeHost(m->h_fscal);
+    cudaFreeHost(m->h_acc); cudaFreeHost(m->h_fscal); cudaFreeHost(m->h_oob);
     for (auto &d : m->def) {
         if (d.acc) cudaFreeHost(d.acc);
         if (d.fscal) cudaFreeHost(d.fscal);
@@ -1415,9 +1420,11 @@ stage_inputs(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const 
             memcpy(m->h_eps[slot], eps, sizeof(float) * (n_mu + n_nu));
             MMV_CUDA(cudaMemcpyAsync(d_eps, m->h_eps[slot], sizeof(float) * (n_mu + n_nu), cudaMemcpyHostToDevice, st));
         } else {
-            static uint64_t draw = 0;
-            normal_kernel<<<(int)min_sz((n_mu + n_nu + 255) / 256, 1024), 256, 0, st>>>(d_eps, n_mu + n_nu, m->seed + 77,
-                                                                                     ++draw); ::mmv::count_launch();
+            // keyed on (model seed, rank, per-model draw counter, element): data-parallel replicas share the seed and
+            // step in lock-step, so without the rank every shard would see the same B noise vectors
+            const uint64_t key = m->seed + 77 + 0x9E3779B97F4A7C15ull * (uint64_t)m->ctx->rank;
+            normal_kernel<<<(int)min_sz((n_mu + n_nu + 255) / 256, 1024), 256, 0, st>>>(d_eps, n_mu + n_nu, key,
+                                                                                     ++m->eps_draw); ::mmv::count_launch();
             MMV_CUDA(cudaGetLastError());
         }
         s.eps_mu = d_eps;
@@ -1426,6 +1433,9 @@ stage_inputs(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const 
     MMV_CUDA(cudaEventRecord(m->ev_stage[slot], st));
     return 0;
 }
+
+const char *const kOobMsg = "mmv_step: the streamed minibatch holds a gene index outside [0, n_genes) (the entry was "
+                            "neutralised on the device; the step's result is not valid)";
 
 // loss terms from the device sums (nb.hh:542-547 / vmf.hh:439)
 void
@@ -1581,6 +1591,7 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         const int prev = m->def_pending;
         if (prev >= 0) {
             MMV_CUDA(cudaEventSynchronize(m->def[prev].ev));
+            MMV_CHECK(!(m->def[prev].has_oob && m->h_oob[2 + 2 * prev + 1]), "%s", kOobMsg);
             fill_terms(m, m->def[prev].acc, m->def[prev].fscal, m->def[prev].n, m->def[prev].klw, m->def[prev].flags, out);
         } else {
             std::memset(out, 0, sizeof(*out));
@@ -1588,6 +1599,9 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         }
         MMV_CUDA(cudaMemcpyAsync(d.acc, m->acc, sizeof(double) * 8, cudaMemcpyDeviceToHost, st));
         MMV_CUDA(cudaMemcpyAsync(d.fscal, m->fscal, sizeof(float) * 8, cudaMemcpyDeviceToHost, st));
+        d.has_oob = (flags & MMV_FWD) && csr->d_unsorted != nullptr;
+        if (d.has_oob)
+            MMV_CUDA(cudaMemcpyAsync(m->h_oob + 2 + 2 * (&d - m->def), csr->d_unsorted, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
         MMV_CUDA(cudaEventRecord(d.ev, st));
         d.n = n; d.klw = kl_weight; d.flags = flags;
         m->def_pending = (int)(&d - m->def);
@@ -1595,7 +1609,10 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
     }
     MMV_CUDA(cudaMemcpyAsync(m->h_acc, m->acc, sizeof(double) * 8, cudaMemcpyDeviceToHost, st));
     MMV_CUDA(cudaMemcpyAsync(m->h_fscal, m->fscal, sizeof(float) * 8, cudaMemcpyDeviceToHost, st));
+    const bool has_oob = (flags & MMV_FWD) && csr->d_unsorted != nullptr;
+    if (has_oob) MMV_CUDA(cudaMemcpyAsync(m->h_oob, csr->d_unsorted, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
     MMV_CUDA(cudaStreamSynchronize(st));
+    MMV_CHECK(!(has_oob && m->h_oob[1]), "%s", kOobMsg);
     fill_terms(m, m->h_acc, m->h_fscal, n, kl_weight, flags, out);
     return 0;
 }
@@ -1607,6 +1624,10 @@ mmv_step_collect(mmv_model *m, mmv_loss_terms *out)
     MMV_CHECK(m->def_pending >= 0, "mmv_step_collect: no deferred step is pending");
     mmv_model::deferred_t &d = m->def[m->def_pending];
     MMV_CUDA(cudaEventSynchronize(d.ev));
+    if (d.has_oob && m->h_oob[2 + 2 * m->def_pending + 1]) {
+        m->def_pending = -1;
+        MMV_CHECK(false, "%s", kOobMsg);
+    }
     fill_terms(m, d.acc, d.fscal, d.n, d.klw, d.flags, out);
     m->def_pending = -1;
     return 0;
@@ -1652,7 +1673,8 @@ mmv_get_output(mmv_model *m, const char *name, float *host, int64_t n)
     std::string key = name;
     int64_t want = 0;
     const float *src = nullptr;
-    if (m->is_vmf) {
+    if (key == "eps_mu") { key = "eps"; want = B * m->R; }   // the noise of the last sampled step (first B x R floats)
+    else if (m->is_vmf) {
         if (key == "mean") { key = "mu_mean"; want = B * m->R; }
         else if (key == "lnvar") { key = "mu_lnvar"; want = B * m->R; }
         else if (key == "recon") want = B * m->D;

@@ -252,7 +252,7 @@ launch_nb_likelihood(const nb_lik_args_t &a, int num_sms, cudaStream_t stream)
     const size_t smem = nb_smem_bytes(Ds, rmax);
     void (*kern)(nb_lik_args_t, int, int) =
         rmax == 1 ? nb_likelihood_kernel<1> : (rmax == 4 ? nb_likelihood_kernel<4> : nb_likelihood_kernel<8>);
-    MMV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(kern), (int)smem));
     int n_clusters = num_sms / cs;
     if (n_clusters > a.B) n_clusters = a.B;
     if (n_clusters < 1) n_clusters = 1;

@@ -596,7 +596,7 @@ launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stre
     void (*kern)(nb_lik_args_t, int, int) = ept <= 4 ? nb_likelihood_fast_kernel<4>
         : ept <= 8 ? nb_likelihood_fast_kernel<8> : ept <= 12 ? nb_likelihood_fast_kernel<12> : nb_likelihood_fast_kernel<16>;
     const size_t smem = fast_smem_bytes(ept_class(ept));
-    MMV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(kern), (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(num_sms / cs * cs);
     cfg.blockDim = dim3(kT);

@@ -10,6 +10,13 @@
 
 namespace mmv {
 
+// Order-deterministic: every block leaves its partial in a slot, the last block to finish (ticket) adds the slots
+// up in index order.  Data-parallel replicas compute the clip coefficient from this sum: an atomicAdd of the
+// partials in arrival order could differ in the last bit from rank to rank and let the replicas drift apart.
+constexpr int kSumsqMaxBlocks = 148 * 16;
+__device__ float g_sumsq_partial[kSumsqMaxBlocks];
+__device__ unsigned int g_sumsq_ticket = 0;
+
 __global__ void
 sumsq_kernel(const float *g, size_t n, double *out)
 {
@@ -29,16 +36,34 @@ sumsq_kernel(const float *g, size_t n, double *out)
     }
     for (size_t k = n4 * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) s = fmaf(g[k], g[k], s);
     __shared__ float scratch[32];
+    __shared__ bool last;
     float v[1] = { s };
     block_sum<1>(v, scratch);
-    if (threadIdx.x == 0) atomicAdd(out, (double)v[0]);
+    if (threadIdx.x == 0) {
+        g_sumsq_partial[blockIdx.x] = v[0];
+        __threadfence();
+        last = atomicAdd(&g_sumsq_ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    if (threadIdx.x < 32) {
+        double t = 0.;
+        for (unsigned b = threadIdx.x; b < gridDim.x; b += 32) t += (double)__ldcg(&g_sumsq_partial[b]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if (threadIdx.x == 0) {
+            *out += t;              // launches on one stream: the only writer at this point
+            g_sumsq_ticket = 0;
+        }
+    }
 }
 
 int
 launch_sumsq(const float *g, size_t n, double *out, int num_sms, cudaStream_t st)
 {
     if (n == 0) return 0;
-    const int grid = (int)min_sz((n + 1023) / 1024, (size_t)num_sms * 8);
+    const int grid = (int)min_sz(min_sz((n + 1023) / 1024, (size_t)num_sms * 8), (size_t)kSumsqMaxBlocks);
     sumsq_kernel<<<grid, 256, 0, st>>>(g, n, out); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;

@@ -280,11 +280,7 @@ launch_panel_build(const panel_args_t &p, cudaStream_t st)
     const int nKl = (nK + nS - 1) / nS + 1;
     const size_t smem = sizeof(int) * (2 * (size_t)nKl + 2);
     MMV_CHECK(smem <= 200 * 1024, "panel_build: %d genes exceed the shared-memory bucket table", p.D);
-    static bool attr = false;
-    if (!attr) {
-        MMV_CUDA(cudaFuncSetAttribute(panel_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr = true;
-    }
+    MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(panel_build_kernel), 200 * 1024));
     batch_rowptr_kernel<<<1, 1024, 0, st>>>(p);
     ::mmv::count_launch();
     panel_build_kernel<<<dim3(nT, nS), kPanelThreads, smem, st>>>(p, nK, nS);
@@ -595,11 +591,7 @@ launch_tc(const senc_tc_args_t &a, cudaStream_t st)
     CUtensorMap ts = tm;
     if (BWD) MMV_TRY(make_tma_map_f32(&ts, a.S, (uint64_t)a.h1, (uint64_t)a.D, (uint64_t)a.h1, 32, 32));
     auto kern = senc_tc_kernel<BN, BWD>;
-    static bool attr = false;
-    if (!attr) {
-        MMV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, cfg::SMEM));
-        attr = true;
-    }
+    MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(kern), cfg::SMEM));
     dim3 grid(ceil_div(a.h1, BN), BWD ? (a.ntiles > 0 ? a.ntiles : ceil_div(a.D, BM)) : ceil_div(a.B, BM));
     kern<<<grid, TCT, cfg::SMEM, st>>>(tm, ts, a, nT, nK);
     ::mmv::count_launch();

@@ -173,7 +173,7 @@ launch_vmf_likelihood(const vmf_lik_args_t &a, int num_sms, cudaStream_t stream)
         MMV_CHECK(cs < 8, "vmf_likelihood: D=%d does not fit a cluster of 8 CTAs", a.D);
     }
     const size_t smem = vmf_smem_bytes(Ds, a.C);
-    MMV_CUDA(cudaFuncSetAttribute(vmf_likelihood_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(vmf_likelihood_kernel), (int)smem));
     int n_clusters = num_sms / cs;
     if (n_clusters > a.B) n_clusters = a.B;
     if (n_clusters < 1) n_clusters = 1;

@@ -98,6 +98,7 @@ private:
         if (n != 18 || hdr[0] != 0x1f || hdr[1] != 0x8b || hdr[2] != 8 || hdr[3] != 4 || hdr[12] != 'B' || hdr[13] != 'C')
             return -1;
         const int bsize = (int)(hdr[16] | (hdr[17] << 8)) + 1;
+        if (bsize < 26) return -1;                  // 18-byte header + 8-byte trailer: anything shorter is corrupt or foreign
         comp_.resize((size_t)bsize - 18);
         if (std::fread(comp_.data(), 1, comp_.size(), fp_) != comp_.size()) return -1;
         block_.resize(0x10000);
@@ -115,6 +116,11 @@ private:
         zs.avail_out = (uInt)block_.size();
         const int rc = inflate(&zs, Z_FINISH);
         if (rc != Z_STREAM_END) return -1;
+        {   // trailer: CRC32, ISIZE (little endian); ISIZE must be what inflate produced (<= 64 KiB)
+            const unsigned char *tr = (const unsigned char *)comp_.data() + comp_.size() - 8;
+            const uint32_t isize = (uint32_t)tr[4] | ((uint32_t)tr[5] << 8) | ((uint32_t)tr[6] << 16) | ((uint32_t)tr[7] << 24);
+            if (isize > 0x10000u || isize != (uint32_t)zs.total_out) return -1;
+        }
         file_pos_ = addr + bsize;
         os_pos_ = file_pos_;
         if (block_length_ != 0) block_offset_ = 0;   // kept when this read follows a seek

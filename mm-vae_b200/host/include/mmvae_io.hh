@@ -221,15 +221,25 @@ public:
     // Reads the header and the index, then parses the whole file once into CSR.
     // csr_cache (or MMV_CSR_CACHE=1): keep the parsed CSR as ${idx_file}.csr beside the index, so that a later run
     // on the same, unchanged mtx file maps three arrays instead of inflating and parsing the text again.
-    mtx_data_block_t(const std::string &mtx_file, const std::string &idx_file, const Index batch_size, bool csr_cache = false)
+    //
+    // [col_lo, col_hi) (default: everything) makes this block ONE SHARD of the data points: only that range of the
+    // text is inflated and parsed (the index table gives its bgzf virtual offsets) and the CSR holds hi - lo cells
+    // with shard-local ids 0 .. hi - lo - 1.  The multi-GPU mains build one such block per GPU, so neither the
+    // host nor any single device ever holds the whole matrix.  ntot() stays the GLOBAL count.
+    mtx_data_block_t(const std::string &mtx_file, const std::string &idx_file, const Index batch_size, bool csr_cache = false,
+                     Index col_lo = 0, Index col_hi = -1)
         : mtx_file_(mtx_file), idx_file_(idx_file), B_(batch_size)
     {
         mmutil::index::mtx_header_t h;
         ASSERT(mmutil::index::peek_bgzf_header(mtx_file, h) == EXIT_SUCCESS, "failed to read the header of " << mtx_file);
         D_ = h.max_row;   // rows = features, columns = data points (mmvae_io.hh:264-267)
         N_ = h.max_col;
+        lo_ = std::max<Index>(0, col_lo);
+        hi_ = col_hi < 0 ? N_ : std::min<Index>(N_, col_hi);
+        ASSERT(lo_ < hi_, "empty shard [" << col_lo << ", " << col_hi << ") of " << N_ << " data points");
         ASSERT(mmutil::index::read_mmutil_index(idx_file, index_tab_) == EXIT_SUCCESS, "failed to read " << idx_file);
         if (const char *e = std::getenv("MMV_CSR_CACHE")) csr_cache = csr_cache || std::atoi(e) != 0;
+        csr_cache = csr_cache && lo_ == 0 && hi_ == N_;   // the cache file describes the whole matrix
         if (csr_cache && load_cache()) {
             TLOG("Read " << idx_file_ << ".csr: " << D_ << " features x " << N_ << " data points, " << indices.size()
                          << " nonzeros (binary CSR cache of " << mtx_file << ")");
@@ -239,10 +249,13 @@ public:
         if (csr_cache && !save_cache()) WLOG("could not write " << idx_file_ << ".csr");
         TLOG("Read " << mtx_file << ": " << D_ << " features x " << N_ << " data points, " << indices.size()
                      << " nonzeros resident as CSR (" << ingest_threads_ << " reader threads: parse " << parse_seconds_
-                     << " s, merge " << merge_seconds_ << " s)");
+                     << " s, merge " << merge_seconds_ << " s)"
+                     << (nlocal() == N_ ? std::string() : ", shard [" + std::to_string(lo_) + ", " + std::to_string(hi_) + ")"));
     }
 
     Index ntot() const { return N_; }
+    Index nlocal() const { return hi_ - lo_; }     // data points held by this block (= ntot() unless it is a shard)
+    Index shard_lo() const { return lo_; }
     Index size() const { return B_; }
     Index nfeature() const { return D_; }
 
@@ -281,8 +294,8 @@ public:
     {
         mem.assign(subcol.size() * (size_t)D_, 0.f);
         for (size_t j = 0; j < subcol.size(); ++j) {
-            const Index c = subcol[j];
-            if (c < 0 || c >= N_) continue;
+            const Index c = subcol[j] - lo_;
+            if (c < 0 || c >= nlocal()) continue;
             for (int64_t q = indptr[(size_t)c]; q < indptr[(size_t)c + 1]; ++q)
                 mem[j * (size_t)D_ + (size_t)indices[(size_t)q]] = values[(size_t)q];
         }
@@ -291,8 +304,8 @@ public:
     // All data points as a dense [N x D] row-major matrix (covariate files: D = C is small).
     void dense_all(std::vector<float> &mem) const
     {
-        std::vector<Index> all((size_t)N_);
-        for (Index i = 0; i < N_; ++i) all[(size_t)i] = i;
+        std::vector<Index> all((size_t)nlocal());
+        for (Index i = 0; i < nlocal(); ++i) all[(size_t)i] = lo_ + i;
         dense_batch_csr(all, mem);
     }
 
@@ -374,9 +387,16 @@ private:
     // mmvae_io.hh:127-130).  MMV_INGEST_THREADS overrides the thread count (1 = the sequential reader).
     int parse_all()
     {
+        const Index N = N_, D = D_, lo = lo_, hi = hi_, NL = hi_ - lo_;
+        // first valid (non-MISSING_POS) offset at or after a column: where that column's — or, when it has no
+        // entries, the next present column's — text begins
+        auto offset_at = [&](Index c) -> int64_t {
+            while (c < N && c < (Index)index_tab_.size() && (int64_t)index_tab_[(size_t)c] == (int64_t)MISSING_POS) ++c;
+            return (c < N && c < (Index)index_tab_.size()) ? (int64_t)index_tab_[(size_t)c] : 0;
+        };
         // start right after the header line (not at voffset 0: the header itself has three fields)
         int64_t start = 0;
-        {
+        if (lo == 0) {
             bgzf_reader_t fp;
             ERR_RET(!fp.open(mtx_file_), "unable to open " << mtx_file_);
             std::string line, tok[3];
@@ -386,16 +406,25 @@ private:
                 if (split_triplet_line(line, tok) == 3) break;
             }
             start = fp.tell();
+        } else {
+            start = offset_at(lo);
+            if (start == 0) {   // no entries at or after the shard's first column: an all-empty shard
+                indptr.assign((size_t)NL + 1, 0);
+                indices.clear(); values.clear();
+                return EXIT_SUCCESS;
+            }
         }
+        const int64_t stop = hi < N ? offset_at(hi) : 0;   // 0 = read to EOF
         int T = (int)std::thread::hardware_concurrency();
         if (const char *e = std::getenv("MMV_INGEST_THREADS")) T = std::atoi(e);
         T = std::max(1, std::min(T, 64));
         // range boundaries: strictly increasing, valid (non-zero) offsets of evenly spaced columns
         std::vector<int64_t> cut{ start };
         for (int t = 1; t < T; ++t) {
-            Index c = (Index)((int64_t)N_ * t / T);
-            while (c < N_ && (int64_t)index_tab_[(size_t)c] <= cut.back()) ++c;   // skips MISSING_POS = 0 and gap-filled repeats
-            if (c >= N_) break;
+            Index c = lo + (Index)((int64_t)NL * t / T);
+            while (c < hi && (int64_t)index_tab_[(size_t)c] <= cut.back()) ++c;   // skips MISSING_POS = 0 and gap-filled repeats
+            if (c >= hi) break;
+            if (stop != 0 && (int64_t)index_tab_[(size_t)c] >= stop) break;
             cut.push_back((int64_t)index_tab_[(size_t)c]);
         }
         const int R = (int)cut.size();
@@ -403,15 +432,15 @@ private:
         struct trip_t { Index c; int32_t g; float w; };
         std::vector<std::vector<trip_t>> part((size_t)R);
         std::vector<int> rc((size_t)R, EXIT_SUCCESS), bad((size_t)R, 0);
-        const Index D = D_, N = N_;
         auto parse_range = [&](int t) {
             std::vector<trip_t> &out = part[(size_t)t];
             int &b = bad[(size_t)t];
-            rc[(size_t)t] = mmutil::index::visit_bgzf_block(mtx_file_, cut[(size_t)t], t + 1 < R ? cut[(size_t)t + 1] : 0,
-                                                            [&out, &b, D, N](Index r, Index c, float w) {
+            rc[(size_t)t] = mmutil::index::visit_bgzf_block(mtx_file_, cut[(size_t)t], t + 1 < R ? cut[(size_t)t + 1] : stop,
+                                                            [&out, &b, D, N, lo, hi](Index r, Index c, float w) {
                 // the reference does not range-check rows (mmutil_bgzf_util.hh:139 -> out-of-bounds write); we fail
                 if (r < 0 || r >= D || c < 0 || c >= N) { b = 1; return; }
-                out.push_back(trip_t{ c, (int32_t)r, w });
+                if (c < lo || c >= hi) return;                      // a line of a neighbouring shard (block granularity)
+                out.push_back(trip_t{ c - lo, (int32_t)r, w });
             });
         };
         if (R == 1) parse_range(0);
@@ -426,12 +455,12 @@ private:
         }
         const auto t_parsed = std::chrono::steady_clock::now();
         // bucket by data point in file order (counting sort: stable)
-        std::vector<int64_t> cnt((size_t)N_ + 1, 0);
+        std::vector<int64_t> cnt((size_t)NL + 1, 0);
         for (auto &p : part)
             for (auto &e : p) ++cnt[(size_t)e.c + 1];
-        for (Index c = 0; c < N_; ++c) cnt[(size_t)c + 1] += cnt[(size_t)c];
+        for (Index c = 0; c < NL; ++c) cnt[(size_t)c + 1] += cnt[(size_t)c];
         struct ent_t { int32_t g; float w; };
-        std::vector<ent_t> all((size_t)cnt[(size_t)N_]);
+        std::vector<ent_t> all((size_t)cnt[(size_t)NL]);
         {
             std::vector<int64_t> cur(cnt.begin(), cnt.end() - 1);
             for (auto &p : part) {
@@ -440,7 +469,7 @@ private:
             }
         }
         // per data point: sort by gene (stable), duplicates keep the last; column ranges in parallel
-        std::vector<int64_t> kept((size_t)N_ + 1, 0);
+        std::vector<int64_t> kept((size_t)NL + 1, 0);
         auto tidy = [&](Index c0, Index c1) {
             for (Index c = c0; c < c1; ++c) {
                 ent_t *v = all.data() + cnt[(size_t)c];
@@ -455,16 +484,16 @@ private:
             }
         };
         auto for_ranges = [&](const std::function<void(Index, Index)> &f) {
-            if (T == 1 || N_ < 1024) { f(0, N_); return; }
+            if (T == 1 || NL < 1024) { f(0, NL); return; }
             std::vector<std::thread> th;
-            for (int t = 0; t < T; ++t) th.emplace_back(f, (Index)((int64_t)N_ * t / T), (Index)((int64_t)N_ * (t + 1) / T));
+            for (int t = 0; t < T; ++t) th.emplace_back(f, (Index)((int64_t)NL * t / T), (Index)((int64_t)NL * (t + 1) / T));
             for (auto &x : th) x.join();
         };
         for_ranges(tidy);
-        indptr.assign((size_t)N_ + 1, 0);
-        for (Index c = 0; c < N_; ++c) indptr[(size_t)c + 1] = indptr[(size_t)c] + kept[(size_t)c + 1];
-        indices.resize((size_t)indptr[(size_t)N_]);
-        values.resize((size_t)indptr[(size_t)N_]);
+        indptr.assign((size_t)NL + 1, 0);
+        for (Index c = 0; c < NL; ++c) indptr[(size_t)c + 1] = indptr[(size_t)c] + kept[(size_t)c + 1];
+        indices.resize((size_t)indptr[(size_t)NL]);
+        values.resize((size_t)indptr[(size_t)NL]);
         for_ranges([&](Index c0, Index c1) {
             for (Index c = c0; c < c1; ++c) {
                 const ent_t *v = all.data() + cnt[(size_t)c];
@@ -491,7 +520,7 @@ private:
     int ingest_threads_ = 1;
     double parse_seconds_ = 0., merge_seconds_ = 0.;
     std::string mtx_file_, idx_file_;
-    Index B_ = 0, D_ = 0, N_ = 0;
+    Index B_ = 0, D_ = 0, N_ = 0, lo_ = 0, hi_ = 0;
     std::vector<Index> index_tab_;
     std::vector<int64_t> batch_;
 };

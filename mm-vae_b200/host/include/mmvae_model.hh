@@ -11,28 +11,59 @@
 #include "mmvae_io.hh"
 #include "mmvae_options.hh"
 
+#include <condition_variable>
 #include <cstdio>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 #include <zlib.h>
 
 namespace mmvae {
 
-struct device_t {   // one context + the resident data of a run
+// What the host threads of one run share (--ngpu G: one thread per GPU): a reusable barrier, the NCCL unique id,
+// and the recorder's latent tables [N x R], which every rank fills for the data points of its own shard.
+struct shared_run_t {
+    explicit shared_run_t(int n) : nthreads(n) { std::memset(uid, 0, sizeof(uid)); }
+    void barrier()
+    {
+        if (nthreads <= 1) return;
+        std::unique_lock<std::mutex> lk(mu);
+        const uint64_t gen = generation;
+        if (++waiting == nthreads) {
+            waiting = 0;
+            ++generation;
+            cv.notify_all();
+        } else {
+            cv.wait(lk, [&] { return generation != gen; });
+        }
+    }
+    int nthreads;
+    unsigned char uid[128];
+    std::vector<float> mean, lnvar;
+    std::mutex mu;
+    std::condition_variable cv;
+    int waiting = 0;
+    uint64_t generation = 0;
+};
+
+struct device_t {   // one context + the resident data (one shard) of a run
     mmv_ctx *ctx = nullptr;
     mmv_csr *csr = nullptr;
+    int rank = 0, nranks = 1;
+    shared_run_t *shared = nullptr;
     ~device_t()
     {
         if (csr) mmv_csr_destroy(csr);
         if (ctx) mmv_ctx_destroy(ctx);
     }
-    // upload the counts (cells x genes CSR) and the covariates (dense [N x C], or none = all ones)
+    void barrier() { if (shared) shared->barrier(); }
+    // upload this block's counts (cells x genes CSR, shard-local cell ids) and covariates (dense [n x C], or none = all ones)
     int upload(int device, const mtx_data_block_t &data, const std::vector<float> *covar, int64_t c_dim)
     {
         MMV_OK(mmv_ctx_create(device, &ctx));
-        MMV_OK(mmv_csr_upload(ctx, data.ntot(), data.nfeature(), data.indptr.data(), data.indices.data(),
+        MMV_OK(mmv_csr_upload(ctx, data.nlocal(), data.nfeature(), data.indptr.data(), data.indices.data(),
                               data.values.data(), covar ? covar->data() : nullptr, c_dim, &csr));
         return EXIT_SUCCESS;
     }
@@ -64,7 +95,32 @@ public:
             os << "  " << name << " [" << r << " x " << c << "]" << (reg ? "" : " (not registered: frozen unless --train_all_layers)") << "\n";
         }
     }
+    // --init_dir: ${dir}/${parameter key}.f32 (raw float32, libtorch [rows x cols] layout) replaces that parameter
+    int load_params(const std::string &dir)
+    {
+        int n = 0, loaded = 0;
+        MMV_OK(mmv_model_num_params(m_, &n));
+        std::vector<float> host;
+        for (int i = 0; i < n; ++i) {
+            char name[MMV_NAME_LEN];
+            int64_t r = 0, c = 0;
+            int reg = 0;
+            MMV_OK(mmv_model_param_info(m_, i, name, &r, &c, &reg));
+            FILE *f = std::fopen((dir + "/" + name + ".f32").c_str(), "rb");
+            if (!f) continue;
+            host.resize((size_t)(r * c));
+            const size_t got = std::fread(host.data(), 4, host.size(), f);
+            const bool at_end = std::fgetc(f) == EOF;
+            std::fclose(f);
+            ERR_RET(got != host.size() || !at_end, dir << "/" << name << ".f32 does not hold " << r << " x " << c << " floats");
+            MMV_OK(mmv_model_set_param(m_, name, host.data(), r * c));
+            ++loaded;
+        }
+        TLOG("Initial values of " << loaded << " / " << n << " parameters read from " << dir);
+        return EXIT_SUCCESS;
+    }
     int64_t latent_dim = 0;
+    int64_t eps_per_cell = 0;   // floats of reparameterisation noise per cell and forward pass (mu latent [+ nu latent])
 
 protected:
     mmv_model *m_ = nullptr;
@@ -89,6 +145,7 @@ public:
         d.mu_r_dim = mu_r_dim; d.nu_h_dim = nu_h_dim; d.nu_r_dim = nu_r_dim; d.do_relu = do_relu ? 1 : 0;
         MMV_OK_EXIT(mmv_nb_model_create(ctx, &d, seed, &m_));
         latent_dim = mu_r_dim;
+        eps_per_cell = mu_r_dim + nu_r_dim;
     }
 };
 
@@ -112,6 +169,7 @@ public:
         d.kappa_min = kappa_min; d.kappa_max = kappa_max; d.do_relu = do_relu ? 1 : 0;
         MMV_OK_EXIT(mmv_vmf_model_create(ctx, &d, seed, &m_));
         latent_dim = z_dim;
+        eps_per_cell = z_dim;
     }
 };
 
@@ -128,25 +186,33 @@ public:
 // The latent tables come from mmv_encode (eval mode, no covariate term: nb.hh:627-628, vmf.hh:516-517).
 class latent_recorder_t {
 public:
-    latent_recorder_t(const std::string &out, int64_t max_epoch, device_t &dev, bool is_vmf = false, bool write_params = true)
-        : out_(out), max_epoch_(max_epoch), dev_(dev), is_vmf_(is_vmf), write_params_(write_params)
+    // One recorder per rank over the run's SHARED latent tables: a rank writes the rows of its own shard
+    // (global data-point id = shard_lo + local id), rank 0 writes the files at the recording epochs.
+    latent_recorder_t(const std::string &out, int64_t max_epoch, shared_run_t *shared, int64_t ntot, bool is_vmf = false,
+                      bool write_params = true)
+        : out_(out), max_epoch_(max_epoch), ntot_(ntot), is_vmf_(is_vmf), write_params_(write_params), mean_(shared->mean),
+          lnvar_(shared->lnvar), shared_(shared)
     {
     }
 
     template <typename MODEL, typename DATA_BLOCK>
-    void update_on_batch(MODEL &model, DATA_BLOCK &data, const std::vector<typename DATA_BLOCK::Index> &batch)
+    void update_on_batch(MODEL &model, DATA_BLOCK &data, const std::vector<typename DATA_BLOCK::Index> &batch, device_t &dev)
     {
         const int64_t R = model.latent_dim, B = (int64_t)batch.size();
-        if (mean_.empty()) {
-            mean_.assign((size_t)(data.ntot() * R), 0.f);
-            lnvar_.assign((size_t)(data.ntot() * R), 0.f);
+        {
+            std::lock_guard<std::mutex> lk(shared_->mu);
+            if (mean_.empty()) {
+                mean_.assign((size_t)(ntot_ * R), 0.f);
+                lnvar_.assign((size_t)(ntot_ * R), 0.f);
+            }
         }
         std::vector<int64_t> cells(batch.begin(), batch.end());
         std::vector<float> mu((size_t)(B * R)), lv((size_t)(B * R));
-        MMV_OK_EXIT(mmv_encode(model.get(), dev_.csr, cells.data(), B, mu.data(), lv.data()));
+        MMV_OK_EXIT(mmv_encode(model.get(), dev.csr, cells.data(), B, mu.data(), lv.data()));
+        const int64_t lo = (int64_t)data.shard_lo();
         for (int64_t j = 0; j < B; ++j) {
-            std::copy(mu.begin() + j * R, mu.begin() + (j + 1) * R, mean_.begin() + cells[(size_t)j] * R);
-            std::copy(lv.begin() + j * R, lv.begin() + (j + 1) * R, lnvar_.begin() + cells[(size_t)j] * R);
+            std::copy(mu.begin() + j * R, mu.begin() + (j + 1) * R, mean_.begin() + (lo + cells[(size_t)j]) * R);
+            std::copy(lv.begin() + j * R, lv.begin() + (j + 1) * R, lnvar_.begin() + (lo + cells[(size_t)j]) * R);
         }
     }
 
@@ -196,10 +262,10 @@ public:
 
 private:
     std::string out_;
-    int64_t max_epoch_;
-    device_t &dev_;
+    int64_t max_epoch_, ntot_;
     bool is_vmf_, write_params_;
-    std::vector<float> mean_, lnvar_;
+    std::vector<float> &mean_, &lnvar_;
+    shared_run_t *shared_;
 };
 
 // io.hh:308-331 write_vector_file: one value per line, gz

@@ -117,7 +117,7 @@ parse_mmvae_options(const int argc, const char *argv[], mmvae_options_t &options
 struct training_options_t {
     explicit training_options_t()
         : lr(1e-3f), grad_clip(1.f), nboot(3), max_epoch(101), recording(10), device(0), seed(0), bf16(false),
-          train_all_layers(false), record_params(true)
+          train_all_layers(false), record_params(true), ngpu(1)
     {
     }
     float lr;          // 1e-3
@@ -130,6 +130,12 @@ struct training_options_t {
     bool bf16;                 // --dtype bf16: tcgen05 GEMMs (1e-2 tolerance); default fp32 (1e-4)
     bool train_all_layers;     // default off = the reference's frozen unregistered Sequentials
     bool record_params;        // default on = the reference's per-parameter text dumps at every recorded epoch (nb.hh:599-615)
+    int ngpu;                  // --ngpu G: cells sharded over G GPUs of this box, one host thread + one context each (default 1)
+    // reproducibility hooks (long options only; the reference has neither: it seeds from random_device and draws
+    // eps inside forward).  --init_dir: ${dir}/${parameter key}.f32 raw float32 in the libtorch [rows x cols] layout
+    // replaces that parameter's initial value; --eps_file: raw float32 noise consumed in forward-call order
+    // (B x (mu latent [+ nu latent]) floats per forward) instead of the library's own Philox draws
+    std::string init_dir, eps_file;
 };
 
 inline int
@@ -141,7 +147,9 @@ parse_training_options(const int argc, const char *argv[], training_options_t &o
                         "--nboot      : #bootstrapped gradients (default: 3)\n"
                         "--max_epoch  : maximum #epoch (default: 101)\n"
                         "--recording  : recording interval (default: 10)\n"
-                        "--seed, --device, --dtype {f32,bf16}, --train_all_layers, --skip_param_record : B200 build additions\n\n";
+                        "--seed, --device, --dtype {f32,bf16}, --train_all_layers, --skip_param_record : B200 build additions\n"
+                        "--ngpu       : shard the cells over this many GPUs of the box (default: 1)\n"
+                        "--init_dir, --eps_file : reproducibility hooks (initial parameters / injected noise)\n\n";
     const option long_opts[] = { { "lr", required_argument, nullptr, 'L' },         { "learning", required_argument, nullptr, 'L' },
                                  { "learn_rate", required_argument, nullptr, 'L' }, { "learning_rate", required_argument, nullptr, 'L' },
                                  { "rate", required_argument, nullptr, 'L' },       { "grad_clip", required_argument, nullptr, 'G' },
@@ -151,6 +159,8 @@ parse_training_options(const int argc, const char *argv[], training_options_t &o
                                  { "seed", required_argument, nullptr, 1001 },      { "device", required_argument, nullptr, 1002 },
                                  { "dtype", required_argument, nullptr, 1003 },     { "train_all_layers", no_argument, nullptr, 1004 },
                                  { "skip_param_record", no_argument, nullptr, 1005 },
+                                 { "ngpu", required_argument, nullptr, 1006 },      { "init_dir", required_argument, nullptr, 1007 },
+                                 { "eps_file", required_argument, nullptr, 1008 },
                                  { "help", no_argument, nullptr, 'h' },             { nullptr, no_argument, nullptr, 0 } };
     bool help = false;
     mmvae_detail::scan_options(argc, argv, "L:G:B:E:R:h", long_opts, [&](int opt, const char *arg) {
@@ -165,6 +175,9 @@ parse_training_options(const int argc, const char *argv[], training_options_t &o
         case 1003: options.bf16 = std::strcmp(arg, "bf16") == 0; break;
         case 1004: options.train_all_layers = true; break;
         case 1005: options.record_params = false; break;
+        case 1006: options.ngpu = std::max(1, std::stoi(arg)); break;
+        case 1007: options.init_dir = arg; break;
+        case 1008: options.eps_file = arg; break;
         case 'h': help = true; break;
         default: break;
         }

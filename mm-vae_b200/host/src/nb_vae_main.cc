@@ -1,4 +1,5 @@
-// nb_vae — same command line as the reference's src/nb_vae_main.cc:39-133, B200 build.
+// nb_vae — same command line as the reference's src/nb_vae_main.cc:39-133, B200 build (+ --ngpu G: cells sharded
+// over G GPUs of the box, one host thread and one context per GPU, see mmvae_alg.hh).
 #include "mmvae_alg.hh"
 
 int
@@ -12,26 +13,9 @@ main(const int argc, const char *argv[])
     CHK(parse_nbvae_options(argc, argv, nb_opt));
     CHK(parse_training_options(argc, argv, train_opt));
 
-    run_inputs_t in;
-    CHK(load_inputs(main_options, in));
-
-    mmvae::device_t dev;
-    CHK(dev.upload(train_opt.device, *in.data, in.has_covar ? &in.covar : nullptr, in.c_dim));
-
-    TLOG("Constructing a model");
-    mmvae::nb::nbvae_t model(dev.ctx, in.data->nfeature(), in.c_dim, nb_opt.mean_encoding_layers,
-                             nb_opt.mean_decoding_layers, nb_opt.mean_latent, nb_opt.overdispersion_encoding,
-                             nb_opt.overdispersion_latent, nb_opt.do_relu, train_opt.seed + 7);
-
-    TLOG("Training the model...");
-    mmvae::latent_recorder_t recorder(main_options.out, train_opt.max_epoch, dev, /*is_vmf=*/false, train_opt.record_params);
-    nb_loss_t loss;
-    loss.min_rate = main_options.kl_min;
-    loss.max_rate = main_options.kl_max;
-    loss.time_discount = main_options.kl_discount;
-
-    auto scores = train_vae_model(model, recorder, *in.data, dev, train_opt, loss);
-    CHK(mmvae::write_vector_file(main_options.out + ".scores.gz", scores));
-    TLOG("Done");
-    return EXIT_SUCCESS;
+    return run_vae_main(main_options, train_opt, /*is_vmf=*/false, [&](mmv_ctx *ctx, int64_t n_features, int64_t c_dim) {
+        return std::unique_ptr<mmvae::nb::nbvae_t>(new mmvae::nb::nbvae_t(
+            ctx, n_features, c_dim, nb_opt.mean_encoding_layers, nb_opt.mean_decoding_layers, nb_opt.mean_latent,
+            nb_opt.overdispersion_encoding, nb_opt.overdispersion_latent, nb_opt.do_relu, train_opt.seed + 7));
+    });
 }

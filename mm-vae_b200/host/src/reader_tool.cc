@@ -18,7 +18,7 @@ write_raw(const std::string &path, const void *p, size_t bytes)
 int
 main(const int argc, const char *argv[])
 {
-    if (argc < 2) { std::cerr << "usage: mmv_reader_tool <header|scan|table|block|dense|csr|floats|write|ones|opts> ..." << std::endl; return 2; }
+    if (argc < 2) { std::cerr << "usage: mmv_reader_tool <header|scan|table|block|dense|csr|shard|floats|write|ones|opts> ..." << std::endl; return 2; }
     const std::string cmd = argv[1];
     using mmutil::index::Index;
     if (cmd == "header" && argc == 3) {
@@ -58,6 +58,12 @@ main(const int argc, const char *argv[])
         write_raw(std::string(argv[4]) + ".values", blk.values.data(), blk.values.size() * 4);
         std::printf("%ld %ld %ld\n", (long)blk.nfeature(), (long)blk.ntot(), (long)blk.indices.size());
         if (argc == 6) std::printf("%s\n", blk.from_cache() ? "cache" : "parsed");
+    } else if (cmd == "shard" && argc == 7) {         // shard <mtx> <idx> <out prefix> <lo> <hi>: CSR of data points [lo, hi) only
+        mmvae::mtx_data_block_t blk(argv[2], argv[3], 1, false, std::stol(argv[5]), std::stol(argv[6]));
+        write_raw(std::string(argv[4]) + ".indptr", blk.indptr.data(), blk.indptr.size() * 8);
+        write_raw(std::string(argv[4]) + ".indices", blk.indices.data(), blk.indices.size() * 4);
+        write_raw(std::string(argv[4]) + ".values", blk.values.data(), blk.values.size() * 4);
+        std::printf("%ld %ld %ld %ld\n", (long)blk.nfeature(), (long)blk.ntot(), (long)blk.nlocal(), (long)blk.indices.size());
     } else if (cmd == "floats") {                     // take_float of each argument -> bits
         for (int i = 2; i < argc; ++i) {
             const float w = mmvae::take_float(argv[i], std::strlen(argv[i]));
@@ -91,7 +97,7 @@ main(const int argc, const char *argv[])
                   << "\ncovar_idx " << mo.covar_idx << "\nbatch_size " << mo.batch_size << "\nkl_discount " << mo.kl_discount
                   << "\nkl_min " << mo.kl_min << "\nkl_max " << mo.kl_max << "\nlr " << to.lr << "\ngrad_clip " << to.grad_clip
                   << "\nnboot " << to.nboot << "\nmax_epoch " << to.max_epoch << "\nrecording " << to.recording << "\nseed " << to.seed
-                  << "\nbf16 " << to.bf16 << "\ntrain_all_layers " << to.train_all_layers << "\nmean_encoding "
+                  << "\nngpu " << to.ngpu << "\nbf16 " << to.bf16 << "\ntrain_all_layers " << to.train_all_layers << "\nmean_encoding "
                   << join(no.mean_encoding_layers) << "\nmean_decoding " << join(no.mean_decoding_layers) << "\nmean_latent "
                   << no.mean_latent << "\noverdispersion_encoding " << no.overdispersion_encoding << "\noverdispersion_latent "
                   << no.overdispersion_latent << "\nnb_relu " << no.do_relu << "\nencoding " << join(vo.encoding_layers)

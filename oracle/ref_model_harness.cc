@@ -6,7 +6,12 @@
 //   dump : runs the step of mmvae_alg.hh:274-311 with a fixed seed and fixed
 //          bootstrap indices, writing params / eps / outputs / loss terms /
 //          grads / post-Adam params as .npy files (golden vectors);
-//   bench: times that step on the host cores (cpu_baseline / --impl reference).
+//   bench: times that step on the host cores (cpu_baseline / --impl reference);
+//   train: the epoch x batch x bootstrap schedule of mmvae_alg.hh:254-334 around the reference's own model,
+//          loss, Adam and clip calls, made reproducible (the reference seeds its bootstrap mt19937 from
+//          std::random_device and draws eps inside forward): mt19937(seed) + uniform_int_distribution<> as in
+//          :242-244, torch::manual_seed before every forward with the drawn eps saved in call order.  Golden
+//          trajectory for the C++ mains (tests/golden/traj_*.npz).
 // The outputs go to oracle/_ref/ (binary) and, via tests/golden/gen_golden.py,
 // to tests/golden/*.npz.  No reference source is copied: it is #included.
 #include <torch/torch.h>
@@ -35,6 +40,7 @@ using mmvae::write_tensor;
 #include <cstdio>
 #include <fstream>
 #include <map>
+#include <random>
 #include <sys/stat.h>
 
 using torch::Tensor;
@@ -354,11 +360,100 @@ run_bench(const args_t &a)
     return 0;
 }
 
+
+// ----------------------------------------------------------------- train
+static void
+save_raw(const std::string &path, const Tensor &t_)
+{
+    Tensor t = t_.detach().to(torch::kCPU).contiguous();
+    std::ofstream f(path, std::ios::binary);
+    f.write((const char *)t.data_ptr(), t.numel() * t.element_size());
+}
+
+template <typename A>
+static int
+run_train(const args_t &a)
+{
+    const int64_t D = a.geti("D", 0), C = 1, N = a.geti("N", 0), B = a.geti("B", 0);
+    const int64_t epochs = a.geti("epochs", 2), nboot = a.geti("nboot", 3), seed = a.geti("seed", 7);
+    const double kl_min = a.getf("kl_min", 1e-2), kl_max = a.getf("kl_max", 1.), kl_discount = a.getf("kl_discount", .1);
+    const bool train_all = a.geti("train_all", 0) != 0;
+    const std::string out = a.get("out");
+    ::mkdir(out.c_str(), 0755);
+    ::mkdir((out + "/init").c_str(), 0755);
+
+    Tensor x_all = load_bin(a.get("x"), { N, D }, torch::kFloat32);
+    Tensor c_all = torch::ones({ N, C });   // create_ones_like (nb_vae_main.cc:67-73)
+    torch::manual_seed(seed);
+    A ad;
+    ad.build(a, D, C);
+    for (auto &p : ad.all_named()) {
+        std::string name = p.first;
+        save_raw(out + "/init/" + name + ".f32", p.second);
+        save_npy(fname(out, "init__param", name), p.second);
+    }
+    auto params = optim_params(ad, train_all);
+    torch::optim::Adam adam(params, torch::optim::AdamOptions(a.getf("lr", 1e-3)).weight_decay(1e-4));   // :234-236
+    const double grad_clip = a.getf("grad_clip", 1.0);
+
+    std::mt19937 rng((unsigned)seed);                                   // :242-244 (seeded, not random_device)
+    std::uniform_int_distribution<> rboot(0, (int)B - 1);
+    std::vector<int64_t> ridx(B);
+    int64_t nbatch = N / B;
+    if (nbatch * B < N) ++nbatch;
+    std::vector<Tensor> eps_stream, ridx_stream;
+    std::vector<float> batch_loss, scores;
+    int64_t fwd_k = 0;
+    auto forward = [&](Tensor x, Tensor c, float w) {
+        torch::manual_seed(seed + 1000 + fwd_k);
+        for (auto &e : ad.eps_like(B)) eps_stream.push_back(e.reshape({ -1 }));
+        torch::manual_seed(seed + 1000 + fwd_k);
+        ++fwd_k;
+        return ad.fwd_loss(x, c, w, nullptr);
+    };
+    for (int64_t epoch = 0; epoch < epochs; ++epoch) {
+        const float w = (float)std::max(kl_max * std::exp(-kl_discount * (double)epoch), kl_min);   // nb_vae_main.cc:14-37
+        float loss_epoch = 0.f;
+        for (int64_t b = 0; b < nbatch; ++b) {
+            std::vector<int64_t> batch(B);
+            for (int64_t j = 0; j < B; ++j) batch[j] = (b * B + j) % N;                            // :264-266
+            Tensor bi = torch::from_blob(batch.data(), { B }, torch::kInt64).clone();
+            Tensor x = torch::index_select(x_all, 0, bi), c = torch::index_select(c_all, 0, bi);
+            ad.model->train(true);
+            {
+                Tensor loss = forward(x, c, w).sum();                                             // :276-279
+                const float lb = loss.template item<float>();
+                loss_epoch += lb * B;
+                batch_loss.push_back(lb);
+            }
+            for (int64_t boot = 0; boot < nboot; ++boot) {
+                for (auto &r : ridx) r = rboot(rng);                                              // :294-295
+                Tensor ri = torch::from_blob(ridx.data(), { B }, torch::kInt64).clone();
+                ridx_stream.push_back(ri);
+                Tensor loss = forward(torch::index_select(x, 0, ri), torch::index_select(c, 0, ri), w);
+                adam.zero_grad();
+                loss.backward();
+                torch::nn::utils::clip_grad_norm_(params, grad_clip);
+                adam.step();
+            }
+            ad.model->train(false);
+        }
+        scores.push_back(loss_epoch / (float)(B * nbatch));                                       // :323
+    }
+    save_raw(out + "/eps.f32", torch::cat(eps_stream));
+    save_npy(out + "/eps.npy", torch::cat(eps_stream));
+    save_npy(out + "/ridx.npy", torch::stack(ridx_stream));
+    save_npy(out + "/batch_loss.npy", torch::from_blob(batch_loss.data(), { (int64_t)batch_loss.size() }, torch::kFloat32).clone());
+    save_npy(out + "/scores.npy", torch::from_blob(scores.data(), { (int64_t)scores.size() }, torch::kFloat32).clone());
+    for (auto &p : ad.all_named()) save_npy(fname(out, "final__param", p.first), p.second);
+    return 0;
+}
+
 int
 main(int argc, char **argv)
 {
     if (argc < 2) {
-        std::fprintf(stderr, "usage: %s dump|bench --key value ...\n", argv[0]);
+        std::fprintf(stderr, "usage: %s dump|bench|train --key value ...\n", argv[0]);
         return 1;
     }
     args_t a;
@@ -373,5 +468,7 @@ main(int argc, char **argv)
         return model == "nb" ? run_dump<nb_adapter>(a) : run_dump<vmf_adapter>(a);
     if (mode == "bench")
         return model == "nb" ? run_bench<nb_adapter>(a) : run_bench<vmf_adapter>(a);
+    if (mode == "train")
+        return model == "nb" ? run_train<nb_adapter>(a) : run_train<vmf_adapter>(a);
     return 1;
 }

@@ -48,6 +48,13 @@ MODEL_CASES = {
     "vmf_bigkappa": dict(model="vmf", D=6, B0=8, B=8, C=1, enc="5", dec="5", R=2,
                          steps=2, seed=41, kl=1.0, density=0.6, ln_kappa=1.5,
                          kappa_min=0.1, kappa_max=100.0),  # df=2 < kappa: second lbessel branch
+    # --relu (nb.hh:339-345 throws with hidden layers, SURVEY 0.5: nb only without them; vmf.hh:342-343 works)
+    "nb_relu": dict(model="nb", D=64, B0=11, B=11, C=1, enc="-", dec="-", R=3, H=1, Rnu=1,
+                    steps=2, seed=43, kl=1.0, density=0.25, relu=1),
+    "vmf_relu": dict(model="vmf", D=88, B0=14, B=12, C=2, enc="28,12", dec="12,28", R=5,
+                     steps=3, seed=47, kl=0.6, density=0.2, ln_kappa=0.2, relu=1),
+    "vmf_relu_trainall": dict(model="vmf", D=72, B0=13, B=13, C=1, enc="24", dec="20", R=4,
+                              steps=2, seed=53, kl=1.0, density=0.2, ln_kappa=0.5, relu=1, train_all=1),
 }
 
 
@@ -95,8 +102,13 @@ def gen_model_case(name, cfg):
 def main():
     if not os.path.exists(HARNESS):
         sys.exit("build the harness first: make -C oracle")
+    only = [a for a in sys.argv[1:] if not a.startswith("-")]   # optional: regenerate the named cases only
     for name, cfg in MODEL_CASES.items():
+        if only and name not in only:
+            continue
         gen_model_case(name, cfg)
+    if only:
+        return
     if os.path.exists(READER):
         sys.path.insert(0, HERE)
         import gen_reader_golden

@@ -9,7 +9,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 MODEL_CASES = ["nb_small", "nb_deep", "nb_nohidden", "nb_trainall", "nb_wide",
-               "vmf_small", "vmf_deep", "vmf_nohidden", "vmf_trainall", "vmf_bigkappa"]
+               "vmf_small", "vmf_deep", "vmf_nohidden", "vmf_trainall", "vmf_bigkappa",
+               "nb_relu", "vmf_relu", "vmf_relu_trainall"]
 
 
 class Golden:

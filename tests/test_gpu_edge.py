@@ -248,3 +248,59 @@ def test_deferred_terms_are_the_previous_steps(mmv, ctx):
     for a, b in zip(*out):      # two separately built models: equal up to the atomic summation order of the fp32 GEMMs
         assert all(abs(a[k] - b[k]) <= 1e-5 * max(abs(b[k]), 1e-6) for k in a), (a, b)
     csr.close()
+
+
+# ------------------------------------------------------------------ vMF at the SURVEY cfg-5 widths
+CFG5 = dict(D=30000, B=4096, enc=[2048, 512], dec=[512, 2048], R=128)
+
+
+@pytest.mark.parametrize("dtype", ["f32", "bf16"])
+def test_full_size_vmf_cfg5_vs_oracle(mmv, ctx, full_batch, dtype):
+    """vmf_vae at the cfg-5 architecture (encoder [2048, 512], decoder [512, 2048], latent 128, D = 30 000, B = 4096):
+    the K = 2048 products (6-stage single-wave GEMM, split-K, persistent kernel), the angular first layer at h1 = 2048
+    and K5 at full size, one minibatch against the oracle (vmf.hh:292-304,419-440): fp32 1e-4, bf16 1e-2."""
+    tol = 1e-4 if dtype == "f32" else 1e-2
+    x = full_batch
+    D, B = CFG5["D"], CFG5["B"]
+    rng = np.random.default_rng(55)
+    csr = mmv.CSR.from_dense(ctx, x)
+    m, neps = make_model(mmv, ctx, "vmf", D, CFG5["enc"], CFG5["dec"], CFG5["R"], dtype, rng)
+    eps = [rng.normal(size=(B, n)).astype(np.float32) for n in neps]
+    terms, worst = check_vs_oracle(mmv, m, "vmf", csr, x, np.arange(B), eps, tol, klw=1.0, cache_key="cfg5")
+    print(dtype, "loss", terms["loss"], {k: f"{v:.1e}" for k, v in sorted(worst.items(), key=lambda kv: -kv[1])[:4]})
+    m.close()
+    csr.close()
+
+
+def test_streamed_minibatch_with_out_of_range_gene_fails_loudly(mmv, ctx):
+    """mmv_csr_update skips the host scan; the device-side check neutralises an out-of-range gene id in the slot and
+    the step that consumes the slot reports it instead of indexing weight rows / shared memory with it."""
+    D, B = 5000, 64
+    rng = np.random.default_rng(21)
+    x = synth(rng, B, D)
+    ip, ix, v = mmv.dense_to_csr(x)
+    h_ip, h_ix, h_v = mmv.pinned_empty(B + 1, np.int64), mmv.pinned_empty(len(ix), np.int32), mmv.pinned_empty(len(ix), np.float32)
+    h_ip[:], h_ix[:], h_v[:] = ip, ix, v
+    m, neps = make_model(mmv, ctx, "nb1", D, [96], [80], 8, "bf16", np.random.default_rng(3))
+    eps = [rng.normal(size=(B, n)).astype(np.float32) for n in neps]
+    csr = mmv.CSR.create(ctx, B, len(ix) + 5, D, 0)
+    csr.update(B, h_ip, h_ix, h_v)
+    good = m.step(csr, np.arange(B), eps=eps, kl_weight=0.5, flags=mmv.FWD | mmv.BWD)
+    assert np.isfinite(good["loss"])
+    for bad in (D, D + 12345, -3):
+        h_ix[int(ip[7]) + 2] = bad
+        csr.update(B, h_ip, h_ix, h_v)
+        with pytest.raises(mmv.MMVError, match="gene index outside"):
+            m.step(csr, np.arange(B), eps=eps, kl_weight=0.5, flags=mmv.FWD | mmv.BWD)
+        h_ix[int(ip[7]) + 2] = ix[int(ip[7]) + 2]
+    csr.update(B, h_ip, h_ix, h_v)          # a clean minibatch afterwards steps again, same result
+    again = m.step(csr, np.arange(B), eps=eps, kl_weight=0.5, flags=mmv.FWD | mmv.BWD)
+    assert abs(again["loss"] - good["loss"]) <= 1e-6 * abs(good["loss"])
+    # adopted device arrays cannot be repaired: refused at wrap time
+    t_ip, t_ix, t_v = torch.from_numpy(ip).cuda(), torch.from_numpy(ix.copy()).cuda(), torch.from_numpy(v).cuda()
+    t_ix[5] = D
+    torch.cuda.synchronize()
+    with pytest.raises(mmv.MMVError, match="out of range"):
+        mmv.CSR.wrap_device(ctx, B, D, len(ix), int(np.diff(ip).max()), t_ip.data_ptr(), t_ix.data_ptr(), t_v.data_ptr())
+    m.close()
+    csr.close()

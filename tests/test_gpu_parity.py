@@ -35,10 +35,10 @@ def build_model(mmv, ctx, g):
     enc = [] if cfg["enc"] == "-" else [int(v) for v in cfg["enc"].split(",")]
     dec = [] if cfg["dec"] == "-" else [int(v) for v in cfg["dec"].split(",")]
     if cfg["model"] == "nb":
-        m = mmv.Model.nb(ctx, cfg["D"], cfg["C"], enc, dec, cfg["R"], cfg["H"], cfg["Rnu"])
+        m = mmv.Model.nb(ctx, cfg["D"], cfg["C"], enc, dec, cfg["R"], cfg["H"], cfg["Rnu"], relu=bool(cfg.get("relu", 0)))
     else:
         m = mmv.Model.vmf(ctx, cfg["D"], cfg["C"], cfg["R"], enc, dec,
-                          cfg.get("kappa_min", 0.1), cfg.get("kappa_max", 10.0))
+                          cfg.get("kappa_min", 0.1), cfg.get("kappa_max", 10.0), relu=bool(cfg.get("relu", 0)))
     m.set_params(g.params("init"))
     m.set_option("train_all_layers", cfg.get("train_all", 0))
     m.set_option("frozen_grads", 1)

@@ -31,9 +31,9 @@ def rg():
     return {k: z[k] for k in z.files}
 
 
-def run(tool, *args):
+def run(tool, *args, env=None):
     return subprocess.run([tool, *map(str, args)], check=True, stdout=subprocess.PIPE, stderr=subprocess.PIPE,
-                          text=True).stdout
+                          text=True, env=None if env is None else dict(os.environ, **env)).stdout
 
 
 def test_take_float_bit_exact(tool, rg):
@@ -254,6 +254,32 @@ def test_synthetic_shard_roundtrip_through_mtx(tool, tmp_path):
     assert np.array_equal(np.fromfile(str(tmp_path / "c") + ".values", dtype=np.float32), values)
 
 
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_shard_ingest_concatenates_to_the_full_csr(tool, tag, rg, tmp_path):
+    """mtx_data_block_t(..., col_lo, col_hi): every shard parses only its own range of the text; the shards'
+    CSR arrays laid end to end are the whole-file CSR, for any cut (incl. cuts next to empty data points)."""
+    gz = os.path.join(GOLDEN, FILES[tag])
+    idx = tmp_path / "i.index"
+    run(tool, "table", gz, idx)
+    run(tool, "csr", gz, idx, tmp_path / "full", env={"MMV_INGEST_THREADS": "1"})
+    full = {k: np.fromfile(str(tmp_path / "full") + "." + k, dtype=d) for k, d in (("indptr", np.int64), ("indices", np.int32), ("values", np.float32))}
+    N = len(full["indptr"]) - 1
+    for cuts in ([0, N], [0, N // 2, N], [0, 1, 2, N - 1, N], [0, N // 3, N // 3 + 1, 2 * N // 3, N]):
+        cuts = sorted(set(cuts))
+        ip, ix, vv = [np.zeros(1, np.int64)], [], []
+        for th, (lo, hi) in enumerate(zip(cuts[:-1], cuts[1:])):
+            out = run(tool, "shard", gz, idx, tmp_path / "s", lo, hi, env={"MMV_INGEST_THREADS": str(1 + th % 3)}).split()
+            assert int(out[2]) == hi - lo
+            p = np.fromfile(str(tmp_path / "s") + ".indptr", dtype=np.int64)
+            assert len(p) == hi - lo + 1 and p[0] == 0
+            ip.append(p[1:] + ip[-1][-1])
+            ix.append(np.fromfile(str(tmp_path / "s") + ".indices", dtype=np.int32))
+            vv.append(np.fromfile(str(tmp_path / "s") + ".values", dtype=np.float32))
+        assert np.array_equal(np.concatenate(ip), full["indptr"]), cuts
+        assert np.array_equal(np.concatenate(ix), full["indices"]), cuts
+        assert np.array_equal(np.concatenate(vv).view(np.uint32), full["values"].view(np.uint32)), cuts
+
+
 def test_reader_under_sanitizers(rg, tmp_path):
     """The host reader (bgzf inflate, in-place line split, index, parallel ingest, CSR cache, dense views) built with
     AddressSanitizer + UBSan: any finding aborts the tool and fails the call."""
@@ -278,6 +304,21 @@ def test_reader_under_sanitizers(rg, tmp_path):
         go("dense", gz, idx, tmp_path / "d.bin", 0, n - 1, n // 2, 0)
     go("floats", "1.5e1", "-3.25", "7", "1e-3", "00012.5000", ".5", "abc")
     go("ones", 37, tmp_path / "ones.mtx.gz")
+    # corrupt / foreign blocks must be refused without touching memory outside the buffers: BSIZE below the
+    # 26-byte minimum (header + trailer; 'bsize - 18 - 8' used to underflow), a truncated block, a wrong ISIZE
+    raw = open(os.path.join(GOLDEN, FILES["a"]), "rb").read()
+    bsize = raw[16] | (raw[17] << 8)
+    cases = {"short_bsize": raw[:16] + bytes([20, 0]) + raw[18:],
+             "truncated": raw[:bsize // 2],
+             "bad_isize": raw[:bsize - 3] + bytes([0xff, 0xff, 0x7f, 0x00]) + raw[bsize + 1:]}
+    for name, blob in cases.items():
+        bad = tmp_path / f"{name}.mtx.gz"
+        bad.write_bytes(blob)
+        p = subprocess.run([asan, "block", str(bad), "0", "0"], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+        assert "AddressSanitizer" not in p.stderr and "runtime error" not in p.stderr, (name, p.stderr[-1500:])
+        p = subprocess.run([asan, "table", str(bad), str(tmp_path / f"{name}.index")], env=env, stdout=subprocess.PIPE,
+                           stderr=subprocess.PIPE, text=True)
+        assert "AddressSanitizer" not in p.stderr and "runtime error" not in p.stderr, (name, p.stderr[-1500:])
 
 
 def test_parallel_ingest_under_thread_sanitizer(tmp_path):

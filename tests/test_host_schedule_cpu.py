@@ -91,6 +91,59 @@ def test_nb_vae_schedule(stub, tmp_path):
     assert not os.path.exists(f"{out}_0.mu_mean.gz") and not os.path.exists(f"{out}_4.mu_mean.gz")
 
 
+def test_nb_vae_ngpu2_schedule(stub, tmp_path):
+    """--ngpu 2 (one process, one host thread + context per GPU): contiguous shards [g N / 2, (g + 1) N / 2) ingested and
+    uploaded per rank, one in-process communicator, the same schedule on every shard with shard-local cell ids, the number
+    of minibatches of the largest shard, losses and files from rank 0, the latent table filled by both ranks."""
+    B, E, nboot = 96, 2, 2
+    calls, out = run_main(stub, tmp_path, "nb_vae", "--batch_size", B, "--max_epoch", E, "--recording", 1, "--nboot", nboot,
+                          "--seed", 5, "--skip_param_record", "--mean_latent", 3, "--ngpu", 2)
+    names = [c[0] for c in calls]
+    assert names.count("comm_unique_id") == 1 and names.count("ctx_create") == 2 and names.count("nb_model") == 2
+    ups = sorted((int(c[1]["dev"]), int(c[1]["cells"])) for c in calls if c[0] == "csr_upload")
+    assert ups == [(0, N // 2), (1, N - N // 2)]
+    inits = sorted((int(c[1]["device"]), int(c[1]["nranks"]), int(c[1]["rank"]), c[1]["id_ok"]) for c in calls if c[0] == "comm_init")
+    assert inits == [(0, 2, 0, "1"), (1, 2, 1, "1")]
+    nbatch = math.ceil(math.ceil(N / 2) / B)
+    for dev in (0, 1):
+        body = [c for c in calls if c[0] in ("step", "encode") and int(c[1]["dev"]) == dev]
+        nloc = N // 2 if dev == 0 else N - N // 2
+        i = 0
+        for epoch in range(E):
+            for b in range(nbatch):
+                ev = body[i][1]; i += 1
+                assert int(ev["flags"]) == FWD | PHILOX | DEFERRED and int(ev["ncells"]) == nloc
+                assert (int(ev["first"]), int(ev["last"])) == ((b * B) % nloc, (b * B + B - 1) % nloc)     # shard-local ids, wrap
+                for _ in range(nboot):
+                    st = body[i][1]; i += 1
+                    assert int(st["flags"]) == FWD | BWD | OPTIM | PHILOX and st["boot"] == "1"
+                en = body[i]; i += 1
+                assert en[0] == "encode" and en[1]["first"] == ev["first"]
+        assert i == len(body)
+    assert scores(str(out) + ".scores.gz").shape == (E,)
+    m = np.loadtxt(gzip.open(f"{out}_1.mu_mean.gz", "rt"))
+    # the stub's encode returns the (shard-local) cell id: rows of shard 1 restart at 0 -> the table is global, ids local
+    assert m.shape == (N, 3)
+    assert np.array_equal(m[:N // 2, 0], np.arange(N // 2)) and np.array_equal(m[N // 2:, 0], np.arange(N - N // 2))
+
+
+def test_init_dir_and_eps_file_hooks(stub, tmp_path):
+    """--init_dir / --eps_file (reproducibility hooks): named parameter files are loaded through mmv_model_set_param before
+    training, and every forward takes its noise from the file instead of the library's Philox draws."""
+    B, R = 250, 3
+    init = tmp_path / "init"
+    init.mkdir()
+    np.zeros(D, np.float32).tofile(init / "x_mean.f32")
+    nfwd = 1 * 2 * (1 + 2)
+    np.arange(nfwd * B * (R + 1), dtype=np.float32).tofile(tmp_path / "eps.f32")
+    # the stub exposes no parameters (num_params = 0): the loader must then load nothing and not fail
+    calls, _ = run_main(stub, tmp_path, "nb_vae", "--batch_size", B, "--max_epoch", 1, "--nboot", 2, "--seed", 5, "--skip_param_record",
+                        "--mean_latent", R, "--init_dir", init, "--eps_file", tmp_path / "eps.f32")
+    steps = [c[1] for c in calls if c[0] == "step"]
+    assert len(steps) == nfwd and all(s["eps"] == "1" for s in steps)
+    assert all(int(s["flags"]) & PHILOX == 0 for s in steps)
+
+
 def test_vmf_vae_schedule_and_vmf_latent_option(stub, tmp_path):
     calls, out = run_main(stub, tmp_path, "vmf_vae", "--batch", 250, "--epoch", 2, "--recording", 2, "--nboot", 1, "--latent", 4,
                           "--encoding", "16,8", "--decoding", "8", "--kappa_max", 20, "--skip_param_record", "--vmf_latent")

@@ -20,7 +20,7 @@ def test_model_oracle_matches_reference(case):
     cfg = g.cfg
     model = cfg["model"]
     P = to_t(g.params("init"))
-    kw = dict(kap_min=cfg.get("kappa_min", 0.1), kap_max=cfg.get("kappa_max", 10.0))
+    kw = dict(kap_min=cfg.get("kappa_min", 0.1), kap_max=cfg.get("kappa_max", 10.0), relu=bool(cfg.get("relu", 0)))
     adam = mo.Adam(lr=1e-3, weight_decay=1e-4)
     train_all = bool(cfg.get("train_all", 0))
     acc = {}  # grads of the unregistered Sequentials accumulate (zero_grad misses them)
@@ -67,7 +67,7 @@ def test_encode_recorder_path(case):
     g = Golden(case)
     P = to_t(g.params("init"))
     x = torch.from_numpy(g.a["x"])
-    mean, lnvar = (mo.nb_encode_mu if g.cfg["model"] == "nb" else mo.vmf_encode)(P, x)
+    mean, lnvar = (mo.nb_encode_mu if g.cfg["model"] == "nb" else mo.vmf_encode)(P, x, relu=bool(g.cfg.get("relu", 0)))
     assert rel_err(mean.numpy(), g.a["enc__mean"]) < 1e-6
     assert rel_err(lnvar.numpy(), g.a["enc__lnvar"]) < 1e-6
 
@@ -131,3 +131,50 @@ def test_reader_dense_minibatches(rg, tag):
     for cols, dense in zip(rg[f"{tag}__batches"], rg[f"{tag}__dense"]):
         got = bgzf_mtx.read_batch_dense(path, tab, cols.tolist(), D)
         assert np.array_equal(got.view(np.uint32), dense.view(np.uint32))
+
+
+@pytest.mark.parametrize("case", ["traj_nb", "traj_vmf"])
+def test_oracle_trajectory(case):
+    """The epoch x batch x bootstrap schedule (mmvae_alg.hh:254-334) replayed by the oracle on the reference's own
+    eps / bootstrap streams (tests/golden/gen_traj_golden.py): per-batch losses, epoch scores, final parameters."""
+    g = Golden(case)
+    cfg = g.cfg
+    model, N, B, R = cfg["model"], cfg["N"], cfg["B"], cfg["R"]
+    n_eps = [R, cfg["Rnu"]] if model == "nb" else [R]
+    P = to_t(g.params("init"))
+    x_all = torch.from_numpy(g.a["x"])
+    eps_stream, ridx = g.a["eps"], g.a["ridx"]
+    adam = mo.Adam(lr=cfg["lr"], weight_decay=1e-4)
+    frozen = _unregistered(model, P) if not cfg["train_all"] else set()
+    pos, kb, batch_loss, scores = 0, 0, [], []
+
+    def next_eps():
+        nonlocal pos
+        out = []
+        for n in n_eps:
+            out.append(torch.from_numpy(eps_stream[pos:pos + B * n].reshape(B, n)))
+            pos += B * n
+        return out
+
+    nbatch = -(-N // B)
+    for epoch in range(cfg["epochs"]):
+        w = max(cfg["kl_max"] * float(np.exp(np.float32(-cfg["kl_discount"] * epoch))), cfg["kl_min"])
+        tot = 0.0
+        for b in range(nbatch):
+            cells = (b * B + np.arange(B)) % N
+            x, c = x_all[cells], torch.ones(B, 1)
+            terms, _, _ = mo.run_step(model, P, x, c, next_eps(), w)
+            batch_loss.append(float(terms["loss"]))
+            tot += float(terms["loss"]) * B
+            for _ in range(cfg["nboot"]):
+                r = torch.from_numpy(ridx[kb]); kb += 1
+                _, _, grads = mo.run_step(model, P, x[r], c[r], next_eps(), w)
+                opt = {k: v.clone() for k, v in grads.items() if k not in frozen}
+                mo.clip_grad_norm_(list(opt.values()), 1.0)
+                adam.step(P, opt)
+        scores.append(tot / (B * nbatch))
+    assert pos == len(eps_stream) and kb == len(ridx)
+    assert np.allclose(batch_loss, g.a["batch_loss"], rtol=2e-5), np.abs(np.array(batch_loss) / g.a["batch_loss"] - 1).max()
+    assert np.allclose(scores, g.a["scores"], rtol=2e-5)
+    for k, ref in g.params("final").items():
+        assert rel_err(P[k].numpy(), ref) < 1e-4, (k, rel_err(P[k].numpy(), ref))
