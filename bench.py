@@ -697,8 +697,11 @@ def run_own(args):
     k1c = k1_contract_bytes(w, B, args.dtype == "bf16")
     kernels = {}
     for name, (t, c) in prof.items():
-        per = t / c
-        ent = {"ms_per_launch_group": round(per, 4), "share": round(t / ms_prof, 4)}
+        # `amount` is the group's work per STEP: divide by the group's time per step (a group may launch several
+        # kernels per step: the 15 small GEMMs of gemm_other were judged on ONE launch's time until round 2)
+        per = t / n_prof
+        ent = {"ms_per_launch_group": round(t / c, 4), "launches_per_step": round(c / n_prof, 2), "ms_per_step": round(per, 4),
+               "share": round(t / ms_prof, 4)}
         if name in work:
             bound, amount = work[name]
             if bound == "hbm":

@@ -28,6 +28,31 @@ vec_combine_kernel(const float *a, const float *b, const float *c, float sb, flo
     if (j < n) out[j] = (a ? a[j] : 0.f) + (b ? sb * b[j] : 0.f) + (c ? sc * c[j] : 0.f);
 }
 
+// per-gene constants of K4 in one launch: abias = mu_decoding.bias + covar_decoding.bias + mu_bias (+ sum_c Wcd[j, c] when the
+// covariates are the implicit all-ones block and the bias travels with the logits), ubias = nu_decoding.bias - nu_bias
+__global__ void
+nb_gene_bias_kernel(const float *blast, const float *bcd, const float *mu_bias, const float *Wcd, int C, const float *bnd,
+                    const float *nu_bias, float *abias, float *ubias, int D)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= D) return;
+    float ab = (blast ? blast[j] : 0.f) + bcd[j] + mu_bias[j];
+    if (Wcd)
+        for (int c = 0; c < C; ++c) ab += Wcd[(size_t)j * C + c];
+    abias[j] = ab;
+    ubias[j] = bnd[j] - nu_bias[j];
+}
+
+int
+launch_nb_gene_bias(const float *blast, const float *bcd, const float *mu_bias, const float *Wcd, int C, const float *bnd,
+                    const float *nu_bias, float *abias, float *ubias, int D, cudaStream_t st)
+{
+    nb_gene_bias_kernel<<<ceil_div(D, 256), 256, 0, st>>>(blast, bcd, mu_bias, Wcd, C, bnd, nu_bias, abias, ubias, D);
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int
 launch_gene_prep(const float *ln_x_sd, float eps, float *inv_t, int D, cudaStream_t st)
 {

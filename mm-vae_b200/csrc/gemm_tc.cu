@@ -48,6 +48,7 @@ struct params_t {
     int relu;
     int tma_epi;   // 0: register epilogue ; 1: TMA tile store ; 2: TMA reduce-add (beta = 1 or split-K)
     double *sumsq; // persistent store epilogue: += sum of squares of the product
+    float2 *row_stats;   // persistent store epilogue: [tiles_n x M] softmax partials (max log2(e), sum exp2) per row and column tile
     int n_fast;    // persistent tile order: 1 = consecutive tiles walk N (A tile reused from L2), 0 = walk M (B tile reused)
 };
 
@@ -364,8 +365,14 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
             mbar_wait(tfull0 + 8 * acc, aph);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            float rmax = -INFINITY, rsum = 0.f;      // softmax partials of this lane's row over the tile's columns (log2 domain)
             for (int c = 0; c < P_BLOCK_N / 32; ++c) {
                 uint32_t v[32];
+                float bl = 0.f;
+                if (p.bias) {
+                    const int col = n0 + 32 * c + lane;
+                    if (col < p.N) bl = __ldg(p.bias + col);
+                }
                 tmem_ld32(tmem_base + ((uint32_t)(32 * e) << 16) + acc * P_BLOCK_N + (uint32_t)(32 * c), v);
                 if (c == P_BLOCK_N / 32 - 1) {   // accumulator fully read: hand it back to the MMA warp
                     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -377,18 +384,51 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                     if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
                     __syncwarp();
                 }
+                // The four epilogue warps sit alone on their sub-partitions: every instruction here is on the critical
+                // path of the tile, so no per-element branches or loads.  The chunk's 32 bias values come in with ONE
+                // coalesced load (issued before the TMEM read above) and are handed round by shuffles.
+                if (p.bias) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __shfl_sync(0xffffffffu, bl, i));
+                }
+                if (p.relu) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), 0.f));
+                }
+                if (p.row_stats) {
+                    const int ncol = p.N - (n0 + 32 * c);             // columns of this chunk inside the matrix
+                    if (ncol < 32) {                                  // edge tile: -inf drops a column from max and sum
+                        // (the TMA store clips such a column, the -inf never reaches memory)
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (i >= ncol) v[i] = __float_as_uint(-INFINITY);
+                    }
+                    float cm = __uint_as_float(v[0]);
+#pragma unroll
+                    for (int i = 1; i < 32; ++i) cm = fmaxf(cm, __uint_as_float(v[i]));
+                    if (cm > -INFINITY) {                             // online merge into the tile's running (max, sum), log2 domain
+                        constexpr float kL2E = 1.4426950408889634f;
+                        const float nm = fmaxf(rmax, cm * kL2E);
+                        float a0 = rmax > -INFINITY ? rsum * exp2f(rmax - nm) : 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+                        for (int i = 0; i < 32; i += 4) {
+                            float t0, t1, t2, t3;
+                            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(fmaf(__uint_as_float(v[i]), kL2E, -nm)));
+                            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(fmaf(__uint_as_float(v[i + 1]), kL2E, -nm)));
+                            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t2) : "f"(fmaf(__uint_as_float(v[i + 2]), kL2E, -nm)));
+                            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t3) : "f"(fmaf(__uint_as_float(v[i + 3]), kL2E, -nm)));
+                            a0 += t0; a1 += t1; a2 += t2; a3 += t3;
+                        }
+                        rsum = (a0 + a1) + (a2 + a3);
+                        rmax = nm;
+                    }
+                }
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    float f[4];
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const int col = n0 + 32 * c + 4 * j + q;
-                        f[q] = __uint_as_float(v[4 * j + q]);
-                        if (p.bias && col < p.N) f[q] += p.bias[col];
-                        if (p.relu) f[q] = fmaxf(f[q], 0.f);
-                    }
-                    ss += f[0] * f[0] + f[1] * f[1] + f[2] * f[2] + f[3] * f[3];   // out-of-range parts of edge tiles are zero (no bias: launcher)
-                    *reinterpret_cast<float4 *>(box + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_float4(f[0], f[1], f[2], f[3]);
+                    const float f0 = __uint_as_float(v[4 * j]), f1 = __uint_as_float(v[4 * j + 1]), f2 = __uint_as_float(v[4 * j + 2]),
+                                f3 = __uint_as_float(v[4 * j + 3]);
+                    if (p.sumsq) ss += f0 * f0 + f1 * f1 + f2 * f2 + f3 * f3;   // out-of-range parts of edge tiles are zero (no bias: launcher)
+                    *reinterpret_cast<float4 *>(box + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_float4(f0, f1, f2, f3);
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
@@ -405,6 +445,10 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");   // (possibly empty) group: keeps the count in step
                 }
                 ++nstore;
+            }
+            if (p.row_stats) {
+                const int row = m0 + 32 * e + lane;
+                if (row < p.M) p.row_stats[(size_t)(n0 / P_BLOCK_N) * p.M + row] = make_float2(rmax, rsum);   // coalesced over rows
             }
         }
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
@@ -504,8 +548,10 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
     p.C = g.C; p.Cb = reinterpret_cast<__nv_bfloat16 *>(g.Cb); p.bias = g.bias;
     p.M = g.M; p.N = g.N; p.K = g.K; p.ldc = g.ldc; p.ldcb = g.ldcb; p.beta = g.beta; p.relu = g.relu;
     p.sumsq = nullptr;
+    p.row_stats = nullptr;
     p.n_fast = g.M > g.N ? 1 : 0;
     if (g.sumsq_done) *g.sumsq_done = 0;
+    if (g.row_stats_tiles) *g.row_stats_tiles = 0;
     dim3 grid(ceil_div(g.N, BLOCK_N), ceil_div(g.M, BLOCK_M));
     const int tiles = (int)(grid.x * grid.y), total_kb = ceil_div(g.K, BLOCK_K);
     if (tiles <= 64 && total_kb >= 16 && !g.relu && !g.Cb && g.C && (g.beta == 1.f || (g.beta == 0.f && g.ldc == g.N))) {
@@ -546,6 +592,10 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
         if (g.sumsq && p.tma_epi == 1 && !g.bias) {
             p.sumsq = g.sumsq;
             if (g.sumsq_done) *g.sumsq_done = 1;
+        }
+        if (g.row_stats && g.row_stats_tiles && p.tma_epi == 1 && !g.relu) {
+            p.row_stats = reinterpret_cast<float2 *>(g.row_stats);
+            *g.row_stats_tiles = ceil_div(g.N, P_BLOCK_N);
         }
         void (*pk)(const CUtensorMap, const CUtensorMap, const CUtensorMap, params_t) =
             g.a_mn ? (g.b_mn ? gemm_tc_persist_kernel<true, true> : gemm_tc_persist_kernel<true, false>)

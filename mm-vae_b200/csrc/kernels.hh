@@ -39,6 +39,11 @@ struct gemm_tc_args_t {
     // *sumsq_done is set to 1 when the chosen kernel did it (persistent store epilogue), else 0
     double *sumsq = nullptr;
     int *sumsq_done = nullptr;
+    // optional softmax statistics of the output rows (decoder-last forward feeding K4): per (256-column tile t, row r)
+    // row_stats[t * M + r] = (max_j x_rj log2(e), sum_j 2^(x_rj log2(e) - max)) over the tile's columns, x including the bias.
+    // *row_stats_tiles = number of column tiles when the chosen kernel wrote them (persistent store epilogue), else 0
+    void *row_stats = nullptr;
+    int *row_stats_tiles = nullptr;
 };
 bool gemm_tc_supported(const gemm_tc_args_t &g);
 int launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream);
@@ -164,8 +169,9 @@ int launch_w1eff_bf16(const float *W1T, const float *col_scale, void *out, int D
 
 // ---- K4 NB likelihood (nb_likelihood.cu)
 struct nb_lik_args_t {
-    const float *G = nullptr;         // [B x D] last decoder layer output WITHOUT bias
-    const float *abias = nullptr;     // [D] mu_decoding.bias + covar_decoding.bias + mu_bias
+    const float *G = nullptr;         // [B x D] last decoder layer output WITHOUT bias (tuned kernel: the complete logits)
+    const float *abias = nullptr;     // [D] mu_decoding.bias + covar_decoding.bias + mu_bias (tuned kernel: nullptr, it is in G)
+    const void *rowmeta = nullptr;    // tuned kernel: float4[B] (max log2(e), 1 / sum exp2, depth, znu) from launch_nb_row_meta
     const float *Wcd = nullptr;       // [D x C] covar_decoding.weight
     const float *cov = nullptr;       // [n_cells x C] covariates (nullptr: ones)
     const int64_t *indptr = nullptr;
@@ -192,6 +198,10 @@ struct nb_lik_args_t {
     int64_t *slice_bounds = nullptr;  // workspace [B x 9] for the tuned kernel (per-row CSR offsets of the gene slices)
 };
 bool nb_likelihood_fast_eligible(const nb_lik_args_t &a);
+// per-row metadata of the tuned kernel from the GEMM epilogue's [n_tiles x B] partials (tile_stats) or, without them, from
+// one pass over the complete logits G
+int launch_nb_row_meta(const float *G, const void *tile_stats, int n_tiles, const float *dpre, const float *znu, int B, int D,
+                       void *meta, cudaStream_t stream);
 int launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stream);
 int launch_nb_likelihood(const nb_lik_args_t &a, int num_sms, cudaStream_t stream);
 
@@ -240,6 +250,8 @@ int launch_vmf_scalar(const vmf_scalar_args_t &s, cudaStream_t st);
 int launch_gene_prep(const float *ln_x_sd, float eps, float *inv_t, int D, cudaStream_t st);
 int launch_vec_combine(const float *a, const float *b, const float *c, float sb, float sc, float *out, int n,
                        cudaStream_t st);
+int launch_nb_gene_bias(const float *blast, const float *bcd, const float *mu_bias, const float *Wcd, int C, const float *bnd,
+                        const float *nu_bias, float *abias, float *ubias, int D, cudaStream_t st);
 
 struct reparam_args_t {
     const float *head = nullptr;      // [B x 2R] mean_raw | lnvar_raw

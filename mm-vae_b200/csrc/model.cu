@@ -688,8 +688,9 @@ tc_ok(const step_t &s, int64_t M, int64_t N, int64_t K, int lda, int ldb)
 // Y = X W^T (+ b)
 int
 lin_fwd(const step_t &s, const float *X, int in, const float *W, const float *b, int out, float *Y, bool relu,
-        const char *tag = "gemm_other", bool want_twin = true)
+        const char *tag = "gemm_other", bool want_twin = true, void *row_stats = nullptr, int *row_stats_tiles = nullptr)
 {
+    if (row_stats_tiles) *row_stats_tiles = 0;
     mmv_model *m = s.m;
     if (tc_ok(s, s.B, out, in, in, in)) {
         gemm_tc_args_t t;
@@ -700,6 +701,7 @@ lin_fwd(const step_t &s, const float *X, int in, const float *W, const float *b,
             t.Cb = bf16_twin(s, Y, (size_t)s.B * out);
             t.ldcb = out;
         }
+        t.row_stats = row_stats; t.row_stats_tiles = row_stats_tiles;
         PROF(tag);
         return launch_gemm_tc(t, s.st);
     }
@@ -815,9 +817,11 @@ encoder_forward(const step_t &s, bool with_covar)
     return launch_reparam_fwd(r, s.st);
 }
 
-// decoder hidden layers + last layer (no bias: it is folded into K4/K5). Output "G" [B x D].
+// decoder hidden layers + last layer. Output "G" [B x D].  The last layer's bias is folded into K4 / K5 — unless the
+// caller hands one in (`last_bias`: K4's tuned kernel wants complete logits and, when the GEMM variant can, the softmax
+// partials of every row from its epilogue: row_stats / row_stats_tiles, see gemm_tc_args_t).
 int
-decoder_forward(const step_t &s)
+decoder_forward(const step_t &s, const float *last_bias = nullptr, void *row_stats = nullptr, int *row_stats_tiles = nullptr)
 {
     mmv_model *m = s.m;
     const int B = s.B, D = (int)m->D;
@@ -832,7 +836,8 @@ decoder_forward(const step_t &s)
     const linear_t &L = m->dec[nd - 1];
     float *G = WS("G", (size_t)B * D); NEED(G);
     // no bf16 twin of the logits: K4 / K5 read them in fp32 and overwrite the buffer with the gradient
-    return lin_fwd(s, h, L.in, m->P(L.w), nullptr, D, G, false, "gemm_dec_last_fwd", /*want_twin=*/false);
+    return lin_fwd(s, h, L.in, m->P(L.w), last_bias, D, G, false, "gemm_dec_last_fwd", /*want_twin=*/false, row_stats,
+                   row_stats_tiles);
 }
 
 // hand a finished gradient range to the comm stream (multi-GPU, optimiser step in this call)
@@ -1118,16 +1123,13 @@ nb_forward_backward(const step_t &s)
     MMV_TRY(launch_reparam_fwd(rn, s.st));
 
     trace_mark(m->ctx, "encoder forward done");
-    MMV_TRY(decoder_forward(s));
-    trace_mark(m->ctx, "decoder forward done");
 
+    // K4's arguments first: whether the tuned kernel runs decides what the decoder's last GEMM has to produce
     const linear_t &Ld = m->dec.back();
     float *abias = WS("abias", D), *ubias = WS("ubias", D); NEED(abias); NEED(ubias);
-    MMV_TRY(launch_vec_combine(m->P(Ld.b), m->P(m->covar_dec.b), m->P(m->t_mu_bias), 1.f, 1.f, abias, D, s.st));
-    MMV_TRY(launch_vec_combine(m->P(m->nu_dec.b), m->P(m->t_nu_bias), nullptr, -1.f, 0.f, ubias, D, s.st));
-
     nb_lik_args_t k;
-    k.G = m->ws["G"].as<float>(); k.abias = abias; k.Wcd = m->P(m->covar_dec.w); k.cov = s.cov;
+    k.G = WS("G", (size_t)B * D); NEED(k.G);
+    k.Wcd = m->P(m->covar_dec.w); k.cov = s.cov;
     k.indptr = s.csr->indptr; k.indices = s.csr->indices; k.vals = s.csr->vals; k.cells = s.cells;
     k.dpre = e.dpre; k.znu = rn.z; k.Wnd = m->P(m->nu_dec.w); k.ubias = ubias;
     k.B = B; k.D = D; k.C = C; k.Rnu = Rnu; k.inv_B = s.inv_B;
@@ -1143,8 +1145,29 @@ nb_forward_backward(const step_t &s)
     if (m->top_grad_bf16) {
         k.dlogits_bf16 = m->W("dG.bf", (size_t)B * D * 2); NEED(k.dlogits_bf16);
     } else if (s.bwd) {
-        k.dlogits = m->ws["G"].as<float>();   // in place: each row is staged in shared memory first
+        k.dlogits = const_cast<float *>(k.G);   // in place: each row is staged in shared memory first
     }
+    const bool fast = k.allow_fast && nb_likelihood_fast_eligible(k);
+    // tuned kernel: all-ones covariates, so covar_decoding.weight's row sums join the bias, and the bias joins the logits
+    MMV_TRY(launch_nb_gene_bias(m->P(Ld.b), m->P(m->covar_dec.b), m->P(m->t_mu_bias), fast ? k.Wcd : nullptr, C,
+                                m->P(m->nu_dec.b), m->P(m->t_nu_bias), abias, ubias, D, s.st));
+    if (fast) {
+        const int max_tiles = (D + 255) / 256;
+        void *stats = m->W("k4_tile_stats", sizeof(float) * 2 * (size_t)max_tiles * B); NEED(stats);
+        void *meta = m->W("k4_rowmeta", sizeof(float) * 4 * (size_t)B); NEED(meta);
+        int tiles = 0;
+        MMV_TRY(decoder_forward(s, abias, stats, &tiles));
+        {
+            PROF("nb_likelihood");
+            MMV_TRY(launch_nb_row_meta(k.G, tiles > 0 ? stats : nullptr, tiles, k.dpre, k.znu, B, D, meta, s.st));
+        }
+        k.rowmeta = meta;
+    } else {
+        MMV_TRY(decoder_forward(s));
+        k.abias = abias;
+    }
+    trace_mark(m->ctx, "decoder forward done");
+
     if (s.bwd) {
         k.ddpre = WS("ddpre", B); k.dznu = WS("dznu", (size_t)B * Rnu);
         k.col_du = WS("col_du", D); k.col_duz = WS("col_duz", (size_t)D * Rnu);

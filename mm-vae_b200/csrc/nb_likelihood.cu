@@ -239,7 +239,7 @@ nb_smem_bytes(int Ds, int rmax)
 int
 launch_nb_likelihood(const nb_lik_args_t &a, int num_sms, cudaStream_t stream)
 {
-    if (a.allow_fast && nb_likelihood_fast_eligible(a)) return launch_nb_likelihood_fast(a, num_sms, stream);
+    if (a.rowmeta != nullptr) return launch_nb_likelihood_fast(a, num_sms, stream);   // the caller prepared the tuned path
     MMV_CHECK(a.Rnu >= 1 && a.Rnu <= 8, "nb_likelihood: overdispersion latent dim %d not in [1,8]", a.Rnu);
     const int rmax = a.Rnu == 1 ? 1 : (a.Rnu <= 4 ? 4 : 8);
     const size_t budget = 200 * 1024;

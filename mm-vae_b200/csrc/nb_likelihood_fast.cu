@@ -1,22 +1,30 @@
 // K4, tuned path (default overdispersion latent Rnu = 1, all-ones covariate) — same math as
 // nb_likelihood.cu (nb.hh:433-460,511-531 + autograd), organised around what the ncu captures
-// under profiles/ showed (r01 step 1-3: stalls on cluster.sync's MEMBAR.GPU + L1 invalidate, on
-// serial global-load chains at the head of every row and on the recomputing patch pass):
+// under profiles/ showed.  Round 1 (r01 step 1-10): cluster.sync stalls, serial global-load chains,
+// a recomputing patch pass; then — with those gone — 1 390 instructions per warp and row at 48 %
+// issue utilisation, bound by the serial phases of a row: two reductions with a cluster hop each,
+// four CTA barriers, the softmax pass holding every logit in registers.  Round 2 (this file):
+//   * the softmax statistics are NOT computed here: the decoder-last GEMM adds the per-gene bias in
+//     its epilogue and leaves per-(row, 256-column tile) max / sum-of-exp2 partials (gemm_tc.cu),
+//     a tiny merge kernel turns them into (max, 1 / sum, depth, z_nu) per row (nb_row_meta).  K4 then
+//     needs ONE pass over a row and ONE cluster reduction (s = sum g p, d z_nu);
+//   * that reduction is software-pipelined: row i's hop travels while row i + 1 is swept, and row i's
+//     dL/dlogit is written after row i + 1's sweep (its p and g wait in shared memory) — no thread
+//     ever waits for a hop, and a row costs two CTA barriers;
 //   * a thread-block cluster owns whole rows, each CTA a fixed gene slice for the entire kernel:
-//     per-gene constants staged in shared memory once, per-gene column sums of the nu gradient
-//     in registers; two CTAs (of different clusters) share an SM so one computes while the other
-//     waits on a hop;
-//   * rows arrive through a double-buffered cp.async.bulk + mbarrier ring (row r+1 streams from
-//     HBM while row r is processed);
-//   * the two row reductions (softmax max/sum merged by the online-softmax identity; sum g p and
-//     d znu) cross the cluster with st.async into every peer's slot + a remote mbarrier
+//     per-gene constants staged in shared memory once, per-gene column sums of the nu gradient in
+//     registers; two CTAs (of different clusters) share an SM;
+//   * rows arrive through a three-deep cp.async.bulk + mbarrier ring (1.5 rows of lead time); the
+//     landing buffer is overwritten in place with p, so the ring is also the store of the deferred
+//     output pass;
+//   * the exchange crosses the cluster with st.async into every peer's slot + a remote mbarrier
 //     complete_tx — no cluster barrier, no memory fence, no L1 invalidate;
 //   * a pre-kernel bisects every cell's CSR run by gene slice, so the nonzero fix-up touches only
-//     its own entries; its indices/values are prefetched one row ahead;
-//   * g lives in shared memory: the nonzero loop overwrites the entries it corrects before the
-//     single coalesced dL/dlogit store (bf16x2 or float2 per thread) — no patch pass;
-//   * dense sweep is branch-free (padded slices), 7 MUFU per element, log1p polynomials on the
-//     FMA pipe; small integer counts use product forms of lgamma / digamma.
+//     its own entries; its indices/values are prefetched one row ahead; it overwrites g in shared
+//     memory before the single coalesced dL/dlogit store (bf16x2 or float2 per thread);
+//   * dense sweep on packed fp32 pairs, branch-free (padded slices), 5 MUFU per element (softmax ex2,
+//     ex2 + lg2 for softplus, ONE rcp for 1 / (1 + t) and 1 / (nu (m + nu)), lg2 for log1p(m / nu));
+//     log1p polynomials on the FMA pipe; small integer counts use product forms of lgamma / digamma.
 #include "common.cuh"
 #include "kernels.hh"
 #include "rowstream.cuh"
@@ -33,8 +41,6 @@ namespace {
 
 using namespace rowstream;
 
-constexpr int kT = 256;
-constexpr int NW = kT / 32;
 constexpr int NZP = 2;                                         // nonzeros prefetched per thread per row
 constexpr float kEps = 1e-4f, kNuMin = 1e-4f, kNuMax = 1e4f;   // nb.hh:514,252,459
 
@@ -52,19 +58,32 @@ struct elem_t {
     float m, nu, l1p, inv_mnu, sig_mask;
 };
 
-// Dense sweep of one adjacent gene pair assuming x = 0 (same formulas as elem_fast, two lanes per
-// FMA-pipe instruction).  v = softmax numerators, u = (zn wn + ub) log2(e).  Outputs: p (softmax),
-// g = dl/dm = nu / (m + nu), nl = nu log1p(m / nu), du = (log1p(m / nu) - m / (m + nu)) dnu/du
-// (NOT yet divided by B: the row / column sums are scaled once at the end).
+// Dense sweep outputs of one adjacent gene pair (x = 0): p (softmax), g = dl/dm = nu / (m + nu), nl = nu log1p(m / nu),
+// du = (log1p(m / nu) - m / (m + nu)) dnu/du (NOT yet divided by B: the row / column sums are scaled once at the end).
 struct pair_t {
     f2_t p, g, nl, du;
 };
 
+// rounding-error compensation of log1p(t) = log(w) + (t - (w - 1)) / w, w = fl(1 + t): the term only matters
+// for small t (it is <= 2^-24 absolute), where 1 / w = 1 - t to the accuracy that matters; beyond t = 1 it is dropped
+__device__ __forceinline__ f2_t
+softplus_comp(f2_t t, f2_t w)
+{
+    const f2_t one = bc2(1.f), neg1 = bc2(-1.f);
+    float t0, t1;
+    up2(t, t0, t1);
+    const f2_t rwa = fma2(pk2(fminf(t0, 1.f), fminf(t1, 1.f)), neg1, one);   // max(1 - t, 0)
+    return mul2(fma2(add2(w, neg1), neg1, t), rwa);
+}
+
+// Dense sweep of one adjacent gene pair assuming x = 0.  v = softmax numerators, u = (zn wn + ub) log2(e).
+// One reciprocal per element: q = 1 / (w nu (m + nu)) gives 1 / w = q nu (m + nu) (the sigmoid) and
+// 1 / (nu (m + nu)) = q w (range: w <= e^20 + 1, nu <= 1e4, m + nu <= depth + 1e4 — far inside fp32).
 // CLAMPS = false: the caller has shown that every u of the row lies inside (log(expm1(1e-4)), 20), so the
-// softplus threshold, the clamp of nb.hh:459 and its gradient mask cannot act (they cost ~15 of ~70 instructions).
+// softplus threshold, the clamp of nb.hh:459 and its gradient mask cannot act.
 template <bool CLAMPS>
 __device__ __forceinline__ pair_t
-pair_fast(f2_t v, f2_t scale, f2_t depth, f2_t u)
+pair_v4(f2_t v, f2_t scale, f2_t depth, f2_t u)
 {
     const f2_t one = bc2(1.f), neg1 = bc2(-1.f), ln2 = bc2(kLn2), eps = bc2(kEps);
     constexpr float c20 = 20.f * kLog2e;                              // softplus threshold 20 (nb.hh:458)
@@ -73,19 +92,15 @@ pair_fast(f2_t v, f2_t scale, f2_t depth, f2_t u)
     const f2_t m = fma2(o.p, depth, eps);                             // nb.hh:519
     float u0, u1;
     up2(u, u0, u1);
-    const float t0 = ex2_f(CLAMPS ? fminf(u0, c20) : u0), t1 = ex2_f(CLAMPS ? fminf(u1, c20) : u1);
-    const f2_t t = pk2(t0, t1);
+    const f2_t t = pk2(ex2_f(CLAMPS ? fminf(u0, c20) : u0), ex2_f(CLAMPS ? fminf(u1, c20) : u1));
     const f2_t w = add2(t, one);
     float w0, w1;
     up2(w, w0, w1);
-    const f2_t rw = pk2(rcp_f(w0), rcp_f(w1));
-    const f2_t lw = pk2(lg2_f(w0), lg2_f(w1));
-    // log1p(t) = log(w) + (t - (w - 1)) / w ; beyond the threshold softplus(u) = u = log1p(e^20) + (u - 20)
-    const f2_t comp = mul2(fma2(add2(w, neg1), neg1, t), rw);
-    f2_t sp = fma2(lw, ln2, comp);
-    f2_t nu, sigm;
-    const f2_t sig = mul2(t, rw);                                     // d softplus / du (-> 1 beyond the threshold)
+    f2_t sp = fma2(pk2(lg2_f(w0), lg2_f(w1)), ln2, softplus_comp(t, w));
+    f2_t nu;
+    bool in0 = true, in1 = true;
     if (CLAMPS) {
+        // beyond the threshold softplus(u) = u = log1p(e^20) + (u - 20)
         const f2_t over = add2(u, bc2(-c20));
         float v0, v1;
         up2(over, v0, v1);
@@ -94,19 +109,24 @@ pair_fast(f2_t v, f2_t scale, f2_t depth, f2_t u)
         up2(sp, s0, s1);
         const float r0 = fminf(fmaxf(s0, kNuMin), kNuMax), r1 = fminf(fmaxf(s1, kNuMin), kNuMax);   // nb.hh:459
         nu = add2(pk2(r0, r1), eps);                                  // nb.hh:518
-        float g0, g1;
-        up2(sig, g0, g1);
-        sigm = pk2(r0 == s0 ? g0 : 0.f, r1 == s1 ? g1 : 0.f);        // clamp passes the gradient inside [min, max]
+        in0 = r0 == s0; in1 = r1 == s1;                               // clamp passes the gradient inside [min, max]
     } else {
         nu = add2(sp, eps);
-        sigm = sig;
     }
     const f2_t mnu = add2(m, nu);
+    const f2_t nm = mul2(nu, mnu);
     float q0, q1;
-    up2(mul2(nu, mnu), q0, q1);
-    const f2_t q = pk2(rcp_f(q0), rcp_f(q1));                         // one MUFU for both reciprocals
-    const f2_t minv = mul2(m, mul2(q, nu));                           // m / (m + nu)
-    const f2_t y = mul2(m, mul2(q, mnu));                             // m / nu
+    up2(mul2(nm, w), q0, q1);
+    const f2_t q = pk2(rcp_f(q0), rcp_f(q1));                         // the element's only reciprocal
+    f2_t sig = mul2(t, mul2(q, nm));                                  // d softplus / du = t / w (-> 1 beyond the threshold)
+    if (CLAMPS) {
+        float g0, g1;
+        up2(sig, g0, g1);
+        sig = pk2(in0 ? g0 : 0.f, in1 ? g1 : 0.f);
+    }
+    const f2_t qn = mul2(q, w);                                       // 1 / (nu (m + nu))
+    const f2_t minv = mul2(m, mul2(qn, nu));                          // m / (m + nu)
+    const f2_t y = mul2(m, mul2(qn, mnu));                            // m / nu
     // log1p(y): Taylor polynomial below 1/16, MUFU lg2 above (see log1p_fast)
     const f2_t ny = mul2(y, neg1);
     f2_t poly = fma2(ny, bc2(0.2f), bc2(0.25f));
@@ -122,10 +142,9 @@ pair_fast(f2_t v, f2_t scale, f2_t depth, f2_t u)
     const f2_t l1p = pk2(y0 < 0.0625f ? p0 : b0, y1 < 0.0625f ? p1 : b1);
     o.g = fma2(minv, neg1, one);                                      // nu / (m + nu)
     o.nl = mul2(nu, l1p);
-    o.du = mul2(fma2(minv, neg1, l1p), sigm);
+    o.du = mul2(fma2(minv, neg1, l1p), sig);
     return o;
 }
-
 // u2 = u * log2(e): the per-gene nu weights are staged pre-scaled so that exp(u) is one ex2.
 // 6 MUFU: ex2, rcp(1 + t), lg2(1 + t), rcp(nu (m + nu)), lg2(1 + m / nu) (+ the softmax ex2 outside).
 __device__ __forceinline__ elem_t
@@ -236,11 +255,65 @@ slice_bounds_kernel(const int64_t *indptr, const int32_t *indices, const int32_t
     bounds[(size_t)row * (cs + 1) + c] = v;
 }
 
-template <int EPT>
-__global__ void __launch_bounds__(kT, 2)
+// ---------------------------------------------------------------------------
+// per-row metadata of the tuned kernel: (max of the logits in the log2 domain, 1 / sum of exp2, depth, z_nu)
+//   tile_stats != nullptr: merge the [n_tiles x B] partials the decoder-last GEMM's epilogue left
+//   tile_stats == nullptr: one pass over G (fp32 mode, or a GEMM variant without the statistics epilogue)
+// ---------------------------------------------------------------------------
+__global__ void
+nb_row_meta_merge_kernel(const float2 *tile_stats, int n_tiles, const float *dpre, const float *znu, int B, float4 *meta)
+{
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= B) return;
+    float gm = -INFINITY, gs = 0.f;
+    for (int t = 0; t < n_tiles; ++t) {          // coalesced over rows; online merge in the log2 domain
+        const float2 p = tile_stats[(size_t)t * B + row];
+        if (p.x > -INFINITY) {
+            const float nm = fmaxf(gm, p.x);
+            gs = gs * (gm > -INFINITY ? ex2_f(gm - nm) : 0.f) + p.y * ex2_f(p.x - nm);
+            gm = nm;
+        }
+    }
+    const float dp = dpre[row];
+    meta[row] = make_float4(gm, 1.f / gs, dp > 20.f ? dp : log1pf(expf(dp)), znu[row]);   // nb.hh:498 (exact, once per row)
+}
+
+__global__ void __launch_bounds__(256)
+nb_row_meta_scan_kernel(const float *G, int D, const float *dpre, const float *znu, float4 *meta)
+{
+    __shared__ float sm[8], ss[8];
+    const int row = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float4 *g4 = reinterpret_cast<const float4 *>(G + (size_t)row * D);   // D % 4 == 0, rows 16-byte aligned
+    float m = -INFINITY, s = 0.f;
+    for (int i = threadIdx.x; i < D / 4; i += 256) {
+        const float4 v = g4[i];
+        const float cm = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)) * kLog2e;
+        const float nm = fmaxf(m, cm);
+        s = s * (m > -INFINITY ? ex2_f(m - nm) : 0.f) + ex2_f(fmaf(v.x, kLog2e, -nm)) + ex2_f(fmaf(v.y, kLog2e, -nm)) +
+            ex2_f(fmaf(v.z, kLog2e, -nm)) + ex2_f(fmaf(v.w, kLog2e, -nm));
+        m = nm;
+    }
+    const float wm = warp_max(m);
+    const float wsum = warp_sum(m > -INFINITY ? s * ex2_f(m - wm) : 0.f);
+    if (lane == 0) { sm[warp] = wm; ss[warp] = wsum; }
+    __syncthreads();
+    if (warp == 0) {
+        const float bm = lane < 8 ? sm[lane] : -INFINITY;
+        const float gm = warp_max(bm);
+        const float gs = warp_sum(lane < 8 && bm > -INFINITY ? ss[lane] * ex2_f(bm - gm) : 0.f);
+        if (lane == 0) {
+            const float dp = dpre[row];
+            meta[row] = make_float4(gm, 1.f / gs, dp > 20.f ? dp : log1pf(expf(dp)), znu[row]);
+        }
+    }
+}
+
+template <int EPT, int T>
+__global__ void __launch_bounds__(T, 2)
 nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
 {
-    static_assert(EPT % 2 == 0, "threads own adjacent gene pairs");
+    static_assert(EPT % 2 == 0 && T % 32 == 0 && T <= 512, "threads own adjacent gene pairs");
+    constexpr int kT = T, NW = T / 32;
     constexpr int HP = EPT / 2;                  // pairs per thread
     constexpr int Dp = EPT * kT;                 // padded slice length (>= Ds)
     cg::cluster_group cluster = cg::this_cluster();
@@ -252,18 +325,17 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
     const bool sorted = a.unsorted != nullptr && *a.unsorted == 0;
 
     extern __shared__ __align__(16) float smem[];
-    float *sG0 = smem, *sG1 = sG0 + Dp;          // TMA landing buffers (raw decoder output)
-    float *s_ab = sG1 + Dp;                      // bias: mu_decoding.bias + covar_decoding.bias + mu_bias + sum_c Wcd
-    float *s_ub = s_ab + Dp;                     // nu_decoding.bias - nu_bias
-    float *s_wn = s_ub + Dp;                     // nu_decoding.weight[:, 0]
-    float *s_g = s_wn + Dp;                      // g = dl/dm of the current row (dense value, nonzeros overwritten)
-    float *wstat = s_g + Dp;                     // [2 parity][NW][4] per-warp partials of the two reductions
-    float *xslot = wstat + 2 * NW * 4;           // [2 parity][2 exchanges][8 ranks][2]
-    uint64_t *bars = reinterpret_cast<uint64_t *>(xslot + 64);   // [2] row ring + [2 parity][2 exchanges]
-    const uint32_t bar0 = smem_addr(bars), bar1 = bar0 + 8, xbar0 = bar0 + 16;
+    float *s_land = smem;                        // [3][Dp] TMA landing ring (complete logits); swept in place into p
+    float *s_gb = s_land + 3 * Dp;               // [2][Dp] g = dl/dm of a row (dense value, nonzeros overwritten), by row parity
+    float *s_ub = s_gb + 2 * Dp;                 // (nu_decoding.bias - nu_bias) log2(e)
+    float *s_wn = s_ub + Dp;                     // nu_decoding.weight[:, 0] log2(e)
+    float *wstat = s_wn + Dp;                    // [2 parity][NW][2] per-warp partials of the row reduction
+    float *xslot = wstat + 2 * NW * 2;           // [2 parity][8 ranks][2]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(xslot + 32);   // [3] landing ring + [2 parity] exchange
+    const uint32_t lbar0 = smem_addr(bars), xbar0 = lbar0 + 24;
 
     if (tid == 0) {
-        for (int i = 0; i < 6; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8 * i));
+        for (int i = 0; i < 5; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(lbar0 + 8 * i));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     // extremes of the slice's nu-decoder constants: a row whose u = zn wn + ub provably stays inside
@@ -271,34 +343,36 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
     float wlo = INFINITY, whi = -INFINITY, blo = INFINITY, bhi = -INFINITY;
     for (int jj = tid; jj < Dp; jj += kT) {
         const int j = j0 + jj;
-        // padding: logit -inf (softmax numerator 0), u -> -inf (nu clamped, gradient masked), weight 0
-        float ab = -INFINITY, ub = -1e30f, wn = 0.f;
+        // padding: logit -inf (softmax numerator 0: the landing buffers' tails are never written, neither by TMA nor by
+        // the sweep), u -> -inf (nu clamped, gradient masked), weight 0
+        float ub = -1e30f, wn = 0.f;
         if (jj < nj) {
-            ab = 0.f;
-            ab += a.abias[j];
-            for (int c = 0; c < a.C; ++c) ab += a.Wcd[(size_t)j * a.C + c];   // covariates are all ones on this path
             ub = a.ubias[j] * kLog2e;   // pre-scaled: u * log2(e) = zn * wn' + ub'
             wn = a.Wnd[j] * kLog2e;
             wlo = fminf(wlo, wn); whi = fmaxf(whi, wn);
             blo = fminf(blo, ub); bhi = fmaxf(bhi, ub);
         }
-        s_ab[jj] = ab;
         s_ub[jj] = ub;
         s_wn[jj] = wn;
-        if (jj >= nj) sG0[jj] = sG1[jj] = 0.f;   // the padding of the landing buffers is never written by TMA
+        if (jj >= nj) s_land[jj] = s_land[Dp + jj] = s_land[2 * Dp + jj] = -INFINITY;
     }
     wlo = -warp_max(-wlo); whi = warp_max(whi); blo = -warp_max(-blo); bhi = warp_max(bhi);
-    if (lane == 0) { wstat[warp * 4 + 0] = wlo; wstat[warp * 4 + 1] = whi; wstat[warp * 4 + 2] = blo; wstat[warp * 4 + 3] = bhi; }
+    float *ext = s_gb;                           // (scratch before the row loop starts)
+    if (lane == 0) { ext[warp * 4 + 0] = wlo; ext[warp * 4 + 1] = whi; ext[warp * 4 + 2] = blo; ext[warp * 4 + 3] = bhi; }
     if (cs > 1) cluster.sync(); else __syncthreads();   // barriers initialised cluster-wide before any remote signal
     for (int w8 = 0; w8 < NW; ++w8) {
-        wlo = fminf(wlo, wstat[w8 * 4 + 0]); whi = fmaxf(whi, wstat[w8 * 4 + 1]);
-        blo = fminf(blo, wstat[w8 * 4 + 2]); bhi = fmaxf(bhi, wstat[w8 * 4 + 3]);
+        wlo = fminf(wlo, ext[w8 * 4 + 0]); whi = fmaxf(whi, ext[w8 * 4 + 1]);
+        blo = fminf(blo, ext[w8 * 4 + 2]); bhi = fmaxf(bhi, ext[w8 * 4 + 3]);
     }
-    __syncthreads();                                     // wstat is reused by the row loop
+    __syncthreads();                                     // the scratch is the g buffer of row 0
 
     const uint32_t row_bytes = (uint32_t)nj * 4u;
-    int row = cluster_id;
-    if (tid == 0 && row < a.B && nj > 0) bulk_load(smem_addr(sG0), a.G + (size_t)row * D + j0, row_bytes, bar0);
+    const int row0 = cluster_id;
+    if (tid == 0 && nj > 0) {                            // rows 0 and 1 of this cluster
+        if (row0 < a.B) bulk_load(smem_addr(s_land), a.G + (size_t)row0 * D + j0, row_bytes, lbar0);
+        if (row0 + n_clusters < a.B)
+            bulk_load(smem_addr(s_land + Dp), a.G + (size_t)(row0 + n_clusters) * D + j0, row_bytes, lbar0 + 8);
+    }
 
     f2_t cdu[HP], cduz[HP];            // per-gene column sums of d nu-logit (x zn), un-normalised (1/B at the end)
 #pragma unroll
@@ -306,16 +380,17 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
     f2_t nll2 = 0ull;
     float nll_acc = 0.f;
 
-    // per-row metadata, one row ahead: scalars, the slice's CSR range, the first NZP nonzeros per thread
+    // per-row metadata, one row ahead: (max, 1 / sum, depth, zn), the slice's CSR range, the first NZP nonzeros per thread
+    const float4 *rowmeta = reinterpret_cast<const float4 *>(a.rowmeta);
     const int bstride = cs + 1;
-    float dp_n = 0.f, zn_n = 0.f;
+    float4 meta_n = make_float4(0.f, 0.f, 0.f, 0.f);
     int64_t qlo_n = 0, qhi_n = 0;
     int pj[NZP];
     float px[NZP];
-    if (row < a.B) {
-        dp_n = a.dpre[row]; zn_n = a.znu[row];
-        qlo_n = a.slice_bounds[(size_t)row * bstride + (sorted ? rank : 0)];
-        qhi_n = a.slice_bounds[(size_t)row * bstride + (sorted ? rank + 1 : cs)];
+    if (row0 < a.B) {
+        meta_n = rowmeta[row0];
+        qlo_n = a.slice_bounds[(size_t)row0 * bstride + (sorted ? rank : 0)];
+        qhi_n = a.slice_bounds[(size_t)row0 * bstride + (sorted ? rank + 1 : cs)];
 #pragma unroll
         for (int i = 0; i < NZP; ++i) {
             const int64_t q = qlo_n + tid + i * kT;
@@ -324,126 +399,123 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         }
     }
 
-    for (int it = 0; row < a.B; row += n_clusters, ++it) {
-        const int cur = it & 1;
-        const uint32_t ph = (uint32_t)(it >> 1) & 1u;
-        const float *sG = cur ? sG1 : sG0;
-        float *ws = wstat + cur * NW * 4;
-        float *xs = xslot + cur * 32;
-        const uint32_t xb = xbar0 + cur * 16;
-        const int next = row + n_clusters;
-        if (tid == 0 && next < a.B && nj > 0)   // stream the next row while this one is processed
-            bulk_load(smem_addr(cur ? sG0 : sG1), a.G + (size_t)next * D + j0, row_bytes, cur ? bar0 : bar1);
+    // the row whose dL/dlogit is still to be written (its p and g sit in shared memory, its hop is in flight)
+    int prev_row = -1, prev_slot = 0;
+    float prev_dp = 0.f, prev_coef = 0.f;
 
-        const float dp = dp_n, zn = zn_n;
-        const int64_t q_lo = qlo_n, q_hi = qhi_n;
-        const float depth = dp > 20.f ? dp : log1pf(expf(dp));       // nb.hh:498 (once per row: exact)
-        if (next < a.B) {                        // next row's scalars and CSR range (consumed next iteration)
-            dp_n = a.dpre[next]; zn_n = a.znu[next];
-            qlo_n = a.slice_bounds[(size_t)next * bstride + (sorted ? rank : 0)];
-            qhi_n = a.slice_bounds[(size_t)next * bstride + (sorted ? rank + 1 : cs)];
-        }
+    int slot = 0;                                        // it % 3
+    for (int it = 0;; ++it) {
+        const int row = row0 + it * n_clusters;
+        const bool active = row < a.B;
+        const int par = it & 1;
+        float *sL = s_land + slot * Dp;
+        float *sg = s_gb + par * Dp;
+        float *ws = wstat + par * NW * 2;
+        float zn = 0.f, depth = 0.f, gm2 = 0.f, invS = 0.f, coef = 0.f;
+        int64_t q_lo = 0, q_hi = 0;
+        f2_t red0 = 0ull, red1 = 0ull;     // s = sum g p ; d znu (un-normalised)
 
-        if (nj > 0) bar_wait(cur ? bar1 : bar0, ph);
-
-        // ---- pass 1: logits into registers; softmax numerators against the WARP max, so one
-        //      block hop + one cluster hop give max and sum together (online-softmax merge)
-        // (log2 domain: every shift is the SAME rounded number wherever it is used, so the merges are exact)
-        f2_t vp[HP];
-        float wm = -INFINITY;
-#pragma unroll
-        for (int h = 0; h < HP; ++h) {
-            vp[h] = 0ull;
-            // warp-uniform skip of a warp that sits wholly on the padding — only for the last two pair slots, where
-            // it can happen at the benchmark shapes: for the others the test folds away at compile time (on padding the
-            // constants make the element a no-op), and with it the predicated moves the compiler emitted around every
-            // slot to merge the skipped and the computed values (10 % of the kernel's instructions were MOVs)
-            if (h >= HP - 2 && h * 2 * kT + warp * 64 >= nj) continue;
-            const int jj = 2 * tid + h * 2 * kT;
-            vp[h] = add2(*reinterpret_cast<const f2_t *>(sG + jj), *reinterpret_cast<const f2_t *>(s_ab + jj));
-            float x0, x1;
-            up2(vp[h], x0, x1);
-            wm = fmaxf(wm, fmaxf(x0, x1));
-        }
-        wm = warp_max(wm);
-        const float cw = wm > -INFINITY ? wm * kLog2e : 0.f;
-        const f2_t l2e = bc2(kLog2e), ncw = bc2(-cw);
-        f2_t ws2 = 0ull;
-#pragma unroll
-        for (int h = 0; h < HP; ++h) {
-            if (h >= HP - 2 && h * 2 * kT + warp * 64 >= nj) continue;
-            float y0, y1;
-            up2(fma2(vp[h], l2e, ncw), y0, y1);
-            vp[h] = pk2(ex2_f(y0), ex2_f(y1));      // ex2(-inf) = 0 on the padding
-            ws2 = add2(ws2, vp[h]);
-        }
-        float wsum;
-        {
-            float s0, s1;
-            up2(ws2, s0, s1);
-            wsum = warp_sum(s0 + s1);
-        }
-        if (lane == 0) { ws[warp * 4 + 0] = wm > -INFINITY ? cw : -INFINITY; ws[warp * 4 + 1] = wsum; }
-        __syncthreads();
-        const float bm = lane < NW ? ws[lane * 4 + 0] : -INFINITY;
-        const float bs_in = lane < NW ? ws[lane * 4 + 1] : 0.f;
-        const float bmax = warp_max(bm);
-        const float bsum = warp_sum(bm > -INFINITY ? bs_in * ex2_f(bm - bmax) : 0.f);
-        float gmax = bmax, gsum = bsum;
-        if (cs > 1) {
-            if (tid == 0) xchg_send(smem_addr(xs + rank * 2), xb, cs, bmax, bsum);
-            bar_wait(xb, ph);
-            gmax = -INFINITY;
-            float rm[8], rs[8];
-#pragma unroll
-            for (int r = 0; r < 8; ++r) {
-                rm[r] = -INFINITY; rs[r] = 0.f;
-                if (r < cs) { rm[r] = xs[r * 2]; rs[r] = xs[r * 2 + 1]; }
-                gmax = fmaxf(gmax, rm[r]);
+        if (active) {
+            gm2 = meta_n.x; invS = meta_n.y; depth = meta_n.z; zn = meta_n.w;
+            q_lo = qlo_n; q_hi = qhi_n;
+            coef = depth * a.inv_B;
+            const int next = row + n_clusters;
+            if (next < a.B) {                        // next row's scalars and CSR range (consumed next iteration)
+                meta_n = rowmeta[next];
+                qlo_n = a.slice_bounds[(size_t)next * bstride + (sorted ? rank : 0)];
+                qhi_n = a.slice_bounds[(size_t)next * bstride + (sorted ? rank + 1 : cs)];
             }
-            gsum = 0.f;
-#pragma unroll
-            for (int r = 0; r < 8; ++r) gsum += rm[r] > -INFINITY ? rs[r] * ex2_f(rm[r] - gmax) : 0.f;
-        }
-        const float inv_sum = 1.f / gsum;
-        const float scale = wm > -INFINITY ? ex2_f(cw - gmax) * inv_sum : 0.f;
-        if (a.row_lse && rank == 0 && tid == 0) a.row_lse[row] = gmax * kLn2 + logf(gsum);
+            if (nj > 0) bar_wait(lbar0 + 8 * slot, (uint32_t)(it / 3) & 1u);
 
-        // ---- pass 2: dense sweep assuming x = 0 (lgammas cancel, no digamma).  Branch-free: the
-        //      out-of-range lanes compute on the padding and are masked at the accumulations.
-        float red[2] = { 0.f, 0.f };           // s = sum g p ; d znu (un-normalised)
-        f2_t red0 = 0ull, red1 = 0ull;
-        {
-            const f2_t scale2 = bc2(scale), depth2 = bc2(depth), zn2 = bc2(zn);
+            // ---- the sweep: softmax from the row statistics, dense NB terms assuming x = 0 (lgammas cancel, no
+            //      digamma).  Branch-free: lanes on the padding compute on the constants and are masked at the sums.
+            const f2_t l2e = bc2(kLog2e), ngm = bc2(-gm2), scale2 = bc2(invS), depth2 = bc2(depth), zn2 = bc2(zn);
             // u' = u log2(e) over the slice lies in [ulo, uhi] (interval arithmetic on zn wn' + ub')
             const float ulo = fminf(zn * wlo, zn * whi) + blo, uhi = fmaxf(zn * wlo, zn * whi) + bhi;
             const bool plain = ulo > -13.f && uhi < 28.5f;    // log2(e) * (-9.21, 20) = (-13.29, 28.85), with margin
             auto sweep = [&](auto clamps) {
 #pragma unroll
                 for (int h = 0; h < HP; ++h) {
+                    // warp-uniform skip of a warp that sits wholly on the padding (only the last two pair slots can:
+                    // the launcher picks the slice class so)
                     if (h >= HP - 2 && h * 2 * kT + warp * 64 >= nj) continue;
                     const int jj = 2 * tid + h * 2 * kT;
+                    float y0, y1;
+                    up2(fma2(*reinterpret_cast<const f2_t *>(sL + jj), l2e, ngm), y0, y1);
+                    const f2_t v = pk2(ex2_f(y0), ex2_f(y1));           // ex2(-inf) = 0 on the padding
                     const f2_t wn2 = *reinterpret_cast<const f2_t *>(s_wn + jj);
                     const f2_t ub2 = *reinterpret_cast<const f2_t *>(s_ub + jj);
-                    const pair_t e = pair_fast<decltype(clamps)::value>(vp[h], scale2, depth2, fma2(zn2, wn2, ub2));
-                    nll2 = fma2(e.nl, bc2(jj < nj ? 1.f : 0.f), nll2);
-                    vp[h] = e.p;
+                    const pair_t e = pair_v4<decltype(clamps)::value>(v, scale2, depth2, fma2(zn2, wn2, ub2));
+                    const bool valid = h < HP - 2 || jj < nj;
+                    nll2 = fma2(e.nl, bc2(valid ? 1.f : 0.f), nll2);
                     red0 = fma2(e.g, e.p, red0);
                     cdu[h] = add2(cdu[h], e.du);
                     cduz[h] = fma2(e.du, zn2, cduz[h]);
                     red1 = fma2(e.du, wn2, red1);
-                    *reinterpret_cast<f2_t *>(s_g + jj) = e.g;
+                    if (valid) *reinterpret_cast<f2_t *>(sL + jj) = e.p;   // the padding keeps its -inf
+                    *reinterpret_cast<f2_t *>(sg + jj) = e.g;
                 }
             };
             if (plain) sweep(std::false_type{}); else sweep(std::true_type{});
         }
-        __syncthreads();                       // s_g complete before the nonzero loop overwrites entries
 
-        // ---- pass 2b: this cell's nonzeros that fall in the slice (prefetched; overflow from global)
+        // ---- deferred output of the previous row: its hop left a whole sweep ago
+        if (prev_row >= 0 && grad) {
+            const int pp = par ^ 1;
+            const float *xs = xslot + pp * 16;
+            bar_wait(xbar0 + 8 * pp, (uint32_t)((it - 1) >> 1) & 1u);
+            float s = 0.f, dz = 0.f;
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+                if (r < cs) { s += xs[r * 2]; dz += xs[r * 2 + 1]; }
+            const float *sLp = s_land + prev_slot * Dp;
+            const float *sgp = s_gb + pp * Dp;
+            // dL/dlogit_j = (d_i / B) p_j (g_j - s_i), one coalesced store per pair
+            const f2_t ns2 = bc2(-s), coef2 = bc2(prev_coef);
+            if (a.dlogits_bf16) {
+                __nv_bfloat16 *orow = reinterpret_cast<__nv_bfloat16 *>(a.dlogits_bf16) + (size_t)prev_row * D + j0 + 2 * tid;
+#pragma unroll
+                for (int h = 0; h < HP; ++h) {
+                    const int jj = 2 * tid + h * 2 * kT;
+                    if (h >= HP - 2 && jj >= nj) continue;
+                    float o0, o1;
+                    up2(mul2(mul2(*reinterpret_cast<const f2_t *>(sLp + jj), coef2), add2(*reinterpret_cast<const f2_t *>(sgp + jj), ns2)), o0, o1);
+                    *reinterpret_cast<__nv_bfloat162 *>(orow + h * 2 * kT) = __floats2bfloat162_rn(o0, o1);
+                }
+            } else {
+                float *orow = a.dlogits + (size_t)prev_row * D + j0 + 2 * tid;
+#pragma unroll
+                for (int h = 0; h < HP; ++h) {
+                    const int jj = 2 * tid + h * 2 * kT;
+                    if (h >= HP - 2 && jj >= nj) continue;
+                    float o0, o1;
+                    up2(mul2(mul2(*reinterpret_cast<const f2_t *>(sLp + jj), coef2), add2(*reinterpret_cast<const f2_t *>(sgp + jj), ns2)), o0, o1);
+                    *reinterpret_cast<float2 *>(orow + h * 2 * kT) = make_float2(o0, o1);
+                }
+            }
+            if (rank == 0 && tid == 0) {
+                a.ddpre[prev_row] = s * a.inv_B * (prev_dp > 20.f ? 1.f : 1.f / (1.f + expf(-prev_dp)));
+                a.dznu[prev_row] = dz;
+            }
+        }
+        if (!active) break;
+
+        // (the sweep wrote the ring slot through the generic proxy; the TMA unit refills it later through the async one)
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();    // A: g / p of this row complete (the fix-up overwrites entries); every thread is done with the
+                            //    previous row's output, so its ring slot can take the row after next
+        if (tid == 0 && nj > 0) {
+            const int r2 = row + 2 * n_clusters;
+            const int s2 = slot == 0 ? 2 : slot - 1;     // (it + 2) % 3
+            if (r2 < a.B) bulk_load(smem_addr(s_land + s2 * Dp), a.G + (size_t)r2 * D + j0, row_bytes, lbar0 + 8 * s2);
+        }
+
+        // ---- this cell's nonzeros that fall in the slice (prefetched; overflow from global)
+        float red[2] = { 0.f, 0.f };
         auto fix = [&](int j, float x) {
             const int jj = j - j0;
             if (jj < 0 || jj >= nj || x == 0.f) return;
-            const float p = ex2_f(fmaf(sG[jj] + s_ab[jj], kLog2e, -gmax)) * inv_sum;
+            const float p = sL[jj];
             const float wn = s_wn[jj];
             const elem_t e = elem_fast(p, depth, fmaf(zn, wn, s_ub[jj]));
             const float L = __logf(e.m + e.nu);
@@ -453,7 +525,7 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
             if (grad) {
                 const float gx = (e.nu + x) * e.inv_mnu - x * rcp_f(e.m);
                 red[0] = fmaf(gx - e.nu * e.inv_mnu, p, red[0]);
-                s_g[jj] = gx;
+                sg[jj] = gx;
                 const float ddu = (dig_diff + x * e.inv_mnu) * e.sig_mask;   // dnu_x - dnu_0 (un-normalised)
                 atomicAdd(a.col_du + j, ddu * a.inv_B);
                 atomicAdd(a.col_duz + j, ddu * zn * a.inv_B);
@@ -464,7 +536,7 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         for (int i = 0; i < NZP; ++i)
             if (pj[i] >= 0) fix(pj[i], px[i]);
         for (int64_t q = q_lo + tid + NZP * kT; q < q_hi; q += kT) fix(a.indices[q], a.vals[q]);
-        if (next < a.B) {                      // prefetch the next row's nonzeros (its range arrived long ago)
+        if (row + n_clusters < a.B) {          // prefetch the next row's nonzeros (its range arrived long ago)
 #pragma unroll
             for (int i = 0; i < NZP; ++i) {
                 const int64_t q = qlo_n + tid + i * kT;
@@ -474,7 +546,7 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         }
 
         if (grad) {
-            // ---- second reduction: s = sum g p, d znu
+            // ---- the row reduction: s = sum g p, d znu; warp 0 finishes it and sends the hop, nobody waits
             {
                 float a0, a1, b0, b1;
                 up2(red0, a0, a1);
@@ -482,47 +554,33 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
                 red[0] = warp_sum(red[0] + a0 + a1);
                 red[1] = warp_sum(red[1] + b0 + b1);
             }
-            if (lane == 0) { ws[warp * 4 + 2] = red[0]; ws[warp * 4 + 3] = red[1]; }
-            __syncthreads();                   // also: every s_g fix is visible
-            float s = warp_sum(lane < NW ? ws[lane * 4 + 2] : 0.f);
-            // red[1] was accumulated against wn * log2(e) and without the 1 / B
-            float dz = warp_sum(lane < NW ? ws[lane * 4 + 3] : 0.f) * (kLn2 * a.inv_B);
-            if (cs > 1) {
-                if (tid == 0) xchg_send(smem_addr(xs + 16 + rank * 2), xb + 8, cs, s, dz);
-                bar_wait(xb + 8, ph);
-                s = 0.f; dz = 0.f;
+            if (lane == 0) { ws[warp * 2 + 0] = red[0]; ws[warp * 2 + 1] = red[1]; }
+            __syncthreads();                   // B: partials in; every fix of g is visible to the output pass
+            if (warp == 0) {
+                float s = lane < NW ? ws[lane * 2 + 0] : 0.f, dz = lane < NW ? ws[lane * 2 + 1] : 0.f;
 #pragma unroll
-                for (int r = 0; r < 8; ++r)
-                    if (r < cs) { s += xs[16 + r * 2]; dz += xs[16 + r * 2 + 1]; }
-            }
-            const float coef = depth * a.inv_B;
-            // ---- pass 3: dL/dlogit_j = (d_i / B) p_j (g_j - s_i), one coalesced store per pair
-            const f2_t coef2 = bc2(coef), ns2 = bc2(-s);
-            if (a.dlogits_bf16) {
-                __nv_bfloat16 *orow = reinterpret_cast<__nv_bfloat16 *>(a.dlogits_bf16) + (size_t)row * D + j0 + 2 * tid;
-#pragma unroll
-                for (int h = 0; h < HP; ++h) {
-                    const int jj = 2 * tid + h * 2 * kT;
-                    float o0, o1;
-                    up2(mul2(mul2(vp[h], coef2), add2(*reinterpret_cast<const f2_t *>(s_g + jj), ns2)), o0, o1);
-                    if (jj < nj) *reinterpret_cast<__nv_bfloat162 *>(orow + h * 2 * kT) = __floats2bfloat162_rn(o0, o1);
+                for (int o = 16; o > 0; o >>= 1) {
+                    s += __shfl_xor_sync(0xffffffffu, s, o);
+                    dz += __shfl_xor_sync(0xffffffffu, dz, o);
                 }
-            } else {
-                float *orow = a.dlogits + (size_t)row * D + j0 + 2 * tid;
-#pragma unroll
-                for (int h = 0; h < HP; ++h) {
-                    const int jj = 2 * tid + h * 2 * kT;
-                    float o0, o1;
-                    up2(mul2(mul2(vp[h], coef2), add2(*reinterpret_cast<const f2_t *>(s_g + jj), ns2)), o0, o1);
-                    if (jj < nj) *reinterpret_cast<float2 *>(orow + h * 2 * kT) = make_float2(o0, o1);
+                // red[1] was accumulated against wn * log2(e) and without the 1 / B
+                dz *= kLn2 * a.inv_B;
+                if (lane == 0) {
+                    const uint32_t xb = xbar0 + 8 * par;
+                    if (cs > 1) {
+                        xchg_send(smem_addr(xslot + par * 16 + rank * 2), xb, cs, s, dz);
+                    } else {
+                        xslot[par * 16 + 0] = s; xslot[par * 16 + 1] = dz;
+                        asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"(xb) : "memory");
+                    }
                 }
             }
-            if (rank == 0 && tid == 0) {
-                a.ddpre[row] = s * a.inv_B * (dp > 20.f ? 1.f : 1.f / (1.f + expf(-dp)));
-                a.dznu[row] = dz;
-            }
+        } else {
+            __syncthreads();
         }
-        __syncthreads();       // everyone is done with sG[cur] / s_g before the TMA unit and the next row refill them
+        prev_row = row; prev_slot = slot; prev_dp = a.dpre[row]; prev_coef = coef;
+        slot = slot == 2 ? 0 : slot + 1;
+        if (a.row_lse && rank == 0 && tid == 0) a.row_lse[row] = gm2 * kLn2 - logf(invS);
     }
 
     {
@@ -550,15 +608,46 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
 }
 
 size_t
-fast_smem_bytes(int ept)
+fast_smem_bytes(int ept, int T)
 {
-    return sizeof(float) * ((size_t)6 * ept * kT + 2 * NW * 4 + 64) + 6 * 8 + 16;
+    return sizeof(float) * ((size_t)7 * ept * T + 2 * (T / 32) * 2 + 32) + 5 * 8 + 16;
 }
 
-int
-ept_class(int ept)
+// One instantiation of the tuned kernel and the slice layout it gives D genes.  The kernel checks the padding only in
+// the last two pair slots of a thread, so the shortest slice (the last rank's) must reach into them.
+// Measured at cfg 4 (D = 30 000, 8 CTAs of 3 752 genes): <16, 256> 0.50 ms, <10, 384> 0.62 ms, <8, 512> 0.80 ms (the
+// last two spill) — fewer, fatter threads win, as in round 1.
+struct k4_variant_t {
+    int ept, T;
+    void (*kern)(nb_lik_args_t, int, int);
+};
+const k4_variant_t kVariants[] = {
+    { 4, 256, nb_likelihood_fast_kernel<4, 256> },   { 8, 256, nb_likelihood_fast_kernel<8, 256> },
+    { 12, 256, nb_likelihood_fast_kernel<12, 256> }, { 16, 256, nb_likelihood_fast_kernel<16, 256> },
+};
+
+bool
+variant_fits(const k4_variant_t &v, int D, int &cs, int &Ds)
 {
-    return ept <= 4 ? 4 : ept <= 8 ? 8 : ept <= 12 ? 12 : 16;
+    const size_t budget = 113 * 1024;   // two CTAs per SM
+    if (fast_smem_bytes(v.ept, v.T) > budget) return false;
+    for (cs = 1; cs <= 8; cs *= 2) {
+        Ds = ((D + cs - 1) / cs + 3) & ~3;
+        if (Ds > v.ept * v.T) continue;
+        const int nj_last = D - (cs - 1) * Ds;
+        if (nj_last <= 0) return false;
+        if (v.ept > 4 && nj_last <= (v.ept / 2 - 2) * 2 * v.T) return false;   // a larger class (more padding) has to take it
+        return true;
+    }
+    return false;
+}
+
+const k4_variant_t *
+fast_layout(int D, int &cs, int &Ds)
+{
+    for (const k4_variant_t &v : kVariants)
+        if (variant_fits(v, D, cs, Ds)) return &v;
+    return nullptr;
 }
 
 } // namespace
@@ -573,33 +662,46 @@ launch_slice_bounds(const int64_t *indptr, const int32_t *indices, const int32_t
     return 0;
 }
 
+int
+launch_nb_row_meta(const float *G, const void *tile_stats, int n_tiles, const float *dpre, const float *znu, int B, int D,
+                   void *meta, cudaStream_t stream)
+{
+    if (tile_stats)
+        nb_row_meta_merge_kernel<<<ceil_div(B, 128), 128, 0, stream>>>(reinterpret_cast<const float2 *>(tile_stats), n_tiles, dpre,
+                                                                      znu, B, reinterpret_cast<float4 *>(meta));
+    else
+        nb_row_meta_scan_kernel<<<B, 256, 0, stream>>>(G, D, dpre, znu, reinterpret_cast<float4 *>(meta));
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// the tuned kernel reads COMPLETE logits (the caller had the per-gene bias added by the producing GEMM) and the
+// per-row metadata of launch_nb_row_meta
 bool
 nb_likelihood_fast_eligible(const nb_lik_args_t &a)
 {
-    return a.Rnu == 1 && a.cov == nullptr && a.D % 4 == 0 && a.D <= 8 * 16 * kT - 32 && a.recon_mu == nullptr &&
-        a.recon_nu == nullptr && a.slice_bounds != nullptr && (reinterpret_cast<uintptr_t>(a.G) & 15) == 0 &&
-        (a.dlogits == nullptr || (reinterpret_cast<uintptr_t>(a.dlogits) & 7) == 0);
+    int cs, Ds;
+    return a.Rnu == 1 && a.cov == nullptr && a.D % 4 == 0 && a.recon_mu == nullptr && a.recon_nu == nullptr &&
+        a.slice_bounds != nullptr && (reinterpret_cast<uintptr_t>(a.G) & 15) == 0 &&
+        (a.dlogits == nullptr || (reinterpret_cast<uintptr_t>(a.dlogits) & 7) == 0) && fast_layout(a.D, cs, Ds) != nullptr;
 }
 
 int
 launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stream)
 {
-    const size_t budget = 110 * 1024;   // two CTAs per SM
-    int cs = 1, Ds = 0, ept = 0;
-    for (;; cs *= 2) {
-        Ds = ((a.D + cs - 1) / cs + 3) & ~3;
-        ept = (Ds + kT - 1) / kT;
-        if (ept <= 16 && fast_smem_bytes(ept_class(ept)) <= budget) break;
-        MMV_CHECK(cs < 8, "nb_likelihood: D=%d does not fit a cluster of 8 CTAs", a.D);
-    }
+    MMV_CHECK(a.rowmeta != nullptr && a.abias == nullptr,
+              "nb_likelihood (tuned): needs the row metadata and logits with the bias already added");
+    int cs = 1, Ds = 0;
+    const k4_variant_t *v = fast_layout(a.D, cs, Ds);
+    MMV_CHECK(v != nullptr, "nb_likelihood: D=%d does not fit a cluster of 8 CTAs", a.D);
     MMV_TRY(launch_slice_bounds(a.indptr, a.indices, a.cells, a.unsorted, a.B, cs, Ds, a.slice_bounds, stream));
-    void (*kern)(nb_lik_args_t, int, int) = ept <= 4 ? nb_likelihood_fast_kernel<4>
-        : ept <= 8 ? nb_likelihood_fast_kernel<8> : ept <= 12 ? nb_likelihood_fast_kernel<12> : nb_likelihood_fast_kernel<16>;
-    const size_t smem = fast_smem_bytes(ept_class(ept));
+    void (*kern)(nb_lik_args_t, int, int) = v->kern;
+    const size_t smem = fast_smem_bytes(v->ept, v->T);
     MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(kern), (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(num_sms / cs * cs);
-    cfg.blockDim = dim3(kT);
+    cfg.blockDim = dim3(v->T);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];

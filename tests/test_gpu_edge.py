@@ -76,7 +76,7 @@ def make_model(mmv, ctx, model, D, enc, dec, R, dtype, rng):
 _ORACLE_CACHE = {}
 
 
-def check_vs_oracle(mmv, m, model, csr, x, cells, eps, tol, klw=0.8, cache_key=None):
+def check_vs_oracle(mmv, m, model, csr, x, cells, eps, tol, klw=0.8, cache_key=None, fp64_referee=False):
     terms = m.step(csr, cells, eps=eps, kl_weight=klw, flags=mmv.FWD | mmv.BWD)
     if cache_key is not None and cache_key in _ORACLE_CACHE:       # same seeded parameters / inputs: one oracle run
         ref, grads = _ORACLE_CACHE[cache_key]
@@ -100,6 +100,22 @@ def check_vs_oracle(mmv, m, model, csr, x, cells, eps, tol, klw=0.8, cache_key=N
     if model == "vmf":
         worst.pop("ln_kappa", None)      # O(D) cancellation in the reference's own fp32 value: pinned in test_gpu_parity
     bad = {k: v for k, v in worst.items() if v >= tol}
+    if bad and fp64_referee:
+        # At B x D x K = 4096 x 30 000 x 2048 the reference's OWN fp32 gradients carry summation noise of the order of the
+        # tolerance (two fp32 implementations that order their sums differently cannot agree better than either agrees
+        # with the exact value).  Referee: the same step in fp64 — a tensor passes when this library is as close to the
+        # fp64 value as the tolerance, or at least as close as twice the reference's own fp32 deviation from it.
+        P64 = {k: v.double() for k, v in oracle_params(m).items()}
+        c = np.ones((len(cells), 1))
+        _, _, g64 = mo.run_step("nb" if model.startswith("nb") else "vmf", P64, torch.from_numpy(x[cells]).double(), torch.from_numpy(c),
+                                [torch.from_numpy(e).double() for e in eps], klw)
+        still = {}
+        for k in bad:
+            ours, ref32 = rel_err(m.get_grad(k), g64[k].numpy()), rel_err(grads[k].numpy(), g64[k].numpy())
+            print(f"fp64 referee {k}: ours vs fp64 {ours:.2e}, reference fp32 vs fp64 {ref32:.2e}, ours vs reference fp32 {bad[k]:.2e}")
+            if ours >= max(tol, 2 * ref32):
+                still[k] = (bad[k], ours, ref32)
+        bad = still
     assert not bad, bad
     return terms, worst
 
@@ -266,7 +282,8 @@ def test_full_size_vmf_cfg5_vs_oracle(mmv, ctx, full_batch, dtype):
     csr = mmv.CSR.from_dense(ctx, x)
     m, neps = make_model(mmv, ctx, "vmf", D, CFG5["enc"], CFG5["dec"], CFG5["R"], dtype, rng)
     eps = [rng.normal(size=(B, n)).astype(np.float32) for n in neps]
-    terms, worst = check_vs_oracle(mmv, m, "vmf", csr, x, np.arange(B), eps, tol, klw=1.0, cache_key="cfg5")
+    terms, worst = check_vs_oracle(mmv, m, "vmf", csr, x, np.arange(B), eps, tol, klw=1.0, cache_key="cfg5",
+                                   fp64_referee=(dtype == "f32"))
     print(dtype, "loss", terms["loss"], {k: f"{v:.1e}" for k, v in sorted(worst.items(), key=lambda kv: -kv[1])[:4]})
     m.close()
     csr.close()
