@@ -195,6 +195,22 @@ MMV_API int mmv_encode(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t
 MMV_API int mmv_test_gemm(mmv_ctx *ctx, int use_tc, int M, int N, int K, int a_mn, int b_mn, const float *A,
                   const float *B, const float *bias, float beta, int relu, float *C);
 
+/* ---- the same tensor-core GEMM for callers that cannot allocate device memory ------
+ * No counterpart in the reference: added (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  C[M x N] = op(A) op(B) (+ bias) (+ beta C) (ReLU) on the
+ * bf16 tcgen05 path, as mmv_test_gemm(use_tc = 1), but d_A / d_B / d_bias / d_C are DEVICE pointers owned by the
+ * caller and the bf16 operand copies go to a static __device__ array of MMV_NOALLOC_SCRATCH_BYTES inside the library
+ * (held by every GPU that loads it): the call makes no cudaMalloc / cudaFree / allocating library call and copies
+ * nothing from or to the host.  Limit: round_up(2 M K, 256) + 2 N K <= MMV_NOALLOC_SCRATCH_BYTES, else an error.
+ * Leading dimensions (K, or M / N for MN-major operands) must be multiples of 8, the pointers 16-byte aligned.
+ * The launch is asynchronous on the context's stream (mmv_ctx_sync waits for it).  All calls on one GPU share the
+ * scratch and it keeps the last call's contents (every call overwrites what it reads; nothing must start at zero):
+ * calls that overlap on the GPU — two contexts or streams on one device — race and must be serialised by the caller.
+ * The first call on a device also does the one-time set-up (scratch address, kernel attributes). */
+#define MMV_NOALLOC_SCRATCH_BYTES (4 << 20)
+MMV_API int mmv_gemm_bf16_noalloc(mmv_ctx *ctx, int M, int N, int K, int a_mn, int b_mn, const float *d_A,
+                  const float *d_B, const float *d_bias, float beta, int relu, float *d_C);
+
 /* ---- data-parallel gradient exchange (no reference counterpart) ----
  * One rank per GPU: separate processes (bench.py under torchrun) or the host threads of one process
  * (nb_vae / vmf_vae --ngpu G), each with its own mmv_ctx.  Rank 0 creates the id, the host program hands

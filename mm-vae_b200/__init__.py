@@ -89,6 +89,7 @@ _PROTOS = {
     "mmv_get_output": [_vp, C.c_char_p, _vp, _i64],
     "mmv_encode": [_vp, _vp, _vp, _i64, _vp, _vp],
     "mmv_test_gemm": [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, C.c_float, C.c_int, _vp],
+    "mmv_gemm_bf16_noalloc": [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, C.c_float, C.c_int, _vp],
     "mmv_comm_unique_id": [_vp],
     "mmv_comm_init": [_vp, C.c_int, C.c_int, _vp],
     "mmv_comm_destroy": [_vp],
@@ -164,6 +165,15 @@ def test_gemm(ctx, A, B, a_mn=False, b_mn=False, bias=None, beta=0.0, relu=False
     _chk(lib.mmv_test_gemm(ctx.h, int(use_tc), M, N, K, int(a_mn), int(b_mn), _ptr(A), _ptr(B), _ptr(bias),
                            float(beta), int(relu), _ptr(out)))
     return out
+
+
+NOALLOC_SCRATCH_BYTES = 4 << 20
+
+
+def gemm_bf16_noalloc(ctx, M, N, K, d_A, d_B, d_C, a_mn=False, b_mn=False, d_bias=0, beta=0.0, relu=False):
+    """mmv_gemm_bf16_noalloc: raw DEVICE pointers (e.g. torch tensor .data_ptr()); asynchronous on ctx's stream."""
+    _chk(lib.mmv_gemm_bf16_noalloc(ctx.h, M, N, K, int(a_mn), int(b_mn), C.c_void_p(d_A), C.c_void_p(d_B),
+                                   C.c_void_p(d_bias) if d_bias else None, float(beta), int(relu), C.c_void_p(d_C)))
 
 
 def device_count() -> int:
