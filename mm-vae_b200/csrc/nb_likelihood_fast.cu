@@ -11,6 +11,8 @@
 //   * that reduction is software-pipelined: row i's hop travels while row i + 1 is swept, and row i's
 //     dL/dlogit is written after row i + 1's sweep (its p and g wait in shared memory) — no thread
 //     ever waits for a hop, and a row costs two CTA barriers;
+//     (tried and measured slower: no CTA barrier at all — mbarrier arrive / wait + "last warp sends" 0.58 ms; the
+//     output pass moved to the end of the iteration for a full iteration of slack on the hop, 0.75 ms);
 //   * a thread-block cluster owns whole rows, each CTA a fixed gene slice for the entire kernel:
 //     per-gene constants staged in shared memory once, per-gene column sums of the nu gradient in
 //     registers; two CTAs (of different clusters) share an SM;
@@ -555,8 +557,16 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
                 red[1] = warp_sum(red[1] + b0 + b1);
             }
             if (lane == 0) { ws[warp * 2 + 0] = red[0]; ws[warp * 2 + 1] = red[1]; }
-            __syncthreads();                   // B: partials in; every fix of g is visible to the output pass
-            if (warp == 0) {
+            // B: partials in.  Only warp 0 (which adds them up and sends the hop) blocks; the others arrive and go on to
+            // the next row.  (Hardware barriers on purpose: warps spinning on an mbarrier inside the CTA take issue slots
+            // from the CTA that shares the SM — measured, 0.52 -> 0.58 ms with mbarrier arrive / wait in their place;
+            // this arrive / sync split: 0.527 -> 0.520 ms, profiles/r02_step3_k4_ab.txt.)
+            // The output pass sees every fix of g through the hop: our share of it leaves after this barrier completes.
+            if (warp != 0) {
+                __syncwarp();
+                asm volatile("bar.arrive 1, %0;" ::"r"(kT) : "memory");
+            } else {
+                asm volatile("bar.sync 1, %0;" ::"r"(kT) : "memory");
                 float s = lane < NW ? ws[lane * 2 + 0] : 0.f, dz = lane < NW ? ws[lane * 2 + 1] : 0.f;
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) {
