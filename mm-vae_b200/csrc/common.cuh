@@ -92,6 +92,27 @@ digamma_f(float x)
     return acc + logf(x) - 0.5f * r - s;
 }
 
+// counter-based N(0,1) of the library's own reparameterisation noise (MMV_EPS_PHILOX): element i of draw `step` under
+// `seed` — splitmix64 finaliser, Box-Muller.  Any element is reproducible on its own, so the kernel that consumes the
+// noise can draw it in place.
+__device__ __forceinline__ uint32_t
+mix32(uint64_t z)
+{
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z = z ^ (z >> 31);
+    return (uint32_t)(z >> 16);
+}
+
+__device__ __forceinline__ float
+normal_draw(uint64_t seed, uint64_t step, uint64_t i)
+{
+    const uint64_t key = seed * 0x9E3779B97F4A7C15ull + step * 0xD1B54A32D192ED03ull + i * 2;
+    const float u1 = ((float)mix32(key) + 1.f) * (1.f / 4294967808.f);          // (0, 1)
+    const float u2 = (float)mix32(key + 1) * (1.f / 4294967296.f);
+    return sqrtf(-2.f * logf(u1)) * cospif(2.f * u2);                            // Box-Muller
+}
+
 // ---------------------------------------------------------------------------
 // warp / block reductions
 // ---------------------------------------------------------------------------

@@ -43,11 +43,39 @@ nb_gene_bias_kernel(const float *blast, const float *bcd, const float *mu_bias, 
     ubias[j] = bnd[j] - nu_bias[j];
 }
 
+// the step's per-gene prologue in ONE launch: gene_prep (inv_t) + nb_gene_bias (abias, ubias)
+__global__ void
+nb_gene_prologue_kernel(const float *ln_x_sd, float eps, float *inv_t, const float *blast, const float *bcd,
+                        const float *mu_bias, const float *Wcd, int C, const float *bnd, const float *nu_bias, float *abias,
+                        float *ubias, int D)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= D) return;
+    inv_t[j] = 1.f / (softplus_f(ln_x_sd[j]) + eps);
+    float ab = (blast ? blast[j] : 0.f) + bcd[j] + mu_bias[j];
+    if (Wcd)
+        for (int c = 0; c < C; ++c) ab += Wcd[(size_t)j * C + c];
+    abias[j] = ab;
+    ubias[j] = bnd[j] - nu_bias[j];
+}
+
 int
 launch_nb_gene_bias(const float *blast, const float *bcd, const float *mu_bias, const float *Wcd, int C, const float *bnd,
                     const float *nu_bias, float *abias, float *ubias, int D, cudaStream_t st)
 {
     nb_gene_bias_kernel<<<ceil_div(D, 256), 256, 0, st>>>(blast, bcd, mu_bias, Wcd, C, bnd, nu_bias, abias, ubias, D);
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int
+launch_nb_gene_prologue(const float *ln_x_sd, float eps, float *inv_t, const float *blast, const float *bcd,
+                        const float *mu_bias, const float *Wcd, int C, const float *bnd, const float *nu_bias, float *abias,
+                        float *ubias, int D, cudaStream_t st)
+{
+    nb_gene_prologue_kernel<<<ceil_div(D, 256), 256, 0, st>>>(ln_x_sd, eps, inv_t, blast, bcd, mu_bias, Wcd, C, bnd, nu_bias,
+                                                             abias, ubias, D);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
@@ -91,10 +119,15 @@ reparam_fwd_kernel(reparam_args_t a)
         const float lv = fminf(fmaxf(raw, -4.f), 4.f);
         const float ev = expf(lv);
         float z = mean;
-        if (a.eps) z = fmaf(a.eps[idx], expf(0.5f * lv), mean);   // nb.hh:466-468
+        if (a.eps_gen) {
+            const float e = normal_draw(a.gen_key, a.gen_step, a.gen_off + (uint64_t)idx);
+            a.eps_gen[idx] = e;
+            z = fmaf(e, expf(0.5f * lv), mean);
+        } else if (a.eps) z = fmaf(a.eps[idx], expf(0.5f * lv), mean);   // nb.hh:466-468
         a.mean[idx] = mean;
         a.lnvar[idx] = lv;
         a.z[idx] = z;
+        if (a.z_bf16) reinterpret_cast<__nv_bfloat16 *>(a.z_bf16)[idx] = __float2bfloat16(z);
         kl += 1.f + lv - mean * mean - ev;                        // nb.hh:536
     }
     __shared__ float scratch[32];
@@ -120,7 +153,136 @@ reparam_bwd_kernel(reparam_args_t a)
         if (!(raw >= -4.f && raw <= 4.f)) dlv = 0.f;              // clamp backward (inclusive)
         a.dhead[(size_t)i * 2 * R + r] = dmean;
         a.dhead[(size_t)i * 2 * R + R + r] = dlv;
+        if (a.dhead_bf16) {
+            reinterpret_cast<__nv_bfloat16 *>(a.dhead_bf16)[(size_t)i * 2 * R + r] = __float2bfloat16(dmean);
+            reinterpret_cast<__nv_bfloat16 *>(a.dhead_bf16)[(size_t)i * 2 * R + R + r] = __float2bfloat16(dlv);
+        }
     }
+}
+
+// ------------------------------------------------- nu heads: Linear(H -> 2 Rnu) fused with reparam
+// The over-dispersion encoder's heads are a [2 Rnu x H] product per cell (default H = Rnu = 1: two multiplies).  One
+// launch forward (heads + clamp + reparam + KL, nb.hh:444-451,466-468,536) and one backward (reparam backward, the
+// heads' dW / db, dHnu = dhead W and its column sums = nu_encoding.bias' gradient, sum of d depth_pre = depth.bias'
+// gradient) replace two FFMA GEMMs, two reparam launches and three column-sum launches.
+template <int H, int RN>
+__global__ void
+nu_head_fwd_kernel(nu_head_args_t a)
+{
+    const int n = a.B * RN;
+    float kl = 0.f;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
+        const int i = idx / RN, r = idx % RN;
+        float mean = a.b[r], raw = a.b[RN + r];
+#pragma unroll
+        for (int h = 0; h < H; ++h) {
+            const float x = a.Hnu[(size_t)i * H + h];
+            mean = fmaf(x, a.W[r * H + h], mean);
+            raw = fmaf(x, a.W[(RN + r) * H + h], raw);
+        }
+        a.head[(size_t)i * 2 * RN + r] = mean;
+        a.head[(size_t)i * 2 * RN + RN + r] = raw;
+        const float lv = fminf(fmaxf(raw, -4.f), 4.f);
+        const float ev = expf(lv);
+        float z = mean;
+        if (a.eps_gen) {
+            const float e = normal_draw(a.gen_key, a.gen_step, a.gen_off + (uint64_t)idx);
+            a.eps_gen[idx] = e;
+            z = fmaf(e, expf(0.5f * lv), mean);
+        } else if (a.eps) z = fmaf(a.eps[idx], expf(0.5f * lv), mean);
+        a.mean[idx] = mean;
+        a.lnvar[idx] = lv;
+        a.z[idx] = z;
+        kl += 1.f + lv - mean * mean - ev;
+    }
+    __shared__ float scratch[32];
+    float k1[1] = { kl };
+    block_sum<1>(k1, scratch);
+    if (threadIdx.x == 0 && a.kl_acc) atomicAdd(a.kl_acc, (double)(-0.5f * k1[0]));
+}
+
+template <int H, int RN>
+__global__ void
+nu_head_bwd_kernel(nu_head_args_t a)
+{
+    constexpr int O = 2 * RN;
+    constexpr int Q = O * H + O + H + 1;          // dW | db | d nu_encoding.bias | d depth.bias
+    float acc[Q];
+#pragma unroll
+    for (int q = 0; q < Q; ++q) acc[q] = 0.f;
+    const float wB = a.kl_weight * a.inv_B;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.B; i += gridDim.x * blockDim.x) {
+        float dh[O];
+#pragma unroll
+        for (int r = 0; r < RN; ++r) {
+            const int idx = i * RN + r;
+            const float dz = a.dz[idx];
+            const float mean = a.mean[idx], lv = a.lnvar[idx];
+            const float raw = a.head[(size_t)i * O + RN + r];
+            const float dmean = fmaf(wB, mean, dz);
+            float dlv = -0.5f * wB * (1.f - expf(lv));
+            if (a.eps) dlv = fmaf(dz * 0.5f * a.eps[idx], expf(0.5f * lv), dlv);
+            if (!(raw >= -4.f && raw <= 4.f)) dlv = 0.f;
+            dh[r] = dmean;
+            dh[RN + r] = dlv;
+        }
+#pragma unroll
+        for (int h = 0; h < H; ++h) {
+            const float x = a.Hnu[(size_t)i * H + h];
+            float d = 0.f;
+#pragma unroll
+            for (int o = 0; o < O; ++o) {
+                d = fmaf(dh[o], a.W[o * H + h], d);
+                acc[o * H + h] = fmaf(dh[o], x, acc[o * H + h]);
+            }
+            a.dHnu[(size_t)i * H + h] = d;
+            acc[O * H + O + h] += d;
+        }
+#pragma unroll
+        for (int o = 0; o < O; ++o) acc[O * H + o] += dh[o];
+        if (a.ddpre) acc[Q - 1] += a.ddpre[i];
+    }
+    __shared__ float scratch[Q * 32];
+    block_sum<Q>(acc, scratch);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int q = 0; q < O * H; ++q) atomicAdd(a.dW + q, acc[q]);
+#pragma unroll
+        for (int o = 0; o < O; ++o) atomicAdd(a.db + o, acc[O * H + o]);
+#pragma unroll
+        for (int h = 0; h < H; ++h) atomicAdd(a.dbnu + h, acc[O * H + O + h]);
+        if (a.ddepth_b) atomicAdd(a.ddepth_b, acc[Q - 1]);
+    }
+}
+
+namespace {
+template <int H, int RN>
+void
+nu_head_launch(const nu_head_args_t &a, bool bwd, cudaStream_t st)
+{
+    if (bwd) nu_head_bwd_kernel<H, RN><<<min(ceil_div(a.B, 128), 296), 128, 0, st>>>(a);
+    else nu_head_fwd_kernel<H, RN><<<min(ceil_div(a.B * RN, 128), 1024), 128, 0, st>>>(a);
+}
+} // namespace
+
+bool
+nu_head_fused_supported(int H, int Rnu)
+{
+    return (Rnu == 1 && (H == 1 || H == 2 || H == 4)) || (Rnu == 2 && (H == 1 || H == 2));
+}
+
+int
+launch_nu_head(const nu_head_args_t &a, bool bwd, cudaStream_t st)
+{
+    MMV_CHECK(nu_head_fused_supported(a.H, a.Rnu), "nu_head: H = %d, Rnu = %d has no fused kernel", a.H, a.Rnu);
+    if (a.Rnu == 1 && a.H == 1) nu_head_launch<1, 1>(a, bwd, st);
+    else if (a.Rnu == 1 && a.H == 2) nu_head_launch<2, 1>(a, bwd, st);
+    else if (a.Rnu == 1 && a.H == 4) nu_head_launch<4, 1>(a, bwd, st);
+    else if (a.Rnu == 2 && a.H == 1) nu_head_launch<1, 2>(a, bwd, st);
+    else nu_head_launch<2, 2>(a, bwd, st);
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
 }
 
 int
@@ -145,11 +307,11 @@ launch_reparam_bwd(const reparam_args_t &a, cudaStream_t st)
 // out[col * (1 + C) + 0]     += sum_i X[i, col]
 // out[col * (1 + C) + 1 + c] += sum_i X[i, col] * cov[cell_i, c]      (C may be 0)
 // The two destinations are separate arrays: out_sum[N] and out_cov[N x C].
-__global__ void
-colsum_kernel(colsum_args_t a)
+__device__ __forceinline__ void
+colsum_body(const colsum_args_t &a, int bx, int by)
 {
-    const int col = blockIdx.x * blockDim.x + threadIdx.x;
-    const int r0 = blockIdx.y * a.rows_per_cta, r1 = min(a.M, r0 + a.rows_per_cta);
+    const int col = bx * blockDim.x + threadIdx.x;
+    const int r0 = by * a.rows_per_cta, r1 = min(a.M, r0 + a.rows_per_cta);
     if (col >= a.N) return;
     float s = 0.f;
     float sc[8];
@@ -181,10 +343,29 @@ colsum_kernel(colsum_args_t a)
         }
     }
     if (a.out_sum) atomicAdd(a.out_sum + col, s);
-    if (a.out_sum2) atomicAdd(a.out_sum2 + col, s);
+    if (a.out_sum2) atomicAdd(a.out_sum2 + col, s * a.scale2);
     if (a.out_sum3) atomicAdd(a.out_sum3 + col, s);
     if (a.out_cov)   // all-ones covariates (cov == nullptr): every covariate column sees the plain sum
         for (int c = 0; c < a.C; ++c) atomicAdd(a.out_cov + (size_t)col * a.C + c, gather ? sc[c] : s);
+}
+
+__global__ void
+colsum_kernel(colsum_args_t a)
+{
+    colsum_body(a, blockIdx.x, blockIdx.y);
+}
+
+// several independent column sums in ONE launch (the bias gradients of a backward pass: each on its own is a 3-7 us
+// kernel whose launch gap costs as much again).  Block b belongs to the segment whose [first, first + gx * gy) holds it.
+__global__ void __launch_bounds__(128)
+colsum_multi_kernel(colsum_multi_args_t m)
+{
+    int sgm = 0;
+#pragma unroll
+    for (int i = 1; i < kColsumMaxSeg; ++i)
+        if (i < m.n && (int)blockIdx.x >= m.first[i]) sgm = i;
+    const int local = (int)blockIdx.x - m.first[sgm];
+    colsum_body(m.seg[sgm], local % m.gx[sgm], local / m.gx[sgm]);
 }
 
 // bf16 input, all-ones covariates, N % 8 == 0: each thread owns 8 adjacent columns (one 16-byte load
@@ -255,6 +436,31 @@ launch_colsum(colsum_args_t a, cudaStream_t st)
     dim3 grid(ceil_div(a.N, 128), ceil_div(a.M, a.rows_per_cta));
     colsum_kernel<<<grid, 128, 0, st>>>(a); ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int
+launch_colsum_multi(const colsum_args_t *segs, int n, cudaStream_t st)
+{
+    for (int i0 = 0; i0 < n; i0 += kColsumMaxSeg) {
+        colsum_multi_args_t m;
+        int blocks = 0;
+        for (int i = i0; i < n && i < i0 + kColsumMaxSeg; ++i) {
+            colsum_args_t a = segs[i];
+            if (a.M <= 0 || a.N <= 0) continue;
+            MMV_CHECK(a.C <= 8, "colsum: covariate dim %d > 8 not supported", a.C);
+            a.rows_per_cta = 64;   // sized as if the segment had the machine to itself: the segments overlap anyway
+            while (a.rows_per_cta > 8 && (int64_t)ceil_div(a.N, 128) * ceil_div(a.M, a.rows_per_cta) < 296) a.rows_per_cta /= 2;
+            m.seg[m.n] = a;
+            m.first[m.n] = blocks;
+            m.gx[m.n] = ceil_div(a.N, 128);
+            blocks += m.gx[m.n] * ceil_div(a.M, a.rows_per_cta);
+            ++m.n;
+        }
+        if (m.n == 0) continue;
+        colsum_multi_kernel<<<blocks, 128, 0, st>>>(m); ::mmv::count_launch();
+        MMV_CUDA(cudaGetLastError());
+    }
     return 0;
 }
 

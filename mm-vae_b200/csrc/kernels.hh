@@ -81,6 +81,10 @@ struct senc_args_t {
 int launch_senc_fwd(const senc_args_t &a, cudaStream_t st);
 int launch_senc_bias(const float *W1T, const float *x_mean, const float *inv_t, const float *col_scale,
                      float *bias_eff, int D, int h1, int angular, cudaStream_t st);
+// the same from the bf16 effective weight [D x h1] of the tensor-core path (bias_eff pre-initialised, -= the mat-vec)
+bool senc_bias_bf16_supported(int h1);
+int launch_senc_bias_bf16(const void *W1b, const float *x_mean, const float *inv_t, float *bias_eff, int D, int h1,
+                          cudaStream_t st);
 
 struct batch_csc_args_t {
     const int64_t *indptr = nullptr;
@@ -171,7 +175,10 @@ int launch_w1eff_bf16(const float *W1T, const float *col_scale, void *out, int D
 struct nb_lik_args_t {
     const float *G = nullptr;         // [B x D] last decoder layer output WITHOUT bias (tuned kernel: the complete logits)
     const float *abias = nullptr;     // [D] mu_decoding.bias + covar_decoding.bias + mu_bias (tuned kernel: nullptr, it is in G)
-    const void *rowmeta = nullptr;    // tuned kernel: float4[B] (max log2(e), 1 / sum exp2, depth, znu) from launch_nb_row_meta
+    const void *rowmeta = nullptr;    // tuned kernel: float4[B] (max log2(e), 1 / sum exp2, depth, znu) from launch_nb_row_meta,
+                                      // or a workspace the launcher fills itself when tile_stats is given
+    const void *tile_stats = nullptr; // tuned kernel: the decoder-last GEMM's [n_tiles x B] softmax partials (gemm_tc_args_t::row_stats)
+    int n_tiles = 0;
     const float *Wcd = nullptr;       // [D x C] covar_decoding.weight
     const float *cov = nullptr;       // [n_cells x C] covariates (nullptr: ones)
     const int64_t *indptr = nullptr;
@@ -250,6 +257,9 @@ int launch_vmf_scalar(const vmf_scalar_args_t &s, cudaStream_t st);
 int launch_gene_prep(const float *ln_x_sd, float eps, float *inv_t, int D, cudaStream_t st);
 int launch_vec_combine(const float *a, const float *b, const float *c, float sb, float sc, float *out, int n,
                        cudaStream_t st);
+int launch_nb_gene_prologue(const float *ln_x_sd, float eps, float *inv_t, const float *blast, const float *bcd,
+                            const float *mu_bias, const float *Wcd, int C, const float *bnd, const float *nu_bias, float *abias,
+                            float *ubias, int D, cudaStream_t st);
 int launch_nb_gene_bias(const float *blast, const float *bcd, const float *mu_bias, const float *Wcd, int C, const float *bnd,
                         const float *nu_bias, float *abias, float *ubias, int D, cudaStream_t st);
 
@@ -259,16 +269,38 @@ struct reparam_args_t {
     const float *cov = nullptr;
     const int32_t *cells = nullptr;
     const float *eps = nullptr;       // [B x R] injected noise (nullptr: z = mean)
+    float *eps_gen = nullptr;         // forward: draw the noise here (normal_draw(gen_key, gen_step, gen_off + idx)), store it to
+    uint64_t gen_key = 0, gen_step = 0, gen_off = 0;   // eps_gen[idx] (== eps) and use it
     int B = 0, R = 0, C = 0;
     float *mean = nullptr, *lnvar = nullptr, *z = nullptr;   // [B x R]
+    void *z_bf16 = nullptr;           // optional bf16 copy of z (feeds the decoder's first tensor-core GEMM)
     double *kl_acc = nullptr;
     // backward
     const float *dz = nullptr;
     float *dhead = nullptr;
+    void *dhead_bf16 = nullptr;       // optional bf16 copy of dhead
     float kl_weight = 1.f, inv_B = 0.f;
 };
 int launch_reparam_fwd(const reparam_args_t &a, cudaStream_t st);
 int launch_reparam_bwd(const reparam_args_t &a, cudaStream_t st);
+
+// nu heads fused with their reparameterisation (elementwise.cu): head = Hnu W^T + b, W [2 Rnu x H]
+struct nu_head_args_t {
+    const float *Hnu = nullptr, *W = nullptr, *b = nullptr;
+    const float *eps = nullptr;
+    float *eps_gen = nullptr;         // as in reparam_args_t
+    uint64_t gen_key = 0, gen_step = 0, gen_off = 0;
+    int B = 0, H = 0, Rnu = 0;
+    float *head = nullptr, *mean = nullptr, *lnvar = nullptr, *z = nullptr;
+    double *kl_acc = nullptr;
+    // backward
+    const float *dz = nullptr, *ddpre = nullptr;
+    float kl_weight = 1.f, inv_B = 0.f;
+    float *dHnu = nullptr;            // [B x H] written
+    float *dW = nullptr, *db = nullptr, *dbnu = nullptr, *ddepth_b = nullptr;   // += (gradient buffers)
+};
+bool nu_head_fused_supported(int H, int Rnu);
+int launch_nu_head(const nu_head_args_t &a, bool bwd, cudaStream_t st);
 
 // ---- true vMF latent (vmf_latent.cu; SURVEY 8 f4, opt-in, no reference counterpart): same head / outputs as
 // the Gaussian block above — mean = unit direction, lnvar = -log kappa broadcast, z on the sphere, kl_acc += KL
@@ -294,8 +326,18 @@ struct colsum_args_t {
     const int32_t *cells = nullptr;
     int C = 0;
     int rows_per_cta = 64;
+    float scale2 = 1.f;               // out_sum2 += scale2 * sum (generic kernel only)
 };
 int launch_colsum(colsum_args_t a, cudaStream_t st);
+// up to kColsumMaxSeg independent fp32 column sums per launch (generic kernel per segment; Xb segments are not accepted)
+constexpr int kColsumMaxSeg = 12;
+struct colsum_multi_args_t {
+    colsum_args_t seg[kColsumMaxSeg];
+    int first[kColsumMaxSeg] = {};    // first block of each segment
+    int gx[kColsumMaxSeg] = {};       // blocks along the columns
+    int n = 0;
+};
+int launch_colsum_multi(const colsum_args_t *segs, int n, cudaStream_t st);
 int launch_relu_bwd(float *dX, const float *Y, size_t n, cudaStream_t st);
 
 // ---- Angular (angular.cu)
@@ -306,6 +348,8 @@ int launch_angular_bwd(const float *W, const float *dWp, const float *scale, flo
 
 // ---- K6 (optim.cu)
 int launch_sumsq(const float *g, size_t n, double *out, int num_sms, cudaStream_t st);
+// the same over several ranges in one launch (four per launch); *out += the total
+int launch_sumsq_ranges(const float *const *g, const size_t *n, int count, double *out, int num_sms, cudaStream_t st);
 struct adam_args_t {
     float *param = nullptr, *grad = nullptr, *m = nullptr, *v = nullptr;
     void *param_bf16 = nullptr;       // optional bf16 mirror refreshed in the same pass

@@ -132,6 +132,7 @@ struct mmv_model {
     double *acc = nullptr;                // device: [0] nll/-, [1] kl_mu, [2] kl_nu, [3] sumsq, [4] t_acc, [5] llik_sum
     float *fscal = nullptr;               // device: [0] kappa, [1] grad norm, [2] clip coefficient
     std::vector<std::pair<size_t, size_t>> ss_done;   // gradient ranges whose sum of squares a producer already added to acc[3]
+    std::vector<colsum_args_t> pending_colsum;        // bias-gradient column sums of this backward pass, launched together
     bool grad_lazy = false;               // the clip scale of the last fused step is still to be applied to .grad
     size_t grad_lazy_n = 0;               //   ... over grads[0, grad_lazy_n)
     double *h_acc = nullptr;              // pinned mirrors
@@ -586,22 +587,6 @@ mmv_model_get_grad(mmv_model *m, const char *name, float *host, int64_t n)
 // ===========================================================================
 namespace {
 
-__global__ void
-axpy_kernel(float *y, const float *x, float a, size_t n)
-{
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-        y[i] = fmaf(a, x[i], y[i]);
-}
-
-int
-axpy(float *y, const float *x, float a, size_t n, cudaStream_t st)
-{
-    if (n == 0) return 0;
-    axpy_kernel<<<(int)min_sz((n + 255) / 256, 2048), 256, 0, st>>>(y, x, a, n); ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
-    return 0;
-}
-
 struct prof_scope_t {   // records a cudaEvent pair around a kernel group when profiling is on
     mmv_model *m;
     size_t idx = 0;
@@ -631,6 +616,9 @@ struct step_t {
     const int32_t *cells;   // device
     const float *cov;       // device or nullptr (ones)
     const float *eps_mu, *eps_nu;   // device or nullptr
+    // library noise (MMV_EPS_PHILOX) drawn by the reparam kernels themselves: they write the draws into eps_mu / eps_nu
+    bool eps_gen = false;
+    uint64_t eps_key = 0, eps_step = 0;
     float klw, inv_B;
     bool bwd;
     bool optim = false;     // this step ends with allreduce + clip + Adam
@@ -761,12 +749,27 @@ lin_bwd_weight(const step_t &s, const float *dY, int out, const float *X, int in
         MMV_TRY(launch_gemm_f32(g, s.st));
     }
     if (db) {
-        PROF("colsum");
         colsum_args_t c;
         c.X = dY; c.Xb = dY ? nullptr : dY_bf; c.M = s.B; c.N = out; c.ldx = out; c.out_sum = db;
+        if (c.X) { m->pending_colsum.push_back(c); return 0; }   // with the pass's other bias gradients: flush_colsums
+        PROF("colsum");
         MMV_TRY(launch_colsum(c, s.st));
     }
     return 0;
+}
+
+// The deferred column sums of a backward pass in one launch.  Their inputs (the dY of every layer) are distinct
+// workspace arrays that live to the end of the step; the only consumer inside the step is the first layer's backward
+// (Delta), so the flush sits right before it.
+int
+flush_colsums(const step_t &s)
+{
+    mmv_model *m = s.m;
+    if (m->pending_colsum.empty()) return 0;
+    PROF("colsum");
+    const int rc = launch_colsum_multi(m->pending_colsum.data(), (int)m->pending_colsum.size(), s.st);
+    m->pending_colsum.clear();
+    return rc;
 }
 
 // encoder tail shared by both models: hidden layers 1.., stacked heads, reparam.
@@ -799,9 +802,12 @@ encoder_forward(const step_t &s, bool with_covar)
     r.head = head; r.B = B; r.R = R; r.C = C;
     if (with_covar) { r.Wce = m->P(m->covar_enc.w); r.bce = m->P(m->covar_enc.b); r.cov = s.cov; r.cells = s.cells; }
     r.eps = s.eps_mu;
+    if (s.eps_gen) { r.eps_gen = const_cast<float *>(s.eps_mu); r.gen_key = s.eps_key; r.gen_step = s.eps_step; r.gen_off = 0; }
     r.mean = WS("mu_mean", (size_t)B * R); r.lnvar = WS("mu_lnvar", (size_t)B * R); r.z = WS("z", (size_t)B * R);
     NEED(r.mean); NEED(r.lnvar); NEED(r.z);
     r.kl_acc = m->acc + 1;
+    // the decoder's first GEMM wants z in bf16: the reparam kernel writes that copy itself (no cast launch)
+    if (!m->vmf_latent && !m->dec.empty() && tc_ok(s, B, m->dec[0].out, R, R, R)) r.z_bf16 = bf16_twin(s, r.z, (size_t)B * R);
     if (m->vmf_latent) {
         vmf_latent_args_t v;
         v.r = r;
@@ -913,6 +919,9 @@ encoder_backward(const step_t &s, bool with_covar)
         PROF("vmf_latent");
         MMV_TRY(launch_vmf_latent_bwd(v, s.st));
     } else {
+        const linear_t &Hh = m->head_mu;   // the heads' dW / dX GEMMs read dhead in bf16 when they run on tensor cores
+        if (tc_ok(s, 2 * R, Hh.in, B, 2 * R, Hh.in) || tc_ok(s, B, Hh.in, 2 * R, 2 * R, Hh.in))
+            r.dhead_bf16 = bf16_twin(s, r.dhead, (size_t)B * 2 * R);
         MMV_TRY(launch_reparam_bwd(r, s.st));
     }
     if (with_covar) {   // covar_encoding grads: dW_ce[r, c] = sum_i dmean_ir c_ic ; db_ce = sum_i dmean_ir
@@ -920,7 +929,7 @@ encoder_backward(const step_t &s, bool with_covar)
         c.X = r.dhead; c.M = B; c.N = R; c.ldx = 2 * R;
         c.out_sum = m->G(m->covar_enc.b); c.out_cov = m->G(m->covar_enc.w);
         c.cov = s.cov; c.cells = s.cells; c.C = C;
-        MMV_TRY(launch_colsum(c, s.st));
+        m->pending_colsum.push_back(c);
     }
     const linear_t &Hd = m->head_mu;
     const float *X = m->ws["enc_act" + std::to_string(k - 1)].as<float>();
@@ -958,7 +967,8 @@ encoder_backward(const step_t &s, bool with_covar)
     colsum_args_t c;
     c.X = dY; c.M = B; c.N = L0.out; c.ldx = L0.out; c.out_sum = Delta;
     if (L0.b >= 0 && m->want_grad(L0.b)) c.out_sum2 = m->G(L0.b);
-    return launch_colsum(c, s.st);
+    m->pending_colsum.push_back(c);
+    return 0;
 }
 
 int
@@ -1086,52 +1096,15 @@ nb_forward_backward(const step_t &s)
     const linear_t &L0 = m->enc[0];
     const int h1 = L0.out;
 
-    float *inv_t = WS("inv_t", D); NEED(inv_t);
-    MMV_TRY(launch_gene_prep(m->P(m->t_ln_x_sd), 1e-4f, inv_t, D, s.st));            // nb.hh:406-410
-    float *bias_eff = WS("bias_eff", h1); NEED(bias_eff);
-    MMV_CUDA(cudaMemcpyAsync(bias_eff, m->P(L0.b), sizeof(float) * h1, cudaMemcpyDeviceToDevice, s.st));
-    MMV_TRY(launch_senc_bias(m->P(L0.w), m->P(m->t_x_mean), inv_t, nullptr, bias_eff, D, h1, 0, s.st));
-
-    senc_args_t e;
-    e.indptr = s.csr->indptr; e.indices = s.csr->indices; e.vals = s.csr->vals; e.cells = s.cells;
-    e.B = B; e.D = D; e.W1T = m->P(L0.w); e.h1 = h1; e.inv_t = inv_t; e.bias_eff = bias_eff; e.relu = m->relu;
-    e.H1 = WS("enc_act0", (size_t)B * h1); NEED(e.H1);
-    e.WnuT = m->P(m->nu_enc.w); e.bnu = m->P(m->nu_enc.b); e.H = H;
-    e.wdepth = m->P(m->depth.w); e.bdepth = m->P(m->depth.b);
-    e.Hnu = WS("Hnu", (size_t)B * H); e.dpre = WS("dpre", B); NEED(e.Hnu); NEED(e.dpre);
-    const bool tc_senc = senc_tc_ok(s);
-    if (tc_senc) {
-        const void *w1b = nullptr;
-        MMV_TRY(bf16_of(s, m->P(L0.w), (size_t)D * h1, &w1b));
-        MMV_TRY(senc_tc_forward(s, e, w1b));
-    } else {
-        PROF("senc_fwd");
-        MMV_TRY(launch_senc_fwd(e, s.st));
-    }
-
-    MMV_TRY(encoder_forward(s, true));
-
-    // over-dispersion encoder heads (nb.hh:444-451) + reparam
-    const linear_t &Hn = m->head_nu;
-    float *head_nu = WS("head_nu", (size_t)B * 2 * Rnu); NEED(head_nu);
-    MMV_TRY(lin_fwd(s, e.Hnu, H, m->P(Hn.w), m->P(Hn.b), 2 * Rnu, head_nu, false));
-    reparam_args_t rn;
-    rn.head = head_nu; rn.B = B; rn.R = Rnu; rn.eps = s.eps_nu;
-    rn.mean = WS("nu_mean", (size_t)B * Rnu); rn.lnvar = WS("nu_lnvar", (size_t)B * Rnu); rn.z = WS("znu", (size_t)B * Rnu);
-    NEED(rn.mean); NEED(rn.lnvar); NEED(rn.z);
-    rn.kl_acc = m->acc + 2;
-    MMV_TRY(launch_reparam_fwd(rn, s.st));
-
-    trace_mark(m->ctx, "encoder forward done");
-
-    // K4's arguments first: whether the tuned kernel runs decides what the decoder's last GEMM has to produce
+    // K4's arguments first: whether the tuned kernel runs decides what the per-gene prologue and the decoder's last GEMM
+    // have to produce
     const linear_t &Ld = m->dec.back();
     float *abias = WS("abias", D), *ubias = WS("ubias", D); NEED(abias); NEED(ubias);
     nb_lik_args_t k;
     k.G = WS("G", (size_t)B * D); NEED(k.G);
     k.Wcd = m->P(m->covar_dec.w); k.cov = s.cov;
     k.indptr = s.csr->indptr; k.indices = s.csr->indices; k.vals = s.csr->vals; k.cells = s.cells;
-    k.dpre = e.dpre; k.znu = rn.z; k.Wnd = m->P(m->nu_dec.w); k.ubias = ubias;
+    k.Wnd = m->P(m->nu_dec.w); k.ubias = ubias;
     k.B = B; k.D = D; k.C = C; k.Rnu = Rnu; k.inv_B = s.inv_B;
     k.loss_acc = m->acc + 0;
     k.allow_fast = m->nb_fast ? 1 : 0;
@@ -1148,18 +1121,75 @@ nb_forward_backward(const step_t &s)
         k.dlogits = const_cast<float *>(k.G);   // in place: each row is staged in shared memory first
     }
     const bool fast = k.allow_fast && nb_likelihood_fast_eligible(k);
-    // tuned kernel: all-ones covariates, so covar_decoding.weight's row sums join the bias, and the bias joins the logits
-    MMV_TRY(launch_nb_gene_bias(m->P(Ld.b), m->P(m->covar_dec.b), m->P(m->t_mu_bias), fast ? k.Wcd : nullptr, C,
-                                m->P(m->nu_dec.b), m->P(m->t_nu_bias), abias, ubias, D, s.st));
+
+    // per-gene prologue, one launch: inv_t (nb.hh:406-410) and K4's per-gene constants.  Tuned kernel: all-ones
+    // covariates, so covar_decoding.weight's row sums join the bias, and the bias joins the logits
+    float *inv_t = WS("inv_t", D); NEED(inv_t);
+    MMV_TRY(launch_nb_gene_prologue(m->P(m->t_ln_x_sd), 1e-4f, inv_t, m->P(Ld.b), m->P(m->covar_dec.b), m->P(m->t_mu_bias),
+                                    fast ? k.Wcd : nullptr, C, m->P(m->nu_dec.b), m->P(m->t_nu_bias), abias, ubias, D, s.st));
+    float *bias_eff = WS("bias_eff", h1); NEED(bias_eff);
+    MMV_CUDA(cudaMemcpyAsync(bias_eff, m->P(L0.b), sizeof(float) * h1, cudaMemcpyDeviceToDevice, s.st));
+    const bool tc_senc = senc_tc_ok(s);
+    const void *w1b = nullptr;
+    if (tc_senc) MMV_TRY(bf16_of(s, m->P(L0.w), (size_t)D * h1, &w1b));
+    if (tc_senc && senc_bias_bf16_supported(h1))   // the mean shift against the same bf16 weights the GEMM multiplies with
+        MMV_TRY(launch_senc_bias_bf16(w1b, m->P(m->t_x_mean), inv_t, bias_eff, D, h1, s.st));
+    else
+        MMV_TRY(launch_senc_bias(m->P(L0.w), m->P(m->t_x_mean), inv_t, nullptr, bias_eff, D, h1, 0, s.st));
+
+    senc_args_t e;
+    e.indptr = s.csr->indptr; e.indices = s.csr->indices; e.vals = s.csr->vals; e.cells = s.cells;
+    e.B = B; e.D = D; e.W1T = m->P(L0.w); e.h1 = h1; e.inv_t = inv_t; e.bias_eff = bias_eff; e.relu = m->relu;
+    e.H1 = WS("enc_act0", (size_t)B * h1); NEED(e.H1);
+    e.WnuT = m->P(m->nu_enc.w); e.bnu = m->P(m->nu_enc.b); e.H = H;
+    e.wdepth = m->P(m->depth.w); e.bdepth = m->P(m->depth.b);
+    e.Hnu = WS("Hnu", (size_t)B * H); e.dpre = WS("dpre", B); NEED(e.Hnu); NEED(e.dpre);
+    if (tc_senc) {
+        MMV_TRY(senc_tc_forward(s, e, w1b));
+    } else {
+        PROF("senc_fwd");
+        MMV_TRY(launch_senc_fwd(e, s.st));
+    }
+
+    MMV_TRY(encoder_forward(s, true));
+
+    // over-dispersion encoder heads (nb.hh:444-451) + reparam
+    const linear_t &Hn = m->head_nu;
+    float *head_nu = WS("head_nu", (size_t)B * 2 * Rnu); NEED(head_nu);
+    reparam_args_t rn;
+    rn.head = head_nu; rn.B = B; rn.R = Rnu; rn.eps = s.eps_nu;
+    if (s.eps_gen) {   // element offset of the nu block in the step's noise stream
+        rn.eps_gen = const_cast<float *>(s.eps_nu); rn.gen_key = s.eps_key; rn.gen_step = s.eps_step; rn.gen_off = (uint64_t)B * m->R;
+    }
+    rn.mean = WS("nu_mean", (size_t)B * Rnu); rn.lnvar = WS("nu_lnvar", (size_t)B * Rnu); rn.z = WS("znu", (size_t)B * Rnu);
+    NEED(rn.mean); NEED(rn.lnvar); NEED(rn.z);
+    rn.kl_acc = m->acc + 2;
+    const bool nu_fused = nu_head_fused_supported(H, Rnu) && !tc_ok(s, B, 2 * Rnu, H, H, H);
+    nu_head_args_t nh;
+    if (nu_fused) {   // heads + reparam in one launch (default H = Rnu = 1: a [2 x 1] product per cell)
+        nh.Hnu = e.Hnu; nh.W = m->P(Hn.w); nh.b = m->P(Hn.b); nh.eps = s.eps_nu; nh.B = B; nh.H = H; nh.Rnu = Rnu;
+        nh.eps_gen = rn.eps_gen; nh.gen_key = rn.gen_key; nh.gen_step = rn.gen_step; nh.gen_off = rn.gen_off;
+        nh.head = head_nu; nh.mean = rn.mean; nh.lnvar = rn.lnvar; nh.z = rn.z; nh.kl_acc = rn.kl_acc;
+        MMV_TRY(launch_nu_head(nh, false, s.st));
+    } else {
+        MMV_TRY(lin_fwd(s, e.Hnu, H, m->P(Hn.w), m->P(Hn.b), 2 * Rnu, head_nu, false));
+        MMV_TRY(launch_reparam_fwd(rn, s.st));
+    }
+
+    trace_mark(m->ctx, "encoder forward done");
+
+    k.dpre = e.dpre; k.znu = rn.z;
     if (fast) {
         const int max_tiles = (D + 255) / 256;
         void *stats = m->W("k4_tile_stats", sizeof(float) * 2 * (size_t)max_tiles * B); NEED(stats);
         void *meta = m->W("k4_rowmeta", sizeof(float) * 4 * (size_t)B); NEED(meta);
         int tiles = 0;
         MMV_TRY(decoder_forward(s, abias, stats, &tiles));
-        {
+        if (tiles > 0) {   // the tuned kernel's launcher merges the partials in its own pre-kernel
+            k.tile_stats = stats; k.n_tiles = tiles;
+        } else {
             PROF("nb_likelihood");
-            MMV_TRY(launch_nb_row_meta(k.G, tiles > 0 ? stats : nullptr, tiles, k.dpre, k.znu, B, D, meta, s.st));
+            MMV_TRY(launch_nb_row_meta(k.G, nullptr, 0, k.dpre, k.znu, B, D, meta, s.st));
         }
         k.rowmeta = meta;
     } else {
@@ -1192,10 +1222,17 @@ nb_forward_backward(const step_t &s)
         c.out_cov = m->G(m->covar_dec.w); c.cov = s.cov; c.cells = s.cells; c.C = C;
         MMV_TRY(launch_colsum(c, s.st));
     }
-    // nu decoder: u = W_nd znu + b_nd - nu_bias
-    MMV_TRY(axpy(m->G(m->nu_dec.b), k.col_du, 1.f, D, s.st));
-    MMV_TRY(axpy(m->G(m->t_nu_bias), k.col_du, -1.f, D, s.st));
-    MMV_TRY(axpy(m->G(m->nu_dec.w), k.col_duz, 1.f, (size_t)D * Rnu, s.st));
+    // nu decoder: u = W_nd znu + b_nd - nu_bias.  K4's per-gene sums are added to the three gradients as one-row
+    // "column sums" of the pass's grouped launch (flush_colsums)
+    {
+        colsum_args_t c;
+        c.X = k.col_du; c.M = 1; c.N = D; c.ldx = D;
+        c.out_sum = m->G(m->nu_dec.b); c.out_sum2 = m->G(m->t_nu_bias); c.scale2 = -1.f;
+        m->pending_colsum.push_back(c);
+        colsum_args_t c2;
+        c2.X = k.col_duz; c2.M = 1; c2.N = D * Rnu; c2.ldx = D * Rnu; c2.out_sum = m->G(m->nu_dec.w);
+        m->pending_colsum.push_back(c2);
+    }
 
     trace_mark(m->ctx, "likelihood + column sums done");
     MMV_TRY(decoder_backward(s));
@@ -1203,20 +1240,25 @@ nb_forward_backward(const step_t &s)
     MMV_TRY(encoder_backward(s, true));
 
     // nu encoder backward
-    rn.dz = k.dznu; rn.dhead = WS("dhead_nu", (size_t)B * 2 * Rnu); NEED(rn.dhead);
-    rn.kl_weight = s.klw; rn.inv_B = s.inv_B;
-    MMV_TRY(launch_reparam_bwd(rn, s.st));
-    MMV_TRY(lin_bwd_weight(s, rn.dhead, 2 * Rnu, e.Hnu, H, m->G(Hn.w), m->G(Hn.b)));
     float *dHnu = WS("dHnu", (size_t)B * H); NEED(dHnu);
-    MMV_TRY(lin_bwd_data(s, rn.dhead, 2 * Rnu, m->P(Hn.w), H, dHnu));
-    {
+    if (nu_fused) {   // reparam backward, the heads' dW / db, dHnu and the two bias sums behind it: one launch
+        nh.dz = k.dznu; nh.ddpre = k.ddpre; nh.kl_weight = s.klw; nh.inv_B = s.inv_B;
+        nh.dHnu = dHnu; nh.dW = m->G(Hn.w); nh.db = m->G(Hn.b); nh.dbnu = m->G(m->nu_enc.b); nh.ddepth_b = m->G(m->depth.b);
+        MMV_TRY(launch_nu_head(nh, true, s.st));
+    } else {
+        rn.dz = k.dznu; rn.dhead = WS("dhead_nu", (size_t)B * 2 * Rnu); NEED(rn.dhead);
+        rn.kl_weight = s.klw; rn.inv_B = s.inv_B;
+        MMV_TRY(launch_reparam_bwd(rn, s.st));
+        MMV_TRY(lin_bwd_weight(s, rn.dhead, 2 * Rnu, e.Hnu, H, m->G(Hn.w), m->G(Hn.b)));
+        MMV_TRY(lin_bwd_data(s, rn.dhead, 2 * Rnu, m->P(Hn.w), H, dHnu));
         colsum_args_t c;
         c.X = dHnu; c.M = B; c.N = H; c.ldx = H; c.out_sum = m->G(m->nu_enc.b);
-        MMV_TRY(launch_colsum(c, s.st));
+        m->pending_colsum.push_back(c);
         colsum_args_t c2;
         c2.X = k.ddpre; c2.M = B; c2.N = 1; c2.ldx = 1; c2.out_sum = m->G(m->depth.b);
-        MMV_TRY(launch_colsum(c2, s.st));
+        m->pending_colsum.push_back(c2);
     }
+    MMV_TRY(flush_colsums(s));   // Delta (first layer's backward reads it) and every bias gradient of the pass
 
     if (!tc_senc) {
         PROF("batch_csc");
@@ -1263,17 +1305,23 @@ vmf_forward_backward(const step_t &s)
     MMV_TRY(launch_angular_scale(m->P(L0.w), col_scale, h1, D, 1, (size_t)h1, s.st));
     float *bias_eff = WS("bias_eff", h1); NEED(bias_eff);
     MMV_CUDA(cudaMemsetAsync(bias_eff, 0, sizeof(float) * h1, s.st));                 // Angular has no bias
-    MMV_TRY(launch_senc_bias(m->P(L0.w), m->P(m->t_x_mean), inv_t, col_scale, bias_eff, D, h1, 1, s.st));
+    const bool tc_senc = senc_tc_ok(s);
+    void *w1b = nullptr;
+    if (tc_senc) {   // B operand = (relu(W) + 1e-4) * col_scale, materialised in bf16 once per step
+        w1b = m->W("w1eff.bf", (size_t)D * h1 * 2); NEED(w1b);
+        MMV_TRY(launch_w1eff_bf16(m->P(L0.w), col_scale, w1b, D, h1, s.st));
+    }
+    if (tc_senc && senc_bias_bf16_supported(h1))
+        MMV_TRY(launch_senc_bias_bf16(w1b, m->P(m->t_x_mean), inv_t, bias_eff, D, h1, s.st));
+    else
+        MMV_TRY(launch_senc_bias(m->P(L0.w), m->P(m->t_x_mean), inv_t, col_scale, bias_eff, D, h1, 1, s.st));
 
     senc_args_t e;
     e.indptr = s.csr->indptr; e.indices = s.csr->indices; e.vals = s.csr->vals; e.cells = s.cells;
     e.B = B; e.D = D; e.angular = 1; e.W1T = m->P(L0.w); e.h1 = h1; e.inv_t = inv_t; e.bias_eff = bias_eff;
     e.col_scale = col_scale; e.relu = m->relu;
     e.H1 = WS("enc_act0", (size_t)B * h1); e.rownorm = WS("rownorm", B); NEED(e.H1); NEED(e.rownorm);
-    const bool tc_senc = senc_tc_ok(s);
-    if (tc_senc) {   // B operand = (relu(W) + 1e-4) * col_scale, materialised in bf16 once per step
-        void *w1b = m->W("w1eff.bf", (size_t)D * h1 * 2); NEED(w1b);
-        MMV_TRY(launch_w1eff_bf16(m->P(L0.w), col_scale, w1b, D, h1, s.st));
+    if (tc_senc) {
         MMV_TRY(senc_tc_forward(s, e, w1b));
     } else {
         PROF("senc_fwd");
@@ -1335,11 +1383,18 @@ vmf_forward_backward(const step_t &s)
         c.X = k.dpre; c.Xb = k.dpre_bf16; c.M = B; c.N = D; c.ldx = D; c.out_sum = m->want_grad(Ld.b) ? m->G(Ld.b) : nullptr;
         if (c.out_sum) MMV_TRY(launch_colsum(c, s.st));
     }
-    MMV_TRY(axpy(m->G(m->covar_dec.b), k.col_dq, 1.f, D, s.st));
-    MMV_TRY(axpy(m->G(m->covar_dec.w), k.col_dqc, 1.f, (size_t)D * C, s.st));
+    {   // K5's per-gene sums join the two gradients as one-row segments of the pass's grouped column-sum launch
+        colsum_args_t c;
+        c.X = k.col_dq; c.M = 1; c.N = D; c.ldx = D; c.out_sum = m->G(m->covar_dec.b);
+        m->pending_colsum.push_back(c);
+        colsum_args_t c2;
+        c2.X = k.col_dqc; c2.M = 1; c2.N = D * C; c2.ldx = D * C; c2.out_sum = m->G(m->covar_dec.w);
+        m->pending_colsum.push_back(c2);
+    }
 
     MMV_TRY(decoder_backward(s));
     MMV_TRY(encoder_backward(s, true));
+    MMV_TRY(flush_colsums(s));   // Delta (first layer's backward reads it) and every bias gradient of the pass
 
     if (!tc_senc) {
         PROF("batch_csc");
@@ -1374,25 +1429,12 @@ vmf_forward_backward(const step_t &s)
 
 namespace {
 
-// counter-based N(0,1): one draw per element keyed on (seed, step, element).
-__device__ __forceinline__ uint32_t
-mix32(uint64_t z)
-{
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-    z = z ^ (z >> 31);
-    return (uint32_t)(z >> 16);
-}
-
+// counter-based N(0,1): one draw per element keyed on (seed, step, element) — normal_draw() in common.cuh
 __global__ void
 normal_kernel(float *out, size_t n, uint64_t seed, uint64_t step)
 {
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        const uint64_t key = seed * 0x9E3779B97F4A7C15ull + step * 0xD1B54A32D192ED03ull + i * 2;
-        const float u1 = ((float)mix32(key) + 1.f) * (1.f / 4294967808.f);          // (0, 1)
-        const float u2 = (float)mix32(key + 1) * (1.f / 4294967296.f);
-        out[i] = sqrtf(-2.f * logf(u1)) * cospif(2.f * u2);                          // Box-Muller
-    }
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = normal_draw(seed, step, i);
 }
 
 int
@@ -1446,9 +1488,14 @@ stage_inputs(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const 
             // keyed on (model seed, rank, per-model draw counter, element): data-parallel replicas share the seed and
             // step in lock-step, so without the rank every shard would see the same B noise vectors
             const uint64_t key = m->seed + 77 + 0x9E3779B97F4A7C15ull * (uint64_t)m->ctx->rank;
-            normal_kernel<<<(int)min_sz((n_mu + n_nu + 255) / 256, 1024), 256, 0, st>>>(d_eps, n_mu + n_nu, key,
-                                                                                     ++m->eps_draw); ::mmv::count_launch();
-            MMV_CUDA(cudaGetLastError());
+            ++m->eps_draw;
+            if (m->vmf_latent) {   // (the vMF-latent kernels read their noise from the buffer)
+                normal_kernel<<<(int)min_sz((n_mu + n_nu + 255) / 256, 1024), 256, 0, st>>>(d_eps, n_mu + n_nu, key, m->eps_draw);
+                ::mmv::count_launch();
+                MMV_CUDA(cudaGetLastError());
+            } else {               // the reparam kernels draw element i of the same stream themselves and store it
+                s.eps_gen = true; s.eps_key = key; s.eps_step = m->eps_draw;
+            }
         }
         s.eps_mu = d_eps;
         s.eps_nu = n_nu ? d_eps + n_mu : nullptr;
@@ -1506,6 +1553,7 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         s.optim = (flags & MMV_OPTIM) != 0;
         m->ar_done.clear();
         m->ss_done.clear();
+        m->pending_colsum.clear();
         if (s.optim && s.bwd) trace_begin(m->ctx);
         MMV_TRY(stage_inputs(m, csr, cells, B, boot_idx, eps, flags, s));
         if (csr->ev_ready) MMV_CUDA(cudaStreamWaitEvent(st, csr->ev_ready, 0));   // streamed slot: its upload is done
@@ -1574,14 +1622,17 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         PROF("clip_adam");
         if (!(flags & MMV_FWD)) m->ss_done.clear();   // acc[3] was re-zeroed: nothing carried over
         std::sort(m->ss_done.begin(), m->ss_done.end());
-        {
+        {   // everything the producers have not covered, in one launch
+            std::vector<const float *> rg;
+            std::vector<size_t> rn;
             size_t pos = 0;
             for (size_t i = 0; i <= m->ss_done.size(); ++i) {
                 const size_t end = i < m->ss_done.size() ? std::min(m->ss_done[i].first, n_opt) : n_opt;
-                if (end > pos) MMV_TRY(launch_sumsq(m->grads + pos, end - pos, m->acc + 3, m->ctx->num_sms, st));
+                if (end > pos) { rg.push_back(m->grads + pos); rn.push_back(end - pos); }
                 if (i < m->ss_done.size()) pos = std::max(pos, std::min(m->ss_done[i].second, n_opt));
             }
             m->ss_done.clear();
+            MMV_TRY(launch_sumsq_ranges(rg.data(), rn.data(), (int)rg.size(), m->acc + 3, m->ctx->num_sms, st));
         }
         adam_args_t a;
         m->adam_t += 1;

@@ -233,12 +233,11 @@ count_terms(float nu, float x, float &lg_terms, float &dig_diff)
 // (bounds[row * (cs + 1) + c]); one warp per row.  Unsorted rows get the whole run for every slice
 // (the kernel's range test filters).
 // ---------------------------------------------------------------------------
-__global__ void
-slice_bounds_kernel(const int64_t *indptr, const int32_t *indices, const int32_t *cells, const int *unsorted, int B,
-                    int cs, int Ds, int64_t *bounds)
+__device__ __forceinline__ void
+slice_bounds_body(const int64_t *indptr, const int32_t *indices, const int32_t *cells, const int *unsorted, int B, int cs,
+                  int Ds, int64_t *bounds, int t)
 {
     // one thread per (row, boundary): lower_bound of c * Ds in the cell's sorted gene ids
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int row = t / (cs + 1), c = t % (cs + 1);
     if (row >= B) return;
     const int64_t cell = cells ? (int64_t)cells[row] : (int64_t)row;
@@ -257,27 +256,62 @@ slice_bounds_kernel(const int64_t *indptr, const int32_t *indices, const int32_t
     bounds[(size_t)row * (cs + 1) + c] = v;
 }
 
+__global__ void
+slice_bounds_kernel(const int64_t *indptr, const int32_t *indices, const int32_t *cells, const int *unsorted, int B,
+                    int cs, int Ds, int64_t *bounds)
+{
+    slice_bounds_body(indptr, indices, cells, unsorted, B, cs, Ds, bounds, blockIdx.x * blockDim.x + threadIdx.x);
+}
+
 // ---------------------------------------------------------------------------
 // per-row metadata of the tuned kernel: (max of the logits in the log2 domain, 1 / sum of exp2, depth, z_nu)
 //   tile_stats != nullptr: merge the [n_tiles x B] partials the decoder-last GEMM's epilogue left
 //   tile_stats == nullptr: one pass over G (fp32 mode, or a GEMM variant without the statistics epilogue)
 // ---------------------------------------------------------------------------
-__global__ void
-nb_row_meta_merge_kernel(const float2 *tile_stats, int n_tiles, const float *dpre, const float *znu, int B, float4 *meta)
+__device__ __forceinline__ void
+row_meta_merge(const float2 *tile_stats, int n_tiles, const float *dpre, const float *znu, int B, float4 *meta, int row)
 {
-    const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= B) return;
     float gm = -INFINITY, gs = 0.f;
-    for (int t = 0; t < n_tiles; ++t) {          // coalesced over rows; online merge in the log2 domain
-        const float2 p = tile_stats[(size_t)t * B + row];
-        if (p.x > -INFINITY) {
-            const float nm = fmaxf(gm, p.x);
-            gs = gs * (gm > -INFINITY ? ex2_f(gm - nm) : 0.f) + p.y * ex2_f(p.x - nm);
+    for (int t0 = 0; t0 < n_tiles; t0 += 8) {    // coalesced over rows, 8 partials in flight; online merge in the log2 domain
+        float2 p[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            p[u] = t0 + u < n_tiles ? __ldg(&tile_stats[(size_t)(t0 + u) * B + row]) : make_float2(-INFINITY, 0.f);
+        float cm = p[0].x;
+#pragma unroll
+        for (int u = 1; u < 8; ++u) cm = fmaxf(cm, p[u].x);
+        if (cm > -INFINITY) {
+            const float nm = fmaxf(gm, cm);
+            float add = 0.f;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) add += p[u].x > -INFINITY ? p[u].y * ex2_f(p[u].x - nm) : 0.f;
+            gs = gs * (gm > -INFINITY ? ex2_f(gm - nm) : 0.f) + add;
             gm = nm;
         }
     }
     const float dp = dpre[row];
     meta[row] = make_float4(gm, 1.f / gs, dp > 20.f ? dp : log1pf(expf(dp)), znu[row]);   // nb.hh:498 (exact, once per row)
+}
+
+__global__ void
+nb_row_meta_merge_kernel(const float2 *tile_stats, int n_tiles, const float *dpre, const float *znu, int B, float4 *meta)
+{
+    row_meta_merge(tile_stats, n_tiles, dpre, znu, B, meta, blockIdx.x * blockDim.x + threadIdx.x);
+}
+
+// both pre-kernels of the tuned kernel in one launch: blocks [0, meta_blocks) merge the GEMM epilogue's partials into the
+// row metadata, the others bisect the CSR runs by gene slice (slice_bounds_kernel's body)
+__global__ void
+nb_row_prep_kernel(const float2 *tile_stats, int n_tiles, const float *dpre, const float *znu, float4 *meta, int meta_blocks,
+                   const int64_t *indptr, const int32_t *indices, const int32_t *cells, const int *unsorted, int B, int cs,
+                   int Ds, int64_t *bounds)
+{
+    if ((int)blockIdx.x < meta_blocks) {
+        row_meta_merge(tile_stats, n_tiles, dpre, znu, B, meta, blockIdx.x * blockDim.x + threadIdx.x);
+        return;
+    }
+    slice_bounds_body(indptr, indices, cells, unsorted, B, cs, Ds, bounds, (blockIdx.x - meta_blocks) * blockDim.x + threadIdx.x);
 }
 
 __global__ void __launch_bounds__(256)
@@ -705,7 +739,17 @@ launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stre
     int cs = 1, Ds = 0;
     const k4_variant_t *v = fast_layout(a.D, cs, Ds);
     MMV_CHECK(v != nullptr, "nb_likelihood: D=%d does not fit a cluster of 8 CTAs", a.D);
-    MMV_TRY(launch_slice_bounds(a.indptr, a.indices, a.cells, a.unsorted, a.B, cs, Ds, a.slice_bounds, stream));
+    if (a.tile_stats) {   // row metadata from the GEMM epilogue's partials + slice bounds: one pre-kernel
+        const int meta_blocks = ceil_div(a.B, 256);
+        nb_row_prep_kernel<<<meta_blocks + ceil_div((int64_t)a.B * (cs + 1), 256), 256, 0, stream>>>(
+            reinterpret_cast<const float2 *>(a.tile_stats), a.n_tiles, a.dpre, a.znu,
+            reinterpret_cast<float4 *>(const_cast<void *>(a.rowmeta)), meta_blocks, a.indptr, a.indices, a.cells, a.unsorted, a.B,
+            cs, Ds, a.slice_bounds);
+        ::mmv::count_launch();
+        MMV_CUDA(cudaGetLastError());
+    } else {              // (the caller ran launch_nb_row_meta's scan over the complete logits)
+        MMV_TRY(launch_slice_bounds(a.indptr, a.indices, a.cells, a.unsorted, a.B, cs, Ds, a.slice_bounds, stream));
+    }
     void (*kern)(nb_lik_args_t, int, int) = v->kern;
     const size_t smem = fast_smem_bytes(v->ept, v->T);
     MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(kern), (int)smem));

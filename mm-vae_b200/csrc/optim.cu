@@ -17,24 +17,35 @@ constexpr int kSumsqMaxBlocks = 148 * 16;
 __device__ float g_sumsq_partial[kSumsqMaxBlocks];
 __device__ unsigned int g_sumsq_ticket = 0;
 
+// up to four ranges per launch: the flat gradient buffer minus the tensors whose producers already added their share
+struct sumsq_ranges_t {
+    const float *g[4];
+    size_t n[4];
+    int count;
+};
+
 __global__ void
-sumsq_kernel(const float *g, size_t n, double *out)
+sumsq_kernel(sumsq_ranges_t rg, double *out)
 {
     float s = 0.f;
-    const size_t n4 = ((reinterpret_cast<uintptr_t>(g) & 15) == 0) ? n / 4 : 0;   // 16-byte loads, 4 in flight
-    const float4 *g4 = reinterpret_cast<const float4 *>(g);
     const size_t stride = (size_t)gridDim.x * blockDim.x;
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    for (; i + 3 * stride < n4; i += 4 * stride) {
-        const float4 a = g4[i], b = g4[i + stride], c = g4[i + 2 * stride], d = g4[i + 3 * stride];
-        s += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
-        s += c.x * c.x + c.y * c.y + c.z * c.z + c.w * c.w + d.x * d.x + d.y * d.y + d.z * d.z + d.w * d.w;
+    for (int r = 0; r < rg.count; ++r) {
+        const float *g = rg.g[r];
+        const size_t n = rg.n[r];
+        const size_t n4 = ((reinterpret_cast<uintptr_t>(g) & 15) == 0) ? n / 4 : 0;   // 16-byte loads, 4 in flight
+        const float4 *g4 = reinterpret_cast<const float4 *>(g);
+        size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+        for (; i + 3 * stride < n4; i += 4 * stride) {
+            const float4 a = g4[i], b = g4[i + stride], c = g4[i + 2 * stride], d = g4[i + 3 * stride];
+            s += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
+            s += c.x * c.x + c.y * c.y + c.z * c.z + c.w * c.w + d.x * d.x + d.y * d.y + d.z * d.z + d.w * d.w;
+        }
+        for (; i < n4; i += stride) {
+            const float4 a = g4[i];
+            s += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
+        }
+        for (size_t k = n4 * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) s = fmaf(g[k], g[k], s);
     }
-    for (; i < n4; i += stride) {
-        const float4 a = g4[i];
-        s += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
-    }
-    for (size_t k = n4 * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) s = fmaf(g[k], g[k], s);
     __shared__ float scratch[32];
     __shared__ bool last;
     float v[1] = { s };
@@ -60,13 +71,31 @@ sumsq_kernel(const float *g, size_t n, double *out)
 }
 
 int
+launch_sumsq_ranges(const float *const *g, const size_t *n, int count, double *out, int num_sms, cudaStream_t st)
+{
+    for (int i0 = 0; i0 < count; i0 += 4) {
+        sumsq_ranges_t rg;
+        rg.count = 0;
+        size_t total = 0;
+        for (int i = i0; i < count && i < i0 + 4; ++i) {
+            if (n[i] == 0) continue;
+            rg.g[rg.count] = g[i];
+            rg.n[rg.count] = n[i];
+            total += n[i];
+            ++rg.count;
+        }
+        if (rg.count == 0) continue;
+        const int grid = (int)min_sz(min_sz((total + 1023) / 1024, (size_t)num_sms * 8), (size_t)kSumsqMaxBlocks);
+        sumsq_kernel<<<grid, 256, 0, st>>>(rg, out); ::mmv::count_launch();
+        MMV_CUDA(cudaGetLastError());
+    }
+    return 0;
+}
+
+int
 launch_sumsq(const float *g, size_t n, double *out, int num_sms, cudaStream_t st)
 {
-    if (n == 0) return 0;
-    const int grid = (int)min_sz(min_sz((n + 1023) / 1024, (size_t)num_sms * 8), (size_t)kSumsqMaxBlocks);
-    sumsq_kernel<<<grid, 256, 0, st>>>(g, n, out); ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
-    return 0;
+    return launch_sumsq_ranges(&g, &n, 1, out, num_sms, st);
 }
 
 __global__ void

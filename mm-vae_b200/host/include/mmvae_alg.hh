@@ -25,6 +25,7 @@
 #include <mutex>
 #include <random>
 #include <thread>
+#include <type_traits>
 
 // KL anneal shared by nb_loss_t / vmf_loss_t (nb_vae_main.cc:14-37, vmf_vae_main.cc:13-36):
 // rate = max(max_rate * exp(-time_discount * epoch), min_rate)
@@ -38,8 +39,8 @@ struct kl_anneal_t {
     }
     float time_discount, max_rate, min_rate;
 };
-using nb_loss_t = kl_anneal_t;
-using vmf_loss_t = kl_anneal_t;
+// (the reference's mains define their own nb_loss_t / vmf_loss_t functors; those work with the six-argument
+// train_vae_model below, this one with the device-aware overload and run_vae_main)
 
 // One rank's share of train_vae_model.  `dev` says which shard this is (rank / nranks / sync); with one GPU
 // it is the reference's loop verbatim.  Returns the epoch losses (meaningful on rank 0).
@@ -232,6 +233,49 @@ run_vae_main(const mmvae_options_t &main_options, training_options_t &train_opt,
     CHK(mmvae::write_vector_file(main_options.out + ".scores.gz", scores));
     TLOG("Done");
     return EXIT_SUCCESS;
+}
+
+// train_vae_model with the reference's own signature (include/mmvae_alg.hh:200-213): model, visitor, data block, covariate
+// block, options, loss functor — what a translation unit written against the reference calls (its two mains compile
+// unchanged against host/include/refcompat, tests/test_refcompat_cpu.py).  Differences that remain, all forced by the
+// absence of host tensors (INTEGRATION.md has the table):
+//   * the model arrives unbound (dimensions only) and is bound to GPU opt.device here;
+//   * `loss_fun(x, y, epoch)` is called with placeholders once per epoch and only its KL weight is used (the ELBO, its
+//     backward and the optimiser run inside mmv_step);
+//   * a visitor that is one of the reference's recorders (recorder_spec_t) becomes a latent_recorder_t; any other
+//     visitor is called as update_on_batch(model, data_block, batch, dev) / update_on_epoch(model, epoch);
+//   * one GPU (the data block was read whole by the caller); the sharded --ngpu run is run_vae_main's.
+template <typename MODEL, typename VISITOR, typename DATA_BLOCK, typename LOSS>
+std::vector<float>
+train_vae_model(MODEL &model, VISITOR &visitor, DATA_BLOCK &data_block, DATA_BLOCK &covar_block, training_options_t &opt,
+                LOSS loss_fun)
+{
+    ASSERT(data_block.ntot() == covar_block.ntot(), "data and covar on the same set of data points");
+    ASSERT(data_block.size() == covar_block.size(), "data and covar on the same batch size");
+    ASSERT(opt.ngpu <= 1, "--ngpu needs the sharded ingest of run_vae_main (each GPU reads its own range of the file)");
+    // covariates: dense [N x C]; the all-ones single column the mains write when no --covar is given stays implicit
+    std::vector<float> covar;
+    covar_block.dense_all(covar);
+    const int64_t c_dim = covar_block.nfeature();
+    bool ones = c_dim == 1;
+    for (size_t i = 0; ones && i < covar.size(); ++i) ones = covar[i] == 1.f;
+
+    mmvae::shared_run_t shared(1);
+    mmvae::device_t dev;
+    dev.shared = &shared;
+    ASSERT(dev.upload(opt.device, data_block, ones ? nullptr : &covar, c_dim) == EXIT_SUCCESS, "upload to GPU " << opt.device);
+    ASSERT(model->bind(dev.ctx, opt.seed + 7) == EXIT_SUCCESS, "model construction on GPU " << opt.device);
+    if (!opt.init_dir.empty()) ASSERT(model->load_params(opt.init_dir) == EXIT_SUCCESS, "--init_dir");
+    auto kl = [&](const int64_t epoch) { return loss_fun(mmvae::batch_ref_t(), mmvae::recon_ref_t(), epoch).kl_weight; };
+    std::vector<float> scores;
+    if constexpr (std::is_base_of<mmvae::recorder_spec_t, VISITOR>::value) {
+        mmvae::latent_recorder_t rec(visitor.header, visitor.max_epoch, &shared, data_block.ntot(), visitor.is_vmf, opt.record_params);
+        scores = train_vae_model(*model.operator->(), rec, data_block, dev, opt, kl);
+    } else {
+        scores = train_vae_model(*model.operator->(), visitor, data_block, dev, opt, kl);
+    }
+    model->release();           // the model goes before its context (dev's destructor)
+    return scores;
 }
 
 #endif

@@ -69,10 +69,27 @@ struct device_t {   // one context + the resident data (one shard) of a run
     }
 };
 
+// What the reference's LOSS functors (nb_loss_t / vmf_loss_t of the two mains) exchange with the training loop.  There
+// the functor gets the minibatch tensor x and the model output y and returns the loss tensor whose backward() the loop
+// calls (mmvae_alg.hh:277-279,303-307).  Here x and y never exist on the host: loss / backward run inside mmv_step, and
+// the one thing the functor decides — the KL weight of this epoch — travels back in the "tensor" it returns.
+struct batch_ref_t { };              // stands for the minibatch x (resident on the device)
+struct recon_ref_t { };              // stands for the model output y
+struct loss_request_t {              // what mmvae::nb::loss / mmvae::vmf::vmf_vae_loss return
+    float kl_weight = 1.f;
+};
+
 class model_base_t {
 public:
-    ~model_base_t() { if (m_) mmv_model_destroy(m_); }
+    model_base_t() = default;
+    model_base_t(const model_base_t &) = delete;
+    model_base_t &operator=(const model_base_t &) = delete;
+    virtual ~model_base_t() { if (m_) mmv_model_destroy(m_); }
     mmv_model *get() const { return m_; }
+    bool bound() const { return m_ != nullptr; }
+    void release() { if (m_) mmv_model_destroy(m_); m_ = nullptr; }
+    // reference-style construction (dims only, no device): the training loop binds the model to its context
+    virtual int bind(mmv_ctx *, uint64_t /*seed*/) { return EXIT_SUCCESS; }
     int configure(const training_options_t &opt)
     {
         MMV_OK(mmv_model_set_option(m_, "lr", opt.lr));
@@ -126,7 +143,27 @@ protected:
     mmv_model *m_ = nullptr;
 };
 
+// positive sizes / scalars with a name, as the reference passes them to its constructors (nb.hh:24-47, vmf.hh:14-48)
+struct pos_size_t {
+    explicit pos_size_t(const int64_t v) : val(v) { ASSERT(v > 0, "a dimension must be positive"); }
+    const int64_t val;
+};
+struct pos_scalar_t {
+    explicit pos_scalar_t(const float v) : val(v) { ASSERT(v > 0.f, "a scalar must be positive"); }
+    const float val;
+};
+#define MMVAE_DIM(V) struct V : ::mmvae::pos_size_t { explicit V(const int64_t x) : ::mmvae::pos_size_t(x) { } }
+#define MMVAE_SC(V) struct V : ::mmvae::pos_scalar_t { explicit V(const float x) : ::mmvae::pos_scalar_t(x) { } }
+
 namespace nb {
+
+MMVAE_DIM(data_dim);
+MMVAE_DIM(covar_dim);
+MMVAE_DIM(mu_encoder_h_dim);
+MMVAE_DIM(mu_decoder_h_dim);
+MMVAE_DIM(mu_encoder_r_dim);
+MMVAE_DIM(nu_encoder_h_dim);
+MMVAE_DIM(nu_encoder_r_dim);
 
 class nbvae_t : public model_base_t {
 public:
@@ -134,44 +171,121 @@ public:
             const std::vector<int64_t> &mu_dec_h, int64_t mu_r_dim, int64_t nu_h_dim, int64_t nu_r_dim, bool do_relu,
             uint64_t seed)
     {
-        mmv_nb_dims d;
-        std::memset(&d, 0, sizeof(d));
-        d.x_dim = data_dim; d.c_dim = covar_dim;
+        set_dims(data_dim, covar_dim, mu_enc_h, mu_dec_h, mu_r_dim, nu_h_dim, nu_r_dim, do_relu);
+        MMV_OK_EXIT(mmv_nb_model_create(ctx, &d_, seed, &m_));
+    }
+    // the reference's constructor (nbvae_tImpl, nb.hh:214-221): dimensions only; train_vae_model binds the device
+    nbvae_t(const data_dim xd, const covar_dim cd, const std::vector<mu_encoder_h_dim> &eh, const std::vector<mu_decoder_h_dim> &dh,
+            const mu_encoder_r_dim mr, const nu_encoder_h_dim oh, const nu_encoder_r_dim orr, const bool do_relu = true)
+    {
+        std::vector<int64_t> e, d;
+        for (const auto &v : eh) e.push_back(v.val);
+        for (const auto &v : dh) d.push_back(v.val);
+        set_dims(xd.val, cd.val, e, d, mr.val, oh.val, orr.val, do_relu);
+    }
+    int bind(mmv_ctx *ctx, uint64_t seed) override
+    {
+        if (m_) return EXIT_SUCCESS;
+        MMV_OK(mmv_nb_model_create(ctx, &d_, seed, &m_));
+        return EXIT_SUCCESS;
+    }
+    nbvae_t *operator->() { return this; }   // the reference's model is a module holder: model->...
+    int64_t dim_data() const { return d_.x_dim; }
+    int64_t dim_mu_latent() const { return d_.mu_r_dim; }
+    int64_t dim_nu_latent() const { return d_.nu_r_dim; }
+
+private:
+    void set_dims(int64_t data_dim, int64_t covar_dim, const std::vector<int64_t> &mu_enc_h, const std::vector<int64_t> &mu_dec_h,
+                  int64_t mu_r_dim, int64_t nu_h_dim, int64_t nu_r_dim, bool do_relu)
+    {
+        std::memset(&d_, 0, sizeof(d_));
+        d_.x_dim = data_dim; d_.c_dim = covar_dim;
         ASSERT(mu_enc_h.size() <= MMV_MAX_LAYERS && mu_dec_h.size() <= MMV_MAX_LAYERS, "too many layers");
-        d.n_enc = (int32_t)mu_enc_h.size();
-        for (size_t i = 0; i < mu_enc_h.size(); ++i) d.enc_dims[i] = mu_enc_h[i];
-        d.n_dec = (int32_t)mu_dec_h.size();
-        for (size_t i = 0; i < mu_dec_h.size(); ++i) d.dec_dims[i] = mu_dec_h[i];
-        d.mu_r_dim = mu_r_dim; d.nu_h_dim = nu_h_dim; d.nu_r_dim = nu_r_dim; d.do_relu = do_relu ? 1 : 0;
-        MMV_OK_EXIT(mmv_nb_model_create(ctx, &d, seed, &m_));
+        d_.n_enc = (int32_t)mu_enc_h.size();
+        for (size_t i = 0; i < mu_enc_h.size(); ++i) d_.enc_dims[i] = mu_enc_h[i];
+        d_.n_dec = (int32_t)mu_dec_h.size();
+        for (size_t i = 0; i < mu_dec_h.size(); ++i) d_.dec_dims[i] = mu_dec_h[i];
+        d_.mu_r_dim = mu_r_dim; d_.nu_h_dim = nu_h_dim; d_.nu_r_dim = nu_r_dim; d_.do_relu = do_relu ? 1 : 0;
         latent_dim = mu_r_dim;
         eps_per_cell = mu_r_dim + nu_r_dim;
     }
+    mmv_nb_dims d_;
 };
+
+// nb.hh:540-548 `loss(x, y, kl_weight)`: on this path the ELBO and its backward run inside mmv_step (K4 + K3); what is
+// left of the call is the KL weight the functor chose
+inline loss_request_t
+loss(batch_ref_t, recon_ref_t, float kl_weight = 1.f)
+{
+    loss_request_t r;
+    r.kl_weight = kl_weight;
+    return r;
+}
 
 } // namespace nb
 
 namespace vmf {
+
+MMVAE_DIM(data_dim);
+MMVAE_DIM(covar_dim);
+MMVAE_DIM(z_repr_dim);
+MMVAE_DIM(z_enc_dim);
+MMVAE_DIM(z_dec_dim);
+MMVAE_SC(kappa_min);
+MMVAE_SC(kappa_max);
 
 class vmf_vae_t : public model_base_t {
 public:
     vmf_vae_t(mmv_ctx *ctx, int64_t data_dim, int64_t covar_dim, int64_t z_dim, const std::vector<int64_t> &enc_h,
               const std::vector<int64_t> &dec_h, float kappa_min, float kappa_max, bool do_relu, uint64_t seed)
     {
-        mmv_vmf_dims d;
-        std::memset(&d, 0, sizeof(d));
-        d.x_dim = data_dim; d.c_dim = covar_dim; d.z_dim = z_dim;
+        set_dims(data_dim, covar_dim, z_dim, enc_h, dec_h, kappa_min, kappa_max, do_relu);
+        MMV_OK_EXIT(mmv_vmf_model_create(ctx, &d_, seed, &m_));
+    }
+    // the reference's constructor (vmf_vae_tImpl, vmf.hh:200-207,307-314): dimensions only
+    vmf_vae_t(const data_dim xd, const covar_dim cd, const z_repr_dim zd, const std::vector<z_enc_dim> &eh,
+              const std::vector<z_dec_dim> &dh, const kappa_min kmin = kappa_min{ 1. }, const kappa_max kmax = kappa_max{ 100. },
+              const bool do_relu = true)
+    {
+        std::vector<int64_t> e, d;
+        for (const auto &v : eh) e.push_back(v.val);
+        for (const auto &v : dh) d.push_back(v.val);
+        set_dims(xd.val, cd.val, zd.val, e, d, kmin.val, kmax.val, do_relu);
+    }
+    int bind(mmv_ctx *ctx, uint64_t seed) override
+    {
+        if (m_) return EXIT_SUCCESS;
+        MMV_OK(mmv_vmf_model_create(ctx, &d_, seed, &m_));
+        return EXIT_SUCCESS;
+    }
+    vmf_vae_t *operator->() { return this; }
+
+private:
+    void set_dims(int64_t data_dim, int64_t covar_dim, int64_t z_dim, const std::vector<int64_t> &enc_h,
+                  const std::vector<int64_t> &dec_h, float kmin, float kmax, bool do_relu)
+    {
+        std::memset(&d_, 0, sizeof(d_));
+        d_.x_dim = data_dim; d_.c_dim = covar_dim; d_.z_dim = z_dim;
         ASSERT(enc_h.size() <= MMV_MAX_LAYERS && dec_h.size() <= MMV_MAX_LAYERS, "too many layers");
-        d.n_enc = (int32_t)enc_h.size();
-        for (size_t i = 0; i < enc_h.size(); ++i) d.enc_dims[i] = enc_h[i];
-        d.n_dec = (int32_t)dec_h.size();
-        for (size_t i = 0; i < dec_h.size(); ++i) d.dec_dims[i] = dec_h[i];
-        d.kappa_min = kappa_min; d.kappa_max = kappa_max; d.do_relu = do_relu ? 1 : 0;
-        MMV_OK_EXIT(mmv_vmf_model_create(ctx, &d, seed, &m_));
+        d_.n_enc = (int32_t)enc_h.size();
+        for (size_t i = 0; i < enc_h.size(); ++i) d_.enc_dims[i] = enc_h[i];
+        d_.n_dec = (int32_t)dec_h.size();
+        for (size_t i = 0; i < dec_h.size(); ++i) d_.dec_dims[i] = dec_h[i];
+        d_.kappa_min = kmin; d_.kappa_max = kmax; d_.do_relu = do_relu ? 1 : 0;
         latent_dim = z_dim;
         eps_per_cell = z_dim;
     }
+    mmv_vmf_dims d_;
 };
+
+// vmf.hh:419-440 `vmf_vae_loss(x, y, kl_weight)`: see mmvae::nb::loss above
+inline loss_request_t
+vmf_vae_loss(batch_ref_t, recon_ref_t, float kl_weight = 1.f)
+{
+    loss_request_t r;
+    r.kl_weight = kl_weight;
+    return r;
+}
 
 } // namespace vmf
 
@@ -267,6 +381,25 @@ private:
     std::vector<float> &mean_, &lnvar_;
     shared_run_t *shared_;
 };
+
+// The recorders as the reference's mains construct them (nb.hh:569-580, vmf.hh:457-468): output header + number of
+// epochs.  The six-argument train_vae_model (mmvae_alg.hh) turns one into a latent_recorder_t over the run's tables.
+struct recorder_spec_t {
+    recorder_spec_t(const std::string &hdr, int64_t max_epoch_, bool is_vmf_) : header(hdr), max_epoch(max_epoch_), is_vmf(is_vmf_) { }
+    const std::string header;
+    const int64_t max_epoch;
+    const bool is_vmf;
+};
+namespace nb {
+struct nbvae_recorder_t : recorder_spec_t {
+    explicit nbvae_recorder_t(const std::string _hdr, const int64_t _max_epoch) : recorder_spec_t(_hdr, _max_epoch, false) { }
+};
+} // namespace nb
+namespace vmf {
+struct vmf_vae_recorder_t : recorder_spec_t {
+    explicit vmf_vae_recorder_t(const std::string _hdr, const int64_t _max_epoch) : recorder_spec_t(_hdr, _max_epoch, true) { }
+};
+} // namespace vmf
 
 // io.hh:308-331 write_vector_file: one value per line, gz
 inline int

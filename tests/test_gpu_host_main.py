@@ -179,3 +179,38 @@ def test_nb_vae_main_two_gpus(bins, tmp_path):
     assert s.shape == (6,) and np.all(np.isfinite(s)) and s[-1] < s[0]
     m = np.loadtxt(gzip.open(f"{out}_5.mu_mean.gz", "rt"))
     assert m.shape == (500, 8) and np.all(np.isfinite(m)) and np.abs(m[:250]).sum() > 0 and np.abs(m[250:]).sum() > 0
+
+
+@pytest.mark.parametrize("model", ["nb", "vmf"])
+def test_tu_written_against_reference_names_trains_identically(bins, tmp_path, model):
+    """tests/refcompat/refcompat_tu.cc — reference header names, strong dimension types, a LOSS functor returning
+    torch::Tensor, the six-argument train_vae_model (mmvae_alg.hh:200-213) — built against host/include/refcompat and the real
+    library: the same epoch losses and latent table as this repo's own main on the same command line (same seeds)."""
+    lib = os.path.join(ROOT, "mm-vae_b200")
+    exe = tmp_path / "tu"
+    cmd = ["g++", "-std=c++17", "-O2", "-pthread", *(["-DREFCOMPAT_VMF"] if model == "vmf" else []),
+           "-I" + os.path.join(HOST, "include", "refcompat"), "-I" + os.path.join(HOST, "include"),
+           os.path.join(ROOT, "tests", "refcompat", "refcompat_tu.cc"), "-o", str(exe), "-L" + lib, "-lmmvae_b200",
+           "-Wl,-rpath," + lib, "-lz"]
+    p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert p.returncode == 0, p.stdout[-3000:]
+    if model == "nb":
+        args = ["--batch_size", "100", "--mean_encoding", "64", "--mean_decoding", "64", "--mean_latent", "8", "--max_epoch", "4",
+                "--recording", "4", "--nboot", "2", "--seed", "5", "--train_all_layers", "--lr", "0.01", "--skip_param_record"]
+        table = "3.mu_mean.gz"
+    else:
+        args = ["--batch", "128", "--encoding", "32", "--decoding", "32", "--latent", "4", "--epoch", "4", "--recording", "4",
+                "--seed", "3", "--train_all_layers", "--skip_param_record"]
+        table = "3.latent_mean.gz"
+    res = {}
+    for tag, prog in (("own", os.path.join(bins, "nb_vae" if model == "nb" else "vmf_vae")), ("tu", str(exe))):
+        d = tmp_path / tag
+        d.mkdir()
+        c = [prog, "--mtx", os.path.join(GOLDEN, "reader_b.mtx.gz"), "--idx", str(d / "b.index"), "--out", str(d / "o"), *args]
+        p = subprocess.run(c, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
+        assert p.returncode == 0, p.stderr[-2000:]
+        res[tag] = (scores(str(d / "o") + ".scores.gz"), np.loadtxt(gzip.open(f"{d / 'o'}_{table}", "rt")))
+    assert np.all(np.isfinite(res["own"][0])) and res["own"][0][-1] <= res["own"][0][0]
+    # same kernels on the same inputs; the only freedom is the order of fp32 atomics inside a step
+    assert np.allclose(res["own"][0], res["tu"][0], rtol=1e-4)
+    assert np.allclose(res["own"][1], res["tu"][1], rtol=1e-3, atol=1e-4)
