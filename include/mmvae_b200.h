@@ -120,6 +120,9 @@ MMV_API int mmv_model_destroy(mmv_model *m);
  *        (what the reference's autograd does); 0 skips that dead work.
  *   "max_batch" : capacity hint (cells per step), grows on demand.
  *   "debug_outputs" (0): keep recon_mu / recon_nu / recon for mmv_get_output.
+ *   "comm_bf16" (1): data-parallel runs in bf16 mode ("dtype" 1) send the two D x h weight gradients over
+ *        NVLink as bf16 (per-rank partial sums rounded once, summed by ncclAllReduce(bf16)); 0 or fp32 mode:
+ *        every gradient is reduced in fp32.  No reference counterpart (the reference is single device).
  *   "vmf_latent" (0): vmf models only, z_dim >= 3.  NOT in the reference (its vmf_vae reparameterises a
  *        Gaussian, vmf.hh:394-404, and uses kl_loss_normal, vmf.hh:410-414); this is the latent the north star
  *        names.  1 = the stacked head is read as a von Mises-Fisher posterior instead: mean direction

@@ -8,6 +8,7 @@
 #include "common.cuh"
 #include "internal.hh"
 
+#include <cuda_bf16.h>
 #include <dlfcn.h>
 #include <mutex>
 
@@ -18,7 +19,7 @@ typedef struct ncclComm *ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 typedef struct ncclWindow *ncclWindow_t;
 enum { ncclSuccess = 0 };
-enum { ncclFloat32 = 7, ncclFloat64 = 8 };
+enum { ncclFloat32 = 7, ncclFloat64 = 8, ncclBfloat16 = 9 };
 enum { ncclSum = 0 };
 
 struct nccl_api_t {
@@ -80,6 +81,33 @@ load_nccl()
             return 1;                                                                       \
         }                                                                                   \
     } while (0)
+
+// fp32 <-> bf16 staging of a bucket that crosses the wire in bf16 (8 elements per thread and trip; n % 8 == 0)
+__global__ void
+pack_bf16_kernel(const float *__restrict__ x, uint4 *__restrict__ y, size_t n8)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 a = reinterpret_cast<const float4 *>(x)[2 * i], b = reinterpret_cast<const float4 *>(x)[2 * i + 1];
+        const __nv_bfloat162 p0 = __floats2bfloat162_rn(a.x, a.y), p1 = __floats2bfloat162_rn(a.z, a.w);
+        const __nv_bfloat162 p2 = __floats2bfloat162_rn(b.x, b.y), p3 = __floats2bfloat162_rn(b.z, b.w);
+        uint4 o;
+        o.x = *reinterpret_cast<const uint32_t *>(&p0); o.y = *reinterpret_cast<const uint32_t *>(&p1);
+        o.z = *reinterpret_cast<const uint32_t *>(&p2); o.w = *reinterpret_cast<const uint32_t *>(&p3);
+        y[i] = o;
+    }
+}
+
+__global__ void
+unpack_bf16_kernel(const uint4 *__restrict__ y, float *__restrict__ x, size_t n8)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+        const uint4 v = y[i];
+        reinterpret_cast<float4 *>(x)[2 * i] = make_float4(__uint_as_float(v.x << 16), __uint_as_float(v.x & 0xFFFF0000u),
+                                                          __uint_as_float(v.y << 16), __uint_as_float(v.y & 0xFFFF0000u));
+        reinterpret_cast<float4 *>(x)[2 * i + 1] = make_float4(__uint_as_float(v.z << 16), __uint_as_float(v.z & 0xFFFF0000u),
+                                                              __uint_as_float(v.w << 16), __uint_as_float(v.w & 0xFFFF0000u));
+    }
+}
 
 } // namespace
 
@@ -207,21 +235,42 @@ comm_allreduce_f64_async(mmv_ctx *ctx, double *buf, size_t n)
 }
 
 int
-comm_allreduce_f32_async(mmv_ctx *ctx, float *buf, size_t n)
+comm_allreduce_f32_async(mmv_ctx *ctx, float *buf, size_t n, bool as_bf16)
 {
     if (ctx->nranks <= 1 || n == 0) return 0;
     if (ctx->in_group) {
         MMV_NCCL(g_nccl.AllReduce(buf, buf, n, ncclFloat32, ncclSum, (ncclComm_t)ctx->nccl_comm, ctx->comm_stream));
         return 0;
     }
+    // bf16 on the wire only where it pays (large buckets) and where the layout allows the 32-byte vector casts
+    as_bf16 = as_bf16 && n >= ((size_t)1 << 20) && n % 8 == 0 && (reinterpret_cast<uintptr_t>(buf) & 31) == 0;
+    if (as_bf16 && ctx->comm_stage_bytes < n * 2) {
+        // (grows to the largest bucket during the first step; freed with the communicator)
+        MMV_CUDA(cudaStreamSynchronize(ctx->comm_stream));
+        if (ctx->comm_stage) cudaFree(ctx->comm_stage);
+        ctx->comm_stage = nullptr; ctx->comm_stage_bytes = 0;
+        MMV_CUDA(cudaMalloc(&ctx->comm_stage, n * 2));
+        ctx->comm_stage_bytes = n * 2;
+    }
     MMV_CUDA(cudaEventRecord(ctx->ev_fork, ctx->stream));
     MMV_CUDA(cudaStreamWaitEvent(ctx->comm_stream, ctx->ev_fork, 0));
     if (ctx->trace_on) {
         char nm[64];
-        snprintf(nm, sizeof nm, "allreduce %.1f MB begin", n * 4e-6);
+        snprintf(nm, sizeof nm, "allreduce %.1f MB%s begin", n * 4e-6, as_bf16 ? " (bf16 on the wire)" : "");
         trace_mark(ctx, nm, true);
     }
-    MMV_NCCL(g_nccl.AllReduce(buf, buf, n, ncclFloat32, ncclSum, (ncclComm_t)ctx->nccl_comm, ctx->comm_stream));
+    if (as_bf16) {
+        // few CTAs on purpose: the casts share the SMs and HBM with the backward kernels they run under
+        const int grid = (int)min_sz((n / 8 + 255) / 256, (size_t)ctx->num_sms * 2);
+        pack_bf16_kernel<<<grid, 256, 0, ctx->comm_stream>>>(buf, reinterpret_cast<uint4 *>(ctx->comm_stage), n / 8);
+        MMV_CUDA(cudaGetLastError());
+        MMV_NCCL(g_nccl.AllReduce(ctx->comm_stage, ctx->comm_stage, n, ncclBfloat16, ncclSum, (ncclComm_t)ctx->nccl_comm,
+                                  ctx->comm_stream));
+        unpack_bf16_kernel<<<grid, 256, 0, ctx->comm_stream>>>(reinterpret_cast<const uint4 *>(ctx->comm_stage), buf, n / 8);
+        MMV_CUDA(cudaGetLastError());
+    } else {
+        MMV_NCCL(g_nccl.AllReduce(buf, buf, n, ncclFloat32, ncclSum, (ncclComm_t)ctx->nccl_comm, ctx->comm_stream));
+    }
     trace_mark(ctx, "allreduce end", true);
     MMV_CUDA(cudaEventRecord(ctx->ev_join, ctx->comm_stream));
     return 0;
@@ -292,6 +341,8 @@ mmv_comm_destroy(mmv_ctx *ctx)
     cudaStreamSynchronize(ctx->stream);
     cudaStreamSynchronize(ctx->comm_stream);
     g_nccl.CommDestroy((ncclComm_t)ctx->nccl_comm);
+    if (ctx->comm_stage) cudaFree(ctx->comm_stage);
+    ctx->comm_stage = nullptr; ctx->comm_stage_bytes = 0;
     cudaStreamDestroy(ctx->comm_stream);
     cudaEventDestroy(ctx->ev_fork);
     cudaEventDestroy(ctx->ev_join);

@@ -21,6 +21,8 @@ struct mmv_ctx {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int nranks = 1, rank = 0;
     bool in_group = false;
+    void *comm_stage = nullptr;                  // bf16 staging of a gradient bucket reduced in bf16 (comm.cu)
+    size_t comm_stage_bytes = 0;
     // MMV_COMM_TRACE=<k>: timed marks on both streams for the k-th optimiser step, printed by rank 0 (comm.cu)
     int trace_step = -1, trace_seen = 0;
     bool trace_on = false;
@@ -52,7 +54,9 @@ int comm_allreduce_f32(mmv_ctx *ctx, float *buf, size_t n);
 int comm_allreduce_f64(mmv_ctx *ctx, double *buf, size_t n);
 // bucketed overlap: reduce buf[0, n) on the comm stream once everything queued so far on the ctx stream
 // has finished; comm_join makes the ctx stream wait for it
-int comm_allreduce_f32_async(mmv_ctx *ctx, float *buf, size_t n);
+// as_bf16: the bucket crosses NVLink as bf16 (cast on the comm stream, ncclAllReduce(bf16), cast back) — half the wire
+// bytes for gradients that are products of bf16 operands anyway (tensor-core mode; see comm.cu)
+int comm_allreduce_f32_async(mmv_ctx *ctx, float *buf, size_t n, bool as_bf16 = false);
 int comm_join(mmv_ctx *ctx);
 // reductions queued between begin and end go out as one NCCL launch on the comm stream
 int comm_group_begin(mmv_ctx *ctx);

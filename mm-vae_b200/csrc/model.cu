@@ -114,6 +114,7 @@ struct mmv_model {
     float lr = 1e-3f, weight_decay = 1e-4f, grad_clip = 1.f;
     bool train_all = false, frozen_grads = true, debug_outputs = false;
     bool nb_fast = true;                  // "nb_fast" option: tuned K4 kernel when eligible
+    bool comm_bf16 = true;                // "comm_bf16" option: in tensor-core mode the two D x h gradients cross NVLink as bf16
     bool use_tc = false;                  // "dtype" option: bf16 tcgen05 GEMMs (fp32 accumulate) vs fp32 FFMA
     void *params_bf16 = nullptr;          // bf16 mirror of `params` (same offsets), GEMM B operands
     bool bf16_dirty = true;
@@ -484,6 +485,7 @@ mmv_model_set_option(mmv_model *m, const char *key, double value)
     else if (k == "debug_outputs") m->debug_outputs = value != 0;
     else if (k == "profile") m->profile = value != 0;
     else if (k == "nb_fast") m->nb_fast = value != 0;
+    else if (k == "comm_bf16") m->comm_bf16 = value != 0;
     else if (k == "dtype") m->use_tc = value != 0;   // 0 = fp32 (parity mode), 1 = bf16 tensor-core GEMMs
     else if (k == "max_batch") { /* capacity hint; buffers grow on demand */ }
     else if (k == "vmf_latent") {
@@ -853,7 +855,10 @@ allreduce_grad_async(const step_t &s, int t)
     mmv_model *m = s.m;
     if (!(s.optim && m->ctx->nranks > 1 && m->optimised(t))) return 0;
     const size_t off = m->tensors[t].off, n = m->tensors[t].numel();
-    MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off, n));
+    // tensor-core mode: these gradients are sums of products of bf16 operands (dlogits, activations); rounding the
+    // per-rank partial sums to bf16 for the wire stays inside that mode's 1e-2 budget and halves the bytes.  fp32 mode
+    // reduces in fp32, bit for bit as before.
+    MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off, n, m->use_tc && m->comm_bf16));
     m->ar_done.emplace_back(off, off + n);
     return 0;
 }
@@ -1067,7 +1072,7 @@ senc_tc_backward(const step_t &s, const senc_bwd_args_t &b)
             trace_mark(m->ctx, "first-layer dW part done");
             // a small last part is not worth a launch of its own: it goes with the step's grouped leftovers
             if (t1 == tiles && t0 > 0 && (r1 - r0) * sizeof(float) < ((size_t)16 << 20)) break;
-            MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off + r0, r1 - r0));
+            MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off + r0, r1 - r0, m->use_tc && m->comm_bf16));
             m->ar_done.emplace_back(off + r0, off + r1);
         }
     } else {

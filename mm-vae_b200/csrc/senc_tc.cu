@@ -695,6 +695,60 @@ panel_aux_bwd_kernel(const int *bp, const uint32_t *ent, const float *xraw, int 
     }
 }
 
+// H = 1 (the default nu encoder): no shared-memory float atomics (they compile to compare-and-swap loops, 74 us at cfg 4).
+// Every warp owns a private [64 x 2] accumulator; lanes that hold the same gene in one trip are merged with
+// match_any + shuffles (the lowest lane of a group collects the others), so a slot has exactly one writer per trip and
+// the update is a plain load / add / store; the eight copies are added up once at the end.
+__global__ void __launch_bounds__(256)
+panel_aux_bwd_h1_kernel(const int *bp, const uint32_t *ent, const float *xraw, int nT, int nK, const float *dHnu,
+                        const float *ddpre, float *dWnuT, float *dwdepth, int D)
+{
+    __shared__ float s_priv[8][64 * 2];
+    const int k = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float *priv = s_priv[warp];
+    for (int i = lane; i < 128; i += 32) priv[i] = 0.f;
+    __syncwarp();
+    for (int T = blockIdx.y * 8 + warp; T < nT; T += 8 * kAuxSplit) {
+        const int *p = bp + (size_t)T * (nK + 1) + k;
+        const int b = p[0], e = p[1];
+        for (int q0 = b; q0 < e; q0 += 32) {
+            const int q = q0 + lane;
+            const bool on = q < e;
+            const unsigned act = __ballot_sync(0xffffffffu, on);
+            if (on) {
+                const uint32_t v = ent[q];
+                const float x = xraw[q];
+                const int r = T * 64 + (int)(v >> 26), c = (int)((v >> 20) & 63);
+                const float o0 = x * ddpre[r], o1 = x * dHnu[r];      // this lane's own terms (what the shuffles hand out)
+                float a0 = o0, a1 = o1;
+                const unsigned peers = __match_any_sync(act, c);
+                unsigned todo = peers & ~((2u << lane) - 1u);          // the lanes of my group above me
+                while (__any_sync(act, todo != 0u)) {
+                    const int src = todo ? __ffs(todo) - 1 : lane;
+                    const float t0 = __shfl_sync(act, o0, src), t1 = __shfl_sync(act, o1, src);
+                    if (todo) { a0 += t0; a1 += t1; todo &= todo - 1u; }
+                }
+                if ((peers & ((1u << lane) - 1u)) == 0u) {             // lowest lane of the group: the slot's only writer
+                    priv[c * 2 + 0] += a0;
+                    priv[c * 2 + 1] += a1;
+                }
+            }
+            __syncwarp();
+        }
+    }
+    __syncthreads();
+    if (tid < 128) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += s_priv[w][tid];
+        const int c = tid >> 1, j = k * 64 + c;
+        if (j < D && t != 0.f) {
+            if (tid & 1) atomicAdd(dWnuT + j, t);
+            else atomicAdd(dwdepth + j, t);
+        }
+    }
+}
+
 __global__ void
 w1eff_bf16_kernel(const float *W1T, const float *col_scale, __nv_bfloat16 *out, size_t n, int h1)
 {
@@ -738,6 +792,13 @@ int
 launch_panel_aux_bwd(const int *bucket_ptr, const uint32_t *ent, const float *xraw, int B, int D, int H,
                      const float *dHnu, const float *ddpre, float *dWnuT, float *dwdepth, cudaStream_t st)
 {
+    if (H == 1 && dwdepth != nullptr) {
+        panel_aux_bwd_h1_kernel<<<dim3(panel_chunks(D), kAuxSplit), 256, 0, st>>>(bucket_ptr, ent, xraw, panel_tiles(B),
+                                                                                  panel_chunks(D), dHnu, ddpre, dWnuT, dwdepth, D);
+        ::mmv::count_launch();
+        MMV_CUDA(cudaGetLastError());
+        return 0;
+    }
     const size_t smem = sizeof(float) * 64 * (size_t)(H + 1);
     MMV_CHECK(smem <= 48 * 1024, "panel_aux_bwd: nu hidden width %d too large", H);
     panel_aux_bwd_kernel<<<dim3(panel_chunks(D), kAuxSplit), 256, smem, st>>>(bucket_ptr, ent, xraw, panel_tiles(B), panel_chunks(D), H,

@@ -66,6 +66,7 @@ def main_gpu():
         m = mmv.Model.nb(ctx, D, 1, enc, dec, R, 1, 1, seed=3)
         m.set_option("train_all_layers", 1)
         m.set_option("dtype", int(bf16))
+        m.set_option("comm_bf16", int(os.environ.get("DP_COMM_BF16", "1")))   # bf16 mode: the two D x h gradients as bf16 on the wire
         if wide:   # off the symmetric initial values, and a clip that acts
             m.set_param("x_mean", np.random.default_rng(8).normal(scale=0.05, size=D).astype(np.float32))
             m.set_option("grad_clip", 0.5)

@@ -10,9 +10,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("case", ["small", "wide"])
-@pytest.mark.parametrize("bf16", ["0", "1"])
-def test_data_parallel_matches_single_gpu(bf16, case):
+@pytest.mark.parametrize("bf16,case,wire", [("0", "small", "1"), ("1", "small", "1"), ("0", "wide", "1"), ("1", "wide", "1"),
+                                            ("1", "wide", "0")])
+def test_data_parallel_matches_single_gpu(bf16, case, wire):
     """case "wide" = SURVEY cfg-4 widths (D = 30 000, [1024, 256] / [256, 1024], 256 cells per rank): the bucketed
     first-layer backward, the persistent decoder-last dW GEMM, the grouped leftovers and the un-fused clip norm are
     all on the tested path; parameters AND gradients against the 1-GPU step on the concatenated batch, every replica
@@ -20,7 +20,9 @@ def test_data_parallel_matches_single_gpu(bf16, case):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    env = dict(os.environ, DP_BF16=bf16, DP_CASE=case)
+    # wire = "1": in bf16 mode the decoder-last and first-layer weight gradients cross NVLink as bf16 (comm_bf16, the
+    # default); "0": every gradient reduced in fp32
+    env = dict(os.environ, DP_BF16=bf16, DP_CASE=case, DP_COMM_BF16=wire)
     p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
                         "--master-addr", "127.0.0.1", "--master-port", "29541",
                         os.path.join(ROOT, "tests", "dp_worker.py")],
