@@ -100,12 +100,12 @@ launch_vec_combine(const float *a, const float *b, const float *c, float sb, flo
 
 // ---------------------------------------------------------------- reparam + KL
 // head = [mean_raw | lnvar_raw]  (B x 2R, from the stacked representation heads)
-__global__ void
-reparam_fwd_kernel(reparam_args_t a)
+__device__ __forceinline__ void
+reparam_fwd_body(const reparam_args_t &a, int bid, int nblk)
 {
     const int R = a.R, n = a.B * R;
     float kl = 0.f;
-    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
+    for (int idx = bid * blockDim.x + threadIdx.x; idx < n; idx += nblk * blockDim.x) {
         const int i = idx / R, r = idx % R;
         float mean = a.head[(size_t)i * 2 * R + r];
         if (a.Wce) {   // + covar_enc(c)  (nb.hh:412,416)
@@ -136,13 +136,19 @@ reparam_fwd_kernel(reparam_args_t a)
     if (threadIdx.x == 0 && a.kl_acc) atomicAdd(a.kl_acc, (double)(-0.5f * k1[0]));
 }
 
-// dhead = [dmean | dlnvar_raw] given dz; loss = (... + w KL) / B
 __global__ void
-reparam_bwd_kernel(reparam_args_t a)
+reparam_fwd_kernel(reparam_args_t a)
+{
+    reparam_fwd_body(a, blockIdx.x, gridDim.x);
+}
+
+// dhead = [dmean | dlnvar_raw] given dz; loss = (... + w KL) / B
+__device__ __forceinline__ void
+reparam_bwd_body(const reparam_args_t &a, int bid, int nblk)
 {
     const int R = a.R, n = a.B * R;
     const float wB = a.kl_weight * a.inv_B;
-    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
+    for (int idx = bid * blockDim.x + threadIdx.x; idx < n; idx += nblk * blockDim.x) {
         const int i = idx / R, r = idx % R;
         const float dz = a.dz[idx];
         const float mean = a.mean[idx], lv = a.lnvar[idx];
@@ -160,18 +166,24 @@ reparam_bwd_kernel(reparam_args_t a)
     }
 }
 
+__global__ void
+reparam_bwd_kernel(reparam_args_t a)
+{
+    reparam_bwd_body(a, blockIdx.x, gridDim.x);
+}
+
 // ------------------------------------------------- nu heads: Linear(H -> 2 Rnu) fused with reparam
 // The over-dispersion encoder's heads are a [2 Rnu x H] product per cell (default H = Rnu = 1: two multiplies).  One
 // launch forward (heads + clamp + reparam + KL, nb.hh:444-451,466-468,536) and one backward (reparam backward, the
 // heads' dW / db, dHnu = dhead W and its column sums = nu_encoding.bias' gradient, sum of d depth_pre = depth.bias'
 // gradient) replace two FFMA GEMMs, two reparam launches and three column-sum launches.
 template <int H, int RN>
-__global__ void
-nu_head_fwd_kernel(nu_head_args_t a)
+__device__ __forceinline__ void
+nu_head_fwd_body(const nu_head_args_t &a, int bid, int nblk)
 {
     const int n = a.B * RN;
     float kl = 0.f;
-    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
+    for (int idx = bid * blockDim.x + threadIdx.x; idx < n; idx += nblk * blockDim.x) {
         const int i = idx / RN, r = idx % RN;
         float mean = a.b[r], raw = a.b[RN + r];
 #pragma unroll
@@ -203,7 +215,14 @@ nu_head_fwd_kernel(nu_head_args_t a)
 
 template <int H, int RN>
 __global__ void
-nu_head_bwd_kernel(nu_head_args_t a)
+nu_head_fwd_kernel(nu_head_args_t a)
+{
+    nu_head_fwd_body<H, RN>(a, blockIdx.x, gridDim.x);
+}
+
+template <int H, int RN>
+__device__ __forceinline__ void
+nu_head_bwd_body(const nu_head_args_t &a, int bid, int nblk)
 {
     constexpr int O = 2 * RN;
     constexpr int Q = O * H + O + H + 1;          // dW | db | d nu_encoding.bias | d depth.bias
@@ -211,7 +230,7 @@ nu_head_bwd_kernel(nu_head_args_t a)
 #pragma unroll
     for (int q = 0; q < Q; ++q) acc[q] = 0.f;
     const float wB = a.kl_weight * a.inv_B;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.B; i += gridDim.x * blockDim.x) {
+    for (int i = bid * blockDim.x + threadIdx.x; i < a.B; i += nblk * blockDim.x) {
         float dh[O];
 #pragma unroll
         for (int r = 0; r < RN; ++r) {
@@ -255,6 +274,30 @@ nu_head_bwd_kernel(nu_head_args_t a)
     }
 }
 
+template <int H, int RN>
+__global__ void
+nu_head_bwd_kernel(nu_head_args_t a)
+{
+    nu_head_bwd_body<H, RN>(a, blockIdx.x, gridDim.x);
+}
+
+// both latent blocks of the NB model in one launch: blocks [0, nb_mu) run the mu reparam, the others the nu heads
+template <int H, int RN>
+__global__ void
+latent_fwd_kernel(reparam_args_t a, nu_head_args_t n, int nb_mu)
+{
+    if ((int)blockIdx.x < nb_mu) reparam_fwd_body(a, blockIdx.x, nb_mu);
+    else nu_head_fwd_body<H, RN>(n, blockIdx.x - nb_mu, gridDim.x - nb_mu);
+}
+
+template <int H, int RN>
+__global__ void
+latent_bwd_kernel(reparam_args_t a, nu_head_args_t n, int nb_mu)
+{
+    if ((int)blockIdx.x < nb_mu) reparam_bwd_body(a, blockIdx.x, nb_mu);
+    else nu_head_bwd_body<H, RN>(n, blockIdx.x - nb_mu, gridDim.x - nb_mu);
+}
+
 namespace {
 template <int H, int RN>
 void
@@ -264,6 +307,32 @@ nu_head_launch(const nu_head_args_t &a, bool bwd, cudaStream_t st)
     else nu_head_fwd_kernel<H, RN><<<min(ceil_div(a.B * RN, 128), 1024), 128, 0, st>>>(a);
 }
 } // namespace
+
+namespace {
+template <int H, int RN>
+void
+latent_launch(const reparam_args_t &a, const nu_head_args_t &n, bool bwd, cudaStream_t st)
+{
+    const int nb_mu = min(ceil_div(a.B * a.R, 256), 1024);
+    const int nb_nu = bwd ? min(ceil_div(n.B, 256), 148) : min(ceil_div(n.B * RN, 256), 256);
+    if (bwd) latent_bwd_kernel<H, RN><<<nb_mu + nb_nu, 256, 0, st>>>(a, n, nb_mu);
+    else latent_fwd_kernel<H, RN><<<nb_mu + nb_nu, 256, 0, st>>>(a, n, nb_mu);
+}
+} // namespace
+
+int
+launch_latent(const reparam_args_t &a, const nu_head_args_t &n, bool bwd, cudaStream_t st)
+{
+    MMV_CHECK(nu_head_fused_supported(n.H, n.Rnu), "latent: H = %d, Rnu = %d has no fused kernel", n.H, n.Rnu);
+    if (n.Rnu == 1 && n.H == 1) latent_launch<1, 1>(a, n, bwd, st);
+    else if (n.Rnu == 1 && n.H == 2) latent_launch<2, 1>(a, n, bwd, st);
+    else if (n.Rnu == 1 && n.H == 4) latent_launch<4, 1>(a, n, bwd, st);
+    else if (n.Rnu == 2 && n.H == 1) latent_launch<1, 2>(a, n, bwd, st);
+    else latent_launch<2, 2>(a, n, bwd, st);
+    ::mmv::count_launch();
+    MMV_CUDA(cudaGetLastError());
+    return 0;
+}
 
 bool
 nu_head_fused_supported(int H, int Rnu)

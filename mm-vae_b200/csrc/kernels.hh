@@ -301,6 +301,8 @@ struct nu_head_args_t {
 };
 bool nu_head_fused_supported(int H, int Rnu);
 int launch_nu_head(const nu_head_args_t &a, bool bwd, cudaStream_t st);
+// the mu reparam (forward or backward) and the nu heads in ONE launch (they are independent and adjacent in the step)
+int launch_latent(const reparam_args_t &a, const nu_head_args_t &n, bool bwd, cudaStream_t st);
 
 // ---- true vMF latent (vmf_latent.cu; SURVEY 8 f4, opt-in, no reference counterpart): same head / outputs as
 // the Gaussian block above — mean = unit direction, lnvar = -log kappa broadcast, z on the sphere, kl_acc += KL

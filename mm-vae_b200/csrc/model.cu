@@ -777,7 +777,7 @@ flush_colsums(const step_t &s)
 // encoder tail shared by both models: hidden layers 1.., stacked heads, reparam.
 // Returns pointers through the workspace names "enc_act<l>", "head_mu", "mu_mean", "mu_lnvar", "z".
 int
-encoder_forward(const step_t &s, bool with_covar)
+encoder_forward(const step_t &s, bool with_covar, const nu_head_args_t *nu = nullptr)
 {
     mmv_model *m = s.m;
     const int B = s.B, R = (int)m->R, C = (int)m->C;
@@ -820,8 +820,10 @@ encoder_forward(const step_t &s, bool with_covar)
         v.attempts = (int *)WS("vmf_attempts", B); NEED(v.attempts);
         v.kl_aux = (double *)WS("vmf_kl_aux", (size_t)4 * B); NEED(v.kl_aux);   // 2 doubles per cell
         PROF("vmf_latent");
-        return launch_vmf_latent_fwd(v, s.st);
+        MMV_TRY(launch_vmf_latent_fwd(v, s.st));
+        return nu ? launch_nu_head(*nu, false, s.st) : 0;
     }
+    if (nu) return launch_latent(r, *nu, false, s.st);   // nb: the nu heads ride along (one launch for both latent blocks)
     return launch_reparam_fwd(r, s.st);
 }
 
@@ -902,7 +904,7 @@ decoder_backward(const step_t &s)
 // backward through reparam + heads + hidden encoder layers -> "d_enc0" (gradient
 // w.r.t. the first layer's output, ReLU mask applied) and "Delta" = its column sums
 int
-encoder_backward(const step_t &s, bool with_covar)
+encoder_backward(const step_t &s, bool with_covar, const nu_head_args_t *nu = nullptr)
 {
     mmv_model *m = s.m;
     const int B = s.B, R = (int)m->R, C = (int)m->C;
@@ -923,11 +925,13 @@ encoder_backward(const step_t &s, bool with_covar)
         v.kl_aux = (double *)m->ws["vmf_kl_aux"].as<float>();
         PROF("vmf_latent");
         MMV_TRY(launch_vmf_latent_bwd(v, s.st));
+        if (nu) MMV_TRY(launch_nu_head(*nu, true, s.st));
     } else {
         const linear_t &Hh = m->head_mu;   // the heads' dW / dX GEMMs read dhead in bf16 when they run on tensor cores
         if (tc_ok(s, 2 * R, Hh.in, B, 2 * R, Hh.in) || tc_ok(s, B, Hh.in, 2 * R, 2 * R, Hh.in))
             r.dhead_bf16 = bf16_twin(s, r.dhead, (size_t)B * 2 * R);
-        MMV_TRY(launch_reparam_bwd(r, s.st));
+        if (nu) MMV_TRY(launch_latent(r, *nu, true, s.st));   // nb: + the nu heads' backward, one launch
+        else MMV_TRY(launch_reparam_bwd(r, s.st));
     }
     if (with_covar) {   // covar_encoding grads: dW_ce[r, c] = sum_i dmean_ir c_ic ; db_ce = sum_i dmean_ir
         colsum_args_t c;
@@ -1156,8 +1160,6 @@ nb_forward_backward(const step_t &s)
         MMV_TRY(launch_senc_fwd(e, s.st));
     }
 
-    MMV_TRY(encoder_forward(s, true));
-
     // over-dispersion encoder heads (nb.hh:444-451) + reparam
     const linear_t &Hn = m->head_nu;
     float *head_nu = WS("head_nu", (size_t)B * 2 * Rnu); NEED(head_nu);
@@ -1175,8 +1177,9 @@ nb_forward_backward(const step_t &s)
         nh.Hnu = e.Hnu; nh.W = m->P(Hn.w); nh.b = m->P(Hn.b); nh.eps = s.eps_nu; nh.B = B; nh.H = H; nh.Rnu = Rnu;
         nh.eps_gen = rn.eps_gen; nh.gen_key = rn.gen_key; nh.gen_step = rn.gen_step; nh.gen_off = rn.gen_off;
         nh.head = head_nu; nh.mean = rn.mean; nh.lnvar = rn.lnvar; nh.z = rn.z; nh.kl_acc = rn.kl_acc;
-        MMV_TRY(launch_nu_head(nh, false, s.st));
+        MMV_TRY(encoder_forward(s, true, &nh));          // mu encoder tail; its reparam launch carries the nu heads
     } else {
+        MMV_TRY(encoder_forward(s, true));
         MMV_TRY(lin_fwd(s, e.Hnu, H, m->P(Hn.w), m->P(Hn.b), 2 * Rnu, head_nu, false));
         MMV_TRY(launch_reparam_fwd(rn, s.st));
     }
@@ -1242,15 +1245,14 @@ nb_forward_backward(const step_t &s)
     trace_mark(m->ctx, "likelihood + column sums done");
     MMV_TRY(decoder_backward(s));
     trace_mark(m->ctx, "decoder backward done");
-    MMV_TRY(encoder_backward(s, true));
-
     // nu encoder backward
     float *dHnu = WS("dHnu", (size_t)B * H); NEED(dHnu);
-    if (nu_fused) {   // reparam backward, the heads' dW / db, dHnu and the two bias sums behind it: one launch
+    if (nu_fused) {   // reparam backward, the heads' dW / db, dHnu and the two bias sums behind it: with the mu reparam's launch
         nh.dz = k.dznu; nh.ddpre = k.ddpre; nh.kl_weight = s.klw; nh.inv_B = s.inv_B;
         nh.dHnu = dHnu; nh.dW = m->G(Hn.w); nh.db = m->G(Hn.b); nh.dbnu = m->G(m->nu_enc.b); nh.ddepth_b = m->G(m->depth.b);
-        MMV_TRY(launch_nu_head(nh, true, s.st));
+        MMV_TRY(encoder_backward(s, true, &nh));
     } else {
+        MMV_TRY(encoder_backward(s, true));
         rn.dz = k.dznu; rn.dhead = WS("dhead_nu", (size_t)B * 2 * Rnu); NEED(rn.dhead);
         rn.kl_weight = s.klw; rn.inv_B = s.inv_B;
         MMV_TRY(launch_reparam_bwd(rn, s.st));

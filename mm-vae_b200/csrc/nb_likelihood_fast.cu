@@ -43,6 +43,13 @@ namespace {
 
 using namespace rowstream;
 
+#ifndef MMV_K4_XWAIT_NS
+#define MMV_K4_XWAIT_NS 0      // suspend-time hint (ns) of the wait for the previous row's cluster hop; 0 = plain polling
+#endif
+#ifndef MMV_K4_LWAIT_NS
+#define MMV_K4_LWAIT_NS 0      // the same for the wait on the row's TMA landing
+#endif
+
 constexpr int NZP = 2;                                         // nonzeros prefetched per thread per row
 constexpr float kEps = 1e-4f, kNuMin = 1e-4f, kNuMax = 1e4f;   // nb.hh:514,252,459
 
@@ -461,7 +468,11 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
                 qlo_n = a.slice_bounds[(size_t)next * bstride + (sorted ? rank : 0)];
                 qhi_n = a.slice_bounds[(size_t)next * bstride + (sorted ? rank + 1 : cs)];
             }
+#if MMV_K4_LWAIT_NS > 0
+            if (nj > 0) bar_wait_hint(lbar0 + 8 * slot, (uint32_t)(it / 3) & 1u, MMV_K4_LWAIT_NS);
+#else
             if (nj > 0) bar_wait(lbar0 + 8 * slot, (uint32_t)(it / 3) & 1u);
+#endif
 
             // ---- the sweep: softmax from the row statistics, dense NB terms assuming x = 0 (lgammas cancel, no
             //      digamma).  Branch-free: lanes on the padding compute on the constants and are masked at the sums.
@@ -499,7 +510,11 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         if (prev_row >= 0 && grad) {
             const int pp = par ^ 1;
             const float *xs = xslot + pp * 16;
+#if MMV_K4_XWAIT_NS > 0
+            bar_wait_hint(xbar0 + 8 * pp, (uint32_t)((it - 1) >> 1) & 1u, MMV_K4_XWAIT_NS);
+#else
             bar_wait(xbar0 + 8 * pp, (uint32_t)((it - 1) >> 1) & 1u);
+#endif
             float s = 0.f, dz = 0.f;
 #pragma unroll
             for (int r = 0; r < 8; ++r)

@@ -31,74 +31,6 @@ namespace {
 // ===========================================================================
 // panel build
 // ===========================================================================
-__global__ void
-batch_rowptr_kernel(panel_args_t p)
-{
-    // minibatch-local CSR offsets (exclusive scan of the selected cells' run lengths) and the row
-    // scalars' bias terms (panel_build adds its per-split partial sums on top).  One CTA, on the critical
-    // path of every step: a thread's rows are gathered with all their loads in flight (up to 8 rows per
-    // thread stay in registers for the second pass), the scan is two levels of warp shuffles.
-    __shared__ int s_warp[32];
-    const int tid = threadIdx.x, T = blockDim.x, B = p.B, lane = tid & 31, warp = tid >> 5;
-    const int per = (B + T - 1) / T;
-    const int r0 = min(B, tid * per), r1 = min(B, r0 + per);
-    constexpr int KEEP = 8;
-    int len[KEEP];
-    int sum = 0;
-#pragma unroll
-    for (int u = 0; u < KEEP; ++u) {
-        len[u] = 0;
-        const int r = r0 + u;
-        if (r < r1) {
-            const int64_t c = p.cells ? (int64_t)p.cells[r] : (int64_t)r;
-            len[u] = (int)(p.indptr[c + 1] - p.indptr[c]);
-        }
-    }
-#pragma unroll
-    for (int u = 0; u < KEEP; ++u) sum += len[u];
-    for (int r = r0 + KEEP; r < r1; ++r) {
-        const int64_t c = p.cells ? (int64_t)p.cells[r] : (int64_t)r;
-        sum += (int)(p.indptr[c + 1] - p.indptr[c]);
-    }
-    for (int r = r0; r < r1; ++r) {
-        if (p.wdepth) p.dpre[r] = p.bdepth[0];
-        for (int h = 0; h < p.H; ++h) p.Hnu[(size_t)r * p.H + h] = p.bnu[h];
-    }
-    int inc = sum;                              // inclusive scan inside the warp
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += v;
-    }
-    if (lane == 31) s_warp[warp] = inc;
-    __syncthreads();
-    if (warp == 0) {
-        int w = lane < (T >> 5) ? s_warp[lane] : 0;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int v = __shfl_up_sync(0xffffffffu, w, o);
-            if (lane >= o) w += v;
-        }
-        s_warp[lane] = w;                       // inclusive totals of the warps
-    }
-    __syncthreads();
-    int run = inc - sum + (warp > 0 ? s_warp[warp - 1] : 0);
-#pragma unroll
-    for (int u = 0; u < KEEP; ++u) {
-        const int r = r0 + u;
-        if (r < r1) {
-            p.rowptr[r] = run;
-            run += len[u];
-        }
-    }
-    for (int r = r0 + KEEP; r < r1; ++r) {
-        p.rowptr[r] = run;
-        const int64_t c = p.cells ? (int64_t)p.cells[r] : (int64_t)r;
-        run += (int)(p.indptr[c + 1] - p.indptr[c]);
-    }
-    if (tid == T - 1) p.rowptr[B] = s_warp[(T >> 5) - 1];
-}
-
 constexpr int kPanelThreads = 512;
 constexpr int kUn = 4;
 
@@ -123,6 +55,13 @@ panel_build_kernel(panel_args_t p, int nK, int nS)
 
     for (int k = tid; k < nKl; k += kPanelThreads) s_cur[k] = 0;
     if (tid == 0) s_before = 0;
+    // minibatch-local CSR offset of the tile's first row = run lengths of all earlier rows.  Every CTA adds them up
+    // itself (<= B gathered loads from L2, 8 per thread at B = 4096): cheaper than a one-CTA scan kernel in front
+    int prefix = 0;
+    for (int r = tid; r < r0; r += kPanelThreads) {
+        const int64_t c = p.cells ? (int64_t)p.cells[r] : (int64_t)r;
+        prefix += (int)(p.indptr[c + 1] - p.indptr[c]);
+    }
     __syncthreads();
     if (tid < 128) {                  // per row: where the split's gene range starts / ends in the run
         const int r = tid >> 1, which = tid & 1;
@@ -172,6 +111,16 @@ panel_build_kernel(panel_args_t p, int nK, int nS)
         if (lane == 0 && before_unsorted) atomicAdd(&s_before, before_unsorted);
     }
     __syncthreads();
+    {   // block sum of the row prefix (s_scan is free until the scan below)
+        prefix = warp_sum(prefix);
+        if (lane == 0) s_scan[warp] = prefix;
+        __syncthreads();
+        prefix = 0;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) prefix += s_scan[w];
+        __syncthreads();
+    }
+    const int base = prefix + s_before;
     // ---- exclusive scan over the chunks (each thread owns a contiguous span)
     const int per = (nKl + kPanelThreads - 1) / kPanelThreads;
     const int k0 = min(nKl, tid * per), k1 = min(nKl, k0 + per);
@@ -185,7 +134,6 @@ panel_build_kernel(panel_args_t p, int nK, int nS)
         s_scan[tid] += v;
         __syncthreads();
     }
-    const int base = p.rowptr[r0] + s_before;
     int run = s_scan[tid] - sum;
     for (int k = k0; k < k1; ++k) {
         const int n = s_cur[k];
@@ -248,13 +196,14 @@ panel_build_kernel(panel_args_t p, int nK, int nS)
                 hn0 = fmaf(x[u], wn[u], hn0);
             }
         }
+        // (Hnu / dpre are zero-filled by the launcher; the first split's CTA brings the bias)
         if (h_inline) {   // nb.hh:448 (raw counts), default H = 1
             hn0 = warp_sum(hn0);
-            if (lane == 0) atomicAdd(p.Hnu + r0 + r, hn0);
+            if (lane == 0) atomicAdd(p.Hnu + r0 + r, hn0 + (sp == 0 ? p.bnu[0] : 0.f));
         }
         if (p.wdepth) {   // nb.hh:498 (raw counts)
             depth = warp_sum(depth);
-            if (lane == 0) atomicAdd(p.dpre + r0 + r, depth);
+            if (lane == 0) atomicAdd(p.dpre + r0 + r, depth + (sp == 0 ? p.bdepth[0] : 0.f));
         }
         for (int h = 0; h < p.H && !h_inline; ++h) {   // nb.hh:448 (raw counts), general H
             float s = 0.f;
@@ -263,7 +212,7 @@ panel_build_kernel(panel_args_t p, int nK, int nS)
                 if (k >= 0 && k < nKl) s = fmaf(p.vals[q], p.WnuT[(size_t)j * p.H + h], s);
             }
             s = warp_sum(s);
-            if (lane == 0) atomicAdd(p.Hnu + (size_t)(r0 + r) * p.H + h, s);
+            if (lane == 0) atomicAdd(p.Hnu + (size_t)(r0 + r) * p.H + h, s + (sp == 0 ? p.bnu[h] : 0.f));
         }
     }
 }
@@ -281,8 +230,8 @@ launch_panel_build(const panel_args_t &p, cudaStream_t st)
     const size_t smem = sizeof(int) * (2 * (size_t)nKl + 2);
     MMV_CHECK(smem <= 200 * 1024, "panel_build: %d genes exceed the shared-memory bucket table", p.D);
     MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(panel_build_kernel), 200 * 1024));
-    batch_rowptr_kernel<<<1, 1024, 0, st>>>(p);
-    ::mmv::count_launch();
+    if (p.wdepth && p.dpre) MMV_CUDA(cudaMemsetAsync(p.dpre, 0, sizeof(float) * p.B, st));
+    if (p.H > 0 && p.Hnu) MMV_CUDA(cudaMemsetAsync(p.Hnu, 0, sizeof(float) * (size_t)p.B * p.H, st));
     panel_build_kernel<<<dim3(nT, nS), kPanelThreads, smem, st>>>(p, nK, nS);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());

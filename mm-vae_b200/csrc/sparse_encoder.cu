@@ -213,30 +213,32 @@ senc_bias_kernel(const float *W1T, const float *x_mean, const float *inv_t, cons
 // The same mat-vec over the bf16 EFFECTIVE weight the tensor-core GEMM multiplies with (parameter mirror for nb, the
 // materialised (relu(W) + 1e-4) * col_scale for vmf): half the bytes, and the bias then cancels exactly what the GEMM
 // adds for the mean shift.  A thread owns 8 adjacent columns (one 16-byte load per gene); 256 / (h1 / 8) gene groups per CTA.
-__global__ void __launch_bounds__(256)
+constexpr int kSbT = 512, kSbU = 8;   // threads per CTA, 16-byte loads in flight per thread
+
+__global__ void __launch_bounds__(kSbT)
 senc_bias_bf16_kernel(const __nv_bfloat16 *W, const float *x_mean, const float *inv_t, float *bias_eff, int D, int h1,
                       int genes_per_cta)
 {
-    __shared__ float s_part[256 * 8];
-    const int nc8 = h1 / 8, ngrp = 256 / nc8;
+    __shared__ float s_part[kSbT * 8];
+    const int nc8 = h1 / 8, ngrp = kSbT / nc8;
     const int cg = threadIdx.x % nc8, grp = threadIdx.x / nc8;
     const int j0 = blockIdx.x * genes_per_cta, j1 = min(D, j0 + genes_per_cta);
     float s[8];
 #pragma unroll
     for (int q = 0; q < 8; ++q) s[q] = 0.f;
     if (grp < ngrp) {
-        for (int jb = j0 + grp; jb < j1; jb += 4 * ngrp) {
-            uint4 w[4];
-            float f[4];
+        for (int jb = j0 + grp; jb < j1; jb += kSbU * ngrp) {
+            uint4 w[kSbU];
+            float f[kSbU];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < kSbU; ++u) {
                 const int j = jb + u * ngrp;
                 const bool ok = j < j1;
-                w[u] = ok ? *reinterpret_cast<const uint4 *>(W + (size_t)j * h1 + 8 * cg) : make_uint4(0u, 0u, 0u, 0u);
+                w[u] = ok ? __ldg(reinterpret_cast<const uint4 *>(W + (size_t)j * h1 + 8 * cg)) : make_uint4(0u, 0u, 0u, 0u);
                 f[u] = ok ? x_mean[j] * inv_t[j] : 0.f;
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < kSbU; ++u) {
                 const uint32_t v[4] = { w[u].x, w[u].y, w[u].z, w[u].w };
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
@@ -249,7 +251,7 @@ senc_bias_bf16_kernel(const __nv_bfloat16 *W, const float *x_mean, const float *
 #pragma unroll
     for (int q = 0; q < 8; ++q) s_part[threadIdx.x * 8 + q] = s[q];
     __syncthreads();
-    if (threadIdx.x < nc8) {
+    if ((int)threadIdx.x < nc8) {
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
             float t = 0.f;
@@ -262,7 +264,7 @@ senc_bias_bf16_kernel(const __nv_bfloat16 *W, const float *x_mean, const float *
 bool
 senc_bias_bf16_supported(int h1)
 {
-    return h1 % 8 == 0 && h1 / 8 <= 256 && 256 % (h1 / 8) == 0;
+    return h1 % 8 == 0 && h1 / 8 <= kSbT && kSbT % (h1 / 8) == 0;
 }
 
 int
@@ -271,9 +273,10 @@ launch_senc_bias_bf16(const void *W1b, const float *x_mean, const float *inv_t, 
 {
     MMV_CHECK(senc_bias_bf16_supported(h1) && (reinterpret_cast<uintptr_t>(W1b) & 15) == 0,
               "senc_bias (bf16): first width %d not supported", h1);
+    // two CTAs per SM, every thread with eight independent 16-byte loads in flight: the [D x h1] bf16 matrix streams once
     const int gpc = std::max(8, (ceil_div(D, 296) + 7) / 8 * 8);
-    senc_bias_bf16_kernel<<<ceil_div(D, gpc), 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16 *>(W1b), x_mean, inv_t,
-                                                           bias_eff, D, h1, gpc);
+    senc_bias_bf16_kernel<<<ceil_div(D, gpc), kSbT, 0, st>>>(reinterpret_cast<const __nv_bfloat16 *>(W1b), x_mean, inv_t,
+                                                            bias_eff, D, h1, gpc);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;

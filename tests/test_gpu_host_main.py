@@ -187,7 +187,7 @@ def test_tu_written_against_reference_names_trains_identically(bins, tmp_path, m
     torch::Tensor, the six-argument train_vae_model (mmvae_alg.hh:200-213) — built against host/include/refcompat and the real
     library: the same epoch losses and latent table as this repo's own main on the same command line (same seeds)."""
     lib = os.path.join(ROOT, "mm-vae_b200")
-    exe = tmp_path / "tu"
+    exe = tmp_path / "tu_bin"
     cmd = ["g++", "-std=c++17", "-O2", "-pthread", *(["-DREFCOMPAT_VMF"] if model == "vmf" else []),
            "-I" + os.path.join(HOST, "include", "refcompat"), "-I" + os.path.join(HOST, "include"),
            os.path.join(ROOT, "tests", "refcompat", "refcompat_tu.cc"), "-o", str(exe), "-L" + lib, "-lmmvae_b200",
