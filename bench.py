@@ -495,6 +495,30 @@ def run_dp_check(mmv, model, ctx, csr, w, args, indptr, indices, values, rank, w
                     f"{args.dtype} mode, injected eps"}
 
 
+def bind_to_gpu_numa_node(torch, local):
+    """N > 1: run this rank's host thread (and so first-touch its pinned minibatch buffers) on the NUMA node its GPU hangs
+    off.  Eight ranks each stream ~50 MB per step out of pinned host memory; buffers on the far socket cross the
+    inter-socket link and the e2e step lags the resident one (3.72 vs 3.42 ms at N = 8 in round 1).  Best effort: returns
+    the node or None when sysfs does not say."""
+    try:
+        pr = torch.cuda.get_device_properties(local)
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except Exception:
+        return None
+
+
 def run_own(args):
     import torch
     import torch.distributed as dist
@@ -503,6 +527,7 @@ def run_own(args):
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa_node = bind_to_gpu_numa_node(torch, local) if world > 1 and os.environ.get("BENCH_NUMA_BIND", "1") != "0" else None
     if world > 1:
         # the library pins its gradient all-reduces to NCCL's ring (comm.cu: measured faster under backward); NCCL
         # reads the variable once per process, so it has to be in place before torch creates its own communicator
@@ -732,10 +757,13 @@ def run_own(args):
                                f"({args.cfg_name}), cells sharded over {world} GPU(s), {n_local} resident per GPU",
                    "batch_per_gpu": B, "global_batch": B * world, "encoder": w["enc"], "decoder": w["dec"],
                    "latent": w["latent"], "train_all_layers": True, "nnz_resident_per_gpu": nnz,
-                   "l2_policy": "inputs larger than L2 (new cells every step; B x D activations = "
+                   "numa_bind": numa_node, "l2_policy": "inputs larger than L2 (new cells every step; B x D activations = "
                                 f"{4 * B * D / 1e6:.0f} MB)", "data_gen_s": round(gen_s, 1)},
         "e2e": {"value": round(world * B * args.steps / (ms_e2e * 1e-3), 1), "unit": "cells/s",
-                "ms_per_step": round(ms_e2e / args.steps, 4), "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 96},
+                "ms_per_step": round(ms_e2e / args.steps, 4), "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 96,
+                "host_gather": "excluded: 4 minibatches sit in pinned host buffers before the timed region and are cycled; under "
+                               "the reference schedule a minibatch is a contiguous cell range (mmvae_alg.hh:264-266), i.e. a "
+                               "slice of the host CSR, so there is no per-step gather to time"},
         "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "kernels": kernels,
         "secondary": {"metric": "unique cells/s under the reference schedule (1 eval fwd + 3 bootstrap fwd+bwd+Adam per minibatch)",
                       "value": round(world * B * n_sched / (ms_sched * 1e-3), 1), "unit": "cells/s",

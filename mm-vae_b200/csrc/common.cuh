@@ -62,6 +62,42 @@ ceil_div(int64_t a, int64_t b)
 }
 
 // ---------------------------------------------------------------------------
+// Programmatic dependent launch (PDL).  A step is ~30 kernels back to back on one stream; between two of them the GPU
+// drains, the next grid is launched and its CTAs ramp up (2-4 us each time).  Kernels launched through launch_k()
+// carry cudaLaunchAttributeProgrammaticStreamSerialization: their CTAs may become resident while the previous kernel's
+// last CTAs still run, and park at pdl_sync() — griddepcontrol.wait returns only when the previous grid has COMPLETED
+// and its memory is visible, so nothing before that point may touch global memory.  pdl_sync() is the first statement
+// of every kernel launched this way (a no-op under an ordinary launch).  MMV_PDL=0 turns the attribute off.
+// ---------------------------------------------------------------------------
+bool pdl_enabled();
+
+__device__ __forceinline__ void
+pdl_sync()
+{
+#if defined(__CUDA_ARCH__)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+}
+
+template <typename... P, typename... A>
+inline cudaError_t
+launch_k(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A &&...args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<P>(args)...);
+}
+
+// ---------------------------------------------------------------------------
 // device math.  Accurate libdevice versions on purpose: parity with the
 // reference's fp32 ATen ops is 1e-4 relative (BASELINE.json north_star).
 // ---------------------------------------------------------------------------

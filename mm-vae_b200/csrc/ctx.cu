@@ -36,6 +36,13 @@ count_launch()
     g_launches.fetch_add(1, std::memory_order_relaxed);
 }
 
+bool
+pdl_enabled()
+{
+    static const bool on = [] { const char *e = getenv("MMV_PDL"); return e ? atoi(e) != 0 : true; }();
+    return on;
+}
+
 long long
 launch_count()
 {

@@ -49,6 +49,7 @@ nb_gene_prologue_kernel(const float *ln_x_sd, float eps, float *inv_t, const flo
                         const float *mu_bias, const float *Wcd, int C, const float *bnd, const float *nu_bias, float *abias,
                         float *ubias, int D)
 {
+    pdl_sync();
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= D) return;
     inv_t[j] = 1.f / (softplus_f(ln_x_sd[j]) + eps);
@@ -74,10 +75,9 @@ launch_nb_gene_prologue(const float *ln_x_sd, float eps, float *inv_t, const flo
                         const float *mu_bias, const float *Wcd, int C, const float *bnd, const float *nu_bias, float *abias,
                         float *ubias, int D, cudaStream_t st)
 {
-    nb_gene_prologue_kernel<<<ceil_div(D, 256), 256, 0, st>>>(ln_x_sd, eps, inv_t, blast, bcd, mu_bias, Wcd, C, bnd, nu_bias,
-                                                             abias, ubias, D);
+    MMV_CUDA(launch_k(nb_gene_prologue_kernel, dim3(ceil_div(D, 256)), dim3(256), 0, st, ln_x_sd, eps, inv_t, blast, bcd, mu_bias, Wcd,
+                      C, bnd, nu_bias, abias, ubias, D));
     ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
     return 0;
 }
 
@@ -139,6 +139,7 @@ reparam_fwd_body(const reparam_args_t &a, int bid, int nblk)
 __global__ void
 reparam_fwd_kernel(reparam_args_t a)
 {
+    pdl_sync();
     reparam_fwd_body(a, blockIdx.x, gridDim.x);
 }
 
@@ -169,6 +170,7 @@ reparam_bwd_body(const reparam_args_t &a, int bid, int nblk)
 __global__ void
 reparam_bwd_kernel(reparam_args_t a)
 {
+    pdl_sync();
     reparam_bwd_body(a, blockIdx.x, gridDim.x);
 }
 
@@ -286,6 +288,7 @@ template <int H, int RN>
 __global__ void
 latent_fwd_kernel(reparam_args_t a, nu_head_args_t n, int nb_mu)
 {
+    pdl_sync();
     if ((int)blockIdx.x < nb_mu) reparam_fwd_body(a, blockIdx.x, nb_mu);
     else nu_head_fwd_body<H, RN>(n, blockIdx.x - nb_mu, gridDim.x - nb_mu);
 }
@@ -294,6 +297,7 @@ template <int H, int RN>
 __global__ void
 latent_bwd_kernel(reparam_args_t a, nu_head_args_t n, int nb_mu)
 {
+    pdl_sync();
     if ((int)blockIdx.x < nb_mu) reparam_bwd_body(a, blockIdx.x, nb_mu);
     else nu_head_bwd_body<H, RN>(n, blockIdx.x - nb_mu, gridDim.x - nb_mu);
 }
@@ -315,8 +319,8 @@ latent_launch(const reparam_args_t &a, const nu_head_args_t &n, bool bwd, cudaSt
 {
     const int nb_mu = min(ceil_div(a.B * a.R, 256), 1024);
     const int nb_nu = bwd ? min(ceil_div(n.B, 256), 148) : min(ceil_div(n.B * RN, 256), 256);
-    if (bwd) latent_bwd_kernel<H, RN><<<nb_mu + nb_nu, 256, 0, st>>>(a, n, nb_mu);
-    else latent_fwd_kernel<H, RN><<<nb_mu + nb_nu, 256, 0, st>>>(a, n, nb_mu);
+    if (bwd) launch_k(latent_bwd_kernel<H, RN>, dim3(nb_mu + nb_nu), dim3(256), 0, st, a, n, nb_mu);
+    else launch_k(latent_fwd_kernel<H, RN>, dim3(nb_mu + nb_nu), dim3(256), 0, st, a, n, nb_mu);
 }
 } // namespace
 
@@ -358,8 +362,7 @@ int
 launch_reparam_fwd(const reparam_args_t &a, cudaStream_t st)
 {
     const int n = a.B * a.R;
-    reparam_fwd_kernel<<<min(ceil_div(n, 256), 1024), 256, 0, st>>>(a); ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
+    MMV_CUDA(launch_k(reparam_fwd_kernel, dim3(min(ceil_div(n, 256), 1024)), dim3(256), 0, st, a)); ::mmv::count_launch();
     return 0;
 }
 
@@ -367,8 +370,7 @@ int
 launch_reparam_bwd(const reparam_args_t &a, cudaStream_t st)
 {
     const int n = a.B * a.R;
-    reparam_bwd_kernel<<<min(ceil_div(n, 256), 1024), 256, 0, st>>>(a); ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
+    MMV_CUDA(launch_k(reparam_bwd_kernel, dim3(min(ceil_div(n, 256), 1024)), dim3(256), 0, st, a)); ::mmv::count_launch();
     return 0;
 }
 
@@ -421,6 +423,7 @@ colsum_body(const colsum_args_t &a, int bx, int by)
 __global__ void
 colsum_kernel(colsum_args_t a)
 {
+    pdl_sync();
     colsum_body(a, blockIdx.x, blockIdx.y);
 }
 
@@ -429,6 +432,7 @@ colsum_kernel(colsum_args_t a)
 __global__ void __launch_bounds__(128)
 colsum_multi_kernel(colsum_multi_args_t m)
 {
+    pdl_sync();
     int sgm = 0;
 #pragma unroll
     for (int i = 1; i < kColsumMaxSeg; ++i)
@@ -443,6 +447,7 @@ __global__ void __launch_bounds__(256)
 colsum_bf16x8_kernel(colsum_args_t a)
 {
     __shared__ float s_part[8][32 * 8 + 1];
+    pdl_sync();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int col = (blockIdx.x * 32 + lane) * 8;
     const int r0 = blockIdx.y * a.rows_per_cta, r1 = min(a.M, r0 + a.rows_per_cta);
@@ -494,8 +499,7 @@ launch_colsum(colsum_args_t a, cudaStream_t st)
         a.N >= 256) {
         a.rows_per_cta = 256;
         dim3 grid(ceil_div(a.N, 256), ceil_div(a.M, a.rows_per_cta));
-        colsum_bf16x8_kernel<<<grid, 256, 0, st>>>(a); ::mmv::count_launch();
-        MMV_CUDA(cudaGetLastError());
+        MMV_CUDA(launch_k(colsum_bf16x8_kernel, grid, dim3(256), 0, st, a)); ::mmv::count_launch();
         return 0;
     }
     // narrow matrices (bias gradients of the hidden layers: N = 64 ... 1024): the pass is a chain of dependent row
@@ -503,8 +507,7 @@ launch_colsum(colsum_args_t a, cudaStream_t st)
     a.rows_per_cta = 64;
     while (a.rows_per_cta > 8 && (int64_t)ceil_div(a.N, 128) * ceil_div(a.M, a.rows_per_cta) < 592) a.rows_per_cta /= 2;
     dim3 grid(ceil_div(a.N, 128), ceil_div(a.M, a.rows_per_cta));
-    colsum_kernel<<<grid, 128, 0, st>>>(a); ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
+    MMV_CUDA(launch_k(colsum_kernel, grid, dim3(128), 0, st, a)); ::mmv::count_launch();
     return 0;
 }
 
@@ -527,8 +530,7 @@ launch_colsum_multi(const colsum_args_t *segs, int n, cudaStream_t st)
             ++m.n;
         }
         if (m.n == 0) continue;
-        colsum_multi_kernel<<<blocks, 128, 0, st>>>(m); ::mmv::count_launch();
-        MMV_CUDA(cudaGetLastError());
+        MMV_CUDA(launch_k(colsum_multi_kernel, dim3(blocks), dim3(128), 0, st, m)); ::mmv::count_launch();
     }
     return 0;
 }

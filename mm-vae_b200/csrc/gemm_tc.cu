@@ -96,6 +96,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
+    pdl_sync();   // (descriptor prefetch, barrier init and the TMEM allocation above overlap the previous kernel's tail)
 
     if (warp == 0) {
         // ================= TMA producer =================
@@ -295,6 +296,7 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
+    pdl_sync();   // (descriptor prefetch, barrier init and the TMEM allocation above overlap the previous kernel's tail)
 
     if (warp == 0) {
         // ================= TMA producer (runs ahead across tiles) =================
@@ -601,9 +603,8 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
             g.a_mn ? (g.b_mn ? gemm_tc_persist_kernel<true, true> : gemm_tc_persist_kernel<true, false>)
                    : (g.b_mn ? gemm_tc_persist_kernel<false, true> : gemm_tc_persist_kernel<false, false>);
         MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(pk), P_SMEM_BYTES));
-        pk<<<std::min(ptiles, num_sms), THREADS, P_SMEM_BYTES, stream>>>(ta, tb, tc_map, p);
+        MMV_CUDA(launch_k(pk, dim3(std::min(ptiles, num_sms)), dim3(THREADS), P_SMEM_BYTES, stream, ta, tb, tc_map, p));
         ::mmv::count_launch();
-        MMV_CUDA(cudaGetLastError());
         return 0;
     }
     const bool deep = (int)(grid.x * grid.y * grid.z) <= num_sms && ceil_div(total_kb, (int)grid.z) >= 6;
@@ -616,9 +617,8 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
                       : (g.b_mn ? gemm_tc_kernel<false, true, 3> : gemm_tc_kernel<false, false, 3>);
     const int smem = smem_bytes(deep ? 6 : 3);
     MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(kern), smem));
-    kern<<<grid, THREADS, smem, stream>>>(ta, tb, tc_map, p);
+    MMV_CUDA(launch_k(kern, grid, dim3(THREADS), smem, stream, ta, tb, tc_map, p));
     ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
     return 0;
 }
 
@@ -626,6 +626,7 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
 __global__ void
 to_bf16_kernel(const float *x, __nv_bfloat16 *y, size_t n)
 {
+    pdl_sync();
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
         y[i] = __float2bfloat16(x[i]);
 }
@@ -634,9 +635,8 @@ int
 launch_to_bf16(const float *x, void *y, size_t n, cudaStream_t st)
 {
     if (n == 0) return 0;
-    to_bf16_kernel<<<(int)min_sz((n + 255) / 256, 4096), 256, 0, st>>>(x, reinterpret_cast<__nv_bfloat16 *>(y), n);
+    MMV_CUDA(launch_k(to_bf16_kernel, dim3((unsigned)min_sz((n + 255) / 256, 4096)), dim3(256), 0, st, x, reinterpret_cast<__nv_bfloat16 *>(y), n));
     ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
     return 0;
 }
 

@@ -5,6 +5,7 @@
 // flat fp32 parameter buffer + a table of named tensors (the reference's
 // named_parameters() keys), and train_vae_model's inner step
 // (mmvae_alg.hh:274-311) as a fixed sequence of kernel launches on one stream.
+#include <nvtx3/nvToolsExt.h>
 #include "common.cuh"
 #include "internal.hh"
 
@@ -114,7 +115,8 @@ struct mmv_model {
     float lr = 1e-3f, weight_decay = 1e-4f, grad_clip = 1.f;
     bool train_all = false, frozen_grads = true, debug_outputs = false;
     bool nb_fast = true;                  // "nb_fast" option: tuned K4 kernel when eligible
-    bool comm_bf16 = true;                // "comm_bf16" option: in tensor-core mode the two D x h gradients cross NVLink as bf16
+    // "comm_bf16" option (MMV_COMM_BF16 overrides the default): in tensor-core mode the two D x h gradients cross NVLink as bf16
+    bool comm_bf16 = [] { const char *e = getenv("MMV_COMM_BF16"); return e ? atoi(e) != 0 : true; }();
     bool use_tc = false;                  // "dtype" option: bf16 tcgen05 GEMMs (fp32 accumulate) vs fp32 FFMA
     void *params_bf16 = nullptr;          // bf16 mirror of `params` (same offsets), GEMM B operands
     bool bf16_dirty = true;
@@ -589,11 +591,27 @@ mmv_model_get_grad(mmv_model *m, const char *name, float *host, int64_t n)
 // ===========================================================================
 namespace {
 
+// MMV_NVTX=1: every kernel group of a step (and the step itself) is an NVTX range, so a timeline / ncu --nvtx capture
+// shows the phases by the names bench.py's "kernels" object uses (tracing)
+bool
+nvtx_on()
+{
+    static const bool on = [] { const char *e = getenv("MMV_NVTX"); return e && atoi(e) != 0; }();
+    return on;
+}
+
+struct nvtx_scope_t {
+    bool on;
+    explicit nvtx_scope_t(const char *name) : on(nvtx_on()) { if (on) nvtxRangePushA(name); }
+    ~nvtx_scope_t() { if (on) nvtxRangePop(); }
+};
+
 struct prof_scope_t {   // records a cudaEvent pair around a kernel group when profiling is on
     mmv_model *m;
     size_t idx = 0;
     bool on;
-    prof_scope_t(mmv_model *m_, const char *name) : m(m_), on(m_->profile)
+    nvtx_scope_t nvtx;
+    prof_scope_t(mmv_model *m_, const char *name) : m(m_), on(m_->profile), nvtx(name)
     {
         if (!on) return;
         mmv_model::prof_rec_t r;
@@ -1552,6 +1570,7 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
     cudaStream_t st = m->ctx->stream;
     const int nranks = m->ctx->nranks;
     const size_t n_opt = m->train_all ? m->n_all : m->n_reg;
+    nvtx_scope_t nvtx_step((flags & MMV_OPTIM) ? "mmv_step fwd+bwd+adam" : ((flags & MMV_BWD) ? "mmv_step fwd+bwd" : "mmv_step fwd"));
 
     if (flags & MMV_FWD) {
         step_t s;

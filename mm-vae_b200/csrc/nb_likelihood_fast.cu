@@ -314,6 +314,7 @@ nb_row_prep_kernel(const float2 *tile_stats, int n_tiles, const float *dpre, con
                    const int64_t *indptr, const int32_t *indices, const int32_t *cells, const int *unsorted, int B, int cs,
                    int Ds, int64_t *bounds)
 {
+    pdl_sync();
     if ((int)blockIdx.x < meta_blocks) {
         row_meta_merge(tile_stats, n_tiles, dpre, znu, B, meta, blockIdx.x * blockDim.x + threadIdx.x);
         return;
@@ -756,12 +757,11 @@ launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stre
     MMV_CHECK(v != nullptr, "nb_likelihood: D=%d does not fit a cluster of 8 CTAs", a.D);
     if (a.tile_stats) {   // row metadata from the GEMM epilogue's partials + slice bounds: one pre-kernel
         const int meta_blocks = ceil_div(a.B, 256);
-        nb_row_prep_kernel<<<meta_blocks + ceil_div((int64_t)a.B * (cs + 1), 256), 256, 0, stream>>>(
-            reinterpret_cast<const float2 *>(a.tile_stats), a.n_tiles, a.dpre, a.znu,
-            reinterpret_cast<float4 *>(const_cast<void *>(a.rowmeta)), meta_blocks, a.indptr, a.indices, a.cells, a.unsorted, a.B,
-            cs, Ds, a.slice_bounds);
+        MMV_CUDA(launch_k(nb_row_prep_kernel, dim3(meta_blocks + ceil_div((int64_t)a.B * (cs + 1), 256)), dim3(256), 0, stream,
+                          reinterpret_cast<const float2 *>(a.tile_stats), a.n_tiles, a.dpre, a.znu,
+                          reinterpret_cast<float4 *>(const_cast<void *>(a.rowmeta)), meta_blocks, a.indptr, a.indices, a.cells,
+                          a.unsorted, a.B, cs, Ds, a.slice_bounds));
         ::mmv::count_launch();
-        MMV_CUDA(cudaGetLastError());
     } else {              // (the caller ran launch_nb_row_meta's scan over the complete logits)
         MMV_TRY(launch_slice_bounds(a.indptr, a.indices, a.cells, a.unsorted, a.B, cs, Ds, a.slice_bounds, stream));
     }
@@ -773,6 +773,9 @@ launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stre
     cfg.blockDim = dim3(v->T);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
+    // (no programmatic dependent launch here, unlike the kernels around it: launched early, while the pre-kernel's CTAs
+    // still hold SMs, the 33 persistent clusters no longer all become resident at once and the kernel takes 0.89 ms
+    // instead of 0.50 — profiles/r02_step6_pdl_ab.txt)
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = cs;

@@ -27,6 +27,7 @@ struct sumsq_ranges_t {
 __global__ void
 sumsq_kernel(sumsq_ranges_t rg, double *out)
 {
+    pdl_sync();
     float s = 0.f;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (int r = 0; r < rg.count; ++r) {
@@ -86,8 +87,7 @@ launch_sumsq_ranges(const float *const *g, const size_t *n, int count, double *o
         }
         if (rg.count == 0) continue;
         const int grid = (int)min_sz(min_sz((total + 1023) / 1024, (size_t)num_sms * 8), (size_t)kSumsqMaxBlocks);
-        sumsq_kernel<<<grid, 256, 0, st>>>(rg, out); ::mmv::count_launch();
-        MMV_CUDA(cudaGetLastError());
+        MMV_CUDA(launch_k(sumsq_kernel, dim3(grid), dim3(256), 0, st, rg, out)); ::mmv::count_launch();
     }
     return 0;
 }
@@ -101,6 +101,7 @@ launch_sumsq(const float *g, size_t n, double *out, int num_sms, cudaStream_t st
 __global__ void
 adam_kernel(adam_args_t a)
 {
+    pdl_sync();
     const float total = (float)sqrt(*a.sumsq);
     float coef = a.max_norm / (total + 1e-6f);
     coef = fminf(coef, 1.f);
@@ -160,8 +161,7 @@ launch_adam(const adam_args_t &a, int num_sms, cudaStream_t st)
 {
     if (a.n == 0) return 0;
     const int grid = (int)min_sz((a.n / 4 + 255) / 256 + 1, (size_t)num_sms * 8);
-    adam_kernel<<<grid, 256, 0, st>>>(a); ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
+    MMV_CUDA(launch_k(adam_kernel, dim3(grid), dim3(256), 0, st, a)); ::mmv::count_launch();
     return 0;
 }
 

@@ -46,6 +46,7 @@ panel_build_kernel(panel_args_t p, int nK, int nS)
     __shared__ int s_before;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = kPanelThreads / 32;
+    pdl_sync();
     const int T = blockIdx.x, sp = blockIdx.y, r0 = T * 64, nrows = min(64, p.B - r0);
     const int k_lo = (int)((int64_t)nK * sp / nS), k_hi = (int)((int64_t)nK * (sp + 1) / nS), nKl = k_hi - k_lo;
     int *s_off = s_int;               // [nKl + 1] exclusive offsets of this CTA's buckets
@@ -232,9 +233,8 @@ launch_panel_build(const panel_args_t &p, cudaStream_t st)
     MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(panel_build_kernel), 200 * 1024));
     if (p.wdepth && p.dpre) MMV_CUDA(cudaMemsetAsync(p.dpre, 0, sizeof(float) * p.B, st));
     if (p.H > 0 && p.Hnu) MMV_CUDA(cudaMemsetAsync(p.Hnu, 0, sizeof(float) * (size_t)p.B * p.H, st));
-    panel_build_kernel<<<dim3(nT, nS), kPanelThreads, smem, st>>>(p, nK, nS);
+    MMV_CUDA(launch_k(panel_build_kernel, dim3(nT, nS), dim3(kPanelThreads), smem, st, p, nK, nS));
     ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
     return 0;
 }
 
@@ -335,6 +335,7 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ 
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
+    pdl_sync();   // (barrier init and the TMEM allocation above overlap the previous kernel's tail)
 
     if (warp == 0) {
         // ================= TMA producer: dense operand, [64 k x 64 n] boxes =================
@@ -542,9 +543,8 @@ launch_tc(const senc_tc_args_t &a, cudaStream_t st)
     auto kern = senc_tc_kernel<BN, BWD>;
     MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(kern), cfg::SMEM));
     dim3 grid(ceil_div(a.h1, BN), BWD ? (a.ntiles > 0 ? a.ntiles : ceil_div(a.D, BM)) : ceil_div(a.B, BM));
-    kern<<<grid, TCT, cfg::SMEM, st>>>(tm, ts, a, nT, nK);
+    MMV_CUDA(launch_k(kern, grid, dim3(TCT), cfg::SMEM, st, tm, ts, a, nT, nK));
     ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
     return 0;
 }
 
@@ -557,6 +557,7 @@ __global__ void __launch_bounds__(256)
 senc_row_pass_kernel(senc_tc_args_t a, const float *ln_x_sd, float *dx_mean, float *dln_x_sd)
 {
     __shared__ float s_ss[8];
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const int j = a.tile0 * 128 + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     const int j_end = a.ntiles > 0 ? min(a.D, (a.tile0 + a.ntiles) * 128) : a.D;
@@ -657,6 +658,7 @@ panel_aux_bwd_h1_kernel(const int *bp, const uint32_t *ent, const float *xraw, i
     float *priv = s_priv[warp];
     for (int i = lane; i < 128; i += 32) priv[i] = 0.f;
     __syncwarp();
+    pdl_sync();
     for (int T = blockIdx.y * 8 + warp; T < nT; T += 8 * kAuxSplit) {
         const int *p = bp + (size_t)T * (nK + 1) + k;
         const int b = p[0], e = p[1];
@@ -701,6 +703,7 @@ panel_aux_bwd_h1_kernel(const int *bp, const uint32_t *ent, const float *xraw, i
 __global__ void
 w1eff_bf16_kernel(const float *W1T, const float *col_scale, __nv_bfloat16 *out, size_t n, int h1)
 {
+    pdl_sync();
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
         out[i] = __float2bfloat16((fmaxf(W1T[i], 0.f) + 1e-4f) * col_scale[i % h1]);   // angular.hh:38-40
 }
@@ -731,9 +734,8 @@ int
 launch_senc_row_pass(const senc_tc_args_t &a, const float *ln_x_sd, float *dx_mean, float *dln_x_sd, cudaStream_t st)
 {
     const int64_t genes = a.ntiles > 0 ? std::min<int64_t>(a.D - (int64_t)a.tile0 * 128, (int64_t)a.ntiles * 128) : a.D;
-    senc_row_pass_kernel<<<ceil_div(genes * 32, 256), 256, 0, st>>>(a, ln_x_sd, dx_mean, dln_x_sd);
+    MMV_CUDA(launch_k(senc_row_pass_kernel, dim3(ceil_div(genes * 32, 256)), dim3(256), 0, st, a, ln_x_sd, dx_mean, dln_x_sd));
     ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
     return 0;
 }
 
@@ -742,10 +744,9 @@ launch_panel_aux_bwd(const int *bucket_ptr, const uint32_t *ent, const float *xr
                      const float *dHnu, const float *ddpre, float *dWnuT, float *dwdepth, cudaStream_t st)
 {
     if (H == 1 && dwdepth != nullptr) {
-        panel_aux_bwd_h1_kernel<<<dim3(panel_chunks(D), kAuxSplit), 256, 0, st>>>(bucket_ptr, ent, xraw, panel_tiles(B),
-                                                                                  panel_chunks(D), dHnu, ddpre, dWnuT, dwdepth, D);
+        MMV_CUDA(launch_k(panel_aux_bwd_h1_kernel, dim3(panel_chunks(D), kAuxSplit), dim3(256), 0, st, bucket_ptr, ent, xraw,
+                          panel_tiles(B), panel_chunks(D), dHnu, ddpre, dWnuT, dwdepth, D));
         ::mmv::count_launch();
-        MMV_CUDA(cudaGetLastError());
         return 0;
     }
     const size_t smem = sizeof(float) * 64 * (size_t)(H + 1);
@@ -761,10 +762,9 @@ int
 launch_w1eff_bf16(const float *W1T, const float *col_scale, void *out, int D, int h1, cudaStream_t st)
 {
     const size_t n = (size_t)D * h1;
-    w1eff_bf16_kernel<<<(int)min_sz((n + 255) / 256, 148 * 16), 256, 0, st>>>(W1T, col_scale,
-                                                                            reinterpret_cast<__nv_bfloat16 *>(out), n, h1);
+    MMV_CUDA(launch_k(w1eff_bf16_kernel, dim3((unsigned)min_sz((n + 255) / 256, 148 * 16)), dim3(256), 0, st, W1T, col_scale,
+                      reinterpret_cast<__nv_bfloat16 *>(out), n, h1));
     ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
     return 0;
 }
 

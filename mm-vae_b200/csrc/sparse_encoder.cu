@@ -220,6 +220,7 @@ senc_bias_bf16_kernel(const __nv_bfloat16 *W, const float *x_mean, const float *
                       int genes_per_cta)
 {
     __shared__ float s_part[kSbT * 8];
+    pdl_sync();
     const int nc8 = h1 / 8, ngrp = kSbT / nc8;
     const int cg = threadIdx.x % nc8, grp = threadIdx.x / nc8;
     const int j0 = blockIdx.x * genes_per_cta, j1 = min(D, j0 + genes_per_cta);
@@ -275,10 +276,9 @@ launch_senc_bias_bf16(const void *W1b, const float *x_mean, const float *inv_t, 
               "senc_bias (bf16): first width %d not supported", h1);
     // two CTAs per SM, every thread with eight independent 16-byte loads in flight: the [D x h1] bf16 matrix streams once
     const int gpc = std::max(8, (ceil_div(D, 296) + 7) / 8 * 8);
-    senc_bias_bf16_kernel<<<ceil_div(D, gpc), kSbT, 0, st>>>(reinterpret_cast<const __nv_bfloat16 *>(W1b), x_mean, inv_t,
-                                                            bias_eff, D, h1, gpc);
+    MMV_CUDA(launch_k(senc_bias_bf16_kernel, dim3(ceil_div(D, gpc)), dim3(kSbT), 0, st, reinterpret_cast<const __nv_bfloat16 *>(W1b),
+                      x_mean, inv_t, bias_eff, D, h1, gpc));
     ::mmv::count_launch();
-    MMV_CUDA(cudaGetLastError());
     return 0;
 }
 

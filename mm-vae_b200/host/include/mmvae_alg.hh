@@ -160,11 +160,15 @@ template <typename MAKE_MODEL>
 int
 run_vae_main(const mmvae_options_t &main_options, training_options_t &train_opt, bool is_vmf, MAKE_MODEL make_model)
 {
-    if (!file_exists(main_options.mtx)) return EXIT_FAILURE;
-    if (!file_exists(main_options.idx)) CHK(mmutil::index::build_mmutil_index(main_options.mtx, main_options.idx));
-    mmutil::index::mtx_header_t hdr;
-    CHK(mmutil::index::peek_bgzf_header(main_options.mtx, hdr));
-    const int64_t N = hdr.max_col;
+    const bool synthetic = main_options.syn_cells > 0;
+    int64_t N = main_options.syn_cells;
+    if (!synthetic) {
+        if (!file_exists(main_options.mtx)) return EXIT_FAILURE;
+        if (!file_exists(main_options.idx)) CHK(mmutil::index::build_mmutil_index(main_options.mtx, main_options.idx));
+        mmutil::index::mtx_header_t hdr;
+        CHK(mmutil::index::peek_bgzf_header(main_options.mtx, hdr));
+        N = hdr.max_col;
+    }
 
     // covariates (small: C x N) are read whole; each rank uploads its rows
     std::vector<float> covar;
@@ -178,7 +182,7 @@ run_vae_main(const mmvae_options_t &main_options, training_options_t &train_opt,
         covar_block.dense_all(covar);
         c_dim = covar_block.nfeature();
         has_covar = true;
-    } else if (main_options.out.size() > 0) {
+    } else if (main_options.out.size() > 0 && !synthetic) {
         // nb_vae_main.cc:67-73: the reference writes a 1 x N all-ones Matrix Market file next to the outputs,
         // indexes it and reads it back; the same two files are produced here (create_ones_like), while the
         // device path keeps the all-ones covariate implicit (no B x 1 tensor, K4's tuned kernel stays eligible)
@@ -205,7 +209,11 @@ run_vae_main(const mmvae_options_t &main_options, training_options_t &train_opt,
         dev.rank = g; dev.nranks = G; dev.shared = &shared;
         const int64_t lo = (int64_t)N * g / G, hi = (int64_t)N * (g + 1) / G;
         // ingest threads are shared between the ranks' readers
-        mmvae::mtx_data_block_t data(main_options.mtx, main_options.idx, main_options.batch_size, main_options.csr_cache, lo, hi);
+        std::unique_ptr<mmvae::mtx_data_block_t> data_p(
+            synthetic ? new mmvae::mtx_data_block_t(mmvae::mtx_data_block_t::synthetic_t(), N, main_options.syn_genes,
+                                                    main_options.syn_density, main_options.batch_size, train_opt.seed + 1234, lo, hi)
+                      : new mmvae::mtx_data_block_t(main_options.mtx, main_options.idx, main_options.batch_size, main_options.csr_cache, lo, hi));
+        mmvae::mtx_data_block_t &data = *data_p;
         std::vector<float> cshard;
         if (has_covar) cshard.assign(covar.begin() + lo * c_dim, covar.begin() + hi * c_dim);
         if (dev.upload(train_opt.device + g, data, has_covar ? &cshard : nullptr, c_dim) != EXIT_SUCCESS) { failed = 1; std::exit(1); }

@@ -311,6 +311,64 @@ public:
 
     const std::vector<Index> &index_tab() const { return index_tab_; }
 
+    // Benchmark hook (--synthetic N,D,density; not in the reference): the shard [col_lo, col_hi) of an N x D count matrix
+    // generated in memory instead of read from a file — cfg-4-sized runs of the mains need no 20 GB Matrix Market text.
+    // Per cell the gene ids advance by 1 + a geometric gap (so they are increasing and distinct, ~density * D nonzeros),
+    // counts are 1 + a small geometric; cell c's row depends only on (seed, c), so any sharding sees the same matrix.
+    struct synthetic_t { };
+    mtx_data_block_t(synthetic_t, Index ntot, Index nfeature, double density, const Index batch_size, uint64_t seed, Index col_lo = 0,
+                     Index col_hi = -1)
+        : mtx_file_("(synthetic)"), B_(batch_size), D_(nfeature), N_(ntot)
+    {
+        lo_ = std::max<Index>(0, col_lo);
+        hi_ = col_hi < 0 ? N_ : std::min<Index>(N_, col_hi);
+        ASSERT(lo_ < hi_ && D_ > 0 && density > 0. && density < 1., "--synthetic: empty shard or bad density");
+        const Index n = hi_ - lo_;
+        const int nthreads = (int)std::max<Index>(1, std::min<Index>(n / 1024, (Index)std::max(1u, std::thread::hardware_concurrency())));
+        std::vector<std::vector<int32_t>> idx((size_t)nthreads);
+        std::vector<std::vector<float>> val((size_t)nthreads);
+        std::vector<std::vector<int32_t>> len((size_t)nthreads);
+        const double lg = std::log1p(-density);
+        auto work = [&](int t) {
+            const Index c0 = lo_ + n * t / nthreads, c1 = lo_ + n * (t + 1) / nthreads;
+            idx[(size_t)t].reserve((size_t)((double)(c1 - c0) * (double)D_ * density * 1.05) + 64);
+            val[(size_t)t].reserve(idx[(size_t)t].capacity());
+            for (Index c = c0; c < c1; ++c) {
+                uint64_t st = (seed + 0x9E3779B97F4A7C15ull * (uint64_t)(c + 1)) | 1ull;
+                auto next = [&]() {                                 // xorshift64*
+                    st ^= st >> 12; st ^= st << 25; st ^= st >> 27;
+                    return (double)((st * 2685821657736338717ull) >> 11) * (1.0 / 9007199254740992.0);
+                };
+                int32_t cnt = 0;
+                for (double j = -1.;;) {
+                    j += 1. + std::floor(std::log(1. - next()) / lg);   // geometric gap, P(gap = k) = (1 - d)^k d
+                    if (j >= (double)D_) break;
+                    idx[(size_t)t].push_back((int32_t)j);
+                    val[(size_t)t].push_back(1.f + std::floor((float)(-1.4 * std::log(1. - next()))));
+                    ++cnt;
+                }
+                len[(size_t)t].push_back(cnt);
+            }
+        };
+        std::vector<std::thread> th;
+        for (int t = 0; t < nthreads; ++t) th.emplace_back(work, t);
+        for (auto &x : th) x.join();
+        indptr.assign((size_t)n + 1, 0);
+        size_t row = 0, total = 0;
+        for (int t = 0; t < nthreads; ++t)
+            for (int32_t l : len[(size_t)t]) { total += (size_t)l; indptr[++row] = (int64_t)total; }
+        indices.reserve(total);
+        values.reserve(total);
+        for (int t = 0; t < nthreads; ++t) {
+            indices.insert(indices.end(), idx[(size_t)t].begin(), idx[(size_t)t].end());
+            values.insert(values.end(), val[(size_t)t].begin(), val[(size_t)t].end());
+            std::vector<int32_t>().swap(idx[(size_t)t]);
+            std::vector<float>().swap(val[(size_t)t]);
+        }
+        TLOG("Synthetic counts: " << D_ << " features x " << N_ << " data points at density " << density << ", shard [" << lo_ << ", "
+                                  << hi_ << ") = " << total << " nonzeros resident as CSR");
+    }
+
     std::vector<int64_t> indptr;    // [N + 1]
     std::vector<int32_t> indices;   // gene ids, increasing inside a cell
     std::vector<float> values;

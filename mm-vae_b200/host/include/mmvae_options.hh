@@ -51,6 +51,10 @@ struct mmvae_options_t {
     int64_t batch_size;
     float kl_discount, kl_min, kl_max;
     bool csr_cache;   // NOT in the reference (long option only): keep the parsed CSR as ${idx}.csr for the next run
+    // NOT in the reference (long option only, benchmark hook): --synthetic N,D,density trains on an N x D count matrix
+    // generated in memory (mmvae_io.hh) instead of --mtx, so the mains run at cfg-4 size without a 20 GB text file
+    int64_t syn_cells = 0, syn_genes = 0;
+    double syn_density = 0.;
 };
 
 inline int
@@ -66,7 +70,8 @@ parse_mmvae_options(const int argc, const char *argv[], mmvae_options_t &options
                         "--covar       : a separate matrix market mtx for other covariates\n"
                         "--covar_idx   : an index file for the covar mtx (default: ${covar}.index)\n"
                         "--batch_size  : #samples in each batch (default: 100)\n"
-                        "--csr_cache   : keep the parsed counts as ${idx}.csr and reuse it while the mtx file is unchanged\n\n"
+                        "--csr_cache   : keep the parsed counts as ${idx}.csr and reuse it while the mtx file is unchanged\n"
+                        "--synthetic   : N,D,density - train on counts generated in memory instead of --mtx (benchmark hook)\n\n"
                         "--kl_discount : KL divergence discount (default: 0)\n"
                         "              : Loss = likelihood_loss + beta * KL_loss\n"
                         "              : where beta = exp(- ${discount} * epoch)\n"
@@ -82,6 +87,7 @@ parse_mmvae_options(const int argc, const char *argv[], mmvae_options_t &options
                                  { "batch", required_argument, nullptr, 'b' },      { "kl_discount", required_argument, nullptr, 'K' },
                                  { "kl_max", required_argument, nullptr, 'L' },     { "kl_min", required_argument, nullptr, 'l' },
                                  { "csr_cache", no_argument, nullptr, 1002 },       { "csr-cache", no_argument, nullptr, 1002 },
+                                 { "synthetic", required_argument, nullptr, 1003 },
                                  { "help", no_argument, nullptr, 'h' },             { nullptr, no_argument, nullptr, 0 } };
     bool help = false;
     mmvae_detail::scan_options(argc, argv, "M:I:O:V:J:r:c:a:b:K:L:l:h?", long_opts, [&](int opt, const char *arg) {
@@ -99,6 +105,12 @@ parse_mmvae_options(const int argc, const char *argv[], mmvae_options_t &options
         case 'l': options.kl_min = std::stof(arg); break;
         case 'L': options.kl_max = std::stof(arg); break;
         case 1002: options.csr_cache = true; break;
+        case 1003: {
+            long long n = 0, d = 0;
+            double rho = 0.;
+            if (std::sscanf(arg, "%lld,%lld,%lf", &n, &d, &rho) == 3) { options.syn_cells = n; options.syn_genes = d; options.syn_density = rho; }
+            break;
+        }
         case 'h': help = true; break;
         default: break;
         }
@@ -107,7 +119,7 @@ parse_mmvae_options(const int argc, const char *argv[], mmvae_options_t &options
         std::cerr << usage << std::endl;
         return EXIT_SUCCESS;
     }
-    ERR_RET(!file_exists(options.mtx), "missing mtx file");
+    ERR_RET(options.syn_cells <= 0 && !file_exists(options.mtx), "missing mtx file");
     ERR_RET(options.out.size() == 0, "need output file header");
     if (options.idx.size() == 0) options.idx = options.mtx + ".index";
     if (options.covar_idx.size() == 0) options.covar_idx = options.covar_mtx + ".index";

@@ -203,3 +203,26 @@ def test_mains_under_sanitizers(stub, tmp_path):
                            env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
         assert p.returncode == 0, p.stderr[-3000:]
     assert "binary CSR cache" in p.stderr or os.path.exists(str(tmp_path / "b.index") + ".csr")
+
+
+def test_synthetic_counts_hook(stub, tmp_path):
+    """--synthetic N,D,density (benchmark hook, not in the reference): no --mtx; every rank generates ITS shard of the same
+    matrix in memory (a cell's row depends only on the seed and the cell id), uploads it and runs the usual schedule."""
+    log = tmp_path / "calls.log"
+    env = dict(os.environ, LD_LIBRARY_PATH=str(stub), MMV_STUB_LOG=str(log))
+    cmd = [os.path.join(HOST, "bin", "nb_vae"), "--synthetic", "3000,300,0.05", "--out", str(tmp_path / "o"), "--batch_size", "256",
+           "--max_epoch", "1", "--nboot", "1", "--seed", "3", "--skip_param_record", "--ngpu", "2"]
+    p = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=120)
+    assert p.returncode == 0, p.stderr[-2000:]
+    ups = {}
+    for ln in open(log):
+        t = ln.split()
+        if t[0] == "csr_upload":
+            kv = dict(x.split("=", 1) for x in t[1:])
+            ups[int(kv["dev"])] = (int(kv["cells"]), int(kv["genes"]), int(kv["nnz"]), kv["covar"])
+    assert set(ups) == {0, 1}
+    for dev in (0, 1):
+        cells, genes, nnz, covar = ups[dev]
+        assert (cells, genes, covar) == (1500, 300, "0")
+        assert abs(nnz / (cells * genes) - 0.05) < 0.005          # geometric gaps: density * D nonzeros per cell on average
+    assert not os.path.exists(str(tmp_path / "o") + ".covar.mtx.gz")   # nothing to mirror: no input file
