@@ -82,7 +82,7 @@ def parse_args():
     ap.add_argument("--enc", default=None, help="encoder widths, comma separated (default: SURVEY cfg 4)")
     ap.add_argument("--dec", default=None, help="decoder widths, comma separated")
     ap.add_argument("--latent", type=int, default=None)
-    ap.add_argument("--dtype", default=None, choices=["bf16", "f32"],
+    ap.add_argument("--dtype", default=None, choices=["bf16", "f32", "f32x3"],
                     help="GEMM operand type: bf16 = tcgen05 tensor cores (fp32 accumulate), f32 = FFMA parity mode")
     ap.add_argument("--vmf-latent", action="store_true",
                     help="vmf model with the true von Mises-Fisher latent (not in the reference; DESIGN K8)")
@@ -464,7 +464,7 @@ def run_dp_check(mmv, model, ctx, csr, w, args, indptr, indices, values, rank, w
             m1 = mmv.Model.nb(ctx1, D, 1, w["enc"], w["dec"], w["latent"], w["nu_h"], w["nu_r"], seed=7)
         else:
             m1 = mmv.Model.vmf(ctx1, D, 1, w["latent"], w["enc"], w["dec"], seed=7)
-        m1.set_option("dtype", 1 if args.dtype == "bf16" else 0)
+        m1.set_option("dtype", {"f32": 0, "bf16": 1, "f32x3": 2}[args.dtype])
         m1.set_option("train_all_layers", 1)
         m1.set_params(P0)
         t1 = m1.step(csr1, np.arange(world * B_chk), eps=eps_all, kl_weight=1.0, flags=mmv.FWD | mmv.BWD | mmv.OPTIM)
@@ -559,7 +559,7 @@ def run_own(args):
         model = mmv.Model.nb(ctx, D, 1, w["enc"], w["dec"], w["latent"], w["nu_h"], w["nu_r"], seed=7)
     else:
         model = mmv.Model.vmf(ctx, D, 1, w["latent"], w["enc"], w["dec"], seed=7)
-    model.set_option("dtype", 1 if args.dtype == "bf16" else 0)
+    model.set_option("dtype", {"f32": 0, "bf16": 1, "f32x3": 2}[args.dtype])
     if args.vmf_latent:
         model.set_option("vmf_latent", 1)
     # train every layer (the reference's unregistered-Sequential bug freezes them; its autograd still

@@ -622,6 +622,30 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
     return 0;
 }
 
+// fp32 -> (hi, lo) bf16 pair, x = hi + lo up to 2^-17 relative: the operands of the error-compensated three-product GEMM
+// of the fp32-tolerance tensor-core mode ("dtype" 2: A B ~ A_hi B_lo + A_lo B_hi + A_hi B_hi, fp32 accumulation)
+__global__ void
+split_bf16_kernel(const float *x, __nv_bfloat16 *hi, __nv_bfloat16 *lo, size_t n)
+{
+    pdl_sync();
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float v = x[i];
+        const __nv_bfloat16 h = __float2bfloat16(v);
+        hi[i] = h;
+        lo[i] = __float2bfloat16(v - __bfloat162float(h));
+    }
+}
+
+int
+launch_split_bf16(const float *x, void *hi, void *lo, size_t n, cudaStream_t st)
+{
+    if (n == 0) return 0;
+    MMV_CUDA(launch_k(split_bf16_kernel, dim3((unsigned)min_sz((n + 255) / 256, 8192)), dim3(256), 0, st, x,
+                      reinterpret_cast<__nv_bfloat16 *>(hi), reinterpret_cast<__nv_bfloat16 *>(lo), n));
+    ::mmv::count_launch();
+    return 0;
+}
+
 // fp32 -> bf16 (activations entering a tensor-core GEMM)
 __global__ void
 to_bf16_kernel(const float *x, __nv_bfloat16 *y, size_t n)

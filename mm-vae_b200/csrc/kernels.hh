@@ -48,6 +48,8 @@ struct gemm_tc_args_t {
 bool gemm_tc_supported(const gemm_tc_args_t &g);
 int launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream);
 int launch_to_bf16(const float *x, void *y, size_t n, cudaStream_t st);
+// x = hi + lo (two bf16 arrays): operands of the three-product fp32-tolerance GEMM ("dtype" 2)
+int launch_split_bf16(const float *x, void *hi, void *lo, size_t n, cudaStream_t st);
 // SWIZZLE_128B tiled map over a row-major bf16 matrix [outer x inner] (leading dimension ld elements); map = CUtensorMap*
 int make_tma_map_bf16(void *map, const void *base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
                       uint32_t box_outer);
@@ -137,6 +139,7 @@ struct panel_args_t {
     int *rowptr = nullptr;                             // [B + 1] workspace
     int *bucket_ptr = nullptr;                         // [nT * (nK + 1)]
     uint32_t *ent = nullptr;                           // [nnz of the minibatch]
+    uint32_t *ent_lo = nullptr;                        // optional ("dtype" 2): same coordinates, value = what bf16 rounding of ent's value lost
     float *xraw = nullptr;                             // [nnz of the minibatch] raw counts, same order
 };
 inline int panel_tiles(int B) { return (B + 63) / 64; }
@@ -148,6 +151,10 @@ struct senc_tc_args_t {
     const uint32_t *ent = nullptr;
     int B = 0, D = 0, h1 = 0;
     const void *dense_bf16 = nullptr;   // fwd: effective W1^T [D x h1] bf16 ; bwd: delta [B x h1] bf16
+    // fp32-tolerance mode ("dtype" 2): residual copies of both operands.  The kernel then walks its K axis three times —
+    // (ent, dense_lo), (ent_lo, dense), (ent, dense) — into the same TMEM accumulator: A B ~ A_hi B_lo + A_lo B_hi + A_hi B_hi
+    const uint32_t *ent_lo = nullptr;
+    const void *dense_lo = nullptr;
     // forward epilogue: H1 = acc + bias_eff (ReLU optional), fp32 + bf16 copies
     const float *bias_eff = nullptr;
     int relu = 0;
@@ -355,6 +362,7 @@ int launch_sumsq_ranges(const float *const *g, const size_t *n, int count, doubl
 struct adam_args_t {
     float *param = nullptr, *grad = nullptr, *m = nullptr, *v = nullptr;
     void *param_bf16 = nullptr;       // optional bf16 mirror refreshed in the same pass
+    void *param_lo = nullptr;         // optional bf16 residual param - float(bf16(param)) ("dtype" 2), same pass
     size_t n = 0;
     const double *sumsq = nullptr;
     float *norm_out = nullptr;

@@ -120,6 +120,12 @@ struct mmv_model {
     bool use_tc = false;                  // "dtype" option: bf16 tcgen05 GEMMs (fp32 accumulate) vs fp32 FFMA
     void *params_bf16 = nullptr;          // bf16 mirror of `params` (same offsets), GEMM B operands
     bool bf16_dirty = true;
+    // "dtype" 2: fp32-tolerance mode ON the tensor cores.  Every GEMM operand is held as a bf16 pair x = hi + lo and a
+    // product is three tcgen05 GEMMs into one fp32 accumulation, A_hi B_lo + A_lo B_hi + A_hi B_hi (the dropped lo x lo
+    // term is 2^-16 relative).  params_lo is the residual mirror (Adam refreshes it with the bf16 mirror).
+    bool tc3 = false;
+    void *params_lo = nullptr;
+    std::map<const float *, void *> lo_cache;   // residual twins of this step's activation casts (cleared with bf_cache)
     bool top_grad_bf16 = false;           // K4 wrote the B x D gradient as bf16 into "dG.bf" this step
     std::map<const float *, const void *> bf_cache;   // activations already converted in this step
     uint64_t seed = 0;
@@ -457,7 +463,7 @@ mmv_model_destroy(mmv_model *m)
     cudaStreamSynchronize(m->ctx->stream);
     cudaFree(m->params); cudaFree(m->adam_m); cudaFree(m->adam_v);
     comm_free_grads(m->ctx, m->grads, m->grads_win, m->grads_nccl);
-    cudaFree(m->acc); cudaFree(m->fscal); cudaFree(m->params_bf16);
+    cudaFree(m->acc); cudaFree(m->fscal); cudaFree(m->params_bf16); cudaFree(m->params_lo);
     cudaFreeHost(m->h_acc); cudaFreeHost(m->h_fscal); cudaFreeHost(m->h_oob);
     for (auto &d : m->def) {
         if (d.acc) cudaFreeHost(d.acc);
@@ -488,7 +494,11 @@ mmv_model_set_option(mmv_model *m, const char *key, double value)
     else if (k == "profile") m->profile = value != 0;
     else if (k == "nb_fast") m->nb_fast = value != 0;
     else if (k == "comm_bf16") m->comm_bf16 = value != 0;
-    else if (k == "dtype") m->use_tc = value != 0;   // 0 = fp32 (parity mode), 1 = bf16 tensor-core GEMMs
+    else if (k == "dtype") {   // 0 = fp32 FFMA (parity mode), 1 = bf16 tensor-core GEMMs, 2 = fp32 tolerance on tensor cores (3 x bf16)
+        m->use_tc = value != 0;
+        m->tc3 = value == 2;
+        m->bf16_dirty = true;
+    }
     else if (k == "max_batch") { /* capacity hint; buffers grow on demand */ }
     else if (k == "vmf_latent") {
         MMV_CHECK(value == 0 || (m->is_vmf && m->R >= 3), "mmv_model_set_option: vmf_latent needs a vmf model with latent dim >= 3");
@@ -629,6 +639,20 @@ struct prof_scope_t {   // records a cudaEvent pair around a kernel group when p
 };
 #define PROF(name) prof_scope_t _prof_scope(m, name)
 
+// bf16 mirror (and, in fp32-tolerance mode, the residual mirror) of the whole parameter buffer after a host-side change
+int
+refresh_mirrors(mmv_model *m, cudaStream_t st)
+{
+    if (m->tc3) {
+        if (!m->params_lo) MMV_CUDA(cudaMalloc(&m->params_lo, m->n_all * 2));
+        MMV_TRY(launch_split_bf16(m->params, m->params_bf16, m->params_lo, m->n_all, st));
+    } else {
+        MMV_TRY(launch_to_bf16(m->params, m->params_bf16, m->n_all, st));
+    }
+    m->bf16_dirty = false;
+    return 0;
+}
+
 struct step_t {
     mmv_model *m;
     mmv_csr *csr;
@@ -666,11 +690,51 @@ bf16_of(const step_t &s, const float *p, size_t n, const void **out)
     MMV_CHECK(buf, "out of device memory: %s", mmv::get_error());
     {
         PROF("to_bf16");
-        MMV_TRY(launch_to_bf16(p, buf, n, s.st));
+        if (m->tc3) {   // hi and lo in one pass
+            void *lo = m->W(name + ".lo", n * 2);
+            MMV_CHECK(lo, "out of device memory: %s", mmv::get_error());
+            MMV_TRY(launch_split_bf16(p, buf, lo, n, s.st));
+            m->lo_cache[p] = lo;
+        } else {
+            MMV_TRY(launch_to_bf16(p, buf, n, s.st));
+        }
     }
     m->bf_cache[p] = buf;
     *out = buf;
     return 0;
+}
+
+// the residual twin of bf16_of ("dtype" 2): x - float(bf16(x)) in bf16
+int
+lo_of(const step_t &s, const float *p, size_t n, const void **out)
+{
+    mmv_model *m = s.m;
+    if (p >= m->params && p < m->params + m->n_all) {
+        *out = reinterpret_cast<const uint16_t *>(m->params_lo) + (p - m->params);
+        return 0;
+    }
+    const void *hi = nullptr;
+    MMV_TRY(bf16_of(s, p, n, &hi));   // (splits on first use)
+    auto it = m->lo_cache.find(p);
+    MMV_CHECK(it != m->lo_cache.end(), "lo_of: array has a bf16 copy without a residual");
+    *out = it->second;
+    return 0;
+}
+
+// One product in fp32-tolerance mode: t describes A_hi B_hi with the epilogue options; the two cross terms go first
+// (small addends first), everything accumulates in C through the GEMM's beta = 1 epilogue.
+int
+gemm3(const step_t &s, gemm_tc_args_t t, const void *A_lo, const void *B_lo)
+{
+    gemm_tc_args_t u = t;
+    u.bias = nullptr; u.relu = 0; u.Cb = nullptr; u.sumsq = nullptr; u.sumsq_done = nullptr;
+    u.row_stats = nullptr; u.row_stats_tiles = nullptr;
+    u.B = B_lo;
+    MMV_TRY(launch_gemm_tc(u, s.st));            // beta C + A_hi B_lo
+    u.A = A_lo; u.B = t.B; u.beta = 1.f;
+    MMV_TRY(launch_gemm_tc(u, s.st));            // + A_lo B_hi
+    t.beta = 1.f; t.Cb = nullptr; t.sumsq = nullptr; t.sumsq_done = nullptr; t.row_stats = nullptr; t.row_stats_tiles = nullptr;
+    return launch_gemm_tc(t, s.st);              // + A_hi B_hi (+ bias, ReLU)
 }
 
 // "<name>.bf" twin of an fp32 workspace array, registered so bf16_of() finds it without a cast kernel:
@@ -679,6 +743,7 @@ void *
 bf16_twin(const step_t &s, const float *p, size_t n)
 {
     mmv_model *m = s.m;
+    if (m->tc3) return nullptr;   // (the consumer needs hi AND lo: it splits the fp32 array itself)
     std::string name;
     for (auto &kv : m->ws) if (kv.second.p == (const void *)p) { name = kv.first; break; }
     if (name.empty()) return nullptr;
@@ -711,6 +776,12 @@ lin_fwd(const step_t &s, const float *X, int in, const float *W, const float *b,
         }
         t.row_stats = row_stats; t.row_stats_tiles = row_stats_tiles;
         PROF(tag);
+        if (m->tc3) {
+            const void *Al = nullptr, *Bl = nullptr;
+            MMV_TRY(lo_of(s, X, (size_t)s.B * in, &Al));
+            MMV_TRY(lo_of(s, W, (size_t)out * in, &Bl));
+            return gemm3(s, t, Al, Bl);
+        }
         return launch_gemm_tc(t, s.st);
     }
     PROF(tag);
@@ -736,6 +807,13 @@ lin_bwd_data(const step_t &s, const float *dY, int out, const float *W, int in, 
             t.ldcb = in;
         }
         PROF(tag);
+        if (m->tc3) {
+            MMV_CHECK(dY != nullptr, "lin_bwd_data: the fp32-tolerance mode needs an fp32 gradient");
+            const void *Al = nullptr, *Bl = nullptr;
+            MMV_TRY(lo_of(s, dY, (size_t)s.B * out, &Al));
+            MMV_TRY(lo_of(s, W, (size_t)out * in, &Bl));
+            return gemm3(s, t, Al, Bl);
+        }
         return launch_gemm_tc(t, s.st);
     }
     MMV_CHECK(dY != nullptr, "lin_bwd_data: fp32 path needs an fp32 gradient");
@@ -759,7 +837,16 @@ lin_bwd_weight(const step_t &s, const float *dY, int out, const float *X, int in
         t.a_mn = 1; t.lda = out; t.b_mn = 1; t.ldb = in; t.C = dW; t.ldc = in; t.M = out; t.N = in; t.K = s.B;
         t.beta = beta; t.sumsq = sumsq; t.sumsq_done = sumsq_done;
         PROF(tag);
-        MMV_TRY(launch_gemm_tc(t, s.st));
+        if (m->tc3) {
+            MMV_CHECK(dY != nullptr, "lin_bwd_weight: the fp32-tolerance mode needs an fp32 gradient");
+            const void *Al = nullptr, *Bl = nullptr;
+            MMV_TRY(lo_of(s, dY, (size_t)s.B * out, &Al));
+            MMV_TRY(lo_of(s, X, (size_t)s.B * in, &Bl));
+            if (sumsq_done) *sumsq_done = 0;
+            MMV_TRY(gemm3(s, t, Al, Bl));
+        } else {
+            MMV_TRY(launch_gemm_tc(t, s.st));
+        }
     } else if (dW) {
         MMV_CHECK(dY != nullptr, "lin_bwd_weight: fp32 path needs an fp32 gradient");
         PROF(tag);
@@ -878,7 +965,7 @@ allreduce_grad_async(const step_t &s, int t)
     // tensor-core mode: these gradients are sums of products of bf16 operands (dlogits, activations); rounding the
     // per-rank partial sums to bf16 for the wire stays inside that mode's 1e-2 budget and halves the bytes.  fp32 mode
     // reduces in fp32, bit for bit as before.
-    MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off, n, m->use_tc && m->comm_bf16));
+    MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off, n, m->use_tc && !m->tc3 && m->comm_bf16));
     m->ar_done.emplace_back(off, off + n);
     return 0;
 }
@@ -1018,7 +1105,9 @@ bool
 senc_tc_ok(const step_t &s)
 {
     const mmv_model *m = s.m;
-    return m->use_tc && senc_tc_supported(m->enc[0].out) && m->H <= 128 && (m->D % 8 == 0 || true);
+    // (fp32-tolerance mode: nb's first layer runs the three-segment densify GEMM; vmf's angular first layer, whose
+    // effective weight is materialised in bf16, stays on the fp32 gather / gene-major kernels, K1')
+    return m->use_tc && !(m->tc3 && m->is_vmf) && senc_tc_supported(m->enc[0].out) && m->H <= 128 && (m->D % 8 == 0 || true);
 }
 
 // Re-bucket the minibatch into the tiled-COO panel ("pan_*" workspaces) and run the densify GEMM
@@ -1039,6 +1128,7 @@ senc_tc_forward(const step_t &s, const senc_args_t &e, const void *w1eff_bf16)
     p.rowptr = (int *)WS("pan_rowptr", B + 1); p.bucket_ptr = (int *)WS("pan_bptr", (size_t)nT * (nK + 1));
     p.ent = (uint32_t *)WS("pan_ent", cap); p.xraw = WS("pan_x", cap);
     NEED(p.rowptr); NEED(p.bucket_ptr); NEED(p.ent); NEED(p.xraw);
+    if (m->tc3) { p.ent_lo = (uint32_t *)WS("pan_ent_lo", cap); NEED(p.ent_lo); }
     {
         PROF("panel_build");
         MMV_TRY(launch_panel_build(p, s.st));
@@ -1046,12 +1136,13 @@ senc_tc_forward(const step_t &s, const senc_args_t &e, const void *w1eff_bf16)
     senc_tc_args_t a;
     a.bucket_ptr = p.bucket_ptr; a.ent = p.ent; a.B = B; a.D = D; a.h1 = h1;
     a.dense_bf16 = w1eff_bf16; a.bias_eff = e.bias_eff; a.relu = e.relu; a.H1 = e.H1;
+    if (m->tc3) { a.ent_lo = p.ent_lo; MMV_TRY(lo_of(s, e.W1T, (size_t)D * h1, &a.dense_lo)); }
     a.H1_bf16 = m->W("enc_act0.bf", (size_t)B * h1 * 2); NEED(a.H1_bf16);
     {
         PROF("senc_fwd");
         MMV_TRY(launch_senc_tc_fwd(a, s.st));
     }
-    m->bf_cache[e.H1] = a.H1_bf16;
+    if (!m->tc3) m->bf_cache[e.H1] = a.H1_bf16;   // (fp32-tolerance mode: the consumer splits H1 into hi + lo itself)
     return 0;
 }
 
@@ -1065,6 +1156,7 @@ senc_tc_backward(const step_t &s, const senc_bwd_args_t &b)
     a.bucket_ptr = m->ws["pan_bptr"].as<int>(); a.ent = m->ws["pan_ent"].as<uint32_t>();
     a.B = B; a.D = D; a.h1 = h1;
     MMV_TRY(bf16_of(s, b.delta, (size_t)B * h1, &a.dense_bf16));
+    if (m->tc3) { a.ent_lo = m->ws["pan_ent_lo"].as<uint32_t>(); MMV_TRY(lo_of(s, b.delta, (size_t)B * h1, &a.dense_lo)); }
     a.W1T = b.W1T; a.col_scale = b.col_scale; a.Delta = b.Delta; a.inv_t = b.inv_t; a.x_mean = b.x_mean;
     a.angular = b.angular; a.accumulate = b.accumulate; a.dW1T = b.dW1T;
     // raw product straight into the gradient when it is overwritten anyway, else into a scratch buffer
@@ -1094,7 +1186,7 @@ senc_tc_backward(const step_t &s, const senc_bwd_args_t &b)
             trace_mark(m->ctx, "first-layer dW part done");
             // a small last part is not worth a launch of its own: it goes with the step's grouped leftovers
             if (t1 == tiles && t0 > 0 && (r1 - r0) * sizeof(float) < ((size_t)16 << 20)) break;
-            MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off + r0, r1 - r0, m->use_tc && m->comm_bf16));
+            MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off + r0, r1 - r0, m->use_tc && !m->tc3 && m->comm_bf16));
             m->ar_done.emplace_back(off + r0, off + r1);
         }
     } else {
@@ -1141,7 +1233,7 @@ nb_forward_backward(const step_t &s)
         k.recon_mu = WS("recon_mu", (size_t)B * D); k.recon_nu = WS("recon_nu", (size_t)B * D);
         NEED(k.recon_mu); NEED(k.recon_nu);
     }
-    m->top_grad_bf16 = s.bwd && tc_ok(s, D, Ld.in, B, D, Ld.in) && tc_ok(s, B, Ld.in, D, D, Ld.in);
+    m->top_grad_bf16 = s.bwd && !m->tc3 && tc_ok(s, D, Ld.in, B, D, Ld.in) && tc_ok(s, B, Ld.in, D, D, Ld.in);
     if (m->top_grad_bf16) {
         k.dlogits_bf16 = m->W("dG.bf", (size_t)B * D * 2); NEED(k.dlogits_bf16);
     } else if (s.bwd) {
@@ -1159,7 +1251,7 @@ nb_forward_backward(const step_t &s)
     const bool tc_senc = senc_tc_ok(s);
     const void *w1b = nullptr;
     if (tc_senc) MMV_TRY(bf16_of(s, m->P(L0.w), (size_t)D * h1, &w1b));
-    if (tc_senc && senc_bias_bf16_supported(h1))   // the mean shift against the same bf16 weights the GEMM multiplies with
+    if (tc_senc && !m->tc3 && senc_bias_bf16_supported(h1))   // the mean shift against the same bf16 weights the GEMM multiplies with
         MMV_TRY(launch_senc_bias_bf16(w1b, m->P(m->t_x_mean), inv_t, bias_eff, D, h1, s.st));
     else
         MMV_TRY(launch_senc_bias(m->P(L0.w), m->P(m->t_x_mean), inv_t, nullptr, bias_eff, D, h1, 0, s.st));
@@ -1236,6 +1328,7 @@ nb_forward_backward(const step_t &s)
         MMV_TRY(launch_nb_likelihood(k, m->ctx->num_sms, s.st));
     }
     m->bf_cache.erase(k.G);   // G may now hold the gradient (in-place fp32 mode)
+    m->lo_cache.erase(k.G);
     if (!s.bwd) return 0;
 
     // per-gene sums of dlogits: mu_decoding.bias, covar_decoding.{bias,weight}, mu_bias
@@ -1370,7 +1463,7 @@ vmf_forward_backward(const step_t &s)
     k.unsorted = s.csr->d_unsorted;
     k.slice_bounds = (int64_t *)WS("k4_bounds", (size_t)B * 9 * 2); NEED(k.slice_bounds);
     // tuned kernel + tensor-core GEMMs behind it: the B x D gradient leaves K5 as bf16
-    m->top_grad_bf16 = s.bwd && k.allow_fast && vmf_likelihood_fast_eligible(k) && tc_ok(s, D, Ld.in, B, D, Ld.in) &&
+    m->top_grad_bf16 = s.bwd && !m->tc3 && k.allow_fast && vmf_likelihood_fast_eligible(k) && tc_ok(s, D, Ld.in, B, D, Ld.in) &&
         tc_ok(s, B, Ld.in, D, D, Ld.in);
     if (s.bwd) {
         if (m->top_grad_bf16) { k.dpre_bf16 = m->W("dG.bf", (size_t)B * D * 2); NEED(k.dpre_bf16); }
@@ -1384,6 +1477,7 @@ vmf_forward_backward(const step_t &s)
         MMV_TRY(launch_vmf_likelihood(k, m->ctx->num_sms, s.st));
     }
     m->bf_cache.erase(k.G);   // G now holds dL/dpre
+    m->lo_cache.erase(k.G);
 
     // scalar part: loss constant, lbessel (operators.hh:49-101) and d ln_kappa (operators.hh:13-47)
     vmf_scalar_args_t sc;
@@ -1585,9 +1679,10 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         if (csr->ev_ready) MMV_CUDA(cudaStreamWaitEvent(st, csr->ev_ready, 0));   // streamed slot: its upload is done
         m->last_B = B;
         m->bf_cache.clear();
+    m->lo_cache.clear();
+        m->lo_cache.clear();
         if (m->use_tc && m->bf16_dirty) {
-            MMV_TRY(launch_to_bf16(m->params, m->params_bf16, m->n_all, st));
-            m->bf16_dirty = false;
+            MMV_TRY(refresh_mirrors(m, st));
         }
         MMV_CUDA(cudaMemsetAsync(m->acc, 0, sizeof(double) * 8, st));
         if (s.bwd) m->grad_lazy = false;
@@ -1669,7 +1764,7 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
             a.write_grad = 0;
             m->grad_lazy = true; m->grad_lazy_n = n_opt;
         }
-        if (m->use_tc && !m->bf16_dirty) a.param_bf16 = m->params_bf16;
+        if (m->use_tc && !m->bf16_dirty) { a.param_bf16 = m->params_bf16; a.param_lo = m->tc3 ? m->params_lo : nullptr; }
         else m->bf16_dirty = true;
         a.max_norm = m->grad_clip; a.weight_decay = m->weight_decay;
         a.bc2_sqrt = (float)std::sqrt(bc2); a.neg_step = (float)(-(double)m->lr / bc1);
@@ -1818,10 +1913,7 @@ mmv_encode(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, float *m
     if (csr->ev_ready) MMV_CUDA(cudaStreamWaitEvent(st, csr->ev_ready, 0));
     m->last_B = B;
     m->bf_cache.clear();
-    if (m->use_tc && m->bf16_dirty) {
-        MMV_TRY(launch_to_bf16(m->params, m->params_bf16, m->n_all, st));
-        m->bf16_dirty = false;
-    }
+    if (m->use_tc && m->bf16_dirty) MMV_TRY(refresh_mirrors(m, st));
     const int D = (int)m->D;
     const linear_t &L0 = m->enc[0];
     const int h1 = L0.out;

@@ -138,6 +138,14 @@ adam_kernel(adam_args_t a)
             pk.x = *reinterpret_cast<const uint32_t *>(&lo);
             pk.y = *reinterpret_cast<const uint32_t *>(&hi);
             reinterpret_cast<uint2 *>(a.param_bf16)[i] = pk;
+            if (a.param_lo) {   // what the bf16 mirror lost, again in bf16: mirror + residual carry ~16 mantissa bits
+                const __nv_bfloat162 rl = __floats2bfloat162_rn(pn[0] - __low2float(lo), pn[1] - __high2float(lo));
+                const __nv_bfloat162 rh = __floats2bfloat162_rn(pn[2] - __low2float(hi), pn[3] - __high2float(hi));
+                uint2 pr;
+                pr.x = *reinterpret_cast<const uint32_t *>(&rl);
+                pr.y = *reinterpret_cast<const uint32_t *>(&rh);
+                reinterpret_cast<uint2 *>(a.param_lo)[i] = pr;
+            }
         }
     }
     for (size_t i = n4 * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += (size_t)gridDim.x * blockDim.x) {
@@ -152,7 +160,11 @@ adam_kernel(adam_args_t a)
         const float denom = sqrtf(v) / a.bc2_sqrt + a.eps;
         const float pn = p + (a.neg_step * m) / denom;
         a.param[i] = pn;
-        if (a.param_bf16) reinterpret_cast<__nv_bfloat16 *>(a.param_bf16)[i] = __float2bfloat16(pn);
+        if (a.param_bf16) {
+            const __nv_bfloat16 h = __float2bfloat16(pn);
+            reinterpret_cast<__nv_bfloat16 *>(a.param_bf16)[i] = h;
+            if (a.param_lo) reinterpret_cast<__nv_bfloat16 *>(a.param_lo)[i] = __float2bfloat16(pn - __bfloat162float(h));
+        }
     }
 }
 

@@ -192,6 +192,11 @@ panel_build_kernel(panel_args_t p, int nK, int nS)
                 const int pos = base + atomicAdd(&s_cur[(j[u] >> 6) - k_lo], 1);
                 const uint32_t bits = (uint32_t)__bfloat16_as_ushort(__float2bfloat16(v));
                 p.ent[pos] = ((uint32_t)r << 26) | ((uint32_t)(j[u] & 63) << 20) | bits;
+                if (p.ent_lo) {
+                    const float lo = v - __bfloat162float(__ushort_as_bfloat16((unsigned short)bits));
+                    p.ent_lo[pos] = ((uint32_t)r << 26) | ((uint32_t)(j[u] & 63) << 20) |
+                                    (uint32_t)__bfloat16_as_ushort(__float2bfloat16(lo));
+                }
                 p.xraw[pos] = x[u];
                 depth = fmaf(x[u], wd[u], depth);
                 hn0 = fmaf(x[u], wn[u], hn0);
@@ -301,8 +306,8 @@ scatter_entry(uint8_t *tileA, uint32_t e, int rowbase)
 
 template <int BN, bool BWD>
 __global__ void __launch_bounds__(TCT, 1)
-senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmS, senc_tc_args_t a, int nT,
-               int nK)
+senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmS,
+               const __grid_constant__ CUtensorMap tmDlo, senc_tc_args_t a, int nT, int nK)
 {
     using cfg = tc_cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
@@ -314,7 +319,10 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ 
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.y + (BWD ? a.tile0 : 0), n0 = blockIdx.x * BN;
-    const int num_kb = BWD ? nT : nK;
+    // K axis = base_kb pipeline stages (gene chunks forward, cell tiles backward), walked once — or, in the fp32-tolerance
+    // mode, three times with different operand copies (segment 0: panel hi x dense lo, 1: panel lo x dense hi, 2: hi x hi)
+    const int base_kb = BWD ? nT : nK;
+    const int num_kb = a.ent_lo ? 3 * base_kb : base_kb;
 
     if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmD) : "memory");
     if (warp == 1 && lane == 0) {
@@ -346,8 +354,10 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ 
                 const uint32_t sb = smem_u32(smem + s * cfg::STAGE + A_TILE);
                 const uint32_t fb = fullb0 + 8 * s;
                 mbar_expect_tx(fb, cfg::B_TILE);
+                const int seg = kb / base_kb, kk = kb - seg * base_kb;
+                const CUtensorMap *tm = (a.ent_lo && seg == 0) ? &tmDlo : &tmD;
 #pragma unroll
-                for (int i = 0; i < BN / 64; ++i) tma_load_2d(sb + i * 8192, &tmD, fb, n0 + 64 * i, kb * BK);
+                for (int i = 0; i < BN / 64; ++i) tma_load_2d(sb + i * 8192, tm, fb, n0 + 64 * i, kk * BK);
             }
         }
     } else if (warp == 1) {
@@ -376,7 +386,6 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ 
         const int grp = (warp - 4) >> 2;
         const int t = threadIdx.x - 128 - 128 * grp;   // 0..127 inside the group
         const int *__restrict__ bp = a.bucket_ptr;
-        const uint32_t *__restrict__ ent = a.ent;
         int4 *rtab = reinterpret_cast<int4 *>(smem + STG * cfg::STAGE + 256) + grp * RT;   // run table of this group
         const int n_own = (num_kb - grp + 1) / 2;      // stages grp, grp + 2, ...
 
@@ -384,13 +393,18 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ 
             asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
             for (int i = t; i < RT; i += 128)
                 if (i0 + i < n_own) {
-                    const run2_t r = stage_runs<BWD>(bp, grp + 2 * (i0 + i), tile, nT, nK);
+                    const run2_t r = stage_runs<BWD>(bp, (grp + 2 * (i0 + i)) % base_kb, tile, nT, nK);
                     rtab[i] = make_int4(r.b0, r.n0, r.b1, r.n1);
                 }
             asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
         };
+        // the panel copy a stage reads: the residual values in segment 1 of the fp32-tolerance mode
+        auto ent_of = [&](int i) -> const uint32_t * {
+            return (a.ent_lo && (grp + 2 * i) / base_kb == 1) ? a.ent_lo : a.ent;
+        };
         auto load = [&](uint32_t (&e)[PF], int i) {
             const int4 r = rtab[i % RT];
+            const uint32_t *__restrict__ ent = ent_of(i);
 #pragma unroll
             for (int q = 0; q < PF; ++q) {
                 const int x = t + 128 * q;
@@ -401,6 +415,7 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ 
             const int kb = grp + 2 * i, s = kb % STG;
             const int4 r = rtab[i % RT];
             const int n = r.y + r.w;
+            const uint32_t *__restrict__ ent = ent_of(i);
             mbar_wait(empty0 + 8 * s, ((kb / STG) & 1) ^ 1);
             uint8_t *tileA = smem + s * cfg::STAGE;
             const uint4 z = make_uint4(0u, 0u, 0u, 0u);
@@ -425,6 +440,7 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ 
         auto l2_prefetch = [&](int i, int i1) {
             if (i >= i1) return;
             const int4 r = rtab[i % RT];
+            const uint32_t *ent = ent_of(i);
             if (t * 32 < r.y) asm volatile("prefetch.global.L2 [%0];" ::"l"(ent + r.x + t * 32));
             if (t * 32 < r.w) asm volatile("prefetch.global.L2 [%0];" ::"l"(ent + r.z + t * 32));
         };
@@ -538,12 +554,14 @@ launch_tc(const senc_tc_args_t &a, cudaStream_t st)
     CUtensorMap tm;
     // dense operand: rows = K index (genes fwd / cells bwd), h1 contiguous
     MMV_TRY(make_tma_map_bf16(&tm, a.dense_bf16, (uint64_t)a.h1, (uint64_t)(BWD ? a.B : a.D), (uint64_t)a.h1, 64, BK));
-    CUtensorMap ts = tm;
+    CUtensorMap ts = tm, tlo = tm;
     if (BWD) MMV_TRY(make_tma_map_f32(&ts, a.S, (uint64_t)a.h1, (uint64_t)a.D, (uint64_t)a.h1, 32, 32));
+    MMV_CHECK((a.ent_lo == nullptr) == (a.dense_lo == nullptr), "senc_tc: the fp32-tolerance mode needs both residual operands");
+    if (a.dense_lo) MMV_TRY(make_tma_map_bf16(&tlo, a.dense_lo, (uint64_t)a.h1, (uint64_t)(BWD ? a.B : a.D), (uint64_t)a.h1, 64, BK));
     auto kern = senc_tc_kernel<BN, BWD>;
     MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(kern), cfg::SMEM));
     dim3 grid(ceil_div(a.h1, BN), BWD ? (a.ntiles > 0 ? a.ntiles : ceil_div(a.D, BM)) : ceil_div(a.B, BM));
-    MMV_CUDA(launch_k(kern, grid, dim3(TCT), cfg::SMEM, st, tm, ts, a, nT, nK));
+    MMV_CUDA(launch_k(kern, grid, dim3(TCT), cfg::SMEM, st, tm, ts, tlo, a, nT, nK));
     ::mmv::count_launch();
     return 0;
 }

@@ -3,6 +3,9 @@
 TAG=${1:-r02n2}
 O=gpurun_out; mkdir -p $O
 ( time timeout 1200 python -m pytest tests/test_gpu_multi.py tests/test_gpu_host_main.py -q -rs -k "data_parallel or two_gpus" ) > $O/${TAG}_pytest.log 2>&1; tail -12 $O/${TAG}_pytest.log
+# fp32 tolerance on the tensor cores ("dtype" 2): the new parity cases, then a bench line (one GPU)
+( CUDA_VISIBLE_DEVICES=0 timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_edge.py -q -rs -k "f32x3" ) > $O/${TAG}_pytest_f32x3.log 2>&1; tail -15 $O/${TAG}_pytest_f32x3.log
+( CUDA_VISIBLE_DEVICES=0 timeout 300 python bench.py --dtype f32x3 --cells 65536 --steps 10 --warmup 3 --no-cpu-baseline ) > $O/${TAG}_bench_f32x3.log 2>&1; tail -c 1500 $O/${TAG}_bench_f32x3.log
 for W in 1 0; do
   MMV_COMM_BF16=$W timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
       bench.py --gpus 2 --steps 60 --warmup 5 --no-cpu-baseline > $O/${TAG}_bench_wire$W.log 2>&1

@@ -102,7 +102,8 @@ def main_gpu():
     dist.broadcast(e0, src=0)
     if rank != 0:
         assert not torch.equal(e, e0), "every rank drew the same reparameterisation noise"
-        assert abs(float((e * e0).mean())) < 0.05 and abs(float(e.std()) - 1.0) < 0.05
+        n_e = e.numel()   # independent N(0,1) streams: sample correlation ~ N(0, 1/n), sample std ~ N(1, 1/(2n)); 4 sigma
+        assert abs(float((e * e0).mean())) < 4.0 / n_e ** 0.5 and abs(float(e.std()) - 1.0) < 4.0 / (2 * n_e) ** 0.5
     # ---- single GPU on the concatenated batch (own context without a communicator)
     ctx1 = mmv.Context(local)
     csr1 = mmv.CSR.from_dense(ctx1, x, None)
