@@ -324,7 +324,15 @@ mmv_comm_init(mmv_ctx *ctx, int nranks, int rank, const unsigned char id[128])
     setenv("NCCL_ALGO", "Ring", 0);
     MMV_NCCL(g_nccl.CommInitRank(&comm, nranks, u, rank));
     ctx->nccl_comm = comm;
-    MMV_CUDA(cudaStreamCreateWithFlags(&ctx->comm_stream, cudaStreamNonBlocking));
+    // highest priority: the reductions run UNDER backward, whose GEMMs keep every SM busy; at default priority NCCL's
+    // CTAs queue behind them and the first 123 MB bucket takes 0.64 ms instead of 0.37 (profiles/r02n8_*_trace.txt)
+    int prio_least = 0, prio_greatest = 0;
+    MMV_CUDA(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
+    {
+        const char *e = getenv("MMV_COMM_PRIORITY");
+        const bool high = e ? atoi(e) != 0 : true;
+        MMV_CUDA(cudaStreamCreateWithPriority(&ctx->comm_stream, cudaStreamNonBlocking, high ? prio_greatest : prio_least));
+    }
     MMV_CUDA(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
     MMV_CUDA(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
     MMV_CUDA(cudaEventRecord(ctx->ev_join, ctx->comm_stream));

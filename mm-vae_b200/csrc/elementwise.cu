@@ -455,20 +455,22 @@ colsum_bf16x8_kernel(colsum_args_t a)
 #pragma unroll
     for (int q = 0; q < 8; ++q) s[q] = 0.f;
     if (col < a.N) {
-        const __nv_bfloat16 *X = reinterpret_cast<const __nv_bfloat16 *>(a.Xb) + col;
-        for (int i = r0 + warp; i < r1; i += 32) {
-            uint4 v[4];
+        for (int pass = 0; pass < (a.Xb2 ? 2 : 1); ++pass) {   // second pass: the residual array of a hi + lo pair
+            const __nv_bfloat16 *X = reinterpret_cast<const __nv_bfloat16 *>(pass ? a.Xb2 : a.Xb) + col;
+            for (int i = r0 + warp; i < r1; i += 32) {
+                uint4 v[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
-                v[u] = i + 8 * u < r1 ? *reinterpret_cast<const uint4 *>(X + (size_t)(i + 8 * u) * a.ldx)
-                                      : make_uint4(0u, 0u, 0u, 0u);
+                for (int u = 0; u < 4; ++u)
+                    v[u] = i + 8 * u < r1 ? *reinterpret_cast<const uint4 *>(X + (size_t)(i + 8 * u) * a.ldx)
+                                          : make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const uint32_t w[4] = { v[u].x, v[u].y, v[u].z, v[u].w };
+                for (int u = 0; u < 4; ++u) {
+                    const uint32_t w[4] = { v[u].x, v[u].y, v[u].z, v[u].w };
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    s[2 * q] += __uint_as_float(w[q] << 16);
-                    s[2 * q + 1] += __uint_as_float(w[q] & 0xFFFF0000u);
+                    for (int q = 0; q < 4; ++q) {
+                        s[2 * q] += __uint_as_float(w[q] << 16);
+                        s[2 * q + 1] += __uint_as_float(w[q] & 0xFFFF0000u);
+                    }
                 }
             }
         }
@@ -495,6 +497,9 @@ launch_colsum(colsum_args_t a, cudaStream_t st)
 {
     if (a.M <= 0 || a.N <= 0) return 0;
     MMV_CHECK(a.C <= 8, "colsum: covariate dim %d > 8 not supported", a.C);
+    MMV_CHECK(!a.Xb2 || (a.Xb && a.cov == nullptr && a.N % 8 == 0 && a.ldx % 8 == 0 && a.N >= 256 &&
+                         ((reinterpret_cast<uintptr_t>(a.Xb) | reinterpret_cast<uintptr_t>(a.Xb2)) & 15) == 0),
+              "colsum: a hi + lo bf16 pair needs the 8-column kernel (N %% 8 == 0, N >= 256, all-ones covariates)");
     if (a.Xb && a.cov == nullptr && a.N % 8 == 0 && a.ldx % 8 == 0 && (reinterpret_cast<uintptr_t>(a.Xb) & 15) == 0 &&
         a.N >= 256) {
         a.rows_per_cta = 256;

@@ -50,6 +50,7 @@ struct params_t {
     double *sumsq; // persistent store epilogue: += sum of squares of the product
     float2 *row_stats;   // persistent store epilogue: [tiles_n x M] softmax partials (max log2(e), sum exp2) per row and column tile
     int n_fast;    // persistent tile order: 1 = consecutive tiles walk N (A tile reused from L2), 0 = walk M (B tile reused)
+    int segs;      // 1, or 3 = fp32-tolerance mode: the K axis is walked three times (A_hi B_lo, A_lo B_hi, A_hi B_hi) into one accumulator
 };
 
 // STAGES = 3: two CTAs per SM (many-tile grids) ; STAGES = 6: one CTA per SM with a deeper ring, for
@@ -57,7 +58,8 @@ struct params_t {
 template <bool A_MN, bool B_MN, int STAGES>
 __global__ void __launch_bounds__(THREADS, STAGES <= 3 ? 2 : 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ CUtensorMap tmC, params_t p)
+               const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAlo,
+               const __grid_constant__ CUtensorMap tmBlo, params_t p)
 {
     extern __shared__ uint8_t smem_raw[];
     // SWIZZLE_128B operands need 1024-byte alignment
@@ -69,7 +71,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.y * BLOCK_M, n0 = blockIdx.x * BLOCK_N;
     // split-K (gridDim.z > 1): this CTA owns k-blocks [kb0, kb0 + num_kb) and adds its partial tile atomically
-    const int total_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+    const int base_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+    const int total_kb = base_kb * p.segs;
     const int kb_per = (total_kb + (int)gridDim.z - 1) / (int)gridDim.z;
     const int kb0 = blockIdx.z * kb_per;
     const int num_kb = max(0, min(total_kb - kb0, kb_per));
@@ -108,18 +111,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const uint32_t sa = smem_u32(smem + s * STAGE_BYTES), sb = sa + A_BYTES;
                 const uint32_t fb = full0 + 8 * s;
                 mbar_expect_tx(fb, STAGE_BYTES);
-                const int k0 = (kb0 + kb) * BLOCK_K;
+                // segment of the K walk: 0 = A_hi B_lo, 1 = A_lo B_hi, 2 (and the only one of a plain product) = A_hi B_hi
+                const int g = kb0 + kb, seg = p.segs == 3 ? g / base_kb : 2;
+                const int k0 = (p.segs == 3 ? g - seg * base_kb : g) * BLOCK_K;
+                const CUtensorMap *mA = seg == 1 ? &tmAlo : &tmA, *mB = seg == 0 ? &tmBlo : &tmB;
                 if (A_MN) {     // tensor dims {MN, K}: two [64 k x 64 m] boxes
-                    tma_load_2d(sa, &tmA, fb, m0, k0);
-                    tma_load_2d(sa + A_BYTES / 2, &tmA, fb, m0 + 64, k0);
+                    tma_load_2d(sa, mA, fb, m0, k0);
+                    tma_load_2d(sa + A_BYTES / 2, mA, fb, m0 + 64, k0);
                 } else {        // tensor dims {K, MN}: one [128 m x 64 k] box
-                    tma_load_2d(sa, &tmA, fb, k0, m0);
+                    tma_load_2d(sa, mA, fb, k0, m0);
                 }
                 if (B_MN) {
-                    tma_load_2d(sb, &tmB, fb, n0, k0);
-                    tma_load_2d(sb + B_BYTES / 2, &tmB, fb, n0 + 64, k0);
+                    tma_load_2d(sb, mB, fb, n0, k0);
+                    tma_load_2d(sb + B_BYTES / 2, mB, fb, n0 + 64, k0);
                 } else {
-                    tma_load_2d(sb, &tmB, fb, k0, n0);
+                    tma_load_2d(sb, mB, fb, k0, n0);
                 }
             }
         }
@@ -256,7 +262,8 @@ constexpr int P_SMEM_BYTES = P_STAGES * P_STAGE_BYTES + P_BOX_BYTES + 1024 + 256
 template <bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                       const __grid_constant__ CUtensorMap tmC, params_t p)
+                       const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAlo,
+                       const __grid_constant__ CUtensorMap tmBlo, params_t p)
 {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -269,7 +276,8 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tiles_m = (p.M + BLOCK_M - 1) / BLOCK_M, tiles_n = (p.N + P_BLOCK_N - 1) / P_BLOCK_N;
     const int num_tiles = tiles_m * tiles_n;
-    const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+    const int base_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+    const int num_kb = base_kb * p.segs;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
@@ -312,18 +320,20 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                     const uint32_t sa = smem_u32(smem + s * P_STAGE_BYTES), sb = sa + A_BYTES;
                     const uint32_t fb = full0 + 8 * s;
                     mbar_expect_tx(fb, P_STAGE_BYTES);
-                    const int k0 = kb * BLOCK_K;
+                    const int seg = p.segs == 3 ? kb / base_kb : 2;       // (see gemm_tc_kernel)
+                    const int k0 = (p.segs == 3 ? kb - seg * base_kb : kb) * BLOCK_K;
+                    const CUtensorMap *mA = seg == 1 ? &tmAlo : &tmA, *mB = seg == 0 ? &tmBlo : &tmB;
                     if (A_MN) {
-                        tma_load_2d(sa, &tmA, fb, m0, k0);
-                        tma_load_2d(sa + A_BYTES / 2, &tmA, fb, m0 + 64, k0);
+                        tma_load_2d(sa, mA, fb, m0, k0);
+                        tma_load_2d(sa + A_BYTES / 2, mA, fb, m0 + 64, k0);
                     } else {
-                        tma_load_2d(sa, &tmA, fb, k0, m0);
+                        tma_load_2d(sa, mA, fb, k0, m0);
                     }
                     if (B_MN) {
 #pragma unroll
-                        for (int q = 0; q < P_BLOCK_N / 64; ++q) tma_load_2d(sb + q * 8192, &tmB, fb, n0 + 64 * q, k0);
+                        for (int q = 0; q < P_BLOCK_N / 64; ++q) tma_load_2d(sb + q * 8192, mB, fb, n0 + 64 * q, k0);
                     } else {
-                        tma_load_2d(sb, &tmB, fb, k0, n0);
+                        tma_load_2d(sb, mB, fb, k0, n0);
                     }
                 }
             }
@@ -546,7 +556,19 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
     else MMV_TRY(make_map(&ta, g.A, g.K, g.M, g.lda, BLOCK_K, BLOCK_M));
     if (g.b_mn) MMV_TRY(make_map(&tb, g.B, g.N, g.K, g.ldb, 64, BLOCK_K));
     else MMV_TRY(make_map(&tb, g.B, g.K, g.N, g.ldb, BLOCK_K, BLOCK_N));
+    // fp32-tolerance mode: the residual copies share the layout of their hi halves
+    MMV_CHECK((g.A_lo == nullptr) == (g.B_lo == nullptr), "gemm_tc: the three-product mode needs both residual operands");
+    auto al16 = [](const void *q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    MMV_CHECK(!g.A_lo || (al16(g.A_lo) && al16(g.B_lo)), "gemm_tc: residual operands must be 16-byte aligned");
+    CUtensorMap tal = ta, tbl = tb;
+    if (g.A_lo) {
+        if (g.a_mn) MMV_TRY(make_map(&tal, g.A_lo, g.M, g.K, g.lda, 64, BLOCK_K));
+        else MMV_TRY(make_map(&tal, g.A_lo, g.K, g.M, g.lda, BLOCK_K, BLOCK_M));
+        if (g.b_mn) MMV_TRY(make_map(&tbl, g.B_lo, g.N, g.K, g.ldb, 64, BLOCK_K));
+        else MMV_TRY(make_map(&tbl, g.B_lo, g.K, g.N, g.ldb, BLOCK_K, BLOCK_N));
+    }
     params_t p;
+    p.segs = g.A_lo ? 3 : 1;
     p.C = g.C; p.Cb = reinterpret_cast<__nv_bfloat16 *>(g.Cb); p.bias = g.bias;
     p.M = g.M; p.N = g.N; p.K = g.K; p.ldc = g.ldc; p.ldcb = g.ldcb; p.beta = g.beta; p.relu = g.relu;
     p.sumsq = nullptr;
@@ -555,7 +577,7 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
     if (g.sumsq_done) *g.sumsq_done = 0;
     if (g.row_stats_tiles) *g.row_stats_tiles = 0;
     dim3 grid(ceil_div(g.N, BLOCK_N), ceil_div(g.M, BLOCK_M));
-    const int tiles = (int)(grid.x * grid.y), total_kb = ceil_div(g.K, BLOCK_K);
+    const int tiles = (int)(grid.x * grid.y), total_kb = ceil_div(g.K, BLOCK_K) * (g.A_lo ? 3 : 1);
     if (tiles <= 64 && total_kb >= 16 && !g.relu && !g.Cb && g.C && (g.beta == 1.f || (g.beta == 0.f && g.ldc == g.N))) {
         int splits = total_kb / 4;                 // at least 4 k-blocks per CTA
         if (splits > 256 / tiles) splits = 256 / tiles;
@@ -591,6 +613,7 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
     const int ptiles = ceil_div(g.M, BLOCK_M) * ceil_div(g.N, P_BLOCK_N);
     if (persist_mode > 0 && p.tma_epi && !g.Cb && grid.z == 1 && ptiles >= 2 * num_sms) {
         if (!g.b_mn) MMV_TRY(make_map(&tb, g.B, g.K, g.N, g.ldb, BLOCK_K, P_BLOCK_N));
+        if (!g.b_mn) { tbl = tb; if (g.B_lo) MMV_TRY(make_map(&tbl, g.B_lo, g.K, g.N, g.ldb, BLOCK_K, P_BLOCK_N)); }
         if (g.sumsq && p.tma_epi == 1 && !g.bias) {
             p.sumsq = g.sumsq;
             if (g.sumsq_done) *g.sumsq_done = 1;
@@ -599,16 +622,16 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
             p.row_stats = reinterpret_cast<float2 *>(g.row_stats);
             *g.row_stats_tiles = ceil_div(g.N, P_BLOCK_N);
         }
-        void (*pk)(const CUtensorMap, const CUtensorMap, const CUtensorMap, params_t) =
+        void (*pk)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, params_t) =
             g.a_mn ? (g.b_mn ? gemm_tc_persist_kernel<true, true> : gemm_tc_persist_kernel<true, false>)
                    : (g.b_mn ? gemm_tc_persist_kernel<false, true> : gemm_tc_persist_kernel<false, false>);
         MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(pk), P_SMEM_BYTES));
-        MMV_CUDA(launch_k(pk, dim3(std::min(ptiles, num_sms)), dim3(THREADS), P_SMEM_BYTES, stream, ta, tb, tc_map, p));
+        MMV_CUDA(launch_k(pk, dim3(std::min(ptiles, num_sms)), dim3(THREADS), P_SMEM_BYTES, stream, ta, tb, tc_map, tal, tbl, p));
         ::mmv::count_launch();
         return 0;
     }
     const bool deep = (int)(grid.x * grid.y * grid.z) <= num_sms && ceil_div(total_kb, (int)grid.z) >= 6;
-    void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, params_t);
+    void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, params_t);
     if (deep)
         kern = g.a_mn ? (g.b_mn ? gemm_tc_kernel<true, true, 6> : gemm_tc_kernel<true, false, 6>)
                       : (g.b_mn ? gemm_tc_kernel<false, true, 6> : gemm_tc_kernel<false, false, 6>);
@@ -617,7 +640,7 @@ launch_gemm_tc(const gemm_tc_args_t &g, cudaStream_t stream)
                       : (g.b_mn ? gemm_tc_kernel<false, true, 3> : gemm_tc_kernel<false, false, 3>);
     const int smem = smem_bytes(deep ? 6 : 3);
     MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(kern), smem));
-    MMV_CUDA(launch_k(kern, grid, dim3(THREADS), smem, stream, ta, tb, tc_map, p));
+    MMV_CUDA(launch_k(kern, grid, dim3(THREADS), smem, stream, ta, tb, tc_map, tal, tbl, p));
     ::mmv::count_launch();
     return 0;
 }

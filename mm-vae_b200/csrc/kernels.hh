@@ -27,6 +27,9 @@ int launch_gemm_f32(const gemm_args_t &g, cudaStream_t stream);
 //   b_mn = 0: B stored [N x K] (ldb) ; b_mn = 1: B stored [K x N] (ldb)
 struct gemm_tc_args_t {
     const void *A = nullptr, *B = nullptr;
+    // fp32-tolerance mode: residual copies (same layout) of both operands.  The kernel then walks K three times into one
+    // accumulator — A B_lo, A_lo B, A B — i.e. A and B stand for hi + lo pairs (both null: the plain bf16 product)
+    const void *A_lo = nullptr, *B_lo = nullptr;
     int a_mn = 0, b_mn = 0, lda = 0, ldb = 0;
     float *C = nullptr;            // fp32 output (may be nullptr if only Cb is wanted)
     void *Cb = nullptr;            // optional bf16 copy of the output
@@ -200,6 +203,7 @@ struct nb_lik_args_t {
     float inv_B = 0.f;
     float *dlogits = nullptr;         // [B x D]  (nullptr: forward only unless dlogits_bf16)
     void *dlogits_bf16 = nullptr;     // [B x D] bf16 instead of fp32 (tensor-core mode)
+    void *dlogits_lo = nullptr;       // tuned kernel, with dlogits_bf16 ("dtype" 2): the bf16 residual, gradient = bf16 + lo
     float *ddpre = nullptr;           // [B]
     float *dznu = nullptr;            // [B x Rnu]
     float *col_du = nullptr;          // [D]       += sum_i du_ij
@@ -328,6 +332,7 @@ int launch_vmf_latent_bwd(const vmf_latent_args_t &a, cudaStream_t st);
 struct colsum_args_t {
     const float *X = nullptr;
     const void *Xb = nullptr;         // bf16 input instead of X
+    const void *Xb2 = nullptr;        // with Xb (bf16x8 kernel only): a second bf16 array added element-wise (hi + lo pair)
     int M = 0, N = 0, ldx = 0;
     float *out_sum = nullptr, *out_sum2 = nullptr, *out_sum3 = nullptr;   // [N] each, +=
     float *out_cov = nullptr;         // [N x C] += sum_i X[i, col] * cov[cell_i, c]

@@ -721,20 +721,14 @@ lo_of(const step_t &s, const float *p, size_t n, const void **out)
     return 0;
 }
 
-// One product in fp32-tolerance mode: t describes A_hi B_hi with the epilogue options; the two cross terms go first
-// (small addends first), everything accumulates in C through the GEMM's beta = 1 epilogue.
+// One product in fp32-tolerance mode: t describes A_hi B_hi with the epilogue options; the kernel walks K three times
+// (A_hi B_lo, A_lo B_hi, A_hi B_hi) into one fp32 accumulator, so bias / ReLU / row statistics / the fused clip norm all
+// apply to the full-precision product in one epilogue.
 int
 gemm3(const step_t &s, gemm_tc_args_t t, const void *A_lo, const void *B_lo)
 {
-    gemm_tc_args_t u = t;
-    u.bias = nullptr; u.relu = 0; u.Cb = nullptr; u.sumsq = nullptr; u.sumsq_done = nullptr;
-    u.row_stats = nullptr; u.row_stats_tiles = nullptr;
-    u.B = B_lo;
-    MMV_TRY(launch_gemm_tc(u, s.st));            // beta C + A_hi B_lo
-    u.A = A_lo; u.B = t.B; u.beta = 1.f;
-    MMV_TRY(launch_gemm_tc(u, s.st));            // + A_lo B_hi
-    t.beta = 1.f; t.Cb = nullptr; t.sumsq = nullptr; t.sumsq_done = nullptr; t.row_stats = nullptr; t.row_stats_tiles = nullptr;
-    return launch_gemm_tc(t, s.st);              // + A_hi B_hi (+ bias, ReLU)
+    t.A_lo = A_lo; t.B_lo = B_lo; t.Cb = nullptr;
+    return launch_gemm_tc(t, s.st);
 }
 
 // "<name>.bf" twin of an fp32 workspace array, registered so bf16_of() finds it without a cast kernel:
@@ -794,7 +788,7 @@ lin_fwd(const step_t &s, const float *X, int in, const float *W, const float *b,
 // dX = dY W
 int
 lin_bwd_data(const step_t &s, const float *dY, int out, const float *W, int in, float *dX,
-             const char *tag = "gemm_other", const void *dY_bf = nullptr)
+             const char *tag = "gemm_other", const void *dY_bf = nullptr, const void *dY_lo = nullptr)
 {
     mmv_model *m = s.m;
     if (tc_ok(s, s.B, in, out, out, in)) {
@@ -808,9 +802,9 @@ lin_bwd_data(const step_t &s, const float *dY, int out, const float *W, int in, 
         }
         PROF(tag);
         if (m->tc3) {
-            MMV_CHECK(dY != nullptr, "lin_bwd_data: the fp32-tolerance mode needs an fp32 gradient");
-            const void *Al = nullptr, *Bl = nullptr;
-            MMV_TRY(lo_of(s, dY, (size_t)s.B * out, &Al));
+            MMV_CHECK(dY != nullptr || dY_lo != nullptr, "lin_bwd_data: the fp32-tolerance mode needs an fp32 gradient or a hi + lo pair");
+            const void *Al = dY_lo, *Bl = nullptr;
+            if (!Al) MMV_TRY(lo_of(s, dY, (size_t)s.B * out, &Al));
             MMV_TRY(lo_of(s, W, (size_t)out * in, &Bl));
             return gemm3(s, t, Al, Bl);
         }
@@ -827,7 +821,8 @@ lin_bwd_data(const step_t &s, const float *dY, int out, const float *W, int in, 
 // dW += dY^T X ; db += colsum(dY)
 int
 lin_bwd_weight(const step_t &s, const float *dY, int out, const float *X, int in, float *dW, float *db, float beta = 1.f,
-               const char *tag = "gemm_other", const void *dY_bf = nullptr, double *sumsq = nullptr, int *sumsq_done = nullptr)
+               const char *tag = "gemm_other", const void *dY_bf = nullptr, double *sumsq = nullptr, int *sumsq_done = nullptr,
+               const void *dY_lo = nullptr)
 {
     mmv_model *m = s.m;
     if (dW && tc_ok(s, out, in, s.B, out, in)) {
@@ -838,11 +833,10 @@ lin_bwd_weight(const step_t &s, const float *dY, int out, const float *X, int in
         t.beta = beta; t.sumsq = sumsq; t.sumsq_done = sumsq_done;
         PROF(tag);
         if (m->tc3) {
-            MMV_CHECK(dY != nullptr, "lin_bwd_weight: the fp32-tolerance mode needs an fp32 gradient");
-            const void *Al = nullptr, *Bl = nullptr;
-            MMV_TRY(lo_of(s, dY, (size_t)s.B * out, &Al));
+            MMV_CHECK(dY != nullptr || dY_lo != nullptr, "lin_bwd_weight: the fp32-tolerance mode needs an fp32 gradient or a hi + lo pair");
+            const void *Al = dY_lo, *Bl = nullptr;
+            if (!Al) MMV_TRY(lo_of(s, dY, (size_t)s.B * out, &Al));
             MMV_TRY(lo_of(s, X, (size_t)s.B * in, &Bl));
-            if (sumsq_done) *sumsq_done = 0;
             MMV_TRY(gemm3(s, t, Al, Bl));
         } else {
             MMV_TRY(launch_gemm_tc(t, s.st));
@@ -980,6 +974,7 @@ decoder_backward(const step_t &s)
     const bool bf_top = m->top_grad_bf16;
     const float *dY = bf_top ? nullptr : m->ws["G"].as<float>();
     const void *dY_bf = bf_top ? m->ws["dG.bf"].p : nullptr;
+    const void *dY_lo = (bf_top && m->tc3) ? m->ws["dG.lo"].p : nullptr;   // fp32-tolerance mode: the top gradient is a bf16 pair
     for (int l = nd - 1; l >= 0; --l) {
         const linear_t &L = m->dec[l];
         const float *X = l == 0 ? m->ws["z"].as<float>() : m->ws["dec_act" + std::to_string(l - 1)].as<float>();
@@ -991,15 +986,15 @@ decoder_backward(const step_t &s)
         MMV_TRY(lin_bwd_weight(s, dY, L.out, X, L.in, m->want_grad(L.w) ? m->G(L.w) : nullptr,
                                (!last && m->want_grad(L.b)) ? m->G(L.b) : nullptr,
                                (last && m->optimised(L.w)) ? 0.f : 1.f,   // mmv_step leaves this one un-zeroed
-                               last ? "gemm_dec_last_dw" : "gemm_other", dY_bf, fuse_ss ? m->acc + 3 : nullptr, &ss_ok));
+                               last ? "gemm_dec_last_dw" : "gemm_other", dY_bf, fuse_ss ? m->acc + 3 : nullptr, &ss_ok, dY_lo));
         // multi GPU, first bucket: the largest gradient is final long before backward ends — reduce it under the rest
         if (last) trace_mark(m->ctx, "decoder-last dW done");
         if (last && m->want_grad(L.w)) MMV_TRY(allreduce_grad_async(s, L.w));
         if (ss_ok) m->ss_done.emplace_back(m->tensors[L.w].off, m->tensors[L.w].off + m->tensors[L.w].numel());
         float *dX = l == 0 ? WS("dz", (size_t)B * R) : WS("d_dec" + std::to_string(l - 1), (size_t)B * L.in);
         NEED(dX);
-        MMV_TRY(lin_bwd_data(s, dY, L.out, m->P(L.w), L.in, dX, last ? "gemm_dec_last_dx" : "gemm_other", dY_bf));
-        dY_bf = nullptr;
+        MMV_TRY(lin_bwd_data(s, dY, L.out, m->P(L.w), L.in, dX, last ? "gemm_dec_last_dx" : "gemm_other", dY_bf, dY_lo));
+        dY_bf = nullptr; dY_lo = nullptr;
         if (l > 0 && m->relu) MMV_TRY(launch_relu_bwd(dX, X, (size_t)B * L.in, s.st));
         dY = dX;
     }
@@ -1233,13 +1228,21 @@ nb_forward_backward(const step_t &s)
         k.recon_mu = WS("recon_mu", (size_t)B * D); k.recon_nu = WS("recon_nu", (size_t)B * D);
         NEED(k.recon_mu); NEED(k.recon_nu);
     }
-    m->top_grad_bf16 = s.bwd && !m->tc3 && tc_ok(s, D, Ld.in, B, D, Ld.in) && tc_ok(s, B, Ld.in, D, D, Ld.in);
+    m->top_grad_bf16 = s.bwd && tc_ok(s, D, Ld.in, B, D, Ld.in) && tc_ok(s, B, Ld.in, D, D, Ld.in);
     if (m->top_grad_bf16) {
         k.dlogits_bf16 = m->W("dG.bf", (size_t)B * D * 2); NEED(k.dlogits_bf16);
+        // fp32-tolerance mode: K4 writes the gradient as a bf16 pair hi + lo (the same bytes as fp32, no split pass)
+        if (m->tc3) { k.dlogits_lo = m->W("dG.lo", (size_t)B * D * 2); NEED(k.dlogits_lo); }
     } else if (s.bwd) {
         k.dlogits = const_cast<float *>(k.G);   // in place: each row is staged in shared memory first
     }
-    const bool fast = k.allow_fast && nb_likelihood_fast_eligible(k);
+    bool fast = k.allow_fast && nb_likelihood_fast_eligible(k);
+    if (m->tc3 && m->top_grad_bf16 && !(fast && D % 8 == 0)) {   // only the tuned kernel writes the pair: fp32 in place otherwise
+        m->top_grad_bf16 = false;
+        k.dlogits_bf16 = nullptr; k.dlogits_lo = nullptr;
+        k.dlogits = const_cast<float *>(k.G);
+        fast = k.allow_fast && nb_likelihood_fast_eligible(k);
+    }
 
     // per-gene prologue, one launch: inv_t (nb.hh:406-410) and K4's per-gene constants.  Tuned kernel: all-ones
     // covariates, so covar_decoding.weight's row sums join the bias, and the bias joins the logits
@@ -1335,7 +1338,7 @@ nb_forward_backward(const step_t &s)
     {
         PROF("colsum_dlogits");
         colsum_args_t c;
-        c.X = k.dlogits; c.Xb = k.dlogits_bf16; c.M = B; c.N = D; c.ldx = D;
+        c.X = k.dlogits; c.Xb = k.dlogits_bf16; c.Xb2 = k.dlogits_lo; c.M = B; c.N = D; c.ldx = D;
         c.out_sum = m->want_grad(Ld.b) ? m->G(Ld.b) : nullptr;
         c.out_sum2 = m->G(m->covar_dec.b); c.out_sum3 = m->G(m->t_mu_bias);
         c.out_cov = m->G(m->covar_dec.w); c.cov = s.cov; c.cells = s.cells; c.C = C;

@@ -352,7 +352,9 @@ nb_row_meta_scan_kernel(const float *G, int D, const float *dpre, const float *z
     }
 }
 
-template <int EPT, int T>
+// LO: the gradient leaves as a bf16 pair hi + lo (fp32-tolerance mode on the tensor cores); a separate instantiation so that
+// the bf16 mode's register allocation is untouched
+template <int EPT, int T, bool LO = false>
 __global__ void __launch_bounds__(T, 2)
 nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
 {
@@ -532,7 +534,13 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
                     if (h >= HP - 2 && jj >= nj) continue;
                     float o0, o1;
                     up2(mul2(mul2(*reinterpret_cast<const f2_t *>(sLp + jj), coef2), add2(*reinterpret_cast<const f2_t *>(sgp + jj), ns2)), o0, o1);
-                    *reinterpret_cast<__nv_bfloat162 *>(orow + h * 2 * kT) = __floats2bfloat162_rn(o0, o1);
+                    const __nv_bfloat162 hi2 = __floats2bfloat162_rn(o0, o1);
+                    *reinterpret_cast<__nv_bfloat162 *>(orow + h * 2 * kT) = hi2;
+                    if (LO) {
+                        __nv_bfloat16 *lrow = reinterpret_cast<__nv_bfloat16 *>(a.dlogits_lo) + (size_t)prev_row * D + j0 + 2 * tid;
+                        *reinterpret_cast<__nv_bfloat162 *>(lrow + h * 2 * kT) =
+                            __floats2bfloat162_rn(o0 - __low2float(hi2), o1 - __high2float(hi2));
+                    }
                 }
             } else {
                 float *orow = a.dlogits + (size_t)prev_row * D + j0 + 2 * tid;
@@ -680,10 +688,13 @@ fast_smem_bytes(int ept, int T)
 struct k4_variant_t {
     int ept, T;
     void (*kern)(nb_lik_args_t, int, int);
+    void (*kern_lo)(nb_lik_args_t, int, int);
 };
 const k4_variant_t kVariants[] = {
-    { 4, 256, nb_likelihood_fast_kernel<4, 256> },   { 8, 256, nb_likelihood_fast_kernel<8, 256> },
-    { 12, 256, nb_likelihood_fast_kernel<12, 256> }, { 16, 256, nb_likelihood_fast_kernel<16, 256> },
+    { 4, 256, nb_likelihood_fast_kernel<4, 256>, nb_likelihood_fast_kernel<4, 256, true> },
+    { 8, 256, nb_likelihood_fast_kernel<8, 256>, nb_likelihood_fast_kernel<8, 256, true> },
+    { 12, 256, nb_likelihood_fast_kernel<12, 256>, nb_likelihood_fast_kernel<12, 256, true> },
+    { 16, 256, nb_likelihood_fast_kernel<16, 256>, nb_likelihood_fast_kernel<16, 256, true> },
 };
 
 bool
@@ -765,7 +776,8 @@ launch_nb_likelihood_fast(const nb_lik_args_t &a, int num_sms, cudaStream_t stre
     } else {              // (the caller ran launch_nb_row_meta's scan over the complete logits)
         MMV_TRY(launch_slice_bounds(a.indptr, a.indices, a.cells, a.unsorted, a.B, cs, Ds, a.slice_bounds, stream));
     }
-    void (*kern)(nb_lik_args_t, int, int) = v->kern;
+    MMV_CHECK(!a.dlogits_lo || a.dlogits_bf16, "nb_likelihood (tuned): the residual gradient goes with the bf16 one");
+    void (*kern)(nb_lik_args_t, int, int) = a.dlogits_lo ? v->kern_lo : v->kern;
     const size_t smem = fast_smem_bytes(v->ept, v->T);
     MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(kern), (int)smem));
     cudaLaunchConfig_t cfg = {};

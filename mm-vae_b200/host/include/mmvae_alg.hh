@@ -97,6 +97,7 @@ train_vae_model(MODEL &model, VISITOR &visitor, DATA_BLOCK &data_block, mmvae::d
     std::vector<float> loss_vec;
     loss_vec.reserve(opt.max_epoch);
     const auto t_begin = std::chrono::steady_clock::now();
+    auto t_warm = t_begin;
 
     for (int64_t epoch = 0; epoch < opt.max_epoch; ++epoch) {
         const float kl_weight = loss_fun(epoch);
@@ -135,6 +136,11 @@ train_vae_model(MODEL &model, VISITOR &visitor, DATA_BLOCK &data_block, mmvae::d
         _loss_epoch /= batch_size * nbatch;
         if (lead) TLOG("[" << std::setw(20) << (epoch + 1) << "] " << std::setw(20) << _loss_epoch);
         loss_vec.emplace_back(_loss_epoch);
+        if (epoch == 0) {   // first epoch = warm-up (workspace allocation, communicator set-up): steady-state rate counts from here
+            MMV_OK_EXIT(mmv_ctx_sync(dev.ctx));
+            dev.barrier();
+            t_warm = std::chrono::steady_clock::now();
+        }
         if ((epoch + 1) % opt.recording == 0) {
             dev.barrier();                                   // every shard's rows of the latent table are in
             if (lead) visitor.update_on_epoch(model, epoch);
@@ -149,6 +155,12 @@ train_vae_model(MODEL &model, VISITOR &visitor, DATA_BLOCK &data_block, mmvae::d
         TLOG("Done training: " << opt.max_epoch << " epochs x " << nbatch << " minibatches x " << batch_size << " cells x "
                                << dev.nranks << " GPU(s) in " << sec << " s = " << uniq / sec << " unique cells/s under the schedule ("
                                << uniq * (double)opt.nboot / sec << " cells/s through the optimiser steps, nboot = " << opt.nboot << ")");
+        if (opt.max_epoch > 1) {
+            const double sec1 = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_warm).count();
+            const double uniq1 = (double)(opt.max_epoch - 1) * nbatch * batch_size * dev.nranks;
+            TLOG("  after the first epoch (warm-up): " << uniq1 / sec1 << " unique cells/s under the schedule, "
+                                                        << uniq1 * (double)opt.nboot / sec1 << " cells/s through the optimiser steps");
+        }
     }
     return loss_vec;
 }
