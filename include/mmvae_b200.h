@@ -119,6 +119,9 @@ MMV_API int mmv_model_destroy(mmv_model *m);
  *   "frozen_grads" (1): compute the gradients of the non-optimised tensors
  *        (what the reference's autograd does); 0 skips that dead work.
  *   "max_batch" : capacity hint (cells per step), grows on demand.
+ *   "dtype" (0): 0 = fp32 FFMA GEMMs + gather first layer (1e-4 parity mode); 1 = bf16 operands on the tcgen05 tensor
+ *        cores, fp32 accumulation (1e-2); 2 = the fp32 tolerance ON the tensor cores: every GEMM operand as a bf16
+ *        pair hi + lo, three products per GEMM into one accumulator (1e-4; no reference counterpart).
  *   "debug_outputs" (0): keep recon_mu / recon_nu / recon for mmv_get_output.
  *   "comm_bf16" (1): data-parallel runs in bf16 mode ("dtype" 1) send the two D x h weight gradients over
  *        NVLink as bf16 (per-rank partial sums rounded once, summed by ncclAllReduce(bf16)); 0 or fp32 mode:

@@ -1170,7 +1170,8 @@ senc_tc_backward(const step_t &s, const senc_bwd_args_t &b)
         // multi GPU: the gene tiles in up to four parts of whole waves; each part's rows of dW1 are all-reduced on
         // the comm stream while the next part is multiplied.  dW1 is produced about as fast as NVLink reduces it, so
         // only the last (partial-wave) part's reduction is left over, and that one runs under the aux kernel below
-        const int per = std::max(1, (int)((int64_t)((waves + 3) / 4) * m->ctx->num_sms / cols));
+        static const int parts = [] { const char *e = getenv("MMV_DW1_PARTS"); return e ? std::max(1, atoi(e)) : 4; }();
+        const int per = std::max(1, (int)((int64_t)((waves + parts - 1) / parts) * m->ctx->num_sms / cols));
         const size_t off = m->tensors[L0.w].off;
         for (int t0 = 0; t0 < tiles; t0 += per) {
             const int t1 = std::min(tiles, t0 + per);

@@ -95,7 +95,7 @@ public:
         MMV_OK(mmv_model_set_option(m_, "lr", opt.lr));
         MMV_OK(mmv_model_set_option(m_, "grad_clip", opt.grad_clip));
         MMV_OK(mmv_model_set_option(m_, "weight_decay", 1e-4));   // mmvae_alg.hh:236
-        MMV_OK(mmv_model_set_option(m_, "dtype", opt.bf16 ? 1 : 0));
+        MMV_OK(mmv_model_set_option(m_, "dtype", opt.f32x3 ? 2 : (opt.bf16 ? 1 : 0)));
         MMV_OK(mmv_model_set_option(m_, "train_all_layers", opt.train_all_layers ? 1 : 0));
         MMV_OK(mmv_model_set_option(m_, "frozen_grads", 0));      // never read on this path: skip the dead work
         return EXIT_SUCCESS;

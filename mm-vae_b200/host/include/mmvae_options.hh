@@ -128,7 +128,7 @@ parse_mmvae_options(const int argc, const char *argv[], mmvae_options_t &options
 
 struct training_options_t {
     explicit training_options_t()
-        : lr(1e-3f), grad_clip(1.f), nboot(3), max_epoch(101), recording(10), device(0), seed(0), bf16(false),
+        : lr(1e-3f), grad_clip(1.f), nboot(3), max_epoch(101), recording(10), device(0), seed(0), bf16(false), f32x3(false),
           train_all_layers(false), record_params(true), ngpu(1)
     {
     }
@@ -140,6 +140,7 @@ struct training_options_t {
     int device;        // CUDA ordinal (the reference picks kCUDA when available, mmvae_alg.hh:16-17)
     uint64_t seed;             // 0 = std::random_device like the reference (mmvae_alg.hh:242-243)
     bool bf16;                 // --dtype bf16: tcgen05 GEMMs (1e-2 tolerance); default fp32 (1e-4)
+    bool f32x3;                // --dtype f32x3: the fp32 tolerance ON the tensor cores (operands as bf16 pairs)
     bool train_all_layers;     // default off = the reference's frozen unregistered Sequentials
     bool record_params;        // default on = the reference's per-parameter text dumps at every recorded epoch (nb.hh:599-615)
     int ngpu;                  // --ngpu G: cells sharded over G GPUs of this box, one host thread + one context each (default 1)
@@ -159,7 +160,7 @@ parse_training_options(const int argc, const char *argv[], training_options_t &o
                         "--nboot      : #bootstrapped gradients (default: 3)\n"
                         "--max_epoch  : maximum #epoch (default: 101)\n"
                         "--recording  : recording interval (default: 10)\n"
-                        "--seed, --device, --dtype {f32,bf16}, --train_all_layers, --skip_param_record : B200 build additions\n"
+                        "--seed, --device, --dtype {f32,bf16,f32x3}, --train_all_layers, --skip_param_record : B200 build additions\n"
                         "--ngpu       : shard the cells over this many GPUs of the box (default: 1)\n"
                         "--init_dir, --eps_file : reproducibility hooks (initial parameters / injected noise)\n\n";
     const option long_opts[] = { { "lr", required_argument, nullptr, 'L' },         { "learning", required_argument, nullptr, 'L' },
@@ -184,7 +185,7 @@ parse_training_options(const int argc, const char *argv[], training_options_t &o
         case 'R': options.recording = std::stol(arg); break;
         case 1001: options.seed = std::stoull(arg); break;
         case 1002: options.device = std::stoi(arg); break;
-        case 1003: options.bf16 = std::strcmp(arg, "bf16") == 0; break;
+        case 1003: options.bf16 = std::strcmp(arg, "bf16") == 0; options.f32x3 = std::strcmp(arg, "f32x3") == 0; break;
         case 1004: options.train_all_layers = true; break;
         case 1005: options.record_params = false; break;
         case 1006: options.ngpu = std::max(1, std::stoi(arg)); break;
