@@ -443,6 +443,7 @@ colsum_multi_kernel(colsum_multi_args_t m)
 
 // bf16 input, all-ones covariates, N % 8 == 0: each thread owns 8 adjacent columns (one 16-byte load
 // per row), 4 rows in flight; a CTA covers 256 columns x rows_per_cta rows.
+template <bool PAIR>   // PAIR: a second bf16 array (the residual of a hi + lo pair) is added in
 __global__ void __launch_bounds__(256)
 colsum_bf16x8_kernel(colsum_args_t a)
 {
@@ -455,7 +456,8 @@ colsum_bf16x8_kernel(colsum_args_t a)
 #pragma unroll
     for (int q = 0; q < 8; ++q) s[q] = 0.f;
     if (col < a.N) {
-        for (int pass = 0; pass < (a.Xb2 ? 2 : 1); ++pass) {   // second pass: the residual array of a hi + lo pair
+#pragma unroll
+        for (int pass = 0; pass < (PAIR ? 2 : 1); ++pass) {   // second pass: the residual array of a hi + lo pair
             const __nv_bfloat16 *X = reinterpret_cast<const __nv_bfloat16 *>(pass ? a.Xb2 : a.Xb) + col;
             for (int i = r0 + warp; i < r1; i += 32) {
                 uint4 v[4];
@@ -504,7 +506,7 @@ launch_colsum(colsum_args_t a, cudaStream_t st)
         a.N >= 256) {
         a.rows_per_cta = 256;
         dim3 grid(ceil_div(a.N, 256), ceil_div(a.M, a.rows_per_cta));
-        MMV_CUDA(launch_k(colsum_bf16x8_kernel, grid, dim3(256), 0, st, a)); ::mmv::count_launch();
+        MMV_CUDA(launch_k(a.Xb2 ? colsum_bf16x8_kernel<true> : colsum_bf16x8_kernel<false>, grid, dim3(256), 0, st, a)); ::mmv::count_launch();
         return 0;
     }
     // narrow matrices (bias gradients of the hidden layers: N = 64 ... 1024): the pass is a chain of dependent row

@@ -38,7 +38,7 @@ constexpr int kUn = 4;
 // [k_lo, k_hi) by bisection of the sorted gene ids, so every CTA owns its buckets outright and the
 // grid covers the machine even at 64 cell tiles.  Unsorted rows: the whole run is scanned and filtered.
 __global__ void __launch_bounds__(kPanelThreads)
-panel_build_kernel(panel_args_t p, int nK, int nS)
+panel_build_kernel(panel_args_t p, int nK, int nS, int stage)
 {
     extern __shared__ int s_int[];
     __shared__ int s_scan[kPanelThreads];
@@ -51,11 +51,27 @@ panel_build_kernel(panel_args_t p, int nK, int nS)
     const int k_lo = (int)((int64_t)nK * sp / nS), k_hi = (int)((int64_t)nK * (sp + 1) / nS), nKl = k_hi - k_lo;
     int *s_off = s_int;               // [nKl + 1] exclusive offsets of this CTA's buckets
     int *s_cur = s_int + nKl + 1;     // [nKl] fill cursors
+    // stage != 0: the per-gene constants of this CTA's gene range live in shared memory for pass 2 (ncu r02 step 4: 7.8
+    // long-scoreboard stalls per issue — every entry's three dependent gathers by gene id went to L2)
+    const int nG = nKl * 64, g_base = k_lo * 64;
+    float *g_it = reinterpret_cast<float *>(s_int + 2 * (nKl + 1));   // [nG] 1 / t_j
+    float *g_wd = g_it + nG;                                          // [nG] depth weights (nb)
+    float *g_wn = g_wd + nG;                                          // [nG] nu_encoding weights (nb, H = 1)
     const bool sorted = p.unsorted != nullptr && *p.unsorted == 0;
     const bool filter = !sorted && nS > 1;
 
     for (int k = tid; k < nKl; k += kPanelThreads) s_cur[k] = 0;
     if (tid == 0) s_before = 0;
+    if (stage) {
+        const bool h1w = p.H == 1 && p.WnuT != nullptr;
+        for (int g = tid; g < nG; g += kPanelThreads) {
+            const int j = g_base + g;
+            const bool in = j < p.D;
+            g_it[g] = in ? p.inv_t[j] : 0.f;
+            g_wd[g] = (in && p.wdepth) ? p.wdepth[j] : 0.f;
+            g_wn[g] = (in && h1w) ? p.WnuT[j] : 0.f;
+        }
+    }
     // minibatch-local CSR offset of the tile's first row = run lengths of all earlier rows.  Every CTA adds them up
     // itself (<= B gathered loads from L2, 8 per thread at B = 4096): cheaper than a one-CTA scan kernel in front
     int prefix = 0;
@@ -181,9 +197,14 @@ panel_build_kernel(panel_args_t p, int nK, int nS)
 #pragma unroll
             for (int u = 0; u < kUn; ++u) {
                 const int jj = max(j[u], 0);
-                it[u] = p.inv_t[jj];
-                wd[u] = p.wdepth ? p.wdepth[jj] : 0.f;
-                wn[u] = h_inline ? p.WnuT[jj] : 0.f;
+                if (stage) {
+                    const int g = max(j[u] - g_base, 0);   // (valid entries lie inside the CTA's range)
+                    it[u] = g_it[g]; wd[u] = g_wd[g]; wn[u] = g_wn[g];
+                } else {
+                    it[u] = p.inv_t[jj];
+                    wd[u] = p.wdepth ? p.wdepth[jj] : 0.f;
+                    wn[u] = h_inline ? p.WnuT[jj] : 0.f;
+                }
             }
 #pragma unroll
             for (int u = 0; u < kUn; ++u) {
@@ -233,12 +254,16 @@ launch_panel_build(const panel_args_t &p, cudaStream_t st)
     int nS = (2 * std::max(p.num_sms, 1) + nT - 1) / nT;
     nS = std::max(1, std::min(std::min(nS, 8), nK));
     const int nKl = (nK + nS - 1) / nS + 1;
-    const size_t smem = sizeof(int) * (2 * (size_t)nKl + 2);
+    size_t smem = sizeof(int) * (2 * (size_t)nKl + 2);
     MMV_CHECK(smem <= 200 * 1024, "panel_build: %d genes exceed the shared-memory bucket table", p.D);
+    // + the gene range's constants when two CTAs still fit an SM with them
+    const size_t staged = smem + sizeof(float) * 3 * (size_t)nKl * 64;
+    const int stage = staged <= 100 * 1024 ? 1 : 0;
+    if (stage) smem = staged;
     MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(panel_build_kernel), 200 * 1024));
     if (p.wdepth && p.dpre) MMV_CUDA(cudaMemsetAsync(p.dpre, 0, sizeof(float) * p.B, st));
     if (p.H > 0 && p.Hnu) MMV_CUDA(cudaMemsetAsync(p.Hnu, 0, sizeof(float) * (size_t)p.B * p.H, st));
-    MMV_CUDA(launch_k(panel_build_kernel, dim3(nT, nS), dim3(kPanelThreads), smem, st, p, nK, nS));
+    MMV_CUDA(launch_k(panel_build_kernel, dim3(nT, nS), dim3(kPanelThreads), smem, st, p, nK, nS, stage));
     ::mmv::count_launch();
     return 0;
 }
@@ -304,7 +329,9 @@ scatter_entry(uint8_t *tileA, uint32_t e, int rowbase)
     *reinterpret_cast<uint16_t *>(tileA + off) = (uint16_t)(e & 0xFFFFu);
 }
 
-template <int BN, bool BWD>
+// SEG: fp32-tolerance mode (three K segments over hi / lo operand copies); compile-time so that the bf16 mode's loops
+// carry none of the segment arithmetic
+template <int BN, bool BWD, bool SEG>
 __global__ void __launch_bounds__(TCT, 1)
 senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmS,
                const __grid_constant__ CUtensorMap tmDlo, senc_tc_args_t a, int nT, int nK)
@@ -322,7 +349,7 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ 
     // K axis = base_kb pipeline stages (gene chunks forward, cell tiles backward), walked once — or, in the fp32-tolerance
     // mode, three times with different operand copies (segment 0: panel hi x dense lo, 1: panel lo x dense hi, 2: hi x hi)
     const int base_kb = BWD ? nT : nK;
-    const int num_kb = a.ent_lo ? 3 * base_kb : base_kb;
+    const int num_kb = SEG ? 3 * base_kb : base_kb;
 
     if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmD) : "memory");
     if (warp == 1 && lane == 0) {
@@ -354,8 +381,8 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ 
                 const uint32_t sb = smem_u32(smem + s * cfg::STAGE + A_TILE);
                 const uint32_t fb = fullb0 + 8 * s;
                 mbar_expect_tx(fb, cfg::B_TILE);
-                const int seg = kb / base_kb, kk = kb - seg * base_kb;
-                const CUtensorMap *tm = (a.ent_lo && seg == 0) ? &tmDlo : &tmD;
+                const int seg = SEG ? kb / base_kb : 0, kk = SEG ? kb - seg * base_kb : kb;
+                const CUtensorMap *tm = (SEG && seg == 0) ? &tmDlo : &tmD;
 #pragma unroll
                 for (int i = 0; i < BN / 64; ++i) tma_load_2d(sb + i * 8192, tm, fb, n0 + 64 * i, kk * BK);
             }
@@ -393,14 +420,14 @@ senc_tc_kernel(const __grid_constant__ CUtensorMap tmD, const __grid_constant__ 
             asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
             for (int i = t; i < RT; i += 128)
                 if (i0 + i < n_own) {
-                    const run2_t r = stage_runs<BWD>(bp, (grp + 2 * (i0 + i)) % base_kb, tile, nT, nK);
+                    const run2_t r = stage_runs<BWD>(bp, SEG ? (grp + 2 * (i0 + i)) % base_kb : grp + 2 * (i0 + i), tile, nT, nK);
                     rtab[i] = make_int4(r.b0, r.n0, r.b1, r.n1);
                 }
             asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
         };
         // the panel copy a stage reads: the residual values in segment 1 of the fp32-tolerance mode
         auto ent_of = [&](int i) -> const uint32_t * {
-            return (a.ent_lo && (grp + 2 * i) / base_kb == 1) ? a.ent_lo : a.ent;
+            return (SEG && (grp + 2 * i) / base_kb == 1) ? a.ent_lo : a.ent;
         };
         auto load = [&](uint32_t (&e)[PF], int i) {
             const int4 r = rtab[i % RT];
@@ -558,7 +585,7 @@ launch_tc(const senc_tc_args_t &a, cudaStream_t st)
     if (BWD) MMV_TRY(make_tma_map_f32(&ts, a.S, (uint64_t)a.h1, (uint64_t)a.D, (uint64_t)a.h1, 32, 32));
     MMV_CHECK((a.ent_lo == nullptr) == (a.dense_lo == nullptr), "senc_tc: the fp32-tolerance mode needs both residual operands");
     if (a.dense_lo) MMV_TRY(make_tma_map_bf16(&tlo, a.dense_lo, (uint64_t)a.h1, (uint64_t)(BWD ? a.B : a.D), (uint64_t)a.h1, 64, BK));
-    auto kern = senc_tc_kernel<BN, BWD>;
+    auto kern = a.ent_lo ? senc_tc_kernel<BN, BWD, true> : senc_tc_kernel<BN, BWD, false>;
     MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(kern), cfg::SMEM));
     dim3 grid(ceil_div(a.h1, BN), BWD ? (a.ntiles > 0 ? a.ntiles : ceil_div(a.D, BM)) : ceil_div(a.B, BM));
     MMV_CUDA(launch_k(kern, grid, dim3(TCT), cfg::SMEM, st, tm, ts, tlo, a, nT, nK));

@@ -12,7 +12,7 @@ import json
 try:
     d=json.loads([l for l in open('$O/${TAG}_${V}_${rep}.log') if l.startswith('{')][-1])
     k=d['kernels']
-    print('$V rep $rep: step', d['ms_per_step'], 'e2e', d['e2e']['ms_per_step'], {n: k[n]['ms_per_step'] for n in ('nb_likelihood','gemm_dec_last_fwd','senc_fwd','senc_bwd','gemm_other','clip_adam') if n in k}, 'launches', d['gpu_launches']/d['steps'])
+    print('$V rep $rep: step', d['ms_per_step'], 'e2e', d['e2e']['ms_per_step'], {n: k[n]['ms_per_step'] for n in ('nb_likelihood','gemm_dec_last_dx','senc_fwd','senc_bwd','panel_build','colsum_dlogits','gemm_other') if n in k}, 'launches', d['gpu_launches']/d['steps'])
 except Exception as e:
     print('$V: bench failed', e)
 PY
