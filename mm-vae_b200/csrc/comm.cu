@@ -109,6 +109,28 @@ unpack_bf16_kernel(const uint4 *__restrict__ y, float *__restrict__ x, size_t n8
     }
 }
 
+// the same, and sum(x^2) of what it writes: one partial per block, summed later in block order (data-parallel replicas
+// must compute the identical clip coefficient, so no arrival-order atomics)
+__global__ void __launch_bounds__(256)
+unpack_bf16_ss_kernel(const uint4 *__restrict__ y, float *__restrict__ x, size_t n8, float *__restrict__ partial)
+{
+    float s = 0.f;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+        const uint4 v = y[i];
+        const float f[8] = { __uint_as_float(v.x << 16), __uint_as_float(v.x & 0xFFFF0000u), __uint_as_float(v.y << 16),
+                             __uint_as_float(v.y & 0xFFFF0000u), __uint_as_float(v.z << 16), __uint_as_float(v.z & 0xFFFF0000u),
+                             __uint_as_float(v.w << 16), __uint_as_float(v.w & 0xFFFF0000u) };
+        reinterpret_cast<float4 *>(x)[2 * i] = make_float4(f[0], f[1], f[2], f[3]);
+        reinterpret_cast<float4 *>(x)[2 * i + 1] = make_float4(f[4], f[5], f[6], f[7]);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) s = fmaf(f[q], f[q], s);
+    }
+    __shared__ float scratch[32];
+    float v1[1] = { s };
+    mmv::block_sum<1>(v1, scratch);
+    if (threadIdx.x == 0) partial[blockIdx.x] = v1[0];
+}
+
 } // namespace
 
 namespace mmv {
@@ -235,8 +257,9 @@ comm_allreduce_f64_async(mmv_ctx *ctx, double *buf, size_t n)
 }
 
 int
-comm_allreduce_f32_async(mmv_ctx *ctx, float *buf, size_t n, bool as_bf16)
+comm_allreduce_f32_async(mmv_ctx *ctx, float *buf, size_t n, bool as_bf16, const float **ss_partial, int *ss_count)
 {
+    if (ss_count) *ss_count = 0;
     if (ctx->nranks <= 1 || n == 0) return 0;
     if (ctx->in_group) {
         MMV_NCCL(g_nccl.AllReduce(buf, buf, n, ncclFloat32, ncclSum, (ncclComm_t)ctx->nccl_comm, ctx->comm_stream));
@@ -266,7 +289,14 @@ comm_allreduce_f32_async(mmv_ctx *ctx, float *buf, size_t n, bool as_bf16)
         MMV_CUDA(cudaGetLastError());
         MMV_NCCL(g_nccl.AllReduce(ctx->comm_stage, ctx->comm_stage, n, ncclBfloat16, ncclSum, (ncclComm_t)ctx->nccl_comm,
                                   ctx->comm_stream));
-        unpack_bf16_kernel<<<grid, 256, 0, ctx->comm_stream>>>(reinterpret_cast<const uint4 *>(ctx->comm_stage), buf, n / 8);
+        if (ss_partial && ss_count && ctx->comm_ss && ctx->comm_ss_used + grid <= ctx->comm_ss_cap) {
+            float *part = ctx->comm_ss + ctx->comm_ss_used;
+            unpack_bf16_ss_kernel<<<grid, 256, 0, ctx->comm_stream>>>(reinterpret_cast<const uint4 *>(ctx->comm_stage), buf, n / 8, part);
+            ctx->comm_ss_used += grid;
+            *ss_partial = part; *ss_count = grid;
+        } else {
+            unpack_bf16_kernel<<<grid, 256, 0, ctx->comm_stream>>>(reinterpret_cast<const uint4 *>(ctx->comm_stage), buf, n / 8);
+        }
         MMV_CUDA(cudaGetLastError());
     } else {
         MMV_NCCL(g_nccl.AllReduce(buf, buf, n, ncclFloat32, ncclSum, (ncclComm_t)ctx->nccl_comm, ctx->comm_stream));
@@ -336,6 +366,9 @@ mmv_comm_init(mmv_ctx *ctx, int nranks, int rank, const unsigned char id[128])
     MMV_CUDA(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
     MMV_CUDA(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
     MMV_CUDA(cudaEventRecord(ctx->ev_join, ctx->comm_stream));
+    ctx->comm_ss_cap = 16 * 1024;
+    MMV_CUDA(cudaMalloc(&ctx->comm_ss, sizeof(float) * ctx->comm_ss_cap));
+    ctx->comm_ss_used = 0;
     ctx->nranks = nranks;
     ctx->rank = rank;
     return 0;
@@ -351,6 +384,8 @@ mmv_comm_destroy(mmv_ctx *ctx)
     g_nccl.CommDestroy((ncclComm_t)ctx->nccl_comm);
     if (ctx->comm_stage) cudaFree(ctx->comm_stage);
     ctx->comm_stage = nullptr; ctx->comm_stage_bytes = 0;
+    if (ctx->comm_ss) cudaFree(ctx->comm_ss);
+    ctx->comm_ss = nullptr; ctx->comm_ss_cap = ctx->comm_ss_used = 0;
     cudaStreamDestroy(ctx->comm_stream);
     cudaEventDestroy(ctx->ev_fork);
     cudaEventDestroy(ctx->ev_join);

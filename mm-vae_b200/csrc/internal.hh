@@ -23,6 +23,8 @@ struct mmv_ctx {
     bool in_group = false;
     void *comm_stage = nullptr;                  // bf16 staging of a gradient bucket reduced in bf16 (comm.cu)
     size_t comm_stage_bytes = 0;
+    float *comm_ss = nullptr;                    // per-block sums of squares left by the unpack kernels of this step's bf16 buckets
+    int comm_ss_used = 0, comm_ss_cap = 0;
     // MMV_COMM_TRACE=<k>: timed marks on both streams for the k-th optimiser step, printed by rank 0 (comm.cu)
     int trace_step = -1, trace_seen = 0;
     bool trace_on = false;
@@ -56,7 +58,10 @@ int comm_allreduce_f64(mmv_ctx *ctx, double *buf, size_t n);
 // has finished; comm_join makes the ctx stream wait for it
 // as_bf16: the bucket crosses NVLink as bf16 (cast on the comm stream, ncclAllReduce(bf16), cast back) — half the wire
 // bytes for gradients that are products of bf16 operands anyway (tensor-core mode; see comm.cu)
-int comm_allreduce_f32_async(mmv_ctx *ctx, float *buf, size_t n, bool as_bf16 = false);
+// ss_partial / ss_count (optional, bf16 buckets only): the unpack pass leaves sum(g^2) of the REDUCED bucket as *ss_count
+// per-block partials at *ss_partial (fixed order, identical on every rank) — the clip norm needs no second pass over it
+int comm_allreduce_f32_async(mmv_ctx *ctx, float *buf, size_t n, bool as_bf16 = false, const float **ss_partial = nullptr,
+                             int *ss_count = nullptr);
 int comm_join(mmv_ctx *ctx);
 // reductions queued between begin and end go out as one NCCL launch on the comm stream
 int comm_group_begin(mmv_ctx *ctx);

@@ -363,7 +363,9 @@ int launch_angular_bwd(const float *W, const float *dWp, const float *scale, flo
 // ---- K6 (optim.cu)
 int launch_sumsq(const float *g, size_t n, double *out, int num_sms, cudaStream_t st);
 // the same over several ranges in one launch (four per launch); *out += the total
-int launch_sumsq_ranges(const float *const *g, const size_t *n, int count, double *out, int num_sms, cudaStream_t st);
+// pre / npre: arrays of already-squared partial sums added as they are (fixed order)
+int launch_sumsq_ranges(const float *const *g, const size_t *n, int count, double *out, int num_sms, cudaStream_t st,
+                        const float *const *pre = nullptr, const int *npre = nullptr, int pre_count = 0);
 struct adam_args_t {
     float *param = nullptr, *grad = nullptr, *m = nullptr, *v = nullptr;
     void *param_bf16 = nullptr;       // optional bf16 mirror refreshed in the same pass

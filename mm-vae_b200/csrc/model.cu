@@ -142,6 +142,7 @@ struct mmv_model {
     float *fscal = nullptr;               // device: [0] kappa, [1] grad norm, [2] clip coefficient
     std::vector<std::pair<size_t, size_t>> ss_done;   // gradient ranges whose sum of squares a producer already added to acc[3]
     std::vector<colsum_args_t> pending_colsum;        // bias-gradient column sums of this backward pass, launched together
+    std::vector<std::pair<const float *, int>> ss_pre; // per-block sum-of-squares partials of this step's bf16 gradient buckets (comm.cu)
     bool grad_lazy = false;               // the clip scale of the last fused step is still to be applied to .grad
     size_t grad_lazy_n = 0;               //   ... over grads[0, grad_lazy_n)
     double *h_acc = nullptr;              // pinned mirrors
@@ -959,7 +960,13 @@ allreduce_grad_async(const step_t &s, int t)
     // tensor-core mode: these gradients are sums of products of bf16 operands (dlogits, activations); rounding the
     // per-rank partial sums to bf16 for the wire stays inside that mode's 1e-2 budget and halves the bytes.  fp32 mode
     // reduces in fp32, bit for bit as before.
-    MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off, n, m->use_tc && !m->tc3 && m->comm_bf16));
+    const float *ssp = nullptr;
+    int ssn = 0;
+    MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off, n, m->use_tc && !m->tc3 && m->comm_bf16, &ssp, &ssn));
+    if (ssn > 0 && m->ss_pre.size() < 8) {   // the unpack pass summed the reduced bucket's squares: no second pass for the clip norm
+        m->ss_pre.emplace_back(ssp, ssn);
+        m->ss_done.emplace_back(off, off + n);
+    }
     m->ar_done.emplace_back(off, off + n);
     return 0;
 }
@@ -1182,7 +1189,14 @@ senc_tc_backward(const step_t &s, const senc_bwd_args_t &b)
             trace_mark(m->ctx, "first-layer dW part done");
             // a small last part is not worth a launch of its own: it goes with the step's grouped leftovers
             if (t1 == tiles && t0 > 0 && (r1 - r0) * sizeof(float) < ((size_t)16 << 20)) break;
-            MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off + r0, r1 - r0, m->use_tc && !m->tc3 && m->comm_bf16));
+            const float *ssp = nullptr;
+            int ssn = 0;
+            MMV_TRY(comm_allreduce_f32_async(m->ctx, m->grads + off + r0, r1 - r0, m->use_tc && !m->tc3 && m->comm_bf16,
+                                             m->ss_pre.size() < 8 ? &ssp : nullptr, &ssn));
+            if (ssn > 0) {
+                m->ss_pre.emplace_back(ssp, ssn);
+                m->ss_done.emplace_back(off + r0, off + r1);
+            }
             m->ar_done.emplace_back(off + r0, off + r1);
         }
     } else {
@@ -1677,6 +1691,8 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         s.optim = (flags & MMV_OPTIM) != 0;
         m->ar_done.clear();
         m->ss_done.clear();
+        m->ss_pre.clear();
+        m->ctx->comm_ss_used = 0;
         m->pending_colsum.clear();
         if (s.optim && s.bwd) trace_begin(m->ctx);
         MMV_TRY(stage_inputs(m, csr, cells, B, boot_idx, eps, flags, s));
@@ -1745,7 +1761,7 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
             trace_mark(m->ctx, "joined the comm stream");
         }
         PROF("clip_adam");
-        if (!(flags & MMV_FWD)) m->ss_done.clear();   // acc[3] was re-zeroed: nothing carried over
+        if (!(flags & MMV_FWD)) { m->ss_done.clear(); m->ss_pre.clear(); }   // acc[3] was re-zeroed: nothing carried over
         std::sort(m->ss_done.begin(), m->ss_done.end());
         {   // everything the producers have not covered, in one launch
             std::vector<const float *> rg;
@@ -1757,7 +1773,12 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
                 if (i < m->ss_done.size()) pos = std::max(pos, std::min(m->ss_done[i].second, n_opt));
             }
             m->ss_done.clear();
-            MMV_TRY(launch_sumsq_ranges(rg.data(), rn.data(), (int)rg.size(), m->acc + 3, m->ctx->num_sms, st));
+            std::vector<const float *> pp;
+            std::vector<int> pn;
+            for (auto &kv : m->ss_pre) { pp.push_back(kv.first); pn.push_back(kv.second); }
+            m->ss_pre.clear();
+            MMV_TRY(launch_sumsq_ranges(rg.data(), rn.data(), (int)rg.size(), m->acc + 3, m->ctx->num_sms, st, pp.data(), pn.data(),
+                                        (int)pp.size()));
         }
         adam_args_t a;
         m->adam_t += 1;

@@ -8,6 +8,8 @@
 
 #include <cuda_bf16.h>
 
+#include <algorithm>
+
 namespace mmv {
 
 // Order-deterministic: every block leaves its partial in a slot, the last block to finish (ticket) adds the slots
@@ -22,6 +24,9 @@ struct sumsq_ranges_t {
     const float *g[4];
     size_t n[4];
     int count;
+    const float *pre[8];   // already-squared partial sums (added as they are): the unpack passes of bf16 gradient buckets
+    int npre[8];
+    int pre_count;
 };
 
 __global__ void
@@ -47,6 +52,8 @@ sumsq_kernel(sumsq_ranges_t rg, double *out)
         }
         for (size_t k = n4 * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) s = fmaf(g[k], g[k], s);
     }
+    for (int r = 0; r < rg.pre_count; ++r)
+        for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < (size_t)rg.npre[r]; k += stride) s += rg.pre[r][k];
     __shared__ float scratch[32];
     __shared__ bool last;
     float v[1] = { s };
@@ -72,12 +79,18 @@ sumsq_kernel(sumsq_ranges_t rg, double *out)
 }
 
 int
-launch_sumsq_ranges(const float *const *g, const size_t *n, int count, double *out, int num_sms, cudaStream_t st)
+launch_sumsq_ranges(const float *const *g, const size_t *n, int count, double *out, int num_sms, cudaStream_t st,
+                    const float *const *pre, const int *npre, int pre_count)
 {
-    for (int i0 = 0; i0 < count; i0 += 4) {
+    MMV_CHECK(pre_count <= 8, "sumsq: at most 8 pre-summed ranges");
+    for (int i0 = 0; i0 < std::max(count, 1); i0 += 4) {
         sumsq_ranges_t rg;
         rg.count = 0;
+        rg.pre_count = 0;
         size_t total = 0;
+        if (i0 == 0)
+            for (int i = 0; i < pre_count; ++i)
+                if (npre[i] > 0) { rg.pre[rg.pre_count] = pre[i]; rg.npre[rg.pre_count] = npre[i]; total += (size_t)npre[i]; ++rg.pre_count; }
         for (int i = i0; i < count && i < i0 + 4; ++i) {
             if (n[i] == 0) continue;
             rg.g[rg.count] = g[i];
@@ -85,7 +98,7 @@ launch_sumsq_ranges(const float *const *g, const size_t *n, int count, double *o
             total += n[i];
             ++rg.count;
         }
-        if (rg.count == 0) continue;
+        if (rg.count == 0 && rg.pre_count == 0) continue;
         const int grid = (int)min_sz(min_sz((total + 1023) / 1024, (size_t)num_sms * 8), (size_t)kSumsqMaxBlocks);
         MMV_CUDA(launch_k(sumsq_kernel, dim3(grid), dim3(256), 0, st, rg, out)); ::mmv::count_launch();
     }
@@ -95,7 +108,7 @@ launch_sumsq_ranges(const float *const *g, const size_t *n, int count, double *o
 int
 launch_sumsq(const float *g, size_t n, double *out, int num_sms, cudaStream_t st)
 {
-    return launch_sumsq_ranges(&g, &n, 1, out, num_sms, st);
+    return launch_sumsq_ranges(&g, &n, 1, out, num_sms, st, nullptr, nullptr, 0);
 }
 
 __global__ void

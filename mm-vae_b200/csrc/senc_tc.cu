@@ -31,6 +31,9 @@ namespace {
 // ===========================================================================
 // panel build
 // ===========================================================================
+#ifndef MMV_PANEL_PREFETCH
+#define MMV_PANEL_PREFETCH 0
+#endif
 constexpr int kPanelThreads = 512;
 constexpr int kUn = 4;
 
@@ -38,7 +41,7 @@ constexpr int kUn = 4;
 // [k_lo, k_hi) by bisection of the sorted gene ids, so every CTA owns its buckets outright and the
 // grid covers the machine even at 64 cell tiles.  Unsorted rows: the whole run is scanned and filtered.
 __global__ void __launch_bounds__(kPanelThreads)
-panel_build_kernel(panel_args_t p, int nK, int nS, int stage)
+panel_build_kernel(panel_args_t p, int nK, int nS)
 {
     extern __shared__ int s_int[];
     __shared__ int s_scan[kPanelThreads];
@@ -51,27 +54,11 @@ panel_build_kernel(panel_args_t p, int nK, int nS, int stage)
     const int k_lo = (int)((int64_t)nK * sp / nS), k_hi = (int)((int64_t)nK * (sp + 1) / nS), nKl = k_hi - k_lo;
     int *s_off = s_int;               // [nKl + 1] exclusive offsets of this CTA's buckets
     int *s_cur = s_int + nKl + 1;     // [nKl] fill cursors
-    // stage != 0: the per-gene constants of this CTA's gene range live in shared memory for pass 2 (ncu r02 step 4: 7.8
-    // long-scoreboard stalls per issue — every entry's three dependent gathers by gene id went to L2)
-    const int nG = nKl * 64, g_base = k_lo * 64;
-    float *g_it = reinterpret_cast<float *>(s_int + 2 * (nKl + 1));   // [nG] 1 / t_j
-    float *g_wd = g_it + nG;                                          // [nG] depth weights (nb)
-    float *g_wn = g_wd + nG;                                          // [nG] nu_encoding weights (nb, H = 1)
     const bool sorted = p.unsorted != nullptr && *p.unsorted == 0;
     const bool filter = !sorted && nS > 1;
 
     for (int k = tid; k < nKl; k += kPanelThreads) s_cur[k] = 0;
     if (tid == 0) s_before = 0;
-    if (stage) {
-        const bool h1w = p.H == 1 && p.WnuT != nullptr;
-        for (int g = tid; g < nG; g += kPanelThreads) {
-            const int j = g_base + g;
-            const bool in = j < p.D;
-            g_it[g] = in ? p.inv_t[j] : 0.f;
-            g_wd[g] = (in && p.wdepth) ? p.wdepth[j] : 0.f;
-            g_wn[g] = (in && h1w) ? p.WnuT[j] : 0.f;
-        }
-    }
     // minibatch-local CSR offset of the tile's first row = run lengths of all earlier rows.  Every CTA adds them up
     // itself (<= B gathered loads from L2, 8 per thread at B = 4096): cheaper than a one-CTA scan kernel in front
     int prefix = 0;
@@ -104,6 +91,17 @@ panel_build_kernel(panel_args_t p, int nK, int nS, int stage)
         }
     }
     __syncthreads();
+#if MMV_PANEL_PREFETCH
+    // pull every row's slice of the CSR arrays into L2 before the two passes walk them: with a resident shard the rows of
+    // a minibatch are scattered over gigabytes, each run a cold DRAM + TLB miss behind only kUn loads in flight
+    for (int r = warp; r < nrows; r += NW) {
+        const int64_t beg = s_qlo[r], end = s_qhi[r];
+        for (int64_t q = beg + lane * 32; q < end; q += 32 * 32) {
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(p.indices + q));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(p.vals + q));
+        }
+    }
+#endif
     // ---- pass 1: bucket sizes
     int before_unsorted = 0;          // unsorted rows: count the entries that belong to earlier splits
     for (int r = warp; r < nrows; r += NW) {
@@ -196,15 +194,12 @@ panel_build_kernel(panel_args_t p, int nK, int nS, int stage)
             }
 #pragma unroll
             for (int u = 0; u < kUn; ++u) {
+                // (tried, r02g A/B: this CTA's gene range of the three arrays staged in shared memory — no gain, 0.106 vs
+                // 0.103 ms: the long-scoreboard stalls are the entry loads, not these L2-resident gathers)
                 const int jj = max(j[u], 0);
-                if (stage) {
-                    const int g = max(j[u] - g_base, 0);   // (valid entries lie inside the CTA's range)
-                    it[u] = g_it[g]; wd[u] = g_wd[g]; wn[u] = g_wn[g];
-                } else {
-                    it[u] = p.inv_t[jj];
-                    wd[u] = p.wdepth ? p.wdepth[jj] : 0.f;
-                    wn[u] = h_inline ? p.WnuT[jj] : 0.f;
-                }
+                it[u] = p.inv_t[jj];
+                wd[u] = p.wdepth ? p.wdepth[jj] : 0.f;
+                wn[u] = h_inline ? p.WnuT[jj] : 0.f;
             }
 #pragma unroll
             for (int u = 0; u < kUn; ++u) {
@@ -254,16 +249,12 @@ launch_panel_build(const panel_args_t &p, cudaStream_t st)
     int nS = (2 * std::max(p.num_sms, 1) + nT - 1) / nT;
     nS = std::max(1, std::min(std::min(nS, 8), nK));
     const int nKl = (nK + nS - 1) / nS + 1;
-    size_t smem = sizeof(int) * (2 * (size_t)nKl + 2);
+    const size_t smem = sizeof(int) * (2 * (size_t)nKl + 2);
     MMV_CHECK(smem <= 200 * 1024, "panel_build: %d genes exceed the shared-memory bucket table", p.D);
-    // + the gene range's constants when two CTAs still fit an SM with them
-    const size_t staged = smem + sizeof(float) * 3 * (size_t)nKl * 64;
-    const int stage = staged <= 100 * 1024 ? 1 : 0;
-    if (stage) smem = staged;
     MMV_TRY(dev_set_smem(reinterpret_cast<const void *>(panel_build_kernel), 200 * 1024));
     if (p.wdepth && p.dpre) MMV_CUDA(cudaMemsetAsync(p.dpre, 0, sizeof(float) * p.B, st));
     if (p.H > 0 && p.Hnu) MMV_CUDA(cudaMemsetAsync(p.Hnu, 0, sizeof(float) * (size_t)p.B * p.H, st));
-    MMV_CUDA(launch_k(panel_build_kernel, dim3(nT, nS), dim3(kPanelThreads), smem, st, p, nK, nS, stage));
+    MMV_CUDA(launch_k(panel_build_kernel, dim3(nT, nS), dim3(kPanelThreads), smem, st, p, nK, nS));
     ::mmv::count_launch();
     return 0;
 }
