@@ -32,7 +32,7 @@ namespace {
 // panel build
 // ===========================================================================
 #ifndef MMV_PANEL_PREFETCH
-#define MMV_PANEL_PREFETCH 0
+#define MMV_PANEL_PREFETCH 1
 #endif
 constexpr int kPanelThreads = 512;
 constexpr int kUn = 4;
