@@ -1174,10 +1174,13 @@ senc_tc_backward(const step_t &s, const senc_bwd_args_t &b)
     const int tiles = (D + 127) / 128, cols = (h1 + 255) / 256;
     const int waves = (tiles * cols + m->ctx->num_sms - 1) / m->ctx->num_sms;
     if (split_ar && waves >= 3) {
-        // multi GPU: the gene tiles in up to four parts of whole waves; each part's rows of dW1 are all-reduced on
+        // multi GPU: the gene tiles in parts of whole waves; each part's rows of dW1 are all-reduced on
         // the comm stream while the next part is multiplied.  dW1 is produced about as fast as NVLink reduces it, so
         // only the last (partial-wave) part's reduction is left over, and that one runs under the aux kernel below
-        static const int parts = [] { const char *e = getenv("MMV_DW1_PARTS"); return e ? std::max(1, atoi(e)) : 4; }();
+        // two parts (MMV_DW1_PARTS overrides): with the gradients as bf16 on the wire the reductions no longer lag the
+        // producers, and every further part costs two more launches and a partial wave (8 GPUs: 2.99 / 2.95 / 2.92 ms per
+        // step with 4 / 3 / 2 parts, profiles/r02n8c_summary.txt)
+        static const int parts = [] { const char *e = getenv("MMV_DW1_PARTS"); return e ? std::max(1, atoi(e)) : 2; }();
         const int per = std::max(1, (int)((int64_t)((waves + parts - 1) / parts) * m->ctx->num_sms / cols));
         const size_t off = m->tensors[L0.w].off;
         for (int t0 = 0; t0 < tiles; t0 += per) {
