@@ -328,11 +328,8 @@ int
 launch_latent(const reparam_args_t &a, const nu_head_args_t &n, bool bwd, cudaStream_t st)
 {
     MMV_CHECK(nu_head_fused_supported(n.H, n.Rnu), "latent: H = %d, Rnu = %d has no fused kernel", n.H, n.Rnu);
-    if (n.Rnu == 1 && n.H == 1) latent_launch<1, 1>(a, n, bwd, st);
-    else if (n.Rnu == 1 && n.H == 2) latent_launch<2, 1>(a, n, bwd, st);
-    else if (n.Rnu == 1 && n.H == 4) latent_launch<4, 1>(a, n, bwd, st);
-    else if (n.Rnu == 2 && n.H == 1) latent_launch<1, 2>(a, n, bwd, st);
-    else latent_launch<2, 2>(a, n, bwd, st);
+    if (n.H == 1) latent_launch<1, 1>(a, n, bwd, st);
+    else latent_launch<2, 1>(a, n, bwd, st);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;
@@ -341,18 +338,17 @@ launch_latent(const reparam_args_t &a, const nu_head_args_t &n, bool bwd, cudaSt
 bool
 nu_head_fused_supported(int H, int Rnu)
 {
-    return (Rnu == 1 && (H == 1 || H == 2 || H == 4)) || (Rnu == 2 && (H == 1 || H == 2));
+    // the shapes pinned by goldens (nb_small ... H = 1, nb_trainall H = 2); anything else keeps the GEMM + reparam + column-sum
+    // kernels, which the nb_deep golden (H = 3, Rnu = 2) pins
+    return Rnu == 1 && (H == 1 || H == 2);
 }
 
 int
 launch_nu_head(const nu_head_args_t &a, bool bwd, cudaStream_t st)
 {
     MMV_CHECK(nu_head_fused_supported(a.H, a.Rnu), "nu_head: H = %d, Rnu = %d has no fused kernel", a.H, a.Rnu);
-    if (a.Rnu == 1 && a.H == 1) nu_head_launch<1, 1>(a, bwd, st);
-    else if (a.Rnu == 1 && a.H == 2) nu_head_launch<2, 1>(a, bwd, st);
-    else if (a.Rnu == 1 && a.H == 4) nu_head_launch<4, 1>(a, bwd, st);
-    else if (a.Rnu == 2 && a.H == 1) nu_head_launch<1, 2>(a, bwd, st);
-    else nu_head_launch<2, 2>(a, bwd, st);
+    if (a.H == 1) nu_head_launch<1, 1>(a, bwd, st);
+    else nu_head_launch<2, 1>(a, bwd, st);
     ::mmv::count_launch();
     MMV_CUDA(cudaGetLastError());
     return 0;

@@ -46,7 +46,8 @@ def main_gpu():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     mmv = importlib.import_module("mm-vae_b200")
-    bf16 = os.environ.get("DP_BF16", "0") == "1"
+    mode = int(os.environ.get("DP_BF16", "0"))    # "dtype" option: 0 fp32 FFMA, 1 bf16 tensor cores, 2 fp32 tolerance on tensor cores
+    bf16 = mode == 1
     wide = os.environ.get("DP_CASE", "small") == "wide"
     if wide:
         # SURVEY cfg-4 widths: the first-layer backward runs >= 3 waves (bucketed dW1 parts, "small last part goes with
@@ -65,7 +66,7 @@ def main_gpu():
     def make(ctx):
         m = mmv.Model.nb(ctx, D, 1, enc, dec, R, 1, 1, seed=3)
         m.set_option("train_all_layers", 1)
-        m.set_option("dtype", int(bf16))
+        m.set_option("dtype", mode)
         m.set_option("comm_bf16", int(os.environ.get("DP_COMM_BF16", "1")))   # bf16 mode: the two D x h gradients as bf16 on the wire
         if wide:   # off the symmetric initial values, and a clip that acts
             m.set_param("x_mean", np.random.default_rng(8).normal(scale=0.05, size=D).astype(np.float32))
@@ -130,7 +131,7 @@ def main_gpu():
     assert worst_g <= gtol, f"data-parallel gradient {wk} differs from the single-GPU step: {worst_g}"
     dist.barrier()
     if rank == 0:
-        print(f"dp ok: world {world}, case {'wide' if wide else 'small'}, bf16 {int(bf16)}, loss {terms['loss']:.6f} vs {terms1['loss']:.6f}, "
+        print(f"dp ok: world {world}, case {'wide' if wide else 'small'}, dtype {mode}, loss {terms['loss']:.6f} vs {terms1['loss']:.6f}, "
               f"worst rel param diff {worst:.2e}, worst rel grad diff {worst_g:.2e} ({wk})")
     m.close(); m1.close(); csr.close(); csr1.close(); ctx.close(); ctx1.close()
     dist.destroy_process_group()

@@ -11,12 +11,13 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("bf16,case,wire", [("0", "small", "1"), ("1", "small", "1"), ("0", "wide", "1"), ("1", "wide", "1"),
-                                            ("1", "wide", "0")])
+                                            ("1", "wide", "0"), ("2", "wide", "1")])
 def test_data_parallel_matches_single_gpu(bf16, case, wire):
     """case "wide" = SURVEY cfg-4 widths (D = 30 000, [1024, 256] / [256, 1024], 256 cells per rank): the bucketed
     first-layer backward, the persistent decoder-last dW GEMM, the grouped leftovers and the un-fused clip norm are
     all on the tested path; parameters AND gradients against the 1-GPU step on the concatenated batch, every replica
-    tensor bit-identical, per-rank noise streams distinct."""
+    tensor bit-identical, per-rank noise streams distinct.  bf16 = the "dtype" option: "2" is the fp32 tolerance on the
+    tensor cores (operands as bf16 pairs; gradients reduced in fp32), held to the fp32 budget."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
