@@ -447,7 +447,7 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
 
     // the row whose dL/dlogit is still to be written (its p and g sit in shared memory, its hop is in flight)
     int prev_row = -1, prev_slot = 0;
-    float prev_dp = 0.f, prev_coef = 0.f;
+    float prev_depth = 0.f, prev_coef = 0.f;
 
     int slot = 0;                                        // it % 3
     for (int it = 0;; ++it) {
@@ -554,7 +554,10 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
                 }
             }
             if (rank == 0 && tid == 0) {
-                a.ddpre[prev_row] = s * a.inv_B * (prev_dp > 20.f ? 1.f : 1.f / (1.f + expf(-prev_dp)));
+                // d softplus(dp) / d dp = sigmoid(dp) = 1 - exp(-softplus(dp)): from the depth the row metadata carries — the
+                // pre-activation itself would be one more global load per row that EVERY warp waits for (6 % of the stall
+                // samples in profiles/r02_step9_ncu_full_sass_nb_likelihood_fast.txt); beyond the threshold it rounds to 1
+                a.ddpre[prev_row] = s * a.inv_B * -expm1f(-prev_depth);
                 a.dznu[prev_row] = dz;
             }
         }
@@ -646,7 +649,7 @@ nb_likelihood_fast_kernel(nb_lik_args_t a, int cs, int Ds)
         } else {
             __syncthreads();
         }
-        prev_row = row; prev_slot = slot; prev_dp = a.dpre[row]; prev_coef = coef;
+        prev_row = row; prev_slot = slot; prev_depth = depth; prev_coef = coef;
         slot = slot == 2 ? 0 : slot + 1;
         if (a.row_lse && rank == 0 && tid == 0) a.row_lse[row] = gm2 * kLn2 - logf(invS);
     }
