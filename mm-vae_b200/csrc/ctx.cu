@@ -123,8 +123,15 @@ mmv_ctx_create(int device, mmv_ctx **out)
     mmv_ctx *c = new mmv_ctx();
     c->device = device;
     c->num_sms = prop.multiProcessorCount;
-    MMV_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    // the step's stream sits one level above the lowest priority, the side stream on the lowest: where both have CTAs
+    // pending, the step's dependency chain goes first (the comm stream, comm.cu, takes the highest)
+    int prio_least = 0, prio_greatest = 0;
+    MMV_CUDA(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
+    MMV_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_greatest < prio_least ? prio_least - 1 : prio_least));
     MMV_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    MMV_CUDA(cudaStreamCreateWithPriority(&c->side_stream, cudaStreamNonBlocking, prio_least));
+    MMV_CUDA(cudaEventCreateWithFlags(&c->ev_side_fork, cudaEventDisableTiming));
+    MMV_CUDA(cudaEventCreateWithFlags(&c->ev_side_join, cudaEventDisableTiming));
     MMV_CUDA(cudaEventCreate(&c->ev0));
     MMV_CUDA(cudaEventCreate(&c->ev1));
     *out = c;
@@ -138,10 +145,14 @@ mmv_ctx_destroy(mmv_ctx *c)
     cudaSetDevice(c->device);
     mmv_comm_destroy(c);
     cudaStreamSynchronize(c->stream);
+    cudaStreamSynchronize(c->side_stream);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
+    cudaEventDestroy(c->ev_side_fork);
+    cudaEventDestroy(c->ev_side_join);
     cudaStreamDestroy(c->stream);
     cudaStreamDestroy(c->copy_stream);
+    cudaStreamDestroy(c->side_stream);
     delete c;
     return 0;
 }

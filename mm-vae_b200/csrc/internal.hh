@@ -15,6 +15,12 @@ struct mmv_ctx {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaStream_t copy_stream = nullptr;   // mmv_csr_update copies here, so minibatch k+1 uploads while step k runs
+    // Lowest-priority stream for work of a backward pass that only the optimiser consumes (the per-gene sums of dlogits,
+    // the hidden layers' weight-gradient GEMMs): it leaves the step's dependency chain and fills what the chain's
+    // kernels leave free (model.cu: side_fork / side_join)
+    cudaStream_t side_stream = nullptr;
+    cudaEvent_t ev_side_fork = nullptr, ev_side_join = nullptr;
+    bool side_busy = false;
     // NCCL data-parallel state (comm.cu)
     void *nccl_comm = nullptr;
     cudaStream_t comm_stream = nullptr;          // early gradient buckets are reduced here, under the rest of backward

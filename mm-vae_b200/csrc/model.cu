@@ -115,6 +115,9 @@ struct mmv_model {
     float lr = 1e-3f, weight_decay = 1e-4f, grad_clip = 1.f;
     bool train_all = false, frozen_grads = true, debug_outputs = false;
     bool nb_fast = true;                  // "nb_fast" option: tuned K4 kernel when eligible
+    // "side_stream" option (MMV_SIDE overrides the default): optimiser-only work of a backward pass leaves the step's stream
+    bool dw_side = false;                 // set by side_dw_t around the weight-gradient products that may leave the step's stream
+    bool side_on = [] { const char *e = getenv("MMV_SIDE"); return e ? atoi(e) != 0 : true; }();
     // "comm_bf16" option (MMV_COMM_BF16 overrides the default): in tensor-core mode the two D x h gradients cross NVLink as bf16
     bool comm_bf16 = [] { const char *e = getenv("MMV_COMM_BF16"); return e ? atoi(e) != 0 : true; }();
     bool use_tc = false;                  // "dtype" option: bf16 tcgen05 GEMMs (fp32 accumulate) vs fp32 FFMA
@@ -495,6 +498,7 @@ mmv_model_set_option(mmv_model *m, const char *key, double value)
     else if (k == "profile") m->profile = value != 0;
     else if (k == "nb_fast") m->nb_fast = value != 0;
     else if (k == "comm_bf16") m->comm_bf16 = value != 0;
+    else if (k == "side_stream") m->side_on = value != 0;
     else if (k == "dtype") {   // 0 = fp32 FFMA (parity mode), 1 = bf16 tensor-core GEMMs, 2 = fp32 tolerance on tensor cores (3 x bf16)
         m->use_tc = value != 0;
         m->tc3 = value == 2;
@@ -622,23 +626,26 @@ struct prof_scope_t {   // records a cudaEvent pair around a kernel group when p
     size_t idx = 0;
     bool on;
     nvtx_scope_t nvtx;
-    prof_scope_t(mmv_model *m_, const char *name) : m(m_), on(m_->profile), nvtx(name)
+    cudaStream_t st;
+    prof_scope_t(mmv_model *m_, const char *name, cudaStream_t st_ = nullptr)
+        : m(m_), on(m_->profile), nvtx(name), st(st_ ? st_ : m_->ctx->stream)
     {
         if (!on) return;
         mmv_model::prof_rec_t r;
         r.id = m->prof_id(name);
         r.e0 = m->prof_event();
         r.e1 = m->prof_event();
-        cudaEventRecord(r.e0, m->ctx->stream);
+        cudaEventRecord(r.e0, st);
         m->prof_recs.push_back(r);
         idx = m->prof_recs.size() - 1;
     }
     ~prof_scope_t()
     {
-        if (on) cudaEventRecord(m->prof_recs[idx].e1, m->ctx->stream);
+        if (on) cudaEventRecord(m->prof_recs[idx].e1, st);
     }
 };
 #define PROF(name) prof_scope_t _prof_scope(m, name)
+#define PROF_ON(name, stream) prof_scope_t _prof_scope(m, name, stream)   // a group launched on the side stream
 
 // bf16 mirror (and, in fp32-tolerance mode, the residual mirror) of the whole parameter buffer after a host-side change
 int
@@ -726,10 +733,40 @@ lo_of(const step_t &s, const float *p, size_t n, const void **out)
 // (A_hi B_lo, A_lo B_hi, A_hi B_hi) into one fp32 accumulator, so bias / ReLU / row statistics / the fused clip norm all
 // apply to the full-precision product in one epilogue.
 int
-gemm3(const step_t &s, gemm_tc_args_t t, const void *A_lo, const void *B_lo)
+gemm3(const step_t &s, gemm_tc_args_t t, const void *A_lo, const void *B_lo, cudaStream_t st = nullptr)
 {
     t.A_lo = A_lo; t.B_lo = B_lo; t.Cb = nullptr;
-    return launch_gemm_tc(t, s.st);
+    return launch_gemm_tc(t, st ? st : s.st);
+}
+
+// The side stream.  Some products of a backward pass are read by nobody before the optimiser: the per-gene sums of
+// dlogits (0.05 ms, HBM-bound, next to tensor-bound GEMMs) and the hidden layers' weight gradients (four launch-latency-
+// bound GEMMs of ~10 us each between the data-gradient GEMMs that ARE the chain).  side_fork() hands back a stream that
+// sees everything issued on the step's stream so far; mmv_step joins it before the first consumer (all-reduce leftovers,
+// clip norm, Adam, or the end of the call).  Inputs of the forked kernels are workspace arrays and activations that
+// nothing overwrites before the end of the step; their outputs are gradient tensors zeroed at the step's start.
+int
+side_fork(const step_t &s, cudaStream_t *out)
+{
+    mmv_ctx *c = s.m->ctx;
+    *out = s.st;
+    if (!s.m->side_on || !c->side_stream) return 0;
+    MMV_CUDA(cudaEventRecord(c->ev_side_fork, s.st));
+    MMV_CUDA(cudaStreamWaitEvent(c->side_stream, c->ev_side_fork, 0));
+    c->side_busy = true;
+    *out = c->side_stream;
+    return 0;
+}
+
+int
+side_join(mmv_model *m, cudaStream_t st)
+{
+    mmv_ctx *c = m->ctx;
+    if (!c->side_busy) return 0;
+    MMV_CUDA(cudaEventRecord(c->ev_side_join, c->side_stream));
+    MMV_CUDA(cudaStreamWaitEvent(st, c->ev_side_join, 0));
+    c->side_busy = false;
+    return 0;
 }
 
 // "<name>.bf" twin of an fp32 workspace array, registered so bf16_of() finds it without a cast kernel:
@@ -826,29 +863,35 @@ lin_bwd_weight(const step_t &s, const float *dY, int out, const float *X, int in
                const void *dY_lo = nullptr)
 {
     mmv_model *m = s.m;
+    const bool side = m->dw_side && sumsq == nullptr;   // (the product is read by the optimiser only: see side_fork)
+    cudaStream_t ws = s.st;
     if (dW && tc_ok(s, out, in, s.B, out, in)) {
         gemm_tc_args_t t;
         if (dY_bf) t.A = dY_bf; else MMV_TRY(bf16_of(s, dY, (size_t)s.B * out, &t.A));
         MMV_TRY(bf16_of(s, X, (size_t)s.B * in, &t.B));
         t.a_mn = 1; t.lda = out; t.b_mn = 1; t.ldb = in; t.C = dW; t.ldc = in; t.M = out; t.N = in; t.K = s.B;
         t.beta = beta; t.sumsq = sumsq; t.sumsq_done = sumsq_done;
-        PROF(tag);
         if (m->tc3) {
             MMV_CHECK(dY != nullptr || dY_lo != nullptr, "lin_bwd_weight: the fp32-tolerance mode needs an fp32 gradient or a hi + lo pair");
             const void *Al = dY_lo, *Bl = nullptr;
             if (!Al) MMV_TRY(lo_of(s, dY, (size_t)s.B * out, &Al));
             MMV_TRY(lo_of(s, X, (size_t)s.B * in, &Bl));
-            MMV_TRY(gemm3(s, t, Al, Bl));
+            if (side) MMV_TRY(side_fork(s, &ws));   // (after the casts / splits, which run on the step's stream)
+            PROF_ON(tag, ws);
+            MMV_TRY(gemm3(s, t, Al, Bl, ws));
         } else {
-            MMV_TRY(launch_gemm_tc(t, s.st));
+            if (side) MMV_TRY(side_fork(s, &ws));
+            PROF_ON(tag, ws);
+            MMV_TRY(launch_gemm_tc(t, ws));
         }
     } else if (dW) {
         MMV_CHECK(dY != nullptr, "lin_bwd_weight: fp32 path needs an fp32 gradient");
-        PROF(tag);
+        if (side) MMV_TRY(side_fork(s, &ws));
+        PROF_ON(tag, ws);
         gemm_args_t g;
         g.A = dY; g.lda = out; g.transA = 1; g.B = X; g.ldb = in;
         g.C = dW; g.ldc = in; g.M = out; g.N = in; g.K = s.B; g.beta = beta;
-        MMV_TRY(launch_gemm_f32(g, s.st));
+        MMV_TRY(launch_gemm_f32(g, ws));
     }
     if (db) {
         colsum_args_t c;
@@ -971,6 +1014,12 @@ allreduce_grad_async(const step_t &s, int t)
     return 0;
 }
 
+struct side_dw_t {   // weight-gradient products issued inside this scope may run on the side stream
+    mmv_model *m;
+    side_dw_t(mmv_model *m_, bool on) : m(m_) { m->dw_side = on; }
+    ~side_dw_t() { m->dw_side = false; }
+};
+
 // backward through the decoder given dG (in "G", in place) -> "dz"
 int
 decoder_backward(const step_t &s)
@@ -990,6 +1039,7 @@ decoder_backward(const step_t &s)
         // single GPU, optimiser step in the same call: the overwriting GEMM also adds ||dW||^2 to the clip norm
         const bool fuse_ss = last && s.optim && m->ctx->nranks == 1 && m->optimised(L.w);
         int ss_ok = 0;
+        side_dw_t side(m, !last);   // the last layer's product covers the machine and feeds the first all-reduce bucket
         MMV_TRY(lin_bwd_weight(s, dY, L.out, X, L.in, m->want_grad(L.w) ? m->G(L.w) : nullptr,
                                (!last && m->want_grad(L.b)) ? m->G(L.b) : nullptr,
                                (last && m->optimised(L.w)) ? 0.f : 1.f,   // mmv_step leaves this one un-zeroed
@@ -1049,7 +1099,10 @@ encoder_backward(const step_t &s, bool with_covar, const nu_head_args_t *nu = nu
     }
     const linear_t &Hd = m->head_mu;
     const float *X = m->ws["enc_act" + std::to_string(k - 1)].as<float>();
-    MMV_TRY(lin_bwd_weight(s, r.dhead, 2 * R, X, Hd.in, m->G(Hd.w), m->G(Hd.b)));
+    {
+        side_dw_t side(m, true);
+        MMV_TRY(lin_bwd_weight(s, r.dhead, 2 * R, X, Hd.in, m->G(Hd.w), m->G(Hd.b)));
+    }
     float *dX = WS("d_enc" + std::to_string(k - 1), (size_t)B * Hd.in); NEED(dX);
     MMV_TRY(lin_bwd_data(s, r.dhead, 2 * R, m->P(Hd.w), Hd.in, dX));
     if (m->relu) MMV_TRY(launch_relu_bwd(dX, X, (size_t)B * Hd.in, s.st));
@@ -1068,6 +1121,7 @@ encoder_backward(const step_t &s, bool with_covar, const nu_head_args_t *nu = nu
                 MMV_TRY(launch_angular_bwd(m->P(L.w), dWp, scale, dot, m->G(L.w), L.out, L.in, L.in, 1, s.st));
             }
         } else {
+            side_dw_t side(m, true);
             MMV_TRY(lin_bwd_weight(s, dY, L.out, Xl, L.in, m->want_grad(L.w) ? m->G(L.w) : nullptr,
                                    (L.b >= 0 && m->want_grad(L.b)) ? m->G(L.b) : nullptr));
         }
@@ -1353,14 +1407,16 @@ nb_forward_backward(const step_t &s)
     if (!s.bwd) return 0;
 
     // per-gene sums of dlogits: mu_decoding.bias, covar_decoding.{bias,weight}, mu_bias
-    {
-        PROF("colsum_dlogits");
+    {   // (on the side stream: an HBM-bound pass over the gradient next to the two tensor-bound GEMMs that read it too)
+        cudaStream_t cs = s.st;
+        MMV_TRY(side_fork(s, &cs));
+        PROF_ON("colsum_dlogits", cs);
         colsum_args_t c;
         c.X = k.dlogits; c.Xb = k.dlogits_bf16; c.Xb2 = k.dlogits_lo; c.M = B; c.N = D; c.ldx = D;
         c.out_sum = m->want_grad(Ld.b) ? m->G(Ld.b) : nullptr;
         c.out_sum2 = m->G(m->covar_dec.b); c.out_sum3 = m->G(m->t_mu_bias);
         c.out_cov = m->G(m->covar_dec.w); c.cov = s.cov; c.cells = s.cells; c.C = C;
-        MMV_TRY(launch_colsum(c, s.st));
+        MMV_TRY(launch_colsum(c, cs));
     }
     // nu decoder: u = W_nd znu + b_nd - nu_bias.  K4's per-gene sums are added to the three gradients as one-row
     // "column sums" of the pass's grouped launch (flush_colsums)
@@ -1519,9 +1575,13 @@ vmf_forward_backward(const step_t &s)
 
     {   // decoding.bias = column sums of dL/dpre ; covar_decoding_ from dL/dq
         colsum_args_t c;
-        PROF("colsum_dlogits");
         c.X = k.dpre; c.Xb = k.dpre_bf16; c.M = B; c.N = D; c.ldx = D; c.out_sum = m->want_grad(Ld.b) ? m->G(Ld.b) : nullptr;
-        if (c.out_sum) MMV_TRY(launch_colsum(c, s.st));
+        if (c.out_sum) {   // (on the side stream, as in the nb pass)
+            cudaStream_t cs = s.st;
+            MMV_TRY(side_fork(s, &cs));
+            PROF_ON("colsum_dlogits", cs);
+            MMV_TRY(launch_colsum(c, cs));
+        }
     }
     {   // K5's per-gene sums join the two gradients as one-row segments of the pass's grouped column-sum launch
         colsum_args_t c;
@@ -1730,7 +1790,9 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
                 if (i < ns) pos = skip[i][1];
             }
         }
-        MMV_TRY(m->is_vmf ? vmf_forward_backward(s) : nb_forward_backward(s));
+        const int rc_fb = m->is_vmf ? vmf_forward_backward(s) : nb_forward_backward(s);
+        MMV_TRY(side_join(m, st));   // (also after a failed pass: nothing may stay in flight behind the caller's back)
+        MMV_TRY(rc_fb);
         if (csr->ev_consumed) MMV_CUDA(cudaEventRecord(csr->ev_consumed, st));   // the slot may be refilled from here on
     } else {
         MMV_CUDA(cudaMemsetAsync(m->acc + 3, 0, sizeof(double), st));

@@ -23,6 +23,7 @@
 #include <cuda_bf16.h>
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace mmv {
 
@@ -245,8 +246,11 @@ int
 launch_panel_build(const panel_args_t &p, cudaStream_t st)
 {
     const int nT = panel_tiles(p.B), nK = panel_chunks(p.D);
-    // enough gene splits per cell tile for two CTAs per SM
-    int nS = (2 * std::max(p.num_sms, 1) + nT - 1) / nT;
+    // gene splits per cell tile: as many as fit ONE wave of two 512-thread CTAs per SM (64 registers per thread).  Rounding
+    // up instead (5 splits x 64 tiles = 320 CTAs on 296 slots at B = 4096) leaves a second, nearly empty wave behind.
+    const int slots = 2 * std::max(p.num_sms, 1);
+    int nS = nT <= slots ? slots / nT : 1;
+    if (const char *e = getenv("MMV_PANEL_SPLITS")) nS = atoi(e);
     nS = std::max(1, std::min(std::min(nS, 8), nK));
     const int nKl = (nK + nS - 1) / nS + 1;
     const size_t smem = sizeof(int) * (2 * (size_t)nKl + 2);
