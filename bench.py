@@ -607,7 +607,7 @@ def run_own(args):
         t, c = model.profile_read(name)
         if c:
             prof[name] = (t, c)
-    for name in ("batch_csc", "allreduce", "colsum", "to_bf16", "vmf_latent"):
+    for name in ("batch_csc", "allreduce", "colsum", "to_bf16", "vmf_latent", "panel_aux_bwd"):
         t, c = model.profile_read(name)
         if c:
             prof[name] = (t, c)
@@ -739,6 +739,10 @@ def run_own(args):
             ent["basis"] = "dense-equivalent flops 2 B D h1 (the densified zeros are multiplied too)"
             ent["hbm_contract_bytes"] = k1c[name]
             ent["frac_hbm_contract"] = round(k1c[name] / (per * 1e-3) / 1e9 / pk["hbm"], 4)
+        if name in ("colsum_dlogits", "colsum", "panel_aux_bwd"):
+            # launched on the library's lowest-priority side stream next to the step's chain (model.cu: side_fork): the time
+            # is the group's own span while it shares the SMs, not time added to the step; gemm_other is half and half
+            ent["stream"] = "side"
         kernels[name] = ent
     dom = max((n for n in kernels if "frac" in kernels[n]), key=lambda n: kernels[n]["share"])
     traffic, traffic_src = measured_traffic(dom)

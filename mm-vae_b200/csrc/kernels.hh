@@ -119,6 +119,7 @@ struct senc_bwd_args_t {
     const float *ddpre = nullptr;     // [B]
     float *dWnuT = nullptr;           // [D x H]
     float *dwdepth = nullptr;         // [D]
+    bool aux_done = false;            // tensor-core path: dWnuT / dwdepth were already issued (side stream, model.cu)
 };
 int launch_senc_bwd(const senc_bwd_args_t &a, cudaStream_t st);
 

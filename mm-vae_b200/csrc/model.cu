@@ -13,6 +13,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <functional>
 #include <map>
 #include <memory>
 #include <set>
@@ -758,6 +759,29 @@ side_fork(const step_t &s, cudaStream_t *out)
     return 0;
 }
 
+// The two halves of side_fork, for work that should be ISSUED behind the step's next kernel but depends only on what
+// precedes it (the chain's kernel then has its CTAs resident before the side kernel's compete for the SMs).
+int
+side_mark(const step_t &s)
+{
+    mmv_ctx *c = s.m->ctx;
+    if (!s.m->side_on || !c->side_stream) return 0;
+    MMV_CUDA(cudaEventRecord(c->ev_side_fork, s.st));
+    return 0;
+}
+
+int
+side_after_mark(const step_t &s, cudaStream_t *out)
+{
+    mmv_ctx *c = s.m->ctx;
+    *out = s.st;
+    if (!s.m->side_on || !c->side_stream) return 0;
+    MMV_CUDA(cudaStreamWaitEvent(c->side_stream, c->ev_side_fork, 0));
+    c->side_busy = true;
+    *out = c->side_stream;
+    return 0;
+}
+
 int
 side_join(mmv_model *m, cudaStream_t st)
 {
@@ -906,14 +930,32 @@ lin_bwd_weight(const step_t &s, const float *dY, int out, const float *X, int in
 // The deferred column sums of a backward pass in one launch.  Their inputs (the dY of every layer) are distinct
 // workspace arrays that live to the end of the step; the only consumer inside the step is the first layer's backward
 // (Delta), so the flush sits right before it.
+// split: the segment that produces Delta is read inside the step, by the first layer's row pass — it goes alone on the
+// step's stream; the others are bias gradients that only the optimiser reads and leave for the side stream (a kernel
+// there does not start while the step's stream has CTAs left to dispatch, so nothing the chain waits for may sit there).
 int
-flush_colsums(const step_t &s)
+flush_colsums(const step_t &s, bool split = false)
 {
     mmv_model *m = s.m;
-    if (m->pending_colsum.empty()) return 0;
-    PROF("colsum");
-    const int rc = launch_colsum_multi(m->pending_colsum.data(), (int)m->pending_colsum.size(), s.st);
-    m->pending_colsum.clear();
+    std::vector<colsum_args_t> &pc = m->pending_colsum;
+    if (pc.empty()) return 0;
+    cudaStream_t st = s.st;
+    if (split && m->side_on && pc.size() > 1) {
+        auto dl = m->ws.find("Delta");
+        for (size_t i = 0; dl != m->ws.end() && i < pc.size(); ++i) {
+            if ((const void *)pc[i].out_sum != dl->second.p) continue;
+            {
+                PROF("colsum");
+                MMV_TRY(launch_colsum_multi(&pc[i], 1, s.st));
+            }
+            pc.erase(pc.begin() + (long)i);
+            MMV_TRY(side_fork(s, &st));
+            break;
+        }
+    }
+    PROF_ON("colsum", st);
+    const int rc = launch_colsum_multi(pc.data(), (int)pc.size(), st);
+    pc.clear();
     return rc;
 }
 
@@ -1022,7 +1064,7 @@ struct side_dw_t {   // weight-gradient products issued inside this scope may ru
 
 // backward through the decoder given dG (in "G", in place) -> "dz"
 int
-decoder_backward(const step_t &s)
+decoder_backward(const step_t &s, const std::function<int()> *after_last_dw = nullptr)
 {
     mmv_model *m = s.m;
     const int B = s.B, R = (int)m->R;
@@ -1045,6 +1087,7 @@ decoder_backward(const step_t &s)
                                (last && m->optimised(L.w)) ? 0.f : 1.f,   // mmv_step leaves this one un-zeroed
                                last ? "gemm_dec_last_dw" : "gemm_other", dY_bf, fuse_ss ? m->acc + 3 : nullptr, &ss_ok, dY_lo));
         // multi GPU, first bucket: the largest gradient is final long before backward ends — reduce it under the rest
+        if (last && after_last_dw) MMV_TRY((*after_last_dw)());   // (side-stream work issued behind the machine-wide product)
         if (last) trace_mark(m->ctx, "decoder-last dW done");
         if (last && m->want_grad(L.w)) MMV_TRY(allreduce_grad_async(s, L.w));
         if (ss_ok) m->ss_done.emplace_back(m->tensors[L.w].off, m->tensors[L.w].off + m->tensors[L.w].numel());
@@ -1061,7 +1104,8 @@ decoder_backward(const step_t &s)
 // backward through reparam + heads + hidden encoder layers -> "d_enc0" (gradient
 // w.r.t. the first layer's output, ReLU mask applied) and "Delta" = its column sums
 int
-encoder_backward(const step_t &s, bool with_covar, const nu_head_args_t *nu = nullptr)
+encoder_backward(const step_t &s, bool with_covar, const nu_head_args_t *nu = nullptr,
+                 const std::function<int()> *after_latent = nullptr)
 {
     mmv_model *m = s.m;
     const int B = s.B, R = (int)m->R, C = (int)m->C;
@@ -1090,6 +1134,7 @@ encoder_backward(const step_t &s, bool with_covar, const nu_head_args_t *nu = nu
         if (nu) MMV_TRY(launch_latent(r, *nu, true, s.st));   // nb: + the nu heads' backward, one launch
         else MMV_TRY(launch_reparam_bwd(r, s.st));
     }
+    if (after_latent) MMV_TRY((*after_latent)());   // (side-stream work whose inputs are complete from here on)
     if (with_covar) {   // covar_encoding grads: dW_ce[r, c] = sum_i dmean_ir c_ic ; db_ce = sum_i dmean_ir
         colsum_args_t c;
         c.X = r.dhead; c.M = B; c.N = R; c.ldx = 2 * R;
@@ -1168,10 +1213,17 @@ senc_tc_ok(const step_t &s)
 
 // Re-bucket the minibatch into the tiled-COO panel ("pan_*" workspaces) and run the densify GEMM
 // H1 = A W1eff^T + bias_eff.  Also produces Hnu / dpre (nb) or rownorm (vmf).
+// prep: launches that prepare the product's other inputs (effective bias; vmf: effective weight) and do not depend on
+// the panel.  They go to the side stream — forked in FRONT of the panel build, issued BEHIND it (the chain's kernel gets
+// its CTAs resident first).  vmf gains the 0.03 ms of its weight materialisation; for nb the mat-vec's HBM stream slows
+// the latency-bound panel build by about what it saves (0.088 -> 0.12 ms next to it, profiles/r02_step12_side_stream_ab.txt).
 int
-senc_tc_forward(const step_t &s, const senc_args_t &e, const void *w1eff_bf16)
+senc_tc_forward(const step_t &s, const senc_args_t &e, const void *w1eff_bf16, const std::function<int(cudaStream_t)> *prep = nullptr)
 {
     mmv_model *m = s.m;
+    mmv_ctx *c = m->ctx;
+    const bool fork = prep && m->side_on && c->side_stream;
+    if (fork) MMV_CUDA(cudaEventRecord(c->ev_side_fork, s.st));
     const int B = s.B, D = (int)m->D, h1 = e.h1;
     const size_t cap = (size_t)B * (size_t)std::max<int64_t>(s.csr->max_row_nnz, 1);
     const int nT = panel_tiles(B), nK = panel_chunks(D);
@@ -1189,6 +1241,16 @@ senc_tc_forward(const step_t &s, const senc_args_t &e, const void *w1eff_bf16)
         PROF("panel_build");
         MMV_TRY(launch_panel_build(p, s.st));
     }
+    if (prep) {
+        cudaStream_t ps = s.st;
+        if (fork) {
+            MMV_CUDA(cudaStreamWaitEvent(c->side_stream, c->ev_side_fork, 0));
+            c->side_busy = true;
+            ps = c->side_stream;
+        }
+        MMV_TRY((*prep)(ps));
+    }
+    MMV_TRY(side_join(m, s.st));
     senc_tc_args_t a;
     a.bucket_ptr = p.bucket_ptr; a.ent = p.ent; a.B = B; a.D = D; a.h1 = h1;
     a.dense_bf16 = w1eff_bf16; a.bias_eff = e.bias_eff; a.relu = e.relu; a.H1 = e.H1;
@@ -1260,7 +1322,7 @@ senc_tc_backward(const step_t &s, const senc_bwd_args_t &b)
         MMV_TRY(launch_senc_tc_bwd(a, s.st));
         MMV_TRY(launch_senc_row_pass(a, b.ln_x_sd, b.dx_mean, b.dln_x_sd, s.st));
     }
-    if (!b.angular && b.dWnuT)
+    if (!b.angular && b.dWnuT && !b.aux_done)
         MMV_TRY(launch_panel_aux_bwd(a.bucket_ptr, a.ent, m->ws["pan_x"].as<float>(), B, D, b.H, b.dHnu, b.ddpre,
                                      b.dWnuT, b.dwdepth, s.st));
     return 0;
@@ -1322,14 +1384,18 @@ nb_forward_backward(const step_t &s)
     MMV_TRY(launch_nb_gene_prologue(m->P(m->t_ln_x_sd), 1e-4f, inv_t, m->P(Ld.b), m->P(m->covar_dec.b), m->P(m->t_mu_bias),
                                     fast ? k.Wcd : nullptr, C, m->P(m->nu_dec.b), m->P(m->t_nu_bias), abias, ubias, D, s.st));
     float *bias_eff = WS("bias_eff", h1); NEED(bias_eff);
-    MMV_CUDA(cudaMemcpyAsync(bias_eff, m->P(L0.b), sizeof(float) * h1, cudaMemcpyDeviceToDevice, s.st));
     const bool tc_senc = senc_tc_ok(s);
     const void *w1b = nullptr;
     if (tc_senc) MMV_TRY(bf16_of(s, m->P(L0.w), (size_t)D * h1, &w1b));
-    if (tc_senc && !m->tc3 && senc_bias_bf16_supported(h1))   // the mean shift against the same bf16 weights the GEMM multiplies with
-        MMV_TRY(launch_senc_bias_bf16(w1b, m->P(m->t_x_mean), inv_t, bias_eff, D, h1, s.st));
-    else
-        MMV_TRY(launch_senc_bias(m->P(L0.w), m->P(m->t_x_mean), inv_t, nullptr, bias_eff, D, h1, 0, s.st));
+    // the effective bias (a mat-vec over the whole first-layer weight) and the panel build are independent: the former
+    // runs on the side stream next to the latter (senc_tc_forward)
+    const std::function<int(cudaStream_t)> prep = [&](cudaStream_t ps) -> int {
+        MMV_CUDA(cudaMemcpyAsync(bias_eff, m->P(L0.b), sizeof(float) * h1, cudaMemcpyDeviceToDevice, ps));
+        if (tc_senc && !m->tc3 && senc_bias_bf16_supported(h1))   // the mean shift against the same bf16 weights the GEMM multiplies with
+            return launch_senc_bias_bf16(w1b, m->P(m->t_x_mean), inv_t, bias_eff, D, h1, ps);
+        return launch_senc_bias(m->P(L0.w), m->P(m->t_x_mean), inv_t, nullptr, bias_eff, D, h1, 0, ps);
+    };
+    if (!tc_senc) MMV_TRY(prep(s.st));
 
     senc_args_t e;
     e.indptr = s.csr->indptr; e.indices = s.csr->indices; e.vals = s.csr->vals; e.cells = s.cells;
@@ -1339,7 +1405,7 @@ nb_forward_backward(const step_t &s)
     e.wdepth = m->P(m->depth.w); e.bdepth = m->P(m->depth.b);
     e.Hnu = WS("Hnu", (size_t)B * H); e.dpre = WS("dpre", B); NEED(e.Hnu); NEED(e.dpre);
     if (tc_senc) {
-        MMV_TRY(senc_tc_forward(s, e, w1b));
+        MMV_TRY(senc_tc_forward(s, e, w1b, &prep));
     } else {
         PROF("senc_fwd");
         MMV_TRY(launch_senc_fwd(e, s.st));
@@ -1407,17 +1473,20 @@ nb_forward_backward(const step_t &s)
     if (!s.bwd) return 0;
 
     // per-gene sums of dlogits: mu_decoding.bias, covar_decoding.{bias,weight}, mu_bias
-    {   // (on the side stream: an HBM-bound pass over the gradient next to the two tensor-bound GEMMs that read it too)
+    // (on the side stream: an HBM-bound pass over the gradient next to the two tensor-bound GEMMs that read it too;
+    // forked here, issued behind the first of them)
+    MMV_TRY(side_mark(s));
+    const std::function<int()> dl_sums = [&]() -> int {
         cudaStream_t cs = s.st;
-        MMV_TRY(side_fork(s, &cs));
+        MMV_TRY(side_after_mark(s, &cs));
         PROF_ON("colsum_dlogits", cs);
         colsum_args_t c;
         c.X = k.dlogits; c.Xb = k.dlogits_bf16; c.Xb2 = k.dlogits_lo; c.M = B; c.N = D; c.ldx = D;
         c.out_sum = m->want_grad(Ld.b) ? m->G(Ld.b) : nullptr;
         c.out_sum2 = m->G(m->covar_dec.b); c.out_sum3 = m->G(m->t_mu_bias);
         c.out_cov = m->G(m->covar_dec.w); c.cov = s.cov; c.cells = s.cells; c.C = C;
-        MMV_TRY(launch_colsum(c, cs));
-    }
+        return launch_colsum(c, cs);
+    };
     // nu decoder: u = W_nd znu + b_nd - nu_bias.  K4's per-gene sums are added to the three gradients as one-row
     // "column sums" of the pass's grouped launch (flush_colsums)
     {
@@ -1431,14 +1500,27 @@ nb_forward_backward(const step_t &s)
     }
 
     trace_mark(m->ctx, "likelihood + column sums done");
-    MMV_TRY(decoder_backward(s));
+    MMV_TRY(decoder_backward(s, &dl_sums));
     trace_mark(m->ctx, "decoder backward done");
     // nu encoder backward
     float *dHnu = WS("dHnu", (size_t)B * H); NEED(dHnu);
+    bool aux_done = false;
     if (nu_fused) {   // reparam backward, the heads' dW / db, dHnu and the two bias sums behind it: with the mu reparam's launch
         nh.dz = k.dznu; nh.ddpre = k.ddpre; nh.kl_weight = s.klw; nh.inv_B = s.inv_B;
         nh.dHnu = dHnu; nh.dW = m->G(Hn.w); nh.db = m->G(Hn.b); nh.dbnu = m->G(m->nu_enc.b); nh.ddepth_b = m->G(m->depth.b);
-        MMV_TRY(encoder_backward(s, true, &nh));
+        // dWnu / dw_depth need the panel, dHnu and d depth — all there once the latent backward has run: on the side
+        // stream under the hidden layers' launch-latency-bound GEMM chain, not after the first layer's product
+        const std::function<int()> aux = [&]() -> int {
+            if (!(tc_senc && m->side_on)) return 0;
+            cudaStream_t as = s.st;
+            MMV_TRY(side_fork(s, &as));
+            PROF_ON("panel_aux_bwd", as);
+            MMV_TRY(launch_panel_aux_bwd(m->ws["pan_bptr"].as<int>(), m->ws["pan_ent"].as<uint32_t>(), m->ws["pan_x"].as<float>(),
+                                         B, D, H, dHnu, k.ddpre, m->G(m->nu_enc.w), m->G(m->depth.w), as));
+            aux_done = true;
+            return 0;
+        };
+        MMV_TRY(encoder_backward(s, true, &nh, &aux));
     } else {
         MMV_TRY(encoder_backward(s, true));
         rn.dz = k.dznu; rn.dhead = WS("dhead_nu", (size_t)B * 2 * Rnu); NEED(rn.dhead);
@@ -1453,7 +1535,7 @@ nb_forward_backward(const step_t &s)
         c2.X = k.ddpre; c2.M = B; c2.N = 1; c2.ldx = 1; c2.out_sum = m->G(m->depth.b);
         m->pending_colsum.push_back(c2);
     }
-    MMV_TRY(flush_colsums(s));   // Delta (first layer's backward reads it) and every bias gradient of the pass
+    MMV_TRY(flush_colsums(s, true));   // Delta (first layer's backward reads it) and every bias gradient of the pass
 
     if (!tc_senc) {
         PROF("batch_csc");
@@ -1470,7 +1552,7 @@ nb_forward_backward(const step_t &s)
     b.W1T = m->P(L0.w); b.inv_t = inv_t; b.x_mean = m->P(m->t_x_mean); b.ln_x_sd = m->P(m->t_ln_x_sd);
     b.dW1T = m->want_grad(L0.w) ? m->G(L0.w) : nullptr;
     b.dx_mean = m->G(m->t_x_mean); b.dln_x_sd = m->G(m->t_ln_x_sd);
-    b.dHnu = dHnu; b.ddpre = k.ddpre; b.dWnuT = m->G(m->nu_enc.w); b.dwdepth = m->G(m->depth.w);
+    b.dHnu = dHnu; b.ddpre = k.ddpre; b.dWnuT = m->G(m->nu_enc.w); b.dwdepth = m->G(m->depth.w); b.aux_done = aux_done;
     trace_mark(m->ctx, "encoder backward (dense part) done");
     if (tc_senc) {
         MMV_TRY(senc_tc_backward(s, b));
@@ -1499,17 +1581,19 @@ vmf_forward_backward(const step_t &s)
     float *col_scale = WS("ang_scale0", h1); NEED(col_scale);
     MMV_TRY(launch_angular_scale(m->P(L0.w), col_scale, h1, D, 1, (size_t)h1, s.st));
     float *bias_eff = WS("bias_eff", h1); NEED(bias_eff);
-    MMV_CUDA(cudaMemsetAsync(bias_eff, 0, sizeof(float) * h1, s.st));                 // Angular has no bias
     const bool tc_senc = senc_tc_ok(s);
     void *w1b = nullptr;
-    if (tc_senc) {   // B operand = (relu(W) + 1e-4) * col_scale, materialised in bf16 once per step
-        w1b = m->W("w1eff.bf", (size_t)D * h1 * 2); NEED(w1b);
-        MMV_TRY(launch_w1eff_bf16(m->P(L0.w), col_scale, w1b, D, h1, s.st));
-    }
-    if (tc_senc && senc_bias_bf16_supported(h1))
-        MMV_TRY(launch_senc_bias_bf16(w1b, m->P(m->t_x_mean), inv_t, bias_eff, D, h1, s.st));
-    else
-        MMV_TRY(launch_senc_bias(m->P(L0.w), m->P(m->t_x_mean), inv_t, col_scale, bias_eff, D, h1, 1, s.st));
+    if (tc_senc) { w1b = m->W("w1eff.bf", (size_t)D * h1 * 2); NEED(w1b); }
+    // effective weight and bias on the side stream, next to the panel build (senc_tc_forward)
+    const std::function<int(cudaStream_t)> prep = [&](cudaStream_t ps) -> int {
+        MMV_CUDA(cudaMemsetAsync(bias_eff, 0, sizeof(float) * h1, ps));               // Angular has no bias
+        if (tc_senc)   // B operand = (relu(W) + 1e-4) * col_scale, materialised in bf16 once per step
+            MMV_TRY(launch_w1eff_bf16(m->P(L0.w), col_scale, w1b, D, h1, ps));
+        if (tc_senc && senc_bias_bf16_supported(h1))
+            return launch_senc_bias_bf16(w1b, m->P(m->t_x_mean), inv_t, bias_eff, D, h1, ps);
+        return launch_senc_bias(m->P(L0.w), m->P(m->t_x_mean), inv_t, col_scale, bias_eff, D, h1, 1, ps);
+    };
+    if (!tc_senc) MMV_TRY(prep(s.st));
 
     senc_args_t e;
     e.indptr = s.csr->indptr; e.indices = s.csr->indices; e.vals = s.csr->vals; e.cells = s.cells;
@@ -1517,7 +1601,7 @@ vmf_forward_backward(const step_t &s)
     e.col_scale = col_scale; e.relu = m->relu;
     e.H1 = WS("enc_act0", (size_t)B * h1); e.rownorm = WS("rownorm", B); NEED(e.H1); NEED(e.rownorm);
     if (tc_senc) {
-        MMV_TRY(senc_tc_forward(s, e, w1b));
+        MMV_TRY(senc_tc_forward(s, e, w1b, &prep));
     } else {
         PROF("senc_fwd");
         MMV_TRY(launch_senc_fwd(e, s.st));
@@ -1573,16 +1657,18 @@ vmf_forward_backward(const step_t &s)
     MMV_TRY(launch_vmf_scalar(sc, s.st));
     if (!s.bwd) return 0;
 
-    {   // decoding.bias = column sums of dL/dpre ; covar_decoding_ from dL/dq
+    // decoding.bias = column sums of dL/dpre (covar_decoding_ from dL/dq: K5's per-gene sums below); on the side stream
+    // behind the decoder-last dW, as in the nb pass
+    MMV_TRY(side_mark(s));
+    const std::function<int()> dl_sums = [&]() -> int {
         colsum_args_t c;
         c.X = k.dpre; c.Xb = k.dpre_bf16; c.M = B; c.N = D; c.ldx = D; c.out_sum = m->want_grad(Ld.b) ? m->G(Ld.b) : nullptr;
-        if (c.out_sum) {   // (on the side stream, as in the nb pass)
-            cudaStream_t cs = s.st;
-            MMV_TRY(side_fork(s, &cs));
-            PROF_ON("colsum_dlogits", cs);
-            MMV_TRY(launch_colsum(c, cs));
-        }
-    }
+        if (!c.out_sum) return 0;
+        cudaStream_t cs = s.st;
+        MMV_TRY(side_after_mark(s, &cs));
+        PROF_ON("colsum_dlogits", cs);
+        return launch_colsum(c, cs);
+    };
     {   // K5's per-gene sums join the two gradients as one-row segments of the pass's grouped column-sum launch
         colsum_args_t c;
         c.X = k.col_dq; c.M = 1; c.N = D; c.ldx = D; c.out_sum = m->G(m->covar_dec.b);
@@ -1592,9 +1678,9 @@ vmf_forward_backward(const step_t &s)
         m->pending_colsum.push_back(c2);
     }
 
-    MMV_TRY(decoder_backward(s));
+    MMV_TRY(decoder_backward(s, &dl_sums));
     MMV_TRY(encoder_backward(s, true));
-    MMV_TRY(flush_colsums(s));   // Delta (first layer's backward reads it) and every bias gradient of the pass
+    MMV_TRY(flush_colsums(s, true));   // Delta (first layer's backward reads it) and every bias gradient of the pass
 
     if (!tc_senc) {
         PROF("batch_csc");
