@@ -739,12 +739,17 @@ def run_own(args):
             ent["basis"] = "dense-equivalent flops 2 B D h1 (the densified zeros are multiplied too)"
             ent["hbm_contract_bytes"] = k1c[name]
             ent["frac_hbm_contract"] = round(k1c[name] / (per * 1e-3) / 1e9 / pk["hbm"], 4)
-        if name in ("colsum_dlogits", "colsum", "panel_aux_bwd"):
+        if name in ("colsum_dlogits", "colsum", "panel_aux_bwd") and os.environ.get("MMV_SIDE", "1") != "0":
             # launched on the library's lowest-priority side stream next to the step's chain (model.cu: side_fork): the time
-            # is the group's own span while it shares the SMs, not time added to the step; gemm_other is half and half
+            # is the group's span from eligible to done while the chain's kernels have the SMs first — not time added to
+            # the step, and not a basis for a roofline fraction
             ent["stream"] = "side"
+            for key in ("frac", "achieved", "unit", "bound"):
+                ent.pop(key, None)
+        elif name == "gemm_other" and os.environ.get("MMV_SIDE", "1") != "0":
+            ent["stream"] = "step (forward, data gradients) + side (hidden layers' weight gradients: spans as above)"
         kernels[name] = ent
-    dom = max((n for n in kernels if "frac" in kernels[n]), key=lambda n: kernels[n]["share"])
+    dom = max((n for n in kernels if "frac" in kernels[n] and "stream" not in kernels[n]), key=lambda n: kernels[n]["share"])
     traffic, traffic_src = measured_traffic(dom)
     roof = {"kernel": dom, "bound": kernels[dom]["bound"], "achieved": kernels[dom]["achieved"],
             "peak": pk["hbm"] if kernels[dom]["bound"] == "hbm" else pk["tc_sustained"],
