@@ -14,7 +14,7 @@ sys.path.insert(0, ROOT)
 import bench  # noqa: E402  (src_sha, KERNEL_SOURCES)
 
 PATTERNS = {"nb_likelihood": "nb_likelihood_fast_kernel", "vmf_likelihood": "vmf_likelihood_fast_kernel",
-            "senc_fwd": "senc_tc_kernel<256, 0>", "senc_bwd": "senc_tc_kernel<256, 1>", "panel_build": "panel_build_kernel",
+            "senc_fwd": "senc_tc_kernel<256, 0,", "senc_bwd": "senc_tc_kernel<256, 1,", "panel_build": "panel_build_kernel",
             "gemm_dec_last_fwd": "gemm_tc_persist_kernel<0, 0>", "gemm_dec_last_dw": "gemm_tc_persist_kernel<1, 1>",
             "clip_adam": "adam_kernel"}
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}

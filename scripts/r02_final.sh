@@ -9,13 +9,10 @@ O=gpurun_out; mkdir -p $O
 ( time timeout 400 python bench.py --impl reference --steps 3 --warmup 1 ) > $O/${TAG}_bench_reference.log 2>&1; tail -c 400 $O/${TAG}_bench_reference.log
 ( timeout 400 python bench.py --model vmf --steps 50 --warmup 5 --no-cpu-baseline ) > $O/${TAG}_bench_vmf.log 2>&1; tail -c 300 $O/${TAG}_bench_vmf.log
 ( timeout 400 python bench.py --config 5 --steps 30 --warmup 5 --cells 262144 --no-cpu-baseline ) > $O/${TAG}_bench_cfg5.log 2>&1; tail -c 300 $O/${TAG}_bench_cfg5.log
-( timeout 400 python bench.py --config 3 --steps 30 --warmup 5 --no-cpu-baseline ) > $O/${TAG}_bench_cfg3.log 2>&1; tail -c 300 $O/${TAG}_bench_cfg3.log
 timeout 300 python bench.py --cells 16384 --steps 3 --warmup 3 --no-cpu-baseline > $O/${TAG}_bench_plain.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $O/${TAG}_ncu_launches.csv \
     python bench.py --cells 16384 --steps 3 --warmup 3 --no-cpu-baseline > $O/${TAG}_ncu_launches.log 2>&1
 timeout 900 ncu --set full --import-source on --clock-control none -k regex:"nb_likelihood_fast|senc_tc_kernel|panel_build|panel_aux|senc_row_pass|gemm_tc_persist|adam_kernel" -s 16 -c 10 -f -o $O/${TAG}_full \
     python bench.py --cells 16384 --steps 3 --warmup 3 --no-cpu-baseline > $O/${TAG}_ncu_full.log 2>&1
 tail -2 $O/${TAG}_ncu_full.log
-timeout 600 ncu --set full --import-source on --clock-control none -k regex:"vmf_likelihood_fast" -s 4 -c 1 -f -o $O/${TAG}_vmf_full \
-    python bench.py --model vmf --cells 16384 --steps 3 --warmup 3 --no-cpu-baseline > $O/${TAG}_ncu_vmf.log 2>&1
 ls -la $O | grep ${TAG}
