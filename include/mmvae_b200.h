@@ -126,6 +126,14 @@ MMV_API int mmv_model_destroy(mmv_model *m);
  *   "comm_bf16" (1): data-parallel runs in bf16 mode ("dtype" 1) send the two D x h weight gradients over
  *        NVLink as bf16 (per-rank partial sums rounded once, summed by ncclAllReduce(bf16)); 0 or fp32 mode:
  *        every gradient is reduced in fp32.  No reference counterpart (the reference is single device).
+ *   "side_stream" (1; the environment's MMV_SIDE overrides the default): work of a backward pass that only the
+ *        optimiser reads (per-gene sums of dlogits, the hidden layers' weight-gradient GEMMs, bias-gradient column
+ *        sums, dW_nu / dw_depth) and the first layer's effective bias run on a second, lowest-priority stream of
+ *        the context next to the step's dependency chain; mmv_step joins it before the optimiser and before it
+ *        returns, so nothing is in flight behind the caller's back.  0 = everything on the context's one stream.
+ *        Same results either way (the sums that cross streams are atomic adds into distinct gradient tensors).
+ *   "nb_fast" (1), "profile" (0): the tuned K4 / K5 kernels when eligible; per-kernel-group CUDA-event times
+ *        (mmv_profile_read).
  *   "vmf_latent" (0): vmf models only, z_dim >= 3.  NOT in the reference (its vmf_vae reparameterises a
  *        Gaussian, vmf.hh:394-404, and uses kl_loss_normal, vmf.hh:410-414); this is the latent the north star
  *        names.  1 = the stacked head is read as a von Mises-Fisher posterior instead: mean direction

@@ -158,6 +158,10 @@ def test_streamed_minibatch_is_bit_identical_to_resident(mmv, ctx, model):
     res = []
     for streamed in (False, True):
         m, neps = make_model(mmv, ctx, model, D, [96], [80], 8, "bf16", np.random.default_rng(3))
+        # one stream: with the side stream the effective bias is summed next to the panel build, the order of its float
+        # atomics varies from run to run, and bf16 rounding of the B x D gradient turns that 1e-7 into 1e-5 ... 1e-4 on
+        # everything downstream (tests/test_zy_side_stream.py) — this test is about the indexing, which is exact
+        m.set_option("side_stream", 0)
         eps = [np.random.default_rng(10 + i).normal(size=(B, n)).astype(np.float32) for i, n in enumerate(neps)]
         if streamed:
             ip, ix, v = mmv.dense_to_csr(x[cells])
