@@ -1848,7 +1848,6 @@ mmv_step(mmv_model *m, mmv_csr *csr, const int64_t *cells, int64_t B, const int6
         if (csr->ev_ready) MMV_CUDA(cudaStreamWaitEvent(st, csr->ev_ready, 0));   // streamed slot: its upload is done
         m->last_B = B;
         m->bf_cache.clear();
-    m->lo_cache.clear();
         m->lo_cache.clear();
         if (m->use_tc && m->bf16_dirty) {
             MMV_TRY(refresh_mirrors(m, st));
