@@ -402,6 +402,43 @@ def k1_contract_bytes(w, B, bf16=True):
             "senc_bwd": 8 * nnz + 4.0 * B * (h1 + H + 1) + 4.0 * D * h1 + e * D * h1 + 16.0 * D}
 
 
+def summarise_kernels(prof, n_prof, ms_prof, work, k1c, pk, bf16, side_on):
+    """The `kernels` object of the JSON line from the profiled pass ({group: (total ms, event pairs)} over n_prof steps
+    that took ms_prof) and the group the `roofline` object is quoted on: the one with the largest share of the step
+    among those that run on the step's own stream and have a work model."""
+    kernels = {}
+    for name, (t, c) in prof.items():
+        # `amount` is the group's work per STEP: divide by the group's time per step (a group may launch several
+        # kernels per step: the 15 small GEMMs of gemm_other were judged on ONE launch's time until round 2)
+        per = t / n_prof
+        ent = {"ms_per_launch_group": round(t / c, 4), "launches_per_step": round(c / n_prof, 2), "ms_per_step": round(per, 4),
+               "share": round(t / ms_prof, 4)}
+        if name in work:
+            bound, amount = work[name]
+            if bound == "hbm":
+                ent.update(bound="hbm", achieved=round(amount / (per * 1e-3) / 1e9, 1), unit="GB/s")
+                ent["frac"] = round(ent["achieved"] / pk["hbm"], 4)
+            else:
+                ent.update(bound="tensor", achieved=round(amount / (per * 1e-3) / 1e12, 2), unit="TFLOP/s")
+                ent["frac"] = round(ent["achieved"] / pk["tc_sustained"], 4)
+        if name in k1c and bf16:   # K1: the dense-equivalent tensor figure AND SURVEY 8d's contract bytes
+            ent["basis"] = "dense-equivalent flops 2 B D h1 (the densified zeros are multiplied too)"
+            ent["hbm_contract_bytes"] = k1c[name]
+            ent["frac_hbm_contract"] = round(k1c[name] / (per * 1e-3) / 1e9 / pk["hbm"], 4)
+        if name in ("colsum_dlogits", "colsum", "panel_aux_bwd") and side_on:
+            # launched on the library's lowest-priority side stream next to the step's chain (model.cu: side_fork): the time
+            # is the group's span from eligible to done while the chain's kernels have the SMs first — not time added to
+            # the step, and not a basis for a roofline fraction
+            ent["stream"] = "side"
+            for key in ("frac", "achieved", "unit", "bound"):
+                ent.pop(key, None)
+        elif name == "gemm_other" and side_on:
+            ent["stream"] = "step (forward, data gradients) + side (hidden layers' weight gradients: spans as above)"
+        kernels[name] = ent
+    dom = max((n for n in kernels if "frac" in kernels[n] and "stream" not in kernels[n]), key=lambda n: kernels[n]["share"])
+    return kernels, dom
+
+
 def src_sha(*names):
     """sha1 over kernel source files: profiles/traffic.json entries carry the hash of the source they were captured on,
     and a stale entry (the kernel changed since the ncu capture) is dropped instead of being reported."""
@@ -720,36 +757,8 @@ def run_own(args):
     pk = peaks()
     work = kernel_work(w, B, args.dtype == "bf16", world)
     k1c = k1_contract_bytes(w, B, args.dtype == "bf16")
-    kernels = {}
-    for name, (t, c) in prof.items():
-        # `amount` is the group's work per STEP: divide by the group's time per step (a group may launch several
-        # kernels per step: the 15 small GEMMs of gemm_other were judged on ONE launch's time until round 2)
-        per = t / n_prof
-        ent = {"ms_per_launch_group": round(t / c, 4), "launches_per_step": round(c / n_prof, 2), "ms_per_step": round(per, 4),
-               "share": round(t / ms_prof, 4)}
-        if name in work:
-            bound, amount = work[name]
-            if bound == "hbm":
-                ent.update(bound="hbm", achieved=round(amount / (per * 1e-3) / 1e9, 1), unit="GB/s")
-                ent["frac"] = round(ent["achieved"] / pk["hbm"], 4)
-            else:
-                ent.update(bound="tensor", achieved=round(amount / (per * 1e-3) / 1e12, 2), unit="TFLOP/s")
-                ent["frac"] = round(ent["achieved"] / pk["tc_sustained"], 4)
-        if name in k1c and args.dtype == "bf16":   # K1: the dense-equivalent tensor figure AND SURVEY 8d's contract bytes
-            ent["basis"] = "dense-equivalent flops 2 B D h1 (the densified zeros are multiplied too)"
-            ent["hbm_contract_bytes"] = k1c[name]
-            ent["frac_hbm_contract"] = round(k1c[name] / (per * 1e-3) / 1e9 / pk["hbm"], 4)
-        if name in ("colsum_dlogits", "colsum", "panel_aux_bwd") and os.environ.get("MMV_SIDE", "1") != "0":
-            # launched on the library's lowest-priority side stream next to the step's chain (model.cu: side_fork): the time
-            # is the group's span from eligible to done while the chain's kernels have the SMs first — not time added to
-            # the step, and not a basis for a roofline fraction
-            ent["stream"] = "side"
-            for key in ("frac", "achieved", "unit", "bound"):
-                ent.pop(key, None)
-        elif name == "gemm_other" and os.environ.get("MMV_SIDE", "1") != "0":
-            ent["stream"] = "step (forward, data gradients) + side (hidden layers' weight gradients: spans as above)"
-        kernels[name] = ent
-    dom = max((n for n in kernels if "frac" in kernels[n] and "stream" not in kernels[n]), key=lambda n: kernels[n]["share"])
+    kernels, dom = summarise_kernels(prof, n_prof, ms_prof, work, k1c, pk, args.dtype == "bf16",
+                                     os.environ.get("MMV_SIDE", "1") != "0")
     traffic, traffic_src = measured_traffic(dom)
     roof = {"kernel": dom, "bound": kernels[dom]["bound"], "achieved": kernels[dom]["achieved"],
             "peak": pk["hbm"] if kernels[dom]["bound"] == "hbm" else pk["tc_sustained"],
